@@ -1,0 +1,102 @@
+// Shared device helpers for the MAESTRO-B200 kernels (sm_100a only).
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#define MB_DTYPE_F32 0
+#define MB_DTYPE_BF16 1
+
+#define MB_CHECK_LAUNCH()                                  \
+  do {                                                     \
+    cudaError_t e__ = cudaGetLastError();                  \
+    if (e__ != cudaSuccess) return static_cast<int>(e__);  \
+  } while (0)
+
+typedef __nv_bfloat16 bf16;
+
+static inline int mb_ceil_div(long long a, long long b) { return static_cast<int>((a + b - 1) / b); }
+
+// ---------------------------------------------------------------- vector access
+// VecIO<T>: 16-byte global access -> float registers (8 bf16 or 4 fp32 per access).
+template <typename T> struct VecIO;
+
+template <> struct VecIO<float> {
+  static constexpr int N = 4;
+  __device__ __forceinline__ static void load(const float* p, float* v) {
+    float4 t = *reinterpret_cast<const float4*>(p);
+    v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+  }
+  __device__ __forceinline__ static void store(float* p, const float* v) {
+    *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+  }
+};
+
+template <> struct VecIO<bf16> {
+  static constexpr int N = 8;
+  __device__ __forceinline__ static void load(const bf16* p, float* v) {
+    uint4 t = *reinterpret_cast<const uint4*>(p);
+    const uint32_t w[4] = {t.x, t.y, t.z, t.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      v[2 * i] = __uint_as_float(w[i] << 16);
+      v[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
+    }
+  }
+  __device__ __forceinline__ static void store(bf16* p, const float* v) {
+    uint32_t w[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      __nv_bfloat162 h = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+      w[i] = *reinterpret_cast<uint32_t*>(&h);
+    }
+    *reinterpret_cast<uint4*>(p) = make_uint4(w[0], w[1], w[2], w[3]);
+  }
+};
+
+__device__ __forceinline__ float to_f32(float x) { return x; }
+__device__ __forceinline__ float to_f32(bf16 x) { return __bfloat162float(x); }
+template <typename T> __device__ __forceinline__ T from_f32(float x);
+template <> __device__ __forceinline__ float from_f32<float>(float x) { return x; }
+template <> __device__ __forceinline__ bf16 from_f32<bf16>(float x) { return __float2bfloat16_rn(x); }
+
+// ---------------------------------------------------------------- reductions
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// ---------------------------------------------------------------- math
+__device__ __forceinline__ float gelu_erf(float x) {
+  return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f));
+}
+__device__ __forceinline__ float gelu_erf_grad(float x) {
+  const float cdf = 0.5f * (1.0f + erff(x * 0.70710678118654752440f));
+  const float pdf = 0.39894228040143267794f * __expf(-0.5f * x * x);
+  return cdf + x * pdf;
+}
+
+// Date-encoding channel value: channels [dim-8, dim) of a token are
+// [diff, diff, diff, diff, sin_doy, cos_doy, sin_hour, cos_hour] * fac  (reference
+// maestro/layers/utils.py:128-173); feat = [diff, sin_doy, cos_doy, sin_hour, cos_hour].
+__device__ __forceinline__ float date_channel(const float* feat5, int k /*0..date_dim-1*/, int date_dim, float fac) {
+  const int lead = date_dim - 4;
+  const float v = (k < lead) ? feat5[0] : feat5[1 + (k - lead)];
+  return v * fac;
+}
+
+#define MB_DISPATCH_DTYPE(dtype, T, ...)                   \
+  if ((dtype) == MB_DTYPE_F32) { typedef float T; __VA_ARGS__; } \
+  else if ((dtype) == MB_DTYPE_BF16) { typedef bf16 T; __VA_ARGS__; } \
+  else { return -1; }

@@ -1,0 +1,241 @@
+// Bandwidth-bound data-movement kernels of the MAESTRO pretraining step:
+//   weight casts (fp32 master -> bf16 shadow, plain and transposed), input resize /
+//   elevation rescale (reference maestro/ssl/mim.py:425-437), patch extraction for the
+//   strided patch-embed convolution (layers/embed.py:57-60), date features
+//   (layers/utils.py:128-173), prediction rows -> image (layers/embed.py:148-160).
+#include "common.cuh"
+
+// ------------------------------------------------------------------ casts
+__global__ void cast_f32_bf16_kernel(const float* __restrict__ src, bf16* __restrict__ dst, size_t n) {
+  size_t i = (static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x) * 8;
+  const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x * 8;
+  for (; i + 8 <= n; i += stride) {
+    float v[8];
+    VecIO<float>::load(src + i, v);
+    VecIO<float>::load(src + i + 4, v + 4);
+    VecIO<bf16>::store(dst + i, v);
+  }
+  if (i < n) {
+    for (size_t j = i; j < n && j < i + 8; ++j) dst[j] = __float2bfloat16_rn(src[j]);
+  }
+}
+
+extern "C" int mb_cast_f32_to_bf16(const float* src, void* dst, size_t n, void* stream) {
+  if (n == 0) return 0;
+  const int threads = 256;
+  long long blocks = (static_cast<long long>(n) / 8 + threads - 1) / threads;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  if (blocks < 1) blocks = 1;
+  cast_f32_bf16_kernel<<<static_cast<int>(blocks), threads, 0, static_cast<cudaStream_t>(stream)>>>(
+      src, static_cast<bf16*>(dst), n);
+  MB_CHECK_LAUNCH();
+  return 0;
+}
+
+// dst[c, r] = bf16(src[r, c]); src is [R, C] row-major fp32, dst is [C, R] row-major.
+__global__ void cast_transpose_kernel(const float* __restrict__ src, bf16* __restrict__ dst, int R, int C) {
+  __shared__ float tile[32][33];
+  const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int r = r0 + i, c = c0 + threadIdx.x;
+    tile[i][threadIdx.x] = (r < R && c < C) ? src[static_cast<size_t>(r) * C + c] : 0.f;
+  }
+  __syncthreads();
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int c = c0 + i, r = r0 + threadIdx.x;
+    if (c < C && r < R) dst[static_cast<size_t>(c) * R + r] = __float2bfloat16_rn(tile[threadIdx.x][i]);
+  }
+}
+
+extern "C" int mb_cast_transpose_f32_to_bf16(const float* src, void* dst, int R, int C, void* stream) {
+  if (R == 0 || C == 0) return 0;
+  dim3 grid(mb_ceil_div(C, 32), mb_ceil_div(R, 32)), block(32, 8);
+  cast_transpose_kernel<<<grid, block, 0, static_cast<cudaStream_t>(stream)>>>(src, static_cast<bf16*>(dst), R, C);
+  MB_CHECK_LAUNCH();
+  return 0;
+}
+
+// ------------------------------------------------------------------ resize / rescale
+// Nearest-neighbour resize as torch F.interpolate(mode="nearest"): src = min(floor(dst * in/out), in-1)
+// with the scale held in fp32.  Optionally applies the elevation rescale in the same pass:
+// ch>=1 of a rescale_elev modality becomes 30 * (ch0 - ch).
+__global__ void resize_nearest_kernel(const float* __restrict__ src, float* __restrict__ dst, int n_img, int C,
+                                      int hin, int win, int hout, int wout, int rescale_elev) {
+  const size_t total = static_cast<size_t>(n_img) * C * hout * wout;
+  const float sh = static_cast<float>(hin) / static_cast<float>(hout);
+  const float sw = static_cast<float>(win) / static_cast<float>(wout);
+  for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const int x = static_cast<int>(i % wout);
+    size_t t = i / wout;
+    const int y = static_cast<int>(t % hout);
+    t /= hout;
+    const int c = static_cast<int>(t % C);
+    const size_t img = t / C;
+    const int sy = min(static_cast<int>(floorf(y * sh)), hin - 1);
+    const int sx = min(static_cast<int>(floorf(x * sw)), win - 1);
+    const float* base = src + img * C * hin * win;
+    float v = base[(static_cast<size_t>(c) * hin + sy) * win + sx];
+    if (rescale_elev && c >= 1) {
+      const float v0 = base[static_cast<size_t>(sy) * win + sx];
+      v = 30.f * (v0 - v);
+    }
+    dst[i] = v;
+  }
+}
+
+extern "C" int mb_resize_nearest(const float* src, float* dst, int n_img, int C, int hin, int win, int hout,
+                                 int wout, int rescale_elev, void* stream) {
+  const size_t total = static_cast<size_t>(n_img) * C * hout * wout;
+  if (total == 0) return 0;
+  long long blocks = (static_cast<long long>(total) + 255) / 256;
+  if (blocks > 148 * 32) blocks = 148 * 32;
+  resize_nearest_kernel<<<static_cast<int>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      src, dst, n_img, C, hin, win, hout, wout, rescale_elev);
+  MB_CHECK_LAUNCH();
+  return 0;
+}
+
+// ------------------------------------------------------------------ patch extraction
+// img [n_img, C, S, S] fp32 -> cols [n_img * g * g, Kpad] (T), column k = (c - c0) * p * p + py * p + px
+// (the flattening of Conv2d weight [E, c, p, p]); columns [K, Kpad) are zero filled.
+template <typename T>
+__global__ void im2col_kernel(const float* __restrict__ img, T* __restrict__ cols, int n_img, int C, int c0, int c,
+                              int S, int p, int Kpad) {
+  const int g = S / p;
+  const int K = c * p * p;
+  const size_t total = static_cast<size_t>(n_img) * g * g * Kpad;
+  for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const int k = static_cast<int>(i % Kpad);
+    float v = 0.f;
+    if (k < K) {
+      size_t row = i / Kpad;
+      const int gx = static_cast<int>(row % g);
+      row /= g;
+      const int gy = static_cast<int>(row % g);
+      const size_t im = row / g;
+      const int px = k % p;
+      const int py = (k / p) % p;
+      const int cc = k / (p * p);
+      v = img[((im * C + c0 + cc) * S + gy * p + py) * S + gx * p + px];
+    }
+    cols[i] = from_f32<T>(v);
+  }
+}
+
+extern "C" int mb_im2col(const float* img, void* cols, int dtype, int n_img, int C, int c0, int c, int S, int p,
+                         int Kpad, void* stream) {
+  const int g = S / p;
+  const size_t total = static_cast<size_t>(n_img) * g * g * Kpad;
+  if (total == 0) return 0;
+  long long blocks = (static_cast<long long>(total) + 255) / 256;
+  if (blocks > 148 * 32) blocks = 148 * 32;
+  MB_DISPATCH_DTYPE(dtype, T,
+                    (im2col_kernel<T><<<static_cast<int>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+                        img, static_cast<T*>(cols), n_img, C, c0, c, S, p, Kpad)));
+  MB_CHECK_LAUNCH();
+  return 0;
+}
+
+// ------------------------------------------------------------------ prediction rows -> image
+// rows [n_img * g * g, c * p * p] (T) with column order (py, px, cc) -> img [n_img, C, S, S] fp32 channels
+// [c0, c0 + c)   (PixelifyBands rearrange, layers/embed.py:155-160).  dir = 0: rows -> img; dir = 1: img -> rows
+// (the adjoint, used for the gradient of an image-layout loss).
+template <typename T>
+__global__ void rows_image_kernel(T* __restrict__ rows, float* __restrict__ img, int n_img, int C, int c0, int c,
+                                  int S, int p, int dir) {
+  const int g = S / p;
+  const int K = c * p * p;
+  const size_t total = static_cast<size_t>(n_img) * g * g * K;
+  for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    // iterate in image order for coalesced image access
+    const int x = static_cast<int>(i % S);
+    size_t t = i / S;
+    const int y = static_cast<int>(t % S);
+    t /= S;
+    const int cc = static_cast<int>(t % c);
+    const size_t im = t / c;
+    const int gx = x / p, px = x % p, gy = y / p, py = y % p;
+    const size_t r = (im * g + gy) * g + gx;
+    const size_t ri = r * K + (static_cast<size_t>(py) * p + px) * c + cc;
+    const size_t ii = ((im * C + c0 + cc) * S + y) * S + x;
+    if (dir == 0) img[ii] = to_f32(rows[ri]);
+    else rows[ri] = from_f32<T>(img[ii]);
+  }
+}
+
+extern "C" int mb_rows_image(void* rows, int dtype, float* img, int n_img, int C, int c0, int c, int S, int p,
+                             int dir, void* stream) {
+  const size_t total = static_cast<size_t>(n_img) * S * S * c;
+  if (total == 0) return 0;
+  long long blocks = (static_cast<long long>(total) + 255) / 256;
+  if (blocks > 148 * 32) blocks = 148 * 32;
+  MB_DISPATCH_DTYPE(dtype, T,
+                    (rows_image_kernel<T><<<static_cast<int>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+                        static_cast<T*>(rows), img, n_img, C, c0, c, S, p, dir)));
+  MB_CHECK_LAUNCH();
+  return 0;
+}
+
+// ------------------------------------------------------------------ date features
+// dates int16 [B, D, 3] (year, day-of-year, hour), ref int16 [B, 1, 3] -> feat fp32 [B, D, 5] =
+// (diff, sin doy, cos doy, sin hour, cos hour) with the reference's fp32 operation order.
+__global__ void date_features_kernel(const short* __restrict__ dates, const short* __restrict__ ref,
+                                     float* __restrict__ feat, int B, int D) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B * D) return;
+  const int b = i / D;
+  const float year = static_cast<float>(dates[i * 3 + 0]);
+  float doy = __fdiv_rn(static_cast<float>(dates[i * 3 + 1]), 365.25f);
+  float hour = __fdiv_rn(static_cast<float>(dates[i * 3 + 2]), 24.0f);
+  const float ry = static_cast<float>(ref[b * 3 + 0]);
+  const float rd = __fdiv_rn(static_cast<float>(ref[b * 3 + 1]), 365.25f);
+  const float diff = __fsub_rn(__fadd_rn(year, doy), __fadd_rn(ry, rd));
+  const float two_pi = 6.283185307179586f;
+  doy = __fmul_rn(two_pi, doy);
+  hour = __fmul_rn(two_pi, hour);
+  feat[i * 5 + 0] = diff;
+  feat[i * 5 + 1] = sinf(doy);
+  feat[i * 5 + 2] = cosf(doy);
+  feat[i * 5 + 3] = sinf(hour);
+  feat[i * 5 + 4] = cosf(hour);
+}
+
+extern "C" int mb_date_features(const short* dates, const short* ref, float* feat, int B, int D, void* stream) {
+  if (B * D == 0) return 0;
+  date_features_kernel<<<mb_ceil_div(B * D, 128), 128, 0, static_cast<cudaStream_t>(stream)>>>(dates, ref, feat, B, D);
+  MB_CHECK_LAUNCH();
+  return 0;
+}
+
+// ------------------------------------------------------------------ column sums (bias gradients)
+// out[n] += sum_m dy[m, n]  (fp32 atomics into a zeroed / accumulating buffer).
+template <typename T>
+__global__ void colsum_kernel(const T* __restrict__ dy, float* __restrict__ out, int M, int N, int rows_per_block) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= N) return;
+  const int m0 = blockIdx.y * rows_per_block;
+  const int m1 = min(M, m0 + rows_per_block);
+  float acc = 0.f;
+  for (int m = m0; m < m1; ++m) acc += to_f32(dy[static_cast<size_t>(m) * N + n]);
+  atomicAdd(out + n, acc);
+}
+
+extern "C" int mb_colsum_accum(const void* dy, int dtype, float* out, int M, int N, void* stream) {
+  if (M == 0 || N == 0) return 0;
+  const int threads = 128;
+  const int bx = mb_ceil_div(N, threads);
+  int by = (148 * 8) / bx;
+  if (by < 1) by = 1;
+  int rows_per_block = mb_ceil_div(M, by);
+  if (rows_per_block < 16) rows_per_block = 16;
+  by = mb_ceil_div(M, rows_per_block);
+  dim3 grid(bx, by);
+  MB_DISPATCH_DTYPE(dtype, T,
+                    (colsum_kernel<T><<<grid, threads, 0, static_cast<cudaStream_t>(stream)>>>(
+                        static_cast<const T*>(dy), out, M, N, rows_per_block)));
+  MB_CHECK_LAUNCH();
+  return 0;
+}

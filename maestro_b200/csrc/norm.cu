@@ -1,0 +1,422 @@
+// Normalisation kernels (bandwidth-bound; warp-shuffle reductions, 128-bit access):
+//   * LayerNorm forward / backward with fused residual-gradient add and row remapping (the remap folds the
+//     reference's torch.cat / split around encoder_inter, maestro/ssl/mim.py:406-423, into the LN pass);
+//   * GroupNorm(1, E) of the patch embedding (maestro/layers/embed.py:55,61): statistics over all E*g*g
+//     values of one (b, d) image, apply fused with the positional + date encoding add
+//     (maestro/ssl/mim.py:232-252) and the group concat (layers/utils.py:12-47).
+#include "common.cuh"
+
+struct RowMap {
+  int n;    // logical rows per sample
+  int bs;   // physical rows per sample
+  int off;  // physical row offset inside a sample
+  __device__ __forceinline__ size_t phys(int r) const { return static_cast<size_t>(r / n) * bs + off + (r % n); }
+};
+
+constexpr int LN_MAX_ELEMS = 32;  // per lane -> d <= 1024
+
+// ------------------------------------------------------------------ LayerNorm forward
+template <typename T>
+__global__ void __launch_bounds__(256) layernorm_fwd_kernel(const T* __restrict__ x, const float* __restrict__ gamma,
+                                                            const float* __restrict__ beta, T* __restrict__ y,
+                                                            float* __restrict__ mean_out, float* __restrict__ rstd_out,
+                                                            int rows, int d, float eps, RowMap in_map, RowMap out_map) {
+  constexpr int V = VecIO<T>::N;
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (warp >= rows) return;
+  const int nvec = d / V;
+  const T* xr = x + in_map.phys(warp) * d;
+  float v[LN_MAX_ELEMS];
+  float s = 0.f;
+#pragma unroll
+  for (int c = 0; c < LN_MAX_ELEMS / V; ++c) {
+    const int idx = lane + c * 32;
+    if (idx < nvec) {
+      VecIO<T>::load(xr + idx * V, v + c * V);
+#pragma unroll
+      for (int j = 0; j < V; ++j) s += v[c * V + j];
+    }
+  }
+  const float mean = warp_sum(s) / d;
+  float ss = 0.f;
+#pragma unroll
+  for (int c = 0; c < LN_MAX_ELEMS / V; ++c) {
+    if (lane + c * 32 < nvec) {
+#pragma unroll
+      for (int j = 0; j < V; ++j) {
+        const float t = v[c * V + j] - mean;
+        ss += t * t;
+      }
+    }
+  }
+  const float rstd = rsqrtf(warp_sum(ss) / d + eps);
+  if (lane == 0 && mean_out != nullptr) {
+    mean_out[warp] = mean;
+    rstd_out[warp] = rstd;
+  }
+  T* yr = y + out_map.phys(warp) * d;
+#pragma unroll
+  for (int c = 0; c < LN_MAX_ELEMS / V; ++c) {
+    const int idx = lane + c * 32;
+    if (idx < nvec) {
+      float o[V];
+#pragma unroll
+      for (int j = 0; j < V; ++j) {
+        const int col = idx * V + j;
+        o[j] = (v[c * V + j] - mean) * rstd * gamma[col] + beta[col];
+      }
+      VecIO<T>::store(yr + idx * V, o);
+    }
+  }
+}
+
+extern "C" int mb_layernorm_fwd(const void* x, const float* gamma, const float* beta, void* y, float* mean,
+                                float* rstd, int dtype, int rows, int d, float eps, int in_n, int in_bs, int in_off,
+                                int out_n, int out_bs, int out_off, void* stream) {
+  if (rows == 0) return 0;
+  if (d > 1024 || d % 8 != 0) return -2;
+  RowMap im{in_n, in_bs, in_off}, om{out_n, out_bs, out_off};
+  const int threads = 256;
+  const int blocks = mb_ceil_div(static_cast<long long>(rows) * 32, threads);
+  MB_DISPATCH_DTYPE(dtype, T,
+                    (layernorm_fwd_kernel<T><<<blocks, threads, 0, static_cast<cudaStream_t>(stream)>>>(
+                        static_cast<const T*>(x), gamma, beta, static_cast<T*>(y), mean, rstd, rows, d, eps, im, om)));
+  MB_CHECK_LAUNCH();
+  return 0;
+}
+
+// ------------------------------------------------------------------ LayerNorm backward
+// dx = rstd * (g - mean(g) - xhat * mean(g * xhat)) [+ dres],  g = dy * gamma.
+// dgamma += sum_rows dy * xhat, dbeta += sum_rows dy (fp32 atomics, one per column per CTA).
+// x / dx / dres rows use in_map, dy rows use out_map (mirrors the forward).
+template <typename T>
+__global__ void __launch_bounds__(256) layernorm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x,
+                                                            const float* __restrict__ mean_in,
+                                                            const float* __restrict__ rstd_in,
+                                                            const float* __restrict__ gamma, const T* __restrict__ dres,
+                                                            T* __restrict__ dx, float* __restrict__ dgamma,
+                                                            float* __restrict__ dbeta, int rows, int d,
+                                                            int rows_per_warp, RowMap in_map, RowMap out_map) {
+  constexpr int V = VecIO<T>::N;
+  extern __shared__ float sm[];  // [2][d] partial dgamma / dbeta of this CTA
+  const int lane = threadIdx.x & 31;
+  const int warp_in_block = threadIdx.x >> 5;
+  const int nwarps = blockDim.x >> 5;
+  const int gwarp = blockIdx.x * nwarps + warp_in_block;
+  const int nvec = d / V;
+  for (int i = threadIdx.x; i < 2 * d; i += blockDim.x) sm[i] = 0.f;
+  __syncthreads();
+
+  float ag[LN_MAX_ELEMS], ab[LN_MAX_ELEMS];
+#pragma unroll
+  for (int i = 0; i < LN_MAX_ELEMS; ++i) { ag[i] = 0.f; ab[i] = 0.f; }
+
+  const int r0 = gwarp * rows_per_warp;
+  const int r1 = min(rows, r0 + rows_per_warp);
+  for (int r = r0; r < r1; ++r) {
+    const size_t pin = in_map.phys(r), pout = out_map.phys(r);
+    const float mean = mean_in[r], rstd = rstd_in[r];
+    float xh[LN_MAX_ELEMS], g[LN_MAX_ELEMS];
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int c = 0; c < LN_MAX_ELEMS / V; ++c) {
+      const int idx = lane + c * 32;
+      if (idx < nvec) {
+        float xv[V], dv[V];
+        VecIO<T>::load(x + pin * d + idx * V, xv);
+        VecIO<T>::load(dy + pout * d + idx * V, dv);
+#pragma unroll
+        for (int j = 0; j < V; ++j) {
+          const float h = (xv[j] - mean) * rstd;
+          const float gg = dv[j] * gamma[idx * V + j];
+          xh[c * V + j] = h;
+          g[c * V + j] = gg;
+          s1 += gg;
+          s2 += gg * h;
+          ag[c * V + j] += dv[j] * h;
+          ab[c * V + j] += dv[j];
+        }
+      }
+    }
+    s1 = warp_sum(s1) / d;
+    s2 = warp_sum(s2) / d;
+#pragma unroll
+    for (int c = 0; c < LN_MAX_ELEMS / V; ++c) {
+      const int idx = lane + c * 32;
+      if (idx < nvec) {
+        float o[V];
+        if (dres != nullptr) VecIO<T>::load(dres + pin * d + idx * V, o);
+        else {
+#pragma unroll
+          for (int j = 0; j < V; ++j) o[j] = 0.f;
+        }
+#pragma unroll
+        for (int j = 0; j < V; ++j) o[j] += rstd * (g[c * V + j] - s1 - xh[c * V + j] * s2);
+        VecIO<T>::store(dx + pin * d + idx * V, o);
+      }
+    }
+  }
+#pragma unroll
+  for (int c = 0; c < LN_MAX_ELEMS / V; ++c) {
+    const int idx = lane + c * 32;
+    if (idx < nvec) {
+#pragma unroll
+      for (int j = 0; j < V; ++j) {
+        atomicAdd(&sm[idx * V + j], ag[c * V + j]);
+        atomicAdd(&sm[d + idx * V + j], ab[c * V + j]);
+      }
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < d; i += blockDim.x) {
+    atomicAdd(dgamma + i, sm[i]);
+    atomicAdd(dbeta + i, sm[d + i]);
+  }
+}
+
+extern "C" int mb_layernorm_bwd(const void* dy, const void* x, const float* mean, const float* rstd,
+                                const float* gamma, const void* dres, void* dx, float* dgamma, float* dbeta,
+                                int dtype, int rows, int d, int in_n, int in_bs, int in_off, int out_n, int out_bs,
+                                int out_off, void* stream) {
+  if (rows == 0) return 0;
+  if (d > 1024 || d % 8 != 0) return -2;
+  RowMap im{in_n, in_bs, in_off}, om{out_n, out_bs, out_off};
+  const int threads = 256, nwarps = threads / 32;
+  // aim for ~4 CTAs per SM; each warp walks a contiguous run of rows
+  int rows_per_warp = mb_ceil_div(rows, 148 * 4 * nwarps);
+  if (rows_per_warp < 1) rows_per_warp = 1;
+  const int blocks = mb_ceil_div(rows, rows_per_warp * nwarps);
+  const size_t smem = 2 * static_cast<size_t>(d) * sizeof(float);
+  MB_DISPATCH_DTYPE(dtype, T,
+                    (layernorm_bwd_kernel<T><<<blocks, threads, smem, static_cast<cudaStream_t>(stream)>>>(
+                        static_cast<const T*>(dy), static_cast<const T*>(x), mean, rstd, gamma,
+                        static_cast<const T*>(dres), static_cast<T*>(dx), dgamma, dbeta, rows, d, rows_per_warp, im,
+                        om)));
+  MB_CHECK_LAUNCH();
+  return 0;
+}
+
+// ------------------------------------------------------------------ GroupNorm(1, E) of the patch embedding
+// Phase 1: per-image sum / sum of squares, split over several CTAs per image (fp64 atomics).
+template <typename T>
+__global__ void __launch_bounds__(256) gn_stats_kernel(const T* __restrict__ y, double* __restrict__ sums,
+                                                       size_t elems_per_img, int splits) {
+  constexpr int V = VecIO<T>::N;
+  const int img = blockIdx.x / splits, part = blockIdx.x % splits;
+  const size_t nvec = elems_per_img / V;
+  const size_t per = (nvec + splits - 1) / splits;
+  const size_t v0 = part * per, v1 = min(nvec, v0 + per);
+  const T* base = y + static_cast<size_t>(img) * elems_per_img;
+  float s = 0.f, ss = 0.f;
+  for (size_t i = v0 + threadIdx.x; i < v1; i += blockDim.x) {
+    float v[V];
+    VecIO<T>::load(base + i * V, v);
+#pragma unroll
+    for (int j = 0; j < V; ++j) { s += v[j]; ss += v[j] * v[j]; }
+  }
+  double ds = warp_sum(static_cast<double>(s)), dss = warp_sum(static_cast<double>(ss));
+  __shared__ double red[2][8];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  if (lane == 0) { red[0][w] = ds; red[1][w] = dss; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double a = 0, b = 0;
+    for (int i = 0; i < (blockDim.x >> 5); ++i) { a += red[0][i]; b += red[1][i]; }
+    atomicAdd(&sums[2 * img], a);
+    atomicAdd(&sums[2 * img + 1], b);
+  }
+}
+
+// sums must be zero on entry ([n_img, 2] doubles).
+extern "C" int mb_gn_stats(const void* y, int dtype, double* sums, int n_img, long long elems_per_img, void* stream) {
+  if (n_img == 0) return 0;
+  if (elems_per_img % 8 != 0) return -2;
+  int splits = (148 * 4) / n_img;
+  if (splits < 1) splits = 1;
+  const long long max_splits = elems_per_img / (8 * 256) + 1;
+  if (splits > max_splits) splits = static_cast<int>(max_splits);
+  MB_DISPATCH_DTYPE(dtype, T,
+                    (gn_stats_kernel<T><<<n_img * splits, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+                        static_cast<const T*>(y), sums, static_cast<size_t>(elems_per_img), splits)));
+  MB_CHECK_LAUNCH();
+  return 0;
+}
+
+// Phase 2: normalise + affine + positional + date encoding, written into the group token buffer.
+//   y      [n_img * L, E]   conv output (image i = b * D + d)
+//   out    [B, out_bs, E]   row = b * out_bs + out_off + d * L + l
+//   pos    [L, E] fp32 (already scaled by fac_abs_enc), feat [B, D, 5] date features.
+template <typename T>
+__global__ void __launch_bounds__(256) gn_apply_kernel(const T* __restrict__ y, const double* __restrict__ sums,
+                                                       const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                       const float* __restrict__ pos, const float* __restrict__ feat,
+                                                       T* __restrict__ out, float* __restrict__ stats_out, int n_img,
+                                                       int D, int L, int E, float eps, int out_bs, int out_off,
+                                                       int date_dim, float fac_date) {
+  constexpr int V = VecIO<T>::N;
+  const int nvec_row = E / V;
+  const size_t total = static_cast<size_t>(n_img) * L * nvec_row;
+  const double inv_n = 1.0 / (static_cast<double>(L) * E);
+  for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const int cv = static_cast<int>(i % nvec_row);
+    const size_t row = i / nvec_row;
+    const int l = static_cast<int>(row % L);
+    const int img = static_cast<int>(row / L);
+    const int b = img / D, d = img % D;
+    const double m = sums[2 * img] * inv_n;
+    const double var = fmax(sums[2 * img + 1] * inv_n - m * m, 0.0);
+    const float mean = static_cast<float>(m);
+    const float rstd = static_cast<float>(1.0 / sqrt(var + static_cast<double>(eps)));
+    if (stats_out != nullptr && l == 0 && cv == 0) {
+      stats_out[2 * img] = mean;
+      stats_out[2 * img + 1] = rstd;
+    }
+    float v[V];
+    VecIO<T>::load(y + row * E + cv * V, v);
+#pragma unroll
+    for (int j = 0; j < V; ++j) {
+      const int e = cv * V + j;
+      float o = (v[j] - mean) * rstd * gamma[e] + beta[e] + pos[static_cast<size_t>(l) * E + e];
+      if (e >= E - date_dim) o += date_channel(feat + (static_cast<size_t>(b) * D + d) * 5, e - (E - date_dim), date_dim, fac_date);
+      v[j] = o;
+    }
+    const size_t orow = static_cast<size_t>(b) * out_bs + out_off + static_cast<size_t>(d) * L + l;
+    VecIO<T>::store(out + orow * E + cv * V, v);
+  }
+}
+
+extern "C" int mb_gn_apply(const void* y, const double* sums, const float* gamma, const float* beta,
+                           const float* pos, const float* feat, void* out, float* stats_out, int dtype, int n_img,
+                           int D, int L, int E, float eps, int out_bs, int out_off, int date_dim, float fac_date,
+                           void* stream) {
+  if (n_img == 0) return 0;
+  if (E % 8 != 0) return -2;
+  const long long total = static_cast<long long>(n_img) * L * (E / 4);
+  long long blocks = (total + 255) / 256;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  MB_DISPATCH_DTYPE(dtype, T,
+                    (gn_apply_kernel<T><<<static_cast<int>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+                        static_cast<const T*>(y), sums, gamma, beta, pos, feat, static_cast<T*>(out), stats_out,
+                        n_img, D, L, E, eps, out_bs, out_off, date_dim, fac_date)));
+  MB_CHECK_LAUNCH();
+  return 0;
+}
+
+// Backward phase 1: per image a = sum(dy * gamma), c = sum(dy * gamma * xhat) (fp64 atomics into sums2 [n_img,2]);
+// per channel dgamma += sum dy * xhat, dbeta += sum dy (fp32 atomics).  dy is read from the group token buffer.
+template <typename T>
+__global__ void __launch_bounds__(256) gn_bwd_reduce_kernel(const T* __restrict__ dy, const T* __restrict__ y,
+                                                            const float* __restrict__ stats,
+                                                            const float* __restrict__ gamma, double* __restrict__ sums2,
+                                                            float* __restrict__ dgamma, float* __restrict__ dbeta,
+                                                            int D, int L, int E, int out_bs, int out_off,
+                                                            int rows_per_block) {
+  // grid: (n_img, ceil(L / rows_per_block)); block: E / V threads (<= 256) each owning V columns
+  constexpr int V = VecIO<T>::N;
+  const int img = blockIdx.x;
+  const int b = img / D, d = img % D;
+  const int l0 = blockIdx.y * rows_per_block, l1 = min(L, l0 + rows_per_block);
+  const float mean = stats[2 * img], rstd = stats[2 * img + 1];
+  const int nvec_row = E / V;
+  float a = 0.f, c = 0.f;
+  for (int cv = threadIdx.x; cv < nvec_row; cv += blockDim.x) {
+    float ag[V], ab[V], gm[V];
+#pragma unroll
+    for (int j = 0; j < V; ++j) { ag[j] = 0.f; ab[j] = 0.f; gm[j] = gamma[cv * V + j]; }
+    for (int l = l0; l < l1; ++l) {
+      const size_t yrow = static_cast<size_t>(img) * L + l;
+      const size_t drow = static_cast<size_t>(b) * out_bs + out_off + static_cast<size_t>(d) * L + l;
+      float yv[V], dv[V];
+      VecIO<T>::load(y + yrow * E + cv * V, yv);
+      VecIO<T>::load(dy + drow * E + cv * V, dv);
+#pragma unroll
+      for (int j = 0; j < V; ++j) {
+        const float h = (yv[j] - mean) * rstd;
+        const float g = dv[j] * gm[j];
+        a += g;
+        c += g * h;
+        ag[j] += dv[j] * h;
+        ab[j] += dv[j];
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < V; ++j) {
+      atomicAdd(dgamma + cv * V + j, ag[j]);
+      atomicAdd(dbeta + cv * V + j, ab[j]);
+    }
+  }
+  double da = warp_sum(static_cast<double>(a)), dc = warp_sum(static_cast<double>(c));
+  __shared__ double red[2][8];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  if (lane == 0) { red[0][w] = da; red[1][w] = dc; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double s0 = 0, s1 = 0;
+    for (int i = 0; i < ((blockDim.x + 31) >> 5); ++i) { s0 += red[0][i]; s1 += red[1][i]; }
+    atomicAdd(&sums2[2 * img], s0);
+    atomicAdd(&sums2[2 * img + 1], s1);
+  }
+}
+
+// Backward phase 2: dconv = rstd * (dy * gamma - a / n - xhat * c / n), rows back in conv order.
+template <typename T>
+__global__ void __launch_bounds__(256) gn_bwd_apply_kernel(const T* __restrict__ dy, const T* __restrict__ y,
+                                                           const float* __restrict__ stats,
+                                                           const float* __restrict__ gamma,
+                                                           const double* __restrict__ sums2, T* __restrict__ dconv,
+                                                           int n_img, int D, int L, int E, int out_bs, int out_off) {
+  constexpr int V = VecIO<T>::N;
+  const int nvec_row = E / V;
+  const size_t total = static_cast<size_t>(n_img) * L * nvec_row;
+  const double inv_n = 1.0 / (static_cast<double>(L) * E);
+  for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const int cv = static_cast<int>(i % nvec_row);
+    const size_t row = i / nvec_row;
+    const int l = static_cast<int>(row % L);
+    const int img = static_cast<int>(row / L);
+    const int b = img / D, d = img % D;
+    const float mean = stats[2 * img], rstd = stats[2 * img + 1];
+    const float ma = static_cast<float>(sums2[2 * img] * inv_n), mc = static_cast<float>(sums2[2 * img + 1] * inv_n);
+    const size_t drow = static_cast<size_t>(b) * out_bs + out_off + static_cast<size_t>(d) * L + l;
+    float yv[V], dv[V];
+    VecIO<T>::load(y + row * E + cv * V, yv);
+    VecIO<T>::load(dy + drow * E + cv * V, dv);
+#pragma unroll
+    for (int j = 0; j < V; ++j) {
+      const float h = (yv[j] - mean) * rstd;
+      dv[j] = rstd * (dv[j] * gamma[cv * V + j] - ma - h * mc);
+    }
+    VecIO<T>::store(dconv + row * E + cv * V, dv);
+  }
+}
+
+// sums2 must be zero on entry.
+extern "C" int mb_gn_bwd(const void* dy, const void* y, const float* stats, const float* gamma, double* sums2,
+                         void* dconv, float* dgamma, float* dbeta, int dtype, int n_img, int D, int L, int E,
+                         int out_bs, int out_off, void* stream) {
+  if (n_img == 0) return 0;
+  if (E % 8 != 0) return -2;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  int row_blocks = (148 * 4) / n_img;
+  if (row_blocks < 1) row_blocks = 1;
+  if (row_blocks > L) row_blocks = L;
+  const int rows_per_block = mb_ceil_div(L, row_blocks);
+  row_blocks = mb_ceil_div(L, rows_per_block);
+  dim3 grid(n_img, row_blocks);
+  const long long total = static_cast<long long>(n_img) * L * (E / 4);
+  long long blocks = (total + 255) / 256;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  MB_DISPATCH_DTYPE(
+      dtype, T,
+      (gn_bwd_reduce_kernel<T><<<grid, 128, 0, st>>>(static_cast<const T*>(dy), static_cast<const T*>(y), stats, gamma,
+                                                     sums2, dgamma, dbeta, D, L, E, out_bs, out_off, rows_per_block),
+       gn_bwd_apply_kernel<T><<<static_cast<int>(blocks), 256, 0, st>>>(static_cast<const T*>(dy),
+                                                                        static_cast<const T*>(y), stats, gamma, sums2,
+                                                                        static_cast<T*>(dconv), n_img, D, L, E, out_bs,
+                                                                        out_off)));
+  MB_CHECK_LAUNCH();
+  return 0;
+}
