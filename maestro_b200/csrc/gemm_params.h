@@ -1,0 +1,24 @@
+// Parameter block shared by the GEMM entry points (mirrored field-for-field in include/maestro_b200.h
+// and in maestro_b200/_lib.py as a ctypes.Structure).
+#pragma once
+
+#define GEMM_GELU 1      // out = gelu(acc + bias); aux <- acc + bias (pre-activation, saved for backward)
+#define GEMM_DGELU 2     // out = acc * gelu'(aux)
+#define GEMM_ACCUM 4     // out += result (fp32 gradient accumulation)
+#define GEMM_OUT_F32 8   // C is fp32 regardless of the activation dtype
+
+struct GemmParams {
+  const void* A;         // A(m, k) = A[m * sam + k * sak]
+  const void* B;         // B(n, k) = B[n * sbn + k * sbk]
+  void* C;               // C[m * ldc + n]
+  const float* bias;     // [N] fp32 or null
+  const void* residual;  // same layout as C (activation dtype) or null
+  void* aux;             // same layout as C (activation dtype) or null
+  int M, N, K;
+  long long sam, sak, sbn, sbk;
+  int ldc;
+  int nb1, nb2;          // batch = nb1 * nb2, z = z1 * nb2 + z2
+  long long a_s1, a_s2, b_s1, b_s2, c_s1, c_s2;
+  float alpha;
+  int flags;
+};

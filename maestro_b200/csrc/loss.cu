@@ -1,0 +1,161 @@
+// Patch-group-wise normalised masked reconstruction loss, forward + gradient in one pass
+// (reference maestro/train/model.py:195-247, norm_bands / loss_fn select :38-67).
+//
+// One warp per patch (b, d, l) of one modality.  The target patch (all C channels) is staged in shared
+// memory, per norm-band-group mean / unbiased variance are reduced with warp shuffles, and the prediction
+// row(s) are streamed once: error accumulated, d(loss)/d(pred) written (zero rows for unmasked patches,
+// whose target is never read).  Algorithmic bytes: masked_fraction * target + pred read + dpred write.
+#include "common.cuh"
+
+constexpr int LOSS_MAX_C = 16;
+constexpr int LOSS_MAX_G = 4;
+
+struct LossParams {
+  const float* target;            // [B*D, C, S, S] fp32 (the resized / rescaled batch)
+  const void* pred[LOSS_MAX_G];   // per band-group rows [B*D*L, c_g*p*p] (T), column order (py, px, cl)
+  void* dpred[LOSS_MAX_G];        // same shape, may be null (forward only)
+  const unsigned char* mask;      // group token mask [B, Lg]
+  const float* coef;              // device scalar: d(loss)/d(err) weight = w_mod / (sum_w * count_mod) * upstream
+  double* accum;                  // [2]: sum of errors over masked elements, number of masked elements
+  int B, D, C, S, p, G;
+  int Lg, mask_off;               // token index = mask_off + (gi * D + d) * L + l
+  int cg[LOSS_MAX_G], c0[LOSS_MAX_G];
+  int n_norm;                     // number of norm groups (0 = no target normalisation)
+  int norm_of_ch[LOSS_MAX_C];     // channel -> norm group
+  int norm_size[LOSS_MAX_C];      // channels per norm group
+  int l2;                         // 0: |.|, 1: (.)^2
+};
+
+template <typename T>
+__global__ void __launch_bounds__(128) group_norm_masked_loss_kernel(LossParams P) {
+  extern __shared__ float smem[];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  const int g = P.S / P.p, L = g * g, pp = P.p * P.p;
+  const int npix = pp * P.C;
+  float* tg = smem + static_cast<size_t>(w) * npix;
+  const long long n_patch = static_cast<long long>(P.B) * P.D * L;
+  float err_sum = 0.f, cnt_sum = 0.f;
+  const float coef = (P.coef != nullptr) ? *P.coef : 0.f;
+
+  for (long long patch = static_cast<long long>(blockIdx.x) * nw + w; patch < n_patch;
+       patch += static_cast<long long>(gridDim.x) * nw) {
+    const int l = static_cast<int>(patch % L);
+    const long long img = patch / L;  // b * D + d
+    const int d = static_cast<int>(img % P.D), b = static_cast<int>(img / P.D);
+    unsigned mbits = 0;
+    for (int gi = 0; gi < P.G; ++gi) {
+      const size_t ti = static_cast<size_t>(b) * P.Lg + P.mask_off + (static_cast<size_t>(gi) * P.D + d) * L + l;
+      if (P.mask[ti]) mbits |= 1u << gi;
+    }
+    if (mbits == 0) {
+      // unmasked patch: gradient rows are zero, nothing else to do
+      for (int gi = 0; gi < P.G; ++gi) {
+        if (P.dpred[gi] == nullptr) continue;
+        T* dp = static_cast<T*>(P.dpred[gi]) + static_cast<size_t>(patch) * P.cg[gi] * pp;
+        for (int e = lane; e < P.cg[gi] * pp; e += 32) dp[e] = from_f32<T>(0.f);
+      }
+      continue;
+    }
+    // stage target patch: global order (ch, py, px) -> smem order (py, px, ch)
+    const int gy = l / g, gx = l % g;
+    const float* tbase = P.target + static_cast<size_t>(img) * P.C * P.S * P.S;
+    for (int i = lane; i < npix; i += 32) {
+      const int px = i % P.p, py = (i / P.p) % P.p, ch = i / pp;
+      tg[(py * P.p + px) * P.C + ch] = tbase[(static_cast<size_t>(ch) * P.S + gy * P.p + py) * P.S + gx * P.p + px];
+    }
+    __syncwarp();
+    // per norm group statistics
+    float mu[LOSS_MAX_C], rs[LOSS_MAX_C];
+    if (P.n_norm > 0) {
+      int ch0 = 0;
+      for (int n = 0; n < P.n_norm; ++n) {
+        const int cn = P.norm_size[n];
+        const int cnt = pp * cn;
+        float s = 0.f;
+        for (int i = lane; i < cnt; i += 32) s += tg[(i / cn) * P.C + ch0 + (i % cn)];
+        const float mean = warp_sum(s) / cnt;
+        float ss = 0.f;
+        for (int i = lane; i < cnt; i += 32) {
+          const float t = tg[(i / cn) * P.C + ch0 + (i % cn)] - mean;
+          ss += t * t;
+        }
+        const float var = warp_sum(ss) / (cnt - 1);
+        mu[n] = mean;
+        rs[n] = sqrtf(var + 1.0e-6f);
+        ch0 += cn;
+      }
+    }
+    // stream prediction rows
+    for (int gi = 0; gi < P.G; ++gi) {
+      const int cgi = P.cg[gi], ne = cgi * pp;
+      const bool masked = (mbits >> gi) & 1u;
+      const T* pr = static_cast<const T*>(P.pred[gi]) + static_cast<size_t>(patch) * ne;
+      T* dp = P.dpred[gi] != nullptr ? static_cast<T*>(P.dpred[gi]) + static_cast<size_t>(patch) * ne : nullptr;
+      if (!masked) {
+        if (dp != nullptr)
+          for (int e = lane; e < ne; e += 32) dp[e] = from_f32<T>(0.f);
+        continue;
+      }
+      for (int e = lane; e < ne; e += 32) {
+        const int cl = e % cgi, pix = e / cgi;
+        const int ch = P.c0[gi] + cl;
+        float t = tg[pix * P.C + ch];
+        if (P.n_norm > 0) {
+          const int n = P.norm_of_ch[ch];
+          float m_ = mu[0], r_ = rs[0];
+#pragma unroll
+          for (int k = 1; k < LOSS_MAX_C; ++k)
+            if (k == n) { m_ = mu[k]; r_ = rs[k]; }
+          t = (t - m_) / r_;
+        }
+        const float diff = t - to_f32(pr[e]);  // reference: loss_fn(target - pred)
+        float gradv;
+        if (P.l2) {
+          err_sum += diff * diff;
+          gradv = -2.f * diff;
+        } else {
+          err_sum += fabsf(diff);
+          gradv = diff > 0.f ? -1.f : (diff < 0.f ? 1.f : 0.f);
+        }
+        if (dp != nullptr) dp[e] = from_f32<T>(gradv * coef);
+      }
+      cnt_sum += static_cast<float>(ne) / 32.f;
+    }
+    __syncwarp();
+  }
+  const double es = warp_sum(static_cast<double>(err_sum));
+  const double cs = warp_sum(static_cast<double>(cnt_sum));
+  if (lane == 0 && (es != 0.0 || cs != 0.0)) {
+    atomicAdd(&P.accum[0], es);
+    atomicAdd(&P.accum[1], cs);
+  }
+}
+
+extern "C" int mb_loss_fwd_bwd(const LossParams* params, int dtype, void* stream) {
+  LossParams P = *params;
+  if (P.C > LOSS_MAX_C || P.G > LOSS_MAX_G || P.n_norm > LOSS_MAX_C) return -2;
+  const int g = P.S / P.p;
+  const long long n_patch = static_cast<long long>(P.B) * P.D * g * g;
+  if (n_patch == 0) return 0;
+  const int nw = 4;
+  const size_t smem = static_cast<size_t>(nw) * P.p * P.p * P.C * sizeof(float);
+  if (smem > 200 * 1024) return -2;
+  long long blocks = (n_patch + nw - 1) / nw;
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (dtype == MB_DTYPE_F32) {
+    if (smem > 48 * 1024)
+      cudaFuncSetAttribute(group_norm_masked_loss_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                           static_cast<int>(smem));
+    group_norm_masked_loss_kernel<float><<<static_cast<int>(blocks), nw * 32, smem, st>>>(P);
+  } else if (dtype == MB_DTYPE_BF16) {
+    if (smem > 48 * 1024)
+      cudaFuncSetAttribute(group_norm_masked_loss_kernel<bf16>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                           static_cast<int>(smem));
+    group_norm_masked_loss_kernel<bf16><<<static_cast<int>(blocks), nw * 32, smem, st>>>(P);
+  } else {
+    return -1;
+  }
+  MB_CHECK_LAUNCH();
+  return 0;
+}
