@@ -1,0 +1,373 @@
+// tcgen05 / TMEM / TMA GEMM for sm_100a (bf16 inputs, fp32 accumulate in tensor memory).
+//
+//   C[m, n] = epilogue( sum_k A(m, k) * B(n, k) )
+//
+// Two operand layouts (template MN):
+//   MN = false  A is [M, K] and B is [N, K], both K-contiguous       -> forward and dgrad (dgrad reads the
+//                                                                        transposed bf16 weight shadow)
+//   MN = true   A is [K, M] and B is [K, N], both MN-contiguous      -> wgrad  dW[n, k] = sum_t dY[t, n] X[t, k]
+//                                                                        (contraction over tokens, split-K + fp32 red)
+// Structure: persistent CTAs (one per SM), warp-specialised: warp 0 = TMA producer, warp 1 = single-thread
+// tcgen05.mma issuer, warp 2 = TMEM allocator, warps 4..7 = epilogue (tcgen05.ld -> registers -> fused
+// bias / GELU / GELU' / residual -> 16-byte global stores).  The accumulator is double-buffered in TMEM
+// (2 x BN columns) so the epilogue of tile i overlaps the main loop of tile i + 1; shared memory holds a
+// STAGES-deep ring of 128 x 64 (A) and BN x 64 (B) bf16 tiles in the 128-byte swizzle layout.
+#include <mutex>
+#include <unordered_map>
+#include <string>
+#include <cstring>
+
+#include "common.cuh"
+#include "gemm_params.h"
+#include "tc_common.cuh"
+
+namespace {
+
+constexpr int BM = 128;
+constexpr int BK = 64;
+constexpr int UMMA_K = 16;
+constexpr int A_BYTES = BM * BK * 2;
+constexpr int NUM_THREADS = 256;
+constexpr int EPI_WARP0 = 4;
+
+template <int BN> struct Cfg {
+  static constexpr int B_BYTES = BN * BK * 2;
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int STAGES = (BN == 256) ? 4 : 6;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+};
+
+struct TcArgs {
+  void* C;
+  const float* bias;
+  const void* residual;
+  void* aux;
+  int M, N, K;
+  int ldc;
+  int flags;
+  int splits;
+  float alpha;
+};
+
+template <int BN, bool MN>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, TcArgs args) {
+  using C_ = Cfg<BN>;
+  constexpr int STAGES = C_::STAGES;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * C_::STAGE_BYTES);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tfull_bar = empty_bar + STAGES;
+  uint64_t* tempty_bar = tfull_bar + 2;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  const int mblocks = (args.M + BM - 1) / BM;
+  const int nblocks = (args.N + BN - 1) / BN;
+  const int kblocks = (args.K + BK - 1) / BK;
+  const int tiles_mn = mblocks * nblocks;
+  const int total_tiles = tiles_mn * args.splits;
+  const int kb_per_split = (kblocks + args.splits - 1) / args.splits;
+
+  if (warp == 0 && lane == 0) {
+    tc::prefetch_tmap(&tmA);
+    tc::prefetch_tmap(&tmB);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      tc::mbar_init(&full_bar[s], 1);
+      tc::mbar_init(&empty_bar[s], 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      tc::mbar_init(&tfull_bar[s], 1);
+      tc::mbar_init(&tempty_bar[s], 128);
+    }
+    tc::fence_barrier_init();
+  }
+  if (warp == 2) {
+    tc::tmem_alloc(tmem_ptr, 2 * BN);
+    tc::tmem_relinquish();
+  }
+  tc::tc_fence_before();
+  __syncthreads();
+  tc::tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        const int split = t / tiles_mn, rem = t % tiles_mn;
+        const int n_blk = rem / mblocks, m_blk = rem % mblocks;
+        const int kb0 = split * kb_per_split;
+        const int kb1 = min(kblocks, kb0 + kb_per_split);
+        for (int kb = kb0; kb < kb1; ++kb) {
+          tc::mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* sA = smem + stage * C_::STAGE_BYTES;
+          uint8_t* sB = sA + A_BYTES;
+          tc::mbar_expect_tx(&full_bar[stage], C_::STAGE_BYTES);
+          if constexpr (!MN) {
+            tc::tma_load_2d(sA, &tmA, &full_bar[stage], kb * BK, m_blk * BM);
+            tc::tma_load_2d(sB, &tmB, &full_bar[stage], kb * BK, n_blk * BN);
+          } else {
+#pragma unroll
+            for (int i = 0; i < BM / 64; ++i)
+              tc::tma_load_2d(sA + i * 8192, &tmA, &full_bar[stage], m_blk * BM + i * 64, kb * BK);
+#pragma unroll
+            for (int i = 0; i < BN / 64; ++i)
+              tc::tma_load_2d(sB + i * 8192, &tmB, &full_bar[stage], n_blk * BN + i * 64, kb * BK);
+          }
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      constexpr uint32_t idesc = tc::make_idesc_bf16(BM, BN, MN ? 1 : 0, MN ? 1 : 0);
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        const int split = t / tiles_mn;
+        const int kb0 = split * kb_per_split;
+        const int kb1 = min(kblocks, kb0 + kb_per_split);
+        tc::mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
+        tc::tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * BN;
+        for (int kb = kb0; kb < kb1; ++kb) {
+          tc::mbar_wait(&full_bar[stage], phase);
+          tc::tc_fence_after();
+          const uint32_t a_addr = tc::smem_u32(smem + stage * C_::STAGE_BYTES);
+          const uint32_t b_addr = a_addr + A_BYTES;
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k) {
+            uint64_t da, db;
+            if constexpr (!MN) {
+              // K-major, 128B swizzle: rows are 128 B, 8-row groups 1024 B apart; K advance = 32 B inside the row
+              da = tc::make_smem_desc(a_addr + k * UMMA_K * 2, 16, 1024);
+              db = tc::make_smem_desc(b_addr + k * UMMA_K * 2, 16, 1024);
+            } else {
+              // MN-major, 128B swizzle: 64-element MN chunks 8192 B apart (one TMA box each), 8-row K groups
+              // 1024 B apart; K advance = 16 rows = 2048 B
+              da = tc::make_smem_desc(a_addr + k * UMMA_K * 128, 8192, 1024);
+              db = tc::make_smem_desc(b_addr + k * UMMA_K * 128, 8192, 1024);
+            }
+            tc::umma_bf16(d_tmem, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+          }
+          tc::umma_commit(&empty_bar[stage]);
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+        tc::umma_commit(&tfull_bar[acc]);
+        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+      }
+    }
+  } else if (warp >= EPI_WARP0) {
+    // ===================== epilogue =====================
+    const int ew = warp - EPI_WARP0;  // == warp % 4 -> TMEM lanes [32 * ew, 32 * ew + 32)
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    const bool out_f32 = (args.flags & GEMM_OUT_F32) != 0;
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+      const int rem = t % tiles_mn;
+      const int n_blk = rem / mblocks, m_blk = rem % mblocks;
+      tc::mbar_wait(&tfull_bar[acc], acc_phase);
+      tc::tc_fence_after();
+      const int row = m_blk * BM + ew * 32 + lane;
+      const bool row_ok = row < args.M;
+      const size_t row_off = static_cast<size_t>(row) * args.ldc;
+#pragma unroll 1
+      for (int ch = 0; ch < BN / 32; ++ch) {
+        const int col0 = n_blk * BN + ch * 32;
+        if (col0 >= args.N) break;  // warp-uniform
+        uint32_t r[32];
+        tc::tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + acc * BN + ch * 32, r);
+        tc::tmem_ld_wait();
+        if (row_ok) {
+#pragma unroll
+          for (int v8 = 0; v8 < 4; ++v8) {
+            const int col = col0 + v8 * 8;
+            if (col >= args.N) break;
+            float v[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[v8 * 8 + j]) * args.alpha;
+            if (args.bias != nullptr) {
+#pragma unroll
+              for (int j = 0; j < 8; ++j) v[j] += __ldg(args.bias + col + j);
+            }
+            if (args.flags & GEMM_GELU) {
+              bf16* aux = static_cast<bf16*>(args.aux) + row_off + col;
+              VecIO<bf16>::store(aux, v);
+#pragma unroll
+              for (int j = 0; j < 8; ++j) v[j] = gelu_erf(__bfloat162float(__float2bfloat16_rn(v[j])));
+            }
+            if (args.flags & GEMM_DGELU) {
+              float a[8];
+              VecIO<bf16>::load(static_cast<const bf16*>(args.aux) + row_off + col, a);
+#pragma unroll
+              for (int j = 0; j < 8; ++j) v[j] *= gelu_erf_grad(a[j]);
+            }
+            if (args.residual != nullptr) {
+              float a[8];
+              VecIO<bf16>::load(static_cast<const bf16*>(args.residual) + row_off + col, a);
+#pragma unroll
+              for (int j = 0; j < 8; ++j) v[j] += a[j];
+            }
+            if (out_f32) {
+              float* c = static_cast<float*>(args.C) + row_off + col;
+              if (args.flags & GEMM_ACCUM) {
+                atomicAdd(reinterpret_cast<float4*>(c), make_float4(v[0], v[1], v[2], v[3]));
+                atomicAdd(reinterpret_cast<float4*>(c + 4), make_float4(v[4], v[5], v[6], v[7]));
+              } else {
+                VecIO<float>::store(c, v);
+                VecIO<float>::store(c + 4, v + 4);
+              }
+            } else {
+              VecIO<bf16>::store(static_cast<bf16*>(args.C) + row_off + col, v);
+            }
+          }
+        }
+      }
+      tc::tc_fence_before();
+      tc::mbar_arrive(&tempty_bar[acc]);
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+  }
+
+  tc::tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tc::tmem_dealloc(tmem_base, 2 * BN);
+}
+
+// ---------------------------------------------------------------- host: tensor maps
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  });
+  return fn;
+}
+
+struct MapKey {
+  const void* ptr;
+  uint64_t d0, d1, stride1;
+  uint32_t b0, b1;
+  bool operator==(const MapKey& o) const { return std::memcmp(this, &o, sizeof(MapKey)) == 0; }
+};
+struct MapKeyHash {
+  size_t operator()(const MapKey& k) const {
+    size_t h = 1469598103934665603ull;
+    const unsigned char* p = reinterpret_cast<const unsigned char*>(&k);
+    for (size_t i = 0; i < sizeof(MapKey); ++i) h = (h ^ p[i]) * 1099511628211ull;
+    return h;
+  }
+};
+
+// 2D bf16 tensor [d1 rows, d0 cols] with row pitch stride1 (elements), box [b1 rows, b0 cols], 128B swizzle.
+int get_tmap(CUtensorMap* out, const void* ptr, uint64_t d0, uint64_t d1, uint64_t stride1, uint32_t b0, uint32_t b1) {
+  static std::unordered_map<MapKey, CUtensorMap, MapKeyHash> cache;
+  static std::mutex mu;
+  MapKey key;
+  std::memset(&key, 0, sizeof(key));
+  key.ptr = ptr; key.d0 = d0; key.d1 = d1; key.stride1 = stride1; key.b0 = b0; key.b1 = b1;
+  std::lock_guard<std::mutex> lock(mu);
+  auto it = cache.find(key);
+  if (it != cache.end()) { *out = it->second; return 0; }
+  EncodeTiledFn fn = get_encode_fn();
+  if (fn == nullptr) return -10;
+  if ((reinterpret_cast<uintptr_t>(ptr) & 15) != 0 || (stride1 * 2) % 16 != 0) return -11;
+  cuuint64_t dims[2] = {d0, d1};
+  cuuint64_t strides[1] = {stride1 * 2};
+  cuuint32_t box[2] = {b0, b1};
+  cuuint32_t estr[2] = {1, 1};
+  CUtensorMap m;
+  CUresult r = fn(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return -12;
+  if (cache.size() > 4096) cache.clear();
+  cache.emplace(key, m);
+  *out = m;
+  return 0;
+}
+
+int num_sms() {
+  static int n = 0;
+  if (n == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+  }
+  return n;
+}
+
+template <int BN, bool MN>
+int launch(const GemmParams& P, cudaStream_t st) {
+  using C_ = Cfg<BN>;
+  CUtensorMap tmA, tmB;
+  int rc;
+  if (!MN) {
+    if ((rc = get_tmap(&tmA, P.A, P.K, P.M, P.sam, BK, BM)) != 0) return rc;
+    if ((rc = get_tmap(&tmB, P.B, P.K, P.N, P.sbn, BK, BN)) != 0) return rc;
+  } else {
+    if ((rc = get_tmap(&tmA, P.A, P.M, P.K, P.sak, 64, BK)) != 0) return rc;
+    if ((rc = get_tmap(&tmB, P.B, P.N, P.K, P.sbk, 64, BK)) != 0) return rc;
+  }
+  const int mblocks = (P.M + BM - 1) / BM, nblocks = (P.N + BN - 1) / BN, kblocks = (P.K + BK - 1) / BK;
+  int splits = 1;
+  if (MN && (P.flags & GEMM_ACCUM)) {
+    // split the token contraction so that the grid covers the chip (fp32 red.add combines the partials)
+    const int tiles = mblocks * nblocks;
+    splits = (2 * num_sms() + tiles - 1) / tiles;
+    if (splits > kblocks) splits = kblocks;
+    if (splits < 1) splits = 1;
+    const int per = (kblocks + splits - 1) / splits;
+    splits = (kblocks + per - 1) / per;  // no empty split
+  }
+  TcArgs a;
+  a.C = P.C; a.bias = P.bias; a.residual = P.residual; a.aux = P.aux;
+  a.M = P.M; a.N = P.N; a.K = P.K; a.ldc = P.ldc; a.flags = P.flags; a.splits = splits; a.alpha = P.alpha;
+  const int total = mblocks * nblocks * splits;
+  const int grid = total < num_sms() ? total : num_sms();
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaFuncSetAttribute(gemm_tc_kernel<BN, MN>, cudaFuncAttributeMaxDynamicSharedMemorySize, C_::SMEM_BYTES);
+    attr_set = true;
+  }
+  gemm_tc_kernel<BN, MN><<<grid, NUM_THREADS, C_::SMEM_BYTES, st>>>(tmA, tmB, a);
+  cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? 0 : static_cast<int>(e);
+}
+
+}  // namespace
+
+// bf16 only.  Supported operand layouts: (sak == 1 && sbk == 1) K-major, (sam == 1 && sbn == 1) MN-major.
+// Unbatched (nb1 == nb2 == 1).  N % 8 == 0, ldc % 8 == 0.
+extern "C" int mb_gemm_tc(const GemmParams* params, void* stream) {
+  const GemmParams& P = *params;
+  if (P.M == 0 || P.N == 0) return 0;
+  if (P.nb1 != 1 || P.nb2 != 1) return -3;
+  if (P.N % 8 != 0 || P.ldc % 8 != 0 || P.K <= 0) return -4;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const bool kmajor = P.sak == 1 && P.sbk == 1;
+  const bool mnmajor = P.sam == 1 && P.sbn == 1;
+  const bool wide = P.N > 128;
+  if (kmajor) return wide ? launch<256, false>(P, st) : launch<128, false>(P, st);
+  if (mnmajor) return wide ? launch<256, true>(P, st) : launch<128, true>(P, st);
+  return -5;
+}
