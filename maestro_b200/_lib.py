@@ -1,0 +1,115 @@
+"""Loader / builder of the C-ABI shared library ``libmaestro_b200.so`` (CUDA kernels for sm_100a).
+
+The library is built in-tree by :func:`build` (plain ``nvcc -shared``; no torch headers, the ABI is
+``extern "C"`` with raw device pointers, sizes and a ``cudaStream_t`` -- see ``include/maestro_b200.h``).
+There is no CPU fallback: :func:`lib` raises if the library is missing.
+"""
+
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+from pathlib import Path
+
+HERE = Path(__file__).resolve().parent
+CSRC = HERE / "csrc"
+SO_PATH = HERE / "libmaestro_b200.so"
+SOURCES = ["elementwise.cu", "norm.cu", "mask.cu", "unmask.cu", "loss.cu", "gemm_simt.cu", "gemm_tc.cu",
+           "attn_tc.cu", "optim.cu"]
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
+              "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"]
+
+
+def _nvcc() -> str:
+    for cand in (os.environ.get("NVCC"), "/usr/local/cuda/bin/nvcc", "nvcc"):
+        if cand and (os.path.isabs(cand) and os.path.exists(cand) or not os.path.isabs(cand)):
+            return cand
+    raise RuntimeError("nvcc not found")
+
+
+def build(force: bool = False, verbose: bool = False) -> Path:
+    """Compile every kernel for sm_100a into ``libmaestro_b200.so`` (incremental per source file)."""
+    srcs = [CSRC / s for s in SOURCES if (CSRC / s).exists()]
+    headers = list(CSRC.glob("*.cuh")) + list(CSRC.glob("*.h"))
+    newest_hdr = max(h.stat().st_mtime for h in headers)
+    objdir = HERE / "build"
+    objdir.mkdir(exist_ok=True)
+    objs, rebuilt = [], False
+    for src in srcs:
+        obj = objdir / (src.stem + ".o")
+        if force or not obj.exists() or obj.stat().st_mtime < max(src.stat().st_mtime, newest_hdr):
+            cmd = [_nvcc(), *NVCC_FLAGS, "-c", str(src), "-o", str(obj)]
+            if verbose:
+                print(" ".join(cmd))
+            subprocess.run(cmd, check=True)
+            rebuilt = True
+        objs.append(str(obj))
+    if rebuilt or not SO_PATH.exists():
+        cmd = [_nvcc(), "-shared", "-o", str(SO_PATH), *objs, "-lcudart"]
+        if verbose:
+            print(" ".join(cmd))
+        subprocess.run(cmd, check=True)
+    return SO_PATH
+
+
+class GemmParams(C.Structure):
+    """Mirror of ``struct GemmParams`` (csrc/gemm_params.h)."""
+
+    _fields_ = [
+        ("A", C.c_void_p), ("B", C.c_void_p), ("C", C.c_void_p),
+        ("bias", C.c_void_p), ("residual", C.c_void_p), ("aux", C.c_void_p),
+        ("M", C.c_int), ("N", C.c_int), ("K", C.c_int),
+        ("sam", C.c_longlong), ("sak", C.c_longlong), ("sbn", C.c_longlong), ("sbk", C.c_longlong),
+        ("ldc", C.c_int), ("nb1", C.c_int), ("nb2", C.c_int),
+        ("a_s1", C.c_longlong), ("a_s2", C.c_longlong), ("b_s1", C.c_longlong), ("b_s2", C.c_longlong),
+        ("c_s1", C.c_longlong), ("c_s2", C.c_longlong),
+        ("alpha", C.c_float), ("flags", C.c_int),
+    ]
+
+
+LOSS_MAX_C, LOSS_MAX_G = 16, 4
+
+
+class LossParams(C.Structure):
+    """Mirror of ``struct LossParams`` (csrc/loss.cu)."""
+
+    _fields_ = [
+        ("target", C.c_void_p),
+        ("pred", C.c_void_p * LOSS_MAX_G), ("dpred", C.c_void_p * LOSS_MAX_G),
+        ("mask", C.c_void_p), ("coef", C.c_void_p), ("accum", C.c_void_p),
+        ("B", C.c_int), ("D", C.c_int), ("C", C.c_int), ("S", C.c_int), ("p", C.c_int), ("G", C.c_int),
+        ("Lg", C.c_int), ("mask_off", C.c_int),
+        ("cg", C.c_int * LOSS_MAX_G), ("c0", C.c_int * LOSS_MAX_G),
+        ("n_norm", C.c_int),
+        ("norm_of_ch", C.c_int * LOSS_MAX_C), ("norm_size", C.c_int * LOSS_MAX_C),
+        ("l2", C.c_int),
+    ]
+
+
+_LIB = None
+
+
+def lib() -> C.CDLL:
+    """The loaded C-ABI library; raises (no fallback) when it has not been built."""
+    global _LIB
+    if _LIB is None:
+        if not SO_PATH.exists():
+            raise RuntimeError(
+                f"{SO_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                "(maestro_b200 has no CPU / eager fallback)")
+        _LIB = C.CDLL(str(SO_PATH))
+        for name in EXPORTS:
+            getattr(_LIB, name).restype = C.c_int
+    return _LIB
+
+
+# every symbol declared in include/maestro_b200.h
+EXPORTS = [
+    "mb_cast_f32_to_bf16", "mb_cast_transpose_f32_to_bf16", "mb_resize_nearest", "mb_im2col", "mb_rows_image",
+    "mb_date_features", "mb_colsum_accum",
+    "mb_layernorm_fwd", "mb_layernorm_bwd", "mb_gn_stats", "mb_gn_apply", "mb_gn_bwd",
+    "mb_mask_indices", "mb_gather_rows", "mb_scatter_kept", "mb_unmask_fwd", "mb_masktoken_grad",
+    "mb_loss_fwd_bwd", "mb_gemm_simt", "mb_softmax_rows", "mb_softmax_bwd_rows", "mb_gemm_tc",
+    "mb_adamw_step",
+]

@@ -180,13 +180,14 @@ extern "C" int mb_rows_image(void* rows, int dtype, float* img, int n_img, int C
 }
 
 // ------------------------------------------------------------------ date features
-// dates int16 [B, D, 3] (year, day-of-year, hour), ref int16 [B, 1, 3] -> feat fp32 [B, D, 5] =
+// dates int16 [B, D, 3] (year, day-of-year, hour), ref int16 [B, 1, 3] -> feat fp32 [B, Dtot, 5] rows doff..doff+D =
 // (diff, sin doy, cos doy, sin hour, cos hour) with the reference's fp32 operation order.
 __global__ void date_features_kernel(const short* __restrict__ dates, const short* __restrict__ ref,
-                                     float* __restrict__ feat, int B, int D) {
+                                     float* __restrict__ feat_base, int B, int D, int Dtot, int doff) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= B * D) return;
   const int b = i / D;
+  float* feat = feat_base + (static_cast<size_t>(b) * Dtot + doff + (i % D)) * 5 - static_cast<size_t>(i) * 5;
   const float year = static_cast<float>(dates[i * 3 + 0]);
   float doy = __fdiv_rn(static_cast<float>(dates[i * 3 + 1]), 365.25f);
   float hour = __fdiv_rn(static_cast<float>(dates[i * 3 + 2]), 24.0f);
@@ -203,9 +204,11 @@ __global__ void date_features_kernel(const short* __restrict__ dates, const shor
   feat[i * 5 + 4] = cosf(hour);
 }
 
-extern "C" int mb_date_features(const short* dates, const short* ref, float* feat, int B, int D, void* stream) {
+extern "C" int mb_date_features(const short* dates, const short* ref, float* feat, int B, int D, int Dtot, int doff,
+                                void* stream) {
   if (B * D == 0) return 0;
-  date_features_kernel<<<mb_ceil_div(B * D, 128), 128, 0, static_cast<cudaStream_t>(stream)>>>(dates, ref, feat, B, D);
+  date_features_kernel<<<mb_ceil_div(B * D, 128), 128, 0, static_cast<cudaStream_t>(stream)>>>(dates, ref, feat, B, D,
+                                                                                              Dtot, doff);
   MB_CHECK_LAUNCH();
   return 0;
 }

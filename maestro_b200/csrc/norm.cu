@@ -246,14 +246,14 @@ extern "C" int mb_gn_stats(const void* y, int dtype, double* sums, int n_img, lo
 // Phase 2: normalise + affine + positional + date encoding, written into the group token buffer.
 //   y      [n_img * L, E]   conv output (image i = b * D + d)
 //   out    [B, out_bs, E]   row = b * out_bs + out_off + d * L + l
-//   pos    [L, E] fp32 (already scaled by fac_abs_enc), feat [B, D, 5] date features.
+//   pos    [L, E] fp32 (already scaled by fac_abs_enc), feat [B, feat_bs, 5] date features (rows feat_off + d).
 template <typename T>
 __global__ void __launch_bounds__(256) gn_apply_kernel(const T* __restrict__ y, const double* __restrict__ sums,
                                                        const float* __restrict__ gamma, const float* __restrict__ beta,
                                                        const float* __restrict__ pos, const float* __restrict__ feat,
                                                        T* __restrict__ out, float* __restrict__ stats_out, int n_img,
                                                        int D, int L, int E, float eps, int out_bs, int out_off,
-                                                       int date_dim, float fac_date) {
+                                                       int date_dim, float fac_date, int feat_bs, int feat_off) {
   constexpr int V = VecIO<T>::N;
   const int nvec_row = E / V;
   const size_t total = static_cast<size_t>(n_img) * L * nvec_row;
@@ -279,7 +279,7 @@ __global__ void __launch_bounds__(256) gn_apply_kernel(const T* __restrict__ y, 
     for (int j = 0; j < V; ++j) {
       const int e = cv * V + j;
       float o = (v[j] - mean) * rstd * gamma[e] + beta[e] + pos[static_cast<size_t>(l) * E + e];
-      if (e >= E - date_dim) o += date_channel(feat + (static_cast<size_t>(b) * D + d) * 5, e - (E - date_dim), date_dim, fac_date);
+      if (e >= E - date_dim) o += date_channel(feat + (static_cast<size_t>(b) * feat_bs + feat_off + d) * 5, e - (E - date_dim), date_dim, fac_date);
       v[j] = o;
     }
     const size_t orow = static_cast<size_t>(b) * out_bs + out_off + static_cast<size_t>(d) * L + l;
@@ -290,7 +290,7 @@ __global__ void __launch_bounds__(256) gn_apply_kernel(const T* __restrict__ y, 
 extern "C" int mb_gn_apply(const void* y, const double* sums, const float* gamma, const float* beta,
                            const float* pos, const float* feat, void* out, float* stats_out, int dtype, int n_img,
                            int D, int L, int E, float eps, int out_bs, int out_off, int date_dim, float fac_date,
-                           void* stream) {
+                           int feat_bs, int feat_off, void* stream) {
   if (n_img == 0) return 0;
   if (E % 8 != 0) return -2;
   const long long total = static_cast<long long>(n_img) * L * (E / 4);
@@ -299,7 +299,7 @@ extern "C" int mb_gn_apply(const void* y, const double* sums, const float* gamma
   MB_DISPATCH_DTYPE(dtype, T,
                     (gn_apply_kernel<T><<<static_cast<int>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(
                         static_cast<const T*>(y), sums, gamma, beta, pos, feat, static_cast<T*>(out), stats_out,
-                        n_img, D, L, E, eps, out_bs, out_off, date_dim, fac_date)));
+                        n_img, D, L, E, eps, out_bs, out_off, date_dim, fac_date, feat_bs, feat_off)));
   MB_CHECK_LAUNCH();
   return 0;
 }

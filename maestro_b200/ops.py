@@ -1,0 +1,237 @@
+"""Tensor-level wrappers over the C-ABI kernels (``include/maestro_b200.h``).
+
+Every method takes pre-allocated CUDA tensors, passes raw pointers + the current CUDA stream to the
+library and raises on a non-zero status.  There is no CPU path: CPU tensors raise ``RuntimeError``
+(SURVEY §8b "Errors").  ``tests/fake_kernels.py`` implements the same method set with plain torch ops;
+it is a *test double* used to exercise the host-side orchestration on CPU and as the per-kernel
+reference in the GPU unit tests -- the product never imports it.
+"""
+
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from . import _lib
+
+F32, BF16 = 0, 1
+GEMM_GELU, GEMM_DGELU, GEMM_ACCUM, GEMM_OUT_F32 = 1, 2, 4, 8
+
+
+def _dt(t: torch.Tensor) -> int:
+    if t.dtype == torch.float32:
+        return F32
+    if t.dtype == torch.bfloat16:
+        return BF16
+    raise TypeError(f"unsupported activation dtype {t.dtype}")
+
+
+def _p(t: torch.Tensor | None):
+    if t is None:
+        return None
+    if not t.is_cuda:
+        raise RuntimeError("maestro_b200 kernels need CUDA tensors (there is no CPU fallback)")
+    return C.c_void_p(t.data_ptr())
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _ck(rc: int, name: str) -> None:
+    if rc != 0:
+        raise RuntimeError(f"{name} failed with status {rc}")
+
+
+IDENT = None  # row map sentinel: identity
+
+
+def _rowmap(m, rows):
+    return (rows, 0, 0) if m is None else m
+
+
+class Kernels:
+    """The CUDA backend.  ``launches`` counts kernel launches issued through this object."""
+
+    name = "cuda"
+
+    def __init__(self) -> None:
+        self.L = _lib.lib()
+        self.launches = 0
+        self.use_tc = True   # tcgen05 GEMM for bf16 (False: CUDA-core GEMM everywhere; debugging aid)
+
+    # ------------------------------------------------------------------ data movement
+    def cast_bf16(self, src, dst):
+        self.launches += 1
+        _ck(self.L.mb_cast_f32_to_bf16(_p(src), _p(dst), C.c_size_t(src.numel()), _stream()), "cast")
+
+    def cast_transpose_bf16(self, src, dst):
+        R, Cc = src.shape
+        self.launches += 1
+        _ck(self.L.mb_cast_transpose_f32_to_bf16(_p(src), _p(dst), R, Cc, _stream()), "cast_transpose")
+
+    def resize_nearest(self, src, dst, rescale_elev):
+        n, Cc, h, w = src.shape
+        self.launches += 1
+        _ck(self.L.mb_resize_nearest(_p(src), _p(dst), n, Cc, h, w, dst.shape[-2], dst.shape[-1], int(rescale_elev),
+                                     _stream()), "resize")
+
+    def im2col(self, img, cols, c0, c, p):
+        n, Cc, S, _ = img.shape
+        self.launches += 1
+        _ck(self.L.mb_im2col(_p(img), _p(cols), _dt(cols), n, Cc, c0, c, S, p, cols.shape[1], _stream()), "im2col")
+
+    def rows_image(self, rows, img, c0, c, p, direction):
+        n, Cc, S, _ = img.shape
+        self.launches += 1
+        _ck(self.L.mb_rows_image(_p(rows), _dt(rows), _p(img), n, Cc, c0, c, S, p, direction, _stream()), "rows_image")
+
+    def date_features(self, dates, ref, feat, doff):
+        B, D, _ = dates.shape
+        self.launches += 1
+        _ck(self.L.mb_date_features(_p(dates), _p(ref), _p(feat), B, D, feat.shape[1], doff, _stream()), "date_features")
+
+    def colsum_accum(self, dy, out):
+        M, N = dy.shape
+        self.launches += 1
+        _ck(self.L.mb_colsum_accum(_p(dy), _dt(dy), _p(out), M, N, _stream()), "colsum")
+
+    # ------------------------------------------------------------------ norms
+    def layernorm_fwd(self, x, gamma, beta, y, mean, rstd, rows, d, eps=1e-5, in_map=IDENT, out_map=IDENT):
+        im, om = _rowmap(in_map, rows), _rowmap(out_map, rows)
+        self.launches += 1
+        _ck(self.L.mb_layernorm_fwd(_p(x), _p(gamma), _p(beta), _p(y), _p(mean), _p(rstd), _dt(x), rows, d,
+                                    C.c_float(eps), *im, *om, _stream()), "layernorm_fwd")
+
+    def layernorm_bwd(self, dy, x, mean, rstd, gamma, dres, dx, dgamma, dbeta, rows, d, in_map=IDENT, out_map=IDENT):
+        im, om = _rowmap(in_map, rows), _rowmap(out_map, rows)
+        self.launches += 1
+        _ck(self.L.mb_layernorm_bwd(_p(dy), _p(x), _p(mean), _p(rstd), _p(gamma), _p(dres), _p(dx), _p(dgamma),
+                                    _p(dbeta), _dt(x), rows, d, *im, *om, _stream()), "layernorm_bwd")
+
+    def gn_stats(self, y, sums, n_img):
+        self.launches += 1
+        _ck(self.L.mb_gn_stats(_p(y), _dt(y), _p(sums), n_img, C.c_longlong(y.numel() // n_img), _stream()), "gn_stats")
+
+    def gn_apply(self, y, sums, gamma, beta, pos, feat, out, stats, n_img, D, L, E, eps, out_bs, out_off, date_dim,
+                 fac_date, feat_off):
+        self.launches += 1
+        _ck(self.L.mb_gn_apply(_p(y), _p(sums), _p(gamma), _p(beta), _p(pos), _p(feat), _p(out), _p(stats), _dt(y),
+                               n_img, D, L, E, C.c_float(eps), out_bs, out_off, date_dim, C.c_float(fac_date),
+                               feat.shape[1], feat_off, _stream()), "gn_apply")
+
+    def gn_bwd(self, dy, y, stats, gamma, sums2, dconv, dgamma, dbeta, n_img, D, L, E, out_bs, out_off):
+        self.launches += 2
+        _ck(self.L.mb_gn_bwd(_p(dy), _p(y), _p(stats), _p(gamma), _p(sums2), _p(dconv), _p(dgamma), _p(dbeta),
+                             _dt(y), n_img, D, L, E, out_bs, out_off, _stream()), "gn_bwd")
+
+    # ------------------------------------------------------------------ masking
+    def mask_indices(self, noise, struct, nm, mask, slot, masked_idx, unmasked_idx, seg_id, seg_counts):
+        B, L = noise.shape
+        self.launches += 1
+        _ck(self.L.mb_mask_indices(_p(noise), _p(struct), B, L, nm, _p(mask), _p(slot), _p(masked_idx),
+                                   _p(unmasked_idx), _p(seg_id), _p(seg_counts), _stream()), "mask_indices")
+
+    def gather_rows(self, x, idx, out):
+        B, L, d = x.shape
+        self.launches += 1
+        _ck(self.L.mb_gather_rows(_p(x), _p(idx), _p(out), _dt(x), B, L, idx.shape[1], d, _stream()), "gather_rows")
+
+    def scatter_kept(self, dkept, mask, slot, dx):
+        B, L, d = dx.shape
+        self.launches += 1
+        _ck(self.L.mb_scatter_kept(_p(dkept), _p(mask), _p(slot), _p(dx), _dt(dx), B, L, dkept.shape[1], d,
+                                   _stream()), "scatter_kept")
+
+    def unmask_fwd(self, y, mask, slot, tok_id, src_pos, tok, pos, feat, date_id, out, date_dim, fac_date):
+        B, L, d = out.shape
+        self.launches += 1
+        _ck(self.L.mb_unmask_fwd(_p(y), _p(mask), _p(slot), _p(tok_id), _p(src_pos), _p(tok), _p(pos), _p(feat),
+                                 _p(date_id), _p(out), _dt(out), B, L, y.shape[1], d, feat.shape[1], date_dim,
+                                 C.c_float(fac_date), _stream()), "unmask_fwd")
+
+    def masktoken_grad(self, dx, mask, tok_id, src_pos, dtok):
+        B, L, d = dx.shape
+        self.launches += 1
+        _ck(self.L.mb_masktoken_grad(_p(dx), _p(mask), _p(tok_id), _p(src_pos), _p(dtok), _dt(dx), B, L, d,
+                                     dtok.shape[0], _stream()), "masktoken_grad")
+
+    # ------------------------------------------------------------------ loss
+    def loss_fwd_bwd(self, target, preds, dpreds, mask, coef, accum, B, D, Cc, S, p, Lg, mask_off, cg, norm_bands,
+                     l2):
+        P = _lib.LossParams()
+        P.target = target.data_ptr()
+        G = len(preds)
+        c0 = 0
+        for i in range(G):
+            P.pred[i] = preds[i].data_ptr()
+            P.dpred[i] = dpreds[i].data_ptr() if dpreds is not None else None
+            P.cg[i] = cg[i]
+            P.c0[i] = c0
+            c0 += cg[i]
+        P.mask = mask.data_ptr()
+        P.coef = coef.data_ptr() if coef is not None else None
+        P.accum = accum.data_ptr()
+        P.B, P.D, P.C, P.S, P.p, P.G, P.Lg, P.mask_off = B, D, Cc, S, p, G, Lg, mask_off
+        nb = list(norm_bands) if norm_bands else []
+        P.n_norm = len(nb)
+        ch = 0
+        for n, cn in enumerate(nb):
+            P.norm_size[n] = cn
+            for _ in range(cn):
+                P.norm_of_ch[ch] = n
+                ch += 1
+        P.l2 = int(l2)
+        if not target.is_cuda:
+            raise RuntimeError("maestro_b200 kernels need CUDA tensors (there is no CPU fallback)")
+        self.launches += 1
+        _ck(self.L.mb_loss_fwd_bwd(C.byref(P), _dt(preds[0]), _stream()), "loss_fwd_bwd")
+
+    # ------------------------------------------------------------------ GEMM
+    def gemm(self, A, B, Cm, M, N, K, sam, sak, sbn, sbk, ldc, bias=None, residual=None, aux=None, flags=0,
+             alpha=1.0, nb1=1, nb2=1, a_s=(0, 0), b_s=(0, 0), c_s=(0, 0), a_off=0, b_off=0, c_off=0):
+        """C[m, n] = epilogue(alpha * sum_k A[m*sam + k*sak] * B[n*sbn + k*sbk]); offsets in elements."""
+        if not (A.is_cuda and B.is_cuda and Cm.is_cuda):
+            raise RuntimeError("maestro_b200 kernels need CUDA tensors (there is no CPU fallback)")
+        P = _lib.GemmParams()
+        P.A = A.data_ptr() + a_off * A.element_size()
+        P.B = B.data_ptr() + b_off * B.element_size()
+        P.C = Cm.data_ptr() + c_off * Cm.element_size()
+        P.bias = bias.data_ptr() if bias is not None else None
+        P.residual = residual.data_ptr() if residual is not None else None
+        P.aux = aux.data_ptr() if aux is not None else None
+        P.M, P.N, P.K = M, N, K
+        P.sam, P.sak, P.sbn, P.sbk, P.ldc = sam, sak, sbn, sbk, ldc
+        P.nb1, P.nb2 = nb1, nb2
+        P.a_s1, P.a_s2 = a_s
+        P.b_s1, P.b_s2 = b_s
+        P.c_s1, P.c_s2 = c_s
+        P.alpha = alpha
+        if Cm.dtype == torch.float32 and A.dtype != torch.float32:
+            flags |= GEMM_OUT_F32
+        P.flags = flags
+        self.launches += 1
+        tc_ok = (self.use_tc and A.dtype == torch.bfloat16 and nb1 == 1 and nb2 == 1 and N % 8 == 0 and ldc % 8 == 0
+                 and ((sak == 1 and sbk == 1 and sam % 8 == 0 and sbn % 8 == 0)
+                      or (sam == 1 and sbn == 1 and sak % 8 == 0 and sbk % 8 == 0))
+                 and P.A % 16 == 0 and P.B % 16 == 0)
+        if tc_ok:
+            _ck(self.L.mb_gemm_tc(C.byref(P), _stream()), "gemm_tc")
+        else:
+            _ck(self.L.mb_gemm_simt(C.byref(P), _dt(A), _stream()), "gemm_simt")
+
+    def softmax_rows(self, s, p, rows, n, scale):
+        self.launches += 1
+        _ck(self.L.mb_softmax_rows(_p(s), _p(p), _dt(p), C.c_longlong(rows), n, C.c_float(scale), _stream()), "softmax")
+
+    def softmax_bwd_rows(self, p, dp, ds, rows, n, scale):
+        self.launches += 1
+        _ck(self.L.mb_softmax_bwd_rows(_p(p), _p(dp), _p(ds), _dt(p), C.c_longlong(rows), n, C.c_float(scale),
+                                       _stream()), "softmax_bwd")
+
+    # ------------------------------------------------------------------ optimiser
+    def adamw_step(self, p, g, m, v, shadow, hyper, zero_grad):
+        self.launches += 1
+        _ck(self.L.mb_adamw_step(_p(p), _p(g), _p(m), _p(v), _p(shadow), _p(hyper), C.c_size_t(p.numel()),
+                                 int(zero_grad), _stream()), "adamw_step")
