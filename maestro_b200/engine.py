@@ -294,3 +294,434 @@ class PretrainEngine:
 
     def grads(self) -> dict[str, torch.Tensor]:
         return self.G
+
+    # ------------------------------------------------------------------ buffers
+    def _new(self, *shape, dtype=None):
+        return torch.empty(*shape, dtype=dtype or self.dtype, device=self.device)
+
+    def _zeros(self, *shape, dtype=None):
+        return torch.zeros(*shape, dtype=dtype or self.dtype, device=self.device)
+
+    # ------------------------------------------------------------------ linear layers
+    def _w(self, name: str) -> torch.Tensor:
+        return self.arena.Wb[name] if self.dtype == torch.bfloat16 else self.P[name]
+
+    def lin_fwd(self, x, M, wname, bname, out, gelu_aux=None, residual=None):
+        """out[M, N] = x[M, Kd] @ W[N, Kd]^T (+ bias) (gelu, saving the pre-activation) (+ residual)."""
+        shp = self.arena.shapes[wname]
+        N, Kd = shp[0], self.P[wname].numel() // shp[0]
+        self.K.gemm(x, self._w(wname), out, M, N, Kd, sam=Kd, sak=1, sbn=Kd, sbk=1, ldc=N,
+                    bias=self.P[bname] if bname else None, residual=residual, aux=gelu_aux,
+                    flags=GEMM_GELU if gelu_aux is not None else 0)
+
+    def lin_bwd(self, dy, M, x, wname, bname, dx=None, dgelu_aux=None):
+        """Accumulate dW, dbias; optionally dx[M, Kd] = dy[M, N] @ W (times gelu'(aux))."""
+        shp = self.arena.shapes[wname]
+        N, Kd = shp[0], self.P[wname].numel() // shp[0]
+        if bname:
+            self.K.colsum_accum(dy, self.G[bname])
+        # dW[n, k] += sum_m dy[m, n] * x[m, k]   (contraction over tokens)
+        self.K.gemm(dy, x, self.G[wname], N, Kd, M, sam=1, sak=N, sbn=1, sbk=Kd, ldc=Kd, flags=GEMM_ACCUM)
+        if dx is None:
+            return
+        fl = GEMM_DGELU if dgelu_aux is not None else 0
+        if self.dtype == torch.bfloat16:
+            self.K.gemm(dy, self.arena.WbT[wname], dx, M, Kd, N, sam=N, sak=1, sbn=N, sbk=1, ldc=Kd,
+                        aux=dgelu_aux, flags=fl)
+        else:
+            self.K.gemm(dy, self.P[wname], dx, M, Kd, N, sam=N, sak=1, sbn=1, sbk=Kd, ldc=Kd,
+                        aux=dgelu_aux, flags=fl)
+
+    # ------------------------------------------------------------------ attention
+    def attn_fwd(self, qkv, Bn, N, H, dh):
+        """softmax(q k^T / sqrt(dh)) v per (sample, head); qkv [Bn*N, 3*H*dh] -> o [Bn*N, H*dh]."""
+        inner = H * dh
+        scale = dh ** -0.5
+        o = self._new(Bn * N, inner)
+        s = self._new(Bn * H * N * N, dtype=torch.float32)
+        self.K.gemm(qkv, qkv, s, N, N, dh, sam=3 * inner, sak=1, sbn=3 * inner, sbk=1, ldc=N, nb1=Bn, nb2=H,
+                    a_s=(N * 3 * inner, dh), b_s=(N * 3 * inner, dh), c_s=(H * N * N, N * N), b_off=inner)
+        p = self._new(Bn * H * N * N)
+        self.K.softmax_rows(s, p, Bn * H * N, N, scale)
+        del s
+        self.K.gemm(p, qkv, o, N, dh, N, sam=N, sak=1, sbn=1, sbk=3 * inner, ldc=inner, nb1=Bn, nb2=H,
+                    a_s=(H * N * N, N * N), b_s=(N * 3 * inner, dh), c_s=(N * inner, dh), b_off=2 * inner)
+        return o, p
+
+    def attn_bwd(self, do, qkv, p, Bn, N, H, dh):
+        inner = H * dh
+        scale = dh ** -0.5
+        dqkv = self._new(Bn * N, 3 * inner)
+        bs_qkv, bs_p, bs_o = (N * 3 * inner, dh), (H * N * N, N * N), (N * inner, dh)
+        # dV[k, n] = sum_m P[m, k] dO[m, n]
+        self.K.gemm(p, do, dqkv, N, dh, N, sam=1, sak=N, sbn=1, sbk=inner, ldc=3 * inner, nb1=Bn, nb2=H,
+                    a_s=bs_p, b_s=bs_o, c_s=bs_qkv, c_off=2 * inner)
+        # dP[m, k] = sum_n dO[m, n] V[k, n]
+        dp = self._new(Bn * H * N * N, dtype=torch.float32)
+        self.K.gemm(do, qkv, dp, N, N, dh, sam=inner, sak=1, sbn=3 * inner, sbk=1, ldc=N, nb1=Bn, nb2=H,
+                    a_s=bs_o, b_s=bs_qkv, c_s=bs_p, b_off=2 * inner)
+        ds = self._new(Bn * H * N * N)
+        self.K.softmax_bwd_rows(p, dp, ds, Bn * H * N, N, scale)
+        del dp
+        # dQ[m, n] = sum_k dS[m, k] K[k, n]
+        self.K.gemm(ds, qkv, dqkv, N, dh, N, sam=N, sak=1, sbn=1, sbk=3 * inner, ldc=3 * inner, nb1=Bn, nb2=H,
+                    a_s=bs_p, b_s=bs_qkv, c_s=bs_qkv, b_off=inner)
+        # dK[k, n] = sum_m dS[m, k] Q[m, n]
+        self.K.gemm(ds, qkv, dqkv, N, dh, N, sam=1, sak=N, sbn=1, sbk=3 * inner, ldc=3 * inner, nb1=Bn, nb2=H,
+                    a_s=bs_p, b_s=bs_qkv, c_s=bs_qkv, c_off=inner)
+        return dqkv
+
+    # ------------------------------------------------------------------ transformer block
+    def block_fwd(self, pre, x, Bn, N, dim, H, dh, mlp):
+        K, P = self.K, self.P
+        rows, inner = Bn * N, H * dh
+        f32 = torch.float32
+        h1, m1, r1 = self._new(rows, dim), self._new(rows, dtype=f32), self._new(rows, dtype=f32)
+        K.layernorm_fwd(x, P[pre + "0.norm.weight"], P[pre + "0.norm.bias"], h1, m1, r1, rows, dim)
+        qkv = self._new(rows, 3 * inner)
+        self.lin_fwd(h1, rows, pre + "0.to_qkv.weight", None, qkv)
+        o, att = self.attn_fwd(qkv, Bn, N, H, dh)
+        x2 = self._new(rows, dim)
+        self.lin_fwd(o, rows, pre + "0.to_out.0.weight", pre + "0.to_out.0.bias", x2, residual=x)
+        h2, m2, r2 = self._new(rows, dim), self._new(rows, dtype=f32), self._new(rows, dtype=f32)
+        K.layernorm_fwd(x2, P[pre + "1.net.0.weight"], P[pre + "1.net.0.bias"], h2, m2, r2, rows, dim)
+        u, a = self._new(rows, mlp), self._new(rows, mlp)
+        self.lin_fwd(h2, rows, pre + "1.net.1.weight", pre + "1.net.1.bias", a, gelu_aux=u)
+        x3 = self._new(rows, dim)
+        self.lin_fwd(a, rows, pre + "1.net.4.weight", pre + "1.net.4.bias", x3, residual=x2)
+        return x3, (x, m1, r1, h1, qkv, att, o, x2, m2, r2, h2, u, a)
+
+    def block_bwd(self, pre, dx3, saved, Bn, N, dim, H, dh, mlp):
+        K, P, G = self.K, self.P, self.G
+        x, m1, r1, h1, qkv, att, o, x2, m2, r2, h2, u, a = saved
+        rows, inner = Bn * N, H * dh
+        du = self._new(rows, mlp)
+        self.lin_bwd(dx3, rows, a, pre + "1.net.4.weight", pre + "1.net.4.bias", dx=du, dgelu_aux=u)
+        dh2 = self._new(rows, dim)
+        self.lin_bwd(du, rows, h2, pre + "1.net.1.weight", pre + "1.net.1.bias", dx=dh2)
+        del du
+        dx2 = self._new(rows, dim)
+        K.layernorm_bwd(dh2, x2, m2, r2, P[pre + "1.net.0.weight"], dx3, dx2, G[pre + "1.net.0.weight"],
+                        G[pre + "1.net.0.bias"], rows, dim)
+        do = self._new(rows, inner)
+        self.lin_bwd(dx2, rows, o, pre + "0.to_out.0.weight", pre + "0.to_out.0.bias", dx=do)
+        dqkv = self.attn_bwd(do, qkv, att, Bn, N, H, dh)
+        dh1 = dh2  # reuse
+        self.lin_bwd(dqkv, rows, h1, pre + "0.to_qkv.weight", None, dx=dh1)
+        dx = self._new(rows, dim)
+        K.layernorm_bwd(dh1, x, m1, r1, P[pre + "0.norm.weight"], dx2, dx, G[pre + "0.norm.weight"],
+                        G[pre + "0.norm.bias"], rows, dim)
+        return dx
+
+    def stack_fwd(self, prefix, x, Bn, N, dim, depth, H, dh, mlp):
+        saved = []
+        for i in range(depth):
+            x, s = self.block_fwd(f"{prefix}layers.{i}.", x, Bn, N, dim, H, dh, mlp)
+            saved.append(s)
+        return x, saved
+
+    def stack_bwd(self, prefix, dx, saved, Bn, N, dim, H, dh, mlp):
+        for i in reversed(range(len(saved))):
+            dx = self.block_bwd(f"{prefix}layers.{i}.", dx, saved[i], Bn, N, dim, H, dh, mlp)
+            saved[i] = None
+        return dx
+
+    # ------------------------------------------------------------------ structural mask (host RNG)
+    def mask_struct(self, batch_size: int) -> dict[str, torch.Tensor]:
+        """Structural mask per group, bool [B, L_group] on the host (reference MAE.mask_struct, mae.py:178-226).
+
+        Draw order of the CPU generator: per modality (input order) mod, bands, dates, loc -- every loop pass
+        draws for all samples; samples whose group is entirely masked take the new draw; repeat until none is.
+        """
+        mc, B = self.mask_cfg, batch_size
+        cur = {g.name: torch.ones(B, g.L, dtype=torch.bool) for g in self.groups.values()}
+        while any(bool(c.all(dim=1).any()) for c in cur.values()):
+            draw = {}
+            for mt in self.mods.values():
+                grp = self.groups[mt.group]
+                alone = len(grp.mods) == 1
+                probs = [
+                    (mc.mask_mod if (self.fusion_mode == "group" and not alone) else None, (B, 1, 1, 1)),
+                    (mc.mask_bands if mt.G > 1 else None, (B, mt.G, 1, 1)),
+                    (mc.mask_dates if mt.D > 1 else None, (B, 1, mt.D, 1)),
+                    (mc.mask_loc, (B, 1, 1, mt.L)),
+                ]
+                acc = torch.zeros(B, mt.G, mt.D, mt.L, dtype=torch.bool)
+                for prob, shape in probs:
+                    if prob:
+                        acc = acc | (torch.rand(shape) < prob)
+                draw[mt.name] = acc.reshape(B, -1)
+            for g in self.groups.values():
+                new = torch.cat([draw[x] for x in g.mods], dim=1)
+                redo = cur[g.name].all(dim=1, keepdim=True)
+                cur[g.name] = torch.where(redo, new, cur[g.name])
+        return cur
+
+    # ------------------------------------------------------------------ forward
+    def forward(self, batch: dict, struct: dict | None = None, noise: dict | None = None,
+                unmask_order: dict | None = None) -> dict:
+        """Run the MAE forward.  Returns the step context (saved activations + outputs).
+
+        ``struct`` / ``noise`` / ``unmask_order`` inject the mask draws (parity tests); by default the
+        structural mask comes from the host generator and the noise from ``torch.rand`` on the device,
+        exactly where the reference draws them.
+        """
+        K, P, dev, f32 = self.K, self.P, self.device, torch.float32
+        E, Dd, hp = self.E, self.Dd, self.hp
+        if not self.shadows_fresh:
+            self.arena.refresh_shadows(K)
+            self.shadows_fresh = True
+        B = batch["ref_date"].shape[0]
+        ctx: dict = {"B": B, "mods": {}, "groups": {}}
+        ref = batch["ref_date"].to(dev).contiguous()
+
+        # 1. resize / rescale (mutates the batch dict like the reference) + date features
+        for g in self.groups.values():
+            ctx["groups"][g.name] = {"feat": self._new(B, g.Dtot, 5, dtype=f32)}
+        for mt in self.mods.values():
+            x = batch[mt.name].to(dev, f32).contiguous()
+            if x.shape[-1] != mt.S or x.shape[-2] != mt.S or mt.rescale_elev:
+                y = self._new(B * mt.D, mt.C, mt.S, mt.S, dtype=f32)
+                K.resize_nearest(x.flatten(0, 1), y, mt.rescale_elev)
+                x = y.view(B, mt.D, mt.C, mt.S, mt.S)
+            batch[mt.name] = x
+            K.date_features(batch[f"{mt.name}_dates"].to(dev).contiguous(), ref, ctx["groups"][mt.group]["feat"],
+                            mt.date_off)
+            ctx["mods"][mt.name] = {"img": x}
+
+        # 2. patch embedding + GroupNorm + encodings, written straight into the group token buffer
+        for g in self.groups.values():
+            ctx["groups"][g.name]["x_embed"] = self._new(B, g.L, E)
+        for mt in self.mods.values():
+            gc, g = ctx["groups"][mt.group], self.groups[mt.group]
+            mc = ctx["mods"][mt.name]
+            mc["cols"], mc["y"], mc["stats"] = [], [], []
+            n_img, rows, c0 = B * mt.D, B * mt.D * mt.L, 0
+            img = mc["img"].view(n_img, mt.C, mt.S, mt.S)
+            for gi, c in enumerate(mt.band_groups):
+                pre = f"patch_embed.{mt.embed}.patchify_bands.{gi}."
+                Kd = c * mt.p * mt.p
+                cols = self._new(rows, Kd)
+                K.im2col(img, cols, c0, c, mt.p)
+                y = self._new(rows, E)
+                self.lin_fwd(cols, rows, pre + "conv.weight", pre + "conv.bias", y)
+                sums = self._zeros(n_img, 2, dtype=torch.float64)
+                K.gn_stats(y, sums, n_img)
+                stats = self._new(n_img, 2, dtype=f32)
+                off = mt.tok_off + gi * mt.D * mt.L
+                K.gn_apply(y, sums, P[pre + "norm.weight"], P[pre + "norm.bias"],
+                           g.consts["enc_pos"][off:off + mt.L], gc["feat"], gc["x_embed"], stats, n_img, mt.D, mt.L,
+                           E, 1e-5, g.L, off, self.date_dim, self.fac_date, mt.date_off)
+                mc["cols"].append(cols)
+                mc["y"].append(y)
+                mc["stats"].append(stats)
+                c0 += c
+
+        # 3. masking: rank -> mask / slots / index lists, keep gather
+        if struct is None:
+            struct = self.mask_struct(B)
+        ctx["seg_counts"] = self._zeros(self.n_seg, dtype=torch.int32)
+        for g in self.groups.values():
+            gc = ctx["groups"][g.name]
+            nz = noise[g.name].to(dev, f32).contiguous() if noise is not None else torch.rand(B, g.L, device=dev)
+            st = struct[g.name].reshape(B, g.L).to(dev, torch.uint8).contiguous()
+            gc["mask"] = self._new(B, g.L, dtype=torch.uint8)
+            gc["slot"] = self._new(B, g.L, dtype=torch.int32)
+            gc["midx"] = self._new(B, g.nm, dtype=torch.int64)
+            gc["uidx"] = self._new(B, g.n_kept, dtype=torch.int64)
+            K.mask_indices(nz, st, g.nm, gc["mask"], gc["slot"], gc["midx"], gc["uidx"], g.consts["seg_id"],
+                           ctx["seg_counts"])
+            gc["x_kept"] = self._new(B, g.n_kept, E)
+            K.gather_rows(gc["x_embed"], gc["uidx"], gc["x_kept"])
+            gc["x_embed"] = None
+            gc["src_pos"] = None
+            if unmask_order is not None:
+                # test hook (reference tie quirk, mae.py:272-285): masked position order[b, j] shows the mask
+                # token that belongs to position midx[b, j]
+                sp = torch.arange(g.L, device=dev, dtype=torch.int32)[None].repeat(B, 1)
+                sp.scatter_(1, unmask_order[g.name].to(dev), gc["midx"].to(torch.int32))
+                gc["src_pos"] = sp
+
+        # 4. per-group encoders, then the joint encoder on the concatenated kept tokens
+        H, dh = hp["heads"], hp["dim_head"]
+        depth_g = hp["depth"] - self.inter_depth
+        nt = self.n_kept_total
+        if self.inter_depth:
+            xcat = self._new(B * nt, E)
+        for g in self.groups.values():
+            gc = ctx["groups"][g.name]
+            pre = f"encoder.{g.name}."
+            rows = B * g.n_kept
+            x, gc["enc_saved"] = self.stack_fwd(pre, gc["x_kept"].view(rows, E), B, g.n_kept, E, depth_g, H, dh,
+                                                self.mlp_e)
+            gc["enc_pre_norm"] = x
+            gc["enc_m"], gc["enc_r"] = self._new(rows, dtype=f32), self._new(rows, dtype=f32)
+            if self.inter_depth:
+                K.layernorm_fwd(x, P[pre + "norm.weight"], P[pre + "norm.bias"], xcat, gc["enc_m"], gc["enc_r"], rows,
+                                E, out_map=(g.n_kept, nt, g.kept_off))
+            else:
+                gc["enc_out"] = self._new(rows, E)
+                K.layernorm_fwd(x, P[pre + "norm.weight"], P[pre + "norm.bias"], gc["enc_out"], gc["enc_m"],
+                                gc["enc_r"], rows, E)
+        if self.inter_depth:
+            x, ctx["inter_saved"] = self.stack_fwd("encoder_inter.", xcat, B, nt, E, self.inter_depth, H, dh,
+                                                   self.mlp_e)
+            ctx["inter_pre_norm"] = x
+            for g in self.groups.values():
+                gc = ctx["groups"][g.name]
+                rows = B * g.n_kept
+                gc["int_m"], gc["int_r"] = self._new(rows, dtype=f32), self._new(rows, dtype=f32)
+                gc["enc_out"] = self._new(rows, E)
+                K.layernorm_fwd(x, P["encoder_inter.norm.weight"], P["encoder_inter.norm.bias"], gc["enc_out"],
+                                gc["int_m"], gc["int_r"], rows, E, in_map=(g.n_kept, nt, g.kept_off))
+
+        # 5. encoder -> decoder projection, unmask (+ decoder encodings), decoder, pixel projection
+        Hd, dhd = hp["decoder_heads"], hp["decoder_dim_head"]
+        for g in self.groups.values():
+            gc = ctx["groups"][g.name]
+            rows = B * g.n_kept
+            if E != Dd:
+                yd = self._new(rows, Dd)
+                self.lin_fwd(gc["enc_out"], rows, f"enc_to_dec.{g.name}.weight", f"enc_to_dec.{g.name}.bias", yd)
+            else:
+                yd = gc["enc_out"]
+            tok = torch.cat([P[f"mask_token.{x}"].reshape(-1, Dd) for x in g.mods], 0)
+            x_dec = self._new(B, g.L, Dd)
+            K.unmask_fwd(yd.view(B, g.n_kept, Dd), gc["mask"], gc["slot"], g.consts["tok_id"], gc["src_pos"], tok,
+                         g.consts["dec_pos"], gc["feat"], g.consts["date_id"], x_dec, self.date_dim, self.fac_date)
+            pre = f"decoder.{g.name}."
+            x, gc["dec_saved"] = self.stack_fwd(pre, x_dec.view(B * g.L, Dd), B, g.L, Dd, hp["decoder_depth"], Hd, dhd,
+                                                self.mlp_d)
+            gc["dec_pre_norm"] = x
+            for name in g.mods:
+                mt, mc = self.mods[name], ctx["mods"][name]
+                mc["xn"], mc["dec_m"], mc["dec_r"], mc["pred"] = [], [], [], []
+                seg_rows = B * mt.D * mt.L
+                for gi, c in enumerate(mt.band_groups):
+                    off = mt.tok_off + gi * mt.D * mt.L
+                    xn = self._new(seg_rows, Dd)
+                    m_, r_ = self._new(seg_rows, dtype=f32), self._new(seg_rows, dtype=f32)
+                    K.layernorm_fwd(x, P[pre + "norm.weight"], P[pre + "norm.bias"], xn, m_, r_, seg_rows, Dd,
+                                    in_map=(mt.D * mt.L, g.L, off))
+                    pw = f"embed_to_rec.{mt.embed}.pixelify_bands.{gi}.conv."
+                    pred = self._new(seg_rows, c * mt.p * mt.p)
+                    self.lin_fwd(xn, seg_rows, pw + "weight", pw + "bias", pred)
+                    mc["xn"].append(xn)
+                    mc["dec_m"].append(m_)
+                    mc["dec_r"].append(r_)
+                    mc["pred"].append(pred)
+        return ctx
+
+    # ------------------------------------------------------------------ loss (+ d loss / d pred)
+    def loss(self, ctx: dict, batch: dict, with_grad: bool = True, upstream: float = 1.0) -> torch.Tensor:
+        """Patch-group-normalised masked L1/L2 (train/model.py:195-247) over the step context.
+
+        Returns the fp32 device scalar; with ``with_grad`` also fills ``ctx['mods'][m]['dpred']``.
+        """
+        K, B = self.K, ctx["B"]
+        n_mod = len(self.mods)
+        counts = ctx["seg_counts"].to(torch.float32) @ self.segmat             # masked elements per modality
+        coef = (self.loss_w * upstream / counts).contiguous()
+        accum = self._zeros(n_mod, 2, dtype=torch.float64)
+        kind = self.loss_kind
+        for i, (name, mt) in enumerate(self.mods.items()):
+            mc, g = ctx["mods"][name], self.groups[mt.group]
+            gc = ctx["groups"][mt.group]
+            if with_grad:
+                mc["dpred"] = [torch.empty_like(p) for p in mc["pred"]]
+            K.loss_fwd_bwd(batch[name], mc["pred"], mc["dpred"] if with_grad else None, gc["mask"], coef[i:i + 1],
+                           accum[i], B, mt.D, mt.C, mt.S, mt.p, g.L, mt.tok_off, mt.band_groups,
+                           mt.loss_bands if kind.endswith("_norm") else None, kind.startswith("l2"))
+        per_mod = (accum[:, 0] / accum[:, 1]).to(torch.float32)
+        ctx["loss_per_mod"] = per_mod
+        return (per_mod * self.loss_w).sum()
+
+    # ------------------------------------------------------------------ backward
+    def backward(self, ctx: dict) -> None:
+        """Accumulate parameter gradients into the arena (``self.G``) from ``ctx['mods'][m]['dpred']``."""
+        K, P, G, f32 = self.K, self.P, self.G, torch.float32
+        E, Dd, hp, B = self.E, self.Dd, self.hp, ctx["B"]
+        H, dh = hp["heads"], hp["dim_head"]
+        Hd, dhd = hp["decoder_heads"], hp["decoder_dim_head"]
+        nt = self.n_kept_total
+        d_enc_out = {}
+        for g in self.groups.values():
+            gc = ctx["groups"][g.name]
+            pre = f"decoder.{g.name}."
+            dxd = self._new(B * g.L, Dd)
+            for name in g.mods:
+                mt, mc = self.mods[name], ctx["mods"][name]
+                seg_rows = B * mt.D * mt.L
+                for gi, c in enumerate(mt.band_groups):
+                    off = mt.tok_off + gi * mt.D * mt.L
+                    pw = f"embed_to_rec.{mt.embed}.pixelify_bands.{gi}.conv."
+                    dxn = self._new(seg_rows, Dd)
+                    self.lin_bwd(mc["dpred"][gi], seg_rows, mc["xn"][gi], pw + "weight", pw + "bias", dx=dxn)
+                    K.layernorm_bwd(dxn, gc["dec_pre_norm"], mc["dec_m"][gi], mc["dec_r"][gi], P[pre + "norm.weight"],
+                                    None, dxd, G[pre + "norm.weight"], G[pre + "norm.bias"], seg_rows, Dd,
+                                    in_map=(mt.D * mt.L, g.L, off))
+                mc["dpred"] = mc["xn"] = None
+            dxd = self.stack_bwd(pre, dxd, gc["dec_saved"], B, g.L, Dd, Hd, dhd, self.mlp_d)
+            # unmask backward: kept rows go back to the projection, masked rows feed the mask tokens
+            dxd3 = dxd.view(B, g.L, Dd)
+            dyd = self._new(B, g.n_kept, Dd)
+            K.gather_rows(dxd3, gc["uidx"], dyd)
+            dtok = self._zeros(sum(self.mods[x].G for x in g.mods), Dd, dtype=f32)
+            K.masktoken_grad(dxd3, gc["mask"], g.consts["tok_id"], gc["src_pos"], dtok)
+            k0 = 0
+            for x in g.mods:
+                Gx = self.mods[x].G
+                G[f"mask_token.{x}"].view(Gx, Dd).add_(dtok[k0:k0 + Gx])
+                k0 += Gx
+            rows = B * g.n_kept
+            if E != Dd:
+                de = self._new(rows, E)
+                self.lin_bwd(dyd.view(rows, Dd), rows, gc["enc_out"], f"enc_to_dec.{g.name}.weight",
+                             f"enc_to_dec.{g.name}.bias", dx=de)
+            else:
+                de = dyd.view(rows, E)
+            d_enc_out[g.name] = de
+
+        if self.inter_depth:
+            dxcat = self._new(B * nt, E)
+            for g in self.groups.values():
+                gc = ctx["groups"][g.name]
+                rows = B * g.n_kept
+                K.layernorm_bwd(d_enc_out[g.name], ctx["inter_pre_norm"], gc["int_m"], gc["int_r"],
+                                P["encoder_inter.norm.weight"], None, dxcat, G["encoder_inter.norm.weight"],
+                                G["encoder_inter.norm.bias"], rows, E, in_map=(g.n_kept, nt, g.kept_off))
+            dxcat = self.stack_bwd("encoder_inter.", dxcat, ctx["inter_saved"], B, nt, E, H, dh, self.mlp_e)
+
+        for g in self.groups.values():
+            gc = ctx["groups"][g.name]
+            pre = f"encoder.{g.name}."
+            rows = B * g.n_kept
+            dx = self._new(rows, E)
+            if self.inter_depth:
+                K.layernorm_bwd(dxcat, gc["enc_pre_norm"], gc["enc_m"], gc["enc_r"], P[pre + "norm.weight"], None, dx,
+                                G[pre + "norm.weight"], G[pre + "norm.bias"], rows, E,
+                                out_map=(g.n_kept, nt, g.kept_off))
+            else:
+                K.layernorm_bwd(d_enc_out[g.name], gc["enc_pre_norm"], gc["enc_m"], gc["enc_r"],
+                                P[pre + "norm.weight"], None, dx, G[pre + "norm.weight"], G[pre + "norm.bias"], rows, E)
+            dx = self.stack_bwd(pre, dx, gc["enc_saved"], B, g.n_kept, E, H, dh, self.mlp_e)
+            dxe = self._new(B, g.L, E)
+            K.scatter_kept(dx.view(B, g.n_kept, E), gc["mask"], gc["slot"], dxe)
+            for name in g.mods:
+                mt, mc = self.mods[name], ctx["mods"][name]
+                n_img, rows_m = B * mt.D, B * mt.D * mt.L
+                for gi, c in enumerate(mt.band_groups):
+                    pw = f"patch_embed.{mt.embed}.patchify_bands.{gi}."
+                    off = mt.tok_off + gi * mt.D * mt.L
+                    sums2 = self._zeros(n_img, 2, dtype=torch.float64)
+                    dconv = self._new(rows_m, E)
+                    K.gn_bwd(dxe, mc["y"][gi], mc["stats"][gi], P[pw + "norm.weight"], sums2, dconv,
+                             G[pw + "norm.weight"], G[pw + "norm.bias"], n_img, mt.D, mt.L, E, g.L, off)
+                    self.lin_bwd(dconv, rows_m, mc["cols"][gi], pw + "conv.weight", pw + "conv.bias", dx=None)
+
+    # ------------------------------------------------------------------ one training step (no optimiser)
+    def step(self, batch: dict, struct=None, noise=None, unmask_order=None) -> torch.Tensor:
+        ctx = self.forward(batch, struct, noise, unmask_order)
+        loss = self.loss(ctx, batch, with_grad=True)
+        self.backward(ctx)
+        return loss

@@ -30,7 +30,7 @@ def _date_channels(feat5, date_dim, fac):
 
 
 def _strided(t, off, shape, strides):
-    return torch.as_strided(t.reshape(-1), shape, strides, storage_offset=off)
+    return torch.as_strided(t, shape, strides, storage_offset=t.storage_offset() + off)
 
 
 class FakeKernels:
