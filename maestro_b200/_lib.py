@@ -46,7 +46,7 @@ def build(force: bool = False, verbose: bool = False) -> Path:
             rebuilt = True
         objs.append(str(obj))
     if rebuilt or not SO_PATH.exists():
-        cmd = [_nvcc(), "-shared", "-o", str(SO_PATH), *objs, "-lcudart"]
+        cmd = [_nvcc(), "-shared", "-Wno-deprecated-gpu-targets", "-o", str(SO_PATH), *objs, "-lcudart"]
         if verbose:
             print(" ".join(cmd))
         subprocess.run(cmd, check=True)

@@ -1,0 +1,363 @@
+"""GPU: every CUDA kernel (through the C-ABI) against its plain-torch definition in tests/fake_kernels.py."""
+
+import math
+
+import pytest
+import torch
+
+from fake_kernels import FakeKernels
+
+pytestmark = pytest.mark.gpu
+
+DT = [torch.float32, torch.bfloat16]
+
+
+@pytest.fixture(scope="module")
+def KK():
+    from maestro_b200.ops import Kernels
+    return Kernels(), FakeKernels()
+
+
+def tol(dt):
+    return dict(rtol=2e-5, atol=2e-5) if dt == torch.float32 else dict(rtol=2e-2, atol=2e-2)
+
+
+def rnd(*shape, dt=torch.float32, seed=0, scale=1.0):
+    g = torch.Generator(device="cpu").manual_seed(seed + sum(shape))
+    return (torch.randn(*shape, generator=g) * scale).to(dt).cuda()
+
+
+def both(KK, fn):
+    """Run fn(kernels) for the CUDA backend and the torch double; return both results."""
+    a = fn(KK[0])
+    torch.cuda.synchronize()
+    b = fn(KK[1])
+    return a, b
+
+
+def close(a, b, **kw):
+    torch.testing.assert_close(a.float(), b.float(), **kw)
+
+
+def test_casts(KK):
+    src = rnd(37, 264)
+
+    def run(K):
+        d1 = torch.zeros(37 * 264, dtype=torch.bfloat16, device="cuda")
+        d2 = torch.zeros(264, 37, dtype=torch.bfloat16, device="cuda")
+        K.cast_bf16(src.view(-1), d1)
+        K.cast_transpose_bf16(src, d2)
+        return d1, d2
+    (a1, a2), (b1, b2) = both(KK, run)
+    assert torch.equal(a1, b1) and torch.equal(a2, b2)
+
+
+@pytest.mark.parametrize("hin,hout,elev", [(12, 12, True), (6, 24, False), (9, 12, True), (8, 8, False)])
+def test_resize(KK, hin, hout, elev):
+    src = rnd(5, 3, hin, hin)
+
+    def run(K):
+        dst = torch.zeros(5, 3, hout, hout, device="cuda")
+        K.resize_nearest(src, dst, elev)
+        return dst
+    a, b = both(KK, run)
+    close(a, b, rtol=1e-6, atol=1e-6)
+
+
+@pytest.mark.parametrize("dt", DT)
+@pytest.mark.parametrize("S,p,C,c0,c", [(32, 16, 4, 0, 4), (6, 2, 10, 0, 10), (40, 20, 5, 1, 3)])
+def test_im2col_rows_image(KK, dt, S, p, C, c0, c):
+    img = rnd(3, C, S, S)
+    g = S // p
+
+    def run(K):
+        cols = torch.zeros(3 * g * g, c * p * p, dtype=dt, device="cuda")
+        K.im2col(img, cols, c0, c, p)
+        img2 = torch.zeros_like(img)
+        rows = rnd(3 * g * g, c * p * p, dt=dt, seed=5)
+        K.rows_image(rows, img2, c0, c, p, 0)
+        rows2 = torch.zeros_like(rows)
+        K.rows_image(rows2, img, c0, c, p, 1)
+        return cols, img2, rows2
+    a, b = both(KK, run)
+    for x, y in zip(a, b):
+        assert torch.equal(x, y)
+
+
+def test_date_features(KK):
+    g = torch.Generator().manual_seed(3)
+    dates = torch.stack([2019 + torch.randint(0, 2, (4, 7), generator=g), torch.randint(1, 366, (4, 7), generator=g),
+                         torch.randint(0, 24, (4, 7), generator=g)], -1).to(torch.int16).cuda()
+    ref = torch.tensor([[[2019, 182, 0]]], dtype=torch.int16).repeat(4, 1, 1).cuda()
+
+    def run(K):
+        feat = torch.zeros(4, 10, 5, device="cuda")
+        K.date_features(dates, ref, feat, 2)
+        return feat
+    a, b = both(KK, run)
+    close(a[..., :1], b[..., :1], rtol=0, atol=0)        # diff: same fp32 operation order -> bit exact
+    close(a, b, rtol=1e-6, atol=1e-6)
+
+
+@pytest.mark.parametrize("dt", DT)
+def test_colsum(KK, dt):
+    dy = rnd(777, 136, dt=dt)
+
+    def run(K):
+        out = torch.ones(136, device="cuda")
+        K.colsum_accum(dy, out)
+        return out
+    a, b = both(KK, run)
+    close(a, b, rtol=1e-4, atol=1e-3)
+
+
+@pytest.mark.parametrize("dt", DT)
+@pytest.mark.parametrize("d", [32, 64, 512, 768, 1024])
+def test_layernorm(KK, dt, d):
+    n, bs, off, Bn = 5, 9, 3, 4
+    rows = n * Bn
+    x = rnd(Bn * bs, d, dt=dt, seed=1)
+    dy = rnd(rows, d, dt=dt, seed=2)
+    dres = rnd(Bn * bs, d, dt=dt, seed=3)
+    gamma, beta = 1 + 0.1 * rnd(d, seed=4), 0.1 * rnd(d, seed=5)
+
+    def run(K):
+        y = torch.zeros(rows, d, dtype=dt, device="cuda")
+        mean, rstd = torch.zeros(rows, device="cuda"), torch.zeros(rows, device="cuda")
+        K.layernorm_fwd(x, gamma, beta, y, mean, rstd, rows, d, in_map=(n, bs, off))
+        dx = torch.zeros_like(x)
+        dg, db = torch.zeros(d, device="cuda"), torch.zeros(d, device="cuda")
+        K.layernorm_bwd(dy, x, mean, rstd, gamma, dres, dx, dg, db, rows, d, in_map=(n, bs, off))
+        y2 = torch.zeros(Bn * bs, d, dtype=dt, device="cuda")
+        K.layernorm_fwd(dy, gamma, beta, y2, None, None, rows, d, out_map=(n, bs, off))
+        return y, mean, rstd, dx, dg, db, y2
+    a, b = both(KK, run)
+    t = tol(dt)
+    for i, (p, q) in enumerate(zip(a, b)):
+        if i in (4, 5):
+            close(p, q, rtol=2e-2 if dt == torch.bfloat16 else 1e-4, atol=5e-2 if dt == torch.bfloat16 else 1e-4)
+        else:
+            close(p, q, **t)
+
+
+@pytest.mark.parametrize("dt", DT)
+@pytest.mark.parametrize("B,D,L,E", [(2, 3, 9, 64), (2, 1, 225, 64), (1, 1, 1024, 768)])
+def test_groupnorm(KK, dt, B, D, L, E):
+    n_img, bs, off = B * D, D * L + 11, 4
+    y = rnd(n_img * L, E, dt=dt, seed=1)
+    dyb = rnd(B, bs, E, dt=dt, seed=2)
+    gamma, beta, pos = 1 + 0.1 * rnd(E, seed=3), 0.1 * rnd(E, seed=4), rnd(L, E, seed=5)
+    feat = rnd(B, D + 2, 5, seed=6)
+
+    def run(K):
+        sums = torch.zeros(n_img, 2, dtype=torch.float64, device="cuda")
+        K.gn_stats(y, sums, n_img)
+        out = torch.zeros(B, bs, E, dtype=dt, device="cuda")
+        stats = torch.zeros(n_img, 2, device="cuda")
+        K.gn_apply(y, sums, gamma, beta, pos, feat, out, stats, n_img, D, L, E, 1e-5, bs, off, 8, 0.7, 1)
+        sums2 = torch.zeros(n_img, 2, dtype=torch.float64, device="cuda")
+        dconv = torch.zeros_like(y)
+        dg, db = torch.zeros(E, device="cuda"), torch.zeros(E, device="cuda")
+        K.gn_bwd(dyb, y, stats, gamma, sums2, dconv, dg, db, n_img, D, L, E, bs, off)
+        return sums.float(), out, stats, dconv, dg, db
+    a, b = both(KK, run)
+    t = tol(dt)
+    close(a[0], b[0], rtol=1e-5, atol=1e-3)
+    close(a[1], b[1], **t)
+    close(a[2], b[2], rtol=1e-5, atol=1e-5)
+    close(a[3], b[3], **t)
+    close(a[4], b[4], rtol=1e-3, atol=1e-1 if dt == torch.bfloat16 else 2e-3)
+    close(a[5], b[5], rtol=1e-3, atol=1e-1 if dt == torch.bfloat16 else 2e-3)
+
+
+@pytest.mark.parametrize("L,nm", [(18, 14), (50, 38), (200, 150), (1024, 768), (1500, 1125), (2048, 1536)])
+def test_mask_indices_bit_exact(KK, L, nm):
+    B = 7
+    g = torch.Generator().manual_seed(L)
+    noise = torch.rand(B, L, generator=g)
+    struct = torch.rand(B, L, generator=g) < 0.4
+    struct[1] = torch.rand(L, generator=g) < 0.9           # more zero keys than nm -> tie-break matters
+    struct[2] = False
+    noise[3, ::3] = noise[3, 0]                            # exact ties away from zero
+    noise, struct = noise.cuda(), struct.to(torch.uint8).cuda()
+    seg_id = (torch.arange(L) * 3 // L).to(torch.int32).cuda()
+
+    def run(K):
+        mask = torch.zeros(B, L, dtype=torch.uint8, device="cuda")
+        slot = torch.zeros(B, L, dtype=torch.int32, device="cuda")
+        mi = torch.zeros(B, nm, dtype=torch.int64, device="cuda")
+        ui = torch.zeros(B, L - nm, dtype=torch.int64, device="cuda")
+        cnt = torch.zeros(3, dtype=torch.int32, device="cuda")
+        K.mask_indices(noise, struct, nm, mask, slot, mi, ui, seg_id, cnt)
+        return mask, slot, mi, ui, cnt
+    a, b = both(KK, run)
+    for x, y in zip(a, b):
+        assert torch.equal(x, y)
+    mask, slot, mi, ui, cnt = a
+    assert int(mask.sum()) == B * nm and int(cnt.sum()) == B * nm
+    assert bool((mi[:, 1:] > mi[:, :-1]).all()) and bool((ui[:, 1:] > ui[:, :-1]).all())
+
+
+@pytest.mark.parametrize("dt", DT)
+def test_gather_scatter_unmask(KK, dt):
+    B, L, nm, d, Dtot = 3, 40, 30, 64, 5
+    x = rnd(B, L, d, dt=dt, seed=1)
+    noise = torch.rand(B, L, generator=torch.Generator().manual_seed(1)).cuda()
+    struct = torch.zeros(B, L, dtype=torch.uint8, device="cuda")
+    tok_id = (torch.arange(L) // 14).to(torch.int32).cuda()
+    date_id = (torch.arange(L) % Dtot).to(torch.int32).cuda()
+    tok, pos, feat = rnd(3, d, seed=2), rnd(L, d, seed=3), rnd(B, Dtot, 5, seed=4)
+    ykept = rnd(B, L - nm, d, dt=dt, seed=5)
+    dxd = rnd(B, L, d, dt=dt, seed=6)
+    src_pos = torch.stack([torch.randperm(L, generator=torch.Generator().manual_seed(i)) for i in range(B)]).to(
+        torch.int32).cuda()
+
+    def run(K):
+        mask = torch.zeros(B, L, dtype=torch.uint8, device="cuda")
+        slot = torch.zeros(B, L, dtype=torch.int32, device="cuda")
+        mi = torch.zeros(B, nm, dtype=torch.int64, device="cuda")
+        ui = torch.zeros(B, L - nm, dtype=torch.int64, device="cuda")
+        K.mask_indices(noise, struct, nm, mask, slot, mi, ui, tok_id, None)
+        kept = torch.zeros(B, L - nm, d, dtype=dt, device="cuda")
+        K.gather_rows(x, ui, kept)
+        dx = torch.ones(B, L, d, dtype=dt, device="cuda")
+        K.scatter_kept(ykept, mask, slot, dx)
+        outs = []
+        for sp in (None, src_pos):
+            out = torch.zeros(B, L, d, dtype=dt, device="cuda")
+            K.unmask_fwd(ykept, mask, slot, tok_id, sp, tok, pos, feat, date_id, out, 8, 1.3)
+            dtok = torch.zeros(3, d, device="cuda")
+            K.masktoken_grad(dxd, mask, tok_id, sp, dtok)
+            outs += [out, dtok]
+        return (kept, dx, *outs)
+    a, b = both(KK, run)
+    assert torch.equal(a[0], b[0]) and torch.equal(a[1], b[1])
+    t = tol(dt)
+    close(a[2], b[2], **t)
+    close(a[4], b[4], **t)
+    close(a[3], b[3], rtol=1e-3, atol=1e-2)
+    close(a[5], b[5], rtol=1e-3, atol=1e-2)
+
+
+@pytest.mark.parametrize("dt", DT)
+@pytest.mark.parametrize("S,p,bands,norm,D,l2", [(32, 16, [4], [1, 3], 1, False), (6, 2, [10], [4, 4, 2], 3, False),
+                                                 (6, 2, [2], [1, 1], 2, True), (64, 32, [2], None, 1, False),
+                                                 (8, 2, [2, 3], [1, 4], 2, False)])
+def test_loss(KK, dt, S, p, bands, norm, D, l2):
+    B, C, g = 3, sum(bands), S // p
+    L, G = g * g, len(bands)
+    Lg, moff = G * D * L + 5, 2
+    target = rnd(B * D, C, S, S, seed=1)
+    preds = [rnd(B * D * L, c * p * p, dt=dt, seed=2 + i) for i, c in enumerate(bands)]
+    mask = (torch.rand(B, Lg, generator=torch.Generator().manual_seed(9)) < 0.7).to(torch.uint8).cuda()
+    coef = torch.tensor([0.37], device="cuda")
+
+    def run(K):
+        dpreds = [torch.ones_like(x) for x in preds]
+        accum = torch.zeros(2, dtype=torch.float64, device="cuda")
+        K.loss_fwd_bwd(target, preds, dpreds, mask, coef, accum, B, D, C, S, p, Lg, moff, bands, norm, l2)
+        return (accum.float(), *dpreds)
+    a, b = both(KK, run)
+    close(a[0], b[0], rtol=2e-5, atol=1e-3)
+    for x, y in zip(a[1:], b[1:]):
+        if l2:
+            close(x, y, **tol(dt))
+        else:                                             # sign gradient: allow flips only where |diff| ~ 0
+            bad = (x.float() - y.float()).abs() > 1e-3
+            assert bad.float().mean() < 1e-4
+
+
+def _gemm_case(K, dt, M, N, Kd, layout, flags, seed=0):
+    A = rnd(M, Kd, dt=dt, seed=seed + 1, scale=0.5)
+    Bm = rnd(N, Kd, dt=dt, seed=seed + 2, scale=0.5)
+    bias = rnd(N, seed=seed + 3)
+    res = rnd(M, N, dt=dt, seed=seed + 4)
+    return A, Bm, bias, res
+
+
+@pytest.mark.parametrize("dt", DT)
+@pytest.mark.parametrize("M,N,Kd", [(200, 96, 64), (1000, 768, 768), (333, 3072, 768), (4096, 512, 3072),
+                                    (130, 8, 512), (1600, 768, 40), (70, 768, 8), (128, 256, 1024), (257, 264, 72)])
+def test_gemm_kmajor_epilogues(KK, dt, M, N, Kd):
+    """Forward-layer layout (both operands K-contiguous): plain, bias+GELU(aux), DGELU, bias+residual."""
+    A, Bm, bias, res = _gemm_case(None, dt, M, N, Kd, "k", 0)
+    auxin = rnd(M, N, dt=dt, seed=7)
+
+    def run(K):
+        outs = []
+        for mode in ("plain", "gelu", "dgelu", "biasres", "f32out"):
+            Cm = torch.zeros(M, N, dtype=torch.float32 if mode == "f32out" else dt, device="cuda")
+            aux = torch.zeros(M, N, dtype=dt, device="cuda") if mode == "gelu" else (auxin.clone() if mode == "dgelu" else None)
+            K.gemm(A, Bm, Cm, M, N, Kd, sam=Kd, sak=1, sbn=Kd, sbk=1, ldc=N,
+                   bias=bias if mode in ("gelu", "biasres") else None,
+                   residual=res if mode == "biasres" else None, aux=aux,
+                   flags={"gelu": 1, "dgelu": 2}.get(mode, 0))
+            outs.append(Cm)
+            if mode == "gelu":
+                outs.append(aux)
+        return outs
+    a, b = both(KK, run)
+    ref_scale = math.sqrt(Kd) * 0.25
+    for x, y in zip(a, b):
+        close(x, y, rtol=2e-2 if dt == torch.bfloat16 else 1e-4, atol=(2e-2 if dt == torch.bfloat16 else 1e-4) * ref_scale)
+
+
+@pytest.mark.parametrize("dt", DT)
+@pytest.mark.parametrize("T,N,Kd", [(1000, 768, 768), (5000, 3072, 768), (640, 768, 8), (333, 40, 512), (64, 96, 64),
+                                    (100, 2304, 768), (9000, 512, 3072)])
+def test_gemm_wgrad_and_dgrad_layouts(KK, dt, T, N, Kd):
+    """wgrad: dW[n,k] += sum_t dY[t,n] X[t,k] (MN-major operands, fp32 accumulate); dgrad with W^T."""
+    dY = rnd(T, N, dt=dt, seed=1, scale=0.5)
+    X = rnd(T, Kd, dt=dt, seed=2, scale=0.5)
+    W = rnd(N, Kd, dt=dt, seed=3, scale=0.5)
+    WT = W.t().contiguous()
+
+    def run(K):
+        dW = torch.full((N, Kd), 0.5, dtype=torch.float32, device="cuda")
+        K.gemm(dY, X, dW, N, Kd, T, sam=1, sak=N, sbn=1, sbk=Kd, ldc=Kd, flags=4)
+        dX = torch.zeros(T, Kd, dtype=dt, device="cuda")
+        K.gemm(dY, WT, dX, T, Kd, N, sam=N, sak=1, sbn=N, sbk=1, ldc=Kd)
+        dX2 = torch.zeros(T, Kd, dtype=dt, device="cuda")
+        K.gemm(dY, W, dX2, T, Kd, N, sam=N, sak=1, sbn=1, sbk=Kd, ldc=Kd)   # strided B (fp32 check-mode form)
+        return dW, dX, dX2
+    a, b = both(KK, run)
+    close(a[0], b[0], rtol=1e-3, atol=2e-3 * math.sqrt(T))
+    s = math.sqrt(N) * 0.25
+    for x, y in zip(a[1:], b[1:]):
+        close(x, y, rtol=2e-2 if dt == torch.bfloat16 else 1e-4, atol=(2e-2 if dt == torch.bfloat16 else 1e-4) * s)
+
+
+@pytest.mark.parametrize("dt", DT)
+def test_batched_gemm_and_softmax(KK, dt):
+    Bn, H, N, dh = 2, 3, 50, 16
+    inner = H * dh
+    qkv = rnd(Bn * N, 3 * inner, dt=dt, seed=1)
+
+    def run(K):
+        s = torch.zeros(Bn * H * N * N, device="cuda")
+        K.gemm(qkv, qkv, s, N, N, dh, sam=3 * inner, sak=1, sbn=3 * inner, sbk=1, ldc=N, nb1=Bn, nb2=H,
+               a_s=(N * 3 * inner, dh), b_s=(N * 3 * inner, dh), c_s=(H * N * N, N * N), b_off=inner)
+        p = torch.zeros(Bn * H * N * N, dtype=dt, device="cuda")
+        K.softmax_rows(s, p, Bn * H * N, N, dh ** -0.5)
+        dp = rnd(Bn * H * N * N, seed=3)
+        ds = torch.zeros_like(p)
+        K.softmax_bwd_rows(p, dp, ds, Bn * H * N, N, dh ** -0.5)
+        return s, p, ds
+    a, b = both(KK, run)
+    for x, y in zip(a, b):
+        close(x, y, **tol(dt))
+
+
+def test_adamw(KK):
+    n = 4096 + 8
+    p0, g0, m0, v0 = rnd(n, seed=1), rnd(n, seed=2), rnd(n, seed=3) * 0.1, rnd(n, seed=4).abs() * 0.01
+    hyper = torch.tensor([1e-3, 0.9, 0.999, 1e-8, 0.01, 1 - 0.9 ** 3, 1 - 0.999 ** 3, 0.5], device="cuda")
+
+    def run(K):
+        p, g, m, v = p0.clone(), g0.clone(), m0.clone(), v0.clone()
+        sh = torch.zeros(n, dtype=torch.bfloat16, device="cuda")
+        K.adamw_step(p, g, m, v, sh, hyper, True)
+        return p, g, m, v, sh
+    a, b = both(KK, run)
+    for x, y in zip(a, b):
+        close(x, y, rtol=1e-5, atol=1e-6 if x.dtype == torch.float32 else 1e-2)
