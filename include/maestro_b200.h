@@ -1,0 +1,142 @@
+/* maestro_b200 -- C ABI of the B200 (sm_100a) kernels behind MAESTRO's MAE pretraining step.
+ *
+ * The reference (IGNF/MAESTRO) is pure Python on eager PyTorch: it has no FFI of its own.  The drop-in boundary is
+ * the Python module interface of maestro/layers + maestro/ssl; this header is what sits underneath
+ * it.  Every entry point replaces the torch ops of the reference lines cited beside it.
+ *
+ * Conventions: plain pointers and sizes, no torch types.  All pointers are DEVICE pointers unless said otherwise.
+ * `dtype` selects the activation type of the `void*` tensors: 0 = float32 (fp32 check mode), 1 = bfloat16.
+ * `stream` is a cudaStream_t.  Return value: 0 on success, a cudaError_t (> 0) or a negative argument-check code.
+ * Kernels never allocate; callers own every buffer.  Functions are re-entrant.
+ */
+#ifndef MAESTRO_B200_H
+#define MAESTRO_B200_H
+
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MB_DTYPE_F32 0
+#define MB_DTYPE_BF16 1
+
+/* Row map: logical row r of a [rows, d] matrix lives at physical row (r / n) * bs + off + (r % n).
+ * It folds the reference's torch.cat / split around encoder_inter (maestro/ssl/mim.py:406-423) and the
+ * ungroup before Pixelify (maestro/ssl/mim.py:326-341) into the LayerNorm pass.  Identity: n = rows, bs = 0, off = 0. */
+
+/* ---- data movement ------------------------------------------------------------------------------------------ */
+/* fp32 master weights -> bf16 shadow (what torch autocast does per op, maestro/conf/trainer.py:13). */
+int mb_cast_f32_to_bf16(const float* src, void* dst, size_t n, void* stream);
+/* dst[C, R] = bf16(src[R, C]^T): transposed shadow read by the dgrad GEMMs. */
+int mb_cast_transpose_f32_to_bf16(const float* src, void* dst, int R, int C, void* stream);
+/* BaseMIM.resize_and_rescale, maestro/ssl/mim.py:425-437 (F.interpolate nearest + DEM 30*(ch0-ch)). */
+int mb_resize_nearest(const float* src, float* dst, int n_img, int C, int hin, int win, int hout, int wout,
+                      int rescale_elev, void* stream);
+/* Patch extraction of the strided conv in PatchifyBands, maestro/layers/embed.py:57-60. */
+int mb_im2col(const float* img, void* cols, int dtype, int n_img, int C, int c0, int c, int S, int p, int Kpad,
+              void* stream);
+/* PixelifyBands depth-to-space "(p1 p2 c) h w -> c (h p1) (w p2)", maestro/layers/embed.py:155-160 (dir 0) / adjoint. */
+int mb_rows_image(void* rows, int dtype, float* img, int n_img, int C, int c0, int c, int S, int p, int dir,
+                  void* stream);
+/* encode_dates features, maestro/layers/utils.py:128-160: int16 (year, doy, hour) -> (diff, sin/cos doy, sin/cos hour). */
+int mb_date_features(const short* dates, const short* ref, float* feat, int B, int D, int Dtot, int doff, void* stream);
+/* Bias gradients: out[n] += sum_m dy[m, n] (autograd of nn.Linear / nn.Conv2d bias). */
+int mb_colsum_accum(const void* dy, int dtype, float* out, int M, int N, void* stream);
+
+/* ---- normalisation ------------------------------------------------------------------------------------------ */
+/* nn.LayerNorm inside vit_pytorch Attention / FeedForward / Transformer.norm (built at maestro/ssl/mae.py:133-176). */
+int mb_layernorm_fwd(const void* x, const float* gamma, const float* beta, void* y, float* mean, float* rstd,
+                     int dtype, int rows, int d, float eps, int in_n, int in_bs, int in_off, int out_n, int out_bs,
+                     int out_off, void* stream);
+/* Its backward, fused with the residual-gradient add (x = f(LN(x)) + x). dgamma / dbeta accumulate. */
+int mb_layernorm_bwd(const void* dy, const void* x, const float* mean, const float* rstd, const float* gamma,
+                     const void* dres, void* dx, float* dgamma, float* dbeta, int dtype, int rows, int d, int in_n,
+                     int in_bs, int in_off, int out_n, int out_bs, int out_off, void* stream);
+/* nn.GroupNorm(1, E) of PatchifyBands, maestro/layers/embed.py:55,61: per-image sum / sum-of-squares (fp64). */
+int mb_gn_stats(const void* y, int dtype, double* sums, int n_img, long long elems_per_img, void* stream);
+/* GroupNorm apply + enc_add_encodings (maestro/ssl/mim.py:232-252) + group_mods concat (layers/utils.py:12-47). */
+int mb_gn_apply(const void* y, const double* sums, const float* gamma, const float* beta, const float* pos,
+                const float* feat, void* out, float* stats_out, int dtype, int n_img, int D, int L, int E, float eps,
+                int out_bs, int out_off, int date_dim, float fac_date, int feat_bs, int feat_off, void* stream);
+int mb_gn_bwd(const void* dy, const void* y, const float* stats, const float* gamma, double* sums2, void* dconv,
+              float* dgamma, float* dbeta, int dtype, int n_img, int D, int L, int E, int out_bs, int out_off,
+              void* stream);
+
+/* ---- masking ------------------------------------------------------------------------------------------------ */
+/* MAE.mask_seq index math, maestro/ssl/mae.py:239-259 (rand*struct -> argsort -> argsort -> gather -> sort x2). */
+int mb_mask_indices(const float* noise, const unsigned char* structm, int B, int L, int nm, unsigned char* mask,
+                    int* slot, long long* masked_idx, long long* unmasked_idx, const int* seg_id, int* seg_counts,
+                    void* stream);
+/* x[batch_indices, unmasked_indices], maestro/ssl/mae.py:261. */
+int mb_gather_rows(const void* x, const long long* idx, void* out, int dtype, int B, int L, int n, int d, void* stream);
+/* Its gradient (index_put of zeros + kept rows). */
+int mb_scatter_kept(const void* dkept, const unsigned char* mask, const int* slot, void* dx, int dtype, int B, int L,
+                    int n, int d, void* stream);
+/* MAE.unmask_seq (maestro/ssl/mae.py:266-287) fused with dec_add_encodings (maestro/ssl/mim.py:254-274). */
+int mb_unmask_fwd(const void* y, const unsigned char* mask, const int* slot, const int* tok_id, const int* src_pos,
+                  const float* tok, const float* pos, const float* feat, const int* date_id, void* out, int dtype,
+                  int B, int L, int n_kept, int d, int Dtot, int date_dim, float fac_date, void* stream);
+int mb_masktoken_grad(const void* dx, const unsigned char* mask, const int* tok_id, const int* src_pos, float* dtok,
+                      int dtype, int B, int L, int d, int n_kinds, void* stream);
+
+/* ---- loss --------------------------------------------------------------------------------------------------- */
+#define MB_LOSS_MAX_C 16
+#define MB_LOSS_MAX_G 4
+typedef struct {
+  const float* target;              /* [B*D, C, S, S] */
+  const void* pred[MB_LOSS_MAX_G];  /* per band-group rows [B*D*L, c_g*p*p], column order (py, px, c) */
+  void* dpred[MB_LOSS_MAX_G];       /* gradient rows or NULL */
+  const unsigned char* mask;        /* group token mask [B, Lg] */
+  const float* coef;                /* device scalar: w_mod / (sum_w * count_mod) * upstream */
+  double* accum;                    /* [2]: sum of errors, number of masked elements */
+  int B, D, C, S, p, G;
+  int Lg, mask_off;
+  int cg[MB_LOSS_MAX_G], c0[MB_LOSS_MAX_G];
+  int n_norm;
+  int norm_of_ch[MB_LOSS_MAX_C];
+  int norm_size[MB_LOSS_MAX_C];
+  int l2;
+} mb_loss_params;                   /* `params` below is a HOST pointer */
+/* SSLModule.compute_loss_rec, maestro/train/model.py:195-247 (+ norm_bands / loss_fn select :38-67), fwd + grad. */
+int mb_loss_fwd_bwd(const mb_loss_params* params, int dtype, void* stream);
+
+/* ---- contractions ------------------------------------------------------------------------------------------- */
+#define MB_GEMM_GELU 1
+#define MB_GEMM_DGELU 2
+#define MB_GEMM_ACCUM 4
+#define MB_GEMM_OUT_F32 8
+typedef struct {
+  const void* A;         /* A(m, k) = A[m * sam + k * sak] */
+  const void* B;         /* B(n, k) = B[n * sbn + k * sbk] */
+  void* C;               /* C[m * ldc + n] */
+  const float* bias;
+  const void* residual;
+  void* aux;
+  int M, N, K;
+  long long sam, sak, sbn, sbk;
+  int ldc;
+  int nb1, nb2;
+  long long a_s1, a_s2, b_s1, b_s2, c_s1, c_s2;
+  float alpha;
+  int flags;
+} mb_gemm_params;                   /* `params` below is a HOST pointer */
+/* nn.Linear / nn.Conv2d(k=p,s=p) / 1x1 conv and their autograd (vit_pytorch to_qkv / to_out / FeedForward,
+ * maestro/layers/embed.py:59-60,148-154, maestro/ssl/mae.py:145-154) on the CUDA cores: fp32 check mode. */
+int mb_gemm_simt(const mb_gemm_params* params, int dtype, void* stream);
+/* The same contractions on tcgen05 tensor cores (bf16 in, fp32 accumulate in TMEM, TMA operand staging). */
+int mb_gemm_tc(const mb_gemm_params* params, void* stream);
+/* softmax(q k^T * scale) of vit_pytorch Attention.attend (check-mode path) and its gradient. */
+int mb_softmax_rows(const float* s, void* p, int dtype, long long rows, int n, float scale, void* stream);
+int mb_softmax_bwd_rows(const void* p, float* dp, void* ds, int dtype, long long rows, int n, float scale,
+                        void* stream);
+
+/* ---- optimiser ---------------------------------------------------------------------------------------------- */
+/* torch.optim.AdamW built at maestro/train/model.py:135-149, fused over the flat arena (+ bf16 shadow refresh). */
+int mb_adamw_step(float* p, float* g, float* m, float* v, void* shadow, const float* hyper, size_t n, int zero_grad,
+                  void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MAESTRO_B200_H */
