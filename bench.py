@@ -1,0 +1,301 @@
+"""Benchmark of the MAE pretraining step (BASELINE.json metric: pretrain tiles/sec, ViT-B, FLAIR-HUB shape).
+
+    python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path (one process per GPU)
+    python bench.py --impl reference --steps K --warmup W    # the reference algorithm on the host cores
+
+A step = forward + loss + backward (+ gradient all-reduce for N > 1) + AdamW over one batch of synthetic
+FLAIR-HUB-shaped tiles with random-init ViT-B weights.  Rank 0 prints ONE JSON line.
+"""
+
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+from maestro_b200.conf import DATASET_SPECS, MODEL_SIZES, MaskSpec  # noqa: E402
+
+STEP_GFLOP = {"flair": 431.9, "treesatai_ts": 94.6, "s2_naip": 301.3, "pastis_hd": 1009.3}  # SURVEY 8(d), per tile
+
+
+def synthetic_batch(spec, B, seed, pin=False):
+    """Host tensors with the value ranges the reference data pipeline leaves (dataset/dataset.py:215-222)."""
+    g = torch.Generator().manual_seed(seed)
+    out = {}
+    for name, m in spec.inputs.items():
+        x = torch.rand(B, m.num_dates, m.channels, m.raw_size, m.raw_size, generator=g)
+        if name.startswith("s1"):
+            x = -1.0 + 0.5 * (x - 0.5) * 3.4
+        if m.rescale_elev:
+            x[:, :, 1:] = x[:, :, :1] - 0.03 * x[:, :, 1:]
+        dates = torch.stack([2019 + torch.randint(0, 2, (B, m.num_dates), generator=g),
+                             torch.randint(1, 366, (B, m.num_dates), generator=g),
+                             torch.randint(0, 24, (B, m.num_dates), generator=g)], -1).to(torch.int16)
+        out[name], out[f"{name}_dates"] = x, dates
+    out["ref_date"] = torch.tensor([[[2019, 182, 0]]], dtype=torch.int16).repeat(B, 1, 1)
+    if pin:
+        out = {k: v.pin_memory() for k, v in out.items()}
+    return out
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled during the timed region."""
+
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int) -> None:
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm = sorted(float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit())
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) > 3 + i and r[3 + i] == "Active" for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(self.rows)}
+
+
+def measured_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            p = json.load(f)
+        return p["hbm_gbs"], p["bf16_tflops"], p.get("bf16_tflops_sustained", p["bf16_tflops"]), "measured"
+    except (OSError, KeyError, ValueError):
+        return 6650.0, 1590.0, 1400.0, "fallback"
+
+
+# ------------------------------------------------------------------------------------------ CPU arms
+def cpu_reference_step_time(dataset, size, batch, steps, warmup, threads):
+    """Oracle (CPU restatement of the reference, torch fp32 autograd) forward + backward, seconds per step."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import mae_oracle as O
+    import synth
+    torch.set_num_threads(threads)
+    spec, hp = DATASET_SPECS[dataset](), MODEL_SIZES[size]
+    inter = 3
+    sd = synth.synthetic_state_dict(synth.param_shapes(spec, hp, inter), seed=0)
+    sd = {k: v.requires_grad_(True) for k, v in sd.items()}
+    batch_t = synthetic_batch(spec, batch, seed=1)
+    mc = MaskSpec()
+    times = []
+    for i in range(warmup + steps):
+        t0 = time.perf_counter()
+        struct = O.struct_mask(spec, mc, batch)
+        noise = {g: torch.rand(batch, spec.group_tokens(g)) for g in spec.group_names}
+        out = O.forward(sd, spec, hp, dict(batch_t), struct, noise, mc, inter_depth=inter)
+        loss, _ = O.reconstruction_loss(out["batch"], out["pixels"], out["mask_px"], spec, "l1_norm")
+        loss.backward()
+        for v in sd.values():
+            v.grad = None
+        dt = time.perf_counter() - t0
+        if i >= warmup:
+            times.append(dt)
+    return sum(times) / len(times)
+
+
+def run_reference(args):
+    """--impl reference: the reference's algorithm on this box's host cores (oracle port; the reference itself
+    is pure Python over eager torch and /root/reference does not exist on the GPU box)."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    B = args.cpu_batch
+    sec = cpu_reference_step_time(args.dataset, args.size, B, max(1, args.steps), max(1, args.warmup), threads)
+    val = B / sec
+    line = {
+        "impl": "reference", "metric": "pretrain_tiles_per_sec", "value": val, "unit": "tiles/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"MAESTRO ViT-B ({args.size}) MAE pretrain step, {args.dataset} shapes, "
+                               f"fwd+bwd on host cores, batch {B}"},
+        "cpu_baseline": {"value": val, "unit": "tiles/s", "cores": threads, "kind": "port",
+                         "sample": f"{args.steps} steps of batch {B} (fp32 torch on CPU, oracle/mae_oracle.py)"},
+        "e2e": {"value": val, "unit": "tiles/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+def run_ours(args):
+    import torch.distributed as dist
+
+    from maestro_b200.engine import PretrainEngine
+    from maestro_b200.ops import Kernels
+    from maestro_b200.optim import FusedAdamW, OneCycle
+
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    spec, hp = DATASET_SPECS[args.dataset](), MODEL_SIZES[args.size]
+    B = args.batch
+    K = Kernels()
+    eng = PretrainEngine(spec, hp, MaskSpec(), K, dev, torch.bfloat16, inter_depth=3, loss="l1_norm")
+    eng.init_random(0)
+    opt = FusedAdamW(eng, lr=1e-4, weight_decay=0.01, schedule=OneCycle(1e-4, 100000))
+    host = [synthetic_batch(spec, B, seed=100 + 7 * rank + i, pin=True) for i in range(2)]
+    devb = {k: v.to(dev) for k, v in host[0].items()}
+    h2d = sum(v.numel() * v.element_size() for v in host[0].values())
+    loss_host = torch.zeros(1).pin_memory()
+    torch.manual_seed(1234 + rank)
+
+    def step_device(batch):
+        loss = eng.step(dict(batch))
+        if world > 1:
+            dist.all_reduce(eng.arena.grad)
+        opt.step(grad_scale=1.0 / world)
+        return loss
+
+    def step_e2e(i):
+        hb = host[i % 2]
+        for k, v in hb.items():
+            devb[k].copy_(v, non_blocking=True)
+        loss = step_device(devb)
+        loss_host.copy_(loss.reshape(1), non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return float(loss_host[0])
+
+    def timed(fn, steps):
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(steps):
+            fn(i)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.barrier()
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms[0])
+
+    for i in range(args.warmup):
+        step_e2e(i)
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    l0 = K.launches
+    ms_dev = timed(lambda i: step_device(devb), args.steps)
+    launches = (K.launches - l0) // args.steps
+    ms_e2e = timed(step_e2e, args.steps)
+    clocks = sampler.stop() if rank == 0 else None
+    last_loss = float(loss_host[0])
+
+    # ---- per-kernel roofline, measured live: one instrumented step, CUDA events around every GEMM launch
+    rec = []
+    orig_gemm = K.gemm
+
+    def gemm_probe(A, Bm, Cm, M, N, Kd, *a, **kw):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        nb = kw.get("nb1", 1) * kw.get("nb2", 1)
+        tc = nb == 1 and A.dtype == torch.bfloat16
+        e0.record()
+        orig_gemm(A, Bm, Cm, M, N, Kd, *a, **kw)
+        e1.record()
+        rec.append((tc, 2.0 * M * N * Kd * nb, e0, e1))
+    K.gemm = gemm_probe
+    step_device(devb)
+    torch.cuda.synchronize()
+    K.gemm = orig_gemm
+    tc_fl = sum(r[1] for r in rec if r[0])
+    tc_ms = sum(r[2].elapsed_time(r[3]) for r in rec if r[0])
+    at_fl = sum(r[1] for r in rec if not r[0])
+    at_ms = sum(r[2].elapsed_time(r[3]) for r in rec if not r[0])
+    n_tc = sum(1 for r in rec if r[0])
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    hbm, tf_burst, tf_sus, src = measured_peaks()
+    step_ms, e2e_ms = ms_dev / args.steps, ms_e2e / args.steps
+    value = B * world / (step_ms * 1e-3)
+    achieved = tc_fl / (tc_ms * 1e-3) / 1e12 if tc_ms > 0 else 0.0
+    cpu = None
+    if world == 1 and not args.no_cpu_baseline:
+        threads = os.cpu_count() or 1
+        sec = cpu_reference_step_time(args.dataset, args.size, args.cpu_batch, 2, 1, threads)
+        cpu = {"value": args.cpu_batch / sec, "unit": "tiles/s", "cores": threads, "kind": "port",
+               "sample": f"2 steps of batch {args.cpu_batch} after 1 warm-up (fp32 torch on CPU, oracle/mae_oracle.py)"}
+    line = {
+        "metric": "pretrain_tiles_per_sec", "value": value, "unit": "tiles/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": step_ms, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+        "config": {"workload": f"MAESTRO ViT-B ({args.size}) MAE pretrain step (fwd+loss+bwd+allreduce+AdamW), "
+                               f"{args.dataset} shapes, mask 0.75, inter_depth 3, {B} tiles/GPU",
+                   "global_batch": B * world, "parallelism": f"dp{world}",
+                   "l2": "inputs larger than L2 (activations >> 126 MB per step); no flush",
+                   "attention": eng.attn_impl, "loss_last": last_loss},
+        "e2e": {"value": B * world / (e2e_ms * 1e-3), "unit": "tiles/s", "h2d_bytes_per_step": h2d,
+                "d2h_bytes_per_step": 4, "ms_per_step": e2e_ms},
+        "gpu_launches": launches,
+        "clocks": clocks,
+        "roofline": {"bound": "tensor", "kernel": "gemm_tc_kernel (tcgen05 GEMM, all linear layers fwd/dgrad/wgrad)",
+                     "achieved": achieved, "peak": tf_sus, "unit": "TFLOP/s", "frac": achieved / tf_sus,
+                     "traffic": None, "peak_source": f"{src} (sustained)", "launches": n_tc,
+                     "avg_launch_ms": tc_ms / max(1, n_tc), "share_of_step": tc_ms / step_ms},
+        "step_roofline": {"gflop_per_tile": STEP_GFLOP.get(args.dataset), "achieved_tflops": value *
+                          STEP_GFLOP.get(args.dataset, 0) / 1e3 / world, "peak": tf_sus,
+                          "frac": value * STEP_GFLOP.get(args.dataset, 0) / 1e3 / world / tf_sus},
+        "attention_gemm": {"tflops": at_fl / (at_ms * 1e-3) / 1e12 if at_ms > 0 else None, "ms": at_ms},
+        "cpu_baseline": cpu,
+    }
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--dataset", default="flair", choices=list(DATASET_SPECS))
+    ap.add_argument("--size", default="medium", choices=list(MODEL_SIZES))
+    ap.add_argument("--batch", type=int, default=32, help="tiles per GPU (reference default, conf/opt.py:20)")
+    ap.add_argument("--cpu-batch", type=int, default=2)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        if not torch.cuda.is_available():
+            raise SystemExit("bench.py: no CUDA device (the product has no CPU path); use --impl reference for the CPU arm")
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

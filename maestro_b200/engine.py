@@ -725,3 +725,18 @@ class PretrainEngine:
         loss = self.loss(ctx, batch, with_grad=True)
         self.backward(ctx)
         return loss
+
+    # ------------------------------------------------------------------ initialisation
+    def init_random(self, seed: int = 0) -> None:
+        """Random-init weights of the architecture (torch-default-like scales), generated on the device."""
+        gen = torch.Generator(device=self.device).manual_seed(seed)
+        for name, p in self.P.items():
+            if name.startswith("mask_token."):
+                p.copy_(torch.randn(p.shape, generator=gen, device=self.device))
+            elif p.dim() == 1:
+                is_gain = name.endswith("norm.weight") or name.endswith("net.0.weight")
+                p.fill_(1.0 if is_gain else 0.0)
+            else:
+                fan_in = p.numel() // p.shape[0]
+                p.copy_(torch.randn(p.shape, generator=gen, device=self.device) * (fan_in ** -0.5))
+        self.shadows_fresh = False

@@ -1,0 +1,60 @@
+"""Fused AdamW + OneCycleLR over the engine's flat arena (reference: SSLModule.configure_optimizers,
+maestro/train/model.py:120-158 -- torch AdamW stepped per batch by a OneCycleLR scheduler)."""
+
+from __future__ import annotations
+
+import math
+
+import torch
+
+
+class OneCycle:
+    """torch.optim.lr_scheduler.OneCycleLR (cos anneal, two phases) as a pure function of the step."""
+
+    def __init__(self, max_lr: float, total_steps: int, pct_start: float = 0.3, div_factor: float = 25.0,
+                 final_div_factor: float = 1e4) -> None:
+        self.max_lr, self.total = max_lr, max(2, int(total_steps))
+        self.initial = max_lr / div_factor
+        self.minimum = self.initial / final_div_factor
+        self.up_end = float(pct_start * self.total) - 1
+
+    @staticmethod
+    def _cos(start: float, end: float, pct: float) -> float:
+        return end + (start - end) / 2.0 * (math.cos(math.pi * pct) + 1)
+
+    def lr(self, step: int) -> float:
+        if step <= self.up_end:
+            return self._cos(self.initial, self.max_lr, step / self.up_end)
+        pct = (step - self.up_end) / (self.total - 1 - self.up_end)
+        return self._cos(self.max_lr, self.minimum, min(1.0, pct))
+
+
+class FusedAdamW:
+    """One kernel per step over (param, grad, m, v); refreshes the bf16 shadow and zeroes the gradient."""
+
+    def __init__(self, engine, lr: float = 1e-4, betas=(0.9, 0.999), eps: float = 1e-8, weight_decay: float = 0.01,
+                 schedule: OneCycle | None = None) -> None:
+        self.engine, self.K = engine, engine.K
+        a = engine.arena
+        self.m = torch.zeros_like(a.param)
+        self.v = torch.zeros_like(a.param)
+        self.lr, self.betas, self.eps, self.wd, self.schedule = lr, betas, eps, weight_decay, schedule
+        self.t = 0
+        self.hyper = torch.zeros(8, dtype=torch.float32, device=a.param.device)
+        self.hyper_host = torch.zeros(8, dtype=torch.float32).pin_memory() if a.param.is_cuda else torch.zeros(8)
+
+    def step(self, grad_scale: float = 1.0) -> None:
+        self.t += 1
+        lr = self.schedule.lr(self.t - 1) if self.schedule is not None else self.lr
+        b1, b2 = self.betas
+        h = self.hyper_host
+        h[0], h[1], h[2], h[3], h[4] = lr, b1, b2, self.eps, self.wd
+        h[5], h[6], h[7] = 1 - b1 ** self.t, 1 - b2 ** self.t, grad_scale
+        self.hyper.copy_(h, non_blocking=True)
+        a = self.engine.arena
+        self.K.adamw_step(a.param, a.grad, self.m, self.v, a.shadow, self.hyper, True)
+        # the plain shadow is fresh; transposed shadows are rebuilt by the engine
+        if a.shadow is not None:
+            for n, dst in a.WbT.items():
+                self.K.cast_transpose_bf16(a.P[n].view(a.shapes[n][0], -1), dst)
+        self.engine.shadows_fresh = True
