@@ -20,6 +20,7 @@
 #include "common.cuh"
 #include "gemm_params.h"
 #include "tc_common.cuh"
+#include "tmap.h"
 
 namespace {
 
@@ -245,76 +246,15 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   if (warp == 2) tc::tmem_dealloc(tmem_base, 2 * BN);
 }
 
-// ---------------------------------------------------------------- host: tensor maps
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
-                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
-                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-EncodeTiledFn get_encode_fn() {
-  static EncodeTiledFn fn = nullptr;
-  static std::once_flag once;
-  std::call_once(once, [] {
-    void* p = nullptr;
-    cudaDriverEntryPointQueryResult q;
-    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
-        q == cudaDriverEntryPointSuccess)
-      fn = reinterpret_cast<EncodeTiledFn>(p);
-  });
-  return fn;
-}
-
-struct MapKey {
-  const void* ptr;
-  uint64_t d0, d1, stride1;
-  uint32_t b0, b1;
-  bool operator==(const MapKey& o) const { return std::memcmp(this, &o, sizeof(MapKey)) == 0; }
-};
-struct MapKeyHash {
-  size_t operator()(const MapKey& k) const {
-    size_t h = 1469598103934665603ull;
-    const unsigned char* p = reinterpret_cast<const unsigned char*>(&k);
-    for (size_t i = 0; i < sizeof(MapKey); ++i) h = (h ^ p[i]) * 1099511628211ull;
-    return h;
-  }
-};
-
+// ---------------------------------------------------------------- host
 // 2D bf16 tensor [d1 rows, d0 cols] with row pitch stride1 (elements), box [b1 rows, b0 cols], 128B swizzle.
 int get_tmap(CUtensorMap* out, const void* ptr, uint64_t d0, uint64_t d1, uint64_t stride1, uint32_t b0, uint32_t b1) {
-  static std::unordered_map<MapKey, CUtensorMap, MapKeyHash> cache;
-  static std::mutex mu;
-  MapKey key;
-  std::memset(&key, 0, sizeof(key));
-  key.ptr = ptr; key.d0 = d0; key.d1 = d1; key.stride1 = stride1; key.b0 = b0; key.b1 = b1;
-  std::lock_guard<std::mutex> lock(mu);
-  auto it = cache.find(key);
-  if (it != cache.end()) { *out = it->second; return 0; }
-  EncodeTiledFn fn = get_encode_fn();
-  if (fn == nullptr) return -10;
-  if ((reinterpret_cast<uintptr_t>(ptr) & 15) != 0 || (stride1 * 2) % 16 != 0) return -11;
-  cuuint64_t dims[2] = {d0, d1};
-  cuuint64_t strides[1] = {stride1 * 2};
-  cuuint32_t box[2] = {b0, b1};
-  cuuint32_t estr[2] = {1, 1};
-  CUtensorMap m;
-  CUresult r = fn(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  if (r != CUDA_SUCCESS) return -12;
-  if (cache.size() > 4096) cache.clear();
-  cache.emplace(key, m);
-  *out = m;
-  return 0;
+  const uint64_t dims[2] = {d0, d1}, strides[1] = {stride1};
+  const uint32_t box[2] = {b0, b1};
+  return mb_get_tmap(out, ptr, 2, dims, strides, box, 128);
 }
 
-int num_sms() {
-  static int n = 0;
-  if (n == 0) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
-  }
-  return n;
-}
+int num_sms() { return mb_num_sms(); }
 
 template <int BN, bool MN>
 int launch(const GemmParams& P, cudaStream_t st) {

@@ -115,14 +115,20 @@ __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.
 // ---------------------------------------------------------------- descriptors
 constexpr uint32_t SWIZZLE_128B = 2;
 
-// Shared-memory matrix descriptor (SWIZZLE_128B).  lbo / sbo in bytes.
-__device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+// Layout-type field of the descriptor for a swizzle span of 128 / 64 / 32 bytes.
+__host__ __device__ constexpr uint32_t layout_type_for(int swizzle_bytes) {
+  return swizzle_bytes == 128 ? 2u : (swizzle_bytes == 64 ? 4u : 6u);
+}
+
+// Shared-memory matrix descriptor.  lbo / sbo in bytes.
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes,
+                                                   uint32_t layout_type = SWIZZLE_128B) {
   uint64_t d = 0;
   d |= static_cast<uint64_t>((smem_addr & 0x3FFFF) >> 4);
   d |= static_cast<uint64_t>((lbo_bytes >> 4) & 0x3FFF) << 16;
   d |= static_cast<uint64_t>((sbo_bytes >> 4) & 0x3FFF) << 32;
   d |= static_cast<uint64_t>(1) << 46;             // descriptor version (Blackwell)
-  d |= static_cast<uint64_t>(SWIZZLE_128B) << 61;  // layout type
+  d |= static_cast<uint64_t>(layout_type) << 61;   // layout type
   return d;
 }
 

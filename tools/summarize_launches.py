@@ -1,0 +1,27 @@
+"""Summarise an `ncu --metrics gpu__time_duration.sum --csv` launch list: per-kernel launches, total time, share."""
+import csv
+import re
+import sys
+from collections import defaultdict
+
+rows = []
+with open(sys.argv[1]) as f:
+    lines = [l for l in f if not l.startswith("==")]
+for r in csv.DictReader(lines):
+    if r.get("Metric Name") != "gpu__time_duration.sum":
+        continue
+    v = float(r["Metric Value"].replace(",", ""))
+    unit = r.get("Metric Unit", "ns")
+    v *= {"ns": 1e-3, "us": 1.0, "ms": 1e3, "s": 1e6}.get(unit, 1e-3)
+    name = re.sub(r"\(.*", "", r["Kernel Name"])
+    rows.append((name, v))
+tot = sum(v for _, v in rows)
+agg = defaultdict(lambda: [0, 0.0])
+for n, v in rows:
+    agg[n][0] += 1
+    agg[n][1] += v
+print(f"# {len(rows)} launches, {tot / 1e3:.3f} ms total (cold-cache, serialised under ncu: compare shares)")
+print("| kernel | launches | total us | avg us | share |")
+print("|---|---:|---:|---:|---:|")
+for n, (c, v) in sorted(agg.items(), key=lambda kv: -kv[1][1]):
+    print(f"| {n} | {c} | {v:.1f} | {v / c:.2f} | {100 * v / tot:.1f}% |")
