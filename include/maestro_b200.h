@@ -131,6 +131,13 @@ int mb_softmax_rows(const float* s, void* p, int dtype, long long rows, int n, f
 int mb_softmax_bwd_rows(const void* p, float* dp, void* ds, int dtype, long long rows, int n, float scale,
                         void* stream);
 
+/* Fused flash-style attention on tcgen05 (bf16): softmax(q k^T * dh^-0.5) v of vit_pytorch Attention.forward without
+ * materialising the [B, h, N, N] scores.  qkv [Bn*N, 3*H*dh], o [Bn*N, H*dh], lse / delta [Bn, H, N] fp32.
+ * dh in {16, 32, 64}. */
+int mb_attn_fwd(const void* qkv, void* o, float* lse, int Bn, int N, int H, int dh, void* stream);
+int mb_attn_bwd(const void* qkv, const void* o, const void* d_o, const float* lse, void* dqkv, float* delta, int Bn,
+                int N, int H, int dh, void* stream);
+
 /* ---- optimiser ---------------------------------------------------------------------------------------------- */
 /* torch.optim.AdamW built at maestro/train/model.py:135-149, fused over the flat arena (+ bf16 shadow refresh). */
 int mb_adamw_step(float* p, float* g, float* m, float* v, void* shadow, const float* hyper, size_t n, int zero_grad,

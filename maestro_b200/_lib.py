@@ -16,7 +16,7 @@ HERE = Path(__file__).resolve().parent
 CSRC = HERE / "csrc"
 SO_PATH = HERE / "libmaestro_b200.so"
 SOURCES = ["elementwise.cu", "norm.cu", "mask.cu", "unmask.cu", "loss.cu", "gemm_simt.cu", "gemm_tc.cu",
-           "tmap.cu", "attn_tc.cu", "optim.cu"]
+           "tmap.cu", "attn_tc.cu", "attn_bwd_tc.cu", "optim.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"]
 
@@ -111,5 +111,5 @@ EXPORTS = [
     "mb_layernorm_fwd", "mb_layernorm_bwd", "mb_gn_stats", "mb_gn_apply", "mb_gn_bwd",
     "mb_mask_indices", "mb_gather_rows", "mb_scatter_kept", "mb_unmask_fwd", "mb_masktoken_grad",
     "mb_loss_fwd_bwd", "mb_gemm_simt", "mb_softmax_rows", "mb_softmax_bwd_rows", "mb_gemm_tc",
-    "mb_adamw_step",
+    "mb_adamw_step", "mb_attn_fwd", "mb_attn_bwd",
 ]

@@ -1,0 +1,272 @@
+// Fused (flash-style) attention for sm_100a on tcgen05 tensor cores with TMEM accumulators and TMA loads.
+// Replaces vit_pytorch Attention.forward's  softmax(q k^T * dh^-0.5) v  (and its autograd), which the reference
+// runs unfused, materialising [B, h, N, N] scores (SURVEY 2.1 "Attention").
+//
+// Layout: qkv [Bn * N, 3 * H * DH] bf16 (row = token; q | k | v column blocks, head h at columns h * DH),
+//         o   [Bn * N, H * DH] bf16, lse [Bn, H, N] fp32 (natural log of the softmax denominator, scaled scores).
+//
+// Forward: one CTA (128 threads) per (sample, head, 128-query tile).  Thread t owns query row t == TMEM lane t, so
+// row max / row sum need no shuffles.  Per 128-key tile: S = Q K^T (tcgen05.mma, fp32 in TMEM) -> two passes of
+// tcgen05.ld over the row (max, then exp2 + sum) -> P (bf16) written to shared memory in the K-major 128B-swizzle
+// layout -> O_tile = P V (V consumed as an MN-major operand straight from its TMA tile) -> registers accumulate
+// O with the online-softmax rescale.  K/V tiles are double-buffered; the next S = Q K^T is issued before the
+// current P V result is consumed so the tensor pipe overlaps the exp work; several CTAs share an SM.
+#include "common.cuh"
+#include "tc_common.cuh"
+#include "tmap.h"
+
+namespace {
+
+constexpr int BQ = 128;   // query rows per CTA
+constexpr int BKV = 128;  // keys per tile
+
+template <int DH> struct ACfg {
+  static constexpr int SW = DH * 2;                       // swizzle span == row bytes of a [rows, DH] bf16 tile
+  static constexpr int TILE_BYTES = BKV * DH * 2;         // one Q / K / V tile
+  static constexpr int P_BYTES = BQ * BKV * 2;            // 32 KB: two [128 x 64] K-major blocks
+  static constexpr int OFF_Q = 0;
+  static constexpr int OFF_K = TILE_BYTES;                // 2 stages
+  static constexpr int OFF_V = 3 * TILE_BYTES;            // 2 stages
+  static constexpr int OFF_P = 5 * TILE_BYTES;
+  static constexpr int OFF_BAR = OFF_P + P_BYTES;
+  static constexpr int SMEM_BYTES = OFF_BAR + 128 + 1024;  // + barriers + alignment slack
+  static constexpr uint32_t LT = tc::layout_type_for(SW);
+};
+
+struct AttnArgs {
+  bf16* o;
+  float* lse;
+  int N, H;
+  float scale_log2;  // dh^-0.5 * log2(e)
+  float scale;
+};
+
+template <int DH>
+__global__ void __launch_bounds__(128) attn_fwd_kernel(const __grid_constant__ CUtensorMap tm, AttnArgs args) {
+  using C_ = ACfg<DH>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+  uint64_t* bar_q = reinterpret_cast<uint64_t*>(smem + C_::OFF_BAR);
+  uint64_t* bar_kv = bar_q + 1;   // [2]
+  uint64_t* bar_s = bar_q + 3;
+  uint64_t* bar_o = bar_q + 4;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bar_q + 5);
+
+  const int tid = threadIdx.x, warp = tid >> 5;
+  const int N = args.N, H = args.H;
+  const int q_tiles = (N + BQ - 1) / BQ;
+  const int qt = blockIdx.x % q_tiles;
+  const int bh = blockIdx.x / q_tiles;
+  const int h = bh % H, b = bh / H;
+  const int inner = H * DH;
+  const int kv_tiles = (N + BKV - 1) / BKV;
+
+  if (tid == 0) {
+    tc::prefetch_tmap(&tm);
+    tc::mbar_init(bar_q, 1);
+    tc::mbar_init(&bar_kv[0], 1);
+    tc::mbar_init(&bar_kv[1], 1);
+    tc::mbar_init(bar_s, 1);
+    tc::mbar_init(bar_o, 1);
+    tc::fence_barrier_init();
+  }
+  if (warp == 0) {
+    tc::tmem_alloc(tmem_ptr, 256);
+    tc::tmem_relinquish();
+  }
+  tc::tc_fence_before();
+  __syncthreads();
+  tc::tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+  const uint32_t tm_s = tmem_base;          // S: columns [0, 128)
+  const uint32_t tm_o = tmem_base + 128;    // O tile: columns [128, 128 + DH)
+  const uint32_t lane_base = static_cast<uint32_t>(warp * 32) << 16;
+
+  constexpr uint32_t idesc_s = tc::make_idesc_bf16(BQ, BKV, 0, 0);   // Q (K-major) x K (K-major)
+  constexpr uint32_t idesc_o = tc::make_idesc_bf16(BQ, DH, 0, 1);    // P (K-major) x V (MN-major)
+  const uint32_t sQ = tc::smem_u32(smem + C_::OFF_Q);
+  const uint32_t sP = tc::smem_u32(smem + C_::OFF_P);
+
+  auto load_kv = [&](int j) {
+    const int st = j & 1;
+    tc::mbar_expect_tx(&bar_kv[st], 2 * C_::TILE_BYTES);
+    tc::tma_load_3d(smem + C_::OFF_K + st * C_::TILE_BYTES, &tm, &bar_kv[st], inner + h * DH, j * BKV, b);
+    tc::tma_load_3d(smem + C_::OFF_V + st * C_::TILE_BYTES, &tm, &bar_kv[st], 2 * inner + h * DH, j * BKV, b);
+  };
+  auto issue_s = [&](int j) {
+    const uint32_t sK = tc::smem_u32(smem + C_::OFF_K + (j & 1) * C_::TILE_BYTES);
+#pragma unroll
+    for (int k = 0; k < DH / 16; ++k) {
+      const uint64_t da = tc::make_smem_desc(sQ + k * 32, 16, 8 * C_::SW, C_::LT);
+      const uint64_t db = tc::make_smem_desc(sK + k * 32, 16, 8 * C_::SW, C_::LT);
+      tc::umma_bf16(tm_s, da, db, idesc_s, k > 0 ? 1u : 0u);
+    }
+    tc::umma_commit(bar_s);
+  };
+  auto issue_pv = [&](int j) {
+    const uint32_t sV = tc::smem_u32(smem + C_::OFF_V + (j & 1) * C_::TILE_BYTES);
+#pragma unroll
+    for (int k = 0; k < BKV / 16; ++k) {
+      const uint64_t da = tc::make_smem_desc(sP + (k / 4) * 16384 + (k % 4) * 32, 16, 1024, tc::SWIZZLE_128B);
+      const uint64_t db = tc::make_smem_desc(sV + k * 16 * C_::SW, 16, 8 * C_::SW, C_::LT);
+      tc::umma_bf16(tm_o, da, db, idesc_o, k > 0 ? 1u : 0u);
+    }
+    tc::umma_commit(bar_o);
+  };
+
+  if (tid == 0) {
+    tc::mbar_expect_tx(bar_q, C_::TILE_BYTES);
+    tc::tma_load_3d(smem + C_::OFF_Q, &tm, bar_q, h * DH, qt * BQ, b);
+    load_kv(0);
+    if (kv_tiles > 1) load_kv(1);
+    tc::mbar_wait(bar_q, 0);
+    tc::mbar_wait(&bar_kv[0], 0);
+    tc::tc_fence_after();
+    issue_s(0);
+  }
+
+  float o_acc[DH];
+#pragma unroll
+  for (int i = 0; i < DH; ++i) o_acc[i] = 0.f;
+  float m_run = -INFINITY, l_run = 0.f;
+  const float c = args.scale_log2;
+  uint8_t* p_row = smem + C_::OFF_P + tid * 128;
+
+  for (int j = 0; j < kv_tiles; ++j) {
+    const uint32_t ph = j & 1;
+    const int kv_valid = min(BKV, N - j * BKV);
+    tc::mbar_wait(bar_s, ph);
+    tc::tc_fence_after();
+    // pass 1: row max over the valid keys
+    float mx = m_run;
+#pragma unroll 1
+    for (int ch = 0; ch < BKV / 32; ++ch) {
+      if (ch * 32 >= kv_valid) break;
+      uint32_t r[32];
+      tc::tmem_ld_32x32(tm_s + lane_base + ch * 32, r);
+      tc::tmem_ld_wait();
+#pragma unroll
+      for (int i = 0; i < 32; ++i)
+        if (ch * 32 + i < kv_valid) mx = fmaxf(mx, __uint_as_float(r[i]));
+    }
+    const float alpha = exp2f((m_run - mx) * c);   // m_run = -inf on the first tile -> 0
+    const float mc = mx * c;
+    float lsum = 0.f;
+    // pass 2: p = exp2(s * c - m * c), write bf16 P row (K-major, 128B swizzle), accumulate the row sum
+#pragma unroll 1
+    for (int ch = 0; ch < BKV / 32; ++ch) {
+      uint32_t r[32];
+      if (ch * 32 < kv_valid) {
+        tc::tmem_ld_32x32(tm_s + lane_base + ch * 32, r);
+        tc::tmem_ld_wait();
+      }
+#pragma unroll
+      for (int v8 = 0; v8 < 4; ++v8) {
+        uint32_t w[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int col = ch * 32 + v8 * 8 + 2 * i;
+          float p0 = 0.f, p1 = 0.f;
+          if (col < kv_valid) p0 = exp2f(fmaf(__uint_as_float(r[v8 * 8 + 2 * i]), c, -mc));
+          if (col + 1 < kv_valid) p1 = exp2f(fmaf(__uint_as_float(r[v8 * 8 + 2 * i + 1]), c, -mc));
+          __nv_bfloat162 hb = __floats2bfloat162_rn(p0, p1);
+          // the row sum uses the rounded probabilities that the P V product will see
+          lsum += __bfloat162float(hb.x) + __bfloat162float(hb.y);
+          w[i] = *reinterpret_cast<uint32_t*>(&hb);
+        }
+        const int colb = ch * 32 + v8 * 8;                 // first key of this 16-byte chunk
+        const int blk = colb >> 6, c16 = (colb & 63) >> 3;
+        *reinterpret_cast<uint4*>(p_row + blk * 16384 + ((c16 ^ (tid & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
+      }
+    }
+    l_run = l_run * alpha + lsum;
+    m_run = mx;
+    tc::fence_proxy_async();     // P (generic-proxy stores) -> visible to the tensor core (async proxy)
+    tc::tc_fence_before();
+    __syncthreads();
+    if (tid == 0) {
+      tc::tc_fence_after();
+      issue_pv(j);
+      if (j + 1 < kv_tiles) {
+        tc::mbar_wait(&bar_kv[(j + 1) & 1], ((j + 1) >> 1) & 1);
+        tc::tc_fence_after();
+        issue_s(j + 1);
+      }
+    }
+    tc::mbar_wait(bar_o, ph);
+    tc::tc_fence_after();
+#pragma unroll
+    for (int ch = 0; ch < (DH + 31) / 32; ++ch) {
+      uint32_t r[32];
+      tc::tmem_ld_32x32(tm_o + lane_base + ch * 32, r);   // DH = 16 reads 16 junk columns of the allocation
+      tc::tmem_ld_wait();
+#pragma unroll
+      for (int i = 0; i < 32; ++i)
+        if (ch * 32 + i < DH) o_acc[ch * 32 + i] = fmaf(o_acc[ch * 32 + i], alpha, __uint_as_float(r[i]));
+    }
+    // K/V stage (j & 1) and the P buffer are free again: prefetch tile j + 2
+    if (tid == 0 && j + 2 < kv_tiles) load_kv(j + 2);
+  }
+
+  const int row = qt * BQ + tid;
+  if (row < N) {
+    const float inv = 1.f / l_run;
+    bf16* orow = args.o + (static_cast<size_t>(b) * N + row) * inner + h * DH;
+#pragma unroll
+    for (int v8 = 0; v8 < DH / 8; ++v8) {
+      float v[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) v[i] = o_acc[v8 * 8 + i] * inv;
+      VecIO<bf16>::store(orow + v8 * 8, v);
+    }
+    args.lse[(static_cast<size_t>(b) * H + h) * N + row] = m_run * args.scale + logf(l_run);
+  }
+  tc::tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tc::tmem_dealloc(tmem_base, 256);
+}
+
+int qkv_tmap(CUtensorMap* tm, const void* qkv, int Bn, int N, int cols, int DH, int box_rows) {
+  const uint64_t dims[3] = {static_cast<uint64_t>(cols), static_cast<uint64_t>(N), static_cast<uint64_t>(Bn)};
+  const uint64_t strides[2] = {static_cast<uint64_t>(cols), static_cast<uint64_t>(N) * cols};
+  const uint32_t box[3] = {static_cast<uint32_t>(DH), static_cast<uint32_t>(box_rows), 1};
+  return mb_get_tmap(tm, qkv, 3, dims, strides, box, DH * 2);
+}
+
+template <int DH>
+int launch_fwd(const void* qkv, void* o, float* lse, int Bn, int N, int H, cudaStream_t st) {
+  using C_ = ACfg<DH>;
+  CUtensorMap tm;
+  int rc = qkv_tmap(&tm, qkv, Bn, N, 3 * H * DH, DH, BKV);
+  if (rc != 0) return rc;
+  AttnArgs a;
+  a.o = static_cast<bf16*>(o);
+  a.lse = lse;
+  a.N = N;
+  a.H = H;
+  a.scale = 1.0f / sqrtf(static_cast<float>(DH));
+  a.scale_log2 = a.scale * 1.4426950408889634f;
+  static bool attr = false;
+  if (!attr) {
+    cudaFuncSetAttribute(attn_fwd_kernel<DH>, cudaFuncAttributeMaxDynamicSharedMemorySize, C_::SMEM_BYTES);
+    attr = true;
+  }
+  const int grid = Bn * H * ((N + BQ - 1) / BQ);
+  attn_fwd_kernel<DH><<<grid, 128, C_::SMEM_BYTES, st>>>(tm, a);
+  cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? 0 : static_cast<int>(e);
+}
+
+}  // namespace
+
+// qkv [Bn*N, 3*H*dh] bf16 -> o [Bn*N, H*dh] bf16, lse [Bn, H, N] fp32.  dh in {16, 32, 64}.
+extern "C" int mb_attn_fwd(const void* qkv, void* o, float* lse, int Bn, int N, int H, int dh, void* stream) {
+  if (Bn == 0 || N == 0) return 0;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  switch (dh) {
+    case 16: return launch_fwd<16>(qkv, o, lse, Bn, N, H, st);
+    case 32: return launch_fwd<32>(qkv, o, lse, Bn, N, H, st);
+    case 64: return launch_fwd<64>(qkv, o, lse, Bn, N, H, st);
+    default: return -2;
+  }
+}

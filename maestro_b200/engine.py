@@ -169,7 +169,9 @@ class PretrainEngine:
         self.E, self.Dd = hp["embed_dim"], hp["decoder_dim"]
         self.mlp_e = int(self.E * hp["mlp_ratio"])
         self.mlp_d = int(self.E * hp["decoder_mlp_ratio"])   # reference quirk: decoder MLP is E * ratio (mae.py:162)
-        self.attn_impl = "gemm"                               # "gemm": materialised scores; "flash": fused tcgen05
+        # "flash": fused tcgen05 attention (bf16, dh in {16, 32, 64}); "gemm": materialised scores (fp32 check mode)
+        flash_ok = dtype == torch.bfloat16 and all(d in (16, 32, 64) for d in (hp["dim_head"], hp["decoder_dim_head"]))
+        self.attn_impl = "flash" if flash_ok else "gemm"
         self._build_tables(fac_abs_enc)
         self._build_params()
 
@@ -338,6 +340,10 @@ class PretrainEngine:
         inner = H * dh
         scale = dh ** -0.5
         o = self._new(Bn * N, inner)
+        if self.attn_impl == "flash":
+            lse = self._new(Bn, H, N, dtype=torch.float32)
+            self.K.attn_fwd(qkv, o, lse, Bn, N, H, dh)
+            return o, lse
         s = self._new(Bn * H * N * N, dtype=torch.float32)
         self.K.gemm(qkv, qkv, s, N, N, dh, sam=3 * inner, sak=1, sbn=3 * inner, sbk=1, ldc=N, nb1=Bn, nb2=H,
                     a_s=(N * 3 * inner, dh), b_s=(N * 3 * inner, dh), c_s=(H * N * N, N * N), b_off=inner)
@@ -348,10 +354,14 @@ class PretrainEngine:
                     a_s=(H * N * N, N * N), b_s=(N * 3 * inner, dh), c_s=(N * inner, dh), b_off=2 * inner)
         return o, p
 
-    def attn_bwd(self, do, qkv, p, Bn, N, H, dh):
+    def attn_bwd(self, do, qkv, p, Bn, N, H, dh, o=None):
         inner = H * dh
         scale = dh ** -0.5
         dqkv = self._new(Bn * N, 3 * inner)
+        if self.attn_impl == "flash":
+            delta = self._new(Bn, H, N, dtype=torch.float32)
+            self.K.attn_bwd(qkv, o, do, p, dqkv, delta, Bn, N, H, dh)   # p holds the log-sum-exp here
+            return dqkv
         bs_qkv, bs_p, bs_o = (N * 3 * inner, dh), (H * N * N, N * N), (N * inner, dh)
         # dV[k, n] = sum_m P[m, k] dO[m, n]
         self.K.gemm(p, do, dqkv, N, dh, N, sam=1, sak=N, sbn=1, sbk=inner, ldc=3 * inner, nb1=Bn, nb2=H,
@@ -405,7 +415,7 @@ class PretrainEngine:
                         G[pre + "1.net.0.bias"], rows, dim)
         do = self._new(rows, inner)
         self.lin_bwd(dx2, rows, o, pre + "0.to_out.0.weight", pre + "0.to_out.0.bias", dx=do)
-        dqkv = self.attn_bwd(do, qkv, att, Bn, N, H, dh)
+        dqkv = self.attn_bwd(do, qkv, att, Bn, N, H, dh, o=o)
         dh1 = dh2  # reuse
         self.lin_bwd(dqkv, rows, h1, pre + "0.to_qkv.weight", None, dx=dh1)
         dx = self._new(rows, dim)

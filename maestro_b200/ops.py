@@ -230,6 +230,16 @@ class Kernels:
         _ck(self.L.mb_softmax_bwd_rows(_p(p), _p(dp), _p(ds), _dt(p), C.c_longlong(rows), n, C.c_float(scale),
                                        _stream()), "softmax_bwd")
 
+    # ------------------------------------------------------------------ fused attention (bf16, tcgen05)
+    def attn_fwd(self, qkv, o, lse, Bn, N, H, dh):
+        self.launches += 1
+        _ck(self.L.mb_attn_fwd(_p(qkv), _p(o), _p(lse), Bn, N, H, dh, _stream()), "attn_fwd")
+
+    def attn_bwd(self, qkv, o, do, lse, dqkv, delta, Bn, N, H, dh):
+        self.launches += 2
+        _ck(self.L.mb_attn_bwd(_p(qkv), _p(o), _p(do), _p(lse), _p(dqkv), _p(delta), Bn, N, H, dh, _stream()),
+            "attn_bwd")
+
     # ------------------------------------------------------------------ optimiser
     def adamw_step(self, p, g, m, v, shadow, hyper, zero_grad):
         self.launches += 1

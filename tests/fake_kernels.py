@@ -254,6 +254,34 @@ class FakeKernels:
         out = scale * pv * (d - (d * pv).sum(-1, keepdim=True))
         ds.reshape(-1)[:rows * n].copy_(out.to(ds.dtype).reshape(-1))
 
+    # ------------------------------------------------------------------ fused attention
+    @staticmethod
+    def _heads(qkv, Bn, N, H, dh):
+        q, k, v = qkv.float().reshape(Bn, N, 3, H, dh).permute(2, 0, 3, 1, 4)
+        return q, k, v
+
+    def attn_fwd(self, qkv, o, lse, Bn, N, H, dh):
+        q, k, v = self._heads(qkv, Bn, N, H, dh)
+        s = (q @ k.transpose(-1, -2)) * dh ** -0.5
+        lse.copy_(torch.logsumexp(s, -1))
+        p = torch.softmax(s, -1)
+        o.copy_((p @ v).permute(0, 2, 1, 3).reshape(Bn * N, H * dh).to(o.dtype))
+
+    def attn_bwd(self, qkv, o, do, lse, dqkv, delta, Bn, N, H, dh):
+        q, k, v = self._heads(qkv, Bn, N, H, dh)
+        dO = do.float().reshape(Bn, N, H, dh).permute(0, 2, 1, 3)
+        O = o.float().reshape(Bn, N, H, dh).permute(0, 2, 1, 3)
+        s = (q @ k.transpose(-1, -2)) * dh ** -0.5
+        p = torch.exp(s - lse[..., None])
+        dl = (dO * O).sum(-1)
+        delta.copy_(dl)
+        dv = p.transpose(-1, -2) @ dO
+        dp = dO @ v.transpose(-1, -2)
+        ds = p * (dp - dl[..., None]) * dh ** -0.5
+        dq, dk = ds @ k, ds.transpose(-1, -2) @ q
+        out = torch.stack([dq, dk, dv], 0).permute(1, 3, 0, 2, 4).reshape(Bn * N, 3 * H * dh)
+        dqkv.copy_(out.to(dqkv.dtype))
+
     # ------------------------------------------------------------------ optimiser
     def adamw_step(self, p, g, m, v, shadow, hyper, zero_grad):
         lr, b1, b2, eps, wd, bc1, bc2, gs = [float(x) for x in hyper.tolist()]

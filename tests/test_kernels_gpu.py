@@ -361,3 +361,27 @@ def test_adamw(KK):
     a, b = both(KK, run)
     for x, y in zip(a, b):
         close(x, y, rtol=1e-5, atol=1e-6 if x.dtype == torch.float32 else 1e-2)
+
+
+@pytest.mark.parametrize("Bn,N,H,dh", [(2, 50, 2, 16), (3, 128, 2, 32), (2, 200, 3, 64), (1, 1024, 2, 32),
+                                       (2, 470, 2, 64), (4, 64, 2, 64), (2, 129, 1, 32), (1, 18, 2, 16),
+                                       (2, 400, 16, 32), (2, 256, 12, 64)])
+def test_fused_attention_fwd_bwd(KK, Bn, N, H, dh):
+    qkv = rnd(Bn * N, 3 * H * dh, dt=torch.bfloat16, seed=1)
+    do = rnd(Bn * N, H * dh, dt=torch.bfloat16, seed=2)
+
+    def run(K):
+        o = torch.zeros(Bn * N, H * dh, dtype=torch.bfloat16, device="cuda")
+        lse = torch.zeros(Bn, H, N, device="cuda")
+        K.attn_fwd(qkv, o, lse, Bn, N, H, dh)
+        dqkv = torch.zeros_like(qkv)
+        delta = torch.zeros(Bn, H, N, device="cuda")
+        K.attn_bwd(qkv, o, do, lse, dqkv, delta, Bn, N, H, dh)
+        return o, lse, dqkv, delta
+    a, b = both(KK, run)
+    close(a[0], b[0], rtol=2e-2, atol=2e-2)
+    close(a[1], b[1], rtol=1e-3, atol=1e-2)
+    close(a[3], b[3], rtol=2e-2, atol=5e-2)
+    close(a[2], b[2], rtol=3e-2, atol=3e-2 * float(b[2].float().abs().max()))
+    cos = torch.nn.functional.cosine_similarity(a[2].float().flatten(), b[2].float().flatten(), dim=0)
+    assert cos > 0.999, float(cos)
