@@ -1,0 +1,97 @@
+"""Micro-benchmark of the tcgen05 GEMM on the layer shapes of the FLAIR-HUB ViT-B step (32 tiles/GPU).
+
+    python tools/gemm_bench.py [--iters 20] [--only fwd_up] [--once]
+
+Prints per-shape time and TFLOP/s (CUDA events, L2 flushed between iterations by streaming a 256 MB buffer).
+"""
+
+import argparse
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+import torch  # noqa: E402
+
+from maestro_b200.ops import Kernels  # noqa: E402
+
+ROWS = {"enc_aerial": 8192, "enc_dem": 2048, "enc_s2": 3200, "enc_s1": 1600, "inter": 15040,
+        "dec_aerial": 32768, "dec_dem": 8192, "dec_s2": 12800, "dec_s1": 6400}
+
+
+def cases():
+    out = []
+    for tag, M in ROWS.items():
+        d, mlp = (768, 3072) if not tag.startswith("dec") else (512, 3072)
+        inner = d
+        out += [
+            (f"{tag}/fwd_qkv", "k", M, 3 * inner, d, 0),
+            (f"{tag}/fwd_out", "k", M, d, inner, "res"),
+            (f"{tag}/fwd_up", "k", M, mlp, d, "gelu"),
+            (f"{tag}/fwd_down", "k", M, d, mlp, "res"),
+            (f"{tag}/dgrad_down", "k", M, mlp, d, "dgelu"),
+            (f"{tag}/dgrad_up", "k", M, d, mlp, 0),
+            (f"{tag}/wgrad_up", "mn", mlp, d, M, 0),
+            (f"{tag}/wgrad_qkv", "mn", 3 * inner, d, M, 0),
+            (f"{tag}/wgrad_down", "mn", d, mlp, M, 0),
+        ]
+    return out
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--iters", type=int, default=10)
+    ap.add_argument("--only", default="")
+    ap.add_argument("--once", action="store_true", help="one launch per shape (for ncu)")
+    args = ap.parse_args()
+    K = Kernels()
+    dev = "cuda"
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    tot_fl, tot_ms = 0.0, 0.0
+    for name, layout, M, N, Kd, epi in cases():
+        if args.only and args.only not in name:
+            continue
+        bf = torch.bfloat16
+        if layout == "k":
+            A = torch.randn(M, Kd, device=dev).to(bf)
+            B = torch.randn(N, Kd, device=dev).to(bf)
+            C = torch.empty(M, N, device=dev, dtype=bf)
+            kw = dict(sam=Kd, sak=1, sbn=Kd, sbk=1, ldc=N)
+            if epi == "res":
+                kw.update(bias=torch.randn(N, device=dev), residual=torch.randn(M, N, device=dev).to(bf))
+            elif epi == "gelu":
+                kw.update(bias=torch.randn(N, device=dev), aux=torch.empty(M, N, device=dev, dtype=bf), flags=1)
+            elif epi == "dgelu":
+                kw.update(aux=torch.randn(M, N, device=dev).to(bf), flags=2)
+        else:  # wgrad: C[M, N] += sum_t A[t, M] * B[t, N]
+            A = torch.randn(Kd, M, device=dev).to(bf)
+            B = torch.randn(Kd, N, device=dev).to(bf)
+            C = torch.zeros(M, N, device=dev)
+            kw = dict(sam=1, sak=M, sbn=1, sbk=N, ldc=N, flags=4)
+        run = lambda: K.gemm(A, B, C, M, N, Kd, **kw)  # noqa: E731
+        if args.once:
+            run()
+            torch.cuda.synchronize()
+            continue
+        for _ in range(2):
+            run()
+        ms = 0.0
+        for _ in range(args.iters):
+            flush.fill_(1)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            run()
+            e1.record()
+            torch.cuda.synchronize()
+            ms += e0.elapsed_time(e1)
+        ms /= args.iters
+        fl = 2.0 * M * N * Kd
+        tot_fl += fl
+        tot_ms += ms
+        print(f"{name:28s} M={M:6d} N={N:5d} K={Kd:6d}  {ms * 1e3:8.1f} us  {fl / ms / 1e9:7.1f} TFLOP/s", flush=True)
+    if tot_ms:
+        print(f"TOTAL {tot_ms:.3f} ms  {tot_fl / tot_ms / 1e9:.1f} TFLOP/s")
+
+
+if __name__ == "__main__":
+    main()
