@@ -87,6 +87,28 @@ __device__ __forceinline__ float gelu_erf_grad(float x) {
   return cdf + x * pdf;
 }
 
+// Fast exact-form GELU for the bf16 tensor-core epilogues: erf by Abramowitz-Stegun 7.1.26 (|err| < 1.5e-7, far
+// below bf16 resolution) sharing one exp between erf and the Gaussian term of the derivative.
+__device__ __forceinline__ void gelu_fast_terms(float x, float& cdf, float& pdf) {
+  const float z = fabsf(x) * 0.70710678118654752440f;
+  const float e = __expf(-z * z);                        // exp(-x^2 / 2)
+  const float t = __fdividef(1.0f, fmaf(0.3275911f, z, 1.0f));
+  const float poly = t * (0.254829592f + t * (-0.284496736f + t * (1.421413741f + t * (-1.453152027f + t * 1.061405429f))));
+  const float erf_abs = 1.0f - poly * e;
+  cdf = 0.5f * (1.0f + copysignf(erf_abs, x));
+  pdf = 0.39894228040143267794f * e;
+}
+__device__ __forceinline__ float gelu_fast(float x) {
+  float cdf, pdf;
+  gelu_fast_terms(x, cdf, pdf);
+  return x * cdf;
+}
+__device__ __forceinline__ float gelu_fast_grad(float x) {
+  float cdf, pdf;
+  gelu_fast_terms(x, cdf, pdf);
+  return fmaf(x, pdf, cdf);
+}
+
 // Date-encoding channel value: channels [dim-8, dim) of a token are
 // [diff, diff, diff, diff, sin_doy, cos_doy, sin_hour, cos_hour] * fac  (reference
 // maestro/layers/utils.py:128-173); feat = [diff, sin_doy, cos_doy, sin_hour, cos_hour].

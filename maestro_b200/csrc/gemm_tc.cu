@@ -8,7 +8,7 @@
 //   MN = true   A is [K, M] and B is [K, N], both MN-contiguous      -> wgrad  dW[n, k] = sum_t dY[t, n] X[t, k]
 //                                                                        (contraction over tokens, split-K + fp32 red)
 // Structure: persistent CTAs (one per SM), warp-specialised: warp 0 = TMA producer, warp 1 = single-thread
-// tcgen05.mma issuer, warp 2 = TMEM allocator, warps 4..7 = epilogue (tcgen05.ld -> registers -> fused
+// tcgen05.mma issuer, warp 2 = TMEM allocator, warps 4..11 = epilogue (tcgen05.ld -> registers -> fused
 // bias / GELU / GELU' / residual -> 16-byte global stores).  The accumulator is double-buffered in TMEM
 // (2 x BN columns) so the epilogue of tile i overlaps the main loop of tile i + 1; shared memory holds a
 // STAGES-deep ring of 128 x 64 (A) and BN x 64 (B) bf16 tiles in the 128-byte swizzle layout.
@@ -28,7 +28,7 @@ constexpr int BM = 128;
 constexpr int BK = 64;
 constexpr int UMMA_K = 16;
 constexpr int A_BYTES = BM * BK * 2;
-constexpr int NUM_THREADS = 256;
+constexpr int NUM_THREADS = 384;
 constexpr int EPI_WARP0 = 4;
 
 template <int BN> struct Cfg {
@@ -84,7 +84,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
     for (int s = 0; s < 2; ++s) {
       tc::mbar_init(&tfull_bar[s], 1);
-      tc::mbar_init(&tempty_bar[s], 128);
+      tc::mbar_init(&tempty_bar[s], 256);
     }
     tc::fence_barrier_init();
   }
@@ -170,11 +170,15 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       }
     }
   } else if (warp >= EPI_WARP0) {
-    // ===================== epilogue =====================
-    const int ew = warp - EPI_WARP0;  // == warp % 4 -> TMEM lanes [32 * ew, 32 * ew + 32)
+    // ===================== epilogue (8 warps: 4 TMEM lane groups x 2 column halves) =====================
+    const int ew = (warp - EPI_WARP0) & 3;     // == warp % 4 -> TMEM lanes [32 * ew, 32 * ew + 32)
+    const int half = (warp - EPI_WARP0) >> 2;  // columns [half * BN / 2, (half + 1) * BN / 2)
+    constexpr int CH_PER_HALF = BN / 64;       // 32-column chunks per half
     int acc = 0;
     uint32_t acc_phase = 0;
     const bool out_f32 = (args.flags & GEMM_OUT_F32) != 0;
+    const bool f_gelu = (args.flags & GEMM_GELU) != 0, f_dgelu = (args.flags & GEMM_DGELU) != 0;
+    const bool has_res = args.residual != nullptr;
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
       const int rem = t % tiles_mn;
       const int n_blk = rem / mblocks, m_blk = rem % mblocks;
@@ -182,11 +186,22 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       tc::tc_fence_after();
       const int row = m_blk * BM + ew * 32 + lane;
       const bool row_ok = row < args.M;
-      const size_t row_off = static_cast<size_t>(row) * args.ldc;
+      const size_t row_off = static_cast<size_t>(row_ok ? row : 0) * args.ldc;
 #pragma unroll 1
-      for (int ch = 0; ch < BN / 32; ++ch) {
+      for (int c2 = 0; c2 < CH_PER_HALF; ++c2) {
+        const int ch = half * CH_PER_HALF + c2;
         const int col0 = n_blk * BN + ch * 32;
         if (col0 >= args.N) break;  // warp-uniform
+        // issue the global reads of this chunk (GELU' pre-activation / residual) before waiting on TMEM
+        uint4 pre[4];
+        const bool need_in = f_dgelu || has_res;
+        if (need_in) {
+          const bf16* src = static_cast<const bf16*>(f_dgelu ? args.aux : args.residual) + row_off + col0;
+#pragma unroll
+          for (int v8 = 0; v8 < 4; ++v8)
+            pre[v8] = (row_ok && col0 + v8 * 8 < args.N) ? __ldg(reinterpret_cast<const uint4*>(src + v8 * 8))
+                                                         : make_uint4(0, 0, 0, 0);
+        }
         uint32_t r[32];
         tc::tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + acc * BN + ch * 32, r);
         tc::tmem_ld_wait();
@@ -199,26 +214,30 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #pragma unroll
             for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[v8 * 8 + j]) * args.alpha;
             if (args.bias != nullptr) {
-#pragma unroll
-              for (int j = 0; j < 8; ++j) v[j] += __ldg(args.bias + col + j);
+              const float4 b0 = __ldg(reinterpret_cast<const float4*>(args.bias + col));
+              const float4 b1 = __ldg(reinterpret_cast<const float4*>(args.bias + col + 4));
+              v[0] += b0.x; v[1] += b0.y; v[2] += b0.z; v[3] += b0.w;
+              v[4] += b1.x; v[5] += b1.y; v[6] += b1.z; v[7] += b1.w;
             }
-            if (args.flags & GEMM_GELU) {
+            if (f_gelu) {
               bf16* aux = static_cast<bf16*>(args.aux) + row_off + col;
               VecIO<bf16>::store(aux, v);
 #pragma unroll
-              for (int j = 0; j < 8; ++j) v[j] = gelu_erf(__bfloat162float(__float2bfloat16_rn(v[j])));
+              for (int j = 0; j < 8; ++j) v[j] = gelu_fast(__bfloat162float(__float2bfloat16_rn(v[j])));
             }
-            if (args.flags & GEMM_DGELU) {
-              float a[8];
-              VecIO<bf16>::load(static_cast<const bf16*>(args.aux) + row_off + col, a);
+            if (need_in) {
+              const uint32_t w[4] = {pre[v8].x, pre[v8].y, pre[v8].z, pre[v8].w};
 #pragma unroll
-              for (int j = 0; j < 8; ++j) v[j] *= gelu_erf_grad(a[j]);
-            }
-            if (args.residual != nullptr) {
-              float a[8];
-              VecIO<bf16>::load(static_cast<const bf16*>(args.residual) + row_off + col, a);
-#pragma unroll
-              for (int j = 0; j < 8; ++j) v[j] += a[j];
+              for (int j = 0; j < 4; ++j) {
+                const float a0 = __uint_as_float(w[j] << 16), a1 = __uint_as_float(w[j] & 0xffff0000u);
+                if (f_dgelu) {
+                  v[2 * j] *= gelu_fast_grad(a0);
+                  v[2 * j + 1] *= gelu_fast_grad(a1);
+                } else {
+                  v[2 * j] += a0;
+                  v[2 * j + 1] += a1;
+                }
+              }
             }
             if (out_f32) {
               float* c = static_cast<float*>(args.C) + row_off + col;
@@ -306,7 +325,14 @@ extern "C" int mb_gemm_tc(const GemmParams* params, void* stream) {
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const bool kmajor = P.sak == 1 && P.sbk == 1;
   const bool mnmajor = P.sam == 1 && P.sbn == 1;
-  const bool wide = P.N > 128;
+  bool wide = P.N > 128;
+  if (kmajor && wide) {
+    // pick the tile width with the smaller quantised cost (waves x tile width; narrow tiles re-read A more)
+    const long long mb = (P.M + BM - 1) / BM, sms = num_sms();
+    const long long w256 = (mb * ((P.N + 255) / 256) + sms - 1) / sms * 256;
+    const long long w128 = (mb * ((P.N + 127) / 128) + sms - 1) / sms * 141;  // 128 * 1.1
+    wide = w256 <= w128;
+  }
   if (kmajor) return wide ? launch<256, false>(P, st) : launch<128, false>(P, st);
   if (mnmajor) return wide ? launch<256, true>(P, st) : launch<128, true>(P, st);
   return -5;
