@@ -126,6 +126,11 @@ typedef struct {
 int mb_gemm_simt(const mb_gemm_params* params, int dtype, void* stream);
 /* The same contractions on tcgen05 tensor cores (bf16 in, fp32 accumulate in TMEM, TMA operand staging). */
 int mb_gemm_tc(const mb_gemm_params* params, void* stream);
+/* `count` (1..4) independent problems of one layer kind (same operand layouts, flags and alpha; M / N / K and all
+ * pointers free) as ONE persistent launch: the per-group encoders / decoders of MAE.encode / MAE.decode
+ * (maestro/ssl/mae.py:289-306, looped per group by encode_or_decode, maestro/ssl/mim.py:396-423) step in lockstep.
+ * Layouts: A and B each K-major or MN-major (forward: K/K, dgrad: K/MN on the untransposed weight, wgrad: MN/MN). */
+int mb_gemm_tc_grouped(const mb_gemm_params* params, int count, void* stream);
 /* softmax(q k^T * scale) of vit_pytorch Attention.attend (check-mode path) and its gradient. */
 int mb_softmax_rows(const float* s, void* p, int dtype, long long rows, int n, float scale, void* stream);
 int mb_softmax_bwd_rows(const void* p, float* dp, void* ds, int dtype, long long rows, int n, float scale,

@@ -89,24 +89,32 @@ __device__ __forceinline__ float gelu_erf_grad(float x) {
 
 // Fast exact-form GELU for the bf16 tensor-core epilogues: erf by Abramowitz-Stegun 7.1.26 (|err| < 1.5e-7, far
 // below bf16 resolution) sharing one exp between erf and the Gaussian term of the derivative.
-__device__ __forceinline__ void gelu_fast_terms(float x, float& cdf, float& pdf) {
-  const float z = fabsf(x) * 0.70710678118654752440f;
-  const float e = __expf(-z * z);                        // exp(-x^2 / 2)
-  const float t = __fdividef(1.0f, fmaf(0.3275911f, z, 1.0f));
-  const float poly = t * (0.254829592f + t * (-0.284496736f + t * (1.421413741f + t * (-1.453152027f + t * 1.061405429f))));
-  const float erf_abs = 1.0f - poly * e;
-  cdf = 0.5f * (1.0f + copysignf(erf_abs, x));
-  pdf = 0.39894228040143267794f * e;
+// q = erfc(|x| / sqrt 2) / 2 (the tail mass beyond |x|) and e = exp(-x^2 / 2); 11 instructions, 2 MUFU (ftz forms:
+// no denormal fix-up code).  Coefficients are the A-S ones halved.
+__device__ __forceinline__ void gelu_fast_terms(float x, float& q, float& e) {
+  const float w = x * (-0.72134752044448170368f * x);      // -x^2 / 2 * log2(e)
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(w));
+  const float d = fmaf(fabsf(x), 0.23164189887f, 1.0f);    // 1 + p * |x| / sqrt 2, p = 0.3275911
+  float t;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(d));
+  float p = fmaf(t, 0.5307027145f, -0.7265760135f);
+  p = fmaf(p, t, 0.7107068705f);
+  p = fmaf(p, t, -0.142248368f);
+  p = fmaf(p, t, 0.127414796f);
+  q = (p * t) * e;
 }
+// gelu(x) = x * Phi(x) = max(x, 0) - |x| * q
 __device__ __forceinline__ float gelu_fast(float x) {
-  float cdf, pdf;
-  gelu_fast_terms(x, cdf, pdf);
-  return x * cdf;
+  float q, e;
+  gelu_fast_terms(x, q, e);
+  return fmaxf(x, 0.0f) - fabsf(q * x);
 }
+// gelu'(x) = Phi(x) + x * phi(x),  Phi(x) = 1/2 + copysign(1/2 - q, x)
 __device__ __forceinline__ float gelu_fast_grad(float x) {
-  float cdf, pdf;
-  gelu_fast_terms(x, cdf, pdf);
-  return fmaf(x, pdf, cdf);
+  float q, e;
+  gelu_fast_terms(x, q, e);
+  const float cdf = 0.5f + copysignf(0.5f - q, x);
+  return fmaf(x * 0.39894228040143267794f, e, cdf);
 }
 
 // Date-encoding channel value: channels [dim-8, dim) of a token are

@@ -1,17 +1,22 @@
-// tcgen05 / TMEM / TMA GEMM for sm_100a (bf16 inputs, fp32 accumulate in tensor memory).
+// tcgen05 / TMEM / TMA GEMM for sm_100a (bf16 inputs, fp32 accumulate in tensor memory), grouped.
 //
-//   C[m, n] = epilogue( sum_k A(m, k) * B(n, k) )
+//   C_p[m, n] = epilogue( sum_k A_p(m, k) * B_p(n, k) )        p = 0 .. count-1 (independent problems, one launch)
 //
-// Two operand layouts (template MN):
-//   MN = false  A is [M, K] and B is [N, K], both K-contiguous       -> forward and dgrad (dgrad reads the
-//                                                                        transposed bf16 weight shadow)
-//   MN = true   A is [K, M] and B is [K, N], both MN-contiguous      -> wgrad  dW[n, k] = sum_t dY[t, n] X[t, k]
-//                                                                        (contraction over tokens, split-K + fp32 red)
+// Operand layouts (template A_MN / B_MN, any combination the callers need):
+//   A K-major  [M, K] (k contiguous), B K-major  [N, K]   -> forward   y = x W^T
+//   A K-major  [M, K],                B MN-major [K, N]   -> dgrad     dx = dy W     (W read in place, no transpose)
+//   A MN-major [K, M],                B MN-major [K, N]   -> wgrad     dW[n, k] = sum_t dY[t, n] X[t, k]
+//                                                            (contraction over tokens, split-K + fp32 red.add)
 // Structure: persistent CTAs (one per SM), warp-specialised: warp 0 = TMA producer, warp 1 = single-thread
-// tcgen05.mma issuer, warp 2 = TMEM allocator, warps 4..11 = epilogue (tcgen05.ld -> registers -> fused
-// bias / GELU / GELU' / residual -> 16-byte global stores).  The accumulator is double-buffered in TMEM
-// (2 x BN columns) so the epilogue of tile i overlaps the main loop of tile i + 1; shared memory holds a
-// STAGES-deep ring of 128 x 64 (A) and BN x 64 (B) bf16 tiles in the 128-byte swizzle layout.
+// tcgen05.mma issuer, warp 2 = TMEM allocator, warps 4..11 = epilogue.  The accumulator is double-buffered in
+// TMEM (2 x BN columns) so the epilogue of tile i overlaps the main loop of tile i + 1; shared memory holds a
+// STAGES-deep ring of 128 x 64 (A) and BN x 64 (B) bf16 tiles in the 128-byte swizzle layout, plus one 4 KB
+// staging buffer per epilogue warp.
+// Epilogue (bf16 outputs): tcgen05.ld -> registers -> fused bias / GELU (+ saved pre-activation) / GELU' /
+// residual -> bf16 -> swizzled shared-memory staging -> TMA tile store (full 128-byte lines, clipped at the
+// matrix edge by the hardware).  Epilogue inputs (residual, saved pre-activation) are read with fully coalesced
+// 16-byte loads (4 rows x 128 B per instruction) and transposed to "thread = row" through the same staging buffer.
+// fp32 outputs (wgrad accumulation) use direct 16-byte stores / red.add.
 #include <mutex>
 #include <unordered_map>
 #include <string>
@@ -30,34 +35,79 @@ constexpr int UMMA_K = 16;
 constexpr int A_BYTES = BM * BK * 2;
 constexpr int NUM_THREADS = 384;
 constexpr int EPI_WARP0 = 4;
+constexpr int EPI_WARPS = 8;
+constexpr int STG_BYTES = 32 * 64 * 2;   // one epilogue warp: 32 rows x 64 bf16 columns
+constexpr int MAX_GROUP = 4;
 
 template <int BN> struct Cfg {
   static constexpr int B_BYTES = BN * BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int STAGES = (BN == 256) ? 4 : 6;
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_WARPS * STG_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
 };
 
-struct TcArgs {
+struct TcProblem {
   void* C;
   const float* bias;
   const void* residual;
   void* aux;
-  int M, N, K;
-  int ldc;
-  int flags;
+  int M, N, K, ldc;
   int splits;
-  float alpha;
+  int mblocks, nblocks;
+  int tile_end;          // exclusive prefix sum of mblocks * nblocks * splits over the group
 };
 
-template <int BN, bool MN>
+struct TcArgs {
+  TcProblem p[MAX_GROUP];
+  int count;
+  int flags;
+  float alpha;
+  int total_tiles;
+};
+
+struct TcMaps {
+  CUtensorMap a[MAX_GROUP], b[MAX_GROUP], c[MAX_GROUP];
+  CUtensorMap x[MAX_GROUP];   // GELU: pre-activation output; GELU': pre-activation input; else residual input
+};
+
+struct TileCoord {
+  int p, m_blk, n_blk, kb0, kb1;
+};
+
+__device__ __forceinline__ TileCoord decode_tile(const TcArgs& args, int t) {
+  TileCoord tc_;
+  int p = 0, start = 0;
+#pragma unroll
+  for (int i = 0; i < MAX_GROUP - 1; ++i)
+    if (i + 1 < args.count && t >= args.p[i].tile_end) { p = i + 1; start = args.p[i].tile_end; }
+  const TcProblem& P = args.p[p];
+  const int tl = t - start;
+  const int tiles_mn = P.mblocks * P.nblocks;
+  const int split = tl / tiles_mn, rem = tl - split * tiles_mn;
+  const int kblocks = (P.K + BK - 1) / BK;
+  const int per = (kblocks + P.splits - 1) / P.splits;
+  tc_.p = p;
+  tc_.n_blk = rem / P.mblocks;
+  tc_.m_blk = rem - tc_.n_blk * P.mblocks;
+  tc_.kb0 = split * per;
+  tc_.kb1 = min(kblocks, tc_.kb0 + per);
+  return tc_;
+}
+
+__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
+  __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&h);
+}
+
+template <int BN, bool A_MN, bool B_MN>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
-gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, TcArgs args) {
+gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcArgs args) {
   using C_ = Cfg<BN>;
   constexpr int STAGES = C_::STAGES;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * C_::STAGE_BYTES);
+  uint8_t* stg_base = smem + STAGES * C_::STAGE_BYTES;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(stg_base + EPI_WARPS * STG_BYTES);
   uint64_t* empty_bar = full_bar + STAGES;
   uint64_t* tfull_bar = empty_bar + STAGES;
   uint64_t* tempty_bar = tfull_bar + 2;
@@ -65,17 +115,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-
-  const int mblocks = (args.M + BM - 1) / BM;
-  const int nblocks = (args.N + BN - 1) / BN;
-  const int kblocks = (args.K + BK - 1) / BK;
-  const int tiles_mn = mblocks * nblocks;
-  const int total_tiles = tiles_mn * args.splits;
-  const int kb_per_split = (kblocks + args.splits - 1) / args.splits;
+  const int total_tiles = args.total_tiles;
 
   if (warp == 0 && lane == 0) {
-    tc::prefetch_tmap(&tmA);
-    tc::prefetch_tmap(&tmB);
+    for (int i = 0; i < args.count; ++i) {
+      tc::prefetch_tmap(&maps.a[i]);
+      tc::prefetch_tmap(&maps.b[i]);
+    }
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < STAGES; ++s) {
@@ -84,7 +130,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
     for (int s = 0; s < 2; ++s) {
       tc::mbar_init(&tfull_bar[s], 1);
-      tc::mbar_init(&tempty_bar[s], 256);
+      tc::mbar_init(&tempty_bar[s], EPI_WARPS * 32);
     }
     tc::fence_barrier_init();
   }
@@ -103,25 +149,41 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       int stage = 0;
       uint32_t phase = 0;
       for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-        const int split = t / tiles_mn, rem = t % tiles_mn;
-        const int n_blk = rem / mblocks, m_blk = rem % mblocks;
-        const int kb0 = split * kb_per_split;
-        const int kb1 = min(kblocks, kb0 + kb_per_split);
-        for (int kb = kb0; kb < kb1; ++kb) {
+        const TileCoord tc_ = decode_tile(args, t);
+        const CUtensorMap* tmA = &maps.a[tc_.p];
+        const CUtensorMap* tmB = &maps.b[tc_.p];
+        {
+          // pull this tile's epilogue input (residual / saved pre-activation) into L2 while the main loop runs
+          const TcProblem& P = args.p[tc_.p];
+          if (!(args.flags & GEMM_OUT_F32) && ((args.flags & GEMM_DGELU) || P.residual != nullptr)) {
+            for (int rg = 0; rg < BM / 32; ++rg) {
+              const int r0 = tc_.m_blk * BM + rg * 32;
+              if (r0 >= P.M) break;
+              for (int cc = 0; cc < BN / 64; ++cc) {
+                const int c0 = tc_.n_blk * BN + cc * 64;
+                if (c0 < P.N) tc::tma_prefetch_l2_2d(&maps.x[tc_.p], c0, r0);
+              }
+            }
+          }
+        }
+        for (int kb = tc_.kb0; kb < tc_.kb1; ++kb) {
           tc::mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* sA = smem + stage * C_::STAGE_BYTES;
           uint8_t* sB = sA + A_BYTES;
           tc::mbar_expect_tx(&full_bar[stage], C_::STAGE_BYTES);
-          if constexpr (!MN) {
-            tc::tma_load_2d(sA, &tmA, &full_bar[stage], kb * BK, m_blk * BM);
-            tc::tma_load_2d(sB, &tmB, &full_bar[stage], kb * BK, n_blk * BN);
+          if constexpr (!A_MN) {
+            tc::tma_load_2d(sA, tmA, &full_bar[stage], kb * BK, tc_.m_blk * BM);
           } else {
 #pragma unroll
             for (int i = 0; i < BM / 64; ++i)
-              tc::tma_load_2d(sA + i * 8192, &tmA, &full_bar[stage], m_blk * BM + i * 64, kb * BK);
+              tc::tma_load_2d(sA + i * 8192, tmA, &full_bar[stage], tc_.m_blk * BM + i * 64, kb * BK);
+          }
+          if constexpr (!B_MN) {
+            tc::tma_load_2d(sB, tmB, &full_bar[stage], kb * BK, tc_.n_blk * BN);
+          } else {
 #pragma unroll
             for (int i = 0; i < BN / 64; ++i)
-              tc::tma_load_2d(sB + i * 8192, &tmB, &full_bar[stage], n_blk * BN + i * 64, kb * BK);
+              tc::tma_load_2d(sB + i * 8192, tmB, &full_bar[stage], tc_.n_blk * BN + i * 64, kb * BK);
           }
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
@@ -130,37 +192,31 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
     if (lane == 0) {
-      constexpr uint32_t idesc = tc::make_idesc_bf16(BM, BN, MN ? 1 : 0, MN ? 1 : 0);
+      constexpr uint32_t idesc = tc::make_idesc_bf16(BM, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
       for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-        const int split = t / tiles_mn;
-        const int kb0 = split * kb_per_split;
-        const int kb1 = min(kblocks, kb0 + kb_per_split);
+        const TileCoord tc_ = decode_tile(args, t);
         tc::mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
         tc::tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * BN;
-        for (int kb = kb0; kb < kb1; ++kb) {
+        for (int kb = tc_.kb0; kb < tc_.kb1; ++kb) {
           tc::mbar_wait(&full_bar[stage], phase);
           tc::tc_fence_after();
           const uint32_t a_addr = tc::smem_u32(smem + stage * C_::STAGE_BYTES);
           const uint32_t b_addr = a_addr + A_BYTES;
 #pragma unroll
           for (int k = 0; k < BK / UMMA_K; ++k) {
-            uint64_t da, db;
-            if constexpr (!MN) {
-              // K-major, 128B swizzle: rows are 128 B, 8-row groups 1024 B apart; K advance = 32 B inside the row
-              da = tc::make_smem_desc(a_addr + k * UMMA_K * 2, 16, 1024);
-              db = tc::make_smem_desc(b_addr + k * UMMA_K * 2, 16, 1024);
-            } else {
-              // MN-major, 128B swizzle: 64-element MN chunks 8192 B apart (one TMA box each), 8-row K groups
-              // 1024 B apart; K advance = 16 rows = 2048 B
-              da = tc::make_smem_desc(a_addr + k * UMMA_K * 128, 8192, 1024);
-              db = tc::make_smem_desc(b_addr + k * UMMA_K * 128, 8192, 1024);
-            }
-            tc::umma_bf16(d_tmem, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+            // K-major, 128B swizzle: rows are 128 B, 8-row groups 1024 B apart; K advance = 32 B inside the row.
+            // MN-major, 128B swizzle: 64-element MN chunks 8192 B apart (one TMA box each), 8-row K groups 1024 B
+            // apart; K advance = 16 rows = 2048 B.
+            const uint64_t da = A_MN ? tc::make_smem_desc(a_addr + k * UMMA_K * 128, 8192, 1024)
+                                     : tc::make_smem_desc(a_addr + k * UMMA_K * 2, 16, 1024);
+            const uint64_t db = B_MN ? tc::make_smem_desc(b_addr + k * UMMA_K * 128, 8192, 1024)
+                                     : tc::make_smem_desc(b_addr + k * UMMA_K * 2, 16, 1024);
+            tc::umma_bf16(d_tmem, da, db, idesc, (kb > tc_.kb0 || k > 0) ? 1u : 0u);
           }
           tc::umma_commit(&empty_bar[stage]);
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
@@ -171,93 +227,199 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
   } else if (warp >= EPI_WARP0) {
     // ===================== epilogue (8 warps: 4 TMEM lane groups x 2 column halves) =====================
-    const int ew = (warp - EPI_WARP0) & 3;     // == warp % 4 -> TMEM lanes [32 * ew, 32 * ew + 32)
+    const int ew = warp & 3;                   // TMEM lanes [32 * ew, 32 * ew + 32) (a warp may only touch its quarter)
     const int half = (warp - EPI_WARP0) >> 2;  // columns [half * BN / 2, (half + 1) * BN / 2)
-    constexpr int CH_PER_HALF = BN / 64;       // 32-column chunks per half
+    uint8_t* stg = stg_base + (warp - EPI_WARP0) * STG_BYTES;
+    const uint32_t stg_u32 = tc::smem_u32(stg);
+    // staging addresses (128-byte swizzle, as the TMA store map expects): "own row" = row `lane`, 16-byte chunk j
+    const uint32_t own_base = stg_u32 + lane * 128;
+    const uint32_t own_x = static_cast<uint32_t>(lane & 7);
     int acc = 0;
     uint32_t acc_phase = 0;
     const bool out_f32 = (args.flags & GEMM_OUT_F32) != 0;
     const bool f_gelu = (args.flags & GEMM_GELU) != 0, f_dgelu = (args.flags & GEMM_DGELU) != 0;
-    const bool has_res = args.residual != nullptr;
+    const float alpha = args.alpha;
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-      const int rem = t % tiles_mn;
-      const int n_blk = rem / mblocks, m_blk = rem % mblocks;
-      tc::mbar_wait(&tfull_bar[acc], acc_phase);
-      tc::tc_fence_after();
-      const int row = m_blk * BM + ew * 32 + lane;
-      const bool row_ok = row < args.M;
-      const size_t row_off = static_cast<size_t>(row_ok ? row : 0) * args.ldc;
-#pragma unroll 1
-      for (int c2 = 0; c2 < CH_PER_HALF; ++c2) {
-        const int ch = half * CH_PER_HALF + c2;
-        const int col0 = n_blk * BN + ch * 32;
-        if (col0 >= args.N) break;  // warp-uniform
-        // issue the global reads of this chunk (GELU' pre-activation / residual) before waiting on TMEM
-        uint4 pre[4];
+      const TileCoord tc_ = decode_tile(args, t);
+      const TcProblem& P = args.p[tc_.p];
+      const int row0 = tc_.m_blk * BM + ew * 32;
+      const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + acc * BN;
+      if (!out_f32) {
+        // ---------------- bf16 outputs through shared memory + TMA store, 64-column chunks ----------------
+        constexpr int CH_PER_HALF = BN / 128;
+        const bool has_res = P.residual != nullptr;
         const bool need_in = f_dgelu || has_res;
-        if (need_in) {
-          const bf16* src = static_cast<const bf16*>(f_dgelu ? args.aux : args.residual) + row_off + col0;
+        const bf16* src = static_cast<const bf16*>(f_dgelu ? P.aux : P.residual);
+        int nch = 0;
 #pragma unroll
-          for (int v8 = 0; v8 < 4; ++v8)
-            pre[v8] = (row_ok && col0 + v8 * 8 < args.N) ? __ldg(reinterpret_cast<const uint4*>(src + v8 * 8))
-                                                         : make_uint4(0, 0, 0, 0);
+        for (int c2 = 0; c2 < CH_PER_HALF; ++c2)
+          if (tc_.n_blk * BN + (half * CH_PER_HALF + c2) * 64 < P.N) nch = c2 + 1;
+        if (nch == 0) {
+          tc::mbar_wait(&tfull_bar[acc], acc_phase);
+          tc::tc_fence_before();
+          tc::mbar_arrive(&tempty_bar[acc]);
         }
-        uint32_t r[32];
-        tc::tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + acc * BN + ch * 32, r);
-        tc::tmem_ld_wait();
-        if (row_ok) {
+#pragma unroll 1
+        for (int c2 = 0; c2 < nch; ++c2) {
+          const int ch = half * CH_PER_HALF + c2;
+          const int col0 = tc_.n_blk * BN + ch * 64;
+          // (1) coalesced prefetch of the epilogue input: instruction i covers rows 4i .. 4i+3, 8 lanes per row
+          uint4 pre[8];
+          if (need_in) {
+            const int cc = col0 + (lane & 7) * 8;
 #pragma unroll
-          for (int v8 = 0; v8 < 4; ++v8) {
-            const int col = col0 + v8 * 8;
-            if (col >= args.N) break;
-            float v[8];
-#pragma unroll
-            for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[v8 * 8 + j]) * args.alpha;
-            if (args.bias != nullptr) {
-              const float4 b0 = __ldg(reinterpret_cast<const float4*>(args.bias + col));
-              const float4 b1 = __ldg(reinterpret_cast<const float4*>(args.bias + col + 4));
-              v[0] += b0.x; v[1] += b0.y; v[2] += b0.z; v[3] += b0.w;
-              v[4] += b1.x; v[5] += b1.y; v[6] += b1.z; v[7] += b1.w;
+            for (int i = 0; i < 8; ++i) {
+              const int rr = row0 + i * 4 + (lane >> 3);
+              pre[i] = (rr < P.M && cc < P.N)
+                           ? __ldg(reinterpret_cast<const uint4*>(src + static_cast<size_t>(rr) * P.ldc + cc))
+                           : make_uint4(0, 0, 0, 0);
             }
-            if (f_gelu) {
-              bf16* aux = static_cast<bf16*>(args.aux) + row_off + col;
-              VecIO<bf16>::store(aux, v);
+          }
+          // (2) accumulator chunk -> registers
+          if (c2 == 0) {
+            tc::mbar_wait(&tfull_bar[acc], acc_phase);
+            tc::tc_fence_after();
+          }
+          uint32_t r[64];
+          tc::tmem_ld_32x32(t_addr + ch * 64, r);
+          tc::tmem_ld_32x32(t_addr + ch * 64 + 32, r + 32);
+          tc::tmem_ld_wait();
+          if (c2 == nch - 1) {   // accumulator fully read: hand the TMEM buffer back to the MMA warp
+            tc::tc_fence_before();
+            tc::mbar_arrive(&tempty_bar[acc]);
+          }
+          // (3) transpose the input chunk to "thread = row" through the staging buffer
+          if (need_in) {
+            if (lane == 0) tc::tma_store_wait_read();
+            __syncwarp();
 #pragma unroll
-              for (int j = 0; j < 8; ++j) v[j] = gelu_fast(__bfloat162float(__float2bfloat16_rn(v[j])));
+            for (int i = 0; i < 8; ++i) {
+              const uint32_t rr = i * 4 + (lane >> 3);
+              const uint32_t a = stg_u32 + rr * 128 + (((lane & 7) ^ (rr & 7)) << 4);
+              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(pre[i].x), "r"(pre[i].y),
+                           "r"(pre[i].z), "r"(pre[i].w) : "memory");
             }
-            if (need_in) {
-              const uint32_t w[4] = {pre[v8].x, pre[v8].y, pre[v8].z, pre[v8].w};
+            __syncwarp();
 #pragma unroll
-              for (int j = 0; j < 4; ++j) {
-                const float a0 = __uint_as_float(w[j] << 16), a1 = __uint_as_float(w[j] & 0xffff0000u);
+            for (int j = 0; j < 8; ++j) {
+              const uint32_t a = own_base + ((j ^ own_x) << 4);
+              asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(pre[j].x), "=r"(pre[j].y), "=r"(pre[j].z),
+                           "=r"(pre[j].w) : "r"(a) : "memory");
+            }
+            __syncwarp();
+          }
+          // (4) alpha, bias
+          float* v = reinterpret_cast<float*>(r);
+          if (P.bias != nullptr) {
+#pragma unroll
+            for (int q = 0; q < 16; ++q) {
+              const float4 b = (col0 + q * 4 < P.N) ? __ldg(reinterpret_cast<const float4*>(P.bias + col0 + q * 4))
+                                                    : make_float4(0.f, 0.f, 0.f, 0.f);
+              v[4 * q] = fmaf(v[4 * q], alpha, b.x);
+              v[4 * q + 1] = fmaf(v[4 * q + 1], alpha, b.y);
+              v[4 * q + 2] = fmaf(v[4 * q + 2], alpha, b.z);
+              v[4 * q + 3] = fmaf(v[4 * q + 3], alpha, b.w);
+            }
+          } else if (alpha != 1.0f) {
+#pragma unroll
+            for (int q = 0; q < 64; ++q) v[q] *= alpha;
+          }
+          // (5) GELU: store the bf16 pre-activation (second output), activate the rounded value
+          if (f_gelu) {
+            if (lane == 0) tc::tma_store_wait_read();
+            __syncwarp();
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              uint32_t w[4];
+#pragma unroll
+              for (int q = 0; q < 4; ++q) {
+                w[q] = pack_bf16x2(v[8 * j + 2 * q], v[8 * j + 2 * q + 1]);
+                v[8 * j + 2 * q] = gelu_fast(__uint_as_float(w[q] << 16));
+                v[8 * j + 2 * q + 1] = gelu_fast(__uint_as_float(w[q] & 0xffff0000u));
+              }
+              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(own_base + ((j ^ own_x) << 4)), "r"(w[0]),
+                           "r"(w[1]), "r"(w[2]), "r"(w[3]) : "memory");
+            }
+            tc::fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) {
+              tc::tma_store_2d(&maps.x[tc_.p], stg, col0, row0);
+              tc::tma_store_commit();
+            }
+          }
+          // (6) GELU' / residual
+          if (need_in) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const uint32_t w[4] = {pre[j].x, pre[j].y, pre[j].z, pre[j].w};
+#pragma unroll
+              for (int q = 0; q < 4; ++q) {
+                const float a0 = __uint_as_float(w[q] << 16), a1 = __uint_as_float(w[q] & 0xffff0000u);
                 if (f_dgelu) {
-                  v[2 * j] *= gelu_fast_grad(a0);
-                  v[2 * j + 1] *= gelu_fast_grad(a1);
+                  v[8 * j + 2 * q] *= gelu_fast_grad(a0);
+                  v[8 * j + 2 * q + 1] *= gelu_fast_grad(a1);
                 } else {
-                  v[2 * j] += a0;
-                  v[2 * j + 1] += a1;
+                  v[8 * j + 2 * q] += a0;
+                  v[8 * j + 2 * q + 1] += a1;
                 }
               }
             }
-            if (out_f32) {
-              float* c = static_cast<float*>(args.C) + row_off + col;
-              if (args.flags & GEMM_ACCUM) {
-                atomicAdd(reinterpret_cast<float4*>(c), make_float4(v[0], v[1], v[2], v[3]));
-                atomicAdd(reinterpret_cast<float4*>(c + 4), make_float4(v[4], v[5], v[6], v[7]));
-              } else {
-                VecIO<float>::store(c, v);
-                VecIO<float>::store(c + 4, v + 4);
+          }
+          // (7) main output
+          if (lane == 0) tc::tma_store_wait_read();
+          __syncwarp();
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const uint32_t w0 = pack_bf16x2(v[8 * j], v[8 * j + 1]), w1 = pack_bf16x2(v[8 * j + 2], v[8 * j + 3]);
+            const uint32_t w2 = pack_bf16x2(v[8 * j + 4], v[8 * j + 5]), w3 = pack_bf16x2(v[8 * j + 6], v[8 * j + 7]);
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(own_base + ((j ^ own_x) << 4)), "r"(w0),
+                         "r"(w1), "r"(w2), "r"(w3) : "memory");
+          }
+          tc::fence_proxy_async();
+          __syncwarp();
+          if (lane == 0) {
+            tc::tma_store_2d(&maps.c[tc_.p], stg, col0, row0);
+            tc::tma_store_commit();
+          }
+        }
+      } else {
+        // ---------------- fp32 outputs (gradient accumulation): direct 16-byte stores / red.add ----------------
+        constexpr int CH_PER_HALF = BN / 64;       // 32-column chunks per half
+        tc::mbar_wait(&tfull_bar[acc], acc_phase);
+        tc::tc_fence_after();
+        const int row = row0 + lane;
+        const bool row_ok = row < P.M;
+        float* crow = static_cast<float*>(P.C) + static_cast<size_t>(row_ok ? row : 0) * P.ldc;
+#pragma unroll 1
+        for (int c2 = 0; c2 < CH_PER_HALF; ++c2) {
+          const int ch = half * CH_PER_HALF + c2;
+          const int col0 = tc_.n_blk * BN + ch * 32;
+          if (col0 >= P.N) break;  // warp-uniform
+          uint32_t r[32];
+          tc::tmem_ld_32x32(t_addr + ch * 32, r);
+          tc::tmem_ld_wait();
+          if (row_ok) {
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+              const int col = col0 + q * 4;
+              if (col >= P.N) break;
+              float4 o = make_float4(__uint_as_float(r[4 * q]) * alpha, __uint_as_float(r[4 * q + 1]) * alpha,
+                                     __uint_as_float(r[4 * q + 2]) * alpha, __uint_as_float(r[4 * q + 3]) * alpha);
+              if (P.bias != nullptr) {
+                const float4 b = __ldg(reinterpret_cast<const float4*>(P.bias + col));
+                o.x += b.x; o.y += b.y; o.z += b.z; o.w += b.w;
               }
-            } else {
-              VecIO<bf16>::store(static_cast<bf16*>(args.C) + row_off + col, v);
+              if (args.flags & GEMM_ACCUM) atomicAdd(reinterpret_cast<float4*>(crow + col), o);
+              else *reinterpret_cast<float4*>(crow + col) = o;
             }
           }
         }
+        tc::tc_fence_before();
+        tc::mbar_arrive(&tempty_bar[acc]);
       }
-      tc::tc_fence_before();
-      tc::mbar_arrive(&tempty_bar[acc]);
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
+    if (lane == 0) tc::tma_store_wait_all();   // shared memory must stay valid until the last store has read it
   }
 
   tc::tc_fence_before();
@@ -275,65 +437,127 @@ int get_tmap(CUtensorMap* out, const void* ptr, uint64_t d0, uint64_t d1, uint64
 
 int num_sms() { return mb_num_sms(); }
 
-template <int BN, bool MN>
-int launch(const GemmParams& P, cudaStream_t st) {
+template <int BN, bool A_MN, bool B_MN>
+int launch(const GemmParams* Ps, int count, cudaStream_t st) {
   using C_ = Cfg<BN>;
-  CUtensorMap tmA, tmB;
-  int rc;
-  if (!MN) {
-    if ((rc = get_tmap(&tmA, P.A, P.K, P.M, P.sam, BK, BM)) != 0) return rc;
-    if ((rc = get_tmap(&tmB, P.B, P.K, P.N, P.sbn, BK, BN)) != 0) return rc;
-  } else {
-    if ((rc = get_tmap(&tmA, P.A, P.M, P.K, P.sak, 64, BK)) != 0) return rc;
-    if ((rc = get_tmap(&tmB, P.B, P.N, P.K, P.sbk, 64, BK)) != 0) return rc;
-  }
-  const int mblocks = (P.M + BM - 1) / BM, nblocks = (P.N + BN - 1) / BN, kblocks = (P.K + BK - 1) / BK;
-  int splits = 1;
-  if (MN && (P.flags & GEMM_ACCUM)) {
-    // split the token contraction so that the grid covers the chip (fp32 red.add combines the partials)
-    const int tiles = mblocks * nblocks;
-    splits = (2 * num_sms() + tiles - 1) / tiles;
-    if (splits > kblocks) splits = kblocks;
-    if (splits < 1) splits = 1;
-    const int per = (kblocks + splits - 1) / splits;
-    splits = (kblocks + per - 1) / per;  // no empty split
-  }
+  TcMaps maps;
   TcArgs a;
-  a.C = P.C; a.bias = P.bias; a.residual = P.residual; a.aux = P.aux;
-  a.M = P.M; a.N = P.N; a.K = P.K; a.ldc = P.ldc; a.flags = P.flags; a.splits = splits; a.alpha = P.alpha;
-  const int total = mblocks * nblocks * splits;
+  std::memset(&a, 0, sizeof(a));
+  const int flags = Ps[0].flags;
+  const bool out_f32 = (flags & GEMM_OUT_F32) != 0;
+  int rc;
+  long long tiles_mn_total = 0;
+  for (int i = 0; i < count; ++i) {
+    const GemmParams& P = Ps[i];
+    if (!A_MN) rc = get_tmap(&maps.a[i], P.A, P.K, P.M, P.sam, BK, BM);
+    else rc = get_tmap(&maps.a[i], P.A, P.M, P.K, P.sak, 64, BK);
+    if (rc != 0) return rc;
+    if (!B_MN) rc = get_tmap(&maps.b[i], P.B, P.K, P.N, P.sbn, BK, BN);
+    else rc = get_tmap(&maps.b[i], P.B, P.N, P.K, P.sbk, 64, BK);
+    if (rc != 0) return rc;
+    if (!out_f32) {
+      if ((rc = get_tmap(&maps.c[i], P.C, P.N, P.M, P.ldc, 64, 32)) != 0) return rc;
+      // x: GELU -> saved pre-activation (second output); GELU' -> the same tensor as epilogue input; else residual
+      const void* xp = (flags & (GEMM_GELU | GEMM_DGELU)) ? P.aux : P.residual;
+      if ((flags & (GEMM_GELU | GEMM_DGELU)) && xp == nullptr) return -6;
+      if (xp != nullptr) {
+        if ((reinterpret_cast<uintptr_t>(xp) & 15) != 0) return -11;
+        if ((rc = get_tmap(&maps.x[i], xp, P.N, P.M, P.ldc, 64, 32)) != 0) return rc;
+      } else {
+        maps.x[i] = maps.c[i];
+      }
+    } else {
+      maps.c[i] = maps.a[i];
+      maps.x[i] = maps.a[i];
+    }
+    TcProblem& q = a.p[i];
+    q.C = P.C; q.bias = P.bias; q.residual = P.residual; q.aux = P.aux;
+    q.M = P.M; q.N = P.N; q.K = P.K; q.ldc = P.ldc;
+    q.mblocks = (P.M + BM - 1) / BM;
+    q.nblocks = (P.N + BN - 1) / BN;
+    tiles_mn_total += static_cast<long long>(q.mblocks) * q.nblocks;
+  }
+  for (int i = count; i < MAX_GROUP; ++i) {
+    maps.a[i] = maps.a[0]; maps.b[i] = maps.b[0]; maps.c[i] = maps.c[0]; maps.x[i] = maps.x[0];
+  }
+  int total = 0;
+  for (int i = 0; i < count; ++i) {
+    TcProblem& q = a.p[i];
+    const int kblocks = (q.K + BK - 1) / BK;
+    int splits = 1;
+    if (flags & GEMM_ACCUM) {
+      // split the contraction so that the grid covers the chip (fp32 red.add combines the partials)
+      splits = static_cast<int>((2LL * num_sms() + tiles_mn_total - 1) / tiles_mn_total);
+      if (splits > kblocks) splits = kblocks;
+      if (splits < 1) splits = 1;
+      const int per = (kblocks + splits - 1) / splits;
+      splits = (kblocks + per - 1) / per;  // no empty split
+    }
+    q.splits = splits;
+    total += q.mblocks * q.nblocks * splits;
+    q.tile_end = total;
+  }
+  a.count = count;
+  a.flags = flags;
+  a.alpha = Ps[0].alpha;
+  a.total_tiles = total;
   const int grid = total < num_sms() ? total : num_sms();
   static bool attr_set = false;
   if (!attr_set) {
-    cudaFuncSetAttribute(gemm_tc_kernel<BN, MN>, cudaFuncAttributeMaxDynamicSharedMemorySize, C_::SMEM_BYTES);
+    cudaFuncSetAttribute(gemm_tc_kernel<BN, A_MN, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize, C_::SMEM_BYTES);
     attr_set = true;
   }
-  gemm_tc_kernel<BN, MN><<<grid, NUM_THREADS, C_::SMEM_BYTES, st>>>(tmA, tmB, a);
+  gemm_tc_kernel<BN, A_MN, B_MN><<<grid, NUM_THREADS, C_::SMEM_BYTES, st>>>(maps, a);
   cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? 0 : static_cast<int>(e);
 }
 
 }  // namespace
 
-// bf16 only.  Supported operand layouts: (sak == 1 && sbk == 1) K-major, (sam == 1 && sbn == 1) MN-major.
-// Unbatched (nb1 == nb2 == 1).  N % 8 == 0, ldc % 8 == 0.
-extern "C" int mb_gemm_tc(const GemmParams* params, void* stream) {
-  const GemmParams& P = *params;
-  if (P.M == 0 || P.N == 0) return 0;
-  if (P.nb1 != 1 || P.nb2 != 1) return -3;
-  if (P.N % 8 != 0 || P.ldc % 8 != 0 || P.K <= 0) return -4;
+// bf16 only.  `params` points to `count` (1..4) problems launched as ONE persistent kernel; they must share the
+// operand layout, flags and alpha (M, N, K and all pointers may differ).
+// Layouts: A K-major (sak == 1) or MN-major (sam == 1); B K-major (sbk == 1) or MN-major (sbn == 1).
+// Unbatched (nb1 == nb2 == 1).  N % 8 == 0, ldc % 8 == 0, all base pointers 16-byte aligned.
+extern "C" int mb_gemm_tc_grouped(const GemmParams* params, int count, void* stream) {
+  if (count < 1 || count > MAX_GROUP) return -2;
+  GemmParams live[MAX_GROUP];
+  int n = 0;
+  for (int i = 0; i < count; ++i) {
+    const GemmParams& P = params[i];
+    if (P.M == 0 || P.N == 0) continue;
+    if (P.nb1 != 1 || P.nb2 != 1) return -3;
+    if (P.N % 8 != 0 || P.ldc % 8 != 0 || P.K <= 0) return -4;
+    if (P.flags != params[0].flags || P.alpha != params[0].alpha) return -7;
+    if ((P.sak == 1) != (params[0].sak == 1) || (P.sbk == 1) != (params[0].sbk == 1)) return -7;
+    if ((reinterpret_cast<uintptr_t>(P.C) & 15) != 0) return -11;
+    live[n++] = P;
+  }
+  if (n == 0) return 0;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  const bool kmajor = P.sak == 1 && P.sbk == 1;
-  const bool mnmajor = P.sam == 1 && P.sbn == 1;
-  bool wide = P.N > 128;
-  if (kmajor && wide) {
+  const GemmParams& P0 = live[0];
+  const bool a_k = P0.sak == 1, a_mn = !a_k && P0.sam == 1;
+  const bool b_k = P0.sbk == 1, b_mn = !b_k && P0.sbn == 1;
+  if (!(a_k || a_mn) || !(b_k || b_mn)) return -5;
+  int maxN = 0;
+  for (int i = 0; i < n; ++i) maxN = live[i].N > maxN ? live[i].N : maxN;
+  bool wide = maxN > 128;
+  if (wide && !(P0.flags & GEMM_ACCUM)) {
     // pick the tile width with the smaller quantised cost (waves x tile width; narrow tiles re-read A more)
-    const long long mb = (P.M + BM - 1) / BM, sms = num_sms();
-    const long long w256 = (mb * ((P.N + 255) / 256) + sms - 1) / sms * 256;
-    const long long w128 = (mb * ((P.N + 127) / 128) + sms - 1) / sms * 141;  // 128 * 1.1
+    long long t256 = 0, t128 = 0;
+    for (int i = 0; i < n; ++i) {
+      const long long mb = (live[i].M + BM - 1) / BM;
+      t256 += mb * ((live[i].N + 255) / 256);
+      t128 += mb * ((live[i].N + 127) / 128);
+    }
+    const long long sms = num_sms();
+    const long long w256 = (t256 + sms - 1) / sms * 256;
+    const long long w128 = (t128 + sms - 1) / sms * 141;  // 128 * 1.1
     wide = w256 <= w128;
   }
-  if (kmajor) return wide ? launch<256, false>(P, st) : launch<128, false>(P, st);
-  if (mnmajor) return wide ? launch<256, true>(P, st) : launch<128, true>(P, st);
+  if (a_k && b_k) return wide ? launch<256, false, false>(live, n, st) : launch<128, false, false>(live, n, st);
+  if (a_k && b_mn) return wide ? launch<256, false, true>(live, n, st) : launch<128, false, true>(live, n, st);
+  if (a_mn && b_mn) return wide ? launch<256, true, true>(live, n, st) : launch<128, true, true>(live, n, st);
   return -5;
 }
+
+extern "C" int mb_gemm_tc(const GemmParams* params, void* stream) { return mb_gemm_tc_grouped(params, 1, stream); }

@@ -38,7 +38,7 @@ class ParamArena:
     final during backward, so that contiguous arena ranges can be all-reduced while backward still runs.
     """
 
-    def __init__(self, shapes: dict[str, tuple], order: list[str], device, need_t: set[str], bf16: bool) -> None:
+    def __init__(self, shapes: dict[str, tuple], order: list[str], device, bf16: bool) -> None:
         self.offsets: dict[str, int] = {}
         off = 0
         for name in order:
@@ -56,19 +56,9 @@ class ParamArena:
         self.G = {n: self._view(self.grad, n) for n in order}
         self.shadow = None
         self.Wb: dict[str, torch.Tensor] = {}
-        self.WbT: dict[str, torch.Tensor] = {}
         if bf16:
             self.shadow = torch.zeros(off, dtype=torch.bfloat16, device=device)
             self.Wb = {n: self._view(self.shadow, n) for n in order}
-            t_off, self.t_offsets = 0, {}
-            for n in order:
-                if n in need_t:
-                    self.t_offsets[n] = t_off
-                    t_off += _pad8(self.P[n].numel())
-            self.shadow_t = torch.zeros(max(t_off, 8), dtype=torch.bfloat16, device=device)
-            for n, o in self.t_offsets.items():
-                rows, cols = self.shapes[n][0], self.P[n].numel() // self.shapes[n][0]
-                self.WbT[n] = self.shadow_t[o:o + rows * cols].view(cols, rows)
 
     def _view(self, flat: torch.Tensor, name: str) -> torch.Tensor:
         shp = self.shapes[name]
@@ -86,9 +76,6 @@ class ParamArena:
         if self.shadow is None:
             return
         K.cast_bf16(self.param, self.shadow)
-        for n, dst in self.WbT.items():
-            rows = self.shapes[n][0]
-            K.cast_transpose_bf16(self.P[n].view(rows, -1), dst)
 
 
 @dataclass
@@ -281,9 +268,7 @@ class PretrainEngine:
         order += keys("encoder.")
         order += keys("patch_embed.")
         assert len(order) == len(shapes) and set(order) == set(shapes)
-        need_t = {k for k in shapes if k.endswith("weight") and len(shapes[k]) >= 2
-                  and not k.startswith("patch_embed.")}
-        self.arena = ParamArena(shapes, order, self.device, need_t, self.dtype == torch.bfloat16)
+        self.arena = ParamArena(shapes, order, self.device, self.dtype == torch.bfloat16)
         self.P, self.G = self.arena.P, self.arena.G
         self.shadows_fresh = False
 
@@ -327,12 +312,8 @@ class PretrainEngine:
         if dx is None:
             return
         fl = GEMM_DGELU if dgelu_aux is not None else 0
-        if self.dtype == torch.bfloat16:
-            self.K.gemm(dy, self.arena.WbT[wname], dx, M, Kd, N, sam=N, sak=1, sbn=N, sbk=1, ldc=Kd,
-                        aux=dgelu_aux, flags=fl)
-        else:
-            self.K.gemm(dy, self.P[wname], dx, M, Kd, N, sam=N, sak=1, sbn=1, sbk=Kd, ldc=Kd,
-                        aux=dgelu_aux, flags=fl)
+        # dx[m, k] = sum_n dy[m, n] W[n, k]: the weight is read in place as an MN-major operand (no transposed copy)
+        self.K.gemm(dy, self._w(wname), dx, M, Kd, N, sam=N, sak=1, sbn=1, sbk=Kd, ldc=Kd, aux=dgelu_aux, flags=fl)
 
     # ------------------------------------------------------------------ attention
     def attn_fwd(self, qkv, Bn, N, H, dh):

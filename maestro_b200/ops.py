@@ -189,9 +189,8 @@ class Kernels:
         _ck(self.L.mb_loss_fwd_bwd(C.byref(P), _dt(preds[0]), _stream()), "loss_fwd_bwd")
 
     # ------------------------------------------------------------------ GEMM
-    def gemm(self, A, B, Cm, M, N, K, sam, sak, sbn, sbk, ldc, bias=None, residual=None, aux=None, flags=0,
-             alpha=1.0, nb1=1, nb2=1, a_s=(0, 0), b_s=(0, 0), c_s=(0, 0), a_off=0, b_off=0, c_off=0):
-        """C[m, n] = epilogue(alpha * sum_k A[m*sam + k*sak] * B[n*sbn + k*sbk]); offsets in elements."""
+    def _gemm_params(self, A, B, Cm, M, N, K, sam, sak, sbn, sbk, ldc, bias=None, residual=None, aux=None, flags=0,
+                     alpha=1.0, nb1=1, nb2=1, a_s=(0, 0), b_s=(0, 0), c_s=(0, 0), a_off=0, b_off=0, c_off=0):
         if not (A.is_cuda and B.is_cuda and Cm.is_cuda):
             raise RuntimeError("maestro_b200 kernels need CUDA tensors (there is no CPU fallback)")
         P = _lib.GemmParams()
@@ -211,15 +210,40 @@ class Kernels:
         if Cm.dtype == torch.float32 and A.dtype != torch.float32:
             flags |= GEMM_OUT_F32
         P.flags = flags
-        self.launches += 1
+        a_k, a_mn = sak == 1 and sam % 8 == 0, sam == 1 and sak % 8 == 0
+        b_k, b_mn = sbk == 1 and sbn % 8 == 0, sbn == 1 and sbk % 8 == 0
         tc_ok = (self.use_tc and A.dtype == torch.bfloat16 and nb1 == 1 and nb2 == 1 and N % 8 == 0 and ldc % 8 == 0
-                 and ((sak == 1 and sbk == 1 and sam % 8 == 0 and sbn % 8 == 0)
-                      or (sam == 1 and sbn == 1 and sak % 8 == 0 and sbk % 8 == 0))
-                 and P.A % 16 == 0 and P.B % 16 == 0)
+                 and ((a_k and (b_k or b_mn)) or (a_mn and not a_k and b_mn and not b_k))
+                 and P.A % 16 == 0 and P.B % 16 == 0 and P.C % 16 == 0
+                 and (aux is None or P.aux % 16 == 0))
+        return P, tc_ok
+
+    def gemm(self, A, B, Cm, M, N, K, sam, sak, sbn, sbk, ldc, **kw):
+        """C[m, n] = epilogue(alpha * sum_k A[m*sam + k*sak] * B[n*sbn + k*sbk]); offsets in elements."""
+        P, tc_ok = self._gemm_params(A, B, Cm, M, N, K, sam, sak, sbn, sbk, ldc, **kw)
+        self.launches += 1
         if tc_ok:
             _ck(self.L.mb_gemm_tc(C.byref(P), _stream()), "gemm_tc")
         else:
             _ck(self.L.mb_gemm_simt(C.byref(P), _dt(A), _stream()), "gemm_simt")
+
+    def gemm_grouped(self, problems):
+        """Independent GEMMs of one layer kind (same layouts / flags, different operands) as ONE launch.
+
+        ``problems``: list of ``(args, kwargs)`` of :meth:`gemm`.  Groups of up to 4 tensor-core problems share a
+        persistent kernel (``mb_gemm_tc_grouped``); anything the tensor-core path cannot take runs one by one.
+        """
+        built = [self._gemm_params(*a, **kw) for a, kw in problems]
+        tc = [P for P, ok in built if ok]
+        for (P, ok), (a, _) in zip(built, problems):
+            if not ok:
+                self.launches += 1
+                _ck(self.L.mb_gemm_simt(C.byref(P), _dt(a[0]), _stream()), "gemm_simt")
+        for i in range(0, len(tc), 4):
+            chunk = tc[i:i + 4]
+            arr = (_lib.GemmParams * len(chunk))(*chunk)
+            self.launches += 1
+            _ck(self.L.mb_gemm_tc_grouped(arr, len(chunk), _stream()), "gemm_tc_grouped")
 
     def softmax_rows(self, s, p, rows, n, scale):
         self.launches += 1

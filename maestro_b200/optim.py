@@ -53,8 +53,5 @@ class FusedAdamW:
         self.hyper.copy_(h, non_blocking=True)
         a = self.engine.arena
         self.K.adamw_step(a.param, a.grad, self.m, self.v, a.shadow, self.hyper, True)
-        # the plain shadow is fresh; transposed shadows are rebuilt by the engine
-        if a.shadow is not None:
-            for n, dst in a.WbT.items():
-                self.K.cast_transpose_bf16(a.P[n].view(a.shapes[n][0], -1), dst)
+        # the kernel refreshed the bf16 shadow in the same pass (dgrad reads it untransposed: no other copies)
         self.engine.shadows_fresh = True

@@ -244,6 +244,10 @@ class FakeKernels:
             v = v + cv.float()
         cv.copy_(v.to(Cm.dtype))
 
+    def gemm_grouped(self, problems):
+        for a, kw in problems:
+            self.gemm(*a, **kw)
+
     def softmax_rows(self, s, p, rows, n, scale):
         p.reshape(-1)[:rows * n].copy_(torch.softmax(s.reshape(-1)[:rows * n].reshape(rows, n) * scale, -1)
                                        .to(p.dtype).reshape(-1))

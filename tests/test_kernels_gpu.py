@@ -327,6 +327,42 @@ def test_gemm_wgrad_and_dgrad_layouts(KK, dt, T, N, Kd):
         close(x, y, rtol=2e-2 if dt == torch.bfloat16 else 1e-4, atol=(2e-2 if dt == torch.bfloat16 else 1e-4) * s)
 
 
+def test_gemm_grouped_matches_single_launches(KK):
+    """Four problems of one layer kind (different row counts / operands) in ONE persistent launch: fwd with GELU,
+    fwd with residual, dgrad on the untransposed weight (+GELU'), wgrad with split-K accumulation."""
+    dt = torch.bfloat16
+    Ms, N, Kd = [1000, 256, 400, 70], 768, 512
+
+    def run(K):
+        outs = []
+        X = [rnd(M, Kd, dt=dt, seed=10 + i, scale=0.5) for i, M in enumerate(Ms)]
+        W = [rnd(N, Kd, dt=dt, seed=20 + i, scale=0.5) for i in range(4)]
+        b = [rnd(N, seed=30 + i) for i in range(4)]
+        R = [rnd(M, N, dt=dt, seed=40 + i) for i, M in enumerate(Ms)]
+        Y = [torch.zeros(M, N, dtype=dt, device="cuda") for M in Ms]
+        U = [torch.zeros(M, N, dtype=dt, device="cuda") for M in Ms]
+        K.gemm_grouped([((X[i], W[i], Y[i], Ms[i], N, Kd), dict(sam=Kd, sak=1, sbn=Kd, sbk=1, ldc=N, bias=b[i],
+                                                               aux=U[i], flags=1)) for i in range(4)])
+        outs += Y + U
+        Y2 = [torch.zeros(M, N, dtype=dt, device="cuda") for M in Ms]
+        K.gemm_grouped([((X[i], W[i], Y2[i], Ms[i], N, Kd), dict(sam=Kd, sak=1, sbn=Kd, sbk=1, ldc=N, bias=b[i],
+                                                                residual=R[i])) for i in range(4)])
+        outs += Y2
+        dX = [torch.zeros(M, Kd, dtype=dt, device="cuda") for M in Ms]
+        A2 = [rnd(M, Kd, dt=dt, seed=50 + i) for i, M in enumerate(Ms)]
+        K.gemm_grouped([((R[i], W[i], dX[i], Ms[i], Kd, N), dict(sam=N, sak=1, sbn=1, sbk=Kd, ldc=Kd, aux=A2[i],
+                                                                flags=2)) for i in range(4)])
+        outs += dX
+        dW = [torch.full((N, Kd), 0.25, dtype=torch.float32, device="cuda") for _ in Ms]
+        K.gemm_grouped([((R[i], X[i], dW[i], N, Kd, Ms[i]), dict(sam=1, sak=N, sbn=1, sbk=Kd, ldc=Kd, flags=4))
+                        for i in range(4)])
+        outs += dW
+        return outs
+    a, b = both(KK, run)
+    for x, y in zip(a, b):
+        close(x, y, rtol=2e-2, atol=2e-2 * math.sqrt(768) * 0.25)
+
+
 @pytest.mark.parametrize("dt", DT)
 def test_batched_gemm_and_softmax(KK, dt):
     Bn, H, N, dh = 2, 3, 50, 16

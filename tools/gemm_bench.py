@@ -29,8 +29,8 @@ def cases():
             (f"{tag}/fwd_out", "k", M, d, inner, "res"),
             (f"{tag}/fwd_up", "k", M, mlp, d, "gelu"),
             (f"{tag}/fwd_down", "k", M, d, mlp, "res"),
-            (f"{tag}/dgrad_down", "k", M, mlp, d, "dgelu"),
-            (f"{tag}/dgrad_up", "k", M, d, mlp, 0),
+            (f"{tag}/dgrad_down", "kmn", M, mlp, d, "dgelu"),
+            (f"{tag}/dgrad_up", "kmn", M, d, mlp, 0),
             (f"{tag}/wgrad_up", "mn", mlp, d, M, 0),
             (f"{tag}/wgrad_qkv", "mn", 3 * inner, d, M, 0),
             (f"{tag}/wgrad_down", "mn", d, mlp, M, 0),
@@ -52,11 +52,15 @@ def main():
         if args.only and args.only not in name:
             continue
         bf = torch.bfloat16
-        if layout == "k":
+        if layout in ("k", "kmn"):
             A = torch.randn(M, Kd, device=dev).to(bf)
-            B = torch.randn(N, Kd, device=dev).to(bf)
             C = torch.empty(M, N, device=dev, dtype=bf)
-            kw = dict(sam=Kd, sak=1, sbn=Kd, sbk=1, ldc=N)
+            if layout == "k":
+                B = torch.randn(N, Kd, device=dev).to(bf)
+                kw = dict(sam=Kd, sak=1, sbn=Kd, sbk=1, ldc=N)
+            else:   # dgrad: B(n, k) = W[k, n], the weight [Kd(out), N(in)] read in place
+                B = torch.randn(Kd, N, device=dev).to(bf)
+                kw = dict(sam=Kd, sak=1, sbn=1, sbk=N, ldc=N)
             if epi == "res":
                 kw.update(bias=torch.randn(N, device=dev), residual=torch.randn(M, N, device=dev).to(bf))
             elif epi == "gelu":
