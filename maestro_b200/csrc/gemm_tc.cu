@@ -8,14 +8,15 @@
 //   A MN-major [K, M],                B MN-major [K, N]   -> wgrad     dW[n, k] = sum_t dY[t, n] X[t, k]
 //                                                            (contraction over tokens, split-K + fp32 red.add)
 // Structure: persistent CTAs (one per SM), warp-specialised: warp 0 = TMA producer, warp 1 = single-thread
-// tcgen05.mma issuer, warp 2 = TMEM allocator, warps 4..11 = epilogue.  The accumulator is double-buffered in
+// tcgen05.mma issuer, warp 2 = TMEM allocator, warps 4..19 = epilogue.  The accumulator is double-buffered in
 // TMEM (2 x BN columns) so the epilogue of tile i overlaps the main loop of tile i + 1; shared memory holds a
-// STAGES-deep ring of 128 x 64 (A) and BN x 64 (B) bf16 tiles in the 128-byte swizzle layout, plus one 4 KB
+// STAGES-deep ring of 128 x 64 (A) and BN x 64 (B) bf16 tiles in the 128-byte swizzle layout, plus one 2 KB
 // staging buffer per epilogue warp.
 // Epilogue (bf16 outputs): tcgen05.ld -> registers -> fused bias / GELU (+ saved pre-activation) / GELU' /
 // residual -> bf16 -> swizzled shared-memory staging -> TMA tile store (full 128-byte lines, clipped at the
 // matrix edge by the hardware).  Epilogue inputs (residual, saved pre-activation) are read with fully coalesced
-// 16-byte loads (4 rows x 128 B per instruction) and transposed to "thread = row" through the same staging buffer.
+// 16-byte loads (8 rows x 64 B per instruction, the tile pulled into L2 by a TMA prefetch while the main loop runs)
+// and transposed to "thread = row" through the same staging buffer.
 // fp32 outputs (wgrad accumulation) use direct 16-byte stores / red.add.
 #include <mutex>
 #include <unordered_map>
@@ -33,10 +34,10 @@ constexpr int BM = 128;
 constexpr int BK = 64;
 constexpr int UMMA_K = 16;
 constexpr int A_BYTES = BM * BK * 2;
-constexpr int NUM_THREADS = 384;
+constexpr int NUM_THREADS = 640;
 constexpr int EPI_WARP0 = 4;
-constexpr int EPI_WARPS = 8;
-constexpr int STG_BYTES = 32 * 64 * 2;   // one epilogue warp: 32 rows x 64 bf16 columns
+constexpr int EPI_WARPS = 16;
+constexpr int STG_BYTES = 32 * 32 * 2;   // one epilogue warp: 32 rows x 32 bf16 columns
 constexpr int MAX_GROUP = 4;
 
 template <int BN> struct Cfg {
@@ -68,13 +69,14 @@ struct TcArgs {
 struct TcMaps {
   CUtensorMap a[MAX_GROUP], b[MAX_GROUP], c[MAX_GROUP];
   CUtensorMap x[MAX_GROUP];   // GELU: pre-activation output; GELU': pre-activation input; else residual input
+  CUtensorMap pf[MAX_GROUP];  // the epilogue input again, with a 128-row x 64-column box for L2 prefetch
 };
 
 struct TileCoord {
   int p, m_blk, n_blk, kb0, kb1;
 };
 
-__device__ __forceinline__ TileCoord decode_tile(const TcArgs& args, int t) {
+__device__ __forceinline__ TileCoord decode_tile(const TcArgs& args, int t, bool n_fastest) {
   TileCoord tc_;
   int p = 0, start = 0;
 #pragma unroll
@@ -87,8 +89,13 @@ __device__ __forceinline__ TileCoord decode_tile(const TcArgs& args, int t) {
   const int kblocks = (P.K + BK - 1) / BK;
   const int per = (kblocks + P.splits - 1) / P.splits;
   tc_.p = p;
-  tc_.n_blk = rem / P.mblocks;
-  tc_.m_blk = rem - tc_.n_blk * P.mblocks;
+  if (n_fastest) {   // activations (A, large) stream from HBM once; the n-blocks of one m-block run side by side
+    tc_.m_blk = rem / P.nblocks;
+    tc_.n_blk = rem - tc_.m_blk * P.nblocks;
+  } else {
+    tc_.n_blk = rem / P.mblocks;
+    tc_.m_blk = rem - tc_.n_blk * P.mblocks;
+  }
   tc_.kb0 = split * per;
   tc_.kb1 = min(kblocks, tc_.kb0 + per);
   return tc_;
@@ -149,20 +156,16 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
       int stage = 0;
       uint32_t phase = 0;
       for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-        const TileCoord tc_ = decode_tile(args, t);
+        const TileCoord tc_ = decode_tile(args, t, !A_MN);
         const CUtensorMap* tmA = &maps.a[tc_.p];
         const CUtensorMap* tmB = &maps.b[tc_.p];
         {
           // pull this tile's epilogue input (residual / saved pre-activation) into L2 while the main loop runs
           const TcProblem& P = args.p[tc_.p];
           if (!(args.flags & GEMM_OUT_F32) && ((args.flags & GEMM_DGELU) || P.residual != nullptr)) {
-            for (int rg = 0; rg < BM / 32; ++rg) {
-              const int r0 = tc_.m_blk * BM + rg * 32;
-              if (r0 >= P.M) break;
-              for (int cc = 0; cc < BN / 64; ++cc) {
-                const int c0 = tc_.n_blk * BN + cc * 64;
-                if (c0 < P.N) tc::tma_prefetch_l2_2d(&maps.x[tc_.p], c0, r0);
-              }
+            for (int cc = 0; cc < BN / 64; ++cc) {
+              const int c0 = tc_.n_blk * BN + cc * 64;
+              if (c0 < P.N) tc::tma_prefetch_l2_2d(&maps.pf[tc_.p], c0, tc_.m_blk * BM);
             }
           }
         }
@@ -198,7 +201,7 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
       int acc = 0;
       uint32_t acc_phase = 0;
       for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-        const TileCoord tc_ = decode_tile(args, t);
+        const TileCoord tc_ = decode_tile(args, t, !A_MN);
         tc::mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
         tc::tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * BN;
@@ -226,50 +229,54 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
       }
     }
   } else if (warp >= EPI_WARP0) {
-    // ===================== epilogue (8 warps: 4 TMEM lane groups x 2 column halves) =====================
-    const int ew = warp & 3;                   // TMEM lanes [32 * ew, 32 * ew + 32) (a warp may only touch its quarter)
-    const int half = (warp - EPI_WARP0) >> 2;  // columns [half * BN / 2, (half + 1) * BN / 2)
+    // ===================== epilogue (16 warps: 4 TMEM lane groups x 4 column quarters) =====================
+    // Four warps per scheduler hide the MUFU / shared-memory / TMEM latencies of the fused math; each warp owns a
+    // 32-row x (BN / 4)-column slab of the accumulator and walks it in 32-column chunks.
+    const int ew = warp & 3;                       // TMEM lanes [32 * ew, 32 * ew + 32) (a warp may only touch its quarter)
+    const int quarter = (warp - EPI_WARP0) >> 2;   // columns [quarter * BN / 4, (quarter + 1) * BN / 4)
+    constexpr int CH_PER_Q = BN / 128;             // 32-column chunks per warp
     uint8_t* stg = stg_base + (warp - EPI_WARP0) * STG_BYTES;
     const uint32_t stg_u32 = tc::smem_u32(stg);
-    // staging addresses (128-byte swizzle, as the TMA store map expects): "own row" = row `lane`, 16-byte chunk j
-    const uint32_t own_base = stg_u32 + lane * 128;
-    const uint32_t own_x = static_cast<uint32_t>(lane & 7);
+    // staging buffer: 32 rows x 64 B, 64-byte swizzle (16-byte chunk j of row r sits at chunk j ^ ((r >> 1) & 3)),
+    // as the TMA store map expects.  "own" = row `lane`; "co" = coalesced view, instruction i covers rows 8i..8i+7.
+    const uint32_t own_base = stg_u32 + lane * 64;
+    const uint32_t own_x = static_cast<uint32_t>((lane >> 1) & 3);
+    const uint32_t co_row = static_cast<uint32_t>(lane >> 2), co_j = static_cast<uint32_t>(lane & 3);
     int acc = 0;
     uint32_t acc_phase = 0;
     const bool out_f32 = (args.flags & GEMM_OUT_F32) != 0;
     const bool f_gelu = (args.flags & GEMM_GELU) != 0, f_dgelu = (args.flags & GEMM_DGELU) != 0;
     const float alpha = args.alpha;
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-      const TileCoord tc_ = decode_tile(args, t);
+      const TileCoord tc_ = decode_tile(args, t, !A_MN);
       const TcProblem& P = args.p[tc_.p];
       const int row0 = tc_.m_blk * BM + ew * 32;
       const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + acc * BN;
+      int nch = 0;
+#pragma unroll
+      for (int c2 = 0; c2 < CH_PER_Q; ++c2)
+        if (tc_.n_blk * BN + (quarter * CH_PER_Q + c2) * 32 < P.N) nch = c2 + 1;
+      if (nch == 0) {
+        tc::mbar_wait(&tfull_bar[acc], acc_phase);
+        tc::tc_fence_before();
+        tc::mbar_arrive(&tempty_bar[acc]);
+      }
       if (!out_f32) {
-        // ---------------- bf16 outputs through shared memory + TMA store, 64-column chunks ----------------
-        constexpr int CH_PER_HALF = BN / 128;
+        // ---------------- bf16 outputs through shared memory + TMA store ----------------
         const bool has_res = P.residual != nullptr;
         const bool need_in = f_dgelu || has_res;
         const bf16* src = static_cast<const bf16*>(f_dgelu ? P.aux : P.residual);
-        int nch = 0;
-#pragma unroll
-        for (int c2 = 0; c2 < CH_PER_HALF; ++c2)
-          if (tc_.n_blk * BN + (half * CH_PER_HALF + c2) * 64 < P.N) nch = c2 + 1;
-        if (nch == 0) {
-          tc::mbar_wait(&tfull_bar[acc], acc_phase);
-          tc::tc_fence_before();
-          tc::mbar_arrive(&tempty_bar[acc]);
-        }
 #pragma unroll 1
         for (int c2 = 0; c2 < nch; ++c2) {
-          const int ch = half * CH_PER_HALF + c2;
-          const int col0 = tc_.n_blk * BN + ch * 64;
-          // (1) coalesced prefetch of the epilogue input: instruction i covers rows 4i .. 4i+3, 8 lanes per row
-          uint4 pre[8];
+          const int ch = quarter * CH_PER_Q + c2;
+          const int col0 = tc_.n_blk * BN + ch * 32;
+          // (1) coalesced prefetch of the epilogue input: instruction i covers rows 8i .. 8i+7, 4 lanes per row
+          uint4 pre[4];
           if (need_in) {
-            const int cc = col0 + (lane & 7) * 8;
+            const int cc = col0 + co_j * 8;
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
-              const int rr = row0 + i * 4 + (lane >> 3);
+            for (int i = 0; i < 4; ++i) {
+              const int rr = row0 + i * 8 + co_row;
               pre[i] = (rr < P.M && cc < P.N)
                            ? __ldg(reinterpret_cast<const uint4*>(src + static_cast<size_t>(rr) * P.ldc + cc))
                            : make_uint4(0, 0, 0, 0);
@@ -280,11 +287,10 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
             tc::mbar_wait(&tfull_bar[acc], acc_phase);
             tc::tc_fence_after();
           }
-          uint32_t r[64];
-          tc::tmem_ld_32x32(t_addr + ch * 64, r);
-          tc::tmem_ld_32x32(t_addr + ch * 64 + 32, r + 32);
+          uint32_t r[32];
+          tc::tmem_ld_32x32(t_addr + ch * 32, r);
           tc::tmem_ld_wait();
-          if (c2 == nch - 1) {   // accumulator fully read: hand the TMEM buffer back to the MMA warp
+          if (c2 == nch - 1) {   // accumulator slab fully read: hand the TMEM buffer back to the MMA warp
             tc::tc_fence_before();
             tc::mbar_arrive(&tempty_bar[acc]);
           }
@@ -293,15 +299,15 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
             if (lane == 0) tc::tma_store_wait_read();
             __syncwarp();
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
-              const uint32_t rr = i * 4 + (lane >> 3);
-              const uint32_t a = stg_u32 + rr * 128 + (((lane & 7) ^ (rr & 7)) << 4);
+            for (int i = 0; i < 4; ++i) {
+              const uint32_t rr = i * 8 + co_row;
+              const uint32_t a = stg_u32 + rr * 64 + ((co_j ^ ((rr >> 1) & 3)) << 4);
               asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(pre[i].x), "r"(pre[i].y),
                            "r"(pre[i].z), "r"(pre[i].w) : "memory");
             }
             __syncwarp();
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
+            for (int j = 0; j < 4; ++j) {
               const uint32_t a = own_base + ((j ^ own_x) << 4);
               asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(pre[j].x), "=r"(pre[j].y), "=r"(pre[j].z),
                            "=r"(pre[j].w) : "r"(a) : "memory");
@@ -312,7 +318,7 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
           float* v = reinterpret_cast<float*>(r);
           if (P.bias != nullptr) {
 #pragma unroll
-            for (int q = 0; q < 16; ++q) {
+            for (int q = 0; q < 8; ++q) {
               const float4 b = (col0 + q * 4 < P.N) ? __ldg(reinterpret_cast<const float4*>(P.bias + col0 + q * 4))
                                                     : make_float4(0.f, 0.f, 0.f, 0.f);
               v[4 * q] = fmaf(v[4 * q], alpha, b.x);
@@ -322,14 +328,14 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
             }
           } else if (alpha != 1.0f) {
 #pragma unroll
-            for (int q = 0; q < 64; ++q) v[q] *= alpha;
+            for (int q = 0; q < 32; ++q) v[q] *= alpha;
           }
           // (5) GELU: store the bf16 pre-activation (second output), activate the rounded value
           if (f_gelu) {
             if (lane == 0) tc::tma_store_wait_read();
             __syncwarp();
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
+            for (int j = 0; j < 4; ++j) {
               uint32_t w[4];
 #pragma unroll
               for (int q = 0; q < 4; ++q) {
@@ -350,7 +356,7 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
           // (6) GELU' / residual
           if (need_in) {
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
+            for (int j = 0; j < 4; ++j) {
               const uint32_t w[4] = {pre[j].x, pre[j].y, pre[j].z, pre[j].w};
 #pragma unroll
               for (int q = 0; q < 4; ++q) {
@@ -369,7 +375,7 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
           if (lane == 0) tc::tma_store_wait_read();
           __syncwarp();
 #pragma unroll
-          for (int j = 0; j < 8; ++j) {
+          for (int j = 0; j < 4; ++j) {
             const uint32_t w0 = pack_bf16x2(v[8 * j], v[8 * j + 1]), w1 = pack_bf16x2(v[8 * j + 2], v[8 * j + 3]);
             const uint32_t w2 = pack_bf16x2(v[8 * j + 4], v[8 * j + 5]), w3 = pack_bf16x2(v[8 * j + 6], v[8 * j + 7]);
             asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(own_base + ((j ^ own_x) << 4)), "r"(w0),
@@ -382,22 +388,24 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
             tc::tma_store_commit();
           }
         }
-      } else {
+      } else if (nch > 0) {
         // ---------------- fp32 outputs (gradient accumulation): direct 16-byte stores / red.add ----------------
-        constexpr int CH_PER_HALF = BN / 64;       // 32-column chunks per half
         tc::mbar_wait(&tfull_bar[acc], acc_phase);
         tc::tc_fence_after();
         const int row = row0 + lane;
         const bool row_ok = row < P.M;
         float* crow = static_cast<float*>(P.C) + static_cast<size_t>(row_ok ? row : 0) * P.ldc;
 #pragma unroll 1
-        for (int c2 = 0; c2 < CH_PER_HALF; ++c2) {
-          const int ch = half * CH_PER_HALF + c2;
+        for (int c2 = 0; c2 < nch; ++c2) {
+          const int ch = quarter * CH_PER_Q + c2;
           const int col0 = tc_.n_blk * BN + ch * 32;
-          if (col0 >= P.N) break;  // warp-uniform
           uint32_t r[32];
           tc::tmem_ld_32x32(t_addr + ch * 32, r);
           tc::tmem_ld_wait();
+          if (c2 == nch - 1) {
+            tc::tc_fence_before();
+            tc::mbar_arrive(&tempty_bar[acc]);
+          }
           if (row_ok) {
 #pragma unroll
             for (int q = 0; q < 8; ++q) {
@@ -414,8 +422,6 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
             }
           }
         }
-        tc::tc_fence_before();
-        tc::mbar_arrive(&tempty_bar[acc]);
       }
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
@@ -429,10 +435,11 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
 
 // ---------------------------------------------------------------- host
 // 2D bf16 tensor [d1 rows, d0 cols] with row pitch stride1 (elements), box [b1 rows, b0 cols], 128B swizzle.
-int get_tmap(CUtensorMap* out, const void* ptr, uint64_t d0, uint64_t d1, uint64_t stride1, uint32_t b0, uint32_t b1) {
+int get_tmap(CUtensorMap* out, const void* ptr, uint64_t d0, uint64_t d1, uint64_t stride1, uint32_t b0, uint32_t b1,
+             int swizzle = 128) {
   const uint64_t dims[2] = {d0, d1}, strides[1] = {stride1};
   const uint32_t box[2] = {b0, b1};
-  return mb_get_tmap(out, ptr, 2, dims, strides, box, 128);
+  return mb_get_tmap(out, ptr, 2, dims, strides, box, swizzle);
 }
 
 int num_sms() { return mb_num_sms(); }
@@ -456,19 +463,22 @@ int launch(const GemmParams* Ps, int count, cudaStream_t st) {
     else rc = get_tmap(&maps.b[i], P.B, P.N, P.K, P.sbk, 64, BK);
     if (rc != 0) return rc;
     if (!out_f32) {
-      if ((rc = get_tmap(&maps.c[i], P.C, P.N, P.M, P.ldc, 64, 32)) != 0) return rc;
+      if ((rc = get_tmap(&maps.c[i], P.C, P.N, P.M, P.ldc, 32, 32, 64)) != 0) return rc;
       // x: GELU -> saved pre-activation (second output); GELU' -> the same tensor as epilogue input; else residual
       const void* xp = (flags & (GEMM_GELU | GEMM_DGELU)) ? P.aux : P.residual;
       if ((flags & (GEMM_GELU | GEMM_DGELU)) && xp == nullptr) return -6;
       if (xp != nullptr) {
         if ((reinterpret_cast<uintptr_t>(xp) & 15) != 0) return -11;
-        if ((rc = get_tmap(&maps.x[i], xp, P.N, P.M, P.ldc, 64, 32)) != 0) return rc;
+        if ((rc = get_tmap(&maps.x[i], xp, P.N, P.M, P.ldc, 32, 32, 64)) != 0) return rc;
+        if ((rc = get_tmap(&maps.pf[i], xp, P.N, P.M, P.ldc, 64, BM)) != 0) return rc;
       } else {
         maps.x[i] = maps.c[i];
+        maps.pf[i] = maps.c[i];
       }
     } else {
       maps.c[i] = maps.a[i];
       maps.x[i] = maps.a[i];
+      maps.pf[i] = maps.a[i];
     }
     TcProblem& q = a.p[i];
     q.C = P.C; q.bias = P.bias; q.residual = P.residual; q.aux = P.aux;
@@ -479,6 +489,7 @@ int launch(const GemmParams* Ps, int count, cudaStream_t st) {
   }
   for (int i = count; i < MAX_GROUP; ++i) {
     maps.a[i] = maps.a[0]; maps.b[i] = maps.b[0]; maps.c[i] = maps.c[0]; maps.x[i] = maps.x[0];
+    maps.pf[i] = maps.pf[0];
   }
   int total = 0;
   for (int i = 0; i < count; ++i) {
