@@ -169,18 +169,52 @@ def run_ours(args):
     loss_host = torch.zeros(1).pin_memory()
     torch.manual_seed(1234 + rank)
 
-    def step_device(batch):
-        loss = eng.step(dict(batch))
-        if world > 1:
-            dist.all_reduce(eng.arena.grad)
+    use_graph = not args.no_graph
+    gstep = None
+    if use_graph:
+        from maestro_b200.graph import GraphedPretrainStep
+        gstep = GraphedPretrainStep(eng, host[0], segments=3 if world > 1 else 1)
+        eng.zero_grad()
+        devb = gstep.batch
+    ranges = eng.grad_ranges()
+    comm = torch.cuda.Stream(device=dev) if world > 1 else None
+
+    def reduce_grads_overlapped():
+        """Replay the step segment by segment; all-reduce each finished arena range on the comm stream."""
+        cur = torch.cuda.current_stream()
+        for i, (a, b) in enumerate(ranges):
+            gstep.replay(i)
+            if b > a:
+                comm.wait_stream(cur)
+                with torch.cuda.stream(comm):
+                    dist.all_reduce(eng.arena.grad[a:b])
+        cur.wait_stream(comm)
+
+    def step_device(batch, staged=False):
+        if use_graph:
+            if not staged:
+                gstep.load(batch)
+            if world > 1:
+                reduce_grads_overlapped()
+            else:
+                gstep.replay()
+            loss = gstep.loss
+        else:
+            loss = eng.step(dict(batch))
+            if world > 1:
+                dist.all_reduce(eng.arena.grad)
         opt.step(grad_scale=1.0 / world)
         return loss
 
     def step_e2e(i):
         hb = host[i % 2]
-        for k, v in hb.items():
-            devb[k].copy_(v, non_blocking=True)
-        loss = step_device(devb)
+        if use_graph:
+            gstep.load(hb)
+            loss = step_device(devb, staged=True)
+        else:
+            for k, v in hb.items():
+                devb[k].copy_(v, non_blocking=True)
+            loss = step_device(devb)
         loss_host.copy_(loss.reshape(1), non_blocking=True)
         torch.cuda.current_stream().synchronize()
         return float(loss_host[0])
@@ -209,26 +243,30 @@ def run_ours(args):
     l0 = K.launches
     ms_dev = timed(lambda i: step_device(devb), args.steps)
     launches = (K.launches - l0) // args.steps
+    if use_graph:
+        launches = gstep.launches_per_step + 1
     ms_e2e = timed(step_e2e, args.steps)
     clocks = sampler.stop() if rank == 0 else None
     last_loss = float(loss_host[0])
 
     # ---- per-kernel roofline, measured live: one instrumented step, CUDA events around every GEMM launch
     rec = []
-    orig_gemm = K.gemm
+    orig_grouped = K.gemm_grouped
 
-    def gemm_probe(A, Bm, Cm, M, N, Kd, *a, **kw):
+    def grouped_probe(problems):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        nb = kw.get("nb1", 1) * kw.get("nb2", 1)
-        tc = nb == 1 and A.dtype == torch.bfloat16
+        fl = sum(2.0 * a[3] * a[4] * a[5] * kw.get("nb1", 1) * kw.get("nb2", 1) for a, kw in problems)
+        tc = all(a[0].dtype == torch.bfloat16 and kw.get("nb1", 1) * kw.get("nb2", 1) == 1 for a, kw in problems)
         e0.record()
-        orig_gemm(A, Bm, Cm, M, N, Kd, *a, **kw)
+        orig_grouped(problems)
         e1.record()
-        rec.append((tc, 2.0 * M * N * Kd * nb, e0, e1))
-    K.gemm = gemm_probe
-    step_device(devb)
+        rec.append((tc, fl, e0, e1))
+    K.gemm_grouped = grouped_probe
+    eng.zero_grad()
+    eng.step(dict(devb))
     torch.cuda.synchronize()
-    K.gemm = orig_gemm
+    K.gemm_grouped = orig_grouped
+    eng.zero_grad()
     tc_fl = sum(r[1] for r in rec if r[0])
     tc_ms = sum(r[2].elapsed_time(r[3]) for r in rec if r[0])
     at_fl = sum(r[1] for r in rec if not r[0])
@@ -257,7 +295,8 @@ def run_ours(args):
                                f"{args.dataset} shapes, mask 0.75, inter_depth 3, {B} tiles/GPU",
                    "global_batch": B * world, "parallelism": f"dp{world}",
                    "l2": "inputs larger than L2 (activations >> 126 MB per step); no flush",
-                   "attention": eng.attn_impl, "loss_last": last_loss},
+                   "attention": eng.attn_impl, "loss_last": last_loss,
+                   "launch": "cuda-graph replay" if use_graph else "python"},
         "e2e": {"value": B * world / (e2e_ms * 1e-3), "unit": "tiles/s", "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": 4, "ms_per_step": e2e_ms},
         "gpu_launches": launches,
@@ -288,6 +327,7 @@ def main():
     ap.add_argument("--batch", type=int, default=32, help="tiles per GPU (reference default, conf/opt.py:20)")
     ap.add_argument("--cpu-batch", type=int, default=2)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-graph", action="store_true", help="issue every launch from Python instead of CUDA-graph replay")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -293,27 +293,47 @@ class PretrainEngine:
     def _w(self, name: str) -> torch.Tensor:
         return self.arena.Wb[name] if self.dtype == torch.bfloat16 else self.P[name]
 
+    def lin_fwd_g(self, items):
+        """Grouped linear layers of one kind, one launch: items = [(x, M, wname, bname, out, gelu_aux, residual)].
+
+        out[M, N] = x[M, Kd] @ W[N, Kd]^T (+ bias) (gelu, saving the pre-activation) (+ residual) per item.
+        """
+        probs = []
+        for x, M, wname, bname, out, gelu_aux, residual in items:
+            shp = self.arena.shapes[wname]
+            N, Kd = shp[0], self.P[wname].numel() // shp[0]
+            probs.append(((x, self._w(wname), out, M, N, Kd),
+                          dict(sam=Kd, sak=1, sbn=Kd, sbk=1, ldc=N, bias=self.P[bname] if bname else None,
+                               residual=residual, aux=gelu_aux, flags=GEMM_GELU if gelu_aux is not None else 0)))
+        self.K.gemm_grouped(probs)
+
+    def lin_bwd_g(self, items):
+        """Grouped backward of linear layers: items = [(dy, M, x, wname, bname, dx, dgelu_aux)].
+
+        Accumulates dW (token contraction, split-K) and dbias; optionally dx[M, Kd] = dy[M, N] @ W (times
+        gelu'(aux)), the weight read in place as an MN-major operand (no transposed copy).
+        """
+        wg, dg = [], []
+        for dy, M, x, wname, bname, dx, dgelu_aux in items:
+            shp = self.arena.shapes[wname]
+            N, Kd = shp[0], self.P[wname].numel() // shp[0]
+            if bname:
+                self.K.colsum_accum(dy, self.G[bname])
+            # dW[n, k] += sum_m dy[m, n] * x[m, k]   (contraction over tokens)
+            wg.append(((dy, x, self.G[wname], N, Kd, M), dict(sam=1, sak=N, sbn=1, sbk=Kd, ldc=Kd, flags=GEMM_ACCUM)))
+            if dx is not None:
+                dg.append(((dy, self._w(wname), dx, M, Kd, N),
+                           dict(sam=N, sak=1, sbn=1, sbk=Kd, ldc=Kd, aux=dgelu_aux,
+                                flags=GEMM_DGELU if dgelu_aux is not None else 0)))
+        self.K.gemm_grouped(wg)
+        if dg:
+            self.K.gemm_grouped(dg)
+
     def lin_fwd(self, x, M, wname, bname, out, gelu_aux=None, residual=None):
-        """out[M, N] = x[M, Kd] @ W[N, Kd]^T (+ bias) (gelu, saving the pre-activation) (+ residual)."""
-        shp = self.arena.shapes[wname]
-        N, Kd = shp[0], self.P[wname].numel() // shp[0]
-        self.K.gemm(x, self._w(wname), out, M, N, Kd, sam=Kd, sak=1, sbn=Kd, sbk=1, ldc=N,
-                    bias=self.P[bname] if bname else None, residual=residual, aux=gelu_aux,
-                    flags=GEMM_GELU if gelu_aux is not None else 0)
+        self.lin_fwd_g([(x, M, wname, bname, out, gelu_aux, residual)])
 
     def lin_bwd(self, dy, M, x, wname, bname, dx=None, dgelu_aux=None):
-        """Accumulate dW, dbias; optionally dx[M, Kd] = dy[M, N] @ W (times gelu'(aux))."""
-        shp = self.arena.shapes[wname]
-        N, Kd = shp[0], self.P[wname].numel() // shp[0]
-        if bname:
-            self.K.colsum_accum(dy, self.G[bname])
-        # dW[n, k] += sum_m dy[m, n] * x[m, k]   (contraction over tokens)
-        self.K.gemm(dy, x, self.G[wname], N, Kd, M, sam=1, sak=N, sbn=1, sbk=Kd, ldc=Kd, flags=GEMM_ACCUM)
-        if dx is None:
-            return
-        fl = GEMM_DGELU if dgelu_aux is not None else 0
-        # dx[m, k] = sum_n dy[m, n] W[n, k]: the weight is read in place as an MN-major operand (no transposed copy)
-        self.K.gemm(dy, self._w(wname), dx, M, Kd, N, sam=N, sak=1, sbn=1, sbk=Kd, ldc=Kd, aux=dgelu_aux, flags=fl)
+        self.lin_bwd_g([(dy, M, x, wname, bname, dx, dgelu_aux)])
 
     # ------------------------------------------------------------------ attention
     def attn_fwd(self, qkv, Bn, N, H, dh):
@@ -362,60 +382,96 @@ class PretrainEngine:
                     a_s=bs_p, b_s=bs_qkv, c_s=bs_qkv, c_off=inner)
         return dqkv
 
-    # ------------------------------------------------------------------ transformer block
-    def block_fwd(self, pre, x, Bn, N, dim, H, dh, mlp):
+    # ------------------------------------------------------------------ transformer blocks (lockstep over stacks)
+    # The per-group encoders (and decoders) have identical layer shapes and different weights / token counts
+    # (reference: one vit_pytorch Transformer per group, looped by encode_or_decode, ssl/mim.py:396-423).  They
+    # advance layer by layer together so that every linear layer of the 4 groups is ONE grouped GEMM launch.
+    def blocks_fwd(self, pres, xs, Bn, Ns, dim, H, dh, mlp):
         K, P = self.K, self.P
-        rows, inner = Bn * N, H * dh
         f32 = torch.float32
-        h1, m1, r1 = self._new(rows, dim), self._new(rows, dtype=f32), self._new(rows, dtype=f32)
-        K.layernorm_fwd(x, P[pre + "0.norm.weight"], P[pre + "0.norm.bias"], h1, m1, r1, rows, dim)
-        qkv = self._new(rows, 3 * inner)
-        self.lin_fwd(h1, rows, pre + "0.to_qkv.weight", None, qkv)
-        o, att = self.attn_fwd(qkv, Bn, N, H, dh)
-        x2 = self._new(rows, dim)
-        self.lin_fwd(o, rows, pre + "0.to_out.0.weight", pre + "0.to_out.0.bias", x2, residual=x)
-        h2, m2, r2 = self._new(rows, dim), self._new(rows, dtype=f32), self._new(rows, dtype=f32)
-        K.layernorm_fwd(x2, P[pre + "1.net.0.weight"], P[pre + "1.net.0.bias"], h2, m2, r2, rows, dim)
-        u, a = self._new(rows, mlp), self._new(rows, mlp)
-        self.lin_fwd(h2, rows, pre + "1.net.1.weight", pre + "1.net.1.bias", a, gelu_aux=u)
-        x3 = self._new(rows, dim)
-        self.lin_fwd(a, rows, pre + "1.net.4.weight", pre + "1.net.4.bias", x3, residual=x2)
-        return x3, (x, m1, r1, h1, qkv, att, o, x2, m2, r2, h2, u, a)
+        inner, n = H * dh, len(pres)
+        rows = [Bn * N for N in Ns]
+        h1 = [self._new(r, dim) for r in rows]
+        m1 = [self._new(r, dtype=f32) for r in rows]
+        r1 = [self._new(r, dtype=f32) for r in rows]
+        for i in range(n):
+            K.layernorm_fwd(xs[i], P[pres[i] + "0.norm.weight"], P[pres[i] + "0.norm.bias"], h1[i], m1[i], r1[i],
+                            rows[i], dim)
+        qkv = [self._new(r, 3 * inner) for r in rows]
+        self.lin_fwd_g([(h1[i], rows[i], pres[i] + "0.to_qkv.weight", None, qkv[i], None, None) for i in range(n)])
+        o, att = [], []
+        for i in range(n):
+            oi, ai = self.attn_fwd(qkv[i], Bn, Ns[i], H, dh)
+            o.append(oi)
+            att.append(ai)
+        x2 = [self._new(r, dim) for r in rows]
+        self.lin_fwd_g([(o[i], rows[i], pres[i] + "0.to_out.0.weight", pres[i] + "0.to_out.0.bias", x2[i], None, xs[i])
+                        for i in range(n)])
+        h2 = [self._new(r, dim) for r in rows]
+        m2 = [self._new(r, dtype=f32) for r in rows]
+        r2 = [self._new(r, dtype=f32) for r in rows]
+        for i in range(n):
+            K.layernorm_fwd(x2[i], P[pres[i] + "1.net.0.weight"], P[pres[i] + "1.net.0.bias"], h2[i], m2[i], r2[i],
+                            rows[i], dim)
+        u = [self._new(r, mlp) for r in rows]
+        a = [self._new(r, mlp) for r in rows]
+        self.lin_fwd_g([(h2[i], rows[i], pres[i] + "1.net.1.weight", pres[i] + "1.net.1.bias", a[i], u[i], None)
+                        for i in range(n)])
+        x3 = [self._new(r, dim) for r in rows]
+        self.lin_fwd_g([(a[i], rows[i], pres[i] + "1.net.4.weight", pres[i] + "1.net.4.bias", x3[i], None, x2[i])
+                        for i in range(n)])
+        saved = [(xs[i], m1[i], r1[i], h1[i], qkv[i], att[i], o[i], x2[i], m2[i], r2[i], h2[i], u[i], a[i])
+                 for i in range(n)]
+        return x3, saved
 
-    def block_bwd(self, pre, dx3, saved, Bn, N, dim, H, dh, mlp):
+    def blocks_bwd(self, pres, dx3, saved, Bn, Ns, dim, H, dh, mlp):
         K, P, G = self.K, self.P, self.G
-        x, m1, r1, h1, qkv, att, o, x2, m2, r2, h2, u, a = saved
-        rows, inner = Bn * N, H * dh
-        du = self._new(rows, mlp)
-        self.lin_bwd(dx3, rows, a, pre + "1.net.4.weight", pre + "1.net.4.bias", dx=du, dgelu_aux=u)
-        dh2 = self._new(rows, dim)
-        self.lin_bwd(du, rows, h2, pre + "1.net.1.weight", pre + "1.net.1.bias", dx=dh2)
+        inner, n = H * dh, len(pres)
+        rows = [Bn * N for N in Ns]
+        x, m1, r1, h1, qkv, att, o, x2, m2, r2, h2, u, a = (list(t) for t in zip(*saved))
+        du = [self._new(r, mlp) for r in rows]
+        self.lin_bwd_g([(dx3[i], rows[i], a[i], pres[i] + "1.net.4.weight", pres[i] + "1.net.4.bias", du[i], u[i])
+                        for i in range(n)])
+        dh2 = [self._new(r, dim) for r in rows]
+        self.lin_bwd_g([(du[i], rows[i], h2[i], pres[i] + "1.net.1.weight", pres[i] + "1.net.1.bias", dh2[i], None)
+                        for i in range(n)])
         del du
-        dx2 = self._new(rows, dim)
-        K.layernorm_bwd(dh2, x2, m2, r2, P[pre + "1.net.0.weight"], dx3, dx2, G[pre + "1.net.0.weight"],
-                        G[pre + "1.net.0.bias"], rows, dim)
-        do = self._new(rows, inner)
-        self.lin_bwd(dx2, rows, o, pre + "0.to_out.0.weight", pre + "0.to_out.0.bias", dx=do)
-        dqkv = self.attn_bwd(do, qkv, att, Bn, N, H, dh, o=o)
+        dx2 = [self._new(r, dim) for r in rows]
+        for i in range(n):
+            K.layernorm_bwd(dh2[i], x2[i], m2[i], r2[i], P[pres[i] + "1.net.0.weight"], dx3[i], dx2[i],
+                            G[pres[i] + "1.net.0.weight"], G[pres[i] + "1.net.0.bias"], rows[i], dim)
+        do = [self._new(r, inner) for r in rows]
+        self.lin_bwd_g([(dx2[i], rows[i], o[i], pres[i] + "0.to_out.0.weight", pres[i] + "0.to_out.0.bias", do[i], None)
+                        for i in range(n)])
+        dqkv = [self.attn_bwd(do[i], qkv[i], att[i], Bn, Ns[i], H, dh, o=o[i]) for i in range(n)]
         dh1 = dh2  # reuse
-        self.lin_bwd(dqkv, rows, h1, pre + "0.to_qkv.weight", None, dx=dh1)
-        dx = self._new(rows, dim)
-        K.layernorm_bwd(dh1, x, m1, r1, P[pre + "0.norm.weight"], dx2, dx, G[pre + "0.norm.weight"],
-                        G[pre + "0.norm.bias"], rows, dim)
+        self.lin_bwd_g([(dqkv[i], rows[i], h1[i], pres[i] + "0.to_qkv.weight", None, dh1[i], None) for i in range(n)])
+        dx = [self._new(r, dim) for r in rows]
+        for i in range(n):
+            K.layernorm_bwd(dh1[i], x[i], m1[i], r1[i], P[pres[i] + "0.norm.weight"], dx2[i], dx[i],
+                            G[pres[i] + "0.norm.weight"], G[pres[i] + "0.norm.bias"], rows[i], dim)
         return dx
 
-    def stack_fwd(self, prefix, x, Bn, N, dim, depth, H, dh, mlp):
+    def stacks_fwd(self, prefixes, xs, Bn, Ns, dim, depth, H, dh, mlp):
+        """Run len(prefixes) transformer stacks of equal shape in lockstep; returns (outputs, saved[layer][stack])."""
         saved = []
         for i in range(depth):
-            x, s = self.block_fwd(f"{prefix}layers.{i}.", x, Bn, N, dim, H, dh, mlp)
+            xs, s = self.blocks_fwd([f"{p}layers.{i}." for p in prefixes], xs, Bn, Ns, dim, H, dh, mlp)
             saved.append(s)
-        return x, saved
+        return xs, saved
+
+    def stacks_bwd(self, prefixes, dxs, saved, Bn, Ns, dim, H, dh, mlp):
+        for i in reversed(range(len(saved))):
+            dxs = self.blocks_bwd([f"{p}layers.{i}." for p in prefixes], dxs, saved[i], Bn, Ns, dim, H, dh, mlp)
+            saved[i] = None
+        return dxs
+
+    def stack_fwd(self, prefix, x, Bn, N, dim, depth, H, dh, mlp):
+        xs, saved = self.stacks_fwd([prefix], [x], Bn, [N], dim, depth, H, dh, mlp)
+        return xs[0], saved
 
     def stack_bwd(self, prefix, dx, saved, Bn, N, dim, H, dh, mlp):
-        for i in reversed(range(len(saved))):
-            dx = self.block_bwd(f"{prefix}layers.{i}.", dx, saved[i], Bn, N, dim, H, dh, mlp)
-            saved[i] = None
-        return dx
+        return self.stacks_bwd([prefix], [dx], saved, Bn, [N], dim, H, dh, mlp)[0]
 
     # ------------------------------------------------------------------ structural mask (host RNG)
     def mask_struct(self, batch_size: int) -> dict[str, torch.Tensor]:
@@ -539,12 +595,13 @@ class PretrainEngine:
         nt = self.n_kept_total
         if self.inter_depth:
             xcat = self._new(B * nt, E)
-        for g in self.groups.values():
+        glist = list(self.groups.values())
+        enc_pre = [f"encoder.{g.name}." for g in glist]
+        xs, ctx["enc_saved"] = self.stacks_fwd(enc_pre, [ctx["groups"][g.name]["x_kept"].view(B * g.n_kept, E) for g in glist],
+                                               B, [g.n_kept for g in glist], E, depth_g, H, dh, self.mlp_e)
+        for g, pre, x in zip(glist, enc_pre, xs):
             gc = ctx["groups"][g.name]
-            pre = f"encoder.{g.name}."
             rows = B * g.n_kept
-            x, gc["enc_saved"] = self.stack_fwd(pre, gc["x_kept"].view(rows, E), B, g.n_kept, E, depth_g, H, dh,
-                                                self.mlp_e)
             gc["enc_pre_norm"] = x
             gc["enc_m"], gc["enc_r"] = self._new(rows, dtype=f32), self._new(rows, dtype=f32)
             if self.inter_depth:
@@ -568,21 +625,26 @@ class PretrainEngine:
 
         # 5. encoder -> decoder projection, unmask (+ decoder encodings), decoder, pixel projection
         Hd, dhd = hp["decoder_heads"], hp["decoder_dim_head"]
-        for g in self.groups.values():
+        yds = []
+        if E != Dd:
+            yds = [self._new(B * g.n_kept, Dd) for g in glist]
+            self.lin_fwd_g([(ctx["groups"][g.name]["enc_out"], B * g.n_kept, f"enc_to_dec.{g.name}.weight",
+                             f"enc_to_dec.{g.name}.bias", yd, None, None) for g, yd in zip(glist, yds)])
+        else:
+            yds = [ctx["groups"][g.name]["enc_out"] for g in glist]
+        x_decs = []
+        for g, yd in zip(glist, yds):
             gc = ctx["groups"][g.name]
-            rows = B * g.n_kept
-            if E != Dd:
-                yd = self._new(rows, Dd)
-                self.lin_fwd(gc["enc_out"], rows, f"enc_to_dec.{g.name}.weight", f"enc_to_dec.{g.name}.bias", yd)
-            else:
-                yd = gc["enc_out"]
             tok = torch.cat([P[f"mask_token.{x}"].reshape(-1, Dd) for x in g.mods], 0)
             x_dec = self._new(B, g.L, Dd)
             K.unmask_fwd(yd.view(B, g.n_kept, Dd), gc["mask"], gc["slot"], g.consts["tok_id"], gc["src_pos"], tok,
                          g.consts["dec_pos"], gc["feat"], g.consts["date_id"], x_dec, self.date_dim, self.fac_date)
-            pre = f"decoder.{g.name}."
-            x, gc["dec_saved"] = self.stack_fwd(pre, x_dec.view(B * g.L, Dd), B, g.L, Dd, hp["decoder_depth"], Hd, dhd,
-                                                self.mlp_d)
+            x_decs.append(x_dec.view(B * g.L, Dd))
+        dec_pre = [f"decoder.{g.name}." for g in glist]
+        xs, ctx["dec_saved"] = self.stacks_fwd(dec_pre, x_decs, B, [g.L for g in glist], Dd, hp["decoder_depth"], Hd, dhd,
+                                               self.mlp_d)
+        for g, pre, x in zip(glist, dec_pre, xs):
+            gc = ctx["groups"][g.name]
             gc["dec_pre_norm"] = x
             for name in g.mods:
                 mt, mc = self.mods[name], ctx["mods"][name]
@@ -628,17 +690,39 @@ class PretrainEngine:
         return (per_mod * self.loss_w).sum()
 
     # ------------------------------------------------------------------ backward
-    def backward(self, ctx: dict) -> None:
-        """Accumulate parameter gradients into the arena (``self.G``) from ``ctx['mods'][m]['dpred']``."""
+    BWD_SEGMENTS = ("decoder", "inter", "encoder")
+
+    def grad_ranges(self) -> list[tuple[int, int]]:
+        """Arena element ranges whose gradients are final after each backward segment (``BWD_SEGMENTS`` order)."""
+        offs, order = self.arena.offsets, self.arena.order
+        first_inter = next((offs[n] for n in order if n.startswith("encoder_inter.")), None)
+        first_enc = next(offs[n] for n in order if n.startswith("encoder."))
+        if first_inter is None:
+            first_inter = first_enc
+        return [(0, first_inter), (first_inter, first_enc), (first_enc, self.arena.numel)]
+
+    def backward(self, ctx: dict, start: str | None = None, stop: str | None = None) -> None:
+        """Accumulate parameter gradients into the arena (``self.G``) from ``ctx['mods'][m]['dpred']``.
+
+        ``start`` / ``stop`` name the last segment already done / the last segment to run (``BWD_SEGMENTS``), so that
+        a caller can interleave gradient all-reduces (or CUDA-graph boundaries) between segments.
+        """
+        seg = self.BWD_SEGMENTS
+        first = 0 if start is None else seg.index(start) + 1
+        last = len(seg) - 1 if stop is None else seg.index(stop)
+        for i in range(first, last + 1):
+            getattr(self, f"_backward_{seg[i]}")(ctx)
+
+    def _backward_decoder(self, ctx: dict) -> None:
         K, P, G, f32 = self.K, self.P, self.G, torch.float32
         E, Dd, hp, B = self.E, self.Dd, self.hp, ctx["B"]
-        H, dh = hp["heads"], hp["dim_head"]
         Hd, dhd = hp["decoder_heads"], hp["decoder_dim_head"]
-        nt = self.n_kept_total
         d_enc_out = {}
-        for g in self.groups.values():
+        glist = list(self.groups.values())
+        dec_pre = [f"decoder.{g.name}." for g in glist]
+        dxds = []
+        for g, pre in zip(glist, dec_pre):
             gc = ctx["groups"][g.name]
-            pre = f"decoder.{g.name}."
             dxd = self._new(B * g.L, Dd)
             for name in g.mods:
                 mt, mc = self.mods[name], ctx["mods"][name]
@@ -652,7 +736,11 @@ class PretrainEngine:
                                     None, dxd, G[pre + "norm.weight"], G[pre + "norm.bias"], seg_rows, Dd,
                                     in_map=(mt.D * mt.L, g.L, off))
                 mc["dpred"] = mc["xn"] = None
-            dxd = self.stack_bwd(pre, dxd, gc["dec_saved"], B, g.L, Dd, Hd, dhd, self.mlp_d)
+            dxds.append(dxd)
+        dxds = self.stacks_bwd(dec_pre, dxds, ctx["dec_saved"], B, [g.L for g in glist], Dd, Hd, dhd, self.mlp_d)
+        dyds = []
+        for g, dxd in zip(glist, dxds):
+            gc = ctx["groups"][g.name]
             # unmask backward: kept rows go back to the projection, masked rows feed the mask tokens
             dxd3 = dxd.view(B, g.L, Dd)
             dyd = self._new(B, g.n_kept, Dd)
@@ -664,15 +752,23 @@ class PretrainEngine:
                 Gx = self.mods[x].G
                 G[f"mask_token.{x}"].view(Gx, Dd).add_(dtok[k0:k0 + Gx])
                 k0 += Gx
-            rows = B * g.n_kept
-            if E != Dd:
-                de = self._new(rows, E)
-                self.lin_bwd(dyd.view(rows, Dd), rows, gc["enc_out"], f"enc_to_dec.{g.name}.weight",
-                             f"enc_to_dec.{g.name}.bias", dx=de)
-            else:
-                de = dyd.view(rows, E)
+            dyds.append(dyd.view(B * g.n_kept, Dd))
+        if E != Dd:
+            des = [self._new(B * g.n_kept, E) for g in glist]
+            self.lin_bwd_g([(dyd, B * g.n_kept, ctx["groups"][g.name]["enc_out"], f"enc_to_dec.{g.name}.weight",
+                             f"enc_to_dec.{g.name}.bias", de, None) for g, dyd, de in zip(glist, dyds, des)])
+        else:
+            des = dyds
+        for g, de in zip(glist, des):
             d_enc_out[g.name] = de
+        ctx["d_enc_out"] = d_enc_out
 
+    def _backward_inter(self, ctx: dict) -> None:
+        K, P, G = self.K, self.P, self.G
+        E, hp, B = self.E, self.hp, ctx["B"]
+        H, dh = hp["heads"], hp["dim_head"]
+        nt = self.n_kept_total
+        d_enc_out = ctx["d_enc_out"]
         if self.inter_depth:
             dxcat = self._new(B * nt, E)
             for g in self.groups.values():
@@ -681,11 +777,19 @@ class PretrainEngine:
                 K.layernorm_bwd(d_enc_out[g.name], ctx["inter_pre_norm"], gc["int_m"], gc["int_r"],
                                 P["encoder_inter.norm.weight"], None, dxcat, G["encoder_inter.norm.weight"],
                                 G["encoder_inter.norm.bias"], rows, E, in_map=(g.n_kept, nt, g.kept_off))
-            dxcat = self.stack_bwd("encoder_inter.", dxcat, ctx["inter_saved"], B, nt, E, H, dh, self.mlp_e)
+            ctx["dxcat"] = self.stack_bwd("encoder_inter.", dxcat, ctx["inter_saved"], B, nt, E, H, dh, self.mlp_e)
 
-        for g in self.groups.values():
+    def _backward_encoder(self, ctx: dict) -> None:
+        K, P, G = self.K, self.P, self.G
+        E, hp, B = self.E, self.hp, ctx["B"]
+        H, dh = hp["heads"], hp["dim_head"]
+        nt = self.n_kept_total
+        glist = list(self.groups.values())
+        d_enc_out, dxcat = ctx["d_enc_out"], ctx.get("dxcat")
+        enc_pre = [f"encoder.{g.name}." for g in glist]
+        dxs = []
+        for g, pre in zip(glist, enc_pre):
             gc = ctx["groups"][g.name]
-            pre = f"encoder.{g.name}."
             rows = B * g.n_kept
             dx = self._new(rows, E)
             if self.inter_depth:
@@ -695,7 +799,10 @@ class PretrainEngine:
             else:
                 K.layernorm_bwd(d_enc_out[g.name], gc["enc_pre_norm"], gc["enc_m"], gc["enc_r"],
                                 P[pre + "norm.weight"], None, dx, G[pre + "norm.weight"], G[pre + "norm.bias"], rows, E)
-            dx = self.stack_bwd(pre, dx, gc["enc_saved"], B, g.n_kept, E, H, dh, self.mlp_e)
+            dxs.append(dx)
+        dxs = self.stacks_bwd(enc_pre, dxs, ctx["enc_saved"], B, [g.n_kept for g in glist], E, H, dh, self.mlp_e)
+        for g, dx in zip(glist, dxs):
+            gc = ctx["groups"][g.name]
             dxe = self._new(B, g.L, E)
             K.scatter_kept(dx.view(B, g.n_kept, E), gc["mask"], gc["slot"], dxe)
             for name in g.mods:

@@ -1,0 +1,122 @@
+"""CUDA-graph replay of the MAE pretraining step.
+
+The step issues ~800 kernel launches whose arguments do not change from one step to the next (same shapes, same
+buffers), so the host-side issue cost (Python + ctypes, ~45 ms) exceeds the GPU time.  ``GraphedPretrainStep``
+captures forward + loss + backward of ``PretrainEngine`` once -- in one or several consecutive graph segments --
+and replays it per step:
+
+* inputs live in static device buffers (``copy_`` from the caller's batch, pinned-host or device);
+* the structural mask (reference ``MAE.mask_struct``, maestro/ssl/mae.py:178-226, a host-RNG loop) is drawn on the
+  host exactly as in eager mode and copied into static ``uint8`` buffers before the replay;
+* the mask noise (``torch.rand`` on the device, mae.py:232) is drawn inside the graph from torch's graph-safe Philox
+  generator, or copied from the caller (parity tests inject it);
+* the backward can be cut after the decoder / after the joint encoder so that a data-parallel caller can start the
+  gradient all-reduce of a finished arena range (``PretrainEngine.grad_ranges``) while the next segment runs.
+"""
+
+from __future__ import annotations
+
+import torch
+
+from .engine import PretrainEngine
+
+
+class GraphedPretrainStep:
+    def __init__(self, engine: PretrainEngine, example_batch: dict, static_noise: bool = False, segments: int = 1,
+                 warmup: int = 2) -> None:
+        if engine.device.type != "cuda":
+            raise RuntimeError("GraphedPretrainStep needs a CUDA engine (there is no CPU path)")
+        self.eng, self.dev = engine, engine.device
+        self.B = int(example_batch["ref_date"].shape[0])
+        self.segments = max(1, min(3, int(segments)))
+        keys = [k for k in example_batch if k == "ref_date" or k in engine.mods or k.endswith("_dates")]
+        self.batch = {}
+        for k in keys:
+            v = example_batch[k]
+            dt = torch.float32 if k in engine.mods else v.dtype
+            self.batch[k] = torch.empty(v.shape, dtype=dt, device=self.dev)
+            self.batch[k].copy_(v)
+        self.struct = {g.name: torch.zeros(self.B, g.L, dtype=torch.uint8, device=self.dev)
+                       for g in engine.groups.values()}
+        self.struct_host = {n: torch.zeros(t.shape, dtype=torch.uint8).pin_memory() for n, t in self.struct.items()}
+        self.noise = ({g.name: torch.rand(self.B, g.L, device=self.dev) for g in engine.groups.values()}
+                      if static_noise else None)
+        self.loss = torch.zeros((), dtype=torch.float32, device=self.dev)
+        self.graphs: list[torch.cuda.CUDAGraph] = []
+        self._ctx = None
+        self._capture(warmup)
+
+    # ------------------------------------------------------------------ capture
+    def _body(self):
+        """Forward + loss (+ d loss / d pred) over the static buffers."""
+        eng = self.eng
+        b = dict(self.batch)          # forward replaces resized / rescaled modalities in the dict, as the reference does
+        ctx = eng.forward(b, dict(self.struct), self.noise)
+        loss = eng.loss(ctx, b, with_grad=True)
+        self.loss.copy_(loss)
+        return ctx
+
+    def _capture(self, warmup: int) -> None:
+        eng = self.eng
+        self._draw_struct()
+        side = torch.cuda.Stream(device=self.dev)
+        side.wait_stream(torch.cuda.current_stream(self.dev))
+        with torch.cuda.stream(side):
+            for _ in range(max(1, warmup)):      # eager warm-up: allocator pools, function attributes, tensor maps
+                ctx = self._body()
+                eng.backward(ctx)
+                del ctx
+        torch.cuda.current_stream(self.dev).wait_stream(side)
+        torch.cuda.synchronize(self.dev)
+        pool = torch.cuda.graph_pool_handle()
+        launches0 = eng.K.launches
+        cuts = {1: [None], 2: ["decoder", None], 3: ["decoder", "inter", None]}[self.segments]
+        ctx = None
+        for i, cut in enumerate(cuts):
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, pool=pool):
+                if i == 0:
+                    ctx = self._body()
+                eng.backward(ctx, start=cuts[i - 1] if i else None, stop=cut)
+            self.graphs.append(g)
+        self.launches_per_step = eng.K.launches - launches0     # kernels of ours inside one replay
+        self._ctx = ctx          # keeps the captured buffers (mask, indices, predictions) readable after a replay
+
+    # ------------------------------------------------------------------ per step
+    def _draw_struct(self) -> None:
+        draws = self.eng.mask_struct(self.B)                      # host generator, reference draw order
+        for n, m in draws.items():
+            self.struct_host[n].copy_(m.reshape(self.B, -1).to(torch.uint8))
+            self.struct[n].copy_(self.struct_host[n], non_blocking=True)
+
+    def load(self, batch: dict, struct: dict | None = None, noise: dict | None = None) -> None:
+        """Stage one step's inputs into the static buffers (async copies on the current stream)."""
+        for k, dst in self.batch.items():
+            dst.copy_(batch[k], non_blocking=True)
+        if struct is None:
+            self._draw_struct()
+        else:
+            for n, m in struct.items():
+                self.struct[n].copy_(m.reshape(self.B, -1).to(torch.uint8), non_blocking=True)
+        if noise is not None:
+            if self.noise is None:
+                raise RuntimeError("noise can only be injected into a step captured with static_noise=True")
+            for n, z in noise.items():
+                self.noise[n].copy_(z, non_blocking=True)
+
+    def replay(self, segment: int | None = None) -> torch.Tensor:
+        """Replay every segment (or one); the gradient arena must have been zeroed by the caller / optimiser."""
+        if segment is None:
+            for g in self.graphs:
+                g.replay()
+        else:
+            self.graphs[segment].replay()
+        return self.loss
+
+    def step(self, batch: dict, struct: dict | None = None, noise: dict | None = None) -> torch.Tensor:
+        self.load(batch, struct, noise)
+        return self.replay()
+
+    @property
+    def context(self) -> dict:
+        return self._ctx
