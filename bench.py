@@ -176,19 +176,15 @@ def run_ours(args):
         gstep = GraphedPretrainStep(eng, host[0], segments=3 if world > 1 else 1)
         eng.zero_grad()
         devb = gstep.batch
-    ranges = eng.grad_ranges()
-    comm = torch.cuda.Stream(device=dev) if world > 1 else None
+    from maestro_b200.dist import GradReducer
+    reducer = GradReducer(eng.arena.grad, eng.grad_ranges())
 
     def reduce_grads_overlapped():
         """Replay the step segment by segment; all-reduce each finished arena range on the comm stream."""
-        cur = torch.cuda.current_stream()
-        for i, (a, b) in enumerate(ranges):
+        for i in range(len(reducer.buckets)):
             gstep.replay(i)
-            if b > a:
-                comm.wait_stream(cur)
-                with torch.cuda.stream(comm):
-                    dist.all_reduce(eng.arena.grad[a:b])
-        cur.wait_stream(comm)
+            reducer.reduce_range(i)
+        reducer.finish()
 
     def step_device(batch, staged=False):
         if use_graph:
@@ -200,10 +196,9 @@ def run_ours(args):
                 gstep.replay()
             loss = gstep.loss
         else:
-            loss = eng.step(dict(batch))
-            if world > 1:
-                dist.all_reduce(eng.arena.grad)
-        opt.step(grad_scale=1.0 / world)
+            from maestro_b200.dist import data_parallel_step
+            loss = data_parallel_step(eng, dict(batch), reducer)
+        opt.step(grad_scale=reducer.grad_scale)
         return loss
 
     def step_e2e(i):
@@ -296,7 +291,8 @@ def run_ours(args):
                    "global_batch": B * world, "parallelism": f"dp{world}",
                    "l2": "inputs larger than L2 (activations >> 126 MB per step); no flush",
                    "attention": eng.attn_impl, "loss_last": last_loss,
-                   "launch": "cuda-graph replay" if use_graph else "python"},
+                   "launch": "cuda-graph replay" if use_graph else "python",
+                   "allreduce_bytes_per_step": reducer.bytes_per_step},
         "e2e": {"value": B * world / (e2e_ms * 1e-3), "unit": "tiles/s", "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": 4, "ms_per_step": e2e_ms},
         "gpu_launches": launches,

@@ -49,10 +49,12 @@ int mb_colsum_accum(const void* dy, int dtype, float* out, int M, int N, void* s
 int mb_layernorm_fwd(const void* x, const float* gamma, const float* beta, void* y, float* mean, float* rstd,
                      int dtype, int rows, int d, float eps, int in_n, int in_bs, int in_off, int out_n, int out_bs,
                      int out_off, void* stream);
-/* Its backward, fused with the residual-gradient add (x = f(LN(x)) + x). dgamma / dbeta accumulate. */
+/* Its backward, fused with the residual-gradient add (x = f(LN(x)) + x). dgamma / dbeta accumulate.  dbias (may be
+ * null) accumulates the column sums of dx: the bias gradient of the nn.Linear that produced this LayerNorm's input
+ * stream (to_out / FeedForward down-projection), whose dY is exactly this dx. */
 int mb_layernorm_bwd(const void* dy, const void* x, const float* mean, const float* rstd, const float* gamma,
-                     const void* dres, void* dx, float* dgamma, float* dbeta, int dtype, int rows, int d, int in_n,
-                     int in_bs, int in_off, int out_n, int out_bs, int out_off, void* stream);
+                     const void* dres, void* dx, float* dgamma, float* dbeta, float* dbias, int dtype, int rows, int d,
+                     int in_n, int in_bs, int in_off, int out_n, int out_bs, int out_off, void* stream);
 /* nn.GroupNorm(1, E) of PatchifyBands, maestro/layers/embed.py:55,61: per-image sum / sum-of-squares (fp64). */
 int mb_gn_stats(const void* y, int dtype, double* sums, int n_img, long long elems_per_img, void* stream);
 /* GroupNorm apply + enc_add_encodings (maestro/ssl/mim.py:232-252) + group_mods concat (layers/utils.py:12-47). */

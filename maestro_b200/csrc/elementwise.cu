@@ -214,30 +214,64 @@ extern "C" int mb_date_features(const short* dates, const short* ref, float* fea
 }
 
 // ------------------------------------------------------------------ column sums (bias gradients)
-// out[n] += sum_m dy[m, n]  (fp32 atomics into a zeroed / accumulating buffer).
+// out[n] += sum_m dy[m, n]  (fp32).  Each thread owns one 16-byte column vector and strides over the rows of its
+// row slab with 4 loads in flight; the CTA's warps cover 8 row phases that are combined in shared memory, then one
+// red.add per column per CTA.
 template <typename T>
-__global__ void colsum_kernel(const T* __restrict__ dy, float* __restrict__ out, int M, int N, int rows_per_block) {
-  const int n = blockIdx.x * blockDim.x + threadIdx.x;
-  if (n >= N) return;
+__global__ void __launch_bounds__(256) colsum_kernel(const T* __restrict__ dy, float* __restrict__ out, int M, int N,
+                                                     int rows_per_block) {
+  constexpr int V = VecIO<T>::N;
+  __shared__ float red[8][32 * V];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int col = (blockIdx.x * 32 + lane) * V;
   const int m0 = blockIdx.y * rows_per_block;
   const int m1 = min(M, m0 + rows_per_block);
-  float acc = 0.f;
-  for (int m = m0; m < m1; ++m) acc += to_f32(dy[static_cast<size_t>(m) * N + n]);
-  atomicAdd(out + n, acc);
+  float acc[V];
+#pragma unroll
+  for (int j = 0; j < V; ++j) acc[j] = 0.f;
+  if (col < N) {
+    int m = m0 + w;
+    for (; m + 24 < m1; m += 32) {
+      float v[4][V];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) VecIO<T>::load(dy + static_cast<size_t>(m + 8 * u) * N + col, v[u]);
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+#pragma unroll
+        for (int j = 0; j < V; ++j) acc[j] += v[u][j];
+    }
+    for (; m < m1; m += 8) {
+      float v[V];
+      VecIO<T>::load(dy + static_cast<size_t>(m) * N + col, v);
+#pragma unroll
+      for (int j = 0; j < V; ++j) acc[j] += v[j];
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < V; ++j) red[w][lane * V + j] = acc[j];
+  __syncthreads();
+  for (int i = threadIdx.x; i < 32 * V; i += blockDim.x) {
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) s += red[k][i];
+    const int c = blockIdx.x * 32 * V + i;
+    if (c < N) atomicAdd(out + c, s);
+  }
 }
 
 extern "C" int mb_colsum_accum(const void* dy, int dtype, float* out, int M, int N, void* stream) {
   if (M == 0 || N == 0) return 0;
-  const int threads = 128;
-  const int bx = mb_ceil_div(N, threads);
-  int by = (148 * 8) / bx;
+  if (N % 8 != 0) return -2;
+  const int V = dtype == MB_DTYPE_BF16 ? 8 : 4;
+  const int bx = mb_ceil_div(N, 32 * V);
+  int by = (148 * 4) / bx;
   if (by < 1) by = 1;
   int rows_per_block = mb_ceil_div(M, by);
-  if (rows_per_block < 16) rows_per_block = 16;
+  if (rows_per_block < 64) rows_per_block = 64;
   by = mb_ceil_div(M, rows_per_block);
   dim3 grid(bx, by);
   MB_DISPATCH_DTYPE(dtype, T,
-                    (colsum_kernel<T><<<grid, threads, 0, static_cast<cudaStream_t>(stream)>>>(
+                    (colsum_kernel<T><<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
                         static_cast<const T*>(dy), out, M, N, rows_per_block)));
   MB_CHECK_LAUNCH();
   return 0;

@@ -88,61 +88,72 @@ extern "C" int mb_layernorm_fwd(const void* x, const float* gamma, const float* 
 
 // ------------------------------------------------------------------ LayerNorm backward
 // dx = rstd * (g - mean(g) - xhat * mean(g * xhat)) [+ dres],  g = dy * gamma.
-// dgamma += sum_rows dy * xhat, dbeta += sum_rows dy (fp32 atomics, one per column per CTA).
+// dgamma += sum_rows dy * xhat, dbeta += sum_rows dy, and optionally dbias += sum_rows dx (the bias gradient of the
+// linear layer whose output this LayerNorm consumed: its dY is exactly this dx, so the column sum rides along).
 // x / dx / dres rows use in_map, dy rows use out_map (mirrors the forward).
-template <typename T>
-__global__ void __launch_bounds__(256) layernorm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x,
-                                                            const float* __restrict__ mean_in,
-                                                            const float* __restrict__ rstd_in,
-                                                            const float* __restrict__ gamma, const T* __restrict__ dres,
-                                                            T* __restrict__ dx, float* __restrict__ dgamma,
-                                                            float* __restrict__ dbeta, int rows, int d,
-                                                            int rows_per_warp, RowMap in_map, RowMap out_map) {
+// One CTA per SM, 12 warps, warp w of the grid walks rows w, w + W, w + 2W, ...; lanes own columns, so the column
+// sums live in registers for the whole kernel and are combined once per CTA (shared-memory red, then one fp32
+// global red per column per CTA: <= 148 per address).
+constexpr int LNB_THREADS = 384;
+
+template <typename T, int NCH>
+__global__ void __launch_bounds__(LNB_THREADS, 1)
+layernorm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x, const float* __restrict__ mean_in,
+                     const float* __restrict__ rstd_in, const float* __restrict__ gamma, const T* __restrict__ dres,
+                     T* __restrict__ dx, float* __restrict__ dgamma, float* __restrict__ dbeta,
+                     float* __restrict__ dbias, int rows, int d, RowMap in_map, RowMap out_map) {
   constexpr int V = VecIO<T>::N;
-  extern __shared__ float sm[];  // [2][d] partial dgamma / dbeta of this CTA
+  constexpr int NE = NCH * V;
+  extern __shared__ float sm[];  // [3][d] partial dgamma / dbeta / dbias of this CTA
   const int lane = threadIdx.x & 31;
-  const int warp_in_block = threadIdx.x >> 5;
   const int nwarps = blockDim.x >> 5;
-  const int gwarp = blockIdx.x * nwarps + warp_in_block;
+  const int gwarp = blockIdx.x * nwarps + (threadIdx.x >> 5);
+  const int total_warps = gridDim.x * nwarps;
   const int nvec = d / V;
-  for (int i = threadIdx.x; i < 2 * d; i += blockDim.x) sm[i] = 0.f;
+  for (int i = threadIdx.x; i < 3 * d; i += blockDim.x) sm[i] = 0.f;
   __syncthreads();
 
-  float ag[LN_MAX_ELEMS], ab[LN_MAX_ELEMS];
+  float ag[NE], ab[NE], ac[NE], gm[NE];
 #pragma unroll
-  for (int i = 0; i < LN_MAX_ELEMS; ++i) { ag[i] = 0.f; ab[i] = 0.f; }
-
-  const int r0 = gwarp * rows_per_warp;
-  const int r1 = min(rows, r0 + rows_per_warp);
-  for (int r = r0; r < r1; ++r) {
+  for (int c = 0; c < NCH; ++c) {
+    const int idx = lane + c * 32;
+#pragma unroll
+    for (int j = 0; j < V; ++j) {
+      ag[c * V + j] = 0.f; ab[c * V + j] = 0.f; ac[c * V + j] = 0.f;
+      gm[c * V + j] = (idx < nvec) ? gamma[idx * V + j] : 0.f;
+    }
+  }
+  const float inv_d = 1.0f / static_cast<float>(d);
+  for (int r = gwarp; r < rows; r += total_warps) {
     const size_t pin = in_map.phys(r), pout = out_map.phys(r);
     const float mean = mean_in[r], rstd = rstd_in[r];
-    float xh[LN_MAX_ELEMS], g[LN_MAX_ELEMS];
+    float xh[NE], dv[NE];
     float s1 = 0.f, s2 = 0.f;
 #pragma unroll
-    for (int c = 0; c < LN_MAX_ELEMS / V; ++c) {
+    for (int c = 0; c < NCH; ++c) {
       const int idx = lane + c * 32;
       if (idx < nvec) {
-        float xv[V], dv[V];
-        VecIO<T>::load(x + pin * d + idx * V, xv);
-        VecIO<T>::load(dy + pout * d + idx * V, dv);
+        VecIO<T>::load(x + pin * d + idx * V, xh + c * V);
+        VecIO<T>::load(dy + pout * d + idx * V, dv + c * V);
+      } else {
 #pragma unroll
-        for (int j = 0; j < V; ++j) {
-          const float h = (xv[j] - mean) * rstd;
-          const float gg = dv[j] * gamma[idx * V + j];
-          xh[c * V + j] = h;
-          g[c * V + j] = gg;
-          s1 += gg;
-          s2 += gg * h;
-          ag[c * V + j] += dv[j] * h;
-          ab[c * V + j] += dv[j];
-        }
+        for (int j = 0; j < V; ++j) { xh[c * V + j] = mean; dv[c * V + j] = 0.f; }
       }
     }
-    s1 = warp_sum(s1) / d;
-    s2 = warp_sum(s2) / d;
 #pragma unroll
-    for (int c = 0; c < LN_MAX_ELEMS / V; ++c) {
+    for (int e = 0; e < NE; ++e) {
+      const float h = (xh[e] - mean) * rstd;
+      const float gg = dv[e] * gm[e];
+      xh[e] = h;
+      s1 += gg;
+      s2 = fmaf(gg, h, s2);
+      ag[e] = fmaf(dv[e], h, ag[e]);
+      ab[e] += dv[e];
+    }
+    s1 = warp_sum(s1) * inv_d;
+    s2 = warp_sum(s2) * inv_d;
+#pragma unroll
+    for (int c = 0; c < NCH; ++c) {
       const int idx = lane + c * 32;
       if (idx < nvec) {
         float o[V];
@@ -152,19 +163,24 @@ __global__ void __launch_bounds__(256) layernorm_bwd_kernel(const T* __restrict_
           for (int j = 0; j < V; ++j) o[j] = 0.f;
         }
 #pragma unroll
-        for (int j = 0; j < V; ++j) o[j] += rstd * (g[c * V + j] - s1 - xh[c * V + j] * s2);
+        for (int j = 0; j < V; ++j) {
+          const int e = c * V + j;
+          o[j] += rstd * (dv[e] * gm[e] - s1 - xh[e] * s2);
+          ac[e] += o[j];
+        }
         VecIO<T>::store(dx + pin * d + idx * V, o);
       }
     }
   }
 #pragma unroll
-  for (int c = 0; c < LN_MAX_ELEMS / V; ++c) {
+  for (int c = 0; c < NCH; ++c) {
     const int idx = lane + c * 32;
     if (idx < nvec) {
 #pragma unroll
       for (int j = 0; j < V; ++j) {
         atomicAdd(&sm[idx * V + j], ag[c * V + j]);
         atomicAdd(&sm[d + idx * V + j], ab[c * V + j]);
+        if (dbias != nullptr) atomicAdd(&sm[2 * d + idx * V + j], ac[c * V + j]);
       }
     }
   }
@@ -172,27 +188,48 @@ __global__ void __launch_bounds__(256) layernorm_bwd_kernel(const T* __restrict_
   for (int i = threadIdx.x; i < d; i += blockDim.x) {
     atomicAdd(dgamma + i, sm[i]);
     atomicAdd(dbeta + i, sm[d + i]);
+    if (dbias != nullptr) atomicAdd(dbias + i, sm[2 * d + i]);
   }
 }
 
+template <typename T>
+static int launch_ln_bwd(const void* dy, const void* x, const float* mean, const float* rstd, const float* gamma,
+                         const void* dres, void* dx, float* dgamma, float* dbeta, float* dbias, int rows, int d,
+                         RowMap im, RowMap om, cudaStream_t st) {
+  constexpr int V = VecIO<T>::N;
+  const int nwarps = LNB_THREADS / 32;
+  int blocks = mb_ceil_div(rows, nwarps);
+  if (blocks > 148) blocks = 148;
+  const size_t smem = 3 * static_cast<size_t>(d) * sizeof(float);
+  const int nch = mb_ceil_div(d / V, 32);
+#define MB_LNB(N_)                                                                                              \
+  case N_:                                                                                                      \
+    layernorm_bwd_kernel<T, N_><<<blocks, LNB_THREADS, smem, st>>>(                                              \
+        static_cast<const T*>(dy), static_cast<const T*>(x), mean, rstd, gamma, static_cast<const T*>(dres),    \
+        static_cast<T*>(dx), dgamma, dbeta, dbias, rows, d, im, om);                                            \
+    break;
+  switch (nch) {
+    MB_LNB(1) MB_LNB(2) MB_LNB(3) MB_LNB(4) MB_LNB(5) MB_LNB(6) MB_LNB(7) MB_LNB(8)
+    default: return -2;
+  }
+#undef MB_LNB
+  return 0;
+}
+
+// dbias may be null.  dgamma / dbeta / dbias accumulate (fp32).
 extern "C" int mb_layernorm_bwd(const void* dy, const void* x, const float* mean, const float* rstd,
                                 const float* gamma, const void* dres, void* dx, float* dgamma, float* dbeta,
-                                int dtype, int rows, int d, int in_n, int in_bs, int in_off, int out_n, int out_bs,
-                                int out_off, void* stream) {
+                                float* dbias, int dtype, int rows, int d, int in_n, int in_bs, int in_off, int out_n,
+                                int out_bs, int out_off, void* stream) {
   if (rows == 0) return 0;
   if (d > 1024 || d % 8 != 0) return -2;
   RowMap im{in_n, in_bs, in_off}, om{out_n, out_bs, out_off};
-  const int threads = 256, nwarps = threads / 32;
-  // aim for ~4 CTAs per SM; each warp walks a contiguous run of rows
-  int rows_per_warp = mb_ceil_div(rows, 148 * 4 * nwarps);
-  if (rows_per_warp < 1) rows_per_warp = 1;
-  const int blocks = mb_ceil_div(rows, rows_per_warp * nwarps);
-  const size_t smem = 2 * static_cast<size_t>(d) * sizeof(float);
-  MB_DISPATCH_DTYPE(dtype, T,
-                    (layernorm_bwd_kernel<T><<<blocks, threads, smem, static_cast<cudaStream_t>(stream)>>>(
-                        static_cast<const T*>(dy), static_cast<const T*>(x), mean, rstd, gamma,
-                        static_cast<const T*>(dres), static_cast<T*>(dx), dgamma, dbeta, rows, d, rows_per_warp, im,
-                        om)));
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  int rc;
+  if (dtype == MB_DTYPE_F32) rc = launch_ln_bwd<float>(dy, x, mean, rstd, gamma, dres, dx, dgamma, dbeta, dbias, rows, d, im, om, st);
+  else if (dtype == MB_DTYPE_BF16) rc = launch_ln_bwd<bf16>(dy, x, mean, rstd, gamma, dres, dx, dgamma, dbeta, dbias, rows, d, im, om, st);
+  else return -1;
+  if (rc != 0) return rc;
   MB_CHECK_LAUNCH();
   return 0;
 }

@@ -424,14 +424,16 @@ class PretrainEngine:
                  for i in range(n)]
         return x3, saved
 
-    def blocks_bwd(self, pres, dx3, saved, Bn, Ns, dim, H, dh, mlp):
+    def blocks_bwd(self, pres, dx3, saved, Bn, Ns, dim, H, dh, mlp, sinks=None):
+        """``sinks[i]``: bias gradient (of the block below) that receives the column sums of this block's dx."""
         K, P, G = self.K, self.P, self.G
         inner, n = H * dh, len(pres)
         rows = [Bn * N for N in Ns]
         x, m1, r1, h1, qkv, att, o, x2, m2, r2, h2, u, a = (list(t) for t in zip(*saved))
         du = [self._new(r, mlp) for r in rows]
-        self.lin_bwd_g([(dx3[i], rows[i], a[i], pres[i] + "1.net.4.weight", pres[i] + "1.net.4.bias", du[i], u[i])
-                        for i in range(n)])
+        # the bias gradients of net.4 / to_out are column sums of dx3 / dx2: they ride on the LayerNorm backward that
+        # produced those tensors (``dbias``), see ``bias_sink``
+        self.lin_bwd_g([(dx3[i], rows[i], a[i], pres[i] + "1.net.4.weight", None, du[i], u[i]) for i in range(n)])
         dh2 = [self._new(r, dim) for r in rows]
         self.lin_bwd_g([(du[i], rows[i], h2[i], pres[i] + "1.net.1.weight", pres[i] + "1.net.1.bias", dh2[i], None)
                         for i in range(n)])
@@ -439,17 +441,18 @@ class PretrainEngine:
         dx2 = [self._new(r, dim) for r in rows]
         for i in range(n):
             K.layernorm_bwd(dh2[i], x2[i], m2[i], r2[i], P[pres[i] + "1.net.0.weight"], dx3[i], dx2[i],
-                            G[pres[i] + "1.net.0.weight"], G[pres[i] + "1.net.0.bias"], rows[i], dim)
+                            G[pres[i] + "1.net.0.weight"], G[pres[i] + "1.net.0.bias"], rows[i], dim,
+                            dbias=G[pres[i] + "0.to_out.0.bias"])
         do = [self._new(r, inner) for r in rows]
-        self.lin_bwd_g([(dx2[i], rows[i], o[i], pres[i] + "0.to_out.0.weight", pres[i] + "0.to_out.0.bias", do[i], None)
-                        for i in range(n)])
+        self.lin_bwd_g([(dx2[i], rows[i], o[i], pres[i] + "0.to_out.0.weight", None, do[i], None) for i in range(n)])
         dqkv = [self.attn_bwd(do[i], qkv[i], att[i], Bn, Ns[i], H, dh, o=o[i]) for i in range(n)]
         dh1 = dh2  # reuse
         self.lin_bwd_g([(dqkv[i], rows[i], h1[i], pres[i] + "0.to_qkv.weight", None, dh1[i], None) for i in range(n)])
         dx = [self._new(r, dim) for r in rows]
         for i in range(n):
             K.layernorm_bwd(dh1[i], x[i], m1[i], r1[i], P[pres[i] + "0.norm.weight"], dx2[i], dx[i],
-                            G[pres[i] + "0.norm.weight"], G[pres[i] + "0.norm.bias"], rows[i], dim)
+                            G[pres[i] + "0.norm.weight"], G[pres[i] + "0.norm.bias"], rows[i], dim,
+                            dbias=sinks[i] if sinks is not None else None)
         return dx
 
     def stacks_fwd(self, prefixes, xs, Bn, Ns, dim, depth, H, dh, mlp):
@@ -460,9 +463,16 @@ class PretrainEngine:
             saved.append(s)
         return xs, saved
 
+    def bias_sink(self, prefix, depth):
+        """Gradient buffer of the last block's down-projection bias: the LayerNorm backward that produces the stack's
+        incoming gradient must be given this as ``dbias`` (its dx is that linear layer's dY)."""
+        return self.G[f"{prefix}layers.{depth - 1}.1.net.4.bias"] if depth > 0 else None
+
     def stacks_bwd(self, prefixes, dxs, saved, Bn, Ns, dim, H, dh, mlp):
+        """The caller has already routed colsum(dxs) to ``bias_sink`` of every stack (via its own LayerNorm backward)."""
         for i in reversed(range(len(saved))):
-            dxs = self.blocks_bwd([f"{p}layers.{i}." for p in prefixes], dxs, saved[i], Bn, Ns, dim, H, dh, mlp)
+            sinks = [self.G[f"{p}layers.{i - 1}.1.net.4.bias"] for p in prefixes] if i > 0 else None
+            dxs = self.blocks_bwd([f"{p}layers.{i}." for p in prefixes], dxs, saved[i], Bn, Ns, dim, H, dh, mlp, sinks)
             saved[i] = None
         return dxs
 
@@ -734,7 +744,7 @@ class PretrainEngine:
                     self.lin_bwd(mc["dpred"][gi], seg_rows, mc["xn"][gi], pw + "weight", pw + "bias", dx=dxn)
                     K.layernorm_bwd(dxn, gc["dec_pre_norm"], mc["dec_m"][gi], mc["dec_r"][gi], P[pre + "norm.weight"],
                                     None, dxd, G[pre + "norm.weight"], G[pre + "norm.bias"], seg_rows, Dd,
-                                    in_map=(mt.D * mt.L, g.L, off))
+                                    in_map=(mt.D * mt.L, g.L, off), dbias=self.bias_sink(pre, hp["decoder_depth"]))
                 mc["dpred"] = mc["xn"] = None
             dxds.append(dxd)
         dxds = self.stacks_bwd(dec_pre, dxds, ctx["dec_saved"], B, [g.L for g in glist], Dd, Hd, dhd, self.mlp_d)
@@ -776,7 +786,8 @@ class PretrainEngine:
                 rows = B * g.n_kept
                 K.layernorm_bwd(d_enc_out[g.name], ctx["inter_pre_norm"], gc["int_m"], gc["int_r"],
                                 P["encoder_inter.norm.weight"], None, dxcat, G["encoder_inter.norm.weight"],
-                                G["encoder_inter.norm.bias"], rows, E, in_map=(g.n_kept, nt, g.kept_off))
+                                G["encoder_inter.norm.bias"], rows, E, in_map=(g.n_kept, nt, g.kept_off),
+                                dbias=self.bias_sink("encoder_inter.", self.inter_depth))
             ctx["dxcat"] = self.stack_bwd("encoder_inter.", dxcat, ctx["inter_saved"], B, nt, E, H, dh, self.mlp_e)
 
     def _backward_encoder(self, ctx: dict) -> None:
@@ -786,6 +797,7 @@ class PretrainEngine:
         nt = self.n_kept_total
         glist = list(self.groups.values())
         d_enc_out, dxcat = ctx["d_enc_out"], ctx.get("dxcat")
+        depth_g = hp["depth"] - self.inter_depth
         enc_pre = [f"encoder.{g.name}." for g in glist]
         dxs = []
         for g, pre in zip(glist, enc_pre):
@@ -795,10 +807,11 @@ class PretrainEngine:
             if self.inter_depth:
                 K.layernorm_bwd(dxcat, gc["enc_pre_norm"], gc["enc_m"], gc["enc_r"], P[pre + "norm.weight"], None, dx,
                                 G[pre + "norm.weight"], G[pre + "norm.bias"], rows, E,
-                                out_map=(g.n_kept, nt, g.kept_off))
+                                out_map=(g.n_kept, nt, g.kept_off), dbias=self.bias_sink(pre, depth_g))
             else:
                 K.layernorm_bwd(d_enc_out[g.name], gc["enc_pre_norm"], gc["enc_m"], gc["enc_r"],
-                                P[pre + "norm.weight"], None, dx, G[pre + "norm.weight"], G[pre + "norm.bias"], rows, E)
+                                P[pre + "norm.weight"], None, dx, G[pre + "norm.weight"], G[pre + "norm.bias"], rows, E,
+                                dbias=self.bias_sink(pre, depth_g))
             dxs.append(dx)
         dxs = self.stacks_bwd(enc_pre, dxs, ctx["enc_saved"], B, [g.n_kept for g in glist], E, H, dh, self.mlp_e)
         for g, dx in zip(glist, dxs):

@@ -38,7 +38,11 @@ class GraphedPretrainStep:
             self.batch[k].copy_(v)
         self.struct = {g.name: torch.zeros(self.B, g.L, dtype=torch.uint8, device=self.dev)
                        for g in engine.groups.values()}
-        self.struct_host = {n: torch.zeros(t.shape, dtype=torch.uint8).pin_memory() for n, t in self.struct.items()}
+        # two pinned staging sets: the host may draw step i + 1 while the copy of step i is still queued
+        self.struct_host = [{n: torch.zeros(t.shape, dtype=torch.uint8).pin_memory() for n, t in self.struct.items()}
+                            for _ in range(2)]
+        self._stage_ev = [None, None]
+        self._stage_i = 0
         self.noise = ({g.name: torch.rand(self.B, g.L, device=self.dev) for g in engine.groups.values()}
                       if static_noise else None)
         self.loss = torch.zeros((), dtype=torch.float32, device=self.dev)
@@ -85,9 +89,16 @@ class GraphedPretrainStep:
     # ------------------------------------------------------------------ per step
     def _draw_struct(self) -> None:
         draws = self.eng.mask_struct(self.B)                      # host generator, reference draw order
+        i = self._stage_i
+        self._stage_i ^= 1
+        if self._stage_ev[i] is not None:
+            self._stage_ev[i].synchronize()                       # the copy issued two steps ago has left this buffer
         for n, m in draws.items():
-            self.struct_host[n].copy_(m.reshape(self.B, -1).to(torch.uint8))
-            self.struct[n].copy_(self.struct_host[n], non_blocking=True)
+            self.struct_host[i][n].copy_(m.reshape(self.B, -1).to(torch.uint8))
+            self.struct[n].copy_(self.struct_host[i][n], non_blocking=True)
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(self.dev))
+        self._stage_ev[i] = ev
 
     def load(self, batch: dict, struct: dict | None = None, noise: dict | None = None) -> None:
         """Stage one step's inputs into the static buffers (async copies on the current stream)."""

@@ -104,11 +104,12 @@ class Kernels:
         _ck(self.L.mb_layernorm_fwd(_p(x), _p(gamma), _p(beta), _p(y), _p(mean), _p(rstd), _dt(x), rows, d,
                                     C.c_float(eps), *im, *om, _stream()), "layernorm_fwd")
 
-    def layernorm_bwd(self, dy, x, mean, rstd, gamma, dres, dx, dgamma, dbeta, rows, d, in_map=IDENT, out_map=IDENT):
+    def layernorm_bwd(self, dy, x, mean, rstd, gamma, dres, dx, dgamma, dbeta, rows, d, in_map=IDENT, out_map=IDENT,
+                      dbias=None):
         im, om = _rowmap(in_map, rows), _rowmap(out_map, rows)
         self.launches += 1
         _ck(self.L.mb_layernorm_bwd(_p(dy), _p(x), _p(mean), _p(rstd), _p(gamma), _p(dres), _p(dx), _p(dgamma),
-                                    _p(dbeta), _dt(x), rows, d, *im, *om, _stream()), "layernorm_bwd")
+                                    _p(dbeta), _p(dbias), _dt(x), rows, d, *im, *om, _stream()), "layernorm_bwd")
 
     def gn_stats(self, y, sums, n_img):
         self.launches += 1

@@ -96,7 +96,8 @@ class FakeKernels:
             rstd[:rows] = rs[:, 0]
         y.reshape(-1, d)[_rows(y, rows, d, out_map)] = ((xi - mu) * rs * gamma + beta).to(y.dtype)
 
-    def layernorm_bwd(self, dy, x, mean, rstd, gamma, dres, dx, dgamma, dbeta, rows, d, in_map=None, out_map=None):
+    def layernorm_bwd(self, dy, x, mean, rstd, gamma, dres, dx, dgamma, dbeta, rows, d, in_map=None, out_map=None,
+                      dbias=None):
         ri, ro = _rows(x, rows, d, in_map), _rows(dy, rows, d, out_map)
         xi = x.reshape(-1, d)[ri].float()
         g = dy.reshape(-1, d)[ro].float()
@@ -108,6 +109,8 @@ class FakeKernels:
         dx.reshape(-1, d)[ri] = out.to(dx.dtype)
         dgamma += (g * xh).sum(0)
         dbeta += g.sum(0)
+        if dbias is not None:
+            dbias += out.sum(0)
 
     def gn_stats(self, y, sums, n_img):
         v = y.reshape(n_img, -1).double()
