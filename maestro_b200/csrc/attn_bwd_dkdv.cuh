@@ -103,12 +103,11 @@ __global__ void __launch_bounds__(128) attn_bwd_dkdv_kernel(const __grid_constan
   const size_t stat_base = (static_cast<size_t>(b) * H + h) * N;
 
   for (int i = 0; i < c_tiles; ++i) {
-    const int valid = min(BC, N - i * BC);
     float* st = s_stat + (i & 1) * 2 * BC;
     if (tid < BC) {
       const int q = i * BC + tid;
       st[tid] = q < N ? args.lse[stat_base + q] * 1.4426950408889634f : 0.f;
-      st[BC + tid] = q < N ? args.delta[stat_base + q] : 0.f;
+      st[BC + tid] = q < N ? args.delta[stat_base + q] * sc : 0.f;      // delta pre-multiplied by the score scale
     }
     tc::mbar_wait(bar_s, i & 1);
     tc::tc_fence_after();
@@ -117,6 +116,8 @@ __global__ void __launch_bounds__(128) attn_bwd_dkdv_kernel(const __grid_constan
       if (tid == 0 && i + 1 < c_tiles) load_q(i + 1);
     }
     __syncthreads();                        // s_stat visible
+    // P^T and dS^T.  No masks: queries past N are zero rows of Q and dO (TMA zero fill), so their columns multiply
+    // zero rows in dV += P^T dO and dK += dS^T Q; key rows past N are never stored.  st[] holds finite values there.
 #pragma unroll
     for (int ch = 0; ch < BC / 32; ++ch) {
       uint32_t s[32], dp[32];
@@ -126,17 +127,21 @@ __global__ void __launch_bounds__(128) attn_bwd_dkdv_kernel(const __grid_constan
 #pragma unroll
       for (int v8 = 0; v8 < 4; ++v8) {
         uint32_t wp[4], wd[4];
+        const int q0 = ch * 32 + v8 * 8;
+        const float4 l0 = *reinterpret_cast<const float4*>(st + q0), l1 = *reinterpret_cast<const float4*>(st + q0 + 4);
+        const float4 e0 = *reinterpret_cast<const float4*>(st + BC + q0);
+        const float4 e1 = *reinterpret_cast<const float4*>(st + BC + q0 + 4);
+        const float ls[8] = {l0.x, l0.y, l0.z, l0.w, l1.x, l1.y, l1.z, l1.w};
+        const float ds[8] = {e0.x, e0.y, e0.z, e0.w, e1.x, e1.y, e1.z, e1.w};
 #pragma unroll
         for (int k2 = 0; k2 < 4; ++k2) {
           float p2[2], d2[2];
 #pragma unroll
           for (int e = 0; e < 2; ++e) {
             const int idx = v8 * 8 + 2 * k2 + e;
-            const int q = ch * 32 + idx;
-            const bool ok = row_ok && q < valid;
-            const float p = exp2f(fmaf(__uint_as_float(s[idx]), c, -st[q]));
-            p2[e] = ok ? p : 0.f;
-            d2[e] = ok ? p * (__uint_as_float(dp[idx]) - st[BC + q]) * sc : 0.f;
+            const float p = fast_exp2(fmaf(__uint_as_float(s[idx]), c, -ls[2 * k2 + e]));
+            p2[e] = p;
+            d2[e] = p * fmaf(__uint_as_float(dp[idx]), sc, -ds[2 * k2 + e]);
           }
           __nv_bfloat162 hp = __floats2bfloat162_rn(p2[0], p2[1]);
           __nv_bfloat162 hd = __floats2bfloat162_rn(d2[0], d2[1]);

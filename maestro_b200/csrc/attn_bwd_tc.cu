@@ -141,16 +141,18 @@ __global__ void __launch_bounds__(128) attn_bwd_dq_kernel(const __grid_constant_
     args.delta[li] = delta;
   }
   const float c = args.scale_log2, sc = args.scale;
+  const float delta_sc = delta * sc;
   uint8_t* ds_row = smem + OFF_DS + tid * 128;
 
   for (int j = 0; j < c_tiles; ++j) {
-    const int valid = min(BC, N - j * BC);
     tc::mbar_wait(bar_s, j & 1);
     tc::tc_fence_after();
     if (j > 0) {
       tc::mbar_wait(bar_o, (j - 1) & 1);           // dQ MMA of tile j-1 done: dS buffer and K/V stage free
       if (tid == 0 && j + 1 < c_tiles) load_kv(j + 1);
     }
+    // dS = P * (dP - delta) * scale.  No masks: keys past N are zero rows of K and V, so whatever lands in their dS
+    // columns multiplies zero rows of K in dQ += dS K; query rows past N are never stored.
 #pragma unroll
     for (int ch = 0; ch < BC / 32; ++ch) {
       uint32_t s[32], dp[32];
@@ -166,9 +168,8 @@ __global__ void __launch_bounds__(128) attn_bwd_dq_kernel(const __grid_constant_
 #pragma unroll
           for (int e = 0; e < 2; ++e) {
             const int idx = v8 * 8 + 2 * i + e;
-            const float p = exp2f(fmaf(__uint_as_float(s[idx]), c, -lse2));
-            const float v = p * (__uint_as_float(dp[idx]) - delta) * sc;
-            d2[e] = (ch * 32 + idx < valid && row_ok) ? v : 0.f;
+            const float p = fast_exp2(fmaf(__uint_as_float(s[idx]), c, -lse2));
+            d2[e] = p * fmaf(__uint_as_float(dp[idx]), sc, -delta_sc);
           }
           __nv_bfloat162 hb = __floats2bfloat162_rn(d2[0], d2[1]);
           w[i] = *reinterpret_cast<uint32_t*>(&hb);
