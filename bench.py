@@ -255,13 +255,22 @@ def run_ours(args):
         e0.record()
         orig_grouped(problems)
         e1.record()
-        rec.append((tc, fl, e0, e1))
+        shape = ";".join(f"{a[3]}x{a[4]}x{a[5]}" for a, _ in problems) + f" f{problems[0][1].get('flags', 0)}" \
+            + ("r" if problems[0][1].get("residual") is not None else "")
+        rec.append((tc, fl, e0, e1, shape))
     K.gemm_grouped = grouped_probe
     eng.zero_grad()
+    # the probe step is issued from Python (slower than the GPU): a 60 ms spin kernel gives the host a head start so
+    # that every timed launch finds its predecessor still running and the event pair brackets device time only
+    torch.cuda._sleep(int(0.060 * 1.9e9))
     eng.step(dict(devb))
     torch.cuda.synchronize()
     K.gemm_grouped = orig_grouped
     eng.zero_grad()
+    if args.gemm_breakdown:
+        for tc, fl, e0, e1, shape in sorted(rec, key=lambda r: -r[2].elapsed_time(r[3])):
+            ms = e0.elapsed_time(e1)
+            print(f"gemm {shape} {ms * 1e3:8.1f} us {fl / ms / 1e9:7.1f} TF/s", file=sys.stderr)
     tc_fl = sum(r[1] for r in rec if r[0])
     tc_ms = sum(r[2].elapsed_time(r[3]) for r in rec if r[0])
     at_fl = sum(r[1] for r in rec if not r[0])
@@ -323,6 +332,7 @@ def main():
     ap.add_argument("--batch", type=int, default=32, help="tiles per GPU (reference default, conf/opt.py:20)")
     ap.add_argument("--cpu-batch", type=int, default=2)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--gemm-breakdown", action="store_true", help="per-launch GEMM times of the probe step on stderr")
     ap.add_argument("--no-graph", action="store_true", help="issue every launch from Python instead of CUDA-graph replay")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -6,11 +6,13 @@
 //         o   [Bn * N, H * DH] bf16, lse [Bn, H, N] fp32 (natural log of the softmax denominator, scaled scores).
 //
 // Forward: one CTA (128 threads) per (sample, head, 128-query tile).  Thread t owns query row t == TMEM lane t, so
-// row max / row sum need no shuffles.  Per 128-key tile: S = Q K^T (tcgen05.mma, fp32 in TMEM) -> two passes of
+// row max / row sum need no shuffles.  Per 64-key tile: S = Q K^T (tcgen05.mma, fp32 in TMEM) -> two passes of
 // tcgen05.ld over the row (max, then exp2 + sum) -> P (bf16) written to shared memory in the K-major 128B-swizzle
 // layout -> O_tile = P V (V consumed as an MN-major operand straight from its TMA tile) -> registers accumulate
 // O with the online-softmax rescale.  K/V tiles are double-buffered; the next S = Q K^T is issued before the
-// current P V result is consumed so the tensor pipe overlaps the exp work; several CTAs share an SM.
+// current P V result is consumed so the tensor pipe overlaps the exp work.  S (64 columns) + O (<= 64) take 128
+// TMEM columns and ~40-64 KB of shared memory, so 3-4 CTAs share an SM and hide each other's MMA / TMEM latencies
+// (measured: dh = 32, N = 1024: 303 us with 128-key tiles and 2 CTAs per SM -> 234 us; MUFU.EX2 bound 115 us).
 #include "common.cuh"
 #include "tc_common.cuh"
 #include "tmap.h"
@@ -18,16 +20,17 @@
 namespace {
 
 constexpr int BQ = 128;   // query rows per CTA
-constexpr int BKV = 128;  // keys per tile
+constexpr int BKV = 64;   // keys per tile: S (64) + O (<= 64) fit 128 TMEM columns -> up to 4 CTAs share an SM
 
 template <int DH> struct ACfg {
   static constexpr int SW = DH * 2;                       // swizzle span == row bytes of a [rows, DH] bf16 tile
-  static constexpr int TILE_BYTES = BKV * DH * 2;         // one Q / K / V tile
-  static constexpr int P_BYTES = BQ * BKV * 2;            // 32 KB: two [128 x 64] K-major blocks
+  static constexpr int Q_BYTES = BQ * DH * 2;             // Q tile (two 64-row TMA boxes)
+  static constexpr int TILE_BYTES = BKV * DH * 2;         // one K / V tile
+  static constexpr int P_BYTES = BQ * BKV * 2;            // 16 KB: one [128 x 64] K-major block
   static constexpr int OFF_Q = 0;
-  static constexpr int OFF_K = TILE_BYTES;                // 2 stages
-  static constexpr int OFF_V = 3 * TILE_BYTES;            // 2 stages
-  static constexpr int OFF_P = 5 * TILE_BYTES;
+  static constexpr int OFF_K = Q_BYTES;                   // 2 stages
+  static constexpr int OFF_V = OFF_K + 2 * TILE_BYTES;    // 2 stages
+  static constexpr int OFF_P = OFF_V + 2 * TILE_BYTES;
   static constexpr int OFF_BAR = OFF_P + P_BYTES;
   static constexpr int SMEM_BYTES = OFF_BAR + 128 + 1024;  // + barriers + alignment slack
   static constexpr uint32_t LT = tc::layout_type_for(SW);
@@ -71,15 +74,15 @@ __global__ void __launch_bounds__(128) attn_fwd_kernel(const __grid_constant__ C
     tc::fence_barrier_init();
   }
   if (warp == 0) {
-    tc::tmem_alloc(tmem_ptr, 256);
+    tc::tmem_alloc(tmem_ptr, 128);
     tc::tmem_relinquish();
   }
   tc::tc_fence_before();
   __syncthreads();
   tc::tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
-  const uint32_t tm_s = tmem_base;          // S: columns [0, 128)
-  const uint32_t tm_o = tmem_base + 128;    // O tile: columns [128, 128 + DH)
+  const uint32_t tm_s = tmem_base;          // S: columns [0, 64)
+  const uint32_t tm_o = tmem_base + BKV;    // O tile: columns [64, 64 + DH)
   const uint32_t lane_base = static_cast<uint32_t>(warp * 32) << 16;
 
   constexpr uint32_t idesc_s = tc::make_idesc_bf16(BQ, BKV, 0, 0);   // Q (K-major) x K (K-major)
@@ -107,7 +110,7 @@ __global__ void __launch_bounds__(128) attn_fwd_kernel(const __grid_constant__ C
     const uint32_t sV = tc::smem_u32(smem + C_::OFF_V + (j & 1) * C_::TILE_BYTES);
 #pragma unroll
     for (int k = 0; k < BKV / 16; ++k) {
-      const uint64_t da = tc::make_smem_desc(sP + (k / 4) * 16384 + (k % 4) * 32, 16, 1024, tc::SWIZZLE_128B);
+      const uint64_t da = tc::make_smem_desc(sP + k * 32, 16, 1024, tc::SWIZZLE_128B);
       const uint64_t db = tc::make_smem_desc(sV + k * 16 * C_::SW, 16, 8 * C_::SW, C_::LT);
       tc::umma_bf16(tm_o, da, db, idesc_o, k > 0 ? 1u : 0u);
     }
@@ -115,8 +118,9 @@ __global__ void __launch_bounds__(128) attn_fwd_kernel(const __grid_constant__ C
   };
 
   if (tid == 0) {
-    tc::mbar_expect_tx(bar_q, C_::TILE_BYTES);
+    tc::mbar_expect_tx(bar_q, C_::Q_BYTES);
     tc::tma_load_3d(smem + C_::OFF_Q, &tm, bar_q, h * DH, qt * BQ, b);
+    tc::tma_load_3d(smem + C_::OFF_Q + C_::Q_BYTES / 2, &tm, bar_q, h * DH, qt * BQ + 64, b);
     load_kv(0);
     if (kv_tiles > 1) load_kv(1);
     tc::mbar_wait(bar_q, 0);
@@ -182,9 +186,8 @@ __global__ void __launch_bounds__(128) attn_fwd_kernel(const __grid_constant__ C
             __nv_bfloat162 hb = __floats2bfloat162_rn(p0, p1);
             w[i] = *reinterpret_cast<uint32_t*>(&hb);
           }
-          const int colb = ch * 32 + v8 * 8;                 // first key of this 16-byte chunk
-          const int blk = colb >> 6, c16 = (colb & 63) >> 3;
-          *reinterpret_cast<uint4*>(p_row + blk * 16384 + ((c16 ^ (tid & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
+          const int c16 = ch * 4 + v8;                       // 16-byte chunk of the 128-byte P row
+          *reinterpret_cast<uint4*>(p_row + ((c16 ^ (tid & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
         }
       }
       lsum = (ls[0] + ls[1]) + (ls[2] + ls[3]);
@@ -209,9 +212,8 @@ __global__ void __launch_bounds__(128) attn_fwd_kernel(const __grid_constant__ C
             __nv_bfloat162 hb = __floats2bfloat162_rn(p0, p1);
             w[i] = *reinterpret_cast<uint32_t*>(&hb);
           }
-          const int colb = ch * 32 + v8 * 8;
-          const int blk = colb >> 6, c16 = (colb & 63) >> 3;
-          *reinterpret_cast<uint4*>(p_row + blk * 16384 + ((c16 ^ (tid & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
+          const int c16 = ch * 4 + v8;
+          *reinterpret_cast<uint4*>(p_row + ((c16 ^ (tid & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
         }
       }
     }
@@ -259,7 +261,7 @@ __global__ void __launch_bounds__(128) attn_fwd_kernel(const __grid_constant__ C
   }
   tc::tc_fence_before();
   __syncthreads();
-  if (warp == 0) tc::tmem_dealloc(tmem_base, 256);
+  if (warp == 0) tc::tmem_dealloc(tmem_base, 128);
 }
 
 int qkv_tmap(CUtensorMap* tm, const void* qkv, int Bn, int N, int cols, int DH, int box_rows) {

@@ -23,6 +23,10 @@ template <typename T> struct VecIO;
 
 template <> struct VecIO<float> {
   static constexpr int N = 4;
+  typedef float4 Raw;   // one 16-byte access, still packed
+  __device__ __forceinline__ static Raw load_raw(const float* p) { return *reinterpret_cast<const float4*>(p); }
+  __device__ __forceinline__ static Raw zero_raw() { return make_float4(0.f, 0.f, 0.f, 0.f); }
+  __device__ __forceinline__ static void unpack(const Raw& t, float* v) { v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w; }
   __device__ __forceinline__ static void load(const float* p, float* v) {
     float4 t = *reinterpret_cast<const float4*>(p);
     v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
@@ -34,6 +38,17 @@ template <> struct VecIO<float> {
 
 template <> struct VecIO<bf16> {
   static constexpr int N = 8;
+  typedef uint4 Raw;
+  __device__ __forceinline__ static Raw load_raw(const bf16* p) { return *reinterpret_cast<const uint4*>(p); }
+  __device__ __forceinline__ static Raw zero_raw() { return make_uint4(0, 0, 0, 0); }
+  __device__ __forceinline__ static void unpack(const Raw& t, float* v) {
+    const uint32_t w[4] = {t.x, t.y, t.z, t.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      v[2 * i] = __uint_as_float(w[i] << 16);
+      v[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
+    }
+  }
   __device__ __forceinline__ static void load(const bf16* p, float* v) {
     uint4 t = *reinterpret_cast<const uint4*>(p);
     const uint32_t w[4] = {t.x, t.y, t.z, t.w};

@@ -113,42 +113,62 @@ layernorm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x, const fl
   for (int i = threadIdx.x; i < 3 * d; i += blockDim.x) sm[i] = 0.f;
   __syncthreads();
 
-  float ag[NE], ab[NE], ac[NE], gm[NE];
+  typedef typename VecIO<T>::Raw Raw;
+  float ag[NE], ab[NE], ac[NE];
 #pragma unroll
-  for (int c = 0; c < NCH; ++c) {
-    const int idx = lane + c * 32;
-#pragma unroll
-    for (int j = 0; j < V; ++j) {
-      ag[c * V + j] = 0.f; ab[c * V + j] = 0.f; ac[c * V + j] = 0.f;
-      gm[c * V + j] = (idx < nvec) ? gamma[idx * V + j] : 0.f;
-    }
-  }
+  for (int e = 0; e < NE; ++e) { ag[e] = 0.f; ab[e] = 0.f; ac[e] = 0.f; }
   const float inv_d = 1.0f / static_cast<float>(d);
-  for (int r = gwarp; r < rows; r += total_warps) {
+  const bool has_res = dres != nullptr;
+
+  // software pipeline over this warp's rows: the (still packed) loads of row r + W are in flight while row r is
+  // reduced and written, so each warp keeps two rows of HBM traffic outstanding
+  Raw nx[NCH], ndy[NCH], nres[NCH];
+  auto issue_loads = [&](int r) {
     const size_t pin = in_map.phys(r), pout = out_map.phys(r);
+#pragma unroll
+    for (int c = 0; c < NCH; ++c) {
+      const int idx = lane + c * 32;
+      const bool ok = idx < nvec;
+      nx[c] = ok ? VecIO<T>::load_raw(x + pin * d + idx * V) : VecIO<T>::zero_raw();
+      ndy[c] = ok ? VecIO<T>::load_raw(dy + pout * d + idx * V) : VecIO<T>::zero_raw();
+      nres[c] = (ok && has_res) ? VecIO<T>::load_raw(dres + pin * d + idx * V) : VecIO<T>::zero_raw();
+    }
+  };
+  int r = gwarp;
+  if (r < rows) issue_loads(r);
+  for (; r < rows; r += total_warps) {
+    const size_t pin = in_map.phys(r);
     const float mean = mean_in[r], rstd = rstd_in[r];
     float xh[NE], dv[NE];
+    Raw cres[NCH];
+#pragma unroll
+    for (int c = 0; c < NCH; ++c) {
+      VecIO<T>::unpack(nx[c], xh + c * V);
+      VecIO<T>::unpack(ndy[c], dv + c * V);
+      cres[c] = nres[c];
+    }
+    if (r + total_warps < rows) issue_loads(r + total_warps);
     float s1 = 0.f, s2 = 0.f;
 #pragma unroll
     for (int c = 0; c < NCH; ++c) {
       const int idx = lane + c * 32;
       if (idx < nvec) {
-        VecIO<T>::load(x + pin * d + idx * V, xh + c * V);
-        VecIO<T>::load(dy + pout * d + idx * V, dv + c * V);
-      } else {
+        float gv[V];
+        VecIO<float>::load(gamma + idx * V, gv);
+        if (V == 8) VecIO<float>::load(gamma + idx * V + 4, gv + 4);
 #pragma unroll
-        for (int j = 0; j < V; ++j) { xh[c * V + j] = mean; dv[c * V + j] = 0.f; }
+        for (int j = 0; j < V; ++j) {
+          const int e = c * V + j;
+          const float h = (xh[e] - mean) * rstd;
+          const float gg = dv[e] * gv[j];
+          xh[e] = h;
+          s1 += gg;
+          s2 = fmaf(gg, h, s2);
+          ag[e] = fmaf(dv[e], h, ag[e]);
+          ab[e] += dv[e];
+          dv[e] = gg;
+        }
       }
-    }
-#pragma unroll
-    for (int e = 0; e < NE; ++e) {
-      const float h = (xh[e] - mean) * rstd;
-      const float gg = dv[e] * gm[e];
-      xh[e] = h;
-      s1 += gg;
-      s2 = fmaf(gg, h, s2);
-      ag[e] = fmaf(dv[e], h, ag[e]);
-      ab[e] += dv[e];
     }
     s1 = warp_sum(s1) * inv_d;
     s2 = warp_sum(s2) * inv_d;
@@ -157,15 +177,11 @@ layernorm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x, const fl
       const int idx = lane + c * 32;
       if (idx < nvec) {
         float o[V];
-        if (dres != nullptr) VecIO<T>::load(dres + pin * d + idx * V, o);
-        else {
-#pragma unroll
-          for (int j = 0; j < V; ++j) o[j] = 0.f;
-        }
+        VecIO<T>::unpack(cres[c], o);
 #pragma unroll
         for (int j = 0; j < V; ++j) {
           const int e = c * V + j;
-          o[j] += rstd * (dv[e] * gm[e] - s1 - xh[e] * s2);
+          o[j] += rstd * (dv[e] - s1 - xh[e] * s2);
           ac[e] += o[j];
         }
         VecIO<T>::store(dx + pin * d + idx * V, o);

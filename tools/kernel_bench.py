@@ -1,0 +1,92 @@
+"""Micro-benchmark of the bandwidth-/exp-bound kernels on the FLAIR-HUB ViT-B shapes (32 tiles/GPU).
+
+    python tools/kernel_bench.py [--iters 10] [--only ln_bwd]
+
+CUDA events around each launch, L2 flushed between iterations; prints time, achieved GB/s (LayerNorm, algorithmic
+bytes) or TFLOP/s (attention, 4 N^2 h dh per sample forward, 2.5x backward).
+"""
+import argparse
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+import torch  # noqa: E402
+
+from maestro_b200.ops import Kernels  # noqa: E402
+
+ENC = {"enc_aerial": 256, "enc_dem": 64, "enc_s2": 100, "enc_s1": 50, "inter": 470}
+DEC = {"dec_aerial": 1024, "dec_dem": 256, "dec_s2": 400, "dec_s1": 200}
+B = 32
+
+
+def timeit(fn, iters, flush):
+    for _ in range(2):
+        fn()
+    ms = 0.0
+    for _ in range(iters):
+        flush.fill_(1)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        fn()
+        e1.record()
+        torch.cuda.synchronize()
+        ms += e0.elapsed_time(e1)
+    return ms / iters
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--iters", type=int, default=10)
+    ap.add_argument("--only", default="")
+    ap.add_argument("--tag", default="", help="restrict to one stack, e.g. dec_aerial")
+    args = ap.parse_args()
+    K = Kernels()
+    dev, bf = "cuda", torch.bfloat16
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    tot = {}
+    for tag, N in {**ENC, **DEC}.items():
+        if args.tag and args.tag != tag:
+            continue
+        d, H, dh = (768, 12, 64) if tag in ENC else (512, 16, 32)
+        rows = B * N
+        x = torch.randn(rows, d, device=dev).to(bf)
+        dy = torch.randn(rows, d, device=dev).to(bf)
+        dres = torch.randn(rows, d, device=dev).to(bf)
+        y, dx = torch.empty_like(x), torch.empty_like(x)
+        gamma, beta = torch.ones(d, device=dev), torch.zeros(d, device=dev)
+        mean, rstd = torch.zeros(rows, device=dev), torch.ones(rows, device=dev)
+        dg, db, dbias = (torch.zeros(d, device=dev) for _ in range(3))
+        qkv = torch.randn(rows, 3 * H * dh, device=dev).to(bf)
+        o = torch.empty(rows, H * dh, device=dev, dtype=bf)
+        do = torch.randn(rows, H * dh, device=dev).to(bf)
+        dqkv = torch.empty_like(qkv)
+        lse = torch.zeros(B, H, N, device=dev)
+        delta = torch.zeros(B, H, N, device=dev)
+        du = torch.randn(rows, 3072, device=dev).to(bf)
+        dbu = torch.zeros(3072, device=dev)
+        fl = 4.0 * N * N * H * dh * B
+        cases = [
+            ("ln_fwd", lambda: K.layernorm_fwd(x, gamma, beta, y, mean, rstd, rows, d), rows * d * 2 * 2, "B"),
+            ("ln_bwd", lambda: K.layernorm_bwd(dy, x, mean, rstd, gamma, dres, dx, dg, db, rows, d, dbias=dbias),
+             rows * d * 2 * 4, "B"),
+            ("colsum_mlp", lambda: K.colsum_accum(du, dbu), rows * 3072 * 2, "B"),
+            ("attn_fwd", lambda: K.attn_fwd(qkv, o, lse, B, N, H, dh), fl, "F"),
+            ("attn_bwd", lambda: K.attn_bwd(qkv, o, do, lse, dqkv, delta, B, N, H, dh), 2.5 * fl, "F"),
+        ]
+        K.attn_fwd(qkv, o, lse, B, N, H, dh)
+        for name, fn, work, kind in cases:
+            if args.only and args.only not in name:
+                continue
+            ms = timeit(fn, args.iters, flush)
+            rate = work / ms / 1e6 if kind == "B" else work / ms / 1e9
+            unit = "GB/s" if kind == "B" else "TFLOP/s"
+            tot[name] = tot.get(name, 0.0) + ms * (9 if tag.startswith("enc") else 3)
+            print(f"{tag:11s} {name:11s} rows={rows:6d} N={N:5d}  {ms * 1e3:8.1f} us  {rate:8.1f} {unit}", flush=True)
+    print("per-step totals (x9 encoder layers, x3 inter / decoder layers; LN: x2 per layer):")
+    for k, v in tot.items():
+        print(f"  {k:11s} {v * (2 if k.startswith('ln') else 1):7.3f} ms")
+
+
+if __name__ == "__main__":
+    main()

@@ -15,6 +15,8 @@ for r in csv.DictReader(lines):
     v *= {"ns": 1e-3, "us": 1.0, "ms": 1e3, "s": 1e6}.get(unit, 1e-3)
     name = re.sub(r"\(.*", "", r["Kernel Name"])
     rows.append((name, v))
+if len(sys.argv) > 2:          # keep only the last N launches (one step)
+    rows = rows[-int(sys.argv[2]):]
 tot = sum(v for _, v in rows)
 agg = defaultdict(lambda: [0, 0.0])
 for n, v in rows:
