@@ -8,6 +8,7 @@ __global__ void __launch_bounds__(128) attn_bwd_dkdv_kernel(const __grid_constan
                                                             const __grid_constant__ CUtensorMap tm_qkv64,
                                                             const __grid_constant__ CUtensorMap tm_do64, BwdArgs args) {
   using C_ = BCfg<DH>;
+  constexpr int BC = C_::BC;
   constexpr int OFF_K = 0, OFF_V = C_::ROW_TILE, OFF_Q = 2 * C_::ROW_TILE, OFF_DO = OFF_Q + 2 * C_::COL_TILE;
   constexpr int OFF_PT = OFF_DO + 2 * C_::COL_TILE, OFF_DST = OFF_PT + C_::A_TILE, OFF_STAT = OFF_DST + C_::A_TILE;
   constexpr int OFF_BAR = OFF_STAT + 2 * 2 * BC * 4;
@@ -36,14 +37,14 @@ __global__ void __launch_bounds__(128) attn_bwd_dkdv_kernel(const __grid_constan
     tc::fence_barrier_init();
   }
   if (warp == 0) {
-    tc::tmem_alloc(tmem_ptr, 256);
+    tc::tmem_alloc(tmem_ptr, C_::TMEM_DKDV);
     tc::tmem_relinquish();
   }
   tc::tc_fence_before();
   __syncthreads();
   tc::tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
-  const uint32_t tm_st = tmem_base, tm_dpt = tmem_base + 64, tm_dk = tmem_base + 128, tm_dv = tmem_base + 128 + DH;
+  const uint32_t tm_st = tmem_base, tm_dpt = tmem_base + BC, tm_dk = tmem_base + 2 * BC, tm_dv = tmem_base + 2 * BC + DH;
   const uint32_t lane_base = static_cast<uint32_t>(warp * 32) << 16;
   constexpr uint32_t idesc_s = tc::make_idesc_bf16(BR, BC, 0, 0);    // [128 keys] x [64 queries], K = DH
   constexpr uint32_t idesc_g = tc::make_idesc_bf16(BR, DH, 0, 1);    // [128 keys] x [DH], K = 64 queries (B MN-major)
@@ -74,11 +75,11 @@ __global__ void __launch_bounds__(128) attn_bwd_dkdv_kernel(const __grid_constan
     const uint32_t sDO = tc::smem_u32(smem + OFF_DO + (i & 1) * C_::COL_TILE);
 #pragma unroll
     for (int k = 0; k < BC / 16; ++k)
-      tc::umma_bf16(tm_dv, tc::make_smem_desc(sPT + k * 32, 16, 1024, tc::SWIZZLE_128B),
+      tc::umma_bf16(tm_dv, tc::make_smem_desc(sPT + k * 32, 16, 8 * C_::A_ROW, C_::A_LT),
                     tc::make_smem_desc(sDO + k * 16 * C_::SW, 16, 8 * C_::SW, C_::LT), idesc_g, (i > 0 || k > 0));
 #pragma unroll
     for (int k = 0; k < BC / 16; ++k)
-      tc::umma_bf16(tm_dk, tc::make_smem_desc(sDST + k * 32, 16, 1024, tc::SWIZZLE_128B),
+      tc::umma_bf16(tm_dk, tc::make_smem_desc(sDST + k * 32, 16, 8 * C_::A_ROW, C_::A_LT),
                     tc::make_smem_desc(sQ + k * 16 * C_::SW, 16, 8 * C_::SW, C_::LT), idesc_g, (i > 0 || k > 0));
     tc::umma_commit(bar_o);
   };
@@ -98,24 +99,39 @@ __global__ void __launch_bounds__(128) attn_bwd_dkdv_kernel(const __grid_constan
   const int row = rt * BR + tid;           // key row owned by this thread
   const bool row_ok = row < N;
   const float c = args.scale_log2, sc = args.scale;
-  uint8_t* pt_row = smem + OFF_PT + tid * 128;
-  uint8_t* dst_row = smem + OFF_DST + tid * 128;
+  uint8_t* pt_row = smem + OFF_PT + tid * C_::A_ROW;
+  uint8_t* dst_row = smem + OFF_DST + tid * C_::A_ROW;
   const size_t stat_base = (static_cast<size_t>(b) * H + h) * N;
+
+  // per-query statistics (log2-domain lse, delta * scale) of tile i live in s_stat[i & 1]; the global loads of tile
+  // i + 1 are issued at the top of iteration i and land in shared memory at its end, so no iteration waits on HBM
+  float n_lse = 0.f, n_delta = 0.f;
+  auto fetch_stats = [&](int i) {
+    const int q = i * BC + tid;
+    const bool ok = tid < BC && q < N;
+    n_lse = ok ? args.lse[stat_base + q] * 1.4426950408889634f : 0.f;
+    n_delta = ok ? args.delta[stat_base + q] * sc : 0.f;      // delta pre-multiplied by the score scale
+  };
+  auto put_stats = [&](int i) {
+    if (tid < BC) {
+      float* d = s_stat + (i & 1) * 2 * BC;
+      d[tid] = n_lse;
+      d[BC + tid] = n_delta;
+    }
+  };
+  fetch_stats(0);
+  put_stats(0);
+  __syncthreads();
 
   for (int i = 0; i < c_tiles; ++i) {
     float* st = s_stat + (i & 1) * 2 * BC;
-    if (tid < BC) {
-      const int q = i * BC + tid;
-      st[tid] = q < N ? args.lse[stat_base + q] * 1.4426950408889634f : 0.f;
-      st[BC + tid] = q < N ? args.delta[stat_base + q] * sc : 0.f;      // delta pre-multiplied by the score scale
-    }
+    if (i + 1 < c_tiles) fetch_stats(i + 1);
     tc::mbar_wait(bar_s, i & 1);
     tc::tc_fence_after();
     if (i > 0) {
       tc::mbar_wait(bar_o, (i - 1) & 1);   // gradient MMAs of tile i-1 done: P^T / dS^T buffers, Q/dO stage free
       if (tid == 0 && i + 1 < c_tiles) load_q(i + 1);
     }
-    __syncthreads();                        // s_stat visible
     // P^T and dS^T.  No masks: queries past N are zero rows of Q and dO (TMA zero fill), so their columns multiply
     // zero rows in dV += P^T dO and dK += dS^T Q; key rows past N are never stored.  st[] holds finite values there.
 #pragma unroll
@@ -148,10 +164,11 @@ __global__ void __launch_bounds__(128) attn_bwd_dkdv_kernel(const __grid_constan
           wp[k2] = *reinterpret_cast<uint32_t*>(&hp);
           wd[k2] = *reinterpret_cast<uint32_t*>(&hd);
         }
-        store_a_chunk(pt_row, tid, ch * 4 + v8, wp);
-        store_a_chunk(dst_row, tid, ch * 4 + v8, wd);
+        store_a_chunk<BC>(pt_row, tid, ch * 4 + v8, wp);
+        store_a_chunk<BC>(dst_row, tid, ch * 4 + v8, wd);
       }
     }
+    if (i + 1 < c_tiles) put_stats(i + 1);
     tc::fence_proxy_async();
     tc::tc_fence_before();
     __syncthreads();
@@ -188,7 +205,7 @@ __global__ void __launch_bounds__(128) attn_bwd_dkdv_kernel(const __grid_constan
   }
   tc::tc_fence_before();
   __syncthreads();
-  if (warp == 0) tc::tmem_dealloc(tmem_base, 256);
+  if (warp == 0) tc::tmem_dealloc(tmem_base, C_::TMEM_DKDV);
 }
 
 int tmap3(CUtensorMap* tm, const void* base, int Bn, int N, int cols, int DH, int box_rows) {
@@ -205,9 +222,9 @@ int launch_bwd(const void* qkv, const void* o, const void* d_o, const float* lse
   CUtensorMap q128, q64, do128, do64;
   int rc;
   if ((rc = tmap3(&q128, qkv, Bn, N, 3 * H * DH, DH, BR)) != 0) return rc;
-  if ((rc = tmap3(&q64, qkv, Bn, N, 3 * H * DH, DH, BC)) != 0) return rc;
+  if ((rc = tmap3(&q64, qkv, Bn, N, 3 * H * DH, DH, C_::BC)) != 0) return rc;
   if ((rc = tmap3(&do128, d_o, Bn, N, H * DH, DH, BR)) != 0) return rc;
-  if ((rc = tmap3(&do64, d_o, Bn, N, H * DH, DH, BC)) != 0) return rc;
+  if ((rc = tmap3(&do64, d_o, Bn, N, H * DH, DH, C_::BC)) != 0) return rc;
   BwdArgs a;
   a.o = static_cast<const bf16*>(o);
   a.d_o = static_cast<const bf16*>(d_o);
@@ -219,7 +236,7 @@ int launch_bwd(const void* qkv, const void* o, const void* d_o, const float* lse
   a.scale = 1.0f / sqrtf(static_cast<float>(DH));
   a.scale_log2 = a.scale * 1.4426950408889634f;
   constexpr int SMEM_DQ = 2 * C_::ROW_TILE + 4 * C_::COL_TILE + C_::A_TILE + 128 + 1024;
-  constexpr int SMEM_DKDV = 2 * C_::ROW_TILE + 4 * C_::COL_TILE + 2 * C_::A_TILE + 2 * 2 * BC * 4 + 128 + 1024;
+  constexpr int SMEM_DKDV = 2 * C_::ROW_TILE + 4 * C_::COL_TILE + 2 * C_::A_TILE + 2 * 2 * C_::BC * 4 + 128 + 1024;
   static bool attr = false;
   if (!attr) {
     cudaFuncSetAttribute(attn_bwd_dq_kernel<DH>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_DQ);

@@ -13,14 +13,20 @@
 namespace {
 
 constexpr int BR = 128;  // rows owned by the CTA (TMEM lanes)
-constexpr int BC = 64;   // columns per inner tile
 
 template <int DH> struct BCfg {
+  // columns per inner tile: 32 for dh <= 32 so that every TMEM accumulator of a CTA fits 128 columns and 4 CTAs share
+  // an SM (the exp-bound decoder case), 64 for dh = 64
+  static constexpr int BC = DH <= 32 ? 32 : 64;
   static constexpr int SW = DH * 2;
   static constexpr int ROW_TILE = BR * DH * 2;   // [128, DH]
-  static constexpr int COL_TILE = BC * DH * 2;   // [64, DH]
-  static constexpr int A_TILE = BR * BC * 2;     // [128, 64] bf16 written by the threads (K-major, SW128)
+  static constexpr int COL_TILE = BC * DH * 2;   // [BC, DH]
+  static constexpr int A_ROW = BC * 2;           // row bytes of the [128, BC] bf16 tiles written by the threads
+  static constexpr int A_TILE = BR * A_ROW;      // K-major, swizzle span = row bytes (128 B or 64 B)
   static constexpr uint32_t LT = tc::layout_type_for(SW);
+  static constexpr uint32_t A_LT = tc::layout_type_for(A_ROW);
+  static constexpr int TMEM_DQ = (2 * BC + DH <= 128) ? 128 : 256;
+  static constexpr int TMEM_DKDV = (2 * BC + 2 * DH <= 128) ? 128 : 256;
 };
 
 struct BwdArgs {
@@ -33,8 +39,12 @@ struct BwdArgs {
   float scale, scale_log2;
 };
 
+// 16-byte chunk c16 of row `tid` of a K-major [128, BCc] tile whose swizzle span equals its row (128 B: chunk ^ row % 8;
+// 64 B: chunk ^ (row / 2) % 4)
+template <int BCc>
 __device__ __forceinline__ void store_a_chunk(uint8_t* row_base, int tid, int c16, const uint32_t* w) {
-  *reinterpret_cast<uint4*>(row_base + ((c16 ^ (tid & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
+  const int x = BCc == 64 ? (tid & 7) : ((tid >> 1) & 3);
+  *reinterpret_cast<uint4*>(row_base + ((c16 ^ x) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
 }
 
 // ------------------------------------------------------------------------------------------------ dQ
@@ -43,6 +53,7 @@ __global__ void __launch_bounds__(128) attn_bwd_dq_kernel(const __grid_constant_
                                                           const __grid_constant__ CUtensorMap tm_qkv64,
                                                           const __grid_constant__ CUtensorMap tm_do128, BwdArgs args) {
   using C_ = BCfg<DH>;
+  constexpr int BC = C_::BC;
   constexpr int OFF_Q = 0, OFF_DO = C_::ROW_TILE, OFF_K = 2 * C_::ROW_TILE, OFF_V = OFF_K + 2 * C_::COL_TILE;
   constexpr int OFF_DS = OFF_V + 2 * C_::COL_TILE, OFF_BAR = OFF_DS + C_::A_TILE;
   extern __shared__ uint8_t smem_raw[];
@@ -69,14 +80,14 @@ __global__ void __launch_bounds__(128) attn_bwd_dq_kernel(const __grid_constant_
     tc::fence_barrier_init();
   }
   if (warp == 0) {
-    tc::tmem_alloc(tmem_ptr, 256);
+    tc::tmem_alloc(tmem_ptr, C_::TMEM_DQ);
     tc::tmem_relinquish();
   }
   tc::tc_fence_before();
   __syncthreads();
   tc::tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
-  const uint32_t tm_s = tmem_base, tm_dp = tmem_base + 64, tm_dq = tmem_base + 128;
+  const uint32_t tm_s = tmem_base, tm_dp = tmem_base + BC, tm_dq = tmem_base + 2 * BC;
   const uint32_t lane_base = static_cast<uint32_t>(warp * 32) << 16;
   constexpr uint32_t idesc_s = tc::make_idesc_bf16(BR, BC, 0, 0);
   constexpr uint32_t idesc_dq = tc::make_idesc_bf16(BR, DH, 0, 1);
@@ -105,7 +116,7 @@ __global__ void __launch_bounds__(128) attn_bwd_dq_kernel(const __grid_constant_
     const uint32_t sK = tc::smem_u32(smem + OFF_K + (j & 1) * C_::COL_TILE);
 #pragma unroll
     for (int k = 0; k < BC / 16; ++k)
-      tc::umma_bf16(tm_dq, tc::make_smem_desc(sDS + k * 32, 16, 1024, tc::SWIZZLE_128B),
+      tc::umma_bf16(tm_dq, tc::make_smem_desc(sDS + k * 32, 16, 8 * C_::A_ROW, C_::A_LT),
                     tc::make_smem_desc(sK + k * 16 * C_::SW, 16, 8 * C_::SW, C_::LT), idesc_dq, (j > 0 || k > 0));
     tc::umma_commit(bar_o);
   };
@@ -142,7 +153,7 @@ __global__ void __launch_bounds__(128) attn_bwd_dq_kernel(const __grid_constant_
   }
   const float c = args.scale_log2, sc = args.scale;
   const float delta_sc = delta * sc;
-  uint8_t* ds_row = smem + OFF_DS + tid * 128;
+  uint8_t* ds_row = smem + OFF_DS + tid * C_::A_ROW;
 
   for (int j = 0; j < c_tiles; ++j) {
     tc::mbar_wait(bar_s, j & 1);
@@ -174,7 +185,7 @@ __global__ void __launch_bounds__(128) attn_bwd_dq_kernel(const __grid_constant_
           __nv_bfloat162 hb = __floats2bfloat162_rn(d2[0], d2[1]);
           w[i] = *reinterpret_cast<uint32_t*>(&hb);
         }
-        store_a_chunk(ds_row, tid, ch * 4 + v8, w);
+        store_a_chunk<BC>(ds_row, tid, ch * 4 + v8, w);
       }
     }
     tc::fence_proxy_async();
@@ -212,7 +223,7 @@ __global__ void __launch_bounds__(128) attn_bwd_dq_kernel(const __grid_constant_
   }
   tc::tc_fence_before();
   __syncthreads();
-  if (warp == 0) tc::tmem_dealloc(tmem_base, 256);
+  if (warp == 0) tc::tmem_dealloc(tmem_base, C_::TMEM_DQ);
 }
 
 }  // namespace
