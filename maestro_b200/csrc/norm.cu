@@ -194,17 +194,19 @@ layernorm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x, const fl
     if (idx < nvec) {
 #pragma unroll
       for (int j = 0; j < V; ++j) {
-        atomicAdd(&sm[idx * V + j], ag[c * V + j]);
-        atomicAdd(&sm[d + idx * V + j], ab[c * V + j]);
-        if (dbias != nullptr) atomicAdd(&sm[2 * d + idx * V + j], ac[c * V + j]);
+        // column (idx * V + j) lives at [j * nvec + idx]: consecutive lanes -> consecutive banks (conflict-free red)
+        atomicAdd(&sm[j * nvec + idx], ag[c * V + j]);
+        atomicAdd(&sm[d + j * nvec + idx], ab[c * V + j]);
+        if (dbias != nullptr) atomicAdd(&sm[2 * d + j * nvec + idx], ac[c * V + j]);
       }
     }
   }
   __syncthreads();
   for (int i = threadIdx.x; i < d; i += blockDim.x) {
-    atomicAdd(dgamma + i, sm[i]);
-    atomicAdd(dbeta + i, sm[d + i]);
-    if (dbias != nullptr) atomicAdd(dbias + i, sm[2 * d + i]);
+    const int si = (i % V) * nvec + i / V;
+    atomicAdd(dgamma + i, sm[si]);
+    atomicAdd(dbeta + i, sm[d + si]);
+    if (dbias != nullptr) atomicAdd(dbias + i, sm[2 * d + si]);
   }
 }
 
