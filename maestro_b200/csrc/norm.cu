@@ -216,7 +216,9 @@ static int launch_ln_bwd(const void* dy, const void* x, const float* mean, const
                          RowMap im, RowMap om, cudaStream_t st) {
   constexpr int V = VecIO<T>::N;
   const int nwarps = LNB_THREADS / 32;
-  int blocks = mb_ceil_div(rows, nwarps);
+  // at least 4 rows per warp before the per-CTA reduction tail pays off; small groups then leave SMs to the
+  // other groups' kernels that run concurrently on forked streams
+  int blocks = mb_ceil_div(rows, nwarps * 4);
   if (blocks > 148) blocks = 148;
   const size_t smem = 3 * static_cast<size_t>(d) * sizeof(float);
   const int nch = mb_ceil_div(d / V, 32);

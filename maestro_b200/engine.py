@@ -159,6 +159,8 @@ class PretrainEngine:
         # "flash": fused tcgen05 attention (bf16, dh in {16, 32, 64}); "gemm": materialised scores (fp32 check mode)
         flash_ok = dtype == torch.bfloat16 and all(d in (16, 32, 64) for d in (hp["dim_head"], hp["decoder_dim_head"]))
         self.attn_impl = "flash" if flash_ok else "gemm"
+        self.multi_stream = self.device.type == "cuda" and self.attn_impl == "flash"
+        self._streams: list = []
         self._build_tables(fac_abs_enc)
         self._build_params()
 
@@ -313,18 +315,19 @@ class PretrainEngine:
         Accumulates dW (token contraction, split-K) and dbias; optionally dx[M, Kd] = dy[M, N] @ W (times
         gelu'(aux)), the weight read in place as an MN-major operand (no transposed copy).
         """
-        wg, dg = [], []
+        wg, dg, cs = [], [], []
         for dy, M, x, wname, bname, dx, dgelu_aux in items:
             shp = self.arena.shapes[wname]
             N, Kd = shp[0], self.P[wname].numel() // shp[0]
             if bname:
-                self.K.colsum_accum(dy, self.G[bname])
+                cs.append(lambda dy=dy, bname=bname: self.K.colsum_accum(dy, self.G[bname]))
             # dW[n, k] += sum_m dy[m, n] * x[m, k]   (contraction over tokens)
             wg.append(((dy, x, self.G[wname], N, Kd, M), dict(sam=1, sak=N, sbn=1, sbk=Kd, ldc=Kd, flags=GEMM_ACCUM)))
             if dx is not None:
                 dg.append(((dy, self._w(wname), dx, M, Kd, N),
                            dict(sam=N, sak=1, sbn=1, sbk=Kd, ldc=Kd, aux=dgelu_aux,
                                 flags=GEMM_DGELU if dgelu_aux is not None else 0)))
+        self._par(cs)
         self.K.gemm_grouped(wg)
         if dg:
             self.K.gemm_grouped(dg)
@@ -334,6 +337,32 @@ class PretrainEngine:
 
     def lin_bwd(self, dy, M, x, wname, bname, dx=None, dgelu_aux=None):
         self.lin_bwd_g([(dy, M, x, wname, bname, dx, dgelu_aux)])
+
+    # ------------------------------------------------------------------ concurrency of per-group kernels
+    def _par(self, fns) -> None:
+        """Run independent launches (one per group) on side streams, forked from and joined into the current stream.
+
+        The per-group LayerNorm / attention kernels are too small to fill 148 SMs one at a time (e.g. 1600 rows);
+        inside a CUDA-graph capture the fork / join becomes parallel graph branches.  Callers allocate every output
+        on the current stream BEFORE calling (the caching allocator tracks blocks per stream).
+        """
+        if not self.multi_stream or len(fns) < 2:
+            for f in fns:
+                f()
+            return
+        main = torch.cuda.current_stream(self.device)
+        while len(self._streams) < len(fns) - 1:
+            self._streams.append(torch.cuda.Stream(device=self.device))
+        fork = torch.cuda.Event()
+        fork.record(main)
+        fns[0]()                                      # the largest group stays on the main stream
+        for f, st in zip(fns[1:], self._streams):
+            st.wait_event(fork)
+            with torch.cuda.stream(st):
+                f()
+            join = torch.cuda.Event()
+            join.record(st)
+            main.wait_event(join)
 
     # ------------------------------------------------------------------ attention
     def attn_fwd(self, qkv, Bn, N, H, dh):
@@ -394,25 +423,28 @@ class PretrainEngine:
         h1 = [self._new(r, dim) for r in rows]
         m1 = [self._new(r, dtype=f32) for r in rows]
         r1 = [self._new(r, dtype=f32) for r in rows]
-        for i in range(n):
-            K.layernorm_fwd(xs[i], P[pres[i] + "0.norm.weight"], P[pres[i] + "0.norm.bias"], h1[i], m1[i], r1[i],
-                            rows[i], dim)
+        self._par([lambda i=i: K.layernorm_fwd(xs[i], P[pres[i] + "0.norm.weight"], P[pres[i] + "0.norm.bias"], h1[i],
+                                               m1[i], r1[i], rows[i], dim) for i in range(n)])
         qkv = [self._new(r, 3 * inner) for r in rows]
         self.lin_fwd_g([(h1[i], rows[i], pres[i] + "0.to_qkv.weight", None, qkv[i], None, None) for i in range(n)])
-        o, att = [], []
-        for i in range(n):
-            oi, ai = self.attn_fwd(qkv[i], Bn, Ns[i], H, dh)
-            o.append(oi)
-            att.append(ai)
+        if self.attn_impl == "flash":
+            o = [self._new(r, inner) for r in rows]
+            att = [self._new(Bn, H, N, dtype=f32) for N in Ns]          # log-sum-exp per (sample, head, query)
+            self._par([lambda i=i: K.attn_fwd(qkv[i], o[i], att[i], Bn, Ns[i], H, dh) for i in range(n)])
+        else:
+            o, att = [], []
+            for i in range(n):
+                oi, ai = self.attn_fwd(qkv[i], Bn, Ns[i], H, dh)
+                o.append(oi)
+                att.append(ai)
         x2 = [self._new(r, dim) for r in rows]
         self.lin_fwd_g([(o[i], rows[i], pres[i] + "0.to_out.0.weight", pres[i] + "0.to_out.0.bias", x2[i], None, xs[i])
                         for i in range(n)])
         h2 = [self._new(r, dim) for r in rows]
         m2 = [self._new(r, dtype=f32) for r in rows]
         r2 = [self._new(r, dtype=f32) for r in rows]
-        for i in range(n):
-            K.layernorm_fwd(x2[i], P[pres[i] + "1.net.0.weight"], P[pres[i] + "1.net.0.bias"], h2[i], m2[i], r2[i],
-                            rows[i], dim)
+        self._par([lambda i=i: K.layernorm_fwd(x2[i], P[pres[i] + "1.net.0.weight"], P[pres[i] + "1.net.0.bias"], h2[i],
+                                               m2[i], r2[i], rows[i], dim) for i in range(n)])
         u = [self._new(r, mlp) for r in rows]
         a = [self._new(r, mlp) for r in rows]
         self.lin_fwd_g([(h2[i], rows[i], pres[i] + "1.net.1.weight", pres[i] + "1.net.1.bias", a[i], u[i], None)
@@ -439,20 +471,24 @@ class PretrainEngine:
                         for i in range(n)])
         del du
         dx2 = [self._new(r, dim) for r in rows]
-        for i in range(n):
-            K.layernorm_bwd(dh2[i], x2[i], m2[i], r2[i], P[pres[i] + "1.net.0.weight"], dx3[i], dx2[i],
-                            G[pres[i] + "1.net.0.weight"], G[pres[i] + "1.net.0.bias"], rows[i], dim,
-                            dbias=G[pres[i] + "0.to_out.0.bias"])
+        self._par([lambda i=i: K.layernorm_bwd(dh2[i], x2[i], m2[i], r2[i], P[pres[i] + "1.net.0.weight"], dx3[i], dx2[i],
+                                               G[pres[i] + "1.net.0.weight"], G[pres[i] + "1.net.0.bias"], rows[i], dim,
+                                               dbias=G[pres[i] + "0.to_out.0.bias"]) for i in range(n)])
         do = [self._new(r, inner) for r in rows]
         self.lin_bwd_g([(dx2[i], rows[i], o[i], pres[i] + "0.to_out.0.weight", None, do[i], None) for i in range(n)])
-        dqkv = [self.attn_bwd(do[i], qkv[i], att[i], Bn, Ns[i], H, dh, o=o[i]) for i in range(n)]
+        if self.attn_impl == "flash":
+            dqkv = [self._new(r, 3 * inner) for r in rows]
+            delta = [self._new(Bn, H, N, dtype=torch.float32) for N in Ns]
+            self._par([lambda i=i: K.attn_bwd(qkv[i], o[i], do[i], att[i], dqkv[i], delta[i], Bn, Ns[i], H, dh)
+                       for i in range(n)])
+        else:
+            dqkv = [self.attn_bwd(do[i], qkv[i], att[i], Bn, Ns[i], H, dh, o=o[i]) for i in range(n)]
         dh1 = dh2  # reuse
         self.lin_bwd_g([(dqkv[i], rows[i], h1[i], pres[i] + "0.to_qkv.weight", None, dh1[i], None) for i in range(n)])
         dx = [self._new(r, dim) for r in rows]
-        for i in range(n):
-            K.layernorm_bwd(dh1[i], x[i], m1[i], r1[i], P[pres[i] + "0.norm.weight"], dx2[i], dx[i],
-                            G[pres[i] + "0.norm.weight"], G[pres[i] + "0.norm.bias"], rows[i], dim,
-                            dbias=sinks[i] if sinks is not None else None)
+        self._par([lambda i=i: K.layernorm_bwd(dh1[i], x[i], m1[i], r1[i], P[pres[i] + "0.norm.weight"], dx2[i], dx[i],
+                                               G[pres[i] + "0.norm.weight"], G[pres[i] + "0.norm.bias"], rows[i], dim,
+                                               dbias=sinks[i] if sinks is not None else None) for i in range(n)])
         return dx
 
     def stacks_fwd(self, prefixes, xs, Bn, Ns, dim, depth, H, dh, mlp):
