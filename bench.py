@@ -154,6 +154,11 @@ def run_ours(args):
 
     rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    # libraries (NCCL prints its version banner on stdout) must not pollute the one-JSON-line contract: route fd 1 to
+    # stderr until the line is printed
+    sys.stdout.flush()
+    saved_stdout = os.dup(1)
+    os.dup2(2, 1)
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
@@ -204,10 +209,18 @@ def run_ours(args):
         opt.step(grad_scale=reducer.grad_scale)
         return loss
 
+    prefetched = [False]
+
     def step_e2e(i):
         hb = host[i % 2]
         if use_graph:
-            gstep.load(hb)
+            # input pipeline: the H2D copy of step i + 1 (pinned host memory -> staging) runs on a copy stream while
+            # step i computes; every step's inputs cross PCIe exactly once, inside the timed region
+            if not prefetched[0]:
+                gstep.prefetch(hb)
+                prefetched[0] = True
+            gstep.load_prefetched()
+            gstep.prefetch(host[(i + 1) % 2])
             loss = step_device(devb, staged=True)
         else:
             for k, v in hb.items():
@@ -304,7 +317,8 @@ def run_ours(args):
                    "l2": "inputs larger than L2 (activations >> 126 MB per step); no flush",
                    "attention": eng.attn_impl, "loss_last": last_loss,
                    "launch": "cuda-graph replay" if use_graph else "python",
-                   "allreduce_bytes_per_step": reducer.bytes_per_step},
+                   "allreduce_bytes_per_step": reducer.bytes_per_step,
+                   "e2e_input_pipeline": "H2D of step i+1 on a copy stream overlaps step i; loss read back every step"},
         "e2e": {"value": B * world / (e2e_ms * 1e-3), "unit": "tiles/s", "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": 4, "ms_per_step": e2e_ms},
         "gpu_launches": launches,
@@ -322,6 +336,8 @@ def run_ours(args):
         "attention_gemm": {"tflops": at_fl / (at_ms * 1e-3) / 1e12 if at_ms > 0 else None, "ms": at_ms},
         "cpu_baseline": cpu,
     }
+    sys.stdout.flush()
+    os.dup2(saved_stdout, 1)
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

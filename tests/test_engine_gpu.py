@@ -106,4 +106,12 @@ def test_graphed_step_matches_eager(K, segments):
         cos = torch.nn.functional.cosine_similarity(eng.arena.grad, g_eager, dim=0)
         assert float(cos) > 0.9999, float(cos)
     assert abs(loss_graph - float(gold["loss"])) <= 2e-2 * abs(float(gold["loss"]))
+    # overlapped input pipeline: pinned host batch -> staging (copy stream) -> static buffers
+    pinned = {k: v.clone().pin_memory() for k, v in batch.items()}
+    gs.prefetch(pinned)
+    gs.load_prefetched(struct)
+    eng.zero_grad()
+    loss_pf = float(gs.replay())
+    torch.cuda.synchronize()
+    assert abs(loss_pf - loss_eager) <= 1e-3 * abs(loss_eager)
     assert eng.grad_ranges()[0][0] == 0 and eng.grad_ranges()[-1][1] == eng.arena.numel
