@@ -122,6 +122,8 @@ typedef struct {
   long long a_s1, a_s2, b_s1, b_s2, c_s1, c_s2;
   float alpha;
   int flags;
+  float* colsum;         /* optional [N] fp32, accumulates the column sums of C (bias gradient of the layer whose dY
+                            this GEMM produces, e.g. FeedForward up-projection bias from dgrad + GELU'); mb_gemm_tc* only */
 } mb_gemm_params;                   /* `params` below is a HOST pointer */
 /* nn.Linear / nn.Conv2d(k=p,s=p) / 1x1 conv and their autograd (vit_pytorch to_qkv / to_out / FeedForward,
  * maestro/layers/embed.py:59-60,148-154, maestro/ssl/mae.py:145-154) on the CUDA cores: fp32 check mode. */

@@ -64,7 +64,7 @@ class GemmParams(C.Structure):
         ("ldc", C.c_int), ("nb1", C.c_int), ("nb2", C.c_int),
         ("a_s1", C.c_longlong), ("a_s2", C.c_longlong), ("b_s1", C.c_longlong), ("b_s2", C.c_longlong),
         ("c_s1", C.c_longlong), ("c_s2", C.c_longlong),
-        ("alpha", C.c_float), ("flags", C.c_int),
+        ("alpha", C.c_float), ("flags", C.c_int), ("colsum", C.c_void_p),
     ]
 
 

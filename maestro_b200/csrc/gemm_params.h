@@ -21,4 +21,5 @@ struct GemmParams {
   long long a_s1, a_s2, b_s1, b_s2, c_s1, c_s2;
   float alpha;
   int flags;
+  float* colsum;         // optional [N] fp32: colsum[n] += sum_m C[m, n] (the rounded outputs), tensor-core path only
 };

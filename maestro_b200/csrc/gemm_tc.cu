@@ -52,6 +52,7 @@ struct TcProblem {
   const float* bias;
   const void* residual;
   void* aux;
+  float* colsum;
   int M, N, K, ldc;
   int splits;
   int mblocks, nblocks;
@@ -387,6 +388,24 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
             tc::tma_store_2d(&maps.c[tc_.p], stg, col0, row0);
             tc::tma_store_commit();
           }
+          // (8) optional column sums of the rounded outputs (bias gradient of the layer that produced this dY): lane
+          // l walks column l of the staged 32 x 32 chunk (one conflict-free 64-byte row segment per step)
+          if (P.colsum != nullptr) {
+            const int nrows = min(32, P.M - row0);
+            const uint32_t cbase = stg_u32 + (lane & 7) * 2;
+            const uint32_t cj = static_cast<uint32_t>(lane >> 3);
+            float cs0 = 0.f, cs1 = 0.f;
+#pragma unroll 8
+            for (int rr = 0; rr < 32; rr += 2) {
+              uint16_t h0, h1;
+              const uint32_t a0 = cbase + rr * 64 + ((cj ^ ((rr >> 1) & 3)) << 4);
+              asm volatile("ld.shared.u16 %0, [%1];" : "=h"(h0) : "r"(a0) : "memory");
+              asm volatile("ld.shared.u16 %0, [%1];" : "=h"(h1) : "r"(a0 + 64) : "memory");
+              if (rr < nrows) cs0 += __uint_as_float(static_cast<uint32_t>(h0) << 16);
+              if (rr + 1 < nrows) cs1 += __uint_as_float(static_cast<uint32_t>(h1) << 16);
+            }
+            if (nrows > 0 && col0 + lane < P.N) atomicAdd(P.colsum + col0 + lane, cs0 + cs1);
+          }
         }
       } else if (nch > 0) {
         // ---------------- fp32 outputs (gradient accumulation): direct 16-byte stores / red.add ----------------
@@ -481,7 +500,7 @@ int launch(const GemmParams* Ps, int count, cudaStream_t st) {
       maps.pf[i] = maps.a[i];
     }
     TcProblem& q = a.p[i];
-    q.C = P.C; q.bias = P.bias; q.residual = P.residual; q.aux = P.aux;
+    q.C = P.C; q.bias = P.bias; q.residual = P.residual; q.aux = P.aux; q.colsum = P.colsum;
     q.M = P.M; q.N = P.N; q.K = P.K; q.ldc = P.ldc;
     q.mblocks = (P.M + BM - 1) / BM;
     q.nblocks = (P.N + BN - 1) / BN;

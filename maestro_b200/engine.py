@@ -316,7 +316,9 @@ class PretrainEngine:
         gelu'(aux)), the weight read in place as an MN-major operand (no transposed copy).
         """
         wg, dg, cs = [], [], []
-        for dy, M, x, wname, bname, dx, dgelu_aux in items:
+        for it in items:
+            dy, M, x, wname, bname, dx, dgelu_aux = it[:7]
+            dx_colsum = it[7] if len(it) > 7 else None      # receives colsum(dx): bias gradient of the layer below
             shp = self.arena.shapes[wname]
             N, Kd = shp[0], self.P[wname].numel() // shp[0]
             if bname:
@@ -325,7 +327,7 @@ class PretrainEngine:
             wg.append(((dy, x, self.G[wname], N, Kd, M), dict(sam=1, sak=N, sbn=1, sbk=Kd, ldc=Kd, flags=GEMM_ACCUM)))
             if dx is not None:
                 dg.append(((dy, self._w(wname), dx, M, Kd, N),
-                           dict(sam=N, sak=1, sbn=1, sbk=Kd, ldc=Kd, aux=dgelu_aux,
+                           dict(sam=N, sak=1, sbn=1, sbk=Kd, ldc=Kd, aux=dgelu_aux, colsum=dx_colsum,
                                 flags=GEMM_DGELU if dgelu_aux is not None else 0)))
         self._par(cs)
         self.K.gemm_grouped(wg)
@@ -465,10 +467,11 @@ class PretrainEngine:
         du = [self._new(r, mlp) for r in rows]
         # the bias gradients of net.4 / to_out are column sums of dx3 / dx2: they ride on the LayerNorm backward that
         # produced those tensors (``dbias``), see ``bias_sink``
-        self.lin_bwd_g([(dx3[i], rows[i], a[i], pres[i] + "1.net.4.weight", None, du[i], u[i]) for i in range(n)])
+        # ... and the up-projection bias gradient (colsum of du) on the GELU' epilogue of the dgrad GEMM that writes du
+        self.lin_bwd_g([(dx3[i], rows[i], a[i], pres[i] + "1.net.4.weight", None, du[i], u[i],
+                         G[pres[i] + "1.net.1.bias"]) for i in range(n)])
         dh2 = [self._new(r, dim) for r in rows]
-        self.lin_bwd_g([(du[i], rows[i], h2[i], pres[i] + "1.net.1.weight", pres[i] + "1.net.1.bias", dh2[i], None)
-                        for i in range(n)])
+        self.lin_bwd_g([(du[i], rows[i], h2[i], pres[i] + "1.net.1.weight", None, dh2[i], None) for i in range(n)])
         del du
         dx2 = [self._new(r, dim) for r in rows]
         self._par([lambda i=i: K.layernorm_bwd(dh2[i], x2[i], m2[i], r2[i], P[pres[i] + "1.net.0.weight"], dx3[i], dx2[i],

@@ -191,7 +191,8 @@ class Kernels:
 
     # ------------------------------------------------------------------ GEMM
     def _gemm_params(self, A, B, Cm, M, N, K, sam, sak, sbn, sbk, ldc, bias=None, residual=None, aux=None, flags=0,
-                     alpha=1.0, nb1=1, nb2=1, a_s=(0, 0), b_s=(0, 0), c_s=(0, 0), a_off=0, b_off=0, c_off=0):
+                     alpha=1.0, nb1=1, nb2=1, a_s=(0, 0), b_s=(0, 0), c_s=(0, 0), a_off=0, b_off=0, c_off=0,
+                     colsum=None):
         if not (A.is_cuda and B.is_cuda and Cm.is_cuda):
             raise RuntimeError("maestro_b200 kernels need CUDA tensors (there is no CPU fallback)")
         P = _lib.GemmParams()
@@ -208,6 +209,7 @@ class Kernels:
         P.b_s1, P.b_s2 = b_s
         P.c_s1, P.c_s2 = c_s
         P.alpha = alpha
+        P.colsum = colsum.data_ptr() if colsum is not None else None
         if Cm.dtype == torch.float32 and A.dtype != torch.float32:
             flags |= GEMM_OUT_F32
         P.flags = flags
@@ -216,7 +218,8 @@ class Kernels:
         tc_ok = (self.use_tc and A.dtype == torch.bfloat16 and nb1 == 1 and nb2 == 1 and N % 8 == 0 and ldc % 8 == 0
                  and ((a_k and (b_k or b_mn)) or (a_mn and not a_k and b_mn and not b_k))
                  and P.A % 16 == 0 and P.B % 16 == 0 and P.C % 16 == 0
-                 and (aux is None or P.aux % 16 == 0))
+                 and (aux is None or P.aux % 16 == 0)
+                 and (colsum is None or Cm.dtype == torch.bfloat16))
         return P, tc_ok
 
     def gemm(self, A, B, Cm, M, N, K, sam, sak, sbn, sbk, ldc, **kw):
@@ -227,6 +230,12 @@ class Kernels:
             _ck(self.L.mb_gemm_tc(C.byref(P), _stream()), "gemm_tc")
         else:
             _ck(self.L.mb_gemm_simt(C.byref(P), _dt(A), _stream()), "gemm_simt")
+            self._simt_colsum(Cm, M, N, kw)
+
+    def _simt_colsum(self, Cm, M, N, kw):
+        """The CUDA-core GEMM has no fused column sum: run the standalone kernel on its output."""
+        if kw.get("colsum") is not None:
+            self.colsum_accum(Cm.view(-1)[:M * N].view(M, N), kw["colsum"])
 
     def gemm_grouped(self, problems):
         """Independent GEMMs of one layer kind (same layouts / flags, different operands) as ONE launch.
@@ -236,10 +245,11 @@ class Kernels:
         """
         built = [self._gemm_params(*a, **kw) for a, kw in problems]
         tc = [P for P, ok in built if ok]
-        for (P, ok), (a, _) in zip(built, problems):
+        for (P, ok), (a, _) in zip(built, problems):   # _ = kwargs of the problem
             if not ok:
                 self.launches += 1
                 _ck(self.L.mb_gemm_simt(C.byref(P), _dt(a[0]), _stream()), "gemm_simt")
+                self._simt_colsum(a[2], a[3], a[4], _)
         for i in range(0, len(tc), 4):
             chunk = tc[i:i + 4]
             arr = (_lib.GemmParams * len(chunk))(*chunk)

@@ -225,7 +225,8 @@ class FakeKernels:
 
     # ------------------------------------------------------------------ GEMM
     def gemm(self, A, B, Cm, M, N, K, sam, sak, sbn, sbk, ldc, bias=None, residual=None, aux=None, flags=0,
-             alpha=1.0, nb1=1, nb2=1, a_s=(0, 0), b_s=(0, 0), c_s=(0, 0), a_off=0, b_off=0, c_off=0):
+             alpha=1.0, nb1=1, nb2=1, a_s=(0, 0), b_s=(0, 0), c_s=(0, 0), a_off=0, b_off=0, c_off=0,
+             colsum=None):
         a = _strided(A, a_off, (nb1, nb2, M, K), (a_s[0], a_s[1], sam, sak)).float()
         b = _strided(B, b_off, (nb1, nb2, N, K), (b_s[0], b_s[1], sbn, sbk)).float()
         v = alpha * (a @ b.transpose(-1, -2))
@@ -246,6 +247,8 @@ class FakeKernels:
         if flags & GEMM_ACCUM:
             v = v + cv.float()
         cv.copy_(v.to(Cm.dtype))
+        if colsum is not None:
+            colsum += cv.float().reshape(-1, N).sum(0)
 
     def gemm_grouped(self, problems):
         for a, kw in problems:

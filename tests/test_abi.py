@@ -26,8 +26,8 @@ def test_library_exports_every_declared_symbol():
 
 def test_struct_mirrors_match_header_sizes():
     from maestro_b200 import _lib
-    # mb_gemm_params: 6 pointers, 3 ints (+pad), 4 int64, 3 ints (+pad), 6 int64, float, int
-    assert ctypes.sizeof(_lib.GemmParams) == 6 * 8 + 16 + 4 * 8 + 16 + 6 * 8 + 8
+    # mb_gemm_params: 6 pointers, 3 ints (+pad), 4 int64, 3 ints (+pad), 6 int64, float, int, pointer
+    assert ctypes.sizeof(_lib.GemmParams) == 6 * 8 + 16 + 4 * 8 + 16 + 6 * 8 + 8 + 8
     assert ctypes.sizeof(_lib.LossParams) % 8 == 0
 
 

@@ -354,9 +354,10 @@ def test_gemm_grouped_matches_single_launches(KK):
         outs += Y2
         dX = [torch.zeros(M, Kd, dtype=dt, device="cuda") for M in Ms]
         A2 = [rnd(M, Kd, dt=dt, seed=50 + i) for i, M in enumerate(Ms)]
+        cs = [torch.full((Kd,), 0.125, device="cuda") for _ in Ms]     # fused column sums of the GELU' outputs
         K.gemm_grouped([((R[i], W[i], dX[i], Ms[i], Kd, N), dict(sam=N, sak=1, sbn=1, sbk=Kd, ldc=Kd, aux=A2[i],
-                                                                flags=2)) for i in range(4)])
-        outs += dX
+                                                                flags=2, colsum=cs[i])) for i in range(4)])
+        outs += dX + cs
         dW = [torch.full((N, Kd), 0.25, dtype=torch.float32, device="cuda") for _ in Ms]
         K.gemm_grouped([((R[i], X[i], dW[i], N, Kd, Ms[i]), dict(sam=1, sak=N, sbn=1, sbk=Kd, ldc=Kd, flags=4))
                         for i in range(4)])
