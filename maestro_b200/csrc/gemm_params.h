@@ -6,6 +6,8 @@
 #define GEMM_DGELU 2     // out = acc * gelu'(aux)
 #define GEMM_ACCUM 4     // out += result (fp32 gradient accumulation)
 #define GEMM_OUT_F32 8   // C is fp32 regardless of the activation dtype
+#define GEMM_PAIR_ON 16  // scheduling hint (tensor-core path): force 2-CTA (cta_group::2) tiles
+#define GEMM_PAIR_OFF 32 // scheduling hint (tensor-core path): force single-CTA tiles
 
 struct GemmParams {
   const void* A;         // A(m, k) = A[m * sam + k * sak]

@@ -21,6 +21,7 @@
 #include <mutex>
 #include <unordered_map>
 #include <string>
+#include <cstdlib>
 #include <cstring>
 
 #include "common.cuh"
@@ -40,10 +41,13 @@ constexpr int EPI_WARPS = 16;
 constexpr int STG_BYTES = 32 * 32 * 2;   // one epilogue warp: 32 rows x 32 bf16 columns
 constexpr int MAX_GROUP = 4;
 
-template <int BN> struct Cfg {
-  static constexpr int B_BYTES = BN * BK * 2;
+// PAIR: two CTAs of a cluster (one TPC) run ONE 256 x BN tcgen05.mma.cta_group::2 tile; each CTA stages its own 128
+// rows of A and HALF of the B tile (BN / 2 rows), so a CTA pulls 32 KB instead of 48 KB per k-block into its SM.
+template <int BN, bool PAIR> struct Cfg {
+  static constexpr int B_ROWS = PAIR ? BN / 2 : BN;
+  static constexpr int B_BYTES = B_ROWS * BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int STAGES = (BN == 256) ? 4 : 6;
+  static constexpr int STAGES = PAIR ? ((BN == 256) ? 6 : 8) : ((BN == 256) ? 4 : 6);
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_WARPS * STG_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
 };
 
@@ -77,7 +81,9 @@ struct TileCoord {
   int p, m_blk, n_blk, kb0, kb1;
 };
 
-__device__ __forceinline__ TileCoord decode_tile(const TcArgs& args, int t, bool n_fastest) {
+// With PAIR `t` indexes PAIRS of vertically adjacent m-blocks: P.mblocks then holds the number of pairs and the CTA of
+// cluster rank r takes m-block 2 * pair + r.
+__device__ __forceinline__ TileCoord decode_tile(const TcArgs& args, int t, bool n_fastest, int mc_rank = -1) {
   TileCoord tc_;
   int p = 0, start = 0;
 #pragma unroll
@@ -97,6 +103,7 @@ __device__ __forceinline__ TileCoord decode_tile(const TcArgs& args, int t, bool
     tc_.n_blk = rem / P.mblocks;
     tc_.m_blk = rem - tc_.n_blk * P.mblocks;
   }
+  if (mc_rank >= 0) tc_.m_blk = 2 * tc_.m_blk + mc_rank;
   tc_.kb0 = split * per;
   tc_.kb1 = min(kblocks, tc_.kb0 + per);
   return tc_;
@@ -107,10 +114,10 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   return *reinterpret_cast<uint32_t*>(&h);
 }
 
-template <int BN, bool A_MN, bool B_MN>
+template <int BN, bool A_MN, bool B_MN, bool PAIR>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcArgs args) {
-  using C_ = Cfg<BN>;
+  using C_ = Cfg<BN, PAIR>;
   constexpr int STAGES = C_::STAGES;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
@@ -124,6 +131,10 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int total_tiles = args.total_tiles;
+  // PAIR: the two CTAs of a cluster walk the same (pair) tile sequence; rank 0 (the leader) issues the MMAs for both
+  const int mc_rank = PAIR ? static_cast<int>(tc::cluster_ctarank()) : -1;
+  const int tile0 = PAIR ? static_cast<int>(blockIdx.x >> 1) : static_cast<int>(blockIdx.x);
+  const int tile_step = PAIR ? static_cast<int>(gridDim.x >> 1) : static_cast<int>(gridDim.x);
 
   if (warp == 0 && lane == 0) {
     for (int i = 0; i < args.count; ++i) {
@@ -133,21 +144,27 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < STAGES; ++s) {
-      tc::mbar_init(&full_bar[s], 1);
+      tc::mbar_init(&full_bar[s], 1);                 // PAIR: only the leader's is used (both CTAs' loads count on it)
       tc::mbar_init(&empty_bar[s], 1);
     }
     for (int s = 0; s < 2; ++s) {
       tc::mbar_init(&tfull_bar[s], 1);
-      tc::mbar_init(&tempty_bar[s], EPI_WARPS * 32);
+      tc::mbar_init(&tempty_bar[s], (PAIR ? 2 : 1) * EPI_WARPS * 32);   // PAIR: the leader's collects both epilogues
     }
     tc::fence_barrier_init();
   }
   if (warp == 2) {
-    tc::tmem_alloc(tmem_ptr, 2 * BN);
-    tc::tmem_relinquish();
+    if constexpr (PAIR) {
+      tc::tmem_alloc_pair(tmem_ptr, 2 * BN);
+      tc::tmem_relinquish_pair();
+    } else {
+      tc::tmem_alloc(tmem_ptr, 2 * BN);
+      tc::tmem_relinquish();
+    }
   }
   tc::tc_fence_before();
   __syncthreads();
+  if constexpr (PAIR) tc::cluster_sync();             // the peer's barriers exist before anything arrives on them
   tc::tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
 
@@ -156,8 +173,8 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-        const TileCoord tc_ = decode_tile(args, t, !A_MN);
+      for (int t = tile0; t < total_tiles; t += tile_step) {
+        const TileCoord tc_ = decode_tile(args, t, !A_MN, mc_rank);
         const CUtensorMap* tmA = &maps.a[tc_.p];
         const CUtensorMap* tmB = &maps.b[tc_.p];
         {
@@ -174,20 +191,40 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
           tc::mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* sA = smem + stage * C_::STAGE_BYTES;
           uint8_t* sB = sA + A_BYTES;
-          tc::mbar_expect_tx(&full_bar[stage], C_::STAGE_BYTES);
-          if constexpr (!A_MN) {
-            tc::tma_load_2d(sA, tmA, &full_bar[stage], kb * BK, tc_.m_blk * BM);
-          } else {
+          if constexpr (!PAIR) {
+            tc::mbar_expect_tx(&full_bar[stage], C_::STAGE_BYTES);
+            if constexpr (!A_MN) {
+              tc::tma_load_2d(sA, tmA, &full_bar[stage], kb * BK, tc_.m_blk * BM);
+            } else {
 #pragma unroll
-            for (int i = 0; i < BM / 64; ++i)
-              tc::tma_load_2d(sA + i * 8192, tmA, &full_bar[stage], tc_.m_blk * BM + i * 64, kb * BK);
-          }
-          if constexpr (!B_MN) {
-            tc::tma_load_2d(sB, tmB, &full_bar[stage], kb * BK, tc_.n_blk * BN);
-          } else {
+              for (int i = 0; i < BM / 64; ++i)
+                tc::tma_load_2d(sA + i * 8192, tmA, &full_bar[stage], tc_.m_blk * BM + i * 64, kb * BK);
+            }
+            if constexpr (!B_MN) {
+              tc::tma_load_2d(sB, tmB, &full_bar[stage], kb * BK, tc_.n_blk * BN);
+            } else {
 #pragma unroll
-            for (int i = 0; i < BN / 64; ++i)
-              tc::tma_load_2d(sB + i * 8192, tmB, &full_bar[stage], tc_.n_blk * BN + i * 64, kb * BK);
+              for (int i = 0; i < BN / 64; ++i)
+                tc::tma_load_2d(sB + i * 8192, tmB, &full_bar[stage], tc_.n_blk * BN + i * 64, kb * BK);
+            }
+          } else {
+            // both CTAs' bytes are counted on the LEADER's full barrier (the leader alone waits on it and issues)
+            const uint32_t fb = tc::mapa_u32(&full_bar[stage], 0);
+            if (mc_rank == 0) tc::mbar_expect_tx(&full_bar[stage], 2 * C_::STAGE_BYTES);
+            if constexpr (!A_MN) {
+              tc::tma_load_2d_pair(sA, tmA, fb, kb * BK, tc_.m_blk * BM);
+            } else {
+#pragma unroll
+              for (int i = 0; i < BM / 64; ++i)
+                tc::tma_load_2d_pair(sA + i * 8192, tmA, fb, tc_.m_blk * BM + i * 64, kb * BK);
+            }
+            const int n0 = tc_.n_blk * BN + mc_rank * (BN / 2);      // this CTA's half of the B tile
+            if constexpr (!B_MN) {
+              tc::tma_load_2d_pair(sB, tmB, fb, kb * BK, n0);
+            } else {
+#pragma unroll
+              for (int i = 0; i < BN / 128; ++i) tc::tma_load_2d_pair(sB + i * 8192, tmB, fb, n0 + i * 64, kb * BK);
+            }
           }
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
@@ -195,14 +232,14 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
-    if (lane == 0) {
-      constexpr uint32_t idesc = tc::make_idesc_bf16(BM, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
+    if (lane == 0 && (!PAIR || mc_rank == 0)) {
+      constexpr uint32_t idesc = tc::make_idesc_bf16(PAIR ? 2 * BM : BM, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-        const TileCoord tc_ = decode_tile(args, t, !A_MN);
+      for (int t = tile0; t < total_tiles; t += tile_step) {
+        const TileCoord tc_ = decode_tile(args, t, !A_MN, mc_rank);
         tc::mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
         tc::tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * BN;
@@ -220,12 +257,15 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
                                      : tc::make_smem_desc(a_addr + k * UMMA_K * 2, 16, 1024);
             const uint64_t db = B_MN ? tc::make_smem_desc(b_addr + k * UMMA_K * 128, 8192, 1024)
                                      : tc::make_smem_desc(b_addr + k * UMMA_K * 2, 16, 1024);
-            tc::umma_bf16(d_tmem, da, db, idesc, (kb > tc_.kb0 || k > 0) ? 1u : 0u);
+            if constexpr (PAIR) tc::umma_bf16_pair(d_tmem, da, db, idesc, (kb > tc_.kb0 || k > 0) ? 1u : 0u);
+            else tc::umma_bf16(d_tmem, da, db, idesc, (kb > tc_.kb0 || k > 0) ? 1u : 0u);
           }
-          tc::umma_commit(&empty_bar[stage]);
+          if constexpr (PAIR) tc::umma_commit_pair(&empty_bar[stage], 0x3);   // frees the stage in both CTAs
+          else tc::umma_commit(&empty_bar[stage]);
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
-        tc::umma_commit(&tfull_bar[acc]);
+        if constexpr (PAIR) tc::umma_commit_pair(&tfull_bar[acc], 0x3);       // both CTAs' epilogues read their half
+        else tc::umma_commit(&tfull_bar[acc]);
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       }
     }
@@ -245,11 +285,17 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
     const uint32_t co_row = static_cast<uint32_t>(lane >> 2), co_j = static_cast<uint32_t>(lane & 3);
     int acc = 0;
     uint32_t acc_phase = 0;
+    // hand the accumulator back to the MMA issuer (PAIR: the leader CTA's barrier counts both CTAs' epilogue threads)
+    const uint32_t te0 = PAIR ? tc::mapa_u32(&tempty_bar[0], 0) : 0u, te1 = PAIR ? tc::mapa_u32(&tempty_bar[1], 0) : 0u;
+    auto release_acc = [&](int a) {
+      if constexpr (PAIR) tc::mbar_arrive_cluster(a == 0 ? te0 : te1);
+      else tc::mbar_arrive(&tempty_bar[a]);
+    };
     const bool out_f32 = (args.flags & GEMM_OUT_F32) != 0;
     const bool f_gelu = (args.flags & GEMM_GELU) != 0, f_dgelu = (args.flags & GEMM_DGELU) != 0;
     const float alpha = args.alpha;
-    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-      const TileCoord tc_ = decode_tile(args, t, !A_MN);
+    for (int t = tile0; t < total_tiles; t += tile_step) {
+      const TileCoord tc_ = decode_tile(args, t, !A_MN, mc_rank);
       const TcProblem& P = args.p[tc_.p];
       const int row0 = tc_.m_blk * BM + ew * 32;
       const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + acc * BN;
@@ -260,7 +306,7 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
       if (nch == 0) {
         tc::mbar_wait(&tfull_bar[acc], acc_phase);
         tc::tc_fence_before();
-        tc::mbar_arrive(&tempty_bar[acc]);
+        release_acc(acc);
       }
       if (!out_f32) {
         // ---------------- bf16 outputs through shared memory + TMA store ----------------
@@ -293,7 +339,7 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
           tc::tmem_ld_wait();
           if (c2 == nch - 1) {   // accumulator slab fully read: hand the TMEM buffer back to the MMA warp
             tc::tc_fence_before();
-            tc::mbar_arrive(&tempty_bar[acc]);
+            release_acc(acc);
           }
           // (3) transpose the input chunk to "thread = row" through the staging buffer
           if (need_in) {
@@ -423,7 +469,7 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
           tc::tmem_ld_wait();
           if (c2 == nch - 1) {
             tc::tc_fence_before();
-            tc::mbar_arrive(&tempty_bar[acc]);
+            release_acc(acc);
           }
           if (row_ok) {
 #pragma unroll
@@ -449,7 +495,11 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
 
   tc::tc_fence_before();
   __syncthreads();
-  if (warp == 2) tc::tmem_dealloc(tmem_base, 2 * BN);
+  if constexpr (PAIR) tc::cluster_sync();             // no CTA leaves while its peer may still read / signal into it
+  if (warp == 2) {
+    if constexpr (PAIR) tc::tmem_dealloc_pair(tmem_base, 2 * BN);
+    else tc::tmem_dealloc(tmem_base, 2 * BN);
+  }
 }
 
 // ---------------------------------------------------------------- host
@@ -463,9 +513,10 @@ int get_tmap(CUtensorMap* out, const void* ptr, uint64_t d0, uint64_t d1, uint64
 
 int num_sms() { return mb_num_sms(); }
 
-template <int BN, bool A_MN, bool B_MN>
+// PAIR: 2-CTA clusters running cta_group::2 MMAs (see the kernel); tiles are scheduled as vertical pairs of m-blocks.
+template <int BN, bool A_MN, bool B_MN, bool MC>
 int launch(const GemmParams* Ps, int count, cudaStream_t st) {
-  using C_ = Cfg<BN>;
+  using C_ = Cfg<BN, MC>;
   TcMaps maps;
   TcArgs a;
   std::memset(&a, 0, sizeof(a));
@@ -478,7 +529,7 @@ int launch(const GemmParams* Ps, int count, cudaStream_t st) {
     if (!A_MN) rc = get_tmap(&maps.a[i], P.A, P.K, P.M, P.sam, BK, BM);
     else rc = get_tmap(&maps.a[i], P.A, P.M, P.K, P.sak, 64, BK);
     if (rc != 0) return rc;
-    if (!B_MN) rc = get_tmap(&maps.b[i], P.B, P.K, P.N, P.sbn, BK, BN);
+    if (!B_MN) rc = get_tmap(&maps.b[i], P.B, P.K, P.N, P.sbn, BK, MC ? BN / 2 : BN);
     else rc = get_tmap(&maps.b[i], P.B, P.N, P.K, P.sbk, 64, BK);
     if (rc != 0) return rc;
     if (!out_f32) {
@@ -503,6 +554,7 @@ int launch(const GemmParams* Ps, int count, cudaStream_t st) {
     q.C = P.C; q.bias = P.bias; q.residual = P.residual; q.aux = P.aux; q.colsum = P.colsum;
     q.M = P.M; q.N = P.N; q.K = P.K; q.ldc = P.ldc;
     q.mblocks = (P.M + BM - 1) / BM;
+    if (MC) q.mblocks = (q.mblocks + 1) / 2;
     q.nblocks = (P.N + BN - 1) / BN;
     tiles_mn_total += static_cast<long long>(q.mblocks) * q.nblocks;
   }
@@ -517,7 +569,8 @@ int launch(const GemmParams* Ps, int count, cudaStream_t st) {
     int splits = 1;
     if (flags & GEMM_ACCUM) {
       // split the contraction so that the grid covers the chip (fp32 red.add combines the partials)
-      splits = static_cast<int>((2LL * num_sms() + tiles_mn_total - 1) / tiles_mn_total);
+      const long long slots = MC ? num_sms() / 2 : num_sms();
+      splits = static_cast<int>((2LL * slots + tiles_mn_total - 1) / tiles_mn_total);
       if (splits > kblocks) splits = kblocks;
       if (splits < 1) splits = 1;
       const int per = (kblocks + splits - 1) / splits;
@@ -531,15 +584,73 @@ int launch(const GemmParams* Ps, int count, cudaStream_t st) {
   a.flags = flags;
   a.alpha = Ps[0].alpha;
   a.total_tiles = total;
-  const int grid = total < num_sms() ? total : num_sms();
+  auto kern = gemm_tc_kernel<BN, A_MN, B_MN, MC>;
   static bool attr_set = false;
+  static int max_clusters = 0;
   if (!attr_set) {
-    cudaFuncSetAttribute(gemm_tc_kernel<BN, A_MN, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize, C_::SMEM_BYTES);
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C_::SMEM_BYTES);
+    if (MC) {
+      cudaLaunchConfig_t qc = {};
+      cudaLaunchAttribute qa[1];
+      qa[0].id = cudaLaunchAttributeClusterDimension;
+      qa[0].val.clusterDim.x = 2; qa[0].val.clusterDim.y = 1; qa[0].val.clusterDim.z = 1;
+      qc.gridDim = dim3(num_sms() & ~1); qc.blockDim = dim3(NUM_THREADS); qc.dynamicSmemBytes = C_::SMEM_BYTES;
+      qc.attrs = qa; qc.numAttrs = 1;
+      if (cudaOccupancyMaxActiveClusters(&max_clusters, kern, &qc) != cudaSuccess || max_clusters < 1) {
+        cudaGetLastError();
+        max_clusters = num_sms() / 2;
+      }
+      if (max_clusters > num_sms() / 2) max_clusters = num_sms() / 2;
+    }
     attr_set = true;
   }
-  gemm_tc_kernel<BN, A_MN, B_MN><<<grid, NUM_THREADS, C_::SMEM_BYTES, st>>>(maps, a);
+  if (!MC) {
+    const int grid = total < num_sms() ? total : num_sms();
+    kern<<<grid, NUM_THREADS, C_::SMEM_BYTES, st>>>(maps, a);
+  } else {
+    const int clusters = total < max_clusters ? total : max_clusters;
+    cudaLaunchConfig_t cfg = {};
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.gridDim = dim3(2 * clusters); cfg.blockDim = dim3(NUM_THREADS); cfg.dynamicSmemBytes = C_::SMEM_BYTES;
+    cfg.stream = st; cfg.attrs = at; cfg.numAttrs = 1;
+    cudaError_t le = cudaLaunchKernelEx(&cfg, kern, maps, a);
+    if (le != cudaSuccess) return static_cast<int>(le);
+  }
   cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? 0 : static_cast<int>(e);
+}
+
+// MB_GEMM_PAIR = 0: never, 1: always, 2 (default): where it measured faster (tools/gemm_bench.py, profiles/):
+// long-K weight-gradient GEMMs gain 11-15 % from the lower operand traffic per SM; short-K tiles are bound by their
+// epilogue and lose 5-10 % to the coupling of the two CTAs' epilogues, so they stay on single-CTA tiles.
+int pair_mode() {
+  static int mode = -1;
+  if (mode < 0) {
+    const char* e = std::getenv("MB_GEMM_PAIR");
+    mode = (e != nullptr && e[0] >= '0' && e[0] <= '2') ? e[0] - '0' : 2;
+  }
+  return mode;
+}
+
+template <int BN, bool A_MN, bool B_MN>
+int launch_any(const GemmParams* Ps, int count, cudaStream_t st) {
+  bool mc = pair_mode() == 1;
+  if (pair_mode() == 2 && (Ps[0].flags & GEMM_ACCUM)) {
+    long long singles = 0, pairs = 0;
+    int max_k = 0;
+    for (int i = 0; i < count; ++i) {
+      const long long mb = (Ps[i].M + BM - 1) / BM, nb = (Ps[i].N + BN - 1) / BN;
+      singles += mb * nb;
+      pairs += (mb + 1) / 2 * nb;
+      max_k = Ps[i].K > max_k ? Ps[i].K : max_k;
+    }
+    mc = 2 * pairs == singles && max_k >= 12000;
+  }
+  if (Ps[0].flags & GEMM_PAIR_ON) mc = true;
+  if (Ps[0].flags & GEMM_PAIR_OFF) mc = false;
+  return mc ? launch<BN, A_MN, B_MN, true>(Ps, count, st) : launch<BN, A_MN, B_MN, false>(Ps, count, st);
 }
 
 }  // namespace
@@ -584,9 +695,9 @@ extern "C" int mb_gemm_tc_grouped(const GemmParams* params, int count, void* str
     const long long w128 = (t128 + sms - 1) / sms * 141;  // 128 * 1.1
     wide = w256 <= w128;
   }
-  if (a_k && b_k) return wide ? launch<256, false, false>(live, n, st) : launch<128, false, false>(live, n, st);
-  if (a_k && b_mn) return wide ? launch<256, false, true>(live, n, st) : launch<128, false, true>(live, n, st);
-  if (a_mn && b_mn) return wide ? launch<256, true, true>(live, n, st) : launch<128, true, true>(live, n, st);
+  if (a_k && b_k) return wide ? launch_any<256, false, false>(live, n, st) : launch_any<128, false, false>(live, n, st);
+  if (a_k && b_mn) return wide ? launch_any<256, false, true>(live, n, st) : launch_any<128, false, true>(live, n, st);
+  if (a_mn && b_mn) return wide ? launch_any<256, true, true>(live, n, st) : launch_any<128, true, true>(live, n, st);
   return -5;
 }
 

@@ -17,6 +17,7 @@ from . import _lib
 
 F32, BF16 = 0, 1
 GEMM_GELU, GEMM_DGELU, GEMM_ACCUM, GEMM_OUT_F32 = 1, 2, 4, 8
+GEMM_PAIR_ON, GEMM_PAIR_OFF = 16, 32      # scheduling hints of the tensor-core path (tests, tuning)
 
 
 def _dt(t: torch.Tensor) -> int:

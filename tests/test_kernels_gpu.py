@@ -331,6 +331,37 @@ def test_gemm_wgrad_and_dgrad_layouts(KK, dt, T, N, Kd):
         close(x, y, rtol=2e-2 if dt == torch.bfloat16 else 1e-4, atol=(2e-2 if dt == torch.bfloat16 else 1e-4) * s)
 
 
+@pytest.mark.parametrize("hint", [16, 32])
+@pytest.mark.parametrize("M,N,Kd", [(1000, 768, 768), (333, 3072, 768), (4096, 512, 3072), (130, 8, 512), (257, 264, 72),
+                                    (2048, 128, 512)])
+def test_gemm_cta_pair_and_single_tiles(KK, hint, M, N, Kd):
+    """Both tile schedules of the tensor-core path -- 2-CTA tcgen05.mma.cta_group::2 pairs (hint 16) and single-CTA
+    tiles (hint 32) -- on all three operand layouts, with odd m-block counts (the pair's second CTA runs on an empty
+    block), fused GELU + aux, GELU' + column sums, residual, and split-K fp32 accumulation."""
+    dt = torch.bfloat16
+    A, Bm, bias, res = _gemm_case(None, dt, M, N, Kd, "k", 0)
+    auxin = rnd(M, N, dt=dt, seed=7)
+    dY, X = rnd(M, N, dt=dt, seed=8, scale=0.5), rnd(M, Kd, dt=dt, seed=9, scale=0.5)
+
+    def run(K):
+        outs = []
+        Y, U = torch.zeros(M, N, dtype=dt, device="cuda"), torch.zeros(M, N, dtype=dt, device="cuda")
+        K.gemm(A, Bm, Y, M, N, Kd, sam=Kd, sak=1, sbn=Kd, sbk=1, ldc=N, bias=bias, aux=U, flags=1 | hint)
+        Y2 = torch.zeros(M, N, dtype=dt, device="cuda")
+        K.gemm(A, Bm, Y2, M, N, Kd, sam=Kd, sak=1, sbn=Kd, sbk=1, ldc=N, bias=bias, residual=res, flags=hint)
+        dX, cs = torch.zeros(M, Kd, dtype=dt, device="cuda"), torch.full((Kd,), 0.125, device="cuda")
+        K.gemm(dY, Bm, dX, M, Kd, N, sam=N, sak=1, sbn=1, sbk=Kd, ldc=Kd, aux=X, flags=2 | hint, colsum=cs)
+        dW = torch.full((N, Kd), 0.5, dtype=torch.float32, device="cuda")
+        K.gemm(dY, X, dW, N, Kd, M, sam=1, sak=N, sbn=1, sbk=Kd, ldc=Kd, flags=4 | hint)
+        return [Y, U, Y2, dX, cs, dW]
+    a, b = both(KK, run)
+    s = math.sqrt(max(Kd, N)) * 0.25
+    for x, y in zip(a[:4], b[:4]):
+        close(x, y, rtol=2e-2, atol=2e-2 * s)
+    close(a[4], b[4], rtol=2e-2, atol=2e-2 * s * math.sqrt(M))
+    close(a[5], b[5], rtol=1e-3, atol=2e-3 * math.sqrt(M))
+
+
 def test_gemm_grouped_matches_single_launches(KK):
     """Four problems of one layer kind (different row counts / operands) in ONE persistent launch: fwd with GELU,
     fwd with residual, dgrad on the untransposed weight (+GELU'), wgrad with split-K accumulation."""
