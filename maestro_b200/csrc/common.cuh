@@ -130,6 +130,25 @@ __device__ __forceinline__ float gelu_fast(float x) {
   gelu_fast_terms(x, q, e);
   return fmaxf(x, 0.0f) - fabsf(q * x);
 }
+// gelu(x) = x * Phi(x) and gelu'(x) = Phi(x) + x * phi(x) from one set of terms (forward epilogue: the derivative is
+// what the backward needs saved).  Abramowitz-Stegun 26.2.17 (|error| < 7.5e-8): phi = exp(-x^2 / 2) / sqrt(2 pi) (the
+// 1 / sqrt(2 pi) is folded into the exponent), t = 1 / (1 + 0.2316419 |x|), tail mass q = phi * t * poly(t),
+// Phi = 1/2 + copysign(1/2 - q, x).  15 FP32 instructions + 2 MUFU (ftz forms) per element.
+__device__ __forceinline__ float gelu_fast_both(float x, float& grad) {
+  const float w = fmaf(x * -0.72134752044448170368f, x, -1.32574806473616f);   // log2(phi(x))
+  float phi, t;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(phi) : "f"(w));
+  const float d = fmaf(fabsf(x), 0.2316419f, 1.0f);
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(d));
+  float p = fmaf(t, 1.330274429f, -1.821255978f);
+  p = fmaf(p, t, 1.781477937f);
+  p = fmaf(p, t, -0.356563782f);
+  p = fmaf(p, t, 0.319381530f);
+  const float q = (p * t) * phi;
+  const float cdf = 0.5f + copysignf(0.5f - q, x);
+  grad = fmaf(x, phi, cdf);
+  return x * cdf;
+}
 // gelu'(x) = Phi(x) + x * phi(x),  Phi(x) = 1/2 + copysign(1/2 - q, x)
 __device__ __forceinline__ float gelu_fast_grad(float x) {
   float q, e;

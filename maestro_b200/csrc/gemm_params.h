@@ -2,8 +2,8 @@
 // and in maestro_b200/_lib.py as a ctypes.Structure).
 #pragma once
 
-#define GEMM_GELU 1      // out = gelu(acc + bias); aux <- acc + bias (pre-activation, saved for backward)
-#define GEMM_DGELU 2     // out = acc * gelu'(aux)
+#define GEMM_GELU 1      // out = gelu(acc + bias); aux <- gelu'(acc + bias) (saved for the backward)
+#define GEMM_DGELU 2     // out = acc * aux (aux = the derivative the forward GEMM_GELU call saved)
 #define GEMM_ACCUM 4     // out += result (fp32 gradient accumulation)
 #define GEMM_OUT_F32 8   // C is fp32 regardless of the activation dtype
 #define GEMM_PAIR_ON 16  // scheduling hint (tensor-core path): force 2-CTA (cta_group::2) tiles

@@ -1,7 +1,7 @@
 // fp32-accumulate CUDA-core GEMM with arbitrary operand strides and a two-level batch.
 // This is the arithmetic of the *fp32 check mode* (north star: 1e-4 parity with the reference) and of the
 // few contractions too small / oddly shaped for the tcgen05 path.  C[m, n] = alpha * sum_k A(m, k) * B(n, k)
-// followed by the shared epilogue (bias, exact GELU with saved pre-activation, GELU gradient, residual).
+// followed by the shared epilogue (bias, exact GELU with saved derivative, GELU gradient, residual).
 #include "common.cuh"
 #include "gemm_params.h"
 
@@ -74,10 +74,10 @@ __global__ void __launch_bounds__(256) gemm_simt_kernel(GemmParams P) {
       float v = acc[i][j] * P.alpha;
       if (P.bias != nullptr) v += P.bias[n];
       if (P.flags & GEMM_GELU) {
-        aux[o] = from_f32<T>(v);
-        v = gelu_erf(to_f32(from_f32<T>(v)));  // activation of the stored (rounded) pre-activation
+        aux[o] = from_f32<T>(gelu_erf_grad(v));  // saved for the backward: gelu'(pre-activation)
+        v = gelu_erf(v);
       }
-      if (P.flags & GEMM_DGELU) v *= gelu_erf_grad(to_f32(aux[o]));
+      if (P.flags & GEMM_DGELU) v *= to_f32(aux[o]);
       if (res != nullptr) v += to_f32(res[o]);
       if (P.flags & GEMM_ACCUM) v += to_f32(C[o]);
       C[o] = from_f32<TC>(v);

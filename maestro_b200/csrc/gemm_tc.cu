@@ -12,9 +12,9 @@
 // TMEM (2 x BN columns) so the epilogue of tile i overlaps the main loop of tile i + 1; shared memory holds a
 // STAGES-deep ring of 128 x 64 (A) and BN x 64 (B) bf16 tiles in the 128-byte swizzle layout, plus one 2 KB
 // staging buffer per epilogue warp.
-// Epilogue (bf16 outputs): tcgen05.ld -> registers -> fused bias / GELU (+ saved pre-activation) / GELU' /
+// Epilogue (bf16 outputs): tcgen05.ld -> registers -> fused bias / GELU (+ saved gelu') / GELU' /
 // residual -> bf16 -> swizzled shared-memory staging -> TMA tile store (full 128-byte lines, clipped at the
-// matrix edge by the hardware).  Epilogue inputs (residual, saved pre-activation) are read with fully coalesced
+// matrix edge by the hardware).  Epilogue inputs (residual, saved gelu') are read with fully coalesced
 // 16-byte loads (8 rows x 64 B per instruction, the tile pulled into L2 by a TMA prefetch while the main loop runs)
 // and transposed to "thread = row" through the same staging buffer.
 // fp32 outputs (wgrad accumulation) use direct 16-byte stores / red.add.
@@ -73,7 +73,7 @@ struct TcArgs {
 
 struct TcMaps {
   CUtensorMap a[MAX_GROUP], b[MAX_GROUP], c[MAX_GROUP];
-  CUtensorMap x[MAX_GROUP];   // GELU: pre-activation output; GELU': pre-activation input; else residual input
+  CUtensorMap x[MAX_GROUP];   // GELU: gelu'(pre-activation) output; GELU': the same tensor as input; else residual input
   CUtensorMap pf[MAX_GROUP];  // the epilogue input again, with a 128-row x 64-column box for L2 prefetch
 };
 
@@ -178,7 +178,7 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
         const CUtensorMap* tmA = &maps.a[tc_.p];
         const CUtensorMap* tmB = &maps.b[tc_.p];
         {
-          // pull this tile's epilogue input (residual / saved pre-activation) into L2 while the main loop runs
+          // pull this tile's epilogue input (residual / saved gelu') into L2 while the main loop runs
           const TcProblem& P = args.p[tc_.p];
           if (!(args.flags & GEMM_OUT_F32) && ((args.flags & GEMM_DGELU) || P.residual != nullptr)) {
             for (int cc = 0; cc < BN / 64; ++cc) {
@@ -377,7 +377,9 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
 #pragma unroll
             for (int q = 0; q < 32; ++q) v[q] *= alpha;
           }
-          // (5) GELU: store the bf16 pre-activation (second output), activate the rounded value
+          // (5) GELU: second output = gelu'(pre-activation) (the backward's dgrad then only multiplies by it; the
+          // erf / exp terms are shared between the activation and its derivative)
+          uint32_t o[16];
           if (f_gelu) {
             if (lane == 0) tc::tma_store_wait_read();
             __syncwarp();
@@ -386,9 +388,11 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
               uint32_t w[4];
 #pragma unroll
               for (int q = 0; q < 4; ++q) {
-                w[q] = pack_bf16x2(v[8 * j + 2 * q], v[8 * j + 2 * q + 1]);
-                v[8 * j + 2 * q] = gelu_fast(__uint_as_float(w[q] << 16));
-                v[8 * j + 2 * q + 1] = gelu_fast(__uint_as_float(w[q] & 0xffff0000u));
+                float d0, d1;
+                const float g0 = gelu_fast_both(v[8 * j + 2 * q], d0);
+                const float g1 = gelu_fast_both(v[8 * j + 2 * q + 1], d1);
+                w[q] = pack_bf16x2(d0, d1);
+                o[4 * j + q] = pack_bf16x2(g0, g1);   // packed at once: 16 live registers instead of 32
               }
               asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(own_base + ((j ^ own_x) << 4)), "r"(w[0]),
                            "r"(w[1]), "r"(w[2]), "r"(w[3]) : "memory");
@@ -409,8 +413,8 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
               for (int q = 0; q < 4; ++q) {
                 const float a0 = __uint_as_float(w[q] << 16), a1 = __uint_as_float(w[q] & 0xffff0000u);
                 if (f_dgelu) {
-                  v[8 * j + 2 * q] *= gelu_fast_grad(a0);
-                  v[8 * j + 2 * q + 1] *= gelu_fast_grad(a1);
+                  v[8 * j + 2 * q] *= a0;
+                  v[8 * j + 2 * q + 1] *= a1;
                 } else {
                   v[8 * j + 2 * q] += a0;
                   v[8 * j + 2 * q + 1] += a1;
@@ -423,8 +427,13 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
           __syncwarp();
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
-            const uint32_t w0 = pack_bf16x2(v[8 * j], v[8 * j + 1]), w1 = pack_bf16x2(v[8 * j + 2], v[8 * j + 3]);
-            const uint32_t w2 = pack_bf16x2(v[8 * j + 4], v[8 * j + 5]), w3 = pack_bf16x2(v[8 * j + 6], v[8 * j + 7]);
+            uint32_t w0, w1, w2, w3;
+            if (f_gelu) {
+              w0 = o[4 * j]; w1 = o[4 * j + 1]; w2 = o[4 * j + 2]; w3 = o[4 * j + 3];
+            } else {
+              w0 = pack_bf16x2(v[8 * j], v[8 * j + 1]); w1 = pack_bf16x2(v[8 * j + 2], v[8 * j + 3]);
+              w2 = pack_bf16x2(v[8 * j + 4], v[8 * j + 5]); w3 = pack_bf16x2(v[8 * j + 6], v[8 * j + 7]);
+            }
             asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(own_base + ((j ^ own_x) << 4)), "r"(w0),
                          "r"(w1), "r"(w2), "r"(w3) : "memory");
           }
@@ -534,7 +543,7 @@ int launch(const GemmParams* Ps, int count, cudaStream_t st) {
     if (rc != 0) return rc;
     if (!out_f32) {
       if ((rc = get_tmap(&maps.c[i], P.C, P.N, P.M, P.ldc, 32, 32, 64)) != 0) return rc;
-      // x: GELU -> saved pre-activation (second output); GELU' -> the same tensor as epilogue input; else residual
+      // x: GELU -> saved gelu'(pre-activation) (second output); GELU' -> the same tensor as epilogue input; else residual
       const void* xp = (flags & (GEMM_GELU | GEMM_DGELU)) ? P.aux : P.residual;
       if ((flags & (GEMM_GELU | GEMM_DGELU)) && xp == nullptr) return -6;
       if (xp != nullptr) {

@@ -298,7 +298,7 @@ class PretrainEngine:
     def lin_fwd_g(self, items):
         """Grouped linear layers of one kind, one launch: items = [(x, M, wname, bname, out, gelu_aux, residual)].
 
-        out[M, N] = x[M, Kd] @ W[N, Kd]^T (+ bias) (gelu, saving the pre-activation) (+ residual) per item.
+        out[M, N] = x[M, Kd] @ W[N, Kd]^T (+ bias) (gelu, saving gelu'(pre-activation) for the backward) (+ residual) per item.
         """
         probs = []
         for x, M, wname, bname, out, gelu_aux, residual in items:

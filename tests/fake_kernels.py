@@ -235,13 +235,12 @@ class FakeKernels:
             v = v + bias
         if flags & GEMM_GELU:
             av = _strided(aux, c_off, (nb1, nb2, M, N), (c_s[0], c_s[1], ldc, 1))
-            av.copy_(v.to(aux.dtype))
-            v = F.gelu(av.float())
+            cdf = 0.5 * (1 + torch.erf(v / math.sqrt(2)))
+            pdf = torch.exp(-0.5 * v * v) / math.sqrt(2 * math.pi)
+            av.copy_((cdf + v * pdf).to(aux.dtype))      # saved for the backward: gelu'(pre-activation)
+            v = F.gelu(v)
         if flags & GEMM_DGELU:
-            u = _strided(aux, c_off, (nb1, nb2, M, N), (c_s[0], c_s[1], ldc, 1)).float()
-            cdf = 0.5 * (1 + torch.erf(u / math.sqrt(2)))
-            pdf = torch.exp(-0.5 * u * u) / math.sqrt(2 * math.pi)
-            v = v * (cdf + u * pdf)
+            v = v * _strided(aux, c_off, (nb1, nb2, M, N), (c_s[0], c_s[1], ldc, 1)).float()
         if residual is not None:
             v = v + _strided(residual, c_off, (nb1, nb2, M, N), (c_s[0], c_s[1], ldc, 1)).float()
         if flags & GEMM_ACCUM:
