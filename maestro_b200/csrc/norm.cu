@@ -5,6 +5,7 @@
 //     values of one (b, d) image, apply fused with the positional + date encoding add
 //     (maestro/ssl/mim.py:232-252) and the group concat (layers/utils.py:12-47).
 #include "common.cuh"
+#include "tc_common.cuh"
 
 struct RowMap {
   int n;    // logical rows per sample
@@ -13,62 +14,106 @@ struct RowMap {
   __device__ __forceinline__ size_t phys(int r) const { return static_cast<size_t>(r / n) * bs + off + (r % n); }
 };
 
-constexpr int LN_MAX_ELEMS = 32;  // per lane -> d <= 1024
 
 // ------------------------------------------------------------------ LayerNorm forward
-template <typename T>
-__global__ void __launch_bounds__(256) layernorm_fwd_kernel(const T* __restrict__ x, const float* __restrict__ gamma,
-                                                            const float* __restrict__ beta, T* __restrict__ y,
-                                                            float* __restrict__ mean_out, float* __restrict__ rstd_out,
-                                                            int rows, int d, float eps, RowMap in_map, RowMap out_map) {
+// y = (x - mean) * rstd * gamma + beta per row (nn.LayerNorm, eps inside the square root; mean / rstd saved for the
+// backward).  HBM-bound: 2 * d * sizeof(T) bytes per row.  Warp w of the grid walks rows w, w + W, w + 2W, ...; a
+// lane owns NCH 16-byte column chunks, gamma / beta of those columns stay in registers for the whole kernel, and the
+// (still packed) loads of row r + W are in flight while row r is reduced and written.
+constexpr int LNF_THREADS = 256;
+
+template <typename T, int NCH>
+__global__ void __launch_bounds__(LNF_THREADS)
+layernorm_fwd_kernel(const T* __restrict__ x, const float* __restrict__ gamma, const float* __restrict__ beta,
+                     T* __restrict__ y, float* __restrict__ mean_out, float* __restrict__ rstd_out, int rows, int d,
+                     float eps, RowMap in_map, RowMap out_map) {
   constexpr int V = VecIO<T>::N;
-  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  constexpr int NE = NCH * V;
+  typedef typename VecIO<T>::Raw Raw;
   const int lane = threadIdx.x & 31;
-  if (warp >= rows) return;
+  const int nwarps = blockDim.x >> 5;
+  const int gwarp = blockIdx.x * nwarps + (threadIdx.x >> 5);
+  const int total_warps = gridDim.x * nwarps;
   const int nvec = d / V;
-  const T* xr = x + in_map.phys(warp) * d;
-  float v[LN_MAX_ELEMS];
-  float s = 0.f;
+  const float inv_d = 1.0f / static_cast<float>(d);
+
+  Raw nx[NCH];
+  auto issue_loads = [&](int r) {
+    const T* xr = x + in_map.phys(r) * d;
 #pragma unroll
-  for (int c = 0; c < LN_MAX_ELEMS / V; ++c) {
+    for (int c = 0; c < NCH; ++c) {
+      const int idx = lane + c * 32;
+      nx[c] = idx < nvec ? VecIO<T>::load_raw(xr + idx * V) : VecIO<T>::zero_raw();
+    }
+  };
+  int r = gwarp;
+  if (r < rows) issue_loads(r);
+
+  float g[NE], b[NE];
+#pragma unroll
+  for (int c = 0; c < NCH; ++c) {
     const int idx = lane + c * 32;
-    if (idx < nvec) {
-      VecIO<T>::load(xr + idx * V, v + c * V);
 #pragma unroll
-      for (int j = 0; j < V; ++j) s += v[c * V + j];
+    for (int j = 0; j < V; j += 4) {
+      const bool ok = idx < nvec;
+      const float4 gv = ok ? __ldg(reinterpret_cast<const float4*>(gamma + idx * V + j)) : make_float4(0.f, 0.f, 0.f, 0.f);
+      const float4 bv = ok ? __ldg(reinterpret_cast<const float4*>(beta + idx * V + j)) : make_float4(0.f, 0.f, 0.f, 0.f);
+      g[c * V + j] = gv.x; g[c * V + j + 1] = gv.y; g[c * V + j + 2] = gv.z; g[c * V + j + 3] = gv.w;
+      b[c * V + j] = bv.x; b[c * V + j + 1] = bv.y; b[c * V + j + 2] = bv.z; b[c * V + j + 3] = bv.w;
     }
   }
-  const float mean = warp_sum(s) / d;
-  float ss = 0.f;
+
+  for (; r < rows; r += total_warps) {
+    float v[NE];
 #pragma unroll
-  for (int c = 0; c < LN_MAX_ELEMS / V; ++c) {
-    if (lane + c * 32 < nvec) {
+    for (int c = 0; c < NCH; ++c) VecIO<T>::unpack(nx[c], v + c * V);
+    if (r + total_warps < rows) issue_loads(r + total_warps);
+    float s = 0.f;
 #pragma unroll
-      for (int j = 0; j < V; ++j) {
-        const float t = v[c * V + j] - mean;
-        ss += t * t;
+    for (int e = 0; e < NE; ++e) s += v[e];                 // padding chunks hold zeros
+    const float mean = warp_sum(s) * inv_d;
+    float ss = 0.f;
+#pragma unroll
+    for (int c = 0; c < NCH; ++c) {
+      if (lane + c * 32 < nvec) {
+#pragma unroll
+        for (int j = 0; j < V; ++j) {
+          const float t = v[c * V + j] - mean;
+          ss = fmaf(t, t, ss);
+        }
+      }
+    }
+    const float rstd = rsqrtf(warp_sum(ss) * inv_d + eps);
+    if (lane == 0 && mean_out != nullptr) {
+      mean_out[r] = mean;
+      rstd_out[r] = rstd;
+    }
+    const float shift = -mean * rstd;
+    T* yr = y + out_map.phys(r) * d;
+#pragma unroll
+    for (int c = 0; c < NCH; ++c) {
+      const int idx = lane + c * 32;
+      if (idx < nvec) {
+        float o[V];
+#pragma unroll
+        for (int j = 0; j < V; ++j) o[j] = fmaf(fmaf(v[c * V + j], rstd, shift), g[c * V + j], b[c * V + j]);
+        VecIO<T>::store(yr + idx * V, o);
       }
     }
   }
-  const float rstd = rsqrtf(warp_sum(ss) / d + eps);
-  if (lane == 0 && mean_out != nullptr) {
-    mean_out[warp] = mean;
-    rstd_out[warp] = rstd;
-  }
-  T* yr = y + out_map.phys(warp) * d;
-#pragma unroll
-  for (int c = 0; c < LN_MAX_ELEMS / V; ++c) {
-    const int idx = lane + c * 32;
-    if (idx < nvec) {
-      float o[V];
-#pragma unroll
-      for (int j = 0; j < V; ++j) {
-        const int col = idx * V + j;
-        o[j] = (v[c * V + j] - mean) * rstd * gamma[col] + beta[col];
-      }
-      VecIO<T>::store(yr + idx * V, o);
-    }
-  }
+}
+
+template <typename T, int NCH>
+static void launch_ln_fwd(const void* x, const float* gamma, const float* beta, void* y, float* mean, float* rstd,
+                          int rows, int d, float eps, RowMap im, RowMap om, cudaStream_t st) {
+  const int wpb = LNF_THREADS / 32;
+  // at least 2 rows per warp (gamma / beta are loaded once per warp), at most 8 CTAs per SM
+  long long blocks = mb_ceil_div(static_cast<long long>(rows), static_cast<long long>(wpb) * 2);
+  const long long cap = 148LL * 8;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  layernorm_fwd_kernel<T, NCH><<<static_cast<int>(blocks), LNF_THREADS, 0, st>>>(
+      static_cast<const T*>(x), gamma, beta, static_cast<T*>(y), mean, rstd, rows, d, eps, im, om);
 }
 
 extern "C" int mb_layernorm_fwd(const void* x, const float* gamma, const float* beta, void* y, float* mean,
@@ -77,11 +122,18 @@ extern "C" int mb_layernorm_fwd(const void* x, const float* gamma, const float* 
   if (rows == 0) return 0;
   if (d > 1024 || d % 8 != 0) return -2;
   RowMap im{in_n, in_bs, in_off}, om{out_n, out_bs, out_off};
-  const int threads = 256;
-  const int blocks = mb_ceil_div(static_cast<long long>(rows) * 32, threads);
-  MB_DISPATCH_DTYPE(dtype, T,
-                    (layernorm_fwd_kernel<T><<<blocks, threads, 0, static_cast<cudaStream_t>(stream)>>>(
-                        static_cast<const T*>(x), gamma, beta, static_cast<T*>(y), mean, rstd, rows, d, eps, im, om)));
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+#define LNF_CASE(n)                                                                                  \
+  case n:                                                                                            \
+    MB_DISPATCH_DTYPE(dtype, T, (launch_ln_fwd<T, n>(x, gamma, beta, y, mean, rstd, rows, d, eps, im, om, st))); \
+    break;
+  const int vec = dtype == MB_DTYPE_F32 ? 4 : 8;
+  const int nch = mb_ceil_div(d / vec, 32);
+  switch (nch) {
+    LNF_CASE(1) LNF_CASE(2) LNF_CASE(3) LNF_CASE(4) LNF_CASE(5) LNF_CASE(6) LNF_CASE(7) LNF_CASE(8)
+    default: return -2;
+  }
+#undef LNF_CASE
   MB_CHECK_LAUNCH();
   return 0;
 }
@@ -94,6 +146,9 @@ extern "C" int mb_layernorm_fwd(const void* x, const float* gamma, const float* 
 // One CTA per SM, 12 warps, warp w of the grid walks rows w, w + W, w + 2W, ...; lanes own columns, so the column
 // sums live in registers for the whole kernel and are combined once per CTA (shared-memory red, then one fp32
 // global red per column per CTA: <= 148 per address).
+// Every warp owns a ring of `depth` row slots in shared memory that one lane fills with 1D bulk copies
+// (cp.async.bulk, mbarrier completion): up to depth x (x, dy, dres) rows per warp are in flight from HBM without
+// holding registers, which is what the bandwidth-latency product of the chip needs (~45 KB per SM).
 constexpr int LNB_THREADS = 384;
 
 template <typename T, int NCH>
@@ -101,61 +156,90 @@ __global__ void __launch_bounds__(LNB_THREADS, 1)
 layernorm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x, const float* __restrict__ mean_in,
                      const float* __restrict__ rstd_in, const float* __restrict__ gamma, const T* __restrict__ dres,
                      T* __restrict__ dx, float* __restrict__ dgamma, float* __restrict__ dbeta,
-                     float* __restrict__ dbias, int rows, int d, RowMap in_map, RowMap out_map) {
+                     float* __restrict__ dbias, int rows, int d, RowMap in_map, RowMap out_map, int depth) {
   constexpr int V = VecIO<T>::N;
   constexpr int NE = NCH * V;
-  extern __shared__ float sm[];  // [3][d] partial dgamma / dbeta / dbias of this CTA
+  typedef typename VecIO<T>::Raw Raw;
+  extern __shared__ __align__(128) uint8_t smem_raw[];
+  // [3][d] partial dgamma / dbeta / dbias | gamma [d] | barriers [nwarps][depth] | ring [nwarps][depth][3][row]
+  float* sm = reinterpret_cast<float*>(smem_raw);
+  float* gam = sm + 3 * d;
   const int lane = threadIdx.x & 31;
+  const int wid = threadIdx.x >> 5;
   const int nwarps = blockDim.x >> 5;
-  const int gwarp = blockIdx.x * nwarps + (threadIdx.x >> 5);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(gam + d) + wid * depth;
+  const uint32_t row_bytes = static_cast<uint32_t>(d) * sizeof(T);
+  uint8_t* ring = reinterpret_cast<uint8_t*>(reinterpret_cast<uint64_t*>(gam + d) + nwarps * depth) +
+                  static_cast<size_t>(wid) * depth * 3 * row_bytes;
+  const int gwarp = blockIdx.x * nwarps + wid;
   const int total_warps = gridDim.x * nwarps;
   const int nvec = d / V;
+  const bool has_res = dres != nullptr;
   for (int i = threadIdx.x; i < 3 * d; i += blockDim.x) sm[i] = 0.f;
+  for (int i = threadIdx.x; i < d; i += blockDim.x) gam[i] = gamma[i];
+  if (lane == 0) {
+    for (int s = 0; s < depth; ++s) tc::mbar_init(&bars[s], 1);
+    tc::fence_barrier_init();
+  }
   __syncthreads();
 
-  typedef typename VecIO<T>::Raw Raw;
+  auto issue_row = [&](int slot, int r) {   // one lane
+    const size_t pin = in_map.phys(r), pout = out_map.phys(r);
+    uint8_t* dst = ring + static_cast<size_t>(slot) * 3 * row_bytes;
+    tc::mbar_expect_tx(&bars[slot], (has_res ? 3u : 2u) * row_bytes);
+    tc::bulk_load_1d(dst, x + pin * d, row_bytes, &bars[slot]);
+    tc::bulk_load_1d(dst + row_bytes, dy + pout * d, row_bytes, &bars[slot]);
+    if (has_res) tc::bulk_load_1d(dst + 2 * row_bytes, dres + pin * d, row_bytes, &bars[slot]);
+  };
+  if (lane == 0) {
+    for (int s = 0; s < depth; ++s) {
+      const long long rs = gwarp + static_cast<long long>(s) * total_warps;
+      if (rs < rows) issue_row(s, static_cast<int>(rs));
+    }
+  }
+
   float ag[NE], ab[NE], ac[NE];
 #pragma unroll
   for (int e = 0; e < NE; ++e) { ag[e] = 0.f; ab[e] = 0.f; ac[e] = 0.f; }
   const float inv_d = 1.0f / static_cast<float>(d);
-  const bool has_res = dres != nullptr;
 
-  // software pipeline over this warp's rows: the (still packed) loads of row r + W are in flight while row r is
-  // reduced and written, so each warp keeps two rows of HBM traffic outstanding
-  Raw nx[NCH], ndy[NCH], nres[NCH];
-  auto issue_loads = [&](int r) {
-    const size_t pin = in_map.phys(r), pout = out_map.phys(r);
-#pragma unroll
-    for (int c = 0; c < NCH; ++c) {
-      const int idx = lane + c * 32;
-      const bool ok = idx < nvec;
-      nx[c] = ok ? VecIO<T>::load_raw(x + pin * d + idx * V) : VecIO<T>::zero_raw();
-      ndy[c] = ok ? VecIO<T>::load_raw(dy + pout * d + idx * V) : VecIO<T>::zero_raw();
-      nres[c] = (ok && has_res) ? VecIO<T>::load_raw(dres + pin * d + idx * V) : VecIO<T>::zero_raw();
-    }
-  };
-  int r = gwarp;
-  if (r < rows) issue_loads(r);
-  for (; r < rows; r += total_warps) {
+  int slot = 0;
+  uint32_t phase = 0;
+  for (int r = gwarp; r < rows; r += total_warps) {
     const size_t pin = in_map.phys(r);
     const float mean = mean_in[r], rstd = rstd_in[r];
     float xh[NE], dv[NE];
     Raw cres[NCH];
+    tc::mbar_wait(&bars[slot], phase);
+    {
+      const T* sx = reinterpret_cast<const T*>(ring + static_cast<size_t>(slot) * 3 * row_bytes);
+      const T* sdy = reinterpret_cast<const T*>(reinterpret_cast<const uint8_t*>(sx) + row_bytes);
+      const T* sres = reinterpret_cast<const T*>(reinterpret_cast<const uint8_t*>(sx) + 2 * row_bytes);
 #pragma unroll
-    for (int c = 0; c < NCH; ++c) {
-      VecIO<T>::unpack(nx[c], xh + c * V);
-      VecIO<T>::unpack(ndy[c], dv + c * V);
-      cres[c] = nres[c];
+      for (int c = 0; c < NCH; ++c) {
+        const int idx = lane + c * 32;
+        const bool ok = idx < nvec;
+        const Raw rx = ok ? VecIO<T>::load_raw(sx + idx * V) : VecIO<T>::zero_raw();
+        const Raw rdy = ok ? VecIO<T>::load_raw(sdy + idx * V) : VecIO<T>::zero_raw();
+        cres[c] = (ok && has_res) ? VecIO<T>::load_raw(sres + idx * V) : VecIO<T>::zero_raw();
+        VecIO<T>::unpack(rx, xh + c * V);
+        VecIO<T>::unpack(rdy, dv + c * V);
+      }
     }
-    if (r + total_warps < rows) issue_loads(r + total_warps);
+    __syncwarp();   // every lane has read the slot: refill it with the row `depth` rounds ahead
+    {
+      const long long rn = r + static_cast<long long>(depth) * total_warps;
+      if (lane == 0 && rn < rows) issue_row(slot, static_cast<int>(rn));
+    }
+    if (++slot == depth) { slot = 0; phase ^= 1; }
     float s1 = 0.f, s2 = 0.f;
 #pragma unroll
     for (int c = 0; c < NCH; ++c) {
       const int idx = lane + c * 32;
       if (idx < nvec) {
         float gv[V];
-        VecIO<float>::load(gamma + idx * V, gv);
-        if (V == 8) VecIO<float>::load(gamma + idx * V + 4, gv + 4);
+        VecIO<float>::load(gam + idx * V, gv);
+        if (V == 8) VecIO<float>::load(gam + idx * V + 4, gv + 4);
 #pragma unroll
         for (int j = 0; j < V; ++j) {
           const int e = c * V + j;
@@ -220,13 +304,26 @@ static int launch_ln_bwd(const void* dy, const void* x, const float* mean, const
   // other groups' kernels that run concurrently on forked streams
   int blocks = mb_ceil_div(rows, nwarps * 4);
   if (blocks > 148) blocks = 148;
-  const size_t smem = 3 * static_cast<size_t>(d) * sizeof(float);
+  // shared memory: column partials + gamma + barriers + per-warp row ring (depth slots of x / dy / dres rows)
+  const size_t row_bytes = static_cast<size_t>(d) * sizeof(T);
+  const size_t fixed = 4 * static_cast<size_t>(d) * sizeof(float);
+  int depth = static_cast<int>((200 * 1024 - fixed - 1024) / (nwarps * 3 * row_bytes));
+  if (depth > 4) depth = 4;
+  if (depth < 1) depth = 1;
+  const size_t smem = fixed + static_cast<size_t>(nwarps) * depth * (8 + 3 * row_bytes);
   const int nch = mb_ceil_div(d / V, 32);
 #define MB_LNB(N_)                                                                                              \
   case N_:                                                                                                      \
+    {                                                                                                           \
+      static bool attr_done = false;                                                                            \
+      if (!attr_done) {                                                                                         \
+        cudaFuncSetAttribute(layernorm_bwd_kernel<T, N_>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024); \
+        attr_done = true;                                                                                       \
+      }                                                                                                         \
+    }                                                                                                           \
     layernorm_bwd_kernel<T, N_><<<blocks, LNB_THREADS, smem, st>>>(                                              \
         static_cast<const T*>(dy), static_cast<const T*>(x), mean, rstd, gamma, static_cast<const T*>(dres),    \
-        static_cast<T*>(dx), dgamma, dbeta, dbias, rows, d, im, om);                                            \
+        static_cast<T*>(dx), dgamma, dbeta, dbias, rows, d, im, om, depth);                                     \
     break;
   switch (nch) {
     MB_LNB(1) MB_LNB(2) MB_LNB(3) MB_LNB(4) MB_LNB(5) MB_LNB(6) MB_LNB(7) MB_LNB(8)
