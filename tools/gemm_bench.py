@@ -38,12 +38,68 @@ def cases():
     return out
 
 
+def build(name, layout, M, N, Kd, epi, dev):
+    bf = torch.bfloat16
+    if layout in ("k", "kmn"):
+        A = torch.randn(M, Kd, device=dev).to(bf)
+        C = torch.empty(M, N, device=dev, dtype=bf)
+        if layout == "k":
+            B = torch.randn(N, Kd, device=dev).to(bf)
+            kw = dict(sam=Kd, sak=1, sbn=Kd, sbk=1, ldc=N)
+        else:
+            B = torch.randn(Kd, N, device=dev).to(bf)
+            kw = dict(sam=Kd, sak=1, sbn=1, sbk=N, ldc=N)
+        if epi == "res":
+            kw.update(bias=torch.randn(N, device=dev), residual=torch.randn(M, N, device=dev).to(bf))
+        elif epi == "gelu":
+            kw.update(bias=torch.randn(N, device=dev), aux=torch.empty(M, N, device=dev, dtype=bf), flags=1)
+        elif epi == "dgelu":
+            kw.update(aux=torch.randn(M, N, device=dev).to(bf), flags=2)
+    else:
+        A = torch.randn(Kd, M, device=dev).to(bf)
+        B = torch.randn(Kd, N, device=dev).to(bf)
+        C = torch.zeros(M, N, device=dev)
+        kw = dict(sam=1, sak=M, sbn=1, sbk=N, ldc=N, flags=4)
+    return ((A, B, C, M, N, Kd), kw)
+
+
+def grouped(args):
+    """The step's launches: the same layer of the 4 per-modality stacks as ONE grouped call."""
+    K = Kernels()
+    dev = "cuda"
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    allc = cases()
+    for stack in ("enc", "dec"):
+        kinds = [c[0].split("/")[1] for c in allc if c[0].startswith(f"{stack}_aerial/")]
+        for kind in kinds:
+            if args.only and args.only not in f"{stack}/{kind}":
+                continue
+            probs = [build(*c, dev) for c in allc if c[0].startswith(stack + "_") and c[0].endswith("/" + kind)]
+            fl = sum(2.0 * a[3] * a[4] * a[5] for a, _ in probs)
+            for _ in range(2):
+                K.gemm_grouped(probs)
+            ms = 0.0
+            for _ in range(args.iters):
+                flush.fill_(1)
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                K.gemm_grouped(probs)
+                e1.record()
+                torch.cuda.synchronize()
+                ms += e0.elapsed_time(e1)
+            ms /= args.iters
+            print(f"{stack}/{kind:12s} grouped x{len(probs)}  {ms * 1e3:8.1f} us  {fl / ms / 1e9:7.1f} TFLOP/s", flush=True)
+
+
 def main():
     ap = argparse.ArgumentParser()
+    ap.add_argument("--grouped", action="store_true", help="time the 4-problem grouped launches of the step")
     ap.add_argument("--iters", type=int, default=10)
     ap.add_argument("--only", default="")
     ap.add_argument("--once", action="store_true", help="one launch per shape (for ncu)")
     args = ap.parse_args()
+    if args.grouped:
+        return grouped(args)
     K = Kernels()
     dev = "cuda"
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
