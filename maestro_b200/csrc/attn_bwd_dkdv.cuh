@@ -3,37 +3,48 @@
 
 namespace {
 
+// Software pipeline over SUB-query half tiles j = 0, 1, ...: half j uses TMEM buffer j & 1 (S^T, dP^T), operand
+// buffer j & 1 (P^T, dS^T) and Q / dO stage j % NS.  While the threads run the exp / dS pass of half j, the tensor
+// pipe works on S^T / dP^T of half j + 1 (issued one pass earlier) and on the gradient MMAs of half j - 1, so neither
+// the MMA latency nor the single-thread issue sequence sits between two passes.  Warps 0-3 (thread = key row = TMEM
+// lane) run the passes; one lane of warp 4 issues every TMA load and MMA, driven by mbarriers only.
+constexpr int DKDV_THREADS = 160;
+
 template <int DH>
-__global__ void __launch_bounds__(128) attn_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap tm_qkv128,
-                                                            const __grid_constant__ CUtensorMap tm_qkv64,
-                                                            const __grid_constant__ CUtensorMap tm_do64, BwdArgs args) {
+__global__ void __launch_bounds__(DKDV_THREADS) attn_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap tm_qkv128,
+                                                            const __grid_constant__ CUtensorMap tm_qsub,
+                                                            const __grid_constant__ CUtensorMap tm_dosub, BwdArgs args) {
   using C_ = BCfg<DH>;
-  constexpr int BC = C_::BC;
-  constexpr int OFF_K = 0, OFF_V = C_::ROW_TILE, OFF_Q = 2 * C_::ROW_TILE, OFF_DO = OFF_Q + 2 * C_::COL_TILE;
-  constexpr int OFF_PT = OFF_DO + 2 * C_::COL_TILE, OFF_DST = OFF_PT + C_::A_TILE, OFF_STAT = OFF_DST + C_::A_TILE;
-  constexpr int OFF_BAR = OFF_STAT + 2 * 2 * BC * 4;
+  constexpr int SUB = C_::SUB, NS = C_::NS;
+  constexpr int OFF_K = 0, OFF_V = C_::ROW_TILE, OFF_Q = 2 * C_::ROW_TILE, OFF_DO = OFF_Q + NS * C_::SUB_TILE;
+  constexpr int OFF_PT = OFF_DO + NS * C_::SUB_TILE, OFF_DST = OFF_PT + 2 * C_::AS_TILE;
+  constexpr int OFF_STAT = OFF_DST + 2 * C_::AS_TILE;
+  constexpr int OFF_BAR = OFF_STAT + 2 * 2 * SUB * 4;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
-  float* s_stat = reinterpret_cast<float*>(smem + OFF_STAT);   // [stage][lse2 | delta][64]
+  float* s_stat = reinterpret_cast<float*>(smem + OFF_STAT);   // [j & 1][lse2 | delta][SUB]
   uint64_t* bar_kv = reinterpret_cast<uint64_t*>(smem + OFF_BAR);
-  uint64_t* bar_q = bar_kv + 1;  // [2]
-  uint64_t* bar_s = bar_kv + 3;
-  uint64_t* bar_o = bar_kv + 4;
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bar_kv + 5);
+  uint64_t* bar_q = bar_kv + 1;        // [NS]
+  uint64_t* bar_s = bar_q + NS;        // [2]
+  uint64_t* bar_o = bar_s + 2;         // [2]
+  uint64_t* bar_p = bar_o + 2;         // [2] operand halves P^T / dS^T written (128 arrivals)
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bar_p + 2);
 
   const int tid = threadIdx.x, warp = tid >> 5;
   const int N = args.N, H = args.H, inner = H * DH;
   const int r_tiles = (N + BR - 1) / BR;
   const int rt = blockIdx.x % r_tiles, bh = blockIdx.x / r_tiles;
   const int h = bh % H, b = bh / H;
-  const int c_tiles = (N + BC - 1) / BC;
+  const int n_sub = (N + SUB - 1) / SUB;
 
   if (tid == 0) {
     tc::mbar_init(bar_kv, 1);
-    tc::mbar_init(&bar_q[0], 1);
-    tc::mbar_init(&bar_q[1], 1);
-    tc::mbar_init(bar_s, 1);
-    tc::mbar_init(bar_o, 1);
+    for (int i = 0; i < NS; ++i) tc::mbar_init(&bar_q[i], 1);
+    for (int i = 0; i < 2; ++i) {
+      tc::mbar_init(&bar_s[i], 1);
+      tc::mbar_init(&bar_o[i], 1);
+      tc::mbar_init(&bar_p[i], BR);
+    }
     tc::fence_barrier_init();
   }
   if (warp == 0) {
@@ -44,109 +55,143 @@ __global__ void __launch_bounds__(128) attn_bwd_dkdv_kernel(const __grid_constan
   __syncthreads();
   tc::tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
-  const uint32_t tm_st = tmem_base, tm_dpt = tmem_base + BC, tm_dk = tmem_base + 2 * BC, tm_dv = tmem_base + 2 * BC + DH;
+  // columns: S^T [2][SUB] | dP^T [2][SUB] | dK [DH] | dV [DH]
+  const uint32_t tm_st = tmem_base, tm_dpt = tmem_base + 2 * SUB, tm_dk = tmem_base + 4 * SUB, tm_dv = tm_dk + DH;
   const uint32_t lane_base = static_cast<uint32_t>(warp * 32) << 16;
-  constexpr uint32_t idesc_s = tc::make_idesc_bf16(BR, BC, 0, 0);    // [128 keys] x [64 queries], K = DH
-  constexpr uint32_t idesc_g = tc::make_idesc_bf16(BR, DH, 0, 1);    // [128 keys] x [DH], K = 64 queries (B MN-major)
+  constexpr uint32_t idesc_s = tc::make_idesc_bf16(BR, SUB, 0, 0);   // [128 keys] x [SUB queries], K = DH
+  constexpr uint32_t idesc_g = tc::make_idesc_bf16(BR, DH, 0, 1);    // [128 keys] x [DH], K = SUB queries (B MN-major)
   const uint32_t sK = tc::smem_u32(smem + OFF_K), sV = tc::smem_u32(smem + OFF_V);
   const uint32_t sPT = tc::smem_u32(smem + OFF_PT), sDST = tc::smem_u32(smem + OFF_DST);
+  const uint32_t sQ0 = tc::smem_u32(smem + OFF_Q), sDO0 = tc::smem_u32(smem + OFF_DO);
 
-  auto load_q = [&](int i) {
-    const int st = i & 1;
-    tc::mbar_expect_tx(&bar_q[st], 2 * C_::COL_TILE);
-    tc::tma_load_3d(smem + OFF_Q + st * C_::COL_TILE, &tm_qkv64, &bar_q[st], h * DH, i * BC, b);
-    tc::tma_load_3d(smem + OFF_DO + st * C_::COL_TILE, &tm_do64, &bar_q[st], h * DH, i * BC, b);
+  // the lambdas below run on thread 0 only; `stage` = j % NS is tracked by the caller
+  auto load_q = [&](int j, int stage) {
+    tc::mbar_expect_tx(&bar_q[stage], 2 * C_::SUB_TILE);
+    tc::tma_load_3d(smem + OFF_Q + stage * C_::SUB_TILE, &tm_qsub, &bar_q[stage], h * DH, j * SUB, b);
+    tc::tma_load_3d(smem + OFF_DO + stage * C_::SUB_TILE, &tm_dosub, &bar_q[stage], h * DH, j * SUB, b);
   };
-  auto issue_s = [&](int i) {
-    const uint32_t sQ = tc::smem_u32(smem + OFF_Q + (i & 1) * C_::COL_TILE);
-    const uint32_t sDO = tc::smem_u32(smem + OFF_DO + (i & 1) * C_::COL_TILE);
+  auto issue_s = [&](int j, int stage) {
+    const uint32_t sQ = sQ0 + stage * C_::SUB_TILE, sDO = sDO0 + stage * C_::SUB_TILE;
+    const uint32_t buf = static_cast<uint32_t>(j & 1) * SUB;
 #pragma unroll
     for (int k = 0; k < DH / 16; ++k)
-      tc::umma_bf16(tm_st, tc::make_smem_desc(sK + k * 32, 16, 8 * C_::SW, C_::LT),
+      tc::umma_bf16(tm_st + buf, tc::make_smem_desc(sK + k * 32, 16, 8 * C_::SW, C_::LT),
                     tc::make_smem_desc(sQ + k * 32, 16, 8 * C_::SW, C_::LT), idesc_s, k > 0);
 #pragma unroll
     for (int k = 0; k < DH / 16; ++k)
-      tc::umma_bf16(tm_dpt, tc::make_smem_desc(sV + k * 32, 16, 8 * C_::SW, C_::LT),
+      tc::umma_bf16(tm_dpt + buf, tc::make_smem_desc(sV + k * 32, 16, 8 * C_::SW, C_::LT),
                     tc::make_smem_desc(sDO + k * 32, 16, 8 * C_::SW, C_::LT), idesc_s, k > 0);
-    tc::umma_commit(bar_s);
+    tc::umma_commit(&bar_s[j & 1]);
   };
-  auto issue_grads = [&](int i) {
-    const uint32_t sQ = tc::smem_u32(smem + OFF_Q + (i & 1) * C_::COL_TILE);
-    const uint32_t sDO = tc::smem_u32(smem + OFF_DO + (i & 1) * C_::COL_TILE);
+  auto issue_grads = [&](int j, int stage) {
+    const uint32_t sQ = sQ0 + stage * C_::SUB_TILE, sDO = sDO0 + stage * C_::SUB_TILE;
+    const uint32_t aoff = static_cast<uint32_t>(j & 1) * C_::AS_TILE;
 #pragma unroll
-    for (int k = 0; k < BC / 16; ++k)
-      tc::umma_bf16(tm_dv, tc::make_smem_desc(sPT + k * 32, 16, 8 * C_::A_ROW, C_::A_LT),
-                    tc::make_smem_desc(sDO + k * 16 * C_::SW, 16, 8 * C_::SW, C_::LT), idesc_g, (i > 0 || k > 0));
+    for (int k = 0; k < SUB / 16; ++k)
+      tc::umma_bf16(tm_dv, tc::make_smem_desc(sPT + aoff + k * 32, 16, 8 * C_::AS_ROW, C_::AS_LT),
+                    tc::make_smem_desc(sDO + k * 16 * C_::SW, 16, 8 * C_::SW, C_::LT), idesc_g, (j > 0 || k > 0));
 #pragma unroll
-    for (int k = 0; k < BC / 16; ++k)
-      tc::umma_bf16(tm_dk, tc::make_smem_desc(sDST + k * 32, 16, 8 * C_::A_ROW, C_::A_LT),
-                    tc::make_smem_desc(sQ + k * 16 * C_::SW, 16, 8 * C_::SW, C_::LT), idesc_g, (i > 0 || k > 0));
-    tc::umma_commit(bar_o);
+    for (int k = 0; k < SUB / 16; ++k)
+      tc::umma_bf16(tm_dk, tc::make_smem_desc(sDST + aoff + k * 32, 16, 8 * C_::AS_ROW, C_::AS_LT),
+                    tc::make_smem_desc(sQ + k * 16 * C_::SW, 16, 8 * C_::SW, C_::LT), idesc_g, (j > 0 || k > 0));
+    tc::umma_commit(&bar_o[j & 1]);
   };
 
-  if (tid == 0) {
-    tc::mbar_expect_tx(bar_kv, 2 * C_::ROW_TILE);
-    tc::tma_load_3d(smem + OFF_K, &tm_qkv128, bar_kv, inner + h * DH, rt * BR, b);
-    tc::tma_load_3d(smem + OFF_V, &tm_qkv128, bar_kv, 2 * inner + h * DH, rt * BR, b);
-    load_q(0);
-    if (c_tiles > 1) load_q(1);
-    tc::mbar_wait(bar_kv, 0);
-    tc::mbar_wait(&bar_q[0], 0);
-    tc::tc_fence_after();
-    issue_s(0);
-  }
-
+  if (warp == 4) {
+    // ===================== control lane: TMA loads + every MMA =====================
+    if (tid == 128) {
+      int s_stage = 0, l_stage = 0, g_stage = 0, l_next = 0;
+      uint32_t s_par = 0;
+      tc::mbar_expect_tx(bar_kv, 2 * C_::ROW_TILE);
+      tc::tma_load_3d(smem + OFF_K, &tm_qkv128, bar_kv, inner + h * DH, rt * BR, b);
+      tc::tma_load_3d(smem + OFF_V, &tm_qkv128, bar_kv, 2 * inner + h * DH, rt * BR, b);
+      for (; l_next < NS && l_next < n_sub; ++l_next) {      // fill the ring
+        load_q(l_next, l_stage);
+        if (++l_stage == NS) l_stage = 0;
+      }
+      tc::mbar_wait(bar_kv, 0);
+      for (int j = 0; j < 2 && j < n_sub; ++j) {
+        tc::mbar_wait(&bar_q[s_stage], s_par);
+        tc::tc_fence_after();
+        issue_s(j, s_stage);
+        if (++s_stage == NS) { s_stage = 0; s_par ^= 1; }
+      }
+      for (int j = 0; j < n_sub; ++j) {
+        tc::mbar_wait(&bar_p[j & 1], (j >> 1) & 1);          // P^T / dS^T of half j are in shared memory
+        tc::tc_fence_after();
+        issue_grads(j, g_stage);
+        if (++g_stage == NS) g_stage = 0;
+        if (j + 2 < n_sub) {               // S^T / dP^T of half j + 2 into the TMEM buffer pass j has just drained
+          tc::mbar_wait(&bar_q[s_stage], s_par);
+          tc::tc_fence_after();
+          issue_s(j + 2, s_stage);
+          if (++s_stage == NS) { s_stage = 0; s_par ^= 1; }
+        }
+        if (j >= 1 && l_next < n_sub) {    // the gradient MMAs of half j - 1 (issued a pass ago) free its Q / dO stage
+          tc::mbar_wait(&bar_o[(j - 1) & 1], ((j - 1) >> 1) & 1);
+          load_q(l_next, l_stage);
+          ++l_next;
+          if (++l_stage == NS) l_stage = 0;
+        }
+      }
+    }
+  } else {
+  // ===================== compute warps =====================
   const int row = rt * BR + tid;           // key row owned by this thread
   const bool row_ok = row < N;
   const float c = args.scale_log2, sc = args.scale;
-  uint8_t* pt_row = smem + OFF_PT + tid * C_::A_ROW;
-  uint8_t* dst_row = smem + OFF_DST + tid * C_::A_ROW;
   const size_t stat_base = (static_cast<size_t>(b) * H + h) * N;
 
-  // per-query statistics (log2-domain lse, delta * scale) of tile i live in s_stat[i & 1]; the global loads of tile
-  // i + 1 are issued at the top of iteration i and land in shared memory at its end, so no iteration waits on HBM
+  // per-query statistics (log2-domain lse, delta * scale) of half j live in s_stat[j & 1]; the global loads of half
+  // j + 1 are issued at the top of pass j and land in shared memory at its end, so no pass waits on HBM
   float n_lse = 0.f, n_delta = 0.f;
-  auto fetch_stats = [&](int i) {
-    const int q = i * BC + tid;
-    const bool ok = tid < BC && q < N;
-    n_lse = ok ? args.lse[stat_base + q] * 1.4426950408889634f : 0.f;
-    n_delta = ok ? args.delta[stat_base + q] * sc : 0.f;      // delta pre-multiplied by the score scale
+  auto fetch_stats = [&](int j) {
+    const int q = j * SUB + tid;
+    const bool ok = tid < SUB && q < N;
+    n_lse = ok ? args.lse[stat_base + q] : 0.f;               // raw: nothing may wait on these loads before put_stats
+    n_delta = ok ? args.delta[stat_base + q] : 0.f;
   };
-  auto put_stats = [&](int i) {
-    if (tid < BC) {
-      float* d = s_stat + (i & 1) * 2 * BC;
-      d[tid] = n_lse;
-      d[BC + tid] = n_delta;
+  auto put_stats = [&](int j) {
+    if (tid < SUB) {
+      float* d = s_stat + (j & 1) * 2 * SUB;
+      d[tid] = n_lse * 1.4426950408889634f;
+      d[SUB + tid] = n_delta * sc;                            // delta pre-multiplied by the score scale
     }
   };
   fetch_stats(0);
   put_stats(0);
-  __syncthreads();
-
-  for (int i = 0; i < c_tiles; ++i) {
-    float* st = s_stat + (i & 1) * 2 * BC;
-    if (i + 1 < c_tiles) fetch_stats(i + 1);
-    tc::mbar_wait(bar_s, i & 1);
-    tc::tc_fence_after();
-    if (i > 0) {
-      tc::mbar_wait(bar_o, (i - 1) & 1);   // gradient MMAs of tile i-1 done: P^T / dS^T buffers, Q/dO stage free
-      if (tid == 0 && i + 1 < c_tiles) load_q(i + 1);
+  asm volatile("bar.sync 1, 128;" ::: "memory");
+  for (int j = 0; j < n_sub; ++j) {
+    const int bufi = j & 1;
+    const uint32_t st = tc::smem_u32(s_stat + bufi * 2 * SUB);
+    const uint32_t pt_row = sPT + bufi * C_::AS_TILE + tid * C_::AS_ROW;
+    const uint32_t dst_row = sDST + bufi * C_::AS_TILE + tid * C_::AS_ROW;
+    if (j + 1 < n_sub) fetch_stats(j + 1);
+    float4 lsv[SUB / 4], dsv[SUB / 4];                        // this half's statistics: in registers before S^T lands
+#pragma unroll
+    for (int q4 = 0; q4 < SUB / 4; ++q4) {
+      lsv[q4] = lds_f4(st + q4 * 16);
+      dsv[q4] = lds_f4(st + (SUB + q4 * 4) * 4);
     }
+    tc::mbar_wait(&bar_s[bufi], (j >> 1) & 1);
+    if (j >= 2) tc::mbar_wait(&bar_o[bufi], ((j - 2) >> 1) & 1);   // gradient MMAs of half j - 2 have read `bufi`
+    tc::tc_fence_after();
     // P^T and dS^T.  No masks: queries past N are zero rows of Q and dO (TMA zero fill), so their columns multiply
     // zero rows in dV += P^T dO and dK += dS^T Q; key rows past N are never stored.  st[] holds finite values there.
-#pragma unroll
-    for (int ch = 0; ch < BC / 32; ++ch) {
-      uint32_t s[32], dp[32];
-      tc::tmem_ld_32x32(tm_st + lane_base + ch * 32, s);
-      tc::tmem_ld_32x32(tm_dpt + lane_base + ch * 32, dp);
+    {
+      uint32_t s[SUB], dp[SUB];
+      if constexpr (SUB == 32) {
+        tc::tmem_ld_32x32(tm_st + lane_base + bufi * SUB, s);
+        tc::tmem_ld_32x32(tm_dpt + lane_base + bufi * SUB, dp);
+      } else {
+        tc::tmem_ld_32x16(tm_st + lane_base + bufi * SUB, s);
+        tc::tmem_ld_32x16(tm_dpt + lane_base + bufi * SUB, dp);
+      }
       tc::tmem_ld_wait();
 #pragma unroll
-      for (int v8 = 0; v8 < 4; ++v8) {
+      for (int v8 = 0; v8 < SUB / 8; ++v8) {
         uint32_t wp[4], wd[4];
-        const int q0 = ch * 32 + v8 * 8;
-        const float4 l0 = *reinterpret_cast<const float4*>(st + q0), l1 = *reinterpret_cast<const float4*>(st + q0 + 4);
-        const float4 e0 = *reinterpret_cast<const float4*>(st + BC + q0);
-        const float4 e1 = *reinterpret_cast<const float4*>(st + BC + q0 + 4);
+        const float4 l0 = lsv[2 * v8], l1 = lsv[2 * v8 + 1], e0 = dsv[2 * v8], e1 = dsv[2 * v8 + 1];
         const float ls[8] = {l0.x, l0.y, l0.z, l0.w, l1.x, l1.y, l1.z, l1.w};
         const float ds[8] = {e0.x, e0.y, e0.z, e0.w, e1.x, e1.y, e1.z, e1.w};
 #pragma unroll
@@ -164,25 +209,17 @@ __global__ void __launch_bounds__(128) attn_bwd_dkdv_kernel(const __grid_constan
           wp[k2] = *reinterpret_cast<uint32_t*>(&hp);
           wd[k2] = *reinterpret_cast<uint32_t*>(&hd);
         }
-        store_a_chunk<BC>(pt_row, tid, ch * 4 + v8, wp);
-        store_a_chunk<BC>(dst_row, tid, ch * 4 + v8, wd);
+        store_a_chunk_s<SUB>(pt_row, tid, v8, wp);
+        store_a_chunk_s<SUB>(dst_row, tid, v8, wd);
       }
     }
-    if (i + 1 < c_tiles) put_stats(i + 1);
+    if (j + 1 < n_sub) put_stats(j + 1);
     tc::fence_proxy_async();
     tc::tc_fence_before();
-    __syncthreads();
-    if (tid == 0) {
-      tc::tc_fence_after();
-      issue_grads(i);
-      if (i + 1 < c_tiles) {
-        tc::mbar_wait(&bar_q[(i + 1) & 1], ((i + 1) >> 1) & 1);
-        tc::tc_fence_after();
-        issue_s(i + 1);
-      }
-    }
+    tc::mbar_arrive(&bar_p[bufi]);
+    asm volatile("bar.sync 1, 128;" ::: "memory");   // next half's statistics are visible to the four warps
   }
-  tc::mbar_wait(bar_o, (c_tiles - 1) & 1);
+  tc::mbar_wait(&bar_o[(n_sub - 1) & 1], ((n_sub - 1) >> 1) & 1);   // a commit covers every MMA issued before it
   tc::tc_fence_after();
   bf16* out = args.dqkv + (static_cast<size_t>(b) * N + (row_ok ? row : 0)) * 3 * inner + h * DH;
 #pragma unroll
@@ -203,6 +240,7 @@ __global__ void __launch_bounds__(128) attn_bwd_dkdv_kernel(const __grid_constan
       }
     }
   }
+  }  // compute warps
   tc::tc_fence_before();
   __syncthreads();
   if (warp == 0) tc::tmem_dealloc(tmem_base, C_::TMEM_DKDV);
@@ -219,12 +257,13 @@ template <int DH>
 int launch_bwd(const void* qkv, const void* o, const void* d_o, const float* lse, void* dqkv, float* delta, int Bn,
                int N, int H, cudaStream_t st) {
   using C_ = BCfg<DH>;
-  CUtensorMap q128, q64, do128, do64;
+  CUtensorMap q128, q64, do128, qsub, dosub;
   int rc;
   if ((rc = tmap3(&q128, qkv, Bn, N, 3 * H * DH, DH, BR)) != 0) return rc;
   if ((rc = tmap3(&q64, qkv, Bn, N, 3 * H * DH, DH, C_::BC)) != 0) return rc;
   if ((rc = tmap3(&do128, d_o, Bn, N, H * DH, DH, BR)) != 0) return rc;
-  if ((rc = tmap3(&do64, d_o, Bn, N, H * DH, DH, C_::BC)) != 0) return rc;
+  if ((rc = tmap3(&qsub, qkv, Bn, N, 3 * H * DH, DH, C_::SUB)) != 0) return rc;
+  if ((rc = tmap3(&dosub, d_o, Bn, N, H * DH, DH, C_::SUB)) != 0) return rc;
   BwdArgs a;
   a.o = static_cast<const bf16*>(o);
   a.d_o = static_cast<const bf16*>(d_o);
@@ -236,7 +275,7 @@ int launch_bwd(const void* qkv, const void* o, const void* d_o, const float* lse
   a.scale = 1.0f / sqrtf(static_cast<float>(DH));
   a.scale_log2 = a.scale * 1.4426950408889634f;
   constexpr int SMEM_DQ = 2 * C_::ROW_TILE + 4 * C_::COL_TILE + C_::A_TILE + 128 + 1024;
-  constexpr int SMEM_DKDV = 2 * C_::ROW_TILE + 4 * C_::COL_TILE + 2 * C_::A_TILE + 2 * 2 * C_::BC * 4 + 128 + 1024;
+  constexpr int SMEM_DKDV = 2 * C_::ROW_TILE + 2 * C_::NS * C_::SUB_TILE + 4 * C_::AS_TILE + 2 * 2 * C_::SUB * 4 + 128 + 1024;
   static bool attr = false;
   if (!attr) {
     cudaFuncSetAttribute(attn_bwd_dq_kernel<DH>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_DQ);
@@ -245,7 +284,7 @@ int launch_bwd(const void* qkv, const void* o, const void* d_o, const float* lse
   }
   const int grid = Bn * H * ((N + BR - 1) / BR);
   attn_bwd_dq_kernel<DH><<<grid, 128, SMEM_DQ, st>>>(q128, q64, do128, a);
-  attn_bwd_dkdv_kernel<DH><<<grid, 128, SMEM_DKDV, st>>>(q128, q64, do64, a);
+  attn_bwd_dkdv_kernel<DH><<<grid, DKDV_THREADS, SMEM_DKDV, st>>>(q128, qsub, dosub, a);
   cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? 0 : static_cast<int>(e);
 }

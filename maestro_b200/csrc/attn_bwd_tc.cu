@@ -25,6 +25,14 @@ template <int DH> struct BCfg {
   static constexpr int A_TILE = BR * A_ROW;      // K-major, swizzle span = row bytes (128 B or 64 B)
   static constexpr uint32_t LT = tc::layout_type_for(SW);
   static constexpr uint32_t A_LT = tc::layout_type_for(A_ROW);
+  // dK / dV kernel: the inner tile is walked as two SUB-query halves with double-buffered S^T / dP^T accumulators and
+  // P^T / dS^T operand buffers, so that the MMAs of one half run under the exp / dS pass of the other
+  static constexpr int SUB = BC / 2;
+  static constexpr int SUB_TILE = SUB * DH * 2;  // [SUB, DH] Q / dO stage
+  static constexpr int NS = DH >= 64 ? 5 : 6;    // Q / dO stages in flight (TMA latency spans ~3 half-tile passes)
+  static constexpr int AS_ROW = SUB * 2;         // row bytes of the [128, SUB] bf16 operand halves
+  static constexpr int AS_TILE = BR * AS_ROW;
+  static constexpr uint32_t AS_LT = tc::layout_type_for(AS_ROW);
   static constexpr int TMEM_DQ = (2 * BC + DH <= 128) ? 128 : 256;
   static constexpr int TMEM_DKDV = (2 * BC + 2 * DH <= 128) ? 128 : 256;
 };
@@ -43,8 +51,21 @@ struct BwdArgs {
 // 64 B: chunk ^ (row / 2) % 4)
 template <int BCc>
 __device__ __forceinline__ void store_a_chunk(uint8_t* row_base, int tid, int c16, const uint32_t* w) {
-  const int x = BCc == 64 ? (tid & 7) : ((tid >> 1) & 3);
+  // swizzle span = row bytes: 128 B: chunk ^ row % 8; 64 B: chunk ^ (row / 2) % 4; 32 B: chunk ^ (row / 4) % 2
+  const int x = BCc == 64 ? (tid & 7) : (BCc == 32 ? ((tid >> 1) & 3) : ((tid >> 2) & 1));
   *reinterpret_cast<uint4*>(row_base + ((c16 ^ x) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
+}
+// the same with a shared-window address (st.shared instead of a generic store)
+template <int BCc>
+__device__ __forceinline__ void store_a_chunk_s(uint32_t row_base, int tid, int c16, const uint32_t* w) {
+  const int x = BCc == 64 ? (tid & 7) : (BCc == 32 ? ((tid >> 1) & 3) : ((tid >> 2) & 1));
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(row_base + ((c16 ^ x) << 4)), "r"(w[0]), "r"(w[1]),
+               "r"(w[2]), "r"(w[3]) : "memory");
+}
+__device__ __forceinline__ float4 lds_f4(uint32_t addr) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr) : "memory");
+  return v;
 }
 
 // ------------------------------------------------------------------------------------------------ dQ
