@@ -257,10 +257,9 @@ template <int DH>
 int launch_bwd(const void* qkv, const void* o, const void* d_o, const float* lse, void* dqkv, float* delta, int Bn,
                int N, int H, cudaStream_t st) {
   using C_ = BCfg<DH>;
-  CUtensorMap q128, q64, do128, qsub, dosub;
+  CUtensorMap q128, do128, qsub, dosub;
   int rc;
   if ((rc = tmap3(&q128, qkv, Bn, N, 3 * H * DH, DH, BR)) != 0) return rc;
-  if ((rc = tmap3(&q64, qkv, Bn, N, 3 * H * DH, DH, C_::BC)) != 0) return rc;
   if ((rc = tmap3(&do128, d_o, Bn, N, H * DH, DH, BR)) != 0) return rc;
   if ((rc = tmap3(&qsub, qkv, Bn, N, 3 * H * DH, DH, C_::SUB)) != 0) return rc;
   if ((rc = tmap3(&dosub, d_o, Bn, N, H * DH, DH, C_::SUB)) != 0) return rc;
@@ -274,7 +273,7 @@ int launch_bwd(const void* qkv, const void* o, const void* d_o, const float* lse
   a.H = H;
   a.scale = 1.0f / sqrtf(static_cast<float>(DH));
   a.scale_log2 = a.scale * 1.4426950408889634f;
-  constexpr int SMEM_DQ = 2 * C_::ROW_TILE + 4 * C_::COL_TILE + C_::A_TILE + 128 + 1024;
+  constexpr int SMEM_DQ = 2 * C_::ROW_TILE + 2 * C_::NS * C_::SUB_TILE + 2 * C_::AS_TILE + 128 + 1024;
   constexpr int SMEM_DKDV = 2 * C_::ROW_TILE + 2 * C_::NS * C_::SUB_TILE + 4 * C_::AS_TILE + 2 * 2 * C_::SUB * 4 + 128 + 1024;
   static bool attr = false;
   if (!attr) {
@@ -283,7 +282,7 @@ int launch_bwd(const void* qkv, const void* o, const void* d_o, const float* lse
     attr = true;
   }
   const int grid = Bn * H * ((N + BR - 1) / BR);
-  attn_bwd_dq_kernel<DH><<<grid, 128, SMEM_DQ, st>>>(q128, q64, do128, a);
+  attn_bwd_dq_kernel<DH><<<grid, DQ_THREADS, SMEM_DQ, st>>>(q128, qsub, do128, a);
   attn_bwd_dkdv_kernel<DH><<<grid, DKDV_THREADS, SMEM_DKDV, st>>>(q128, qsub, dosub, a);
   cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? 0 : static_cast<int>(e);

@@ -1,8 +1,8 @@
 // Backward of the fused attention on tcgen05 (see attn_tc.cu for layouts).  Two kernels, no atomics:
-//   dq kernel    one CTA per (sample, head, 128-query tile), loops over 64-key tiles:
+//   dq kernel    one CTA per (sample, head, 128-query tile), loops over key tiles (two half tiles in flight):
 //                S = Q K^T, dP = dO V^T (TMEM) -> dS = P * (dP - delta) * scale (bf16, smem) -> dQ += dS K (TMEM).
 //                Also emits delta[row] = sum_d dO * O for the second kernel.
-//   dkdv kernel  one CTA per (sample, head, 128-key tile), loops over 64-query tiles:
+//   dkdv kernel  one CTA per (sample, head, 128-key tile), loops over query tiles (two half tiles in flight):
 //                S^T = K Q^T, dP^T = V dO^T (TMEM) -> P^T, dS^T (bf16, smem) -> dV += P^T dO, dK += dS^T Q (TMEM).
 // Thread t owns TMEM lane t (a query row in the first kernel, a key row in the second); P is recomputed from
 // the saved log-sum-exp, so nothing of size N x N ever touches HBM.
@@ -20,13 +20,9 @@ template <int DH> struct BCfg {
   static constexpr int BC = DH <= 32 ? 32 : 64;
   static constexpr int SW = DH * 2;
   static constexpr int ROW_TILE = BR * DH * 2;   // [128, DH]
-  static constexpr int COL_TILE = BC * DH * 2;   // [BC, DH]
-  static constexpr int A_ROW = BC * 2;           // row bytes of the [128, BC] bf16 tiles written by the threads
-  static constexpr int A_TILE = BR * A_ROW;      // K-major, swizzle span = row bytes (128 B or 64 B)
   static constexpr uint32_t LT = tc::layout_type_for(SW);
-  static constexpr uint32_t A_LT = tc::layout_type_for(A_ROW);
-  // dK / dV kernel: the inner tile is walked as two SUB-query halves with double-buffered S^T / dP^T accumulators and
-  // P^T / dS^T operand buffers, so that the MMAs of one half run under the exp / dS pass of the other
+  // the inner tile is walked as two SUB-wide halves with double-buffered score accumulators and bf16 operand buffers
+  // (K-major, swizzle span = row bytes), so that the MMAs of one half run under the exp / dS pass of the other
   static constexpr int SUB = BC / 2;
   static constexpr int SUB_TILE = SUB * DH * 2;  // [SUB, DH] Q / dO stage
   static constexpr int NS = DH >= 64 ? 5 : 6;    // Q / dO stages in flight (TMA latency spans ~3 half-tile passes)
@@ -48,14 +44,7 @@ struct BwdArgs {
 };
 
 // 16-byte chunk c16 of row `tid` of a K-major [128, BCc] tile whose swizzle span equals its row (128 B: chunk ^ row % 8;
-// 64 B: chunk ^ (row / 2) % 4)
-template <int BCc>
-__device__ __forceinline__ void store_a_chunk(uint8_t* row_base, int tid, int c16, const uint32_t* w) {
-  // swizzle span = row bytes: 128 B: chunk ^ row % 8; 64 B: chunk ^ (row / 2) % 4; 32 B: chunk ^ (row / 4) % 2
-  const int x = BCc == 64 ? (tid & 7) : (BCc == 32 ? ((tid >> 1) & 3) : ((tid >> 2) & 1));
-  *reinterpret_cast<uint4*>(row_base + ((c16 ^ x) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
-}
-// the same with a shared-window address (st.shared instead of a generic store)
+// 64 B: chunk ^ (row / 2) % 4; 32 B: chunk ^ (row / 4) % 2)
 template <int BCc>
 __device__ __forceinline__ void store_a_chunk_s(uint32_t row_base, int tid, int c16, const uint32_t* w) {
   const int x = BCc == 64 ? (tid & 7) : (BCc == 32 ? ((tid >> 1) & 3) : ((tid >> 2) & 1));
@@ -69,35 +58,44 @@ __device__ __forceinline__ float4 lds_f4(uint32_t addr) {
 }
 
 // ------------------------------------------------------------------------------------------------ dQ
+// Same software pipeline as the dK / dV kernel (attn_bwd_dkdv.cuh): SUB-key half tiles, S / dP accumulators and the dS
+// operand double-buffered, K / V halves in an NS-stage TMA ring, warps 0-3 = query rows, one lane of warp 4 issues
+// every TMA load and MMA.
+constexpr int DQ_THREADS = 160;
+
 template <int DH>
-__global__ void __launch_bounds__(128) attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_qkv128,
-                                                          const __grid_constant__ CUtensorMap tm_qkv64,
-                                                          const __grid_constant__ CUtensorMap tm_do128, BwdArgs args) {
+__global__ void __launch_bounds__(DQ_THREADS) attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_qkv128,
+                                                                 const __grid_constant__ CUtensorMap tm_qsub,
+                                                                 const __grid_constant__ CUtensorMap tm_do128,
+                                                                 BwdArgs args) {
   using C_ = BCfg<DH>;
-  constexpr int BC = C_::BC;
-  constexpr int OFF_Q = 0, OFF_DO = C_::ROW_TILE, OFF_K = 2 * C_::ROW_TILE, OFF_V = OFF_K + 2 * C_::COL_TILE;
-  constexpr int OFF_DS = OFF_V + 2 * C_::COL_TILE, OFF_BAR = OFF_DS + C_::A_TILE;
+  constexpr int SUB = C_::SUB, NS = C_::NS;
+  constexpr int OFF_Q = 0, OFF_DO = C_::ROW_TILE, OFF_K = 2 * C_::ROW_TILE, OFF_V = OFF_K + NS * C_::SUB_TILE;
+  constexpr int OFF_DS = OFF_V + NS * C_::SUB_TILE, OFF_BAR = OFF_DS + 2 * C_::AS_TILE;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
   uint64_t* bar_q = reinterpret_cast<uint64_t*>(smem + OFF_BAR);
-  uint64_t* bar_kv = bar_q + 1;  // [2]
-  uint64_t* bar_s = bar_q + 3;
-  uint64_t* bar_o = bar_q + 4;
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bar_q + 5);
+  uint64_t* bar_kv = bar_q + 1;        // [NS]
+  uint64_t* bar_s = bar_kv + NS;       // [2]
+  uint64_t* bar_o = bar_s + 2;         // [2]
+  uint64_t* bar_p = bar_o + 2;         // [2] dS half written (128 arrivals)
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bar_p + 2);
 
   const int tid = threadIdx.x, warp = tid >> 5;
   const int N = args.N, H = args.H, inner = H * DH;
   const int r_tiles = (N + BR - 1) / BR;
   const int rt = blockIdx.x % r_tiles, bh = blockIdx.x / r_tiles;
   const int h = bh % H, b = bh / H;
-  const int c_tiles = (N + BC - 1) / BC;
+  const int n_sub = (N + SUB - 1) / SUB;
 
   if (tid == 0) {
     tc::mbar_init(bar_q, 1);
-    tc::mbar_init(&bar_kv[0], 1);
-    tc::mbar_init(&bar_kv[1], 1);
-    tc::mbar_init(bar_s, 1);
-    tc::mbar_init(bar_o, 1);
+    for (int i = 0; i < NS; ++i) tc::mbar_init(&bar_kv[i], 1);
+    for (int i = 0; i < 2; ++i) {
+      tc::mbar_init(&bar_s[i], 1);
+      tc::mbar_init(&bar_o[i], 1);
+      tc::mbar_init(&bar_p[i], BR);
+    }
     tc::fence_barrier_init();
   }
   if (warp == 0) {
@@ -108,91 +106,122 @@ __global__ void __launch_bounds__(128) attn_bwd_dq_kernel(const __grid_constant_
   __syncthreads();
   tc::tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
-  const uint32_t tm_s = tmem_base, tm_dp = tmem_base + BC, tm_dq = tmem_base + 2 * BC;
+  // columns: S [2][SUB] | dP [2][SUB] | dQ [DH]
+  const uint32_t tm_s = tmem_base, tm_dp = tmem_base + 2 * SUB, tm_dq = tmem_base + 4 * SUB;
   const uint32_t lane_base = static_cast<uint32_t>(warp * 32) << 16;
-  constexpr uint32_t idesc_s = tc::make_idesc_bf16(BR, BC, 0, 0);
+  constexpr uint32_t idesc_s = tc::make_idesc_bf16(BR, SUB, 0, 0);
   constexpr uint32_t idesc_dq = tc::make_idesc_bf16(BR, DH, 0, 1);
   const uint32_t sQ = tc::smem_u32(smem + OFF_Q), sDO = tc::smem_u32(smem + OFF_DO), sDS = tc::smem_u32(smem + OFF_DS);
+  const uint32_t sK0 = tc::smem_u32(smem + OFF_K), sV0 = tc::smem_u32(smem + OFF_V);
 
-  auto load_kv = [&](int j) {
-    const int st = j & 1;
-    tc::mbar_expect_tx(&bar_kv[st], 2 * C_::COL_TILE);
-    tc::tma_load_3d(smem + OFF_K + st * C_::COL_TILE, &tm_qkv64, &bar_kv[st], inner + h * DH, j * BC, b);
-    tc::tma_load_3d(smem + OFF_V + st * C_::COL_TILE, &tm_qkv64, &bar_kv[st], 2 * inner + h * DH, j * BC, b);
+  auto load_kv = [&](int j, int stage) {
+    tc::mbar_expect_tx(&bar_kv[stage], 2 * C_::SUB_TILE);
+    tc::tma_load_3d(smem + OFF_K + stage * C_::SUB_TILE, &tm_qsub, &bar_kv[stage], inner + h * DH, j * SUB, b);
+    tc::tma_load_3d(smem + OFF_V + stage * C_::SUB_TILE, &tm_qsub, &bar_kv[stage], 2 * inner + h * DH, j * SUB, b);
   };
-  auto issue_s_dp = [&](int j) {
-    const uint32_t sK = tc::smem_u32(smem + OFF_K + (j & 1) * C_::COL_TILE);
-    const uint32_t sV = tc::smem_u32(smem + OFF_V + (j & 1) * C_::COL_TILE);
+  auto issue_s_dp = [&](int j, int stage) {
+    const uint32_t sK = sK0 + stage * C_::SUB_TILE, sV = sV0 + stage * C_::SUB_TILE;
+    const uint32_t buf = static_cast<uint32_t>(j & 1) * SUB;
 #pragma unroll
     for (int k = 0; k < DH / 16; ++k)
-      tc::umma_bf16(tm_s, tc::make_smem_desc(sQ + k * 32, 16, 8 * C_::SW, C_::LT),
+      tc::umma_bf16(tm_s + buf, tc::make_smem_desc(sQ + k * 32, 16, 8 * C_::SW, C_::LT),
                     tc::make_smem_desc(sK + k * 32, 16, 8 * C_::SW, C_::LT), idesc_s, k > 0);
 #pragma unroll
     for (int k = 0; k < DH / 16; ++k)
-      tc::umma_bf16(tm_dp, tc::make_smem_desc(sDO + k * 32, 16, 8 * C_::SW, C_::LT),
+      tc::umma_bf16(tm_dp + buf, tc::make_smem_desc(sDO + k * 32, 16, 8 * C_::SW, C_::LT),
                     tc::make_smem_desc(sV + k * 32, 16, 8 * C_::SW, C_::LT), idesc_s, k > 0);
-    tc::umma_commit(bar_s);
+    tc::umma_commit(&bar_s[j & 1]);
   };
-  auto issue_dq = [&](int j) {
-    const uint32_t sK = tc::smem_u32(smem + OFF_K + (j & 1) * C_::COL_TILE);
+  auto issue_dq = [&](int j, int stage) {
+    const uint32_t sK = sK0 + stage * C_::SUB_TILE;
+    const uint32_t aoff = static_cast<uint32_t>(j & 1) * C_::AS_TILE;
 #pragma unroll
-    for (int k = 0; k < BC / 16; ++k)
-      tc::umma_bf16(tm_dq, tc::make_smem_desc(sDS + k * 32, 16, 8 * C_::A_ROW, C_::A_LT),
+    for (int k = 0; k < SUB / 16; ++k)
+      tc::umma_bf16(tm_dq, tc::make_smem_desc(sDS + aoff + k * 32, 16, 8 * C_::AS_ROW, C_::AS_LT),
                     tc::make_smem_desc(sK + k * 16 * C_::SW, 16, 8 * C_::SW, C_::LT), idesc_dq, (j > 0 || k > 0));
-    tc::umma_commit(bar_o);
+    tc::umma_commit(&bar_o[j & 1]);
   };
 
-  if (tid == 0) {
-    tc::mbar_expect_tx(bar_q, 2 * C_::ROW_TILE);
-    tc::tma_load_3d(smem + OFF_Q, &tm_qkv128, bar_q, h * DH, rt * BR, b);
-    tc::tma_load_3d(smem + OFF_DO, &tm_do128, bar_q, h * DH, rt * BR, b);
-    load_kv(0);
-    if (c_tiles > 1) load_kv(1);
-    tc::mbar_wait(bar_q, 0);
-    tc::mbar_wait(&bar_kv[0], 0);
-    tc::tc_fence_after();
-    issue_s_dp(0);
-  }
-
-  // per-row constants: lse (log2 domain) and delta = sum_d dO * O
-  const int row = rt * BR + tid;
-  const bool row_ok = row < N;
-  float lse2 = 0.f, delta = 0.f;
-  if (row_ok) {
-    const size_t ro = (static_cast<size_t>(b) * N + row) * inner + h * DH;
-#pragma unroll
-    for (int v8 = 0; v8 < DH / 8; ++v8) {
-      float a[8], g[8];
-      VecIO<bf16>::load(args.o + ro + v8 * 8, a);
-      VecIO<bf16>::load(args.d_o + ro + v8 * 8, g);
-#pragma unroll
-      for (int i = 0; i < 8; ++i) delta = fmaf(a[i], g[i], delta);
+  if (warp == 4) {
+    // ===================== control lane: TMA loads + every MMA =====================
+    if (tid == 128) {
+      int s_stage = 0, l_stage = 0, g_stage = 0, l_next = 0;
+      uint32_t s_par = 0;
+      tc::mbar_expect_tx(bar_q, 2 * C_::ROW_TILE);
+      tc::tma_load_3d(smem + OFF_Q, &tm_qkv128, bar_q, h * DH, rt * BR, b);
+      tc::tma_load_3d(smem + OFF_DO, &tm_do128, bar_q, h * DH, rt * BR, b);
+      for (; l_next < NS && l_next < n_sub; ++l_next) {      // fill the ring
+        load_kv(l_next, l_stage);
+        if (++l_stage == NS) l_stage = 0;
+      }
+      tc::mbar_wait(bar_q, 0);
+      for (int j = 0; j < 2 && j < n_sub; ++j) {
+        tc::mbar_wait(&bar_kv[s_stage], s_par);
+        tc::tc_fence_after();
+        issue_s_dp(j, s_stage);
+        if (++s_stage == NS) { s_stage = 0; s_par ^= 1; }
+      }
+      for (int j = 0; j < n_sub; ++j) {
+        tc::mbar_wait(&bar_p[j & 1], (j >> 1) & 1);          // dS of half j is in shared memory
+        tc::tc_fence_after();
+        issue_dq(j, g_stage);
+        if (++g_stage == NS) g_stage = 0;
+        if (j + 2 < n_sub) {               // S / dP of half j + 2 into the TMEM buffer pass j has just drained
+          tc::mbar_wait(&bar_kv[s_stage], s_par);
+          tc::tc_fence_after();
+          issue_s_dp(j + 2, s_stage);
+          if (++s_stage == NS) { s_stage = 0; s_par ^= 1; }
+        }
+        if (j >= 1 && l_next < n_sub) {    // the dQ MMA of half j - 1 (issued a pass ago) frees its K / V stage
+          tc::mbar_wait(&bar_o[(j - 1) & 1], ((j - 1) >> 1) & 1);
+          load_kv(l_next, l_stage);
+          ++l_next;
+          if (++l_stage == NS) l_stage = 0;
+        }
+      }
     }
-    const size_t li = (static_cast<size_t>(b) * H + h) * N + row;
-    lse2 = args.lse[li] * 1.4426950408889634f;
-    args.delta[li] = delta;
-  }
-  const float c = args.scale_log2, sc = args.scale;
-  const float delta_sc = delta * sc;
-  uint8_t* ds_row = smem + OFF_DS + tid * C_::A_ROW;
-
-  for (int j = 0; j < c_tiles; ++j) {
-    tc::mbar_wait(bar_s, j & 1);
-    tc::tc_fence_after();
-    if (j > 0) {
-      tc::mbar_wait(bar_o, (j - 1) & 1);           // dQ MMA of tile j-1 done: dS buffer and K/V stage free
-      if (tid == 0 && j + 1 < c_tiles) load_kv(j + 1);
-    }
-    // dS = P * (dP - delta) * scale.  No masks: keys past N are zero rows of K and V, so whatever lands in their dS
-    // columns multiplies zero rows of K in dQ += dS K; query rows past N are never stored.
+  } else {
+    // ===================== compute warps: thread = query row =====================
+    // per-row constants: lse (log2 domain) and delta = sum_d dO * O
+    const int row = rt * BR + tid;
+    const bool row_ok = row < N;
+    float lse2 = 0.f, delta = 0.f;
+    if (row_ok) {
+      const size_t ro = (static_cast<size_t>(b) * N + row) * inner + h * DH;
 #pragma unroll
-    for (int ch = 0; ch < BC / 32; ++ch) {
-      uint32_t s[32], dp[32];
-      tc::tmem_ld_32x32(tm_s + lane_base + ch * 32, s);
-      tc::tmem_ld_32x32(tm_dp + lane_base + ch * 32, dp);
+      for (int v8 = 0; v8 < DH / 8; ++v8) {
+        float a[8], g[8];
+        VecIO<bf16>::load(args.o + ro + v8 * 8, a);
+        VecIO<bf16>::load(args.d_o + ro + v8 * 8, g);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) delta = fmaf(a[i], g[i], delta);
+      }
+      const size_t li = (static_cast<size_t>(b) * H + h) * N + row;
+      lse2 = args.lse[li] * 1.4426950408889634f;
+      args.delta[li] = delta;
+    }
+    const float c = args.scale_log2, sc = args.scale;
+    const float delta_sc = delta * sc;
+
+    for (int j = 0; j < n_sub; ++j) {
+      const int bufi = j & 1;
+      const uint32_t ds_row = sDS + bufi * C_::AS_TILE + tid * C_::AS_ROW;
+      tc::mbar_wait(&bar_s[bufi], (j >> 1) & 1);
+      if (j >= 2) tc::mbar_wait(&bar_o[bufi], ((j - 2) >> 1) & 1);   // the dQ MMA of half j - 2 has read `bufi`
+      tc::tc_fence_after();
+      // dS = P * (dP - delta) * scale.  No masks: keys past N are zero rows of K and V, so whatever lands in their
+      // dS columns multiplies zero rows of K in dQ += dS K; query rows past N are never stored.
+      uint32_t s[SUB], dp[SUB];
+      if constexpr (SUB == 32) {
+        tc::tmem_ld_32x32(tm_s + lane_base + bufi * SUB, s);
+        tc::tmem_ld_32x32(tm_dp + lane_base + bufi * SUB, dp);
+      } else {
+        tc::tmem_ld_32x16(tm_s + lane_base + bufi * SUB, s);
+        tc::tmem_ld_32x16(tm_dp + lane_base + bufi * SUB, dp);
+      }
       tc::tmem_ld_wait();
 #pragma unroll
-      for (int v8 = 0; v8 < 4; ++v8) {
+      for (int v8 = 0; v8 < SUB / 8; ++v8) {
         uint32_t w[4];
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
@@ -206,25 +235,14 @@ __global__ void __launch_bounds__(128) attn_bwd_dq_kernel(const __grid_constant_
           __nv_bfloat162 hb = __floats2bfloat162_rn(d2[0], d2[1]);
           w[i] = *reinterpret_cast<uint32_t*>(&hb);
         }
-        store_a_chunk<BC>(ds_row, tid, ch * 4 + v8, w);
+        store_a_chunk_s<SUB>(ds_row, tid, v8, w);
       }
+      tc::fence_proxy_async();
+      tc::tc_fence_before();
+      tc::mbar_arrive(&bar_p[bufi]);
     }
-    tc::fence_proxy_async();
-    tc::tc_fence_before();
-    __syncthreads();
-    if (tid == 0) {
-      tc::tc_fence_after();
-      issue_dq(j);
-      if (j + 1 < c_tiles) {
-        tc::mbar_wait(&bar_kv[(j + 1) & 1], ((j + 1) >> 1) & 1);
-        tc::tc_fence_after();
-        issue_s_dp(j + 1);
-      }
-    }
-  }
-  tc::mbar_wait(bar_o, (c_tiles - 1) & 1);
-  tc::tc_fence_after();
-  {
+    tc::mbar_wait(&bar_o[(n_sub - 1) & 1], ((n_sub - 1) >> 1) & 1);   // a commit covers every MMA issued before it
+    tc::tc_fence_after();
     bf16* out = args.dqkv + (static_cast<size_t>(b) * N + (row_ok ? row : 0)) * 3 * inner + h * DH;
 #pragma unroll
     for (int ch = 0; ch < (DH + 31) / 32; ++ch) {
