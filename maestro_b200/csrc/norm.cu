@@ -479,20 +479,33 @@ __global__ void __launch_bounds__(256) gn_bwd_reduce_kernel(const T* __restrict_
     float ag[V], ab[V], gm[V];
 #pragma unroll
     for (int j = 0; j < V; ++j) { ag[j] = 0.f; ab[j] = 0.f; gm[j] = gamma[cv * V + j]; }
-    for (int l = l0; l < l1; ++l) {
-      const size_t yrow = static_cast<size_t>(img) * L + l;
-      const size_t drow = static_cast<size_t>(b) * out_bs + out_off + static_cast<size_t>(d) * L + l;
-      float yv[V], dv[V];
-      VecIO<T>::load(y + yrow * E + cv * V, yv);
-      VecIO<T>::load(dy + drow * E + cv * V, dv);
+    typedef typename VecIO<T>::Raw Raw;
+    constexpr int U = 4;                      // rows in flight per thread (the loop is latency-bound otherwise)
+    for (int l = l0; l < l1; l += U) {
+      Raw ry[U], rd[U];
 #pragma unroll
-      for (int j = 0; j < V; ++j) {
-        const float h = (yv[j] - mean) * rstd;
-        const float g = dv[j] * gm[j];
-        a += g;
-        c += g * h;
-        ag[j] += dv[j] * h;
-        ab[j] += dv[j];
+      for (int u = 0; u < U; ++u) {
+        const int lu = min(l + u, l1 - 1);    // clamped rows are loaded twice and skipped below
+        const size_t yrow = static_cast<size_t>(img) * L + lu;
+        const size_t drow = static_cast<size_t>(b) * out_bs + out_off + static_cast<size_t>(d) * L + lu;
+        ry[u] = VecIO<T>::load_raw(y + yrow * E + cv * V);
+        rd[u] = VecIO<T>::load_raw(dy + drow * E + cv * V);
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        if (l + u >= l1) break;
+        float yv[V], dv[V];
+        VecIO<T>::unpack(ry[u], yv);
+        VecIO<T>::unpack(rd[u], dv);
+#pragma unroll
+        for (int j = 0; j < V; ++j) {
+          const float h = (yv[j] - mean) * rstd;
+          const float g = dv[j] * gm[j];
+          a += g;
+          c += g * h;
+          ag[j] += dv[j] * h;
+          ab[j] += dv[j];
+        }
       }
     }
 #pragma unroll
@@ -554,7 +567,7 @@ extern "C" int mb_gn_bwd(const void* dy, const void* y, const float* stats, cons
   if (n_img == 0) return 0;
   if (E % 8 != 0) return -2;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  int row_blocks = (148 * 4) / n_img;
+  int row_blocks = (148 * 8) / n_img;
   if (row_blocks < 1) row_blocks = 1;
   if (row_blocks > L) row_blocks = L;
   const int rows_per_block = mb_ceil_div(L, row_blocks);

@@ -59,50 +59,89 @@ extern "C" int mb_unmask_fwd(const void* y, const unsigned char* mask, const int
 }
 
 // Mask-token gradient: dtok[k, :] += sum over masked (b, p) with tok_id[src(b,p)] == k of dx[b, p, :].
-// grid (ceil(d / 128), chunks over B*L rows); thread = one channel; fp32 atomics per kind at the end.
+// A thread owns one 16-byte column chunk; the block's threads are laid out as [row lane][column chunk], each row lane
+// walks its rows four at a time (mask bytes, then token ids, then dx chunks: three dependent load rounds per four
+// rows instead of twelve); fp32 atomics per kind at the end.
 constexpr int MAX_TOK_KINDS = 8;
-template <typename T>
-__global__ void __launch_bounds__(128) masktoken_grad_kernel(const T* __restrict__ dx,
+template <typename T, int NK>
+__global__ void __launch_bounds__(256) masktoken_grad_kernel(const T* __restrict__ dx,
                                                              const unsigned char* __restrict__ mask,
                                                              const int* __restrict__ tok_id,
                                                              const int* __restrict__ src_pos, float* __restrict__ dtok,
                                                              int B, int L, int d, int n_kinds, int rows_per_block) {
-  const int e = blockIdx.x * blockDim.x + threadIdx.x;
-  if (e >= d) return;
-  const int r0 = blockIdx.y * rows_per_block;
+  constexpr int V = VecIO<T>::N;
+  constexpr int U = 4;
+  typedef typename VecIO<T>::Raw Raw;
+  const int nvec = d / V;
+  const int cv = threadIdx.x % nvec, rl = threadIdx.x / nvec, nrl = blockDim.x / nvec;
+  if (rl >= nrl) return;
+  const int r0 = blockIdx.x * rows_per_block;
   const int r1 = min(B * L, r0 + rows_per_block);
-  float acc[MAX_TOK_KINDS];
+  float acc[NK][V];
 #pragma unroll
-  for (int k = 0; k < MAX_TOK_KINDS; ++k) acc[k] = 0.f;
-  for (int r = r0; r < r1; ++r) {
-    if (mask[r] == 0) continue;
-    const int p = r % L;
-    const int sp = src_pos != nullptr ? src_pos[r] : p;
-    const int k = tok_id[sp];
-    const float v = to_f32(dx[static_cast<size_t>(r) * d + e]);
+  for (int k = 0; k < NK; ++k)
 #pragma unroll
-    for (int kk = 0; kk < MAX_TOK_KINDS; ++kk)
-      if (kk == k) acc[kk] += v;
+    for (int j = 0; j < V; ++j) acc[k][j] = 0.f;
+  for (int r = r0 + rl; r < r1; r += nrl * U) {
+    int kind[U];
+    Raw raw[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int ru = r + u * nrl;
+      kind[u] = (ru < r1 && mask[ru] != 0) ? ru : -1;
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      if (kind[u] >= 0) {
+        const int ru = kind[u];
+        raw[u] = VecIO<T>::load_raw(dx + static_cast<size_t>(ru) * d + cv * V);
+        const int sp = src_pos != nullptr ? src_pos[ru] : ru % L;
+        kind[u] = tok_id[sp];
+      } else {
+        raw[u] = VecIO<T>::zero_raw();
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      float v[V];
+      VecIO<T>::unpack(raw[u], v);
+#pragma unroll
+      for (int kk = 0; kk < NK; ++kk) {
+        const float sel = (kk == kind[u]) ? 1.f : 0.f;       // branch-free: the accumulators stay in registers
+#pragma unroll
+        for (int j = 0; j < V; ++j) acc[kk][j] = fmaf(sel, v[j], acc[kk][j]);
+      }
+    }
   }
 #pragma unroll
-  for (int k = 0; k < MAX_TOK_KINDS; ++k)
-    if (k < n_kinds && acc[k] != 0.f) atomicAdd(dtok + static_cast<size_t>(k) * d + e, acc[k]);
+  for (int k = 0; k < NK; ++k) {
+    if (k < n_kinds) {
+#pragma unroll
+      for (int j = 0; j < V; ++j)
+        if (acc[k][j] != 0.f) atomicAdd(dtok + static_cast<size_t>(k) * d + cv * V + j, acc[k][j]);
+    }
+  }
 }
 
 extern "C" int mb_masktoken_grad(const void* dx, const unsigned char* mask, const int* tok_id, const int* src_pos,
                                  float* dtok, int dtype, int B, int L, int d, int n_kinds, void* stream) {
   if (B * L == 0) return 0;
-  if (n_kinds > MAX_TOK_KINDS) return -2;
-  const int bx = mb_ceil_div(d, 128);
-  int by = (148 * 8) / bx;
-  if (by < 1) by = 1;
-  int rows_per_block = mb_ceil_div(static_cast<long long>(B) * L, by);
-  if (rows_per_block < 8) rows_per_block = 8;
-  by = mb_ceil_div(static_cast<long long>(B) * L, rows_per_block);
-  dim3 grid(bx, by);
-  MB_DISPATCH_DTYPE(dtype, T,
-                    (masktoken_grad_kernel<T><<<grid, 128, 0, static_cast<cudaStream_t>(stream)>>>(
-                        static_cast<const T*>(dx), mask, tok_id, src_pos, dtok, B, L, d, n_kinds, rows_per_block)));
+  if (n_kinds > MAX_TOK_KINDS || d % 8 != 0 || d / (dtype == MB_DTYPE_F32 ? 4 : 8) > 256) return -2;   // one column chunk per thread
+  int blocks = 148 * 4;
+  int rows_per_block = mb_ceil_div(static_cast<long long>(B) * L, blocks);
+  if (rows_per_block < 32) rows_per_block = 32;
+  blocks = mb_ceil_div(static_cast<long long>(B) * L, rows_per_block);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+#define MTG(NK_)                                                                                              \
+  MB_DISPATCH_DTYPE(dtype, T,                                                                                 \
+                    (masktoken_grad_kernel<T, NK_><<<blocks, 256, 0, st>>>(static_cast<const T*>(dx), mask, tok_id, \
+                                                                           src_pos, dtok, B, L, d, n_kinds,    \
+                                                                           rows_per_block)))
+  if (n_kinds <= 1) { MTG(1); }
+  else if (n_kinds <= 2) { MTG(2); }
+  else if (n_kinds <= 4) { MTG(4); }
+  else { MTG(8); }
+#undef MTG
   MB_CHECK_LAUNCH();
   return 0;
 }
