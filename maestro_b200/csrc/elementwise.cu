@@ -59,22 +59,23 @@ extern "C" int mb_cast_transpose_f32_to_bf16(const float* src, void* dst, int R,
 // Nearest-neighbour resize as torch F.interpolate(mode="nearest"): src = min(floor(dst * in/out), in-1)
 // with the scale held in fp32.  Optionally applies the elevation rescale in the same pass:
 // ch>=1 of a rescale_elev modality becomes 30 * (ch0 - ch).
+template <typename I>   // index type: unsigned when the element count fits 32 bits (64-bit divisions cost ~10x)
 __global__ void resize_nearest_kernel(const float* __restrict__ src, float* __restrict__ dst, int n_img, int C,
                                       int hin, int win, int hout, int wout, int rescale_elev) {
-  const size_t total = static_cast<size_t>(n_img) * C * hout * wout;
+  const I total = static_cast<I>(n_img) * C * hout * wout;
   const float sh = static_cast<float>(hin) / static_cast<float>(hout);
   const float sw = static_cast<float>(win) / static_cast<float>(wout);
-  for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
-       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
-    const int x = static_cast<int>(i % wout);
-    size_t t = i / wout;
-    const int y = static_cast<int>(t % hout);
-    t /= hout;
-    const int c = static_cast<int>(t % C);
-    const size_t img = t / C;
+  for (I i = static_cast<I>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<I>(gridDim.x) * blockDim.x) {
+    const I t0 = i / wout;
+    const int x = static_cast<int>(i - t0 * wout);
+    const I t1 = t0 / hout;
+    const int y = static_cast<int>(t0 - t1 * hout);
+    const I img = t1 / C;
+    const int c = static_cast<int>(t1 - img * C);
     const int sy = min(static_cast<int>(floorf(y * sh)), hin - 1);
     const int sx = min(static_cast<int>(floorf(x * sw)), win - 1);
-    const float* base = src + img * C * hin * win;
+    const float* base = src + static_cast<size_t>(img) * C * hin * win;
     float v = base[(static_cast<size_t>(c) * hin + sy) * win + sx];
     if (rescale_elev && c >= 1) {
       const float v0 = base[static_cast<size_t>(sy) * win + sx];
@@ -90,8 +91,12 @@ extern "C" int mb_resize_nearest(const float* src, float* dst, int n_img, int C,
   if (total == 0) return 0;
   long long blocks = (static_cast<long long>(total) + 255) / 256;
   if (blocks > 148 * 32) blocks = 148 * 32;
-  resize_nearest_kernel<<<static_cast<int>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      src, dst, n_img, C, hin, win, hout, wout, rescale_elev);
+  if (total < 0xffffffffull)
+    resize_nearest_kernel<unsigned><<<static_cast<int>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        src, dst, n_img, C, hin, win, hout, wout, rescale_elev);
+  else
+    resize_nearest_kernel<size_t><<<static_cast<int>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        src, dst, n_img, C, hin, win, hout, wout, rescale_elev);
   MB_CHECK_LAUNCH();
   return 0;
 }

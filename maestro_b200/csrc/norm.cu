@@ -409,30 +409,41 @@ __global__ void __launch_bounds__(256) gn_apply_kernel(const T* __restrict__ y, 
                                                        int D, int L, int E, float eps, int out_bs, int out_off,
                                                        int date_dim, float fac_date, int feat_bs, int feat_off) {
   constexpr int V = VecIO<T>::N;
-  const int nvec_row = E / V;
-  const size_t total = static_cast<size_t>(n_img) * L * nvec_row;
+  extern __shared__ float st_s[];            // [n_img][2]: mean, rstd (the fp64 finalisation runs once per block)
   const double inv_n = 1.0 / (static_cast<double>(L) * E);
-  for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
-       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
-    const int cv = static_cast<int>(i % nvec_row);
-    const size_t row = i / nvec_row;
-    const int l = static_cast<int>(row % L);
-    const int img = static_cast<int>(row / L);
-    const int b = img / D, d = img % D;
-    const double m = sums[2 * img] * inv_n;
-    const double var = fmax(sums[2 * img + 1] * inv_n - m * m, 0.0);
+  for (int i = threadIdx.x; i < n_img; i += blockDim.x) {
+    const double m = sums[2 * i] * inv_n;
+    const double var = fmax(sums[2 * i + 1] * inv_n - m * m, 0.0);
     const float mean = static_cast<float>(m);
     const float rstd = static_cast<float>(1.0 / sqrt(var + static_cast<double>(eps)));
-    if (stats_out != nullptr && l == 0 && cv == 0) {
-      stats_out[2 * img] = mean;
-      stats_out[2 * img + 1] = rstd;
+    st_s[2 * i] = mean;
+    st_s[2 * i + 1] = rstd;
+    if (stats_out != nullptr && blockIdx.x == 0) {
+      stats_out[2 * i] = mean;
+      stats_out[2 * i + 1] = rstd;
     }
-    float v[V];
-    VecIO<T>::load(y + row * E + cv * V, v);
+  }
+  __syncthreads();
+  const unsigned nvec_row = E / V;
+  const unsigned total = static_cast<unsigned>(n_img) * L * nvec_row;      // host checks < 2^32
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const unsigned row = i / nvec_row, cv = i - row * nvec_row;
+    const unsigned img = row / L, l = row - img * L;
+    const unsigned b = img / D, d = img - b * D;
+    const float mean = st_s[2 * img], rstd = st_s[2 * img + 1];
+    const float shift = -mean * rstd;
+    float v[V], gm[V], bt[V], ps[V];
+    VecIO<T>::load(y + static_cast<size_t>(row) * E + cv * V, v);
+#pragma unroll
+    for (int j = 0; j < V; j += 4) {
+      VecIO<float>::load(gamma + cv * V + j, gm + j);
+      VecIO<float>::load(beta + cv * V + j, bt + j);
+      VecIO<float>::load(pos + static_cast<size_t>(l) * E + cv * V + j, ps + j);
+    }
 #pragma unroll
     for (int j = 0; j < V; ++j) {
       const int e = cv * V + j;
-      float o = (v[j] - mean) * rstd * gamma[e] + beta[e] + pos[static_cast<size_t>(l) * E + e];
+      float o = fmaf(fmaf(v[j], rstd, shift), gm[j], bt[j]) + ps[j];
       if (e >= E - date_dim) o += date_channel(feat + (static_cast<size_t>(b) * feat_bs + feat_off + d) * 5, e - (E - date_dim), date_dim, fac_date);
       v[j] = o;
     }
@@ -448,10 +459,12 @@ extern "C" int mb_gn_apply(const void* y, const double* sums, const float* gamma
   if (n_img == 0) return 0;
   if (E % 8 != 0) return -2;
   const long long total = static_cast<long long>(n_img) * L * (E / 4);
+  if (total >= 0xffffffffll || n_img > 4096) return -2;
   long long blocks = (total + 255) / 256;
-  if (blocks > 148 * 16) blocks = 148 * 16;
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  const size_t st_bytes = static_cast<size_t>(n_img) * 2 * sizeof(float);
   MB_DISPATCH_DTYPE(dtype, T,
-                    (gn_apply_kernel<T><<<static_cast<int>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+                    (gn_apply_kernel<T><<<static_cast<int>(blocks), 256, st_bytes, static_cast<cudaStream_t>(stream)>>>(
                         static_cast<const T*>(y), sums, gamma, beta, pos, feat, static_cast<T*>(out), stats_out,
                         n_img, D, L, E, eps, out_bs, out_off, date_dim, fac_date, feat_bs, feat_off)));
   MB_CHECK_LAUNCH();
@@ -535,28 +548,35 @@ __global__ void __launch_bounds__(256) gn_bwd_apply_kernel(const T* __restrict__
                                                            const double* __restrict__ sums2, T* __restrict__ dconv,
                                                            int n_img, int D, int L, int E, int out_bs, int out_off) {
   constexpr int V = VecIO<T>::N;
-  const int nvec_row = E / V;
-  const size_t total = static_cast<size_t>(n_img) * L * nvec_row;
+  extern __shared__ float st_s[];            // [n_img][4]: mean, rstd, a / n, c / n (fp64 -> fp32 once per block)
   const double inv_n = 1.0 / (static_cast<double>(L) * E);
-  for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
-       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
-    const int cv = static_cast<int>(i % nvec_row);
-    const size_t row = i / nvec_row;
-    const int l = static_cast<int>(row % L);
-    const int img = static_cast<int>(row / L);
-    const int b = img / D, d = img % D;
-    const float mean = stats[2 * img], rstd = stats[2 * img + 1];
-    const float ma = static_cast<float>(sums2[2 * img] * inv_n), mc = static_cast<float>(sums2[2 * img + 1] * inv_n);
+  for (int i = threadIdx.x; i < n_img; i += blockDim.x) {
+    st_s[4 * i] = stats[2 * i];
+    st_s[4 * i + 1] = stats[2 * i + 1];
+    st_s[4 * i + 2] = static_cast<float>(sums2[2 * i] * inv_n);
+    st_s[4 * i + 3] = static_cast<float>(sums2[2 * i + 1] * inv_n);
+  }
+  __syncthreads();
+  const unsigned nvec_row = E / V;
+  const unsigned total = static_cast<unsigned>(n_img) * L * nvec_row;      // host checks < 2^32
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const unsigned row = i / nvec_row, cv = i - row * nvec_row;
+    const unsigned img = row / L, l = row - img * L;
+    const unsigned b = img / D, d = img - b * D;
+    const float4 q = *reinterpret_cast<const float4*>(st_s + 4 * img);
+    const float mean = q.x, rstd = q.y, ma = q.z, mc = q.w;
     const size_t drow = static_cast<size_t>(b) * out_bs + out_off + static_cast<size_t>(d) * L + l;
-    float yv[V], dv[V];
-    VecIO<T>::load(y + row * E + cv * V, yv);
+    float yv[V], dv[V], gm[V];
+    VecIO<T>::load(y + static_cast<size_t>(row) * E + cv * V, yv);
     VecIO<T>::load(dy + drow * E + cv * V, dv);
+#pragma unroll
+    for (int j = 0; j < V; j += 4) VecIO<float>::load(gamma + cv * V + j, gm + j);
 #pragma unroll
     for (int j = 0; j < V; ++j) {
       const float h = (yv[j] - mean) * rstd;
-      dv[j] = rstd * (dv[j] * gamma[cv * V + j] - ma - h * mc);
+      dv[j] = rstd * (dv[j] * gm[j] - ma - h * mc);
     }
-    VecIO<T>::store(dconv + row * E + cv * V, dv);
+    VecIO<T>::store(dconv + static_cast<size_t>(row) * E + cv * V, dv);
   }
 }
 
@@ -574,13 +594,15 @@ extern "C" int mb_gn_bwd(const void* dy, const void* y, const float* stats, cons
   row_blocks = mb_ceil_div(L, rows_per_block);
   dim3 grid(n_img, row_blocks);
   const long long total = static_cast<long long>(n_img) * L * (E / 4);
+  if (total >= 0xffffffffll || n_img > 2048) return -2;
   long long blocks = (total + 255) / 256;
-  if (blocks > 148 * 16) blocks = 148 * 16;
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  const size_t st_bytes = static_cast<size_t>(n_img) * 4 * sizeof(float);
   MB_DISPATCH_DTYPE(
       dtype, T,
       (gn_bwd_reduce_kernel<T><<<grid, 128, 0, st>>>(static_cast<const T*>(dy), static_cast<const T*>(y), stats, gamma,
                                                      sums2, dgamma, dbeta, D, L, E, out_bs, out_off, rows_per_block),
-       gn_bwd_apply_kernel<T><<<static_cast<int>(blocks), 256, 0, st>>>(static_cast<const T*>(dy),
+       gn_bwd_apply_kernel<T><<<static_cast<int>(blocks), 256, st_bytes, st>>>(static_cast<const T*>(dy),
                                                                         static_cast<const T*>(y), stats, gamma, sums2,
                                                                         static_cast<T*>(dconv), n_img, D, L, E, out_bs,
                                                                         out_off)));
