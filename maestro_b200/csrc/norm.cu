@@ -473,32 +473,43 @@ extern "C" int mb_gn_apply(const void* y, const double* sums, const float* gamma
 
 // Backward phase 1: per image a = sum(dy * gamma), c = sum(dy * gamma * xhat) (fp64 atomics into sums2 [n_img,2]);
 // per channel dgamma += sum dy * xhat, dbeta += sum dy (fp32 atomics).  dy is read from the group token buffer.
+// grid (n_img, row blocks); the block's threads are laid out as [row lane][16-byte column chunk], every row lane
+// keeps 4 rows of loads in flight, and the row lanes are combined in shared memory so that a block issues ONE
+// atomic per column (same-address atomics from many blocks are what bounds this kernel).
+constexpr int GNR_THREADS = 512;
 template <typename T>
-__global__ void __launch_bounds__(256) gn_bwd_reduce_kernel(const T* __restrict__ dy, const T* __restrict__ y,
-                                                            const float* __restrict__ stats,
-                                                            const float* __restrict__ gamma, double* __restrict__ sums2,
-                                                            float* __restrict__ dgamma, float* __restrict__ dbeta,
-                                                            int D, int L, int E, int out_bs, int out_off,
-                                                            int rows_per_block) {
-  // grid: (n_img, ceil(L / rows_per_block)); block: E / V threads (<= 256) each owning V columns
+__global__ void __launch_bounds__(GNR_THREADS) gn_bwd_reduce_kernel(const T* __restrict__ dy, const T* __restrict__ y,
+                                                                    const float* __restrict__ stats,
+                                                                    const float* __restrict__ gamma,
+                                                                    double* __restrict__ sums2,
+                                                                    float* __restrict__ dgamma,
+                                                                    float* __restrict__ dbeta, int D, int L, int E,
+                                                                    int out_bs, int out_off, int rows_per_block) {
   constexpr int V = VecIO<T>::N;
+  constexpr int U = 4;
+  typedef typename VecIO<T>::Raw Raw;
+  extern __shared__ float cs[];              // [2][E]: dgamma / dbeta partials, column (cv * V + j) at [j * nvec + cv]
+  __shared__ double red[2][GNR_THREADS / 32];
   const int img = blockIdx.x;
   const int b = img / D, d = img % D;
   const int l0 = blockIdx.y * rows_per_block, l1 = min(L, l0 + rows_per_block);
   const float mean = stats[2 * img], rstd = stats[2 * img + 1];
-  const int nvec_row = E / V;
+  const int nvec = E / V;
+  const int cv = threadIdx.x % nvec, rl = threadIdx.x / nvec, nrl = blockDim.x / nvec;
+  for (int i = threadIdx.x; i < 2 * E; i += blockDim.x) cs[i] = 0.f;
+  __syncthreads();
   float a = 0.f, c = 0.f;
-  for (int cv = threadIdx.x; cv < nvec_row; cv += blockDim.x) {
+  if (rl < nrl) {
     float ag[V], ab[V], gm[V];
 #pragma unroll
-    for (int j = 0; j < V; ++j) { ag[j] = 0.f; ab[j] = 0.f; gm[j] = gamma[cv * V + j]; }
-    typedef typename VecIO<T>::Raw Raw;
-    constexpr int U = 4;                      // rows in flight per thread (the loop is latency-bound otherwise)
-    for (int l = l0; l < l1; l += U) {
+    for (int j = 0; j < V; j += 4) VecIO<float>::load(gamma + cv * V + j, gm + j);
+#pragma unroll
+    for (int j = 0; j < V; ++j) { ag[j] = 0.f; ab[j] = 0.f; }
+    for (int l = l0 + rl; l < l1; l += nrl * U) {
       Raw ry[U], rd[U];
 #pragma unroll
       for (int u = 0; u < U; ++u) {
-        const int lu = min(l + u, l1 - 1);    // clamped rows are loaded twice and skipped below
+        const int lu = min(l + u * nrl, l1 - 1);    // clamped rows are loaded again and skipped below
         const size_t yrow = static_cast<size_t>(img) * L + lu;
         const size_t drow = static_cast<size_t>(b) * out_bs + out_off + static_cast<size_t>(d) * L + lu;
         ry[u] = VecIO<T>::load_raw(y + yrow * E + cv * V);
@@ -506,7 +517,7 @@ __global__ void __launch_bounds__(256) gn_bwd_reduce_kernel(const T* __restrict_
       }
 #pragma unroll
       for (int u = 0; u < U; ++u) {
-        if (l + u >= l1) break;
+        if (l + u * nrl >= l1) break;
         float yv[V], dv[V];
         VecIO<T>::unpack(ry[u], yv);
         VecIO<T>::unpack(rd[u], dv);
@@ -523,15 +534,19 @@ __global__ void __launch_bounds__(256) gn_bwd_reduce_kernel(const T* __restrict_
     }
 #pragma unroll
     for (int j = 0; j < V; ++j) {
-      atomicAdd(dgamma + cv * V + j, ag[j]);
-      atomicAdd(dbeta + cv * V + j, ab[j]);
+      atomicAdd(&cs[j * nvec + cv], ag[j]);
+      atomicAdd(&cs[E + j * nvec + cv], ab[j]);
     }
   }
   double da = warp_sum(static_cast<double>(a)), dc = warp_sum(static_cast<double>(c));
-  __shared__ double red[2][8];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   if (lane == 0) { red[0][w] = da; red[1][w] = dc; }
   __syncthreads();
+  for (int i = threadIdx.x; i < E; i += blockDim.x) {
+    const int si = (i % V) * nvec + i / V;
+    atomicAdd(dgamma + i, cs[si]);
+    atomicAdd(dbeta + i, cs[E + si]);
+  }
   if (threadIdx.x == 0) {
     double s0 = 0, s1 = 0;
     for (int i = 0; i < ((blockDim.x + 31) >> 5); ++i) { s0 += red[0][i]; s1 += red[1][i]; }
@@ -587,7 +602,8 @@ extern "C" int mb_gn_bwd(const void* dy, const void* y, const float* stats, cons
   if (n_img == 0) return 0;
   if (E % 8 != 0) return -2;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  int row_blocks = (148 * 8) / n_img;
+  if (E / 4 > GNR_THREADS) return -2;        // one column chunk per thread
+  int row_blocks = (148 * 2) / n_img;        // ~2 blocks per SM; every block ends in 2 E same-address atomics
   if (row_blocks < 1) row_blocks = 1;
   if (row_blocks > L) row_blocks = L;
   const int rows_per_block = mb_ceil_div(L, row_blocks);
@@ -600,7 +616,7 @@ extern "C" int mb_gn_bwd(const void* dy, const void* y, const float* stats, cons
   const size_t st_bytes = static_cast<size_t>(n_img) * 4 * sizeof(float);
   MB_DISPATCH_DTYPE(
       dtype, T,
-      (gn_bwd_reduce_kernel<T><<<grid, 128, 0, st>>>(static_cast<const T*>(dy), static_cast<const T*>(y), stats, gamma,
+      (gn_bwd_reduce_kernel<T><<<grid, GNR_THREADS, 2 * E * sizeof(float), st>>>(static_cast<const T*>(dy), static_cast<const T*>(y), stats, gamma,
                                                      sums2, dgamma, dbeta, D, L, E, out_bs, out_off, rows_per_block),
        gn_bwd_apply_kernel<T><<<static_cast<int>(blocks), 256, st_bytes, st>>>(static_cast<const T*>(dy),
                                                                         static_cast<const T*>(y), stats, gamma, sums2,

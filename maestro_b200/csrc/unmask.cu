@@ -64,7 +64,7 @@ extern "C" int mb_unmask_fwd(const void* y, const unsigned char* mask, const int
 // rows instead of twelve); fp32 atomics per kind at the end.
 constexpr int MAX_TOK_KINDS = 8;
 template <typename T, int NK>
-__global__ void __launch_bounds__(256) masktoken_grad_kernel(const T* __restrict__ dx,
+__global__ void __launch_bounds__(512) masktoken_grad_kernel(const T* __restrict__ dx,
                                                              const unsigned char* __restrict__ mask,
                                                              const int* __restrict__ tok_id,
                                                              const int* __restrict__ src_pos, float* __restrict__ dtok,
@@ -73,8 +73,11 @@ __global__ void __launch_bounds__(256) masktoken_grad_kernel(const T* __restrict
   constexpr int U = 4;
   typedef typename VecIO<T>::Raw Raw;
   const int nvec = d / V;
+  extern __shared__ float red[];            // [NK][d] partial sums of this block (row lanes combined before the atomics)
   const int cv = threadIdx.x % nvec, rl = threadIdx.x / nvec, nrl = blockDim.x / nvec;
-  if (rl >= nrl) return;
+  for (int i = threadIdx.x; i < NK * d; i += blockDim.x) red[i] = 0.f;
+  __syncthreads();
+  const bool active = rl < nrl;
   const int r0 = blockIdx.x * rows_per_block;
   const int r1 = min(B * L, r0 + rows_per_block);
   float acc[NK][V];
@@ -82,7 +85,7 @@ __global__ void __launch_bounds__(256) masktoken_grad_kernel(const T* __restrict
   for (int k = 0; k < NK; ++k)
 #pragma unroll
     for (int j = 0; j < V; ++j) acc[k][j] = 0.f;
-  for (int r = r0 + rl; r < r1; r += nrl * U) {
+  for (int r = r0 + rl; active && r < r1; r += nrl * U) {
     int kind[U];
     Raw raw[U];
 #pragma unroll
@@ -113,13 +116,18 @@ __global__ void __launch_bounds__(256) masktoken_grad_kernel(const T* __restrict
       }
     }
   }
+  if (active) {
 #pragma unroll
-  for (int k = 0; k < NK; ++k) {
-    if (k < n_kinds) {
+    for (int k = 0; k < NK; ++k)
 #pragma unroll
-      for (int j = 0; j < V; ++j)
-        if (acc[k][j] != 0.f) atomicAdd(dtok + static_cast<size_t>(k) * d + cv * V + j, acc[k][j]);
-    }
+      for (int j = 0; j < V; ++j)   // column (cv * V + j) of kind k lives at [k][j * nvec + cv]: conflict-free across a warp
+        if (acc[k][j] != 0.f) atomicAdd(&red[k * d + j * nvec + cv], acc[k][j]);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < NK * d; i += blockDim.x) {
+    const int k = i / d, c = i - k * d;
+    const float v = red[k * d + (c % V) * nvec + c / V];
+    if (k < n_kinds && v != 0.f) atomicAdd(dtok + static_cast<size_t>(k) * d + c, v);
   }
 }
 
@@ -127,14 +135,14 @@ extern "C" int mb_masktoken_grad(const void* dx, const unsigned char* mask, cons
                                  float* dtok, int dtype, int B, int L, int d, int n_kinds, void* stream) {
   if (B * L == 0) return 0;
   if (n_kinds > MAX_TOK_KINDS || d % 8 != 0 || d / (dtype == MB_DTYPE_F32 ? 4 : 8) > 256) return -2;   // one column chunk per thread
-  int blocks = 148 * 4;
+  int blocks = 148;                         // one same-address atomic per column per block at the end
   int rows_per_block = mb_ceil_div(static_cast<long long>(B) * L, blocks);
-  if (rows_per_block < 32) rows_per_block = 32;
+  if (rows_per_block < 64) rows_per_block = 64;
   blocks = mb_ceil_div(static_cast<long long>(B) * L, rows_per_block);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
 #define MTG(NK_)                                                                                              \
   MB_DISPATCH_DTYPE(dtype, T,                                                                                 \
-                    (masktoken_grad_kernel<T, NK_><<<blocks, 256, 0, st>>>(static_cast<const T*>(dx), mask, tok_id, \
+                    (masktoken_grad_kernel<T, NK_><<<blocks, 512, NK_ * d * sizeof(float), st>>>(static_cast<const T*>(dx), mask, tok_id, \
                                                                            src_pos, dtok, B, L, d, n_kinds,    \
                                                                            rows_per_block)))
   if (n_kinds <= 1) { MTG(1); }
