@@ -24,7 +24,7 @@ import torch  # noqa: E402
 
 from maestro_b200.conf import DATASET_SPECS, MODEL_SIZES, MaskSpec  # noqa: E402
 
-GEMM_DRAM_BYTES_PER_LAUNCH = 148.8e6   # measured under ncu, see profiles/r1c_summary.md
+GEMM_DRAM_BYTES_PER_LAUNCH = 145.3e6   # measured under ncu, see profiles/r1d_summary.md
 STEP_GFLOP = {"flair": 431.9, "treesatai_ts": 94.6, "s2_naip": 301.3, "pastis_hd": 1009.3}  # SURVEY 8(d), per tile
 
 
@@ -353,8 +353,8 @@ def run_ours(args):
         "clocks": clocks,
         "roofline": {"bound": "tensor", "kernel": "gemm_tc_kernel (tcgen05 GEMM, all linear layers fwd/dgrad/wgrad)",
                      "achieved": achieved, "peak": tf_sus, "unit": "TFLOP/s", "frac": achieved / tf_sus,
-                     "traffic": GEMM_DRAM_BYTES_PER_LAUNCH, "traffic_source": "profiles/r1c_gemm_dram.csv (ncu dram__bytes_"
-                     "read.sum + dram__bytes_write.sum, average over the 201 GEMM launches of one step; algorithmic "
+                     "traffic": GEMM_DRAM_BYTES_PER_LAUNCH, "traffic_source": "profiles/r1d_gemm_dram.csv (ncu dram__bytes_"
+                     "read.sum + dram__bytes_write.sum, average over the 208 GEMM launches of one step; algorithmic "
                      "167 MB per launch)",
                      "peak_source": f"{src} (sustained)", "launches": n_tc,
                      "avg_launch_ms": tc_ms / max(1, n_tc), "share_of_step": tc_ms / step_ms},
