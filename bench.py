@@ -181,7 +181,7 @@ def run_ours(args):
     gstep = None
     if use_graph:
         from maestro_b200.graph import GraphedPretrainStep
-        gstep = GraphedPretrainStep(eng, host[0], segments=3 if world > 1 else 1)
+        gstep = GraphedPretrainStep(eng, host[0], segments=len(eng.BWD_SEGMENTS) if world > 1 else 1)
         eng.zero_grad()
         devb = gstep.batch
     from maestro_b200.dist import GradReducer

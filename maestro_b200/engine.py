@@ -17,6 +17,7 @@ one CUDA graph.  Parameter names are the reference ``state_dict`` keys (SURVEY Â
 from __future__ import annotations
 
 from dataclasses import dataclass, field
+import re
 
 import torch
 
@@ -267,7 +268,11 @@ class PretrainEngine:
         order += keys("mask_token.")
         order += keys("enc_to_dec.")
         order += keys("encoder_inter.")
-        order += keys("encoder.")
+        # per-group encoders step in lockstep, so their gradients become final chunk of layers by chunk of layers
+        # (top chunk first): group the arena that way so that every backward segment owns one contiguous range
+        enc = keys("encoder.")
+        for ci in range(len(self._enc_chunks())):
+            order += [k for k in enc if self._enc_chunk_of(k) == ci]
         order += keys("patch_embed.")
         assert len(order) == len(shapes) and set(order) == set(shapes)
         self.arena = ParamArena(shapes, order, self.device, self.dtype == torch.bfloat16)
@@ -507,9 +512,10 @@ class PretrainEngine:
         incoming gradient must be given this as ``dbias`` (its dx is that linear layer's dY)."""
         return self.G[f"{prefix}layers.{depth - 1}.1.net.4.bias"] if depth > 0 else None
 
-    def stacks_bwd(self, prefixes, dxs, saved, Bn, Ns, dim, H, dh, mlp):
-        """The caller has already routed colsum(dxs) to ``bias_sink`` of every stack (via its own LayerNorm backward)."""
-        for i in reversed(range(len(saved))):
+    def stacks_bwd(self, prefixes, dxs, saved, Bn, Ns, dim, H, dh, mlp, lo=0, hi=None):
+        """The caller has already routed colsum(dxs) to ``bias_sink`` of every stack (via its own LayerNorm backward).
+        ``lo`` / ``hi`` restrict the pass to layers [lo, hi) (backward segments)."""
+        for i in reversed(range(lo, len(saved) if hi is None else hi)):
             sinks = [self.G[f"{p}layers.{i - 1}.1.net.4.bias"] for p in prefixes] if i > 0 else None
             dxs = self.blocks_bwd([f"{p}layers.{i}." for p in prefixes], dxs, saved[i], Bn, Ns, dim, H, dh, mlp, sinks)
             saved[i] = None
@@ -739,16 +745,50 @@ class PretrainEngine:
         return (per_mod * self.loss_w).sum()
 
     # ------------------------------------------------------------------ backward
-    BWD_SEGMENTS = ("decoder", "inter", "encoder")
+    # backward segments (cut points for gradient all-reduce overlap and CUDA-graph boundaries); the per-group encoder
+    # stacks are cut into three chunks of layers so that the all-reduce of the upper layers runs under the backward
+    # of the lower ones (the encoders hold 3/4 of the parameters)
+    BWD_SEGMENTS = ("decoder", "inter", "encoder_top", "encoder_mid", "encoder_low")
+
+    def _enc_chunks(self) -> list[tuple[int, int]]:
+        """Layer ranges [lo, hi) of the per-group encoder stacks handled by the three encoder segments, top first."""
+        d = self.hp["depth"] - self.inter_depth
+        a, b = d - d // 3, d - 2 * (d // 3)
+        return [(a, d), (b, a), (0, b)]
+
+    def _enc_chunk_of(self, name: str) -> int:
+        m = re.search(r"\.layers\.(\d+)\.", name)
+        if m is None:
+            return 0                                     # the stack's final norm: first thing the backward touches
+        layer = int(m.group(1))
+        return next(i for i, (lo, hi) in enumerate(self._enc_chunks()) if lo <= layer < hi)
+
+    def _segment_of(self, name: str) -> int:
+        if name.startswith("encoder_inter."):
+            return 1
+        if name.startswith("encoder."):
+            return 2 + self._enc_chunk_of(name)
+        if name.startswith("patch_embed."):
+            return 4
+        return 0
 
     def grad_ranges(self) -> list[tuple[int, int]]:
         """Arena element ranges whose gradients are final after each backward segment (``BWD_SEGMENTS`` order)."""
         offs, order = self.arena.offsets, self.arena.order
-        first_inter = next((offs[n] for n in order if n.startswith("encoder_inter.")), None)
-        first_enc = next(offs[n] for n in order if n.startswith("encoder."))
-        if first_inter is None:
-            first_inter = first_enc
-        return [(0, first_inter), (first_inter, first_enc), (first_enc, self.arena.numel)]
+        starts = [None] * len(self.BWD_SEGMENTS)
+        for n in order:                                  # the arena is ordered by segment (_build_params)
+            si = self._segment_of(n)
+            if starts[si] is None:
+                starts[si] = offs[n]
+        ends, nxt = [], self.arena.numel
+        for si in reversed(range(len(starts))):
+            if starts[si] is None:
+                starts[si] = nxt                         # empty segment (e.g. no encoder_inter, shallow stacks)
+            ends.append(nxt)
+            nxt = starts[si]
+        ends.reverse()
+        assert starts[0] == 0 and all(a <= b for a, b in zip(starts, ends))
+        return list(zip(starts, ends))
 
     def backward(self, ctx: dict, start: str | None = None, stop: str | None = None) -> None:
         """Accumulate parameter gradients into the arena (``self.G``) from ``ctx['mods'][m]['dpred']``.
@@ -829,7 +869,7 @@ class PretrainEngine:
                                 dbias=self.bias_sink("encoder_inter.", self.inter_depth))
             ctx["dxcat"] = self.stack_bwd("encoder_inter.", dxcat, ctx["inter_saved"], B, nt, E, H, dh, self.mlp_e)
 
-    def _backward_encoder(self, ctx: dict) -> None:
+    def _backward_encoder_top(self, ctx: dict) -> None:
         K, P, G = self.K, self.P, self.G
         E, hp, B = self.E, self.hp, ctx["B"]
         H, dh = hp["heads"], hp["dim_head"]
@@ -852,8 +892,26 @@ class PretrainEngine:
                                 P[pre + "norm.weight"], None, dx, G[pre + "norm.weight"], G[pre + "norm.bias"], rows, E,
                                 dbias=self.bias_sink(pre, depth_g))
             dxs.append(dx)
-        dxs = self.stacks_bwd(enc_pre, dxs, ctx["enc_saved"], B, [g.n_kept for g in glist], E, H, dh, self.mlp_e)
-        for g, dx in zip(glist, dxs):
+        lo, hi = self._enc_chunks()[0]
+        ctx["enc_dxs"] = self.stacks_bwd(enc_pre, dxs, ctx["enc_saved"], B, [g.n_kept for g in glist], E, H, dh,
+                                         self.mlp_e, lo, hi)
+
+    def _backward_encoder_chunk(self, ctx: dict, ci: int) -> None:
+        hp, glist = self.hp, list(self.groups.values())
+        lo, hi = self._enc_chunks()[ci]
+        ctx["enc_dxs"] = self.stacks_bwd([f"encoder.{g.name}." for g in glist], ctx["enc_dxs"], ctx["enc_saved"],
+                                         ctx["B"], [g.n_kept for g in glist], self.E, hp["heads"], hp["dim_head"],
+                                         self.mlp_e, lo, hi)
+
+    def _backward_encoder_mid(self, ctx: dict) -> None:
+        self._backward_encoder_chunk(ctx, 1)
+
+    def _backward_encoder_low(self, ctx: dict) -> None:
+        self._backward_encoder_chunk(ctx, 2)
+        K, P, G = self.K, self.P, self.G
+        E, B = self.E, ctx["B"]
+        glist = list(self.groups.values())
+        for g, dx in zip(glist, ctx.pop("enc_dxs")):
             gc = ctx["groups"][g.name]
             dxe = self._new(B, g.L, E)
             K.scatter_kept(dx.view(B, g.n_kept, E), gc["mask"], gc["slot"], dxe)

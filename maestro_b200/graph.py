@@ -28,7 +28,8 @@ class GraphedPretrainStep:
             raise RuntimeError("GraphedPretrainStep needs a CUDA engine (there is no CPU path)")
         self.eng, self.dev = engine, engine.device
         self.B = int(example_batch["ref_date"].shape[0])
-        self.segments = max(1, min(3, int(segments)))
+        nseg = len(engine.BWD_SEGMENTS)
+        self.segments = max(1, min(nseg, int(segments)))
         keys = [k for k in example_batch if k == "ref_date" or k in engine.mods or k.endswith("_dates")]
         self.batch = {}
         for k in keys:
@@ -74,7 +75,8 @@ class GraphedPretrainStep:
         torch.cuda.synchronize(self.dev)
         pool = torch.cuda.graph_pool_handle()
         launches0 = eng.K.launches
-        cuts = {1: [None], 2: ["decoder", None], 3: ["decoder", "inter", None]}[self.segments]
+        # the first `segments - 1` backward segments end a graph each; the last graph runs the rest
+        cuts = list(eng.BWD_SEGMENTS[:self.segments - 1]) + [None]
         ctx = None
         for i, cut in enumerate(cuts):
             g = torch.cuda.CUDAGraph()
