@@ -104,8 +104,8 @@ typedef struct {
 int mb_loss_fwd_bwd(const mb_loss_params* params, int dtype, void* stream);
 
 /* ---- contractions ------------------------------------------------------------------------------------------- */
-#define MB_GEMM_GELU 1
-#define MB_GEMM_DGELU 2
+#define MB_GEMM_GELU 1      /* out = gelu(acc + bias) (exact erf form); aux <- gelu'(acc + bias), saved for the backward */
+#define MB_GEMM_DGELU 2     /* out = acc * aux (aux = the derivative a MB_GEMM_GELU call saved) */
 #define MB_GEMM_ACCUM 4
 #define MB_GEMM_OUT_F32 8
 #define MB_GEMM_PAIR_ON 16  /* scheduling hint: force 2-CTA (cta_group::2) tiles on the tensor-core path */
@@ -116,7 +116,7 @@ typedef struct {
   void* C;               /* C[m * ldc + n] */
   const float* bias;
   const void* residual;
-  void* aux;
+  void* aux;             /* [M, ldc] second output (MB_GEMM_GELU) / epilogue input (MB_GEMM_DGELU), activation dtype */
   int M, N, K;
   long long sam, sak, sbn, sbk;
   int ldc;
