@@ -181,27 +181,28 @@ def run_ours(args):
     gstep = None
     if use_graph:
         from maestro_b200.graph import GraphedPretrainStep
-        gstep = GraphedPretrainStep(eng, host[0], segments=len(eng.BWD_SEGMENTS) if world > 1 else 1)
+        gstep = GraphedPretrainStep(eng, host[0], segments=len(eng.BWD_SEGMENTS))
         eng.zero_grad()
         devb = gstep.batch
     from maestro_b200.dist import GradReducer
     reducer = GradReducer(eng.arena.grad, eng.grad_ranges())
 
-    def reduce_grads_overlapped():
-        """Replay the step segment by segment; all-reduce each finished arena range on the comm stream."""
-        for i in range(len(reducer.buckets)):
+    def replay_segments(before_last=None):
+        """Replay the step graph by graph; for N > 1 all-reduce each finished arena range on the comm stream."""
+        n = len(gstep.graphs)
+        for i in range(n):
+            if i == n - 1 and before_last is not None:
+                before_last()
             gstep.replay(i)
-            reducer.reduce_range(i)
+            if world > 1:
+                reducer.reduce_range(i)
         reducer.finish()
 
-    def step_device(batch, staged=False):
+    def step_device(batch, staged=False, before_last=None):
         if use_graph:
             if not staged:
                 gstep.load(batch)
-            if world > 1:
-                reduce_grads_overlapped()
-            else:
-                gstep.replay()
+            replay_segments(before_last)
             loss = gstep.loss
         else:
             from maestro_b200.dist import data_parallel_step
@@ -210,25 +211,39 @@ def run_ours(args):
         return loss
 
     prefetched = [False]
+    loss_pin = [torch.zeros(1, dtype=torch.float32).pin_memory() for _ in range(2)]
+    loss_ev = [torch.cuda.Event() for _ in range(2)]
+    loss_pending = [False, False]
 
     def step_e2e(i):
         hb = host[i % 2]
         if use_graph:
             # input pipeline: the H2D copy of step i + 1 (pinned host memory -> staging) runs on a copy stream while
-            # step i computes; every step's inputs cross PCIe exactly once, inside the timed region
+            # step i computes; every step's inputs cross PCIe exactly once, inside the timed region.  The transfer is
+            # gated to start with the last backward segment, so that it runs under the tail of the backward and the
+            # AdamW update: PCIe ingress slows concurrent kernels (tools/h2d_interference.py), least so there.
             if not prefetched[0]:
                 gstep.prefetch(hb)
                 prefetched[0] = True
             gstep.load_prefetched()
-            gstep.prefetch(host[(i + 1) % 2])
-            loss = step_device(devb, staged=True)
+            nxt = host[(i + 1) % 2]
+            loss = step_device(devb, staged=True, before_last=lambda: gstep.prefetch(nxt, after_current_work=True))
         else:
             for k, v in hb.items():
                 devb[k].copy_(v, non_blocking=True)
             loss = step_device(devb)
-        loss_host.copy_(loss.reshape(1), non_blocking=True)
-        torch.cuda.current_stream().synchronize()
-        return float(loss_host[0])
+        # loss read-back, every step, without draining the queue: step i's loss goes to pinned slot i % 2 behind an
+        # event, and the host blocks on step i - 1's event only, so it stays one step ahead of the GPU (the struct-mask
+        # draw and the launch of step i + 1 overlap step i).  The last step's copy completes before the closing event.
+        slot = i % 2
+        loss_pin[slot].copy_(loss.reshape(1), non_blocking=True)
+        loss_ev[slot].record()
+        prev = 1 - slot
+        if loss_pending[prev]:
+            loss_ev[prev].synchronize()
+            loss_host[0] = loss_pin[prev][0]
+        loss_pending[slot] = True
+        return None
 
     def timed(fn, steps):
         if world > 1:
@@ -260,6 +275,7 @@ def run_ours(args):
     if use_graph:
         launches = gstep.launches_per_step + 1
     ms_e2e = timed(step_e2e, args.steps)
+    loss_host[0] = loss_pin[(args.steps - 1) % 2][0]      # timed() has synchronised: the last read-back is complete
     clocks = sampler.stop() if rank == 0 else None
     last_loss = float(loss_host[0])
 
@@ -346,7 +362,7 @@ def run_ours(args):
                    "attention": eng.attn_impl, "loss_last": last_loss,
                    "launch": "cuda-graph replay" if use_graph else "python",
                    "allreduce_bytes_per_step": reducer.bytes_per_step,
-                   "e2e_input_pipeline": "H2D of step i+1 on a copy stream overlaps step i; loss read back every step"},
+                   "e2e_input_pipeline": "H2D of step i+1 on a copy stream overlaps step i; loss of every step read back to pinned memory, the host waits one step behind"},
         "e2e": {"value": B * world / (e2e_ms * 1e-3), "unit": "tiles/s", "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": 4, "ms_per_step": e2e_ms},
         "gpu_launches": launches,

@@ -118,9 +118,14 @@ class GraphedPretrainStep:
                 self.noise[n].copy_(z, non_blocking=True)
 
     # ------------------------------------------------------------------ overlapped input pipeline
-    def prefetch(self, batch: dict) -> None:
+    def prefetch(self, batch: dict, after_current_work: bool = False) -> None:
         """Start the host->device copy of the NEXT step's inputs on a copy stream (into staging buffers), so that the
-        PCIe transfer (203 MB per step for FLAIR-HUB tiles) overlaps the current step's compute."""
+        PCIe transfer (203 MB per step for FLAIR-HUB tiles) overlaps the current step's compute.  The overlap is not
+        free on B200: while the 52 GB/s ingress runs, concurrent kernels slow down (tools/h2d_interference.py: tcgen05
+        GEMM +9 %, LayerNorm +32 %), which costs ~1.8 ms per step against device-resident inputs; copying in small
+        chunks changes nothing.  ``after_current_work`` makes the copy start only when the work queued so far on the
+        current stream has finished: callers use it to place the transfer under the end of the backward and the AdamW
+        update (the least sensitive phase) instead of under the forward."""
         if getattr(self, "_copy_stream", None) is None:
             self._copy_stream = torch.cuda.Stream(device=self.dev)
             self.staging = {k: torch.empty_like(v) for k, v in self.batch.items()}
@@ -128,6 +133,10 @@ class GraphedPretrainStep:
         cs = self._copy_stream
         if self._staging_free is not None:
             cs.wait_event(self._staging_free)          # the previous step has copied the staging buffers out
+        if after_current_work:
+            gate = torch.cuda.Event()
+            gate.record(torch.cuda.current_stream(self.dev))
+            cs.wait_event(gate)
         with torch.cuda.stream(cs):
             for k, dst in self.staging.items():
                 dst.copy_(batch[k], non_blocking=True)
