@@ -187,22 +187,27 @@ def run_ours(args):
     from maestro_b200.dist import GradReducer
     reducer = GradReducer(eng.arena.grad, eng.grad_ranges())
 
-    def replay_segments(before_last=None):
-        """Replay the step graph by graph; for N > 1 all-reduce each finished arena range on the comm stream."""
+    def replay_segments(before_tail=None):
+        """Replay the step graph by graph; for N > 1 all-reduce each finished arena range on the comm stream.
+        ``before_tail`` runs ahead of the third-last graph (lowest three encoder layers + patch embedding: ~3.5 ms of
+        backward, then 1.8 ms of AdamW -- longer than the 3.9 ms H2D transfer it gates).
+        (Updating each finished range with AdamW on the side stream under the remaining backward was measured too:
+        no gain at N = 1, 0.6 % at N = 2 -- the update's CTAs cannot share an SM with the register-full GEMM /
+        attention CTAs, so it only displaces them.)"""
         n = len(gstep.graphs)
         for i in range(n):
-            if i == n - 1 and before_last is not None:
-                before_last()
+            if i == max(0, n - 3) and before_tail is not None:
+                before_tail()
             gstep.replay(i)
             if world > 1:
                 reducer.reduce_range(i)
         reducer.finish()
 
-    def step_device(batch, staged=False, before_last=None):
+    def step_device(batch, staged=False, before_tail=None):
         if use_graph:
             if not staged:
                 gstep.load(batch)
-            replay_segments(before_last)
+            replay_segments(before_tail)
             loss = gstep.loss
         else:
             from maestro_b200.dist import data_parallel_step
@@ -220,14 +225,14 @@ def run_ours(args):
         if use_graph:
             # input pipeline: the H2D copy of step i + 1 (pinned host memory -> staging) runs on a copy stream while
             # step i computes; every step's inputs cross PCIe exactly once, inside the timed region.  The transfer is
-            # gated to start with the last backward segment, so that it runs under the tail of the backward and the
-            # AdamW update: PCIe ingress slows concurrent kernels (tools/h2d_interference.py), least so there.
+            # gated to start with the last three backward segments, so that it runs under the tail of the backward and
+            # the AdamW update: PCIe ingress slows concurrent kernels (tools/h2d_interference.py), least so there.
             if not prefetched[0]:
                 gstep.prefetch(hb)
                 prefetched[0] = True
             gstep.load_prefetched()
             nxt = host[(i + 1) % 2]
-            loss = step_device(devb, staged=True, before_last=lambda: gstep.prefetch(nxt, after_current_work=True))
+            loss = step_device(devb, staged=True, before_tail=lambda: gstep.prefetch(nxt, after_current_work=True))
         else:
             for k, v in hb.items():
                 devb[k].copy_(v, non_blocking=True)

@@ -745,16 +745,20 @@ class PretrainEngine:
         return (per_mod * self.loss_w).sum()
 
     # ------------------------------------------------------------------ backward
-    # backward segments (cut points for gradient all-reduce overlap and CUDA-graph boundaries); the per-group encoder
-    # stacks are cut into three chunks of layers so that the all-reduce of the upper layers runs under the backward
-    # of the lower ones (the encoders hold 3/4 of the parameters)
-    BWD_SEGMENTS = ("decoder", "inter", "encoder_top", "encoder_mid", "encoder_low")
+    # backward segments (cut points for gradient all-reduce overlap and CUDA-graph boundaries): decoder side, joint
+    # encoder, then the per-group encoder stacks (3/4 of the parameters) cut into chunks of layers -- the upper two
+    # thirds as two chunks, the lowest third layer by layer, so that the all-reduce left exposed after the last
+    # segment covers one layer + the patch embedding only
+    @property
+    def BWD_SEGMENTS(self) -> tuple:
+        return ("decoder", "inter") + tuple(f"encoder_{i}" for i in range(len(self._enc_chunks())))
 
     def _enc_chunks(self) -> list[tuple[int, int]]:
-        """Layer ranges [lo, hi) of the per-group encoder stacks handled by the three encoder segments, top first."""
+        """Layer ranges [lo, hi) of the per-group encoder stacks handled by the encoder segments, top first."""
         d = self.hp["depth"] - self.inter_depth
         a, b = d - d // 3, d - 2 * (d // 3)
-        return [(a, d), (b, a), (0, b)]
+        chunks = [(a, d), (b, a)] + [(i, i + 1) for i in reversed(range(1, b))] + [(0, min(1, b))]
+        return [c for i, c in enumerate(chunks) if c[1] > c[0] or i == len(chunks) - 1]
 
     def _enc_chunk_of(self, name: str) -> int:
         m = re.search(r"\.layers\.(\d+)\.", name)
@@ -769,7 +773,7 @@ class PretrainEngine:
         if name.startswith("encoder."):
             return 2 + self._enc_chunk_of(name)
         if name.startswith("patch_embed."):
-            return 4
+            return 2 + len(self._enc_chunks()) - 1
         return 0
 
     def grad_ranges(self) -> list[tuple[int, int]]:
@@ -800,7 +804,10 @@ class PretrainEngine:
         first = 0 if start is None else seg.index(start) + 1
         last = len(seg) - 1 if stop is None else seg.index(stop)
         for i in range(first, last + 1):
-            getattr(self, f"_backward_{seg[i]}")(ctx)
+            if seg[i].startswith("encoder_"):
+                self._backward_encoder_chunk(ctx, int(seg[i][len("encoder_"):]))
+            else:
+                getattr(self, f"_backward_{seg[i]}")(ctx)
 
     def _backward_decoder(self, ctx: dict) -> None:
         K, P, G, f32 = self.K, self.P, self.G, torch.float32
@@ -869,7 +876,8 @@ class PretrainEngine:
                                 dbias=self.bias_sink("encoder_inter.", self.inter_depth))
             ctx["dxcat"] = self.stack_bwd("encoder_inter.", dxcat, ctx["inter_saved"], B, nt, E, H, dh, self.mlp_e)
 
-    def _backward_encoder_top(self, ctx: dict) -> None:
+    def _encoder_bwd_begin(self, ctx: dict) -> None:
+        """Gradient of the stacks' final LayerNorms (first thing the encoder backward touches)."""
         K, P, G = self.K, self.P, self.G
         E, hp, B = self.E, self.hp, ctx["B"]
         H, dh = hp["heads"], hp["dim_head"]
@@ -892,22 +900,22 @@ class PretrainEngine:
                                 P[pre + "norm.weight"], None, dx, G[pre + "norm.weight"], G[pre + "norm.bias"], rows, E,
                                 dbias=self.bias_sink(pre, depth_g))
             dxs.append(dx)
-        lo, hi = self._enc_chunks()[0]
-        ctx["enc_dxs"] = self.stacks_bwd(enc_pre, dxs, ctx["enc_saved"], B, [g.n_kept for g in glist], E, H, dh,
-                                         self.mlp_e, lo, hi)
+        ctx["enc_dxs"] = dxs
 
     def _backward_encoder_chunk(self, ctx: dict, ci: int) -> None:
+        chunks = self._enc_chunks()
+        if ci == 0:
+            self._encoder_bwd_begin(ctx)
         hp, glist = self.hp, list(self.groups.values())
-        lo, hi = self._enc_chunks()[ci]
+        lo, hi = chunks[ci]
         ctx["enc_dxs"] = self.stacks_bwd([f"encoder.{g.name}." for g in glist], ctx["enc_dxs"], ctx["enc_saved"],
                                          ctx["B"], [g.n_kept for g in glist], self.E, hp["heads"], hp["dim_head"],
                                          self.mlp_e, lo, hi)
+        if ci == len(chunks) - 1:
+            self._encoder_bwd_end(ctx)
 
-    def _backward_encoder_mid(self, ctx: dict) -> None:
-        self._backward_encoder_chunk(ctx, 1)
-
-    def _backward_encoder_low(self, ctx: dict) -> None:
-        self._backward_encoder_chunk(ctx, 2)
+    def _encoder_bwd_end(self, ctx: dict) -> None:
+        """Keep-gather, GroupNorm and patch-embedding gradients (after the lowest encoder layer)."""
         K, P, G = self.K, self.P, self.G
         E, B = self.E, ctx["B"]
         glist = list(self.groups.values())

@@ -41,17 +41,42 @@ class FusedAdamW:
         self.lr, self.betas, self.eps, self.wd, self.schedule = lr, betas, eps, weight_decay, schedule
         self.t = 0
         self.hyper = torch.zeros(8, dtype=torch.float32, device=a.param.device)
-        self.hyper_host = torch.zeros(8, dtype=torch.float32).pin_memory() if a.param.is_cuda else torch.zeros(8)
+        # hyper-parameters travel through a ring of pinned slots: the host may run several steps ahead of the GPU, and
+        # a single slot would be overwritten before its (asynchronous) copy has executed
+        self._cuda = a.param.is_cuda
+        self._slots = [torch.zeros(8, dtype=torch.float32).pin_memory() if self._cuda else torch.zeros(8)
+                       for _ in range(4)]
+        self._slot_ev = [None] * len(self._slots)
 
-    def step(self, grad_scale: float = 1.0) -> None:
+    def step_begin(self, grad_scale: float = 1.0) -> None:
+        """Advance the step counter / schedule and publish this step's hyper-parameters (current stream)."""
         self.t += 1
         lr = self.schedule.lr(self.t - 1) if self.schedule is not None else self.lr
         b1, b2 = self.betas
-        h = self.hyper_host
+        i = self.t % len(self._slots)
+        if self._slot_ev[i] is not None:
+            self._slot_ev[i].synchronize()
+        h = self._slots[i]
         h[0], h[1], h[2], h[3], h[4] = lr, b1, b2, self.eps, self.wd
         h[5], h[6], h[7] = 1 - b1 ** self.t, 1 - b2 ** self.t, grad_scale
         self.hyper.copy_(h, non_blocking=True)
+        if self._cuda:
+            ev = torch.cuda.Event()
+            ev.record()
+            self._slot_ev[i] = ev
+
+    def step_range(self, start: int, stop: int) -> None:
+        """Update arena elements [start, stop) (a parameter-aligned range, e.g. one of ``engine.grad_ranges()``) on the
+        current stream: a caller can update the ranges whose gradients are final while the backward still runs."""
+        if stop <= start:
+            return
         a = self.engine.arena
-        self.K.adamw_step(a.param, a.grad, self.m, self.v, a.shadow, self.hyper, True)
+        sh = a.shadow[start:stop] if a.shadow is not None else None
+        self.K.adamw_step(a.param[start:stop], a.grad[start:stop], self.m[start:stop], self.v[start:stop], sh,
+                          self.hyper, True)
+
+    def step(self, grad_scale: float = 1.0) -> None:
+        self.step_begin(grad_scale)
+        self.step_range(0, self.engine.arena.numel)
         # the kernel refreshed the bf16 shadow in the same pass (dgrad reads it untransposed: no other copies)
         self.engine.shadows_fresh = True

@@ -79,9 +79,9 @@ def test_default_mask_draws_are_valid(K):
     assert torch.isfinite(g).all() and float(g.abs().sum()) > 0
 
 
-@pytest.mark.parametrize("segments", [1, 3, 5])
+@pytest.mark.parametrize("segments", [1, 3, 99])
 def test_graphed_step_matches_eager(K, segments):
-    """CUDA-graph replay (1, 3 or all 5 backward segments) of the step == the eager step on the same mask draws."""
+    """CUDA-graph replay (1, 3 or every backward segment) of the step == the eager step on the same mask draws."""
     from maestro_b200.conf import MaskSpec
     from maestro_b200.engine import PretrainEngine
     from maestro_b200.graph import GraphedPretrainStep
