@@ -115,3 +115,35 @@ def test_graphed_step_matches_eager(K, segments):
     torch.cuda.synchronize()
     assert abs(loss_pf - loss_eager) <= 1e-3 * abs(loss_eager)
     assert eng.grad_ranges()[0][0] == 0 and eng.grad_ranges()[-1][1] == eng.arena.numel
+
+
+def test_ranged_adamw_equals_whole_arena_update(K):
+    """FusedAdamW.step_range over engine.grad_ranges() == one update of the whole arena (same hyper-parameters), and the
+    ranges tile the arena in backward-completion order."""
+    from maestro_b200.conf import MaskSpec
+    from maestro_b200.engine import PretrainEngine
+    from maestro_b200.optim import FusedAdamW, OneCycle
+    name = "micro_flair"
+    spec, hp, sd, batch, inter, loss_kind, seed, bs = U.case_inputs(name)
+    outs = []
+    for ranged in (False, True):
+        eng = PretrainEngine(spec, hp, MaskSpec(), K, "cuda", torch.bfloat16, inter_depth=inter, loss=loss_kind)
+        eng.load_state_dict(sd)
+        opt = FusedAdamW(eng, lr=1e-3, weight_decay=0.05, schedule=OneCycle(1e-3, 10))
+        gen = torch.Generator(device="cuda").manual_seed(1)
+        for _ in range(3):
+            eng.arena.grad.copy_(torch.randn(eng.arena.numel, generator=gen, device="cuda") * 1e-2)
+            if ranged:
+                rng = eng.grad_ranges()
+                assert rng[0][0] == 0 and rng[-1][1] == eng.arena.numel
+                assert all(a[1] == b[0] for a, b in zip(rng, rng[1:])) and len(rng) == len(eng.BWD_SEGMENTS)
+                opt.step_begin(grad_scale=0.5)
+                for a, b in rng:
+                    opt.step_range(a, b)
+            else:
+                opt.step(grad_scale=0.5)
+            assert float(eng.arena.grad.abs().max()) == 0.0          # the update zeroes the gradient
+        torch.cuda.synchronize()
+        outs.append((eng.arena.param.clone(), eng.arena.shadow.clone(), opt.m.clone(), opt.v.clone()))
+    for x, y in zip(*outs):
+        assert torch.equal(x, y)
