@@ -187,17 +187,25 @@ def run_ours(args):
     from maestro_b200.dist import GradReducer
     reducer = GradReducer(eng.arena.grad, eng.grad_ranges())
 
+    gate = {"seg": 0, "marks": None}       # graph index ahead of which the next step's H2D copy may start
+
     def replay_segments(before_tail=None):
         """Replay the step graph by graph; for N > 1 all-reduce each finished arena range on the comm stream.
-        ``before_tail`` runs ahead of the third-last graph (lowest three encoder layers + patch embedding: ~3.5 ms of
-        backward, then 1.8 ms of AdamW -- longer than the 3.9 ms H2D transfer it gates).
+        ``before_tail`` runs ahead of graph ``gate['seg']``: the latest point that still leaves 1.3x the measured H2D
+        transfer time before the step ends (chosen after the warm-up from event timings: at N = 1 the last three
+        graphs + AdamW = ~5 ms for a 3.9 ms transfer; with 8 ranks sharing the host's memory the transfer is slower
+        and the gate moves earlier).
         (Updating each finished range with AdamW on the side stream under the remaining backward was measured too:
         no gain at N = 1, 0.6 % at N = 2 -- the update's CTAs cannot share an SM with the register-full GEMM /
         attention CTAs, so it only displaces them.)"""
         n = len(gstep.graphs)
         for i in range(n):
-            if i == max(0, n - 3) and before_tail is not None:
+            if i == gate["seg"] and before_tail is not None:
                 before_tail()
+            if gate["marks"] is not None:
+                ev = torch.cuda.Event(enable_timing=True)
+                ev.record()
+                gate["marks"].append(ev)
             gstep.replay(i)
             if world > 1:
                 reducer.reduce_range(i)
@@ -213,6 +221,10 @@ def run_ours(args):
             from maestro_b200.dist import data_parallel_step
             loss = data_parallel_step(eng, dict(batch), reducer)
         opt.step(grad_scale=reducer.grad_scale)
+        if gate["marks"] is not None:
+            ev = torch.cuda.Event(enable_timing=True)
+            ev.record()
+            gate["marks"].append(ev)
         return loss
 
     prefetched = [False]
@@ -267,7 +279,19 @@ def run_ours(args):
         return float(ms[0])
 
     for i in range(args.warmup):
+        if use_graph and i == args.warmup - 1:
+            gate["marks"] = []                           # time the graphs of the last warm-up step
         step_e2e(i)
+    if use_graph and gate["marks"]:
+        torch.cuda.synchronize()
+        marks, (h0, h1) = gate["marks"], gstep.h2d_events
+        gate["marks"] = None
+        h2d_ms = h0.elapsed_time(h1)                     # measured with every rank's transfer running
+        tail = [m.elapsed_time(marks[-1]) for m in marks[:-1]]      # time from the start of graph i to the step's end
+        ok = [i for i, t in enumerate(tail) if t >= 1.3 * h2d_ms]
+        gate["seg"] = max(ok) if ok else 0
+        print(f"[rank {rank}] H2D {h2d_ms:.2f} ms per step; gated ahead of graph {gate['seg']} of {len(tail)} "
+              f"({tail[gate['seg']]:.2f} ms before the step ends)", file=sys.stderr)
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()

@@ -138,10 +138,13 @@ class GraphedPretrainStep:
             gate.record(torch.cuda.current_stream(self.dev))
             cs.wait_event(gate)
         with torch.cuda.stream(cs):
+            t0 = torch.cuda.Event(enable_timing=True)
+            t0.record(cs)
             for k, dst in self.staging.items():
                 dst.copy_(batch[k], non_blocking=True)
-            self._staged = torch.cuda.Event()
+            self._staged = torch.cuda.Event(enable_timing=True)
             self._staged.record(cs)
+            self.h2d_events = (t0, self._staged)       # callers size the gate from the measured transfer time
 
     def load_prefetched(self, struct: dict | None = None) -> None:
         """Make the prefetched inputs current (device-to-device into the graph's static buffers) + struct mask."""
