@@ -28,7 +28,7 @@ struct LossParams {
 
 template <typename T>
 __global__ void __launch_bounds__(128) group_norm_masked_loss_kernel(LossParams P) {
-  extern __shared__ float smem[];
+  extern __shared__ __align__(16) float smem[];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = blockDim.x >> 5;
   const int g = P.S / P.p, L = g * g, pp = P.p * P.p;
   const int npix = pp * P.C;
@@ -131,21 +131,25 @@ __global__ void __launch_bounds__(128) group_norm_masked_loss_kernel(LossParams 
   }
 }
 
-// Vector form of the kernel above for p % 4 == 0 (every modality with real patches; the scalar kernel keeps p = 1, 2):
-// the target patch is fetched as float4 rows (one runtime division per 4 pixels), the per-channel mean / 1 / std go
-// through a small shared table instead of a register select chain, and predictions / gradients move as 16-byte
-// chunks with (pixel, channel) tracked incrementally (one division per chunk).
+// Vector form of the kernel above for p % 4 == 0 (every modality with real patches; the scalar kernel keeps p = 1, 2).
+// The target patch stays CHANNEL-PLANAR in shared memory, the order it has in HBM: float4 rows are fetched eight deep
+// per lane (all in flight before the first use) and stored as float4 (conflict-free), the channels of one norm group
+// are one contiguous span, so the centred second pass reads float4 as well; per-channel mean / 1 / std go through a
+// small shared table and, when a 16-byte prediction chunk holds whole pixels, into registers once per patch.
+// Predictions / gradients move as 16-byte chunks with (pixel, channel) tracked incrementally.
 template <typename T>
-__global__ void __launch_bounds__(128) group_norm_masked_loss_vec_kernel(LossParams P) {
+__global__ void __launch_bounds__(128, 6) group_norm_masked_loss_vec_kernel(LossParams P) {
   constexpr int V = VecIO<T>::N;
-  extern __shared__ float smem[];
+  constexpr int DEPTH = 8;
+  extern __shared__ __align__(16) float smem[];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = blockDim.x >> 5;
   const int g = P.S / P.p, L = g * g, pp = P.p * P.p, p4 = P.p / 4, pp4 = pp / 4;
   const int npix = pp * P.C;
-  float* tg = smem + static_cast<size_t>(w) * (npix + 2 * LOSS_MAX_C);
+  float* tg = smem + static_cast<size_t>(w) * (npix + 2 * LOSS_MAX_C);   // [C][p][p]
   float* mu_s = tg + npix;                 // per channel: mean, 1 / sqrt(var + eps) of its norm group
   float* ri_s = mu_s + LOSS_MAX_C;
   const long long n_patch = static_cast<long long>(P.B) * P.D * L;
+  const size_t plane = static_cast<size_t>(P.S) * P.S;
   float err_sum = 0.f, cnt_sum = 0.f;
   const float coef = (P.coef != nullptr) ? *P.coef : 0.f;
   float zeros[V];
@@ -169,23 +173,35 @@ __global__ void __launch_bounds__(128) group_norm_masked_loss_vec_kernel(LossPar
       for (int e = lane * V; e < P.cg[gi] * pp; e += 32 * V) VecIO<T>::store(dp + e, zeros);
     }
     if (mbits == 0) continue;
-    // stage the target patch: global (ch, py, px) -> shared (py, px, ch); group sums on the way
+    // stage the target patch, channel-planar as in HBM; group sums on the way
     const int gy = l / g, gx = l % g;
-    const float* tbase = P.target + static_cast<size_t>(img) * P.C * P.S * P.S + static_cast<size_t>(gy) * P.p * P.S +
+    const float* tbase = P.target + static_cast<size_t>(img) * P.C * plane + static_cast<size_t>(gy) * P.p * P.S +
                          gx * P.p;
     int ch0 = 0;
     const int ngroups = P.n_norm > 0 ? P.n_norm : 1;
     for (int n = 0; n < ngroups; ++n) {
       const int cn = P.n_norm > 0 ? P.norm_size[n] : P.C;
+      const int tot = cn * pp4;              // float4 elements of this norm group's channels
+      float4* span = reinterpret_cast<float4*>(tg + ch0 * pp);
       float sacc = 0.f;
-      for (int ch = ch0; ch < ch0 + cn; ++ch) {
-        const float* tch = tbase + static_cast<size_t>(ch) * P.S * P.S;
-        for (int i4 = lane; i4 < pp4; i4 += 32) {
-          const int py = i4 / p4, px = (i4 - py * p4) * 4;
-          const float4 v = __ldg(reinterpret_cast<const float4*>(tch + static_cast<size_t>(py) * P.S + px));
-          float* o = tg + (py * P.p + px) * P.C + ch;
-          o[0] = v.x; o[P.C] = v.y; o[2 * P.C] = v.z; o[3 * P.C] = v.w;
-          sacc += (v.x + v.y) + (v.z + v.w);
+      for (int base = lane; base < tot; base += 32 * DEPTH) {
+        float4 v[DEPTH];
+#pragma unroll
+        for (int k = 0; k < DEPTH; ++k) {
+          const int idx = base + 32 * k;
+          if (idx < tot) {
+            const int ch = idx / pp4, i4 = idx - ch * pp4;
+            const int py = i4 / p4, px = (i4 - py * p4) * 4;
+            v[k] = __ldg(reinterpret_cast<const float4*>(tbase + (ch0 + ch) * plane + static_cast<size_t>(py) * P.S + px));
+          }
+        }
+#pragma unroll
+        for (int k = 0; k < DEPTH; ++k) {
+          const int idx = base + 32 * k;
+          if (idx < tot) {
+            span[idx] = v[k];
+            sacc += (v[k].x + v[k].y) + (v[k].z + v[k].w);
+          }
         }
       }
       if (P.n_norm > 0) {
@@ -193,11 +209,10 @@ __global__ void __launch_bounds__(128) group_norm_masked_loss_vec_kernel(LossPar
         const float mean = warp_sum(sacc) / cnt;
         __syncwarp();
         float ss = 0.f;
-        for (int ch = ch0; ch < ch0 + cn; ++ch) {
-          for (int i = lane; i < pp; i += 32) {
-            const float t = tg[i * P.C + ch] - mean;
-            ss = fmaf(t, t, ss);
-          }
+        for (int idx = lane; idx < tot; idx += 32) {
+          const float4 t = span[idx];
+          const float a0 = t.x - mean, a1 = t.y - mean, a2 = t.z - mean, a3 = t.w - mean;
+          ss = fmaf(a0, a0, ss); ss = fmaf(a1, a1, ss); ss = fmaf(a2, a2, ss); ss = fmaf(a3, a3, ss);
         }
         const float var = warp_sum(ss) / (cnt - 1);
         if (lane >= ch0 && lane < ch0 + cn) {
@@ -217,6 +232,15 @@ __global__ void __launch_bounds__(128) group_norm_masked_loss_vec_kernel(LossPar
       const int cgi = P.cg[gi], ne = cgi * pp, c0 = P.c0[gi];
       const T* pr = static_cast<const T*>(P.pred[gi]) + static_cast<size_t>(patch) * ne;
       T* dp = P.dpred[gi] != nullptr ? static_cast<T*>(P.dpred[gi]) + static_cast<size_t>(patch) * ne : nullptr;
+      const bool whole = (V % cgi) == 0;      // a chunk holds whole pixels: channel of element k is c0 + k % cgi
+      float muk[V] = {}, rik[V] = {};
+      if (whole) {
+#pragma unroll
+        for (int k = 0; k < V; ++k) {
+          muk[k] = mu_s[c0 + k % cgi];
+          rik[k] = ri_s[c0 + k % cgi];
+        }
+      }
       for (int e0 = lane * V; e0 < ne; e0 += 32 * V) {
         float pv[V], gv[V];
         VecIO<T>::load(pr + e0, pv);
@@ -224,7 +248,8 @@ __global__ void __launch_bounds__(128) group_norm_masked_loss_vec_kernel(LossPar
 #pragma unroll
         for (int k = 0; k < V; ++k) {
           const int ch = c0 + cl;
-          const float t = (tg[pix * P.C + ch] - mu_s[ch]) * ri_s[ch];
+          const float tv = tg[ch * pp + pix];
+          const float t = whole ? (tv - muk[k]) * rik[k] : (tv - mu_s[ch]) * ri_s[ch];
           const float diff = t - pv[k];  // reference: loss_fn(target - pred)
           if (P.l2) {
             err_sum = fmaf(diff, diff, err_sum);
@@ -262,6 +287,10 @@ static void launch_loss(const LossParams& P, int blocks, int nw, cudaStream_t st
     if (smem > 48 * 1024)
       cudaFuncSetAttribute(group_norm_masked_loss_vec_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                            static_cast<int>(smem));
+    // persistent grid: exactly the CTAs that are resident at once (registers / shared memory decide), so no tail wave
+    int per_sm = 0;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, group_norm_masked_loss_vec_kernel<T>, nw * 32, smem);
+    if (per_sm > 0 && blocks > 148 * per_sm) blocks = 148 * per_sm;
     group_norm_masked_loss_vec_kernel<T><<<blocks, nw * 32, smem, st>>>(P);
   } else {
     const size_t smem = static_cast<size_t>(nw) * pp * P.C * sizeof(float);

@@ -85,6 +85,25 @@ def main():
             unit = "GB/s" if kind == "B" else "TFLOP/s"
             tot[name] = tot.get(name, 0.0) + ms * (9 if tag.startswith("enc") else 3)
             print(f"{tag:11s} {name:11s} rows={rows:6d} N={N:5d}  {ms * 1e3:8.1f} us  {rate:8.1f} {unit}", flush=True)
+    # reconstruction loss (forward + gradient in one pass), FLAIR-HUB image modalities: algorithmic bytes =
+    # masked fraction x fp32 target + bf16 pred read + bf16 dpred write
+    for tag, (Cc, S, p, nb) in {"loss_aerial": (4, 512, 16, [1, 3]), "loss_dem": (2, 512, 32, [2])}.items():
+        if (args.tag and args.tag != tag) or (args.only and args.only not in "loss"):
+            continue
+        g = S // p
+        L = g * g
+        target = torch.rand(B, 1, Cc, S, S, device=dev)
+        pred = torch.randn(B * L, Cc * p * p, device=dev).to(bf)
+        dpred = torch.empty_like(pred)
+        mask = (torch.rand(B, L, device=dev) < 0.75).to(torch.uint8)
+        coef = torch.full((1,), 1e-3, device=dev)
+        accum = torch.zeros(2, device=dev, dtype=torch.float64)
+        frac = float(mask.float().mean())
+        work = frac * target.numel() * 4 + pred.numel() * 2 * 2
+        ms = timeit(lambda: K.loss_fwd_bwd(target, [pred], [dpred], mask, coef, accum, B, 1, Cc, S, p, L, 0, [Cc], nb,
+                                           False), args.iters, flush)
+        print(f"{tag:11s} {'loss':11s} rows={B * L:6d} N={L:5d}  {ms * 1e3:8.1f} us  {work / ms / 1e6:8.1f} GB/s",
+              flush=True)
     print("per-step totals (x9 encoder layers, x3 inter / decoder layers; LN: x2 per layer):")
     for k, v in tot.items():
         print(f"  {k:11s} {v * (2 if k.startswith('ln') else 1):7.3f} ms")
