@@ -149,6 +149,40 @@ int mb_attn_fwd(const void* qkv, void* o, float* lse, int Bn, int N, int H, int 
 int mb_attn_bwd(const void* qkv, const void* o, const void* d_o, const float* lse, void* dqkv, float* delta, int Bn,
                 int N, int H, int dh, void* stream);
 
+/* ---- device-side input pipeline ----------------------------------------------------------------- */
+#define MB_RAW_U8 0
+#define MB_RAW_I16 1
+#define MB_RAW_U16 2
+#define MB_RAW_F32 3
+#define MB_AUG_FLIP_H 1     /* np.flip(axis=2) */
+#define MB_AUG_FLIP_W 2     /* np.flip(axis=3) */
+#define MB_AUG_TRANSPOSE 4  /* np.swapaxes(2, 3), applied after the flips */
+/* Raster as stored on disk -> fp32 model input: maestro/dataset/dataset.py:215-222 (astype(float32),
+ * log(max(x, 1e-10)) if log_scale, /= norm_fac if use_norm) and transform_rasters :225-257 (the dihedral
+ * augmentation; aug[sample] holds the MB_AUG_* bits, NULL = none; image i belongs to sample i / imgs_per_sample).
+ * raw [n_img, C, H, W] (or [.., W, H] for a transposed sample), out [n_img, C, H, W]; H == W when transposing. */
+int mb_raster_transform(const void* raw, int raw_dtype, float* out, const unsigned char* aug, int n_img,
+                        int imgs_per_sample, int C, int H, int W, float norm_fac, int use_norm, int log_scale,
+                        void* stream);
+
+#define MB_STRUCT_MAX_MODS 8
+typedef struct {
+  int G, D, L;                             /* band groups, dates per band group, grid^2 locations */
+  float p_mod, p_bands, p_dates, p_loc;    /* <= 0: draw skipped (maestro/ssl/mae.py:199-208) */
+} mb_struct_mod;
+typedef struct {
+  mb_struct_mod mods[MB_STRUCT_MAX_MODS];  /* modalities of the group in dataset.groups order */
+  int n_mods;
+  int L_group;                             /* sum of G * D * L */
+  unsigned long long seed, offset;         /* Philox key / per-step counter offset */
+} mb_struct_params;
+/* MAE.mask_struct, maestro/ssl/mae.py:178-226, drawn on the device (performance mode; the reference's host
+ * torch.rand order stays available on the host side): Philox4x32-10, counter (index, kind | mod << 8, sample,
+ * offset + pass), u = (x >> 8) * 2^-24 < p.  One CTA per sample redraws (pass + 1) until its group is not entirely
+ * masked.  `params` is a HOST pointer.  out [B, L_group] u8; passes [B] (may be NULL) = draws the sample took. */
+int mb_struct_mask(const mb_struct_params* params, unsigned char* out, int* passes, int B, int max_pass,
+                   void* stream);
+
 /* ---- optimiser ---------------------------------------------------------------------------------------------- */
 /* torch.optim.AdamW built at maestro/train/model.py:135-149, fused over the flat arena (+ bf16 shadow refresh). */
 int mb_adamw_step(float* p, float* g, float* m, float* v, void* shadow, const float* hyper, size_t n, int zero_grad,

@@ -16,7 +16,7 @@ HERE = Path(__file__).resolve().parent
 CSRC = HERE / "csrc"
 SO_PATH = HERE / "libmaestro_b200.so"
 SOURCES = ["elementwise.cu", "norm.cu", "mask.cu", "unmask.cu", "loss.cu", "gemm_simt.cu", "gemm_tc.cu",
-           "tmap.cu", "attn_tc.cu", "attn_bwd_tc.cu", "optim.cu"]
+           "tmap.cu", "attn_tc.cu", "attn_bwd_tc.cu", "optim.cu", "input.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"]
 
@@ -87,6 +87,23 @@ class LossParams(C.Structure):
     ]
 
 
+STRUCT_MAX_MODS = 8
+
+
+class StructMod(C.Structure):
+    """Mirror of ``mb_struct_mod`` (include/maestro_b200.h, csrc/input.cu)."""
+
+    _fields_ = [("G", C.c_int), ("D", C.c_int), ("L", C.c_int),
+                ("p_mod", C.c_float), ("p_bands", C.c_float), ("p_dates", C.c_float), ("p_loc", C.c_float)]
+
+
+class StructParams(C.Structure):
+    """Mirror of ``mb_struct_params``."""
+
+    _fields_ = [("mods", StructMod * STRUCT_MAX_MODS), ("n_mods", C.c_int), ("L_group", C.c_int),
+                ("seed", C.c_ulonglong), ("offset", C.c_ulonglong)]
+
+
 _LIB = None
 
 
@@ -111,5 +128,5 @@ EXPORTS = [
     "mb_layernorm_fwd", "mb_layernorm_bwd", "mb_gn_stats", "mb_gn_apply", "mb_gn_bwd",
     "mb_mask_indices", "mb_gather_rows", "mb_scatter_kept", "mb_unmask_fwd", "mb_masktoken_grad",
     "mb_loss_fwd_bwd", "mb_gemm_simt", "mb_softmax_rows", "mb_softmax_bwd_rows", "mb_gemm_tc", "mb_gemm_tc_grouped",
-    "mb_adamw_step", "mb_attn_fwd", "mb_attn_bwd",
+    "mb_adamw_step", "mb_attn_fwd", "mb_attn_bwd", "mb_raster_transform", "mb_struct_mask",
 ]

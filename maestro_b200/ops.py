@@ -18,6 +18,8 @@ from . import _lib
 F32, BF16 = 0, 1
 GEMM_GELU, GEMM_DGELU, GEMM_ACCUM, GEMM_OUT_F32 = 1, 2, 4, 8
 GEMM_PAIR_ON, GEMM_PAIR_OFF = 16, 32      # scheduling hints of the tensor-core path (tests, tuning)
+RAW_CODES = {torch.uint8: 0, torch.int16: 1, torch.uint16: 2, torch.float32: 3}   # MB_RAW_* of the header
+AUG_FLIP_H, AUG_FLIP_W, AUG_TRANSPOSE = 1, 2, 4
 
 
 def _dt(t: torch.Tensor) -> int:
@@ -281,3 +283,35 @@ class Kernels:
         self.launches += 1
         _ck(self.L.mb_adamw_step(_p(p), _p(g), _p(m), _p(v), _p(shadow), _p(hyper), C.c_size_t(p.numel()),
                                  int(zero_grad), _stream()), "adamw_step")
+
+    # ------------------------------------------------------------------ device-side input pipeline
+    def raster_transform(self, raw, out, aug, imgs_per_sample, norm_fac, log_scale):
+        """raw [n_img, C, H, W] (uint8 / int16 / uint16 / float32) -> out fp32 (dataset.py:215-257 on the device)."""
+        code = RAW_CODES.get(raw.dtype)
+        if code is None:
+            raise TypeError(f"unsupported raster dtype {raw.dtype}")
+        n, Cc, H, W = out.shape
+        if raw.numel() != out.numel() or not raw.is_contiguous() or not out.is_contiguous():
+            raise ValueError("raster_transform needs contiguous raw / out tensors of equal element count")
+        self.launches += 1
+        _ck(self.L.mb_raster_transform(_p(raw), code, _p(out), _p(aug), n, int(imgs_per_sample), Cc, H, W,
+                                       C.c_float(norm_fac if norm_fac is not None else 1.0),
+                                       int(norm_fac is not None), int(bool(log_scale)), _stream()),
+            "raster_transform")
+
+    def struct_mask(self, mods, seed, offset, out, passes=None, max_pass=0):
+        """mods: [(G, D, L, p_mod, p_bands, p_dates, p_loc)] of one group; out [B, L_group] uint8."""
+        P = _lib.StructParams()
+        if not 0 < len(mods) <= _lib.STRUCT_MAX_MODS:
+            raise ValueError(f"a group holds 1..{_lib.STRUCT_MAX_MODS} modalities")
+        for i, (G, D, L, pm, pb, pd, pl) in enumerate(mods):
+            P.mods[i] = _lib.StructMod(int(G), int(D), int(L), float(pm or 0.0), float(pb or 0.0), float(pd or 0.0),
+                                       float(pl or 0.0))
+        P.n_mods = len(mods)
+        P.L_group = sum(int(m[0]) * int(m[1]) * int(m[2]) for m in mods)
+        P.seed, P.offset = int(seed) & (2**64 - 1), int(offset) & (2**64 - 1)
+        if out.shape[-1] != P.L_group or out.dtype != torch.uint8:
+            raise ValueError("struct_mask: out must be uint8 [B, L_group]")
+        self.launches += 1
+        _ck(self.L.mb_struct_mask(C.byref(P), _p(out), _p(passes), out.shape[0], int(max_pass), _stream()),
+            "struct_mask")

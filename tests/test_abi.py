@@ -29,6 +29,9 @@ def test_struct_mirrors_match_header_sizes():
     # mb_gemm_params: 6 pointers, 3 ints (+pad), 4 int64, 3 ints (+pad), 6 int64, float, int, pointer
     assert ctypes.sizeof(_lib.GemmParams) == 6 * 8 + 16 + 4 * 8 + 16 + 6 * 8 + 8 + 8
     assert ctypes.sizeof(_lib.LossParams) % 8 == 0
+    # mb_struct_mod: 3 ints + 4 floats; mb_struct_params: 8 mods, 2 ints, 2 uint64
+    assert ctypes.sizeof(_lib.StructMod) == 28
+    assert ctypes.sizeof(_lib.StructParams) == 8 * 28 + 8 + 16
 
 
 def test_product_has_no_cpu_path():
