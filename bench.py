@@ -48,6 +48,27 @@ def synthetic_batch(spec, B, seed, pin=False):
     return out
 
 
+def synthetic_raw_batch(spec, rasters, B, seed, pin=False):
+    """The same tiles as ``synthetic_batch`` one stage earlier: rasters in their on-disk dtype (what
+    ``preprocess_raster`` holds before dataset/dataset.py:215) plus the per-sample augmentation bits of
+    ``transform_rasters`` (:224-257); value ranges chosen so that the device transform lands in the fp32 batch's."""
+    import numpy as np
+    from maestro_b200.dataset import draw_augmentation
+    out = synthetic_batch(spec, B, seed)
+    for name, m in spec.inputs.items():
+        r, x = rasters[name], out[name]
+        if r.log_scale:
+            x = torch.exp(x * r.norm_fac)
+        elif r.norm_fac is not None:
+            x = x * r.norm_fac
+        out[name] = x.round().clamp_(0, 255).to(torch.uint8) if r.dtype == torch.uint8 else (
+            x.round().to(r.dtype) if not r.dtype.is_floating_point else x.to(r.dtype))
+    out["aug"] = draw_augmentation(np.random.default_rng(seed), B)
+    if pin:
+        out = {k: v.pin_memory() for k, v in out.items()}
+    return out
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons sampled during the timed region."""
 
@@ -173,7 +194,16 @@ def run_ours(args):
     opt = FusedAdamW(eng, lr=1e-4, weight_decay=0.01, schedule=OneCycle(1e-4, 100000))
     host = [synthetic_batch(spec, B, seed=100 + 7 * rank + i, pin=True) for i in range(2)]
     devb = {k: v.to(dev) for k, v in host[0].items()}
-    h2d = sum(v.numel() * v.element_size() for v in host[0].values())
+    raw_rasters = None
+    if args.input == "raw":
+        from maestro_b200.dataset import FLAIR_RASTERS
+        if args.no_graph:
+            raise SystemExit("bench.py: --input raw needs the graphed step")
+        raw_rasters = {n: FLAIR_RASTERS[n] for n in spec.inputs}
+        host_e2e = [synthetic_raw_batch(spec, raw_rasters, B, seed=100 + 7 * rank + i, pin=True) for i in range(2)]
+    else:
+        host_e2e = host
+    h2d = sum(v.numel() * v.element_size() for v in host_e2e[0].values())
     loss_host = torch.zeros(1).pin_memory()
     torch.manual_seed(1234 + rank)
 
@@ -181,7 +211,8 @@ def run_ours(args):
     gstep = None
     if use_graph:
         from maestro_b200.graph import GraphedPretrainStep
-        gstep = GraphedPretrainStep(eng, host[0], segments=len(eng.BWD_SEGMENTS))
+        gstep = GraphedPretrainStep(eng, host[0], segments=len(eng.BWD_SEGMENTS), raw_rasters=raw_rasters,
+                                    struct_on_device=args.struct == "device", struct_seed=4321 + rank)
         eng.zero_grad()
         devb = gstep.batch
     from maestro_b200.dist import GradReducer
@@ -233,7 +264,7 @@ def run_ours(args):
     loss_pending = [False, False]
 
     def step_e2e(i):
-        hb = host[i % 2]
+        hb = host_e2e[i % 2]
         if use_graph:
             # input pipeline: the H2D copy of step i + 1 (pinned host memory -> staging) runs on a copy stream while
             # step i computes; every step's inputs cross PCIe exactly once, inside the timed region.  The transfer is
@@ -243,7 +274,7 @@ def run_ours(args):
                 gstep.prefetch(hb)
                 prefetched[0] = True
             gstep.load_prefetched()
-            nxt = host[(i + 1) % 2]
+            nxt = host_e2e[(i + 1) % 2]
             loss = step_device(devb, staged=True, before_tail=lambda: gstep.prefetch(nxt, after_current_work=True))
         else:
             for k, v in hb.items():
@@ -391,7 +422,12 @@ def run_ours(args):
                    "attention": eng.attn_impl, "loss_last": last_loss,
                    "launch": "cuda-graph replay" if use_graph else "python",
                    "allreduce_bytes_per_step": reducer.bytes_per_step,
-                   "e2e_input_pipeline": "H2D of step i+1 on a copy stream overlaps step i; loss of every step read back to pinned memory, the host waits one step behind"},
+                   "e2e_input_pipeline": "H2D of step i+1 on a copy stream overlaps step i; loss of every step read back to pinned memory, the host waits one step behind",
+                   "e2e_input": ("on-disk dtypes (aerial u8, s2 i16, dem / s1 f32) + augmentation bits, finished by "
+                                 "mb_raster_transform on the device" if raw_rasters else
+                                 "fp32 tiles as the reference DataLoader delivers them"),
+                   "struct_mask": "device Philox (mb_struct_mask)" if args.struct == "device" else
+                                  "host generator, reference draw order"},
         "e2e": {"value": B * world / (e2e_ms * 1e-3), "unit": "tiles/s", "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": 4, "ms_per_step": e2e_ms},
         "gpu_launches": launches,
@@ -422,6 +458,11 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--input", default="fp32", choices=["fp32", "raw"],
+                    help="e2e host buffers: fp32 tiles (the reference's DataLoader output) or on-disk dtypes + "
+                         "augmentation bits finished on the device (mb_raster_transform)")
+    ap.add_argument("--struct", default="host", choices=["host", "device"],
+                    help="structural mask: reference host RNG order, or Philox on the device (mb_struct_mask)")
     ap.add_argument("--dataset", default="flair", choices=list(DATASET_SPECS))
     ap.add_argument("--size", default="medium", choices=list(MODEL_SIZES))
     ap.add_argument("--batch", type=int, default=32, help="tiles per GPU (reference default, conf/opt.py:20)")

@@ -559,6 +559,35 @@ class PretrainEngine:
                 cur[g.name] = torch.where(redo, new, cur[g.name])
         return cur
 
+    def struct_mods(self, group: str) -> list[tuple]:
+        """(G, D, L, p_mod, p_bands, p_dates, p_loc) per modality of ``group``: the draws ``mask_struct`` makes."""
+        mc, grp = self.mask_cfg, self.groups[group]
+        alone = len(grp.mods) == 1
+        out = []
+        for name in grp.mods:
+            mt = self.mods[name]
+            out.append((mt.G, mt.D, mt.L,
+                        (mc.mask_mod or 0.0) if (self.fusion_mode == "group" and not alone) else 0.0,
+                        (mc.mask_bands or 0.0) if mt.G > 1 else 0.0,
+                        (mc.mask_dates or 0.0) if mt.D > 1 else 0.0,
+                        mc.mask_loc or 0.0))
+        return out
+
+    def mask_struct_device(self, batch_size: int, seed: int, step: int,
+                           out: dict[str, torch.Tensor] | None = None) -> dict[str, torch.Tensor]:
+        """``mask_struct`` drawn on the device (performance mode): uint8 [B, L_group] per group from the
+        Philox stream of ``mb_struct_mask`` -- no host RNG loop, no H2D copy, no sync.  Same distribution as the
+        reference (mae.py:178-226: a sample redraws while its group is entirely masked), different random stream;
+        parity tests keep injecting the reference's own draws through ``forward(struct=...)``.  Each group gets its own
+        key, each step a disjoint counter range (2^20 redraws)."""
+        out = {} if out is None else out
+        for gi, g in enumerate(self.groups.values()):
+            if g.name not in out:
+                out[g.name] = torch.empty(batch_size, g.L, dtype=torch.uint8, device=self.device)
+            key = (int(seed) ^ ((gi + 1) * 0x9E3779B97F4A7C15)) & (2**64 - 1)
+            self.K.struct_mask(self.struct_mods(g.name), key, int(step) << 20, out[g.name], None, 1 << 20)
+        return out
+
     # ------------------------------------------------------------------ forward
     def forward(self, batch: dict, struct: dict | None = None, noise: dict | None = None,
                 unmask_order: dict | None = None) -> dict:

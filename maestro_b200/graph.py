@@ -23,7 +23,12 @@ from .engine import PretrainEngine
 
 class GraphedPretrainStep:
     def __init__(self, engine: PretrainEngine, example_batch: dict, static_noise: bool = False, segments: int = 1,
-                 warmup: int = 2) -> None:
+                 warmup: int = 2, raw_rasters: dict | None = None, struct_on_device: bool = False,
+                 struct_seed: int = 0) -> None:
+        """``raw_rasters`` ({modality: maestro_b200.dataset.RasterSpec}): ``prefetch`` then takes those modalities in
+        their on-disk dtype (+ ``batch["aug"]`` bits) and ``load_prefetched`` runs ``mb_raster_transform`` from the
+        staging buffers into the static fp32 inputs instead of a device-to-device copy.  ``struct_on_device``: the
+        structural mask comes from ``mb_struct_mask`` (Philox, no host loop / H2D) instead of the host generator."""
         if engine.device.type != "cuda":
             raise RuntimeError("GraphedPretrainStep needs a CUDA engine (there is no CPU path)")
         self.eng, self.dev = engine, engine.device
@@ -44,6 +49,8 @@ class GraphedPretrainStep:
                             for _ in range(2)]
         self._stage_ev = [None, None]
         self._stage_i = 0
+        self.raw_rasters = dict(raw_rasters or {})
+        self.struct_on_device, self.struct_seed, self._struct_step = bool(struct_on_device), int(struct_seed), 0
         self.noise = ({g.name: torch.rand(self.B, g.L, device=self.dev) for g in engine.groups.values()}
                       if static_noise else None)
         self.loss = torch.zeros((), dtype=torch.float32, device=self.dev)
@@ -90,6 +97,10 @@ class GraphedPretrainStep:
 
     # ------------------------------------------------------------------ per step
     def _draw_struct(self) -> None:
+        if self.struct_on_device:                                 # Philox on the device, straight into the static buffers
+            self.eng.mask_struct_device(self.B, self.struct_seed, self._struct_step, self.struct)
+            self._struct_step += 1
+            return
         draws = self.eng.mask_struct(self.B)                      # host generator, reference draw order
         i = self._stage_i
         self._stage_i ^= 1
@@ -128,7 +139,10 @@ class GraphedPretrainStep:
         update (the least sensitive phase) instead of under the forward."""
         if getattr(self, "_copy_stream", None) is None:
             self._copy_stream = torch.cuda.Stream(device=self.dev)
-            self.staging = {k: torch.empty_like(v) for k, v in self.batch.items()}
+            self.staging = {k: (torch.empty(v.shape, dtype=self.raw_rasters[k].dtype, device=self.dev)
+                                if k in self.raw_rasters else torch.empty_like(v)) for k, v in self.batch.items()}
+            if self.raw_rasters:
+                self.staging["aug"] = torch.zeros(self.B, dtype=torch.uint8, device=self.dev)
             self._staging_free = None
         cs = self._copy_stream
         if self._staging_free is not None:
@@ -141,6 +155,11 @@ class GraphedPretrainStep:
             t0 = torch.cuda.Event(enable_timing=True)
             t0.record(cs)
             for k, dst in self.staging.items():
+                if k == "aug" and batch.get("aug") is None:
+                    dst.zero_()
+                    continue
+                if batch[k].dtype != dst.dtype:
+                    raise TypeError(f"{k}: expected {dst.dtype}, got {batch[k].dtype}")
                 dst.copy_(batch[k], non_blocking=True)
             self._staged = torch.cuda.Event(enable_timing=True)
             self._staged.record(cs)
@@ -151,7 +170,13 @@ class GraphedPretrainStep:
         main = torch.cuda.current_stream(self.dev)
         main.wait_event(self._staged)
         for k, dst in self.batch.items():
-            dst.copy_(self.staging[k], non_blocking=True)
+            r = self.raw_rasters.get(k)
+            if r is None:
+                dst.copy_(self.staging[k], non_blocking=True)
+            else:       # on-disk dtype -> fp32 (+ augmentation, log scale, normalisation): dataset.py:215-257 on the device
+                Bq, D, Cc, H, W = dst.shape
+                self.eng.K.raster_transform(self.staging[k].view(Bq * D, Cc, H, W), dst.view(Bq * D, Cc, H, W),
+                                            self.staging["aug"], D, r.norm_fac, r.log_scale)
         self._staging_free = torch.cuda.Event()
         self._staging_free.record(main)
         if struct is None:

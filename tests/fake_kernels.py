@@ -304,3 +304,19 @@ class FakeKernels:
             g.zero_()
         if shadow is not None:
             shadow.copy_(p.to(torch.bfloat16))
+
+    # ------------------------------------------------------------------ device-side input pipeline (oracle-backed)
+    def raster_transform(self, raw, out, aug, imgs_per_sample, norm_fac, log_scale):
+        import input_oracle as O
+        n, Cc, H, W = out.shape
+        x = raw.cpu().numpy().reshape(n // imgs_per_sample, imgs_per_sample, Cc, *raw.shape[-2:])
+        bits = aug.cpu().numpy() if aug is not None else None
+        out.copy_(torch.from_numpy(O.raster_pipeline(x, bits, norm_fac, log_scale)).reshape(n, Cc, H, W))
+
+    def struct_mask(self, mods, seed, offset, out, passes=None, max_pass=0):
+        import input_oracle as O
+        m, ps = O.struct_mask([tuple(x) for x in mods], int(seed) & (2**64 - 1), int(offset) & (2**64 - 1),
+                              out.shape[0], max_pass or 1 << 20)
+        out.copy_(torch.from_numpy(m))
+        if passes is not None:
+            passes.copy_(torch.from_numpy(ps))

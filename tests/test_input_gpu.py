@@ -136,3 +136,65 @@ def test_struct_mask_full_batch_properties(K):
     assert torch.equal(v, dates[:, :, None] | loc[:, None, :])
     want = 1 - (1 - pd) * (1 - pl)
     assert abs(float(out.float().mean()) - want) < 0.01
+
+
+def test_graphed_step_raw_rasters_and_device_struct(K):
+    """The graphed step fed with on-disk-dtype rasters + augmentation bits (prefetch -> mb_raster_transform) equals the
+    same step fed with the fp32 tiles the oracle's host pipeline produces; the device structural mask replays into the
+    static buffers, is never entirely masked and changes from step to step."""
+    import parity_util as U
+    from maestro_b200.conf import MaskSpec
+    from maestro_b200.dataset import RasterSpec
+    from maestro_b200.engine import PretrainEngine
+    from maestro_b200.graph import GraphedPretrainStep
+    name = "micro_flair"
+    spec, hp, sd, batch, inter, loss_kind, seed, bs = U.case_inputs(name)
+    gold = U.load_golden(name)
+    struct, noise, _ = U.golden_draws(gold, spec)
+    B = batch["ref_date"].shape[0]
+    rng = np.random.default_rng(5)
+    rasters, raw, fp32 = {}, {}, {k: v for k, v in batch.items()}
+    aug = rng.integers(0, 8, B).astype(np.uint8)
+    for i, (n, m) in enumerate(spec.inputs.items()):
+        shape = tuple(batch[n].shape)
+        if i % 2 == 0:
+            rasters[n] = RasterSpec(torch.uint8, 255.0)
+            raw[n] = rng.integers(0, 256, shape, dtype=np.uint8)
+        else:
+            rasters[n] = RasterSpec(torch.int16, 3000.0)
+            raw[n] = rng.integers(0, 6000, shape).astype(np.int16)
+        fp32[n] = torch.from_numpy(O.raster_pipeline(raw[n], aug, rasters[n].norm_fac, False))
+    eng = PretrainEngine(spec, hp, MaskSpec(), K, "cuda", torch.bfloat16, inter_depth=inter, loss=loss_kind)
+    eng.load_state_dict(sd)
+    gs = GraphedPretrainStep(eng, batch, static_noise=True, segments=2, raw_rasters=rasters)
+    eng.zero_grad()
+    loss_fp32 = float(gs.step(fp32, struct, noise))
+    g_fp32 = eng.arena.grad.clone()
+    pinned = {k: (torch.from_numpy(raw[k]) if k in raw else v.clone()).pin_memory() for k, v in batch.items()}
+    pinned["aug"] = torch.from_numpy(aug).pin_memory()
+    gs.prefetch(pinned)
+    gs.load_prefetched(struct)
+    for n in raw:                                   # the static inputs hold exactly the host pipeline's tiles
+        assert torch.equal(gs.batch[n].cpu(), fp32[n])
+    eng.zero_grad()
+    loss_raw = float(gs.replay())
+    torch.cuda.synchronize()
+    assert abs(loss_raw - loss_fp32) <= 1e-5 * abs(loss_fp32)          # same inputs; fp32 atomics reorder sums
+    assert float(torch.nn.functional.cosine_similarity(eng.arena.grad, g_fp32, dim=0)) > 0.99999
+    with pytest.raises(TypeError):                  # fp32 tiles where raw rasters were announced
+        gs.prefetch({**pinned, **{n: fp32[n].pin_memory() for n in list(raw)[:1]}})
+    torch.cuda.synchronize()
+    # device structural mask
+    gd = GraphedPretrainStep(eng, batch, static_noise=True, struct_on_device=True, struct_seed=9)
+    seen = []
+    for _ in range(3):
+        eng.zero_grad()
+        loss = float(gd.step(batch, None, noise))
+        assert np.isfinite(loss)
+        for m in gd.struct.values():
+            assert not bool(m.bool().all(dim=1).any())
+        seen.append(torch.cat([m.flatten() for m in gd.struct.values()]).clone())
+    assert not torch.equal(seen[0], seen[1]) and not torch.equal(seen[1], seen[2])
+    want = eng.mask_struct_device(B, 9, 3)           # capture drew step 0; the three steps used 1..3
+    for n, m in want.items():
+        assert torch.equal(m, gd.struct[n])
