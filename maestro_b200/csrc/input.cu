@@ -60,34 +60,131 @@ raster_transform_kernel(const Raw* __restrict__ raw, float* __restrict__ out, co
   }
 }
 
+// Fast path for rasters whose sides are multiples of 64 (the aerial / DEM tiles): a CTA moves a 64 x 64 tile, every
+// thread 4 x (4 consecutive source elements -> one 16-byte store).  Flips only reverse the order of whole 4-element
+// chunks and of the elements inside a chunk, so untransposed samples go registers -> HBM directly; transposed samples
+// turn the tile through shared memory.
+template <typename Raw> struct Raw4;
+template <> struct Raw4<unsigned char> {
+  __device__ __forceinline__ static void load(const unsigned char* p, float* v) {
+    const uchar4 t = *reinterpret_cast<const uchar4*>(p);
+    v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+  }
+};
+template <> struct Raw4<short> {
+  __device__ __forceinline__ static void load(const short* p, float* v) {
+    const short4 t = *reinterpret_cast<const short4*>(p);
+    v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+  }
+};
+template <> struct Raw4<unsigned short> {
+  __device__ __forceinline__ static void load(const unsigned short* p, float* v) {
+    const ushort4 t = *reinterpret_cast<const ushort4*>(p);
+    v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+  }
+};
+template <> struct Raw4<float> {
+  __device__ __forceinline__ static void load(const float* p, float* v) {
+    const float4 t = *reinterpret_cast<const float4*>(p);
+    v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+  }
+};
+
+template <typename Raw>
+__global__ void __launch_bounds__(256)
+raster_transform64_kernel(const Raw* __restrict__ raw, float* __restrict__ out, const unsigned char* __restrict__ aug,
+                          int imgs_per_sample, int C, int H, int W, int tiles_x, int tiles_per_plane, float norm_fac,
+                          int use_norm, int log_scale) {
+  __shared__ float tile[64][65];
+  const unsigned plane = blockIdx.x / tiles_per_plane;
+  const unsigned t = blockIdx.x - plane * tiles_per_plane;
+  const int ti = t / tiles_x, tj = t - ti * tiles_x;
+  const int img = plane / C;
+  const int bits = aug ? aug[img / imgs_per_sample] : 0;
+  const bool fh = bits & MB_AUG_FLIP_H, fw = bits & MB_AUG_FLIP_W, tr = bits & MB_AUG_TRANSPOSE;
+  const int Hs = tr ? W : H, Ws = tr ? H : W;
+  const Raw* src = raw + static_cast<size_t>(plane) * Hs * Ws;
+  float* dst = out + static_cast<size_t>(plane) * H * W;
+  const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+  const int r0 = tr ? 64 * tj : 64 * ti, c0 = tr ? 64 * ti : 64 * tj;
+  float v[4][4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const int r = r0 + ty + 16 * k, c = c0 + 4 * tx;
+    const int sr = fh ? Hs - 1 - r : r, sc = fw ? Ws - 4 - c : c;
+    Raw4<Raw>::load(src + static_cast<size_t>(sr) * Ws + sc, v[k]);
+  }
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    if (fw) {
+      float a = v[k][0]; v[k][0] = v[k][3]; v[k][3] = a;
+      a = v[k][1]; v[k][1] = v[k][2]; v[k][2] = a;
+    }
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      float x = v[k][e];
+      if (log_scale) x = logf(x < 1e-10f ? 1e-10f : x);
+      if (use_norm) x = __fdiv_rn(x, norm_fac);
+      v[k][e] = x;
+    }
+  }
+  if (!tr) {
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+      *reinterpret_cast<float4*>(dst + static_cast<size_t>(r0 + ty + 16 * k) * W + c0 + 4 * tx) =
+          make_float4(v[k][0], v[k][1], v[k][2], v[k][3]);
+    return;
+  }
+#pragma unroll
+  for (int k = 0; k < 4; ++k)
+#pragma unroll
+    for (int e = 0; e < 4; ++e) tile[ty + 16 * k][4 * tx + e] = v[k][e];
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const int i = ty + 16 * k;
+    *reinterpret_cast<float4*>(dst + static_cast<size_t>(64 * ti + i) * W + 64 * tj + 4 * tx) =
+        make_float4(tile[4 * tx][i], tile[4 * tx + 1][i], tile[4 * tx + 2][i], tile[4 * tx + 3][i]);
+  }
+}
+
+template <typename Raw>
+static void launch_raster(const void* raw, float* out, const unsigned char* aug, int n_img, int imgs_per_sample, int C,
+                          int H, int W, float norm_fac, int use_norm, int log_scale, cudaStream_t s) {
+  const Raw* r = static_cast<const Raw*>(raw);
+  const bool fast = H % 64 == 0 && W % 64 == 0 && reinterpret_cast<uintptr_t>(raw) % (4 * sizeof(Raw)) == 0 &&
+                    reinterpret_cast<uintptr_t>(out) % 16 == 0;
+  const int ts = fast ? 64 : 32;
+  const int tiles_x = (W + ts - 1) / ts, tiles_y = (H + ts - 1) / ts;
+  const int g = n_img * C * tiles_x * tiles_y, tpp = tiles_x * tiles_y;
+  if (fast)
+    raster_transform64_kernel<Raw><<<g, 256, 0, s>>>(r, out, aug, imgs_per_sample, C, H, W, tiles_x, tpp, norm_fac,
+                                                    use_norm, log_scale);
+  else
+    raster_transform_kernel<Raw><<<g, 256, 0, s>>>(r, out, aug, imgs_per_sample, C, H, W, tiles_x, tpp, norm_fac,
+                                                  use_norm, log_scale);
+}
+
 extern "C" int mb_raster_transform(const void* raw, int raw_dtype, float* out, const unsigned char* aug,
                                    int n_img, int imgs_per_sample, int C, int H, int W, float norm_fac,
                                    int use_norm, int log_scale, void* stream) {
   if (n_img <= 0 || C <= 0 || H <= 0 || W <= 0) return 0;
   if (imgs_per_sample <= 0 || raw_dtype < MB_RAW_U8 || raw_dtype > MB_RAW_F32) return static_cast<int>(cudaErrorInvalidValue);
-  const int tiles_x = (W + 31) / 32, tiles_y = (H + 31) / 32;
-  const long long blocks = static_cast<long long>(n_img) * C * tiles_x * tiles_y;
+  const long long blocks = static_cast<long long>(n_img) * C * ((W + 31) / 32) * ((H + 31) / 32);
   if (blocks > 0x7fffffffll) return static_cast<int>(cudaErrorInvalidValue);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  const int g = static_cast<int>(blocks), tpp = tiles_x * tiles_y;
   switch (raw_dtype) {
     case MB_RAW_U8:
-      raster_transform_kernel<unsigned char><<<g, 256, 0, s>>>(static_cast<const unsigned char*>(raw), out, aug,
-                                                              imgs_per_sample, C, H, W, tiles_x, tpp, norm_fac,
-                                                              use_norm, log_scale);
+      launch_raster<unsigned char>(raw, out, aug, n_img, imgs_per_sample, C, H, W, norm_fac, use_norm, log_scale, s);
       break;
     case MB_RAW_I16:
-      raster_transform_kernel<short><<<g, 256, 0, s>>>(static_cast<const short*>(raw), out, aug, imgs_per_sample, C,
-                                                      H, W, tiles_x, tpp, norm_fac, use_norm, log_scale);
+      launch_raster<short>(raw, out, aug, n_img, imgs_per_sample, C, H, W, norm_fac, use_norm, log_scale, s);
       break;
     case MB_RAW_U16:
-      raster_transform_kernel<unsigned short><<<g, 256, 0, s>>>(static_cast<const unsigned short*>(raw), out, aug,
-                                                               imgs_per_sample, C, H, W, tiles_x, tpp, norm_fac,
-                                                               use_norm, log_scale);
+      launch_raster<unsigned short>(raw, out, aug, n_img, imgs_per_sample, C, H, W, norm_fac, use_norm, log_scale, s);
       break;
     default:
-      raster_transform_kernel<float><<<g, 256, 0, s>>>(static_cast<const float*>(raw), out, aug, imgs_per_sample, C,
-                                                      H, W, tiles_x, tpp, norm_fac, use_norm, log_scale);
+      launch_raster<float>(raw, out, aug, n_img, imgs_per_sample, C, H, W, norm_fac, use_norm, log_scale, s);
   }
   MB_CHECK_LAUNCH();
   return 0;

@@ -104,6 +104,18 @@ def main():
                                            False), args.iters, flush)
         print(f"{tag:11s} {'loss':11s} rows={B * L:6d} N={L:5d}  {ms * 1e3:8.1f} us  {work / ms / 1e6:8.1f} GB/s",
               flush=True)
+    # device input pipeline: on-disk dtype -> fp32 tiles (mb_raster_transform); bytes = raw read + fp32 write
+    for tag, (Cc, S, dt) in {"raster_aerial_u8": (4, 512, torch.uint8), "raster_dem_f32": (2, 512, torch.float32)}.items():
+        if (args.tag and args.tag != tag) or (args.only and args.only not in "raster"):
+            continue
+        raw = (torch.rand(B, Cc, S, S, device=dev) * 255).to(dt)
+        out = torch.empty(B, Cc, S, S, device=dev)
+        for aname, aug in (("none", torch.zeros(B, dtype=torch.uint8, device=dev)),
+                           ("flips", torch.full((B,), 3, dtype=torch.uint8, device=dev)),
+                           ("mixed", (torch.arange(B, device=dev) % 8).to(torch.uint8))):
+            work = raw.numel() * raw.element_size() + out.numel() * 4
+            ms = timeit(lambda: K.raster_transform(raw, out, aug, 1, 255.0, False), args.iters, flush)
+            print(f"{tag:16s} aug={aname:6s} {ms * 1e3:8.1f} us  {work / ms / 1e6:8.1f} GB/s", flush=True)
     print("per-step totals (x9 encoder layers, x3 inter / decoder layers; LN: x2 per layer):")
     for k, v in tot.items():
         print(f"  {k:11s} {v * (2 if k.startswith('ln') else 1):7.3f} ms")
