@@ -589,14 +589,8 @@ class PretrainEngine:
         return out
 
     # ------------------------------------------------------------------ forward
-    def forward(self, batch: dict, struct: dict | None = None, noise: dict | None = None,
-                unmask_order: dict | None = None) -> dict:
-        """Run the MAE forward.  Returns the step context (saved activations + outputs).
-
-        ``struct`` / ``noise`` / ``unmask_order`` inject the mask draws (parity tests); by default the
-        structural mask comes from the host generator and the noise from ``torch.rand`` on the device,
-        exactly where the reference draws them.
-        """
+    def _embed(self, batch: dict) -> dict:
+        """resize_and_rescale + embed + enc_add_encodings (ssl/mim.py:476-479): fills ``x_embed`` per group."""
         K, P, dev, f32 = self.K, self.P, self.device, torch.float32
         E, Dd, hp = self.E, self.Dd, self.hp
         if not self.shadows_fresh:
@@ -647,6 +641,20 @@ class PretrainEngine:
                 mc["y"].append(y)
                 mc["stats"].append(stats)
                 c0 += c
+        return ctx
+
+    def forward(self, batch: dict, struct: dict | None = None, noise: dict | None = None,
+                unmask_order: dict | None = None) -> dict:
+        """Run the MAE forward.  Returns the step context (saved activations + outputs).
+
+        ``struct`` / ``noise`` / ``unmask_order`` inject the mask draws (parity tests); by default the
+        structural mask comes from the host generator and the noise from ``torch.rand`` on the device,
+        exactly where the reference draws them.
+        """
+        K, P, dev, f32 = self.K, self.P, self.device, torch.float32
+        E, Dd, hp = self.E, self.Dd, self.hp
+        ctx = self._embed(batch)
+        B = ctx["B"]
 
         # 3. masking: rank -> mask / slots / index lists, keep gather
         if struct is None:
@@ -748,6 +756,45 @@ class PretrainEngine:
                     mc["dec_r"].append(r_)
                     mc["pred"].append(pred)
         return ctx
+
+    # ------------------------------------------------------------------ unmasked encoder (probe / finetune features)
+    @torch.no_grad()
+    def encode(self, batch: dict) -> dict[str, torch.Tensor]:
+        """Encoder forward over EVERY token: ``BaseMIM.forward`` with ``ssl_phase`` "probe" / "finetune" up to the
+        tensors ``compute_logits`` receives (ssl/mim.py:473-490, 503; ``mask`` is bypassed :276-300) -- the same
+        kernels as the pretraining step at 4x the tokens.  Forward only: returns ``[B, L_group, E]`` per
+        group in the engine dtype; the heads (``layers/head.py``) stay with the caller."""
+        K, P, E, hp = self.K, self.P, self.E, self.hp
+        ctx = self._embed(batch)
+        B = ctx["B"]
+        H, dh = hp["heads"], hp["dim_head"]
+        glist = list(self.groups.values())
+        enc_pre = [f"encoder.{g.name}." for g in glist]
+        xs, saved = self.stacks_fwd(enc_pre, [ctx["groups"][g.name]["x_embed"].view(B * g.L, E) for g in glist], B,
+                                    [g.L for g in glist], E, hp["depth"] - self.inter_depth, H, dh, self.mlp_e)
+        del saved
+        nt, offs, f32 = sum(g.L for g in glist), {}, torch.float32
+        for g in glist:
+            offs[g.name] = sum(x.L for x in glist[:glist.index(g)])
+        out = {g.name: self._new(B * g.L, E) for g in glist}
+        xcat = self._new(B * nt, E) if self.inter_depth else None
+        for g, pre, x in zip(glist, enc_pre, xs):
+            rows = B * g.L
+            m_, r_ = self._new(rows, dtype=f32), self._new(rows, dtype=f32)
+            if self.inter_depth:
+                K.layernorm_fwd(x, P[pre + "norm.weight"], P[pre + "norm.bias"], xcat, m_, r_, rows, E,
+                                out_map=(g.L, nt, offs[g.name]))
+            else:
+                K.layernorm_fwd(x, P[pre + "norm.weight"], P[pre + "norm.bias"], out[g.name], m_, r_, rows, E)
+        if self.inter_depth:
+            x, saved = self.stack_fwd("encoder_inter.", xcat, B, nt, E, self.inter_depth, H, dh, self.mlp_e)
+            del saved
+            for g in glist:
+                rows = B * g.L
+                m_, r_ = self._new(rows, dtype=f32), self._new(rows, dtype=f32)
+                K.layernorm_fwd(x, P["encoder_inter.norm.weight"], P["encoder_inter.norm.bias"], out[g.name], m_, r_,
+                                rows, E, in_map=(g.L, nt, offs[g.name]))
+        return {n: t.view(B, -1, E) for n, t in out.items()}
 
     # ------------------------------------------------------------------ loss (+ d loss / d pred)
     def loss(self, ctx: dict, batch: dict, with_grad: bool = True, upstream: float = 1.0) -> torch.Tensor:

@@ -172,10 +172,20 @@ class MAE(nn.Module):
         dev = next(self.parameters()).device
         return self._engine(dev).mask_struct(batch_size)
 
+    @torch.no_grad()
+    def encode_features(self, batch: dict) -> dict[str, torch.Tensor]:
+        """Encoded tokens of EVERY position per group, ``[B, L_group, embed_dim]`` fp32: what the reference's
+        ``BaseMIM.forward`` hands to ``compute_logits`` for ``ssl_phase`` "probe" / "finetune" (ssl/mim.py:473-490, 503;
+        masking bypassed).  Forward only (frozen-encoder probing / feature extraction) on the same CUDA kernels as the
+        pretraining step; mutates ``batch`` like ``resize_and_rescale`` does."""
+        eng = self._engine(batch["ref_date"].device)
+        return {g: x.float() for g, x in eng.encode(batch).items()}
+
     def forward(self, batch: dict, ssl_phase: str = "pretrain", struct=None, noise=None, unmask_order=None):
         if ssl_phase != "pretrain":
-            raise NotImplementedError("probe / finetune forward (compute_logits + heads) is outside the B200 "
-                                      "pretraining path; see DESIGN.md 'out of scope'")
+            raise NotImplementedError("probe / finetune forward: compute_logits + heads are outside the B200 "
+                                      "pretraining path (DESIGN.md 'out of scope'); encode_features(batch) returns "
+                                      "the encoder output compute_logits consumes")
         dev = batch["ref_date"].device
         eng = self._engine(dev)
         params = dict(self.named_parameters())

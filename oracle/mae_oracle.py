@@ -265,8 +265,12 @@ def reconstruction_loss(batch: dict, pixels: dict, mask_px: dict, spec, kind: st
 def forward(sd: dict, spec, hp: dict, batch: dict, struct: dict, noise: dict, mask_cfg,
             fusion_mode: str = "group", inter_depth: int = 3, interpolate: str = "nearest",
             fac_abs_enc: float = 1.0, fac_date_enc: float = 1.0, date_dim: int = 8,
-            unmask_order: dict | None = None) -> dict:
+            unmask_order: dict | None = None, ssl_phase: str = "pretrain") -> dict:
     """One MAE pretrain forward.  Returns a dict of named stage tensors.
+
+    ``ssl_phase`` "probe" / "finetune": ``BaseMIM.mask`` is bypassed (ssl/mim.py:276-300 returns the tokens
+    unchanged), every token is encoded and the function returns after ``x_encoded`` (what ``compute_logits``
+    receives, ssl/mim.py:473-505); ``struct`` / ``noise`` are not read.
 
     struct[g]: bool [B,L_g] structural mask, noise[g]: fp32 [B,L_g] uniform noise
     (what mask_seq draws with torch.rand).  unmask_order[g] (optional) is the
@@ -309,6 +313,9 @@ def forward(sd: dict, spec, hp: dict, batch: dict, struct: dict, noise: dict, ma
     kept, mask_tok, mask, midx, uidx = {}, {}, {}, {}, {}
     bidx = torch.arange(B)[:, None]
     for g, x in x_grp.items():
+        if ssl_phase != "pretrain":
+            kept[g] = x
+            continue
         L = x.shape[1]
         if fusion_mode == "group":
             ratio = group_mask_ratio(spec, mask_cfg, g)
@@ -332,6 +339,8 @@ def forward(sd: dict, spec, hp: dict, batch: dict, struct: dict, noise: dict, ma
         for g, part in zip(names, cat.split([enc[g].shape[1] for g in names], 1)):
             enc[g] = part
     out["x_encoded"] = enc
+    if ssl_phase != "pretrain":
+        return out
 
     # enc -> dec, unmask, decoder encodings
     dec_in = {}
