@@ -114,6 +114,70 @@ def measured_peaks():
         return 6650.0, 1590.0, 1400.0, "fallback"
 
 
+def hbm_kernel_rooflines(K, eng, opt, dev, hbm_peak):
+    """Achieved HBM GB/s of the bandwidth-bound kernels on the step's largest shapes (FLAIR-HUB aerial decoder rows,
+    aerial tiles, the whole arena): every kernel runs 12 times back to back over 4 rotating buffer sets (> L2 together,
+    so no launch re-reads the previous one's lines from L2) between ONE pair of CUDA events; algorithmic bytes as in
+    DESIGN.md section 4.  Run after the timed region (it steps the optimiser on stale gradients)."""
+    bf, f32, Bt = torch.bfloat16, torch.float32, 32
+    out = []
+
+    def run(name, fns, nbytes, reps=12):
+        for f in fns:
+            f()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(reps):
+            fns[i % len(fns)]()
+        e1.record()
+        torch.cuda.synchronize()
+        us = e0.elapsed_time(e1) * 1e3 / reps
+        gbs = nbytes / us / 1e3
+        out.append({"kernel": name, "us": round(us, 2), "bytes": int(nbytes), "achieved": round(gbs, 1), "unit": "GB/s",
+                    "frac": round(gbs / hbm_peak, 3)})
+
+    rows, d = Bt * 1024, 512
+    sets = []
+    for _ in range(4):
+        x, dy, dres = (torch.randn(rows, d, device=dev).to(bf) for _ in range(3))
+        sets.append(dict(x=x, dy=dy, dres=dres, y=torch.empty_like(x), dx=torch.empty_like(x),
+                         mean=torch.zeros(rows, device=dev), rstd=torch.ones(rows, device=dev)))
+    gamma, beta = torch.ones(d, device=dev), torch.zeros(d, device=dev)
+    dg, db, dbias = (torch.zeros(d, device=dev) for _ in range(3))
+    run("layernorm_fwd_kernel [32768 x 512 bf16]",
+        [lambda s=s: K.layernorm_fwd(s["x"], gamma, beta, s["y"], s["mean"], s["rstd"], rows, d) for s in sets],
+        rows * d * 2 * 2)
+    run("layernorm_bwd_kernel [32768 x 512 bf16, + dgamma / dbeta / bias grad]",
+        [lambda s=s: K.layernorm_bwd(s["dy"], s["x"], s["mean"], s["rstd"], gamma, s["dres"], s["dx"], dg, db, rows, d,
+                                     dbias=dbias) for s in sets], rows * d * 2 * 4)
+    del sets
+    Cc, S, p = 4, 512, 16
+    L = (S // p) ** 2
+    lsets = []
+    for _ in range(3):
+        pred = torch.randn(Bt * L, Cc * p * p, device=dev).to(bf)
+        lsets.append(dict(target=torch.rand(Bt, 1, Cc, S, S, device=dev), pred=pred, dpred=torch.empty_like(pred),
+                          mask=(torch.rand(Bt, L, device=dev) < 0.75).to(torch.uint8)))
+    coef = torch.full((1,), 1e-3, device=dev)
+    accum = torch.zeros(2, device=dev, dtype=torch.float64)
+    frac = float(lsets[0]["mask"].float().mean())
+    run("group_norm_masked_loss_vec_kernel [aerial 32 x 4 x 512 x 512, fwd + grad]",
+        [lambda s=s: K.loss_fwd_bwd(s["target"], [s["pred"]], [s["dpred"]], s["mask"], coef, accum, Bt, 1, Cc, S, p, L, 0,
+                                    [Cc], [1, 3], False) for s in lsets],
+        frac * lsets[0]["target"].numel() * 4 + lsets[0]["pred"].numel() * 2 * 2)
+    aug = (torch.arange(Bt, device=dev) % 8).to(torch.uint8)
+    rsets = [((torch.rand(Bt, Cc, S, S, device=dev) * 255).to(torch.uint8), s["target"].view(Bt, Cc, S, S)) for s in lsets]
+    run("raster_transform64_kernel [aerial u8 -> fp32, mixed augmentation]",
+        [lambda r=r, o=o: K.raster_transform(r, o, aug, 1, 255.0, False) for r, o in rsets],
+        rsets[0][0].numel() * 5)
+    del lsets, rsets
+    n = eng.arena.numel
+    run("adamw_kernel [whole arena: p, g, m, v fp32 read + write, bf16 shadow write]", [lambda: opt.step()],
+        n * 34, reps=3)
+    return out
+
+
 # ------------------------------------------------------------------------------------------ CPU arms
 def cpu_reference_step_time(dataset, size, batch, steps, warmup, threads):
     """Oracle (CPU restatement of the reference, torch fp32 autograd) forward + backward, seconds per step."""
@@ -405,6 +469,9 @@ def run_ours(args):
     step_ms, e2e_ms = ms_dev / args.steps, ms_e2e / args.steps
     value = B * world / (step_ms * 1e-3)
     achieved = tc_fl / (tc_ms * 1e-3) / 1e12 if tc_ms > 0 else 0.0
+    hbm_kernels = None
+    if world == 1 and not args.no_hbm_kernels:
+        hbm_kernels = hbm_kernel_rooflines(K, eng, opt, dev, hbm)
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
         threads = os.cpu_count() or 1
@@ -442,6 +509,7 @@ def run_ours(args):
         "step_roofline": {"gflop_per_tile": STEP_GFLOP.get(args.dataset), "achieved_tflops": value *
                           STEP_GFLOP.get(args.dataset, 0) / 1e3 / world, "peak": tf_sus,
                           "frac": value * STEP_GFLOP.get(args.dataset, 0) / 1e3 / world / tf_sus},
+        "hbm_kernels": hbm_kernels,
         "attention_gemm": {"tflops": at_fl / (at_ms * 1e-3) / 1e12 if at_ms > 0 else None, "ms": at_ms},
         "cpu_baseline": cpu,
     }
@@ -458,6 +526,8 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-hbm-kernels", action="store_true",
+                    help="skip the live GB/s measurement of the bandwidth-bound kernels (N = 1 only, ~1 s)")
     ap.add_argument("--input", default="fp32", choices=["fp32", "raw"],
                     help="e2e host buffers: fp32 tiles (the reference's DataLoader output) or on-disk dtypes + "
                          "augmentation bits finished on the device (mb_raster_transform)")

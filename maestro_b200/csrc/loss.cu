@@ -137,14 +137,20 @@ __global__ void __launch_bounds__(128) group_norm_masked_loss_kernel(LossParams 
 // are one contiguous span, so the centred second pass reads float4 as well; per-channel mean / 1 / std go through a
 // small shared table and, when a 16-byte prediction chunk holds whole pixels, into registers once per patch.
 // Predictions / gradients move as 16-byte chunks with (pixel, channel) tracked incrementally.
-template <typename T>
-__global__ void __launch_bounds__(128, 6) group_norm_masked_loss_vec_kernel(LossParams P) {
+// PP / CC > 0: patch side and channel count fixed at compile time (one band group holding every channel), so that the
+// index divisions become shifts and the chunk loops unroll -- the generic form is issue-bound on them (~2000 warp
+// instructions per aerial patch).  PP = CC = 0: everything from LossParams.
+template <typename T, int PP, int CC>
+__global__ void __launch_bounds__(128, 5) group_norm_masked_loss_vec_kernel(LossParams P) {
+  const int Pp = PP > 0 ? PP : P.p;
+  const int PC = CC > 0 ? CC : P.C;
   constexpr int V = VecIO<T>::N;
   constexpr int DEPTH = 8;
+  constexpr int PD = 4;     // prediction chunks per lane requested ahead (4 x 16 B x 32 lanes = one aerial patch row set)
   extern __shared__ __align__(16) float smem[];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = blockDim.x >> 5;
-  const int g = P.S / P.p, L = g * g, pp = P.p * P.p, p4 = P.p / 4, pp4 = pp / 4;
-  const int npix = pp * P.C;
+  const int g = P.S / Pp, L = g * g, pp = Pp * Pp, p4 = Pp / 4, pp4 = pp / 4;
+  const int npix = pp * PC;
   float* tg = smem + static_cast<size_t>(w) * (npix + 2 * LOSS_MAX_C);   // [C][p][p]
   float* mu_s = tg + npix;                 // per channel: mean, 1 / sqrt(var + eps) of its norm group
   float* ri_s = mu_s + LOSS_MAX_C;
@@ -173,14 +179,27 @@ __global__ void __launch_bounds__(128, 6) group_norm_masked_loss_vec_kernel(Loss
       for (int e = lane * V; e < P.cg[gi] * pp; e += 32 * V) VecIO<T>::store(dp + e, zeros);
     }
     if (mbits == 0) continue;
+    // the first PD prediction chunks of band group 0 are requested now, next to the target rows, so that the patch has
+    // one memory round trip instead of one per 512-byte chunk row (G = 1 in every shipped configuration)
+    const bool use_pre = mbits & 1u;
+    typename VecIO<T>::Raw pre[PD];
+    if (use_pre) {
+      const int ne0 = (CC > 0 ? CC : P.cg[0]) * pp;
+      const T* pr0 = static_cast<const T*>(P.pred[0]) + static_cast<size_t>(patch) * ne0;
+#pragma unroll
+      for (int k = 0; k < PD; ++k) {
+        const int e = (lane + 32 * k) * V;
+        pre[k] = e < ne0 ? VecIO<T>::load_raw(pr0 + e) : VecIO<T>::zero_raw();
+      }
+    }
     // stage the target patch, channel-planar as in HBM; group sums on the way
     const int gy = l / g, gx = l % g;
-    const float* tbase = P.target + static_cast<size_t>(img) * P.C * plane + static_cast<size_t>(gy) * P.p * P.S +
-                         gx * P.p;
+    const float* tbase = P.target + static_cast<size_t>(img) * PC * plane + static_cast<size_t>(gy) * Pp * P.S +
+                         gx * Pp;
     int ch0 = 0;
     const int ngroups = P.n_norm > 0 ? P.n_norm : 1;
     for (int n = 0; n < ngroups; ++n) {
-      const int cn = P.n_norm > 0 ? P.norm_size[n] : P.C;
+      const int cn = P.n_norm > 0 ? P.norm_size[n] : PC;
       const int tot = cn * pp4;              // float4 elements of this norm group's channels
       float4* span = reinterpret_cast<float4*>(tg + ch0 * pp);
       float sacc = 0.f;
@@ -219,7 +238,7 @@ __global__ void __launch_bounds__(128, 6) group_norm_masked_loss_vec_kernel(Loss
           mu_s[lane] = mean;
           ri_s[lane] = 1.0f / sqrtf(var + 1.0e-6f);
         }
-      } else if (lane < P.C) {
+      } else if (lane < PC) {
         mu_s[lane] = 0.f;
         ri_s[lane] = 1.f;
       }
@@ -229,7 +248,7 @@ __global__ void __launch_bounds__(128, 6) group_norm_masked_loss_vec_kernel(Loss
     // stream prediction rows
     for (int gi = 0; gi < P.G; ++gi) {
       if (!((mbits >> gi) & 1u)) continue;
-      const int cgi = P.cg[gi], ne = cgi * pp, c0 = P.c0[gi];
+      const int cgi = CC > 0 ? CC : P.cg[gi], ne = cgi * pp, c0 = CC > 0 ? 0 : P.c0[gi];
       const T* pr = static_cast<const T*>(P.pred[gi]) + static_cast<size_t>(patch) * ne;
       T* dp = P.dpred[gi] != nullptr ? static_cast<T*>(P.dpred[gi]) + static_cast<size_t>(patch) * ne : nullptr;
       const bool whole = (V % cgi) == 0;      // a chunk holds whole pixels: channel of element k is c0 + k % cgi
@@ -241,9 +260,19 @@ __global__ void __launch_bounds__(128, 6) group_norm_masked_loss_vec_kernel(Loss
           rik[k] = ri_s[c0 + k % cgi];
         }
       }
-      for (int e0 = lane * V; e0 < ne; e0 += 32 * V) {
+      int it = 0;
+      for (int e0 = lane * V; e0 < ne; e0 += 32 * V, ++it) {
         float pv[V], gv[V];
-        VecIO<T>::load(pr + e0, pv);
+        typename VecIO<T>::Raw r;
+        if (gi == 0 && it < PD) {          // use_pre holds: band group 0 is masked here
+          r = pre[0];
+#pragma unroll
+          for (int k = 1; k < PD; ++k)
+            if (it == k) r = pre[k];
+        } else {
+          r = VecIO<T>::load_raw(pr + e0);
+        }
+        VecIO<T>::unpack(r, pv);
         int pix = e0 / cgi, cl = e0 - pix * cgi;
 #pragma unroll
         for (int k = 0; k < V; ++k) {
@@ -284,14 +313,18 @@ static void launch_loss(const LossParams& P, int blocks, int nw, cudaStream_t st
   }
   if (vec) {
     const size_t smem = static_cast<size_t>(nw) * (pp * P.C + 2 * LOSS_MAX_C) * sizeof(float);
+    const bool one = P.G == 1 && P.cg[0] == P.C && P.c0[0] == 0;
+    void (*kern)(LossParams) = group_norm_masked_loss_vec_kernel<T, 0, 0>;
+    if (one && P.p == 16 && P.C == 4) kern = group_norm_masked_loss_vec_kernel<T, 16, 4>;        // aerial / NAIP RGBN
+    else if (one && P.p == 32 && P.C == 2) kern = group_norm_masked_loss_vec_kernel<T, 32, 2>;   // DEM + DSM
+    else if (one && P.p == 16 && P.C == 3) kern = group_norm_masked_loss_vec_kernel<T, 16, 3>;   // SPOT
     if (smem > 48 * 1024)
-      cudaFuncSetAttribute(group_norm_masked_loss_vec_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                           static_cast<int>(smem));
+      cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
     // persistent grid: exactly the CTAs that are resident at once (registers / shared memory decide), so no tail wave
     int per_sm = 0;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, group_norm_masked_loss_vec_kernel<T>, nw * 32, smem);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, nw * 32, smem);
     if (per_sm > 0 && blocks > 148 * per_sm) blocks = 148 * per_sm;
-    group_norm_masked_loss_vec_kernel<T><<<blocks, nw * 32, smem, st>>>(P);
+    kern<<<blocks, nw * 32, smem, st>>>(P);
   } else {
     const size_t smem = static_cast<size_t>(nw) * pp * P.C * sizeof(float);
     if (smem > 48 * 1024)
