@@ -339,7 +339,8 @@ def run_ours(args):
                 prefetched[0] = True
             gstep.load_prefetched()
             nxt = host_e2e[(i + 1) % 2]
-            loss = step_device(devb, staged=True, before_tail=lambda: gstep.prefetch(nxt, after_current_work=True))
+            tail = None if args.e2e_ablate == "h2d" else (lambda: gstep.prefetch(nxt, after_current_work=True))
+            loss = step_device(devb, staged=True, before_tail=tail)
         else:
             for k, v in hb.items():
                 devb[k].copy_(v, non_blocking=True)
@@ -347,6 +348,8 @@ def run_ours(args):
         # loss read-back, every step, without draining the queue: step i's loss goes to pinned slot i % 2 behind an
         # event, and the host blocks on step i - 1's event only, so it stays one step ahead of the GPU (the struct-mask
         # draw and the launch of step i + 1 overlap step i).  The last step's copy completes before the closing event.
+        if args.e2e_ablate == "readback":
+            return None
         slot = i % 2
         loss_pin[slot].copy_(loss.reshape(1), non_blocking=True)
         loss_ev[slot].record()
@@ -385,6 +388,13 @@ def run_ours(args):
         tail = [m.elapsed_time(marks[-1]) for m in marks[:-1]]      # time from the start of graph i to the step's end
         ok = [i for i, t in enumerate(tail) if t >= 1.3 * h2d_ms]
         gate["seg"] = max(ok) if ok else 0
+        if world > 1:
+            # with a gradient all-reduce in flight the backward is the wrong place for PCIe ingress: measured on 8 GPUs
+            # e2e 32.0 ms gated into the tail (33.2 ms from graph 2) against 30.3 ms with the copy under the forward
+            # (= the run without any H2D copy); 2 GPUs 29.69 -> 29.14 ms.  One GPU keeps the tail (27.43 vs 27.60 ms).
+            gate["seg"] = 0
+        if args.h2d_gate >= 0:
+            gate["seg"] = min(args.h2d_gate, len(tail) - 1)
         print(f"[rank {rank}] H2D {h2d_ms:.2f} ms per step; gated ahead of graph {gate['seg']} of {len(tail)} "
               f"({tail[gate['seg']]:.2f} ms before the step ends)", file=sys.stderr)
     sampler = ClockSampler(local)
@@ -493,6 +503,8 @@ def run_ours(args):
                    "e2e_input": ("on-disk dtypes (aerial u8, s2 i16, dem / s1 f32) + augmentation bits, finished by "
                                  "mb_raster_transform on the device" if raw_rasters else
                                  "fp32 tiles as the reference DataLoader delivers them"),
+                   **({"e2e_ablate": args.e2e_ablate + " (diagnostic run: e2e is NOT a valid end-to-end number)"}
+                      if args.e2e_ablate != "none" else {}),
                    "struct_mask": "device Philox (mb_struct_mask)" if args.struct == "device" else
                                   "host generator, reference draw order"},
         "e2e": {"value": B * world / (e2e_ms * 1e-3), "unit": "tiles/s", "h2d_bytes_per_step": h2d,
@@ -526,6 +538,12 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--h2d-gate", type=int, default=-1,
+                    help="graph segment ahead of which the next step's H2D copy starts (-1: chosen from the measured "
+                         "transfer time and segment timings of the last warm-up step)")
+    ap.add_argument("--e2e-ablate", default="none", choices=["none", "h2d", "readback"],
+                    help="diagnostic only (the line is not a valid e2e number): drop the per-step H2D copy (stale staging "
+                         "buffers are re-used) or the loss read-back from the e2e loop to attribute its overhead")
     ap.add_argument("--no-hbm-kernels", action="store_true",
                     help="skip the live GB/s measurement of the bandwidth-bound kernels (N = 1 only, ~1 s)")
     ap.add_argument("--input", default="fp32", choices=["fp32", "raw"],
