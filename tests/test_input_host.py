@@ -75,3 +75,26 @@ def test_mask_struct_device_structure(dataset):
         alone = len(ms) == 1
         for (Gb, D, L, pm, pb, pd, pl) in ms:
             assert (pm > 0) == (not alone) and (pb > 0) == (Gb > 1) and (pd > 0) == (D > 1) and pl > 0
+
+
+def test_bench_raw_batch_is_the_fp32_batch_one_stage_earlier():
+    """bench.py --input raw: the on-disk-dtype tiles, finished by the (oracle) pipeline, land on the fp32 synthetic tiles
+    up to the quantisation of the integer dtypes and the augmentation (undone here through the dihedral inverse)."""
+    import bench
+    import input_oracle as O
+    from maestro_b200.conf import DATASET_SPECS
+    from maestro_b200.dataset import FLAIR_RASTERS
+    spec = DATASET_SPECS["treesatai_ts"]()
+    rasters = {n: FLAIR_RASTERS[n] for n in spec.inputs}
+    B = 3
+    fp32 = bench.synthetic_batch(spec, B, seed=5)
+    raw = bench.synthetic_raw_batch(spec, rasters, B, seed=5)
+    assert raw["aug"].dtype == torch.uint8 and raw["aug"].shape == (B,)
+    for n, r in rasters.items():
+        assert raw[n].dtype == r.dtype and raw[n].shape == fp32[n].shape
+        got = O.raster_pipeline(raw[n].numpy(), None, r.norm_fac, r.log_scale)       # no augmentation: same pixels
+        step = 0.5 / r.norm_fac if not r.dtype.is_floating_point else 1e-5
+        np.testing.assert_allclose(got, fp32[n].numpy(), atol=step * 1.01 + 1e-6, rtol=1e-5)
+    for k in fp32:
+        if k not in rasters:
+            assert torch.equal(raw[k], fp32[k])
