@@ -33,6 +33,9 @@ int mb_cast_transpose_f32_to_bf16(const float* src, void* dst, int R, int C, voi
 /* BaseMIM.resize_and_rescale, maestro/ssl/mim.py:425-437 (F.interpolate nearest + DEM 30*(ch0-ch)). */
 int mb_resize_nearest(const float* src, float* dst, int n_img, int C, int hin, int win, int hout, int wout,
                       int rescale_elev, void* stream);
+/* The same with F.interpolate's other modes (align_corners=False): mode 0 nearest, 1 bilinear, 2 bicubic (A = -0.75). */
+int mb_resize(const float* src, float* dst, int n_img, int C, int hin, int win, int hout, int wout, int mode,
+              int rescale_elev, void* stream);
 /* Patch extraction of the strided conv in PatchifyBands, maestro/layers/embed.py:57-60. */
 int mb_im2col(const float* img, void* cols, int dtype, int n_img, int C, int c0, int c, int S, int p, int Kpad,
               void* stream);

@@ -128,5 +128,5 @@ EXPORTS = [
     "mb_layernorm_fwd", "mb_layernorm_bwd", "mb_gn_stats", "mb_gn_apply", "mb_gn_bwd",
     "mb_mask_indices", "mb_gather_rows", "mb_scatter_kept", "mb_unmask_fwd", "mb_masktoken_grad",
     "mb_loss_fwd_bwd", "mb_gemm_simt", "mb_softmax_rows", "mb_softmax_bwd_rows", "mb_gemm_tc", "mb_gemm_tc_grouped",
-    "mb_adamw_step", "mb_attn_fwd", "mb_attn_bwd", "mb_raster_transform", "mb_struct_mask",
+    "mb_adamw_step", "mb_attn_fwd", "mb_attn_bwd", "mb_raster_transform", "mb_struct_mask", "mb_resize",
 ]

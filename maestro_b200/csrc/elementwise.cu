@@ -101,6 +101,94 @@ extern "C" int mb_resize_nearest(const float* src, float* dst, int n_img, int C,
   return 0;
 }
 
+// Bilinear / bicubic resize as torch F.interpolate(mode=..., align_corners=False) (upsample_bilinear2d /
+// upsample_bicubic2d, A = -0.75): src = scale * (dst + 0.5) - 0.5 with scale = in / out in fp32; bilinear clamps the
+// coordinate at 0 and the second tap at in - 1, bicubic clamps every tap index.  Same optional elevation rescale.
+#define MB_RESIZE_NEAREST 0
+#define MB_RESIZE_BILINEAR 1
+#define MB_RESIZE_BICUBIC 2
+
+__device__ __forceinline__ void cubic_coeffs(float t, float* w) {
+  const float A = -0.75f;
+  const float x0 = t + 1.f, x1 = t, x2 = 1.f - t, x3 = 2.f - t;
+  w[0] = ((A * x0 - 5.f * A) * x0 + 8.f * A) * x0 - 4.f * A;
+  w[1] = ((A + 2.f) * x1 - (A + 3.f)) * x1 * x1 + 1.f;
+  w[2] = ((A + 2.f) * x2 - (A + 3.f)) * x2 * x2 + 1.f;
+  w[3] = ((A * x3 - 5.f * A) * x3 + 8.f * A) * x3 - 4.f * A;
+}
+
+template <int MODE>
+__device__ __forceinline__ float sample_plane(const float* __restrict__ pl, int hin, int win, float fy, float fx) {
+  if (MODE == MB_RESIZE_BILINEAR) {
+    fy = fmaxf(fy, 0.f);
+    fx = fmaxf(fx, 0.f);
+    const int y0 = min(static_cast<int>(fy), hin - 1), x0 = min(static_cast<int>(fx), win - 1);
+    const int y1 = y0 + (y0 < hin - 1), x1 = x0 + (x0 < win - 1);
+    const float ly = fy - y0, lx = fx - x0, hy = 1.f - ly, hx = 1.f - lx;
+    return hy * (hx * pl[y0 * win + x0] + lx * pl[y0 * win + x1]) +
+           ly * (hx * pl[y1 * win + x0] + lx * pl[y1 * win + x1]);
+  }
+  const float yf = floorf(fy), xf = floorf(fx);
+  const int iy = static_cast<int>(yf), ix = static_cast<int>(xf);
+  float wy[4], wx[4];
+  cubic_coeffs(fy - yf, wy);
+  cubic_coeffs(fx - xf, wx);
+  float acc = 0.f;
+#pragma unroll
+  for (int a = 0; a < 4; ++a) {
+    const int yy = min(max(iy - 1 + a, 0), hin - 1);
+    float row = 0.f;
+#pragma unroll
+    for (int b = 0; b < 4; ++b) row += wx[b] * pl[yy * win + min(max(ix - 1 + b, 0), win - 1)];
+    acc += wy[a] * row;
+  }
+  return acc;
+}
+
+template <int MODE>
+__global__ void resize_interp_kernel(const float* __restrict__ src, float* __restrict__ dst, int n_img, int C, int hin,
+                                     int win, int hout, int wout, int rescale_elev) {
+  const size_t total = static_cast<size_t>(n_img) * C * hout * wout;
+  const float sh = static_cast<float>(hin) / static_cast<float>(hout);
+  const float sw = static_cast<float>(win) / static_cast<float>(wout);
+  for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const size_t t0 = i / wout;
+    const int x = static_cast<int>(i - t0 * wout);
+    const size_t t1 = t0 / hout;
+    const int y = static_cast<int>(t0 - t1 * hout);
+    const size_t img = t1 / C;
+    const int c = static_cast<int>(t1 - img * C);
+    const float fy = sh * (y + 0.5f) - 0.5f, fx = sw * (x + 0.5f) - 0.5f;
+    const float* base = src + img * C * hin * win;
+    float v = sample_plane<MODE>(base + static_cast<size_t>(c) * hin * win, hin, win, fy, fx);
+    if (rescale_elev && c >= 1) v = 30.f * (sample_plane<MODE>(base, hin, win, fy, fx) - v);
+    dst[i] = v;
+  }
+}
+
+extern "C" int mb_resize_nearest(const float* src, float* dst, int n_img, int C, int hin, int win, int hout,
+                                 int wout, int rescale_elev, void* stream);
+
+extern "C" int mb_resize(const float* src, float* dst, int n_img, int C, int hin, int win, int hout, int wout, int mode,
+                         int rescale_elev, void* stream) {
+  if (mode == MB_RESIZE_NEAREST) return mb_resize_nearest(src, dst, n_img, C, hin, win, hout, wout, rescale_elev, stream);
+  if (mode != MB_RESIZE_BILINEAR && mode != MB_RESIZE_BICUBIC) return -1;
+  const size_t total = static_cast<size_t>(n_img) * C * hout * wout;
+  if (total == 0) return 0;
+  long long blocks = (static_cast<long long>(total) + 255) / 256;
+  if (blocks > 148 * 32) blocks = 148 * 32;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (mode == MB_RESIZE_BILINEAR)
+    resize_interp_kernel<MB_RESIZE_BILINEAR><<<static_cast<int>(blocks), 256, 0, s>>>(src, dst, n_img, C, hin, win, hout,
+                                                                                      wout, rescale_elev);
+  else
+    resize_interp_kernel<MB_RESIZE_BICUBIC><<<static_cast<int>(blocks), 256, 0, s>>>(src, dst, n_img, C, hin, win, hout,
+                                                                                     wout, rescale_elev);
+  MB_CHECK_LAUNCH();
+  return 0;
+}
+
 // ------------------------------------------------------------------ patch extraction
 // img [n_img, C, S, S] fp32 -> cols [n_img * g * g, Kpad] (T), column k = (c - c0) * p * p + py * p + px
 // (the flattening of Conv2d weight [E, c, p, p]); columns [K, Kpad) are zero filled.

@@ -144,8 +144,10 @@ class PretrainEngine:
                  loss: str = "l1_norm") -> None:
         if fusion_mode not in ("group", "mod"):
             raise NotImplementedError(f"fusion_mode={fusion_mode!r}: only 'group' and 'mod' run on the CUDA path")
-        if interpolate != "nearest":
-            raise NotImplementedError(f"interpolate={interpolate!r}: only 'nearest' runs on the CUDA path")
+        if interpolate not in ("nearest", "bilinear", "bicubic"):
+            raise NotImplementedError(f"interpolate={interpolate!r}: F.interpolate modes nearest / bilinear / bicubic "
+                                      "run on the CUDA path")
+        self.interpolate = interpolate
         if loss not in ("l1_norm", "l2_norm", "l1", "l2"):
             raise ValueError(f"Invalid loss {loss}.")
         if hp["heads"] == 1 and hp["dim_head"] == hp["embed_dim"]:
@@ -607,7 +609,10 @@ class PretrainEngine:
             x = batch[mt.name].to(dev, f32).contiguous()
             if x.shape[-1] != mt.S or x.shape[-2] != mt.S or mt.rescale_elev:
                 y = self._new(B * mt.D, mt.C, mt.S, mt.S, dtype=f32)
-                K.resize_nearest(x.flatten(0, 1), y, mt.rescale_elev)
+                if self.interpolate == "nearest":
+                    K.resize_nearest(x.flatten(0, 1), y, mt.rescale_elev)
+                else:       # same-size rasters are the identity in every mode (scale 1: zero fractional weights)
+                    K.resize(x.flatten(0, 1), y, self.interpolate, mt.rescale_elev)
                 x = y.view(B, mt.D, mt.C, mt.S, mt.S)
             batch[mt.name] = x
             K.date_features(batch[f"{mt.name}_dates"].to(dev).contiguous(), ref, ctx["groups"][mt.group]["feat"],

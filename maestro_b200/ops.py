@@ -20,6 +20,7 @@ GEMM_GELU, GEMM_DGELU, GEMM_ACCUM, GEMM_OUT_F32 = 1, 2, 4, 8
 GEMM_PAIR_ON, GEMM_PAIR_OFF = 16, 32      # scheduling hints of the tensor-core path (tests, tuning)
 RAW_CODES = {torch.uint8: 0, torch.int16: 1, torch.uint16: 2, torch.float32: 3}   # MB_RAW_* of the header
 AUG_FLIP_H, AUG_FLIP_W, AUG_TRANSPOSE = 1, 2, 4
+RESIZE_MODES = {"nearest": 0, "bilinear": 1, "bicubic": 2}                         # F.interpolate modes of mim.py:425-437
 
 
 def _dt(t: torch.Tensor) -> int:
@@ -79,6 +80,13 @@ class Kernels:
         self.launches += 1
         _ck(self.L.mb_resize_nearest(_p(src), _p(dst), n, Cc, h, w, dst.shape[-2], dst.shape[-1], int(rescale_elev),
                                      _stream()), "resize")
+
+    def resize(self, src, dst, mode, rescale_elev):
+        """F.interpolate(src, dst.shape[-2:], mode) (+ elevation rescale); mode in nearest / bilinear / bicubic."""
+        n, Cc, h, w = src.shape
+        self.launches += 1
+        _ck(self.L.mb_resize(_p(src), _p(dst), n, Cc, h, w, dst.shape[-2], dst.shape[-1], RESIZE_MODES[mode],
+                             int(rescale_elev), _stream()), "resize")
 
     def im2col(self, img, cols, c0, c, p):
         n, Cc, S, _ = img.shape

@@ -55,6 +55,12 @@ class FakeKernels:
             x = torch.cat([x[:, :1], 30 * (x[:, :1] - x[:, 1:])], 1)
         dst.copy_(x)
 
+    def resize(self, src, dst, mode, rescale_elev):
+        x = F.interpolate(src, size=dst.shape[-2:], mode=mode)        # the reference's own call (ssl/mim.py:428-432)
+        if rescale_elev:
+            x = torch.cat([x[:, :1], 30 * (x[:, :1] - x[:, 1:])], 1)
+        dst.copy_(x)
+
     def im2col(self, img, cols, c0, c, p):
         n, _, S, _ = img.shape
         g = S // p
