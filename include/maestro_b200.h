@@ -69,10 +69,13 @@ int mb_gn_bwd(const void* dy, const void* y, const float* stats, const float* ga
               void* stream);
 
 /* ---- masking ------------------------------------------------------------------------------------------------ */
-/* MAE.mask_seq index math, maestro/ssl/mae.py:239-259 (rand*struct -> argsort -> argsort -> gather -> sort x2). */
+/* MAE.mask_seq index math, maestro/ssl/mae.py:239-259 (rand*struct -> argsort -> argsort -> gather -> sort x2).
+ * B sequences of L tokens.  Lt (0 = L): period of the per-sample tables (here seg_id) over the flat token index
+ * b * L + p -- a multiple of L when fusion modes "shared" / "monotemp" flatten the dates of a sample into the batch
+ * (maestro/layers/utils.py:26-33) and one sample therefore spans Lt / L sequences. */
 int mb_mask_indices(const float* noise, const unsigned char* structm, int B, int L, int nm, unsigned char* mask,
                     int* slot, long long* masked_idx, long long* unmasked_idx, const int* seg_id, int* seg_counts,
-                    void* stream);
+                    int Lt, void* stream);
 /* x[batch_indices, unmasked_indices], maestro/ssl/mae.py:261. */
 int mb_gather_rows(const void* x, const long long* idx, void* out, int dtype, int B, int L, int n, int d, void* stream);
 /* Its gradient (index_put of zeros + kept rows). */
@@ -81,9 +84,9 @@ int mb_scatter_kept(const void* dkept, const unsigned char* mask, const int* slo
 /* MAE.unmask_seq (maestro/ssl/mae.py:266-287) fused with dec_add_encodings (maestro/ssl/mim.py:254-274). */
 int mb_unmask_fwd(const void* y, const unsigned char* mask, const int* slot, const int* tok_id, const int* src_pos,
                   const float* tok, const float* pos, const float* feat, const int* date_id, void* out, int dtype,
-                  int B, int L, int n_kept, int d, int Dtot, int date_dim, float fac_date, void* stream);
+                  int B, int L, int n_kept, int d, int Dtot, int date_dim, float fac_date, int Lt, void* stream);
 int mb_masktoken_grad(const void* dx, const unsigned char* mask, const int* tok_id, const int* src_pos, float* dtok,
-                      int dtype, int B, int L, int d, int n_kinds, void* stream);
+                      int dtype, int B, int L, int d, int n_kinds, int Lt, void* stream);
 
 /* ---- loss --------------------------------------------------------------------------------------------------- */
 #define MB_LOSS_MAX_C 16

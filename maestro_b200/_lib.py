@@ -105,6 +105,49 @@ class StructParams(C.Structure):
 
 
 _LIB = None
+HEADER = HERE.parent / "include" / "maestro_b200.h"
+
+
+class _CheckedInt(C.c_int):
+    """``int`` argument that refuses values outside 32 bits (ctypes would truncate them silently)."""
+
+    @classmethod
+    def from_param(cls, v):  # noqa: ANN001, ANN206
+        v = int(v)
+        if not -2**31 <= v < 2**31:
+            raise OverflowError(f"argument {v} does not fit the C ABI's int (rows * d products must stay below 2^31)")
+        return C.c_int(v)
+
+
+def _ctype_of(decl: str):
+    """ctypes type of one parameter declaration of include/maestro_b200.h."""
+    d = decl.strip()
+    if "*" in d:
+        return C.c_void_p
+    words = d.split()[:-1]                       # drop the parameter name
+    if "size_t" in words:
+        return C.c_size_t
+    if words[:3] == ["unsigned", "long", "long"]:
+        return C.c_ulonglong
+    if words[:2] == ["long", "long"]:
+        return C.c_longlong
+    if "float" in words:
+        return C.c_float
+    if "double" in words:
+        return C.c_double
+    if "int" in words:
+        return _CheckedInt
+    raise ValueError(f"unhandled parameter declaration {decl!r}")
+
+
+def header_prototypes() -> dict[str, list]:
+    """``{symbol: [ctypes argument types]}`` parsed from the ``int mb_*(...);`` prototypes of the header."""
+    import re
+    text = re.sub(r"/\*.*?\*/", " ", HEADER.read_text(), flags=re.S)
+    protos = {}
+    for m in re.finditer(r"\bint\s+(mb_\w+)\s*\(([^)]*)\)\s*;", text):
+        protos[m.group(1)] = [_ctype_of(a) for a in m.group(2).split(",")]
+    return protos
 
 
 def lib() -> C.CDLL:
@@ -116,8 +159,12 @@ def lib() -> C.CDLL:
                 f"{SO_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
                 "(maestro_b200 has no CPU / eager fallback)")
         _LIB = C.CDLL(str(SO_PATH))
+        protos = header_prototypes() if HEADER.exists() else {}
         for name in EXPORTS:
-            getattr(_LIB, name).restype = C.c_int
+            fn = getattr(_LIB, name)
+            fn.restype = C.c_int
+            if name in protos:
+                fn.argtypes = protos[name]
     return _LIB
 
 

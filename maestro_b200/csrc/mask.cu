@@ -7,13 +7,16 @@
 
 // One CTA (1024 threads) per sample row.  rank(i) = #{j : (key_j, j) < (key_i, i)}; masked iff rank < nm.
 // Outputs: mask u8 [B, L]; slot i32 [B, L] (index inside the masked / kept list); masked_idx i64 [B, nm] and
-// unmasked_idx i64 [B, L - nm], both ascending; seg_counts[seg_id[p]] += 1 for every masked position.
+// unmasked_idx i64 [B, L - nm], both ascending; seg_counts[seg_id[p]] += 1 for every masked position.  The seg_id table
+// has period Lt over the flat token index b * L + i (Lt = L, or a multiple of L when every date of a sample is its own
+// sequence: fusion modes "shared" / "monotemp", layers/utils.py:26-33).
 __global__ void __launch_bounds__(1024) mask_rank_kernel(const float* __restrict__ noise,
                                                          const unsigned char* __restrict__ structm, int L, int nm,
                                                          unsigned char* __restrict__ mask, int* __restrict__ slot,
                                                          long long* __restrict__ masked_idx,
                                                          long long* __restrict__ unmasked_idx,
-                                                         const int* __restrict__ seg_id, int* __restrict__ seg_counts) {
+                                                         const int* __restrict__ seg_id, int* __restrict__ seg_counts,
+                                                         int Lt) {
   extern __shared__ float keys[];  // [L]
   __shared__ int warp_tot[2][32];
   __shared__ int run[2];
@@ -54,7 +57,7 @@ __global__ void __launch_bounds__(1024) mask_rank_kernel(const float* __restrict
       if (is_m) {
         slot[o] = pm;
         masked_idx[static_cast<size_t>(b) * nm + pm] = i;
-        if (seg_counts != nullptr) atomicAdd(&seg_counts[seg_id[i]], 1);
+        if (seg_counts != nullptr) atomicAdd(&seg_counts[seg_id[o % Lt]], 1);
       } else {
         slot[o] = pu;
         unmasked_idx[static_cast<size_t>(b) * (L - nm) + pu] = i;
@@ -73,14 +76,16 @@ __global__ void __launch_bounds__(1024) mask_rank_kernel(const float* __restrict
 
 extern "C" int mb_mask_indices(const float* noise, const unsigned char* structm, int B, int L, int nm,
                                unsigned char* mask, int* slot, long long* masked_idx, long long* unmasked_idx,
-                               const int* seg_id, int* seg_counts, void* stream) {
+                               const int* seg_id, int* seg_counts, int Lt, void* stream) {
   if (B == 0 || L == 0) return 0;
+  if (Lt <= 0) Lt = L;
+  if (Lt % L != 0) return -2;
   const size_t smem = static_cast<size_t>(L) * sizeof(float);
   if (smem > 200 * 1024) return -2;
   if (smem > 48 * 1024)
     cudaFuncSetAttribute(mask_rank_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
   mask_rank_kernel<<<B, 1024, smem, static_cast<cudaStream_t>(stream)>>>(noise, structm, L, nm, mask, slot,
-                                                                        masked_idx, unmasked_idx, seg_id, seg_counts);
+                                                                        masked_idx, unmasked_idx, seg_id, seg_counts, Lt);
   MB_CHECK_LAUNCH();
   return 0;
 }

@@ -5,7 +5,10 @@
 //   y       [B, n_kept, d] (T)   encoder->decoder projected tokens
 //   tok     [n_kinds, d] fp32    mask-token table, tok_id[p] selects the (modality, band-group) token
 //   src_pos [B, L] i32 or null   test hook: position whose tok_id feeds masked position p (reference tie quirk)
-//   pos     [L, d] fp32, feat [B, Dtot, 5] fp32, date_id[p] in [0, Dtot)
+//   pos     [Lt, d] fp32, feat [B / (Lt / L), Dtot, 5] fp32, date_id[t] in [0, Dtot)
+// Tables (tok_id, pos, date_id) have period Lt over the flat token index b * L + p and one feat block per Lt tokens:
+// Lt = L for fusion modes "group" / "mod"; for "shared" / "monotemp" every (band group, date) of a sample is its own
+// sequence of L = grid^2 tokens (layers/utils.py:26-33) and Lt = G * D * L tokens make up one sample.
 template <typename T>
 __global__ void __launch_bounds__(256) unmask_fwd_kernel(const T* __restrict__ y, const unsigned char* __restrict__ mask,
                                                          const int* __restrict__ slot, const int* __restrict__ tok_id,
@@ -13,16 +16,17 @@ __global__ void __launch_bounds__(256) unmask_fwd_kernel(const T* __restrict__ y
                                                          const float* __restrict__ pos, const float* __restrict__ feat,
                                                          const int* __restrict__ date_id, T* __restrict__ out, int B,
                                                          int L, int n_kept, int d, int Dtot, int date_dim,
-                                                         float fac_date) {
+                                                         float fac_date, int Lt) {
   constexpr int V = VecIO<T>::N;
   const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (row >= B * L) return;
   const int b = row / L, p = row % L;
+  const int bs = row / Lt, pt = row % Lt;             // sample / index into the per-sample tables
   const bool m = mask[row] != 0;
-  const float* f5 = feat + (static_cast<size_t>(b) * Dtot + date_id[p]) * 5;
+  const float* f5 = feat + (static_cast<size_t>(bs) * Dtot + date_id[pt]) * 5;
   const int sp = (m && src_pos != nullptr) ? src_pos[row] : p;
-  const float* tk = tok + static_cast<size_t>(tok_id[sp]) * d;
+  const float* tk = tok + static_cast<size_t>(tok_id[pt - p + sp]) * d;
   const T* src = y + (static_cast<size_t>(b) * n_kept + (m ? 0 : slot[row])) * d;
   for (int c = lane; c < d / V; c += 32) {
     float v[V];
@@ -35,7 +39,7 @@ __global__ void __launch_bounds__(256) unmask_fwd_kernel(const T* __restrict__ y
 #pragma unroll
     for (int j = 0; j < V; ++j) {
       const int e = c * V + j;
-      float add = pos[static_cast<size_t>(p) * d + e];
+      float add = pos[static_cast<size_t>(pt) * d + e];
       if (e >= d - date_dim) add += date_channel(f5, e - (d - date_dim), date_dim, fac_date);
       v[j] += add;
     }
@@ -46,14 +50,15 @@ __global__ void __launch_bounds__(256) unmask_fwd_kernel(const T* __restrict__ y
 extern "C" int mb_unmask_fwd(const void* y, const unsigned char* mask, const int* slot, const int* tok_id,
                              const int* src_pos, const float* tok, const float* pos, const float* feat,
                              const int* date_id, void* out, int dtype, int B, int L, int n_kept, int d, int Dtot,
-                             int date_dim, float fac_date, void* stream) {
+                             int date_dim, float fac_date, int Lt, void* stream) {
   if (B * L == 0) return 0;
-  if (d % 8 != 0) return -2;
+  if (Lt <= 0) Lt = L;
+  if (d % 8 != 0 || Lt % L != 0) return -2;
   const int blocks = mb_ceil_div(static_cast<long long>(B) * L * 32, 256);
   MB_DISPATCH_DTYPE(dtype, T,
                     (unmask_fwd_kernel<T><<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
                         static_cast<const T*>(y), mask, slot, tok_id, src_pos, tok, pos, feat, date_id,
-                        static_cast<T*>(out), B, L, n_kept, d, Dtot, date_dim, fac_date)));
+                        static_cast<T*>(out), B, L, n_kept, d, Dtot, date_dim, fac_date, Lt)));
   MB_CHECK_LAUNCH();
   return 0;
 }
@@ -68,7 +73,8 @@ __global__ void __launch_bounds__(512) masktoken_grad_kernel(const T* __restrict
                                                              const unsigned char* __restrict__ mask,
                                                              const int* __restrict__ tok_id,
                                                              const int* __restrict__ src_pos, float* __restrict__ dtok,
-                                                             int B, int L, int d, int n_kinds, int rows_per_block) {
+                                                             int B, int L, int d, int n_kinds, int rows_per_block,
+                                                             int Lt) {
   constexpr int V = VecIO<T>::N;
   constexpr int U = 4;
   typedef typename VecIO<T>::Raw Raw;
@@ -98,8 +104,9 @@ __global__ void __launch_bounds__(512) masktoken_grad_kernel(const T* __restrict
       if (kind[u] >= 0) {
         const int ru = kind[u];
         raw[u] = VecIO<T>::load_raw(dx + static_cast<size_t>(ru) * d + cv * V);
-        const int sp = src_pos != nullptr ? src_pos[ru] : ru % L;
-        kind[u] = tok_id[sp];
+        const int p = ru % L;
+        const int sp = src_pos != nullptr ? src_pos[ru] : p;
+        kind[u] = tok_id[ru % Lt - p + sp];
       } else {
         raw[u] = VecIO<T>::zero_raw();
       }
@@ -132,8 +139,10 @@ __global__ void __launch_bounds__(512) masktoken_grad_kernel(const T* __restrict
 }
 
 extern "C" int mb_masktoken_grad(const void* dx, const unsigned char* mask, const int* tok_id, const int* src_pos,
-                                 float* dtok, int dtype, int B, int L, int d, int n_kinds, void* stream) {
+                                 float* dtok, int dtype, int B, int L, int d, int n_kinds, int Lt, void* stream) {
   if (B * L == 0) return 0;
+  if (Lt <= 0) Lt = L;
+  if (Lt % L != 0) return -2;
   if (n_kinds > MAX_TOK_KINDS || d % 8 != 0 || d / (dtype == MB_DTYPE_F32 ? 4 : 8) > 256) return -2;   // one column chunk per thread
   int blocks = 148;                         // one same-address atomic per column per block at the end
   int rows_per_block = mb_ceil_div(static_cast<long long>(B) * L, blocks);
@@ -144,7 +153,7 @@ extern "C" int mb_masktoken_grad(const void* dx, const unsigned char* mask, cons
   MB_DISPATCH_DTYPE(dtype, T,                                                                                 \
                     (masktoken_grad_kernel<T, NK_><<<blocks, 512, NK_ * d * sizeof(float), st>>>(static_cast<const T*>(dx), mask, tok_id, \
                                                                            src_pos, dtok, B, L, d, n_kinds,    \
-                                                                           rows_per_block)))
+                                                                           rows_per_block, Lt)))
   if (n_kinds <= 1) { MTG(1); }
   else if (n_kinds <= 2) { MTG(2); }
   else if (n_kinds <= 4) { MTG(4); }

@@ -111,6 +111,9 @@ class GroupTable:
     Dtot: int = 0
     ratio: float = 0.75
     kept_off: int = 0       # offset of this group's kept tokens in the inter-encoder concat
+    bmul: int = 1           # sequences per sample: G * D for "shared" / "monotemp" (dates flattened into the batch)
+    Lt: int = 0             # tokens per sample = bmul * L (length of the per-sample tables)
+    wname: str = ""         # name of the encoder / decoder stack that serves this group ("shared" or the group name)
     consts: dict = field(default_factory=dict)
 
 
@@ -142,8 +145,11 @@ class PretrainEngine:
                  fusion_mode: str = "group", inter_depth: int = 3, interpolate: str = "nearest",
                  fac_abs_enc: float = 1.0, fac_date_enc: float = 1.0, date_dim: int = 8,
                  loss: str = "l1_norm") -> None:
-        if fusion_mode not in ("group", "mod"):
-            raise NotImplementedError(f"fusion_mode={fusion_mode!r}: only 'group' and 'mod' run on the CUDA path")
+        if fusion_mode not in ("group", "mod", "shared", "monotemp"):
+            raise ValueError(f"Invalid fusion mode {fusion_mode}.")
+        if inter_depth and fusion_mode not in ("mod", "group"):      # as SSLModule.__init__, train/model.py:85-90
+            raise NotImplementedError("Simultaneous encoding of all mods"
+                                      f" not yet compatible with fusion mode: {fusion_mode}.")
         if interpolate not in ("nearest", "bilinear", "bicubic"):
             raise NotImplementedError(f"interpolate={interpolate!r}: F.interpolate modes nearest / bilinear / bicubic "
                                       "run on the CUDA path")
@@ -173,6 +179,7 @@ class PretrainEngine:
         self.mods: dict[str, ModTable] = {}
         self.groups: dict[str, GroupTable] = {}
         seg = 0
+        flat_dates = self.fusion_mode in ("shared", "monotemp")     # layers/utils.py:26-33: (B, D) -> batch
         for name, m in spec.inputs.items():
             gname = m.group if self.fusion_mode == "group" else name
             mt = ModTable(name=name, group=gname, embed=m.embed, G=len(m.band_groups), D=m.num_dates,
@@ -180,10 +187,13 @@ class PretrainEngine:
                           C=m.channels, band_groups=list(m.band_groups), loss_bands=list(m.loss_bands),
                           rescale_elev=m.rescale_elev)
             g = self.groups.setdefault(gname, GroupTable(name=gname, mods=[]))
-            mt.tok_off, mt.date_off, mt.seg0 = g.L, g.Dtot, seg
+            g.wname = "shared" if self.fusion_mode == "shared" else gname
+            mt.tok_off, mt.date_off, mt.seg0 = g.Lt, g.Dtot, seg
             mt.tok0 = sum(self.mods[x].G for x in g.mods)
             g.mods.append(name)
-            g.L += mt.G * mt.D * mt.L
+            g.Lt += mt.G * mt.D * mt.L
+            g.bmul = mt.G * mt.D if flat_dates else 1
+            g.L = g.Lt // g.bmul
             g.Dtot += mt.D
             seg += mt.G
             self.mods[name] = mt
@@ -193,11 +203,14 @@ class PretrainEngine:
         kept_off = 0
         for g in self.groups.values():
             n_dates = sum(self.mods[x].D * self.mods[x].G for x in g.mods)
-            g.ratio = 1 - (1 - self.mask_cfg.mask_ratio) / (n_dates ** self.mask_cfg.mask_scale)
+            if flat_dates:
+                g.ratio = self.mask_cfg.mask_ratio                    # ssl/mae.py:85-96: no date scaling
+            else:
+                g.ratio = 1 - (1 - self.mask_cfg.mask_ratio) / (n_dates ** self.mask_cfg.mask_scale)
             g.nm = round(g.ratio * g.L)          # python banker's rounding, as the reference (mae.py:244-246)
             g.n_kept = g.L - g.nm
             g.kept_off = kept_off
-            kept_off += g.n_kept
+            kept_off += g.n_kept * g.bmul
             enc_pos, dec_pos, date_id, tok_id, seg_id = [], [], [], [], []
             for x in g.mods:
                 mt = self.mods[x]
@@ -227,6 +240,15 @@ class PretrainEngine:
         self.loss_w = (w / w.sum()).to(dev)
 
     # ------------------------------------------------------------------ parameters
+    @property
+    def stack_names(self) -> list[str]:
+        """Names of the per-group encoder / decoder stacks (ssl/mae.py:84-131): groups, modalities or ["shared"]."""
+        out: list[str] = []
+        for g in self.groups.values():
+            if g.wname not in out:
+                out.append(g.wname)
+        return out
+
     def param_shapes(self) -> dict[str, tuple]:
         hp, E, Dd = self.hp, self.E, self.Dd
         s: dict[str, tuple] = {}
@@ -246,7 +268,7 @@ class PretrainEngine:
                 s[pre + "bias"] = (c * mt.p * mt.p,)
         for mt in self.mods.values():
             s[f"mask_token.{mt.name}"] = (1, mt.G, 1, 1, Dd)
-        for g in self.groups:
+        for g in self.stack_names:
             s.update(transformer_param_shapes(f"encoder.{g}.", E, hp["depth"] - self.inter_depth, hp["heads"],
                                               hp["dim_head"], self.mlp_e))
             if E != Dd:
@@ -280,6 +302,7 @@ class PretrainEngine:
         self.arena = ParamArena(shapes, order, self.device, self.dtype == torch.bfloat16)
         self.P, self.G = self.arena.P, self.arena.G
         self.shadows_fresh = False
+        self.grads_dirty = False      # True once a backward accumulated into the arena; zero_grad / FusedAdamW clear it
 
     def load_state_dict(self, sd: dict[str, torch.Tensor]) -> None:
         self.arena.load(sd)
@@ -287,6 +310,7 @@ class PretrainEngine:
 
     def zero_grad(self) -> None:
         self.arena.grad.zero_()
+        self.grads_dirty = False
 
     def grads(self) -> dict[str, torch.Tensor]:
         return self.G
@@ -424,11 +448,17 @@ class PretrainEngine:
     # The per-group encoders (and decoders) have identical layer shapes and different weights / token counts
     # (reference: one vit_pytorch Transformer per group, looped by encode_or_decode, ssl/mim.py:396-423).  They
     # advance layer by layer together so that every linear layer of the 4 groups is ONE grouped GEMM launch.
-    def blocks_fwd(self, pres, xs, Bn, Ns, dim, H, dh, mlp):
+    @staticmethod
+    def _bns(Bn, n):
+        """Sequences per stack: one int for all stacks or a list (fusion "shared" / "monotemp": B * G * D per modality)."""
+        return list(Bn) if isinstance(Bn, (list, tuple)) else [Bn] * n
+
+    def blocks_fwd(self, pres, xs, Bn, Ns, dim, H, dh, mlp, save=True):
         K, P = self.K, self.P
         f32 = torch.float32
         inner, n = H * dh, len(pres)
-        rows = [Bn * N for N in Ns]
+        Bn = self._bns(Bn, n)
+        rows = [b * N for b, N in zip(Bn, Ns)]
         h1 = [self._new(r, dim) for r in rows]
         m1 = [self._new(r, dtype=f32) for r in rows]
         r1 = [self._new(r, dtype=f32) for r in rows]
@@ -438,12 +468,12 @@ class PretrainEngine:
         self.lin_fwd_g([(h1[i], rows[i], pres[i] + "0.to_qkv.weight", None, qkv[i], None, None) for i in range(n)])
         if self.attn_impl == "flash":
             o = [self._new(r, inner) for r in rows]
-            att = [self._new(Bn, H, N, dtype=f32) for N in Ns]          # log-sum-exp per (sample, head, query)
-            self._par([lambda i=i: K.attn_fwd(qkv[i], o[i], att[i], Bn, Ns[i], H, dh) for i in range(n)])
+            att = [self._new(b, H, N, dtype=f32) for b, N in zip(Bn, Ns)]   # log-sum-exp per (sample, head, query)
+            self._par([lambda i=i: K.attn_fwd(qkv[i], o[i], att[i], Bn[i], Ns[i], H, dh) for i in range(n)])
         else:
             o, att = [], []
             for i in range(n):
-                oi, ai = self.attn_fwd(qkv[i], Bn, Ns[i], H, dh)
+                oi, ai = self.attn_fwd(qkv[i], Bn[i], Ns[i], H, dh)
                 o.append(oi)
                 att.append(ai)
         x2 = [self._new(r, dim) for r in rows]
@@ -462,14 +492,15 @@ class PretrainEngine:
         self.lin_fwd_g([(a[i], rows[i], pres[i] + "1.net.4.weight", pres[i] + "1.net.4.bias", x3[i], None, x2[i])
                         for i in range(n)])
         saved = [(xs[i], m1[i], r1[i], h1[i], qkv[i], att[i], o[i], x2[i], m2[i], r2[i], h2[i], u[i], a[i])
-                 for i in range(n)]
+                 for i in range(n)] if save else None
         return x3, saved
 
     def blocks_bwd(self, pres, dx3, saved, Bn, Ns, dim, H, dh, mlp, sinks=None):
         """``sinks[i]``: bias gradient (of the block below) that receives the column sums of this block's dx."""
         K, P, G = self.K, self.P, self.G
         inner, n = H * dh, len(pres)
-        rows = [Bn * N for N in Ns]
+        Bn = self._bns(Bn, n)
+        rows = [b * N for b, N in zip(Bn, Ns)]
         x, m1, r1, h1, qkv, att, o, x2, m2, r2, h2, u, a = (list(t) for t in zip(*saved))
         du = [self._new(r, mlp) for r in rows]
         # the bias gradients of net.4 / to_out are column sums of dx3 / dx2: they ride on the LayerNorm backward that
@@ -488,11 +519,11 @@ class PretrainEngine:
         self.lin_bwd_g([(dx2[i], rows[i], o[i], pres[i] + "0.to_out.0.weight", None, do[i], None) for i in range(n)])
         if self.attn_impl == "flash":
             dqkv = [self._new(r, 3 * inner) for r in rows]
-            delta = [self._new(Bn, H, N, dtype=torch.float32) for N in Ns]
-            self._par([lambda i=i: K.attn_bwd(qkv[i], o[i], do[i], att[i], dqkv[i], delta[i], Bn, Ns[i], H, dh)
+            delta = [self._new(b, H, N, dtype=torch.float32) for b, N in zip(Bn, Ns)]
+            self._par([lambda i=i: K.attn_bwd(qkv[i], o[i], do[i], att[i], dqkv[i], delta[i], Bn[i], Ns[i], H, dh)
                        for i in range(n)])
         else:
-            dqkv = [self.attn_bwd(do[i], qkv[i], att[i], Bn, Ns[i], H, dh, o=o[i]) for i in range(n)]
+            dqkv = [self.attn_bwd(do[i], qkv[i], att[i], Bn[i], Ns[i], H, dh, o=o[i]) for i in range(n)]
         dh1 = dh2  # reuse
         self.lin_bwd_g([(dqkv[i], rows[i], h1[i], pres[i] + "0.to_qkv.weight", None, dh1[i], None) for i in range(n)])
         dx = [self._new(r, dim) for r in rows]
@@ -501,11 +532,12 @@ class PretrainEngine:
                                                dbias=sinks[i] if sinks is not None else None) for i in range(n)])
         return dx
 
-    def stacks_fwd(self, prefixes, xs, Bn, Ns, dim, depth, H, dh, mlp):
-        """Run len(prefixes) transformer stacks of equal shape in lockstep; returns (outputs, saved[layer][stack])."""
+    def stacks_fwd(self, prefixes, xs, Bn, Ns, dim, depth, H, dh, mlp, save=True):
+        """Run len(prefixes) transformer stacks of equal shape in lockstep; returns (outputs, saved[layer][stack]).
+        Several stacks may name the SAME weights (fusion mode "shared"): their gradients accumulate atomically."""
         saved = []
         for i in range(depth):
-            xs, s = self.blocks_fwd([f"{p}layers.{i}." for p in prefixes], xs, Bn, Ns, dim, H, dh, mlp)
+            xs, s = self.blocks_fwd([f"{p}layers.{i}." for p in prefixes], xs, Bn, Ns, dim, H, dh, mlp, save)
             saved.append(s)
         return xs, saved
 
@@ -523,8 +555,8 @@ class PretrainEngine:
             saved[i] = None
         return dxs
 
-    def stack_fwd(self, prefix, x, Bn, N, dim, depth, H, dh, mlp):
-        xs, saved = self.stacks_fwd([prefix], [x], Bn, [N], dim, depth, H, dh, mlp)
+    def stack_fwd(self, prefix, x, Bn, N, dim, depth, H, dh, mlp, save=True):
+        xs, saved = self.stacks_fwd([prefix], [x], Bn, [N], dim, depth, H, dh, mlp, save)
         return xs[0], saved
 
     def stack_bwd(self, prefix, dx, saved, Bn, N, dim, H, dh, mlp):
@@ -532,12 +564,16 @@ class PretrainEngine:
 
     # ------------------------------------------------------------------ structural mask (host RNG)
     def mask_struct(self, batch_size: int) -> dict[str, torch.Tensor]:
-        """Structural mask per group, bool [B, L_group] on the host (reference MAE.mask_struct, mae.py:178-226).
+        """Structural mask per group, bool [B * bmul, L] on the host (reference MAE.mask_struct, mae.py:178-226).
 
         Draw order of the CPU generator: per modality (input order) mod, bands, dates, loc -- every loop pass
         draws for all samples; samples whose group is entirely masked take the new draw; repeat until none is.
+        Fusion modes "shared" / "monotemp" set every probability to None (mae.py:85-96): the loop runs once, draws
+        nothing and leaves an all-false mask per (sample, date) sequence.
         """
         mc, B = self.mask_cfg, batch_size
+        if self.fusion_mode in ("shared", "monotemp"):
+            return {g.name: torch.zeros(B * g.bmul, g.L, dtype=torch.bool) for g in self.groups.values()}
         cur = {g.name: torch.ones(B, g.L, dtype=torch.bool) for g in self.groups.values()}
         while any(bool(c.all(dim=1).any()) for c in cur.values()):
             draw = {}
@@ -585,7 +621,10 @@ class PretrainEngine:
         out = {} if out is None else out
         for gi, g in enumerate(self.groups.values()):
             if g.name not in out:
-                out[g.name] = torch.empty(batch_size, g.L, dtype=torch.uint8, device=self.device)
+                out[g.name] = torch.empty(batch_size * g.bmul, g.L, dtype=torch.uint8, device=self.device)
+            if g.bmul > 1:                                # "shared" / "monotemp": no structural masking at all
+                out[g.name].zero_()
+                continue
             key = (int(seed) ^ ((gi + 1) * 0x9E3779B97F4A7C15)) & (2**64 - 1)
             self.K.struct_mask(self.struct_mods(g.name), key, int(step) << 20, out[g.name], None, 1 << 20)
         return out
@@ -619,9 +658,10 @@ class PretrainEngine:
                             mt.date_off)
             ctx["mods"][mt.name] = {"img": x}
 
-        # 2. patch embedding + GroupNorm + encodings, written straight into the group token buffer
+        # 2. patch embedding + GroupNorm + encodings, written straight into the group token buffer ([B, G, D, L, E] per
+        #    modality: the same bytes are [B, G * D * L, E] for "group" / "mod" and [(B G D), L, E] for "shared" / "monotemp")
         for g in self.groups.values():
-            ctx["groups"][g.name]["x_embed"] = self._new(B, g.L, E)
+            ctx["groups"][g.name]["x_embed"] = self._new(B, g.Lt, E)
         for mt in self.mods.values():
             gc, g = ctx["groups"][mt.group], self.groups[mt.group]
             mc = ctx["mods"][mt.name]
@@ -641,12 +681,56 @@ class PretrainEngine:
                 off = mt.tok_off + gi * mt.D * mt.L
                 K.gn_apply(y, sums, P[pre + "norm.weight"], P[pre + "norm.bias"],
                            g.consts["enc_pos"][off:off + mt.L], gc["feat"], gc["x_embed"], stats, n_img, mt.D, mt.L,
-                           E, 1e-5, g.L, off, self.date_dim, self.fac_date, mt.date_off)
+                           E, 1e-5, g.Lt, off, self.date_dim, self.fac_date, mt.date_off)
                 mc["cols"].append(cols)
                 mc["y"].append(y)
                 mc["stats"].append(stats)
                 c0 += c
         return ctx
+
+    def _encode_groups(self, ctx: dict, toks: list, ns: list, save: bool = True) -> None:
+        """MAE.encode (ssl/mae.py:289-296): the per-group stacks, their final LayerNorm and -- when ``inter_depth`` -- the
+        joint ``encoder_inter`` over the concatenation of every group's tokens (encode_or_decode_all, mim.py:406-423; the
+        cat / split are row maps of the LayerNorms).  ``toks[i]`` [B_g * ns[i], E] are the tokens of group i (the kept
+        ones in pretraining, all of them for probe / finetune); fills ``ctx['groups'][g]['enc_out']``."""
+        K, P, E, hp, f32 = self.K, self.P, self.E, self.hp, torch.float32
+        B = ctx["B"]
+        H, dh = hp["heads"], hp["dim_head"]
+        depth_g = hp["depth"] - self.inter_depth
+        glist = list(self.groups.values())
+        Bg = [B * g.bmul for g in glist]
+        offs, nt = [], 0
+        for n in ns:
+            offs.append(nt)
+            nt += n
+        ctx["enc_n"], ctx["enc_off"], ctx["enc_nt"] = list(ns), offs, nt
+        if self.inter_depth:
+            xcat = self._new(B * nt, E)
+        enc_pre = [f"encoder.{g.wname}." for g in glist]
+        xs, ctx["enc_saved"] = self.stacks_fwd(enc_pre, toks, Bg, ns, E, depth_g, H, dh, self.mlp_e, save)
+        for g, pre, x, n, off, bg in zip(glist, enc_pre, xs, ns, offs, Bg):
+            gc = ctx["groups"][g.name]
+            rows = bg * n
+            gc["enc_pre_norm"] = x
+            gc["enc_m"], gc["enc_r"] = self._new(rows, dtype=f32), self._new(rows, dtype=f32)
+            if self.inter_depth:
+                K.layernorm_fwd(x, P[pre + "norm.weight"], P[pre + "norm.bias"], xcat, gc["enc_m"], gc["enc_r"], rows,
+                                E, out_map=(n, nt, off))
+            else:
+                gc["enc_out"] = self._new(rows, E)
+                K.layernorm_fwd(x, P[pre + "norm.weight"], P[pre + "norm.bias"], gc["enc_out"], gc["enc_m"],
+                                gc["enc_r"], rows, E)
+        if self.inter_depth:
+            x, ctx["inter_saved"] = self.stack_fwd("encoder_inter.", xcat, B, nt, E, self.inter_depth, H, dh,
+                                                   self.mlp_e, save)
+            ctx["inter_pre_norm"] = x
+            for g, n, off in zip(glist, ns, offs):
+                gc = ctx["groups"][g.name]
+                rows = B * n
+                gc["int_m"], gc["int_r"] = self._new(rows, dtype=f32), self._new(rows, dtype=f32)
+                gc["enc_out"] = self._new(rows, E)
+                K.layernorm_fwd(x, P["encoder_inter.norm.weight"], P["encoder_inter.norm.bias"], gc["enc_out"],
+                                gc["int_m"], gc["int_r"], rows, E, in_map=(n, nt, off))
 
     def forward(self, batch: dict, struct: dict | None = None, noise: dict | None = None,
                 unmask_order: dict | None = None) -> dict:
@@ -661,85 +745,58 @@ class PretrainEngine:
         ctx = self._embed(batch)
         B = ctx["B"]
 
-        # 3. masking: rank -> mask / slots / index lists, keep gather
+        # 3. masking: rank -> mask / slot / index lists, keep gather (sequences: [B * bmul, L] per group)
         if struct is None:
             struct = self.mask_struct(B)
         ctx["seg_counts"] = self._zeros(self.n_seg, dtype=torch.int32)
         for g in self.groups.values():
             gc = ctx["groups"][g.name]
-            nz = noise[g.name].to(dev, f32).contiguous() if noise is not None else torch.rand(B, g.L, device=dev)
-            st = struct[g.name].reshape(B, g.L).to(dev, torch.uint8).contiguous()
-            gc["mask"] = self._new(B, g.L, dtype=torch.uint8)
-            gc["slot"] = self._new(B, g.L, dtype=torch.int32)
-            gc["midx"] = self._new(B, g.nm, dtype=torch.int64)
-            gc["uidx"] = self._new(B, g.n_kept, dtype=torch.int64)
+            Bg = B * g.bmul
+            nz = noise[g.name].to(dev, f32).contiguous() if noise is not None else torch.rand(Bg, g.L, device=dev)
+            st = struct[g.name].reshape(Bg, g.L).to(dev, torch.uint8).contiguous()
+            gc["mask"] = self._new(Bg, g.L, dtype=torch.uint8)
+            gc["slot"] = self._new(Bg, g.L, dtype=torch.int32)
+            gc["midx"] = self._new(Bg, g.nm, dtype=torch.int64)
+            gc["uidx"] = self._new(Bg, g.n_kept, dtype=torch.int64)
             K.mask_indices(nz, st, g.nm, gc["mask"], gc["slot"], gc["midx"], gc["uidx"], g.consts["seg_id"],
-                           ctx["seg_counts"])
-            gc["x_kept"] = self._new(B, g.n_kept, E)
-            K.gather_rows(gc["x_embed"], gc["uidx"], gc["x_kept"])
+                           ctx["seg_counts"], g.Lt)
+            gc["x_kept"] = self._new(Bg, g.n_kept, E)
+            K.gather_rows(gc["x_embed"].view(Bg, g.L, E), gc["uidx"], gc["x_kept"])
             gc["x_embed"] = None
             gc["src_pos"] = None
             if unmask_order is not None:
                 # test hook (reference tie quirk, mae.py:272-285): masked position order[b, j] shows the mask
                 # token that belongs to position midx[b, j]
-                sp = torch.arange(g.L, device=dev, dtype=torch.int32)[None].repeat(B, 1)
+                sp = torch.arange(g.L, device=dev, dtype=torch.int32)[None].repeat(Bg, 1)
                 sp.scatter_(1, unmask_order[g.name].to(dev), gc["midx"].to(torch.int32))
                 gc["src_pos"] = sp
 
         # 4. per-group encoders, then the joint encoder on the concatenated kept tokens
-        H, dh = hp["heads"], hp["dim_head"]
-        depth_g = hp["depth"] - self.inter_depth
-        nt = self.n_kept_total
-        if self.inter_depth:
-            xcat = self._new(B * nt, E)
         glist = list(self.groups.values())
-        enc_pre = [f"encoder.{g.name}." for g in glist]
-        xs, ctx["enc_saved"] = self.stacks_fwd(enc_pre, [ctx["groups"][g.name]["x_kept"].view(B * g.n_kept, E) for g in glist],
-                                               B, [g.n_kept for g in glist], E, depth_g, H, dh, self.mlp_e)
-        for g, pre, x in zip(glist, enc_pre, xs):
-            gc = ctx["groups"][g.name]
-            rows = B * g.n_kept
-            gc["enc_pre_norm"] = x
-            gc["enc_m"], gc["enc_r"] = self._new(rows, dtype=f32), self._new(rows, dtype=f32)
-            if self.inter_depth:
-                K.layernorm_fwd(x, P[pre + "norm.weight"], P[pre + "norm.bias"], xcat, gc["enc_m"], gc["enc_r"], rows,
-                                E, out_map=(g.n_kept, nt, g.kept_off))
-            else:
-                gc["enc_out"] = self._new(rows, E)
-                K.layernorm_fwd(x, P[pre + "norm.weight"], P[pre + "norm.bias"], gc["enc_out"], gc["enc_m"],
-                                gc["enc_r"], rows, E)
-        if self.inter_depth:
-            x, ctx["inter_saved"] = self.stack_fwd("encoder_inter.", xcat, B, nt, E, self.inter_depth, H, dh,
-                                                   self.mlp_e)
-            ctx["inter_pre_norm"] = x
-            for g in self.groups.values():
-                gc = ctx["groups"][g.name]
-                rows = B * g.n_kept
-                gc["int_m"], gc["int_r"] = self._new(rows, dtype=f32), self._new(rows, dtype=f32)
-                gc["enc_out"] = self._new(rows, E)
-                K.layernorm_fwd(x, P["encoder_inter.norm.weight"], P["encoder_inter.norm.bias"], gc["enc_out"],
-                                gc["int_m"], gc["int_r"], rows, E, in_map=(g.n_kept, nt, g.kept_off))
+        self._encode_groups(ctx, [ctx["groups"][g.name]["x_kept"].view(-1, E) for g in glist],
+                            [g.n_kept for g in glist])
 
         # 5. encoder -> decoder projection, unmask (+ decoder encodings), decoder, pixel projection
         Hd, dhd = hp["decoder_heads"], hp["decoder_dim_head"]
+        Bgs = [B * g.bmul for g in glist]
         yds = []
         if E != Dd:
-            yds = [self._new(B * g.n_kept, Dd) for g in glist]
-            self.lin_fwd_g([(ctx["groups"][g.name]["enc_out"], B * g.n_kept, f"enc_to_dec.{g.name}.weight",
-                             f"enc_to_dec.{g.name}.bias", yd, None, None) for g, yd in zip(glist, yds)])
+            yds = [self._new(bg * g.n_kept, Dd) for g, bg in zip(glist, Bgs)]
+            self.lin_fwd_g([(ctx["groups"][g.name]["enc_out"], bg * g.n_kept, f"enc_to_dec.{g.wname}.weight",
+                             f"enc_to_dec.{g.wname}.bias", yd, None, None) for g, yd, bg in zip(glist, yds, Bgs)])
         else:
             yds = [ctx["groups"][g.name]["enc_out"] for g in glist]
         x_decs = []
-        for g, yd in zip(glist, yds):
+        for g, yd, bg in zip(glist, yds, Bgs):
             gc = ctx["groups"][g.name]
             tok = torch.cat([P[f"mask_token.{x}"].reshape(-1, Dd) for x in g.mods], 0)
-            x_dec = self._new(B, g.L, Dd)
-            K.unmask_fwd(yd.view(B, g.n_kept, Dd), gc["mask"], gc["slot"], g.consts["tok_id"], gc["src_pos"], tok,
-                         g.consts["dec_pos"], gc["feat"], g.consts["date_id"], x_dec, self.date_dim, self.fac_date)
-            x_decs.append(x_dec.view(B * g.L, Dd))
-        dec_pre = [f"decoder.{g.name}." for g in glist]
-        xs, ctx["dec_saved"] = self.stacks_fwd(dec_pre, x_decs, B, [g.L for g in glist], Dd, hp["decoder_depth"], Hd, dhd,
-                                               self.mlp_d)
+            x_dec = self._new(bg, g.L, Dd)
+            K.unmask_fwd(yd.view(bg, g.n_kept, Dd), gc["mask"], gc["slot"], g.consts["tok_id"], gc["src_pos"], tok,
+                         g.consts["dec_pos"], gc["feat"], g.consts["date_id"], x_dec, self.date_dim, self.fac_date, g.Lt)
+            x_decs.append(x_dec.view(bg * g.L, Dd))
+        dec_pre = [f"decoder.{g.wname}." for g in glist]
+        xs, ctx["dec_saved"] = self.stacks_fwd(dec_pre, x_decs, Bgs, [g.L for g in glist], Dd, hp["decoder_depth"], Hd,
+                                               dhd, self.mlp_d)
         for g, pre, x in zip(glist, dec_pre, xs):
             gc = ctx["groups"][g.name]
             gc["dec_pre_norm"] = x
@@ -752,7 +809,7 @@ class PretrainEngine:
                     xn = self._new(seg_rows, Dd)
                     m_, r_ = self._new(seg_rows, dtype=f32), self._new(seg_rows, dtype=f32)
                     K.layernorm_fwd(x, P[pre + "norm.weight"], P[pre + "norm.bias"], xn, m_, r_, seg_rows, Dd,
-                                    in_map=(mt.D * mt.L, g.L, off))
+                                    in_map=(mt.D * mt.L, g.Lt, off))
                     pw = f"embed_to_rec.{mt.embed}.pixelify_bands.{gi}.conv."
                     pred = self._new(seg_rows, c * mt.p * mt.p)
                     self.lin_fwd(xn, seg_rows, pw + "weight", pw + "bias", pred)
@@ -763,43 +820,33 @@ class PretrainEngine:
         return ctx
 
     # ------------------------------------------------------------------ unmasked encoder (probe / finetune features)
-    @torch.no_grad()
-    def encode(self, batch: dict) -> dict[str, torch.Tensor]:
+    def encode(self, batch: dict, save: bool = False):
         """Encoder forward over EVERY token: ``BaseMIM.forward`` with ``ssl_phase`` "probe" / "finetune" up to the
         tensors ``compute_logits`` receives (ssl/mim.py:473-490, 503; ``mask`` is bypassed :276-300) -- the same
-        kernels as the pretraining step at 4x the tokens.  Forward only: returns ``[B, L_group, E]`` per
-        group in the engine dtype; the heads (``layers/head.py``) stay with the caller."""
-        K, P, E, hp = self.K, self.P, self.E, self.hp
-        ctx = self._embed(batch)
-        B = ctx["B"]
-        H, dh = hp["heads"], hp["dim_head"]
-        glist = list(self.groups.values())
-        enc_pre = [f"encoder.{g.name}." for g in glist]
-        xs, saved = self.stacks_fwd(enc_pre, [ctx["groups"][g.name]["x_embed"].view(B * g.L, E) for g in glist], B,
-                                    [g.L for g in glist], E, hp["depth"] - self.inter_depth, H, dh, self.mlp_e)
-        del saved
-        nt, offs, f32 = sum(g.L for g in glist), {}, torch.float32
-        for g in glist:
-            offs[g.name] = sum(x.L for x in glist[:glist.index(g)])
-        out = {g.name: self._new(B * g.L, E) for g in glist}
-        xcat = self._new(B * nt, E) if self.inter_depth else None
-        for g, pre, x in zip(glist, enc_pre, xs):
-            rows = B * g.L
-            m_, r_ = self._new(rows, dtype=f32), self._new(rows, dtype=f32)
-            if self.inter_depth:
-                K.layernorm_fwd(x, P[pre + "norm.weight"], P[pre + "norm.bias"], xcat, m_, r_, rows, E,
-                                out_map=(g.L, nt, offs[g.name]))
-            else:
-                K.layernorm_fwd(x, P[pre + "norm.weight"], P[pre + "norm.bias"], out[g.name], m_, r_, rows, E)
-        if self.inter_depth:
-            x, saved = self.stack_fwd("encoder_inter.", xcat, B, nt, E, self.inter_depth, H, dh, self.mlp_e)
-            del saved
-            for g in glist:
-                rows = B * g.L
-                m_, r_ = self._new(rows, dtype=f32), self._new(rows, dtype=f32)
-                K.layernorm_fwd(x, P["encoder_inter.norm.weight"], P["encoder_inter.norm.bias"], out[g.name], m_, r_,
-                                rows, E, in_map=(g.L, nt, offs[g.name]))
-        return {n: t.view(B, -1, E) for n, t in out.items()}
+        kernels as the pretraining step at 4x the tokens.  Returns ``[B * bmul, L, E]`` per group in the
+        engine dtype (``[B, L_group, E]`` for fusion "group" / "mod").  ``save=True`` (finetune) also returns the
+        context :meth:`encode_backward` needs; ``save=False`` (probe, frozen encoder) keeps no activations."""
+        E = self.E
+        with torch.no_grad():
+            ctx = self._embed(batch)
+            B = ctx["B"]
+            glist = list(self.groups.values())
+            ctx["unmasked"] = True
+            self._encode_groups(ctx, [ctx["groups"][g.name]["x_embed"].view(-1, E) for g in glist],
+                                [g.L for g in glist], save)
+            out = {g.name: ctx["groups"][g.name]["enc_out"].view(B * g.bmul, g.L, E) for g in glist}
+        return (out, ctx) if save else out
+
+    def encode_backward(self, ctx: dict, d_out: dict[str, torch.Tensor]) -> None:
+        """Backward of :meth:`encode` (finetune: the prediction loss reaches the encoder through ``compute_logits``,
+        train/base.py:189-222): accumulates the encoder-side parameter gradients into the arena from
+        ``d_out[group]`` = d loss / d encoded tokens."""
+        E = self.E
+        ctx["d_enc_out"] = {g.name: d_out[g.name].to(self.dtype).contiguous().view(-1, E) for g in self.groups.values()}
+        self.grads_dirty = True
+        self._backward_inter(ctx)
+        for ci in range(len(self._enc_chunks())):
+            self._backward_encoder_chunk(ctx, ci)
 
     # ------------------------------------------------------------------ loss (+ d loss / d pred)
     def loss(self, ctx: dict, batch: dict, with_grad: bool = True, upstream: float = 1.0) -> torch.Tensor:
@@ -819,7 +866,7 @@ class PretrainEngine:
             if with_grad:
                 mc["dpred"] = [torch.empty_like(p) for p in mc["pred"]]
             K.loss_fwd_bwd(batch[name], mc["pred"], mc["dpred"] if with_grad else None, gc["mask"], coef[i:i + 1],
-                           accum[i], B, mt.D, mt.C, mt.S, mt.p, g.L, mt.tok_off, mt.band_groups,
+                           accum[i], B, mt.D, mt.C, mt.S, mt.p, g.Lt, mt.tok_off, mt.band_groups,
                            mt.loss_bands if kind.endswith("_norm") else None, kind.startswith("l2"))
         per_mod = (accum[:, 0] / accum[:, 1]).to(torch.float32)
         ctx["loss_per_mod"] = per_mod
@@ -882,6 +929,7 @@ class PretrainEngine:
         a caller can interleave gradient all-reduces (or CUDA-graph boundaries) between segments.
         """
         seg = self.BWD_SEGMENTS
+        self.grads_dirty = True
         first = 0 if start is None else seg.index(start) + 1
         last = len(seg) - 1 if stop is None else seg.index(stop)
         for i in range(first, last + 1):
@@ -896,11 +944,12 @@ class PretrainEngine:
         Hd, dhd = hp["decoder_heads"], hp["decoder_dim_head"]
         d_enc_out = {}
         glist = list(self.groups.values())
-        dec_pre = [f"decoder.{g.name}." for g in glist]
+        Bgs = [B * g.bmul for g in glist]
+        dec_pre = [f"decoder.{g.wname}." for g in glist]
         dxds = []
         for g, pre in zip(glist, dec_pre):
             gc = ctx["groups"][g.name]
-            dxd = self._new(B * g.L, Dd)
+            dxd = self._new(B * g.Lt, Dd)
             for name in g.mods:
                 mt, mc = self.mods[name], ctx["mods"][name]
                 seg_rows = B * mt.D * mt.L
@@ -911,29 +960,29 @@ class PretrainEngine:
                     self.lin_bwd(mc["dpred"][gi], seg_rows, mc["xn"][gi], pw + "weight", pw + "bias", dx=dxn)
                     K.layernorm_bwd(dxn, gc["dec_pre_norm"], mc["dec_m"][gi], mc["dec_r"][gi], P[pre + "norm.weight"],
                                     None, dxd, G[pre + "norm.weight"], G[pre + "norm.bias"], seg_rows, Dd,
-                                    in_map=(mt.D * mt.L, g.L, off), dbias=self.bias_sink(pre, hp["decoder_depth"]))
+                                    in_map=(mt.D * mt.L, g.Lt, off), dbias=self.bias_sink(pre, hp["decoder_depth"]))
                 mc["dpred"] = mc["xn"] = None
             dxds.append(dxd)
-        dxds = self.stacks_bwd(dec_pre, dxds, ctx["dec_saved"], B, [g.L for g in glist], Dd, Hd, dhd, self.mlp_d)
+        dxds = self.stacks_bwd(dec_pre, dxds, ctx["dec_saved"], Bgs, [g.L for g in glist], Dd, Hd, dhd, self.mlp_d)
         dyds = []
-        for g, dxd in zip(glist, dxds):
+        for g, dxd, bg in zip(glist, dxds, Bgs):
             gc = ctx["groups"][g.name]
             # unmask backward: kept rows go back to the projection, masked rows feed the mask tokens
-            dxd3 = dxd.view(B, g.L, Dd)
-            dyd = self._new(B, g.n_kept, Dd)
+            dxd3 = dxd.view(bg, g.L, Dd)
+            dyd = self._new(bg, g.n_kept, Dd)
             K.gather_rows(dxd3, gc["uidx"], dyd)
             dtok = self._zeros(sum(self.mods[x].G for x in g.mods), Dd, dtype=f32)
-            K.masktoken_grad(dxd3, gc["mask"], g.consts["tok_id"], gc["src_pos"], dtok)
+            K.masktoken_grad(dxd3, gc["mask"], g.consts["tok_id"], gc["src_pos"], dtok, g.Lt)
             k0 = 0
             for x in g.mods:
                 Gx = self.mods[x].G
                 G[f"mask_token.{x}"].view(Gx, Dd).add_(dtok[k0:k0 + Gx])
                 k0 += Gx
-            dyds.append(dyd.view(B * g.n_kept, Dd))
+            dyds.append(dyd.view(bg * g.n_kept, Dd))
         if E != Dd:
-            des = [self._new(B * g.n_kept, E) for g in glist]
-            self.lin_bwd_g([(dyd, B * g.n_kept, ctx["groups"][g.name]["enc_out"], f"enc_to_dec.{g.name}.weight",
-                             f"enc_to_dec.{g.name}.bias", de, None) for g, dyd, de in zip(glist, dyds, des)])
+            des = [self._new(bg * g.n_kept, E) for g, bg in zip(glist, Bgs)]
+            self.lin_bwd_g([(dyd, bg * g.n_kept, ctx["groups"][g.name]["enc_out"], f"enc_to_dec.{g.wname}.weight",
+                             f"enc_to_dec.{g.wname}.bias", de, None) for g, dyd, de, bg in zip(glist, dyds, des, Bgs)])
         else:
             des = dyds
         for g, de in zip(glist, des):
@@ -944,16 +993,16 @@ class PretrainEngine:
         K, P, G = self.K, self.P, self.G
         E, hp, B = self.E, self.hp, ctx["B"]
         H, dh = hp["heads"], hp["dim_head"]
-        nt = self.n_kept_total
+        nt = ctx["enc_nt"]
         d_enc_out = ctx["d_enc_out"]
         if self.inter_depth:
             dxcat = self._new(B * nt, E)
-            for g in self.groups.values():
+            for g, n, off in zip(self.groups.values(), ctx["enc_n"], ctx["enc_off"]):
                 gc = ctx["groups"][g.name]
-                rows = B * g.n_kept
+                rows = B * n
                 K.layernorm_bwd(d_enc_out[g.name], ctx["inter_pre_norm"], gc["int_m"], gc["int_r"],
                                 P["encoder_inter.norm.weight"], None, dxcat, G["encoder_inter.norm.weight"],
-                                G["encoder_inter.norm.bias"], rows, E, in_map=(g.n_kept, nt, g.kept_off),
+                                G["encoder_inter.norm.bias"], rows, E, in_map=(n, nt, off),
                                 dbias=self.bias_sink("encoder_inter.", self.inter_depth))
             ctx["dxcat"] = self.stack_bwd("encoder_inter.", dxcat, ctx["inter_saved"], B, nt, E, H, dh, self.mlp_e)
 
@@ -961,21 +1010,20 @@ class PretrainEngine:
         """Gradient of the stacks' final LayerNorms (first thing the encoder backward touches)."""
         K, P, G = self.K, self.P, self.G
         E, hp, B = self.E, self.hp, ctx["B"]
-        H, dh = hp["heads"], hp["dim_head"]
-        nt = self.n_kept_total
+        nt = ctx["enc_nt"]
         glist = list(self.groups.values())
         d_enc_out, dxcat = ctx["d_enc_out"], ctx.get("dxcat")
         depth_g = hp["depth"] - self.inter_depth
-        enc_pre = [f"encoder.{g.name}." for g in glist]
         dxs = []
-        for g, pre in zip(glist, enc_pre):
+        for g, n, off in zip(glist, ctx["enc_n"], ctx["enc_off"]):
+            pre = f"encoder.{g.wname}."
             gc = ctx["groups"][g.name]
-            rows = B * g.n_kept
+            rows = B * g.bmul * n
             dx = self._new(rows, E)
             if self.inter_depth:
                 K.layernorm_bwd(dxcat, gc["enc_pre_norm"], gc["enc_m"], gc["enc_r"], P[pre + "norm.weight"], None, dx,
                                 G[pre + "norm.weight"], G[pre + "norm.bias"], rows, E,
-                                out_map=(g.n_kept, nt, g.kept_off), dbias=self.bias_sink(pre, depth_g))
+                                out_map=(n, nt, off), dbias=self.bias_sink(pre, depth_g))
             else:
                 K.layernorm_bwd(d_enc_out[g.name], gc["enc_pre_norm"], gc["enc_m"], gc["enc_r"],
                                 P[pre + "norm.weight"], None, dx, G[pre + "norm.weight"], G[pre + "norm.bias"], rows, E,
@@ -989,9 +1037,9 @@ class PretrainEngine:
             self._encoder_bwd_begin(ctx)
         hp, glist = self.hp, list(self.groups.values())
         lo, hi = chunks[ci]
-        ctx["enc_dxs"] = self.stacks_bwd([f"encoder.{g.name}." for g in glist], ctx["enc_dxs"], ctx["enc_saved"],
-                                         ctx["B"], [g.n_kept for g in glist], self.E, hp["heads"], hp["dim_head"],
-                                         self.mlp_e, lo, hi)
+        ctx["enc_dxs"] = self.stacks_bwd([f"encoder.{g.wname}." for g in glist], ctx["enc_dxs"], ctx["enc_saved"],
+                                         [ctx["B"] * g.bmul for g in glist], ctx["enc_n"], self.E, hp["heads"],
+                                         hp["dim_head"], self.mlp_e, lo, hi)
         if ci == len(chunks) - 1:
             self._encoder_bwd_end(ctx)
 
@@ -1002,8 +1050,11 @@ class PretrainEngine:
         glist = list(self.groups.values())
         for g, dx in zip(glist, ctx.pop("enc_dxs")):
             gc = ctx["groups"][g.name]
-            dxe = self._new(B, g.L, E)
-            K.scatter_kept(dx.view(B, g.n_kept, E), gc["mask"], gc["slot"], dxe)
+            if ctx.get("unmasked"):
+                dxe = dx.view(B, g.Lt, E)                      # probe / finetune: every token was encoded
+            else:
+                dxe = self._new(B, g.Lt, E)
+                K.scatter_kept(dx.view(B * g.bmul, g.n_kept, E), gc["mask"], gc["slot"], dxe.view(B * g.bmul, g.L, E))
             for name in g.mods:
                 mt, mc = self.mods[name], ctx["mods"][name]
                 n_img, rows_m = B * mt.D, B * mt.D * mt.L
@@ -1013,7 +1064,7 @@ class PretrainEngine:
                     sums2 = self._zeros(n_img, 2, dtype=torch.float64)
                     dconv = self._new(rows_m, E)
                     K.gn_bwd(dxe, mc["y"][gi], mc["stats"][gi], P[pw + "norm.weight"], sums2, dconv,
-                             G[pw + "norm.weight"], G[pw + "norm.bias"], n_img, mt.D, mt.L, E, g.L, off)
+                             G[pw + "norm.weight"], G[pw + "norm.bias"], n_img, mt.D, mt.L, E, g.Lt, off)
                     self.lin_bwd(dconv, rows_m, mc["cols"][gi], pw + "conv.weight", pw + "conv.bias", dx=None)
 
     # ------------------------------------------------------------------ one training step (no optimiser)

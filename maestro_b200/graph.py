@@ -94,6 +94,7 @@ class GraphedPretrainStep:
             self.graphs.append(g)
         self.launches_per_step = eng.K.launches - launches0     # kernels of ours inside one replay
         self._ctx = ctx          # keeps the captured buffers (mask, indices, predictions) readable after a replay
+        eng.zero_grad()          # the eager warm-up steps accumulated into the arena: the first replay starts clean
 
     # ------------------------------------------------------------------ per step
     def _draw_struct(self) -> None:
@@ -186,7 +187,15 @@ class GraphedPretrainStep:
                 self.struct[n].copy_(m.reshape(self.B, -1).to(torch.uint8), non_blocking=True)
 
     def replay(self, segment: int | None = None) -> torch.Tensor:
-        """Replay every segment (or one); the gradient arena must have been zeroed by the caller / optimiser."""
+        """Replay every segment (or one); the gradient arena must have been zeroed by the caller / optimiser.
+
+        The bf16 weight-shadow refresh is NOT part of the captured graphs (``shadows_fresh`` was true during capture): when
+        the fp32 parameters changed behind the engine's back (``load_state_dict``, an optimiser other than ``FusedAdamW``)
+        the shadows are refreshed eagerly before the forward graph."""
+        eng = self.eng
+        if not eng.shadows_fresh and (segment is None or segment == 0):
+            eng.arena.refresh_shadows(eng.K)
+            eng.shadows_fresh = True
         if segment is None:
             for g in self.graphs:
                 g.replay()

@@ -39,10 +39,6 @@ def _p(t: torch.Tensor | None):
     return C.c_void_p(t.data_ptr())
 
 
-def _stream():
-    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
-
-
 def _ck(rc: int, name: str) -> None:
     if rc != 0:
         raise RuntimeError(f"{name} failed with status {rc}")
@@ -60,114 +56,128 @@ class Kernels:
 
     name = "cuda"
 
-    def __init__(self) -> None:
+    def __init__(self, device=None) -> None:
+        """``device``: the CUDA device whose current stream receives the launches (default: the device that is current
+        when the object is built).  An engine on ``cuda:1`` keeps launching on ``cuda:1``'s stream whatever the
+        caller's current device is."""
         self.L = _lib.lib()
         self.launches = 0
+        self.device = None if device is None else torch.device(device)
         self.use_tc = True   # tcgen05 GEMM for bf16 (False: CUDA-core GEMM everywhere; debugging aid)
+
+    def _s(self):
+        cur = torch.cuda.current_device()
+        if self.device is None:
+            self.device = torch.device("cuda", cur)
+        elif self.device.index is not None and self.device.index != cur:
+            # a launch goes to the calling thread's current device: refuse to enqueue on a foreign device's stream
+            raise RuntimeError(f"maestro_b200 kernels bound to {self.device} were called with cuda:{cur} current; "
+                               f"wrap the call in torch.cuda.device({self.device.index})")
+        return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
 
     # ------------------------------------------------------------------ data movement
     def cast_bf16(self, src, dst):
         self.launches += 1
-        _ck(self.L.mb_cast_f32_to_bf16(_p(src), _p(dst), C.c_size_t(src.numel()), _stream()), "cast")
+        _ck(self.L.mb_cast_f32_to_bf16(_p(src), _p(dst), C.c_size_t(src.numel()), self._s()), "cast")
 
     def cast_transpose_bf16(self, src, dst):
         R, Cc = src.shape
         self.launches += 1
-        _ck(self.L.mb_cast_transpose_f32_to_bf16(_p(src), _p(dst), R, Cc, _stream()), "cast_transpose")
+        _ck(self.L.mb_cast_transpose_f32_to_bf16(_p(src), _p(dst), R, Cc, self._s()), "cast_transpose")
 
     def resize_nearest(self, src, dst, rescale_elev):
         n, Cc, h, w = src.shape
         self.launches += 1
         _ck(self.L.mb_resize_nearest(_p(src), _p(dst), n, Cc, h, w, dst.shape[-2], dst.shape[-1], int(rescale_elev),
-                                     _stream()), "resize")
+                                     self._s()), "resize")
 
     def resize(self, src, dst, mode, rescale_elev):
         """F.interpolate(src, dst.shape[-2:], mode) (+ elevation rescale); mode in nearest / bilinear / bicubic."""
         n, Cc, h, w = src.shape
         self.launches += 1
         _ck(self.L.mb_resize(_p(src), _p(dst), n, Cc, h, w, dst.shape[-2], dst.shape[-1], RESIZE_MODES[mode],
-                             int(rescale_elev), _stream()), "resize")
+                             int(rescale_elev), self._s()), "resize")
 
     def im2col(self, img, cols, c0, c, p):
         n, Cc, S, _ = img.shape
         self.launches += 1
-        _ck(self.L.mb_im2col(_p(img), _p(cols), _dt(cols), n, Cc, c0, c, S, p, cols.shape[1], _stream()), "im2col")
+        _ck(self.L.mb_im2col(_p(img), _p(cols), _dt(cols), n, Cc, c0, c, S, p, cols.shape[1], self._s()), "im2col")
 
     def rows_image(self, rows, img, c0, c, p, direction):
         n, Cc, S, _ = img.shape
         self.launches += 1
-        _ck(self.L.mb_rows_image(_p(rows), _dt(rows), _p(img), n, Cc, c0, c, S, p, direction, _stream()), "rows_image")
+        _ck(self.L.mb_rows_image(_p(rows), _dt(rows), _p(img), n, Cc, c0, c, S, p, direction, self._s()), "rows_image")
 
     def date_features(self, dates, ref, feat, doff):
         B, D, _ = dates.shape
         self.launches += 1
-        _ck(self.L.mb_date_features(_p(dates), _p(ref), _p(feat), B, D, feat.shape[1], doff, _stream()), "date_features")
+        _ck(self.L.mb_date_features(_p(dates), _p(ref), _p(feat), B, D, feat.shape[1], doff, self._s()), "date_features")
 
     def colsum_accum(self, dy, out):
         M, N = dy.shape
         self.launches += 1
-        _ck(self.L.mb_colsum_accum(_p(dy), _dt(dy), _p(out), M, N, _stream()), "colsum")
+        _ck(self.L.mb_colsum_accum(_p(dy), _dt(dy), _p(out), M, N, self._s()), "colsum")
 
     # ------------------------------------------------------------------ norms
     def layernorm_fwd(self, x, gamma, beta, y, mean, rstd, rows, d, eps=1e-5, in_map=IDENT, out_map=IDENT):
         im, om = _rowmap(in_map, rows), _rowmap(out_map, rows)
         self.launches += 1
         _ck(self.L.mb_layernorm_fwd(_p(x), _p(gamma), _p(beta), _p(y), _p(mean), _p(rstd), _dt(x), rows, d,
-                                    C.c_float(eps), *im, *om, _stream()), "layernorm_fwd")
+                                    C.c_float(eps), *im, *om, self._s()), "layernorm_fwd")
 
     def layernorm_bwd(self, dy, x, mean, rstd, gamma, dres, dx, dgamma, dbeta, rows, d, in_map=IDENT, out_map=IDENT,
                       dbias=None):
         im, om = _rowmap(in_map, rows), _rowmap(out_map, rows)
         self.launches += 1
         _ck(self.L.mb_layernorm_bwd(_p(dy), _p(x), _p(mean), _p(rstd), _p(gamma), _p(dres), _p(dx), _p(dgamma),
-                                    _p(dbeta), _p(dbias), _dt(x), rows, d, *im, *om, _stream()), "layernorm_bwd")
+                                    _p(dbeta), _p(dbias), _dt(x), rows, d, *im, *om, self._s()), "layernorm_bwd")
 
     def gn_stats(self, y, sums, n_img):
         self.launches += 1
-        _ck(self.L.mb_gn_stats(_p(y), _dt(y), _p(sums), n_img, C.c_longlong(y.numel() // n_img), _stream()), "gn_stats")
+        _ck(self.L.mb_gn_stats(_p(y), _dt(y), _p(sums), n_img, C.c_longlong(y.numel() // n_img), self._s()), "gn_stats")
 
     def gn_apply(self, y, sums, gamma, beta, pos, feat, out, stats, n_img, D, L, E, eps, out_bs, out_off, date_dim,
                  fac_date, feat_off):
         self.launches += 1
         _ck(self.L.mb_gn_apply(_p(y), _p(sums), _p(gamma), _p(beta), _p(pos), _p(feat), _p(out), _p(stats), _dt(y),
                                n_img, D, L, E, C.c_float(eps), out_bs, out_off, date_dim, C.c_float(fac_date),
-                               feat.shape[1], feat_off, _stream()), "gn_apply")
+                               feat.shape[1], feat_off, self._s()), "gn_apply")
 
     def gn_bwd(self, dy, y, stats, gamma, sums2, dconv, dgamma, dbeta, n_img, D, L, E, out_bs, out_off):
         self.launches += 2
         _ck(self.L.mb_gn_bwd(_p(dy), _p(y), _p(stats), _p(gamma), _p(sums2), _p(dconv), _p(dgamma), _p(dbeta),
-                             _dt(y), n_img, D, L, E, out_bs, out_off, _stream()), "gn_bwd")
+                             _dt(y), n_img, D, L, E, out_bs, out_off, self._s()), "gn_bwd")
 
     # ------------------------------------------------------------------ masking
-    def mask_indices(self, noise, struct, nm, mask, slot, masked_idx, unmasked_idx, seg_id, seg_counts):
+    def mask_indices(self, noise, struct, nm, mask, slot, masked_idx, unmasked_idx, seg_id, seg_counts, Lt=0):
         B, L = noise.shape
         self.launches += 1
         _ck(self.L.mb_mask_indices(_p(noise), _p(struct), B, L, nm, _p(mask), _p(slot), _p(masked_idx),
-                                   _p(unmasked_idx), _p(seg_id), _p(seg_counts), _stream()), "mask_indices")
+                                   _p(unmasked_idx), _p(seg_id), _p(seg_counts), Lt, self._s()), "mask_indices")
 
     def gather_rows(self, x, idx, out):
         B, L, d = x.shape
         self.launches += 1
-        _ck(self.L.mb_gather_rows(_p(x), _p(idx), _p(out), _dt(x), B, L, idx.shape[1], d, _stream()), "gather_rows")
+        _ck(self.L.mb_gather_rows(_p(x), _p(idx), _p(out), _dt(x), B, L, idx.shape[1], d, self._s()), "gather_rows")
 
     def scatter_kept(self, dkept, mask, slot, dx):
         B, L, d = dx.shape
         self.launches += 1
         _ck(self.L.mb_scatter_kept(_p(dkept), _p(mask), _p(slot), _p(dx), _dt(dx), B, L, dkept.shape[1], d,
-                                   _stream()), "scatter_kept")
+                                   self._s()), "scatter_kept")
 
-    def unmask_fwd(self, y, mask, slot, tok_id, src_pos, tok, pos, feat, date_id, out, date_dim, fac_date):
+    def unmask_fwd(self, y, mask, slot, tok_id, src_pos, tok, pos, feat, date_id, out, date_dim, fac_date, Lt=0):
         B, L, d = out.shape
         self.launches += 1
         _ck(self.L.mb_unmask_fwd(_p(y), _p(mask), _p(slot), _p(tok_id), _p(src_pos), _p(tok), _p(pos), _p(feat),
                                  _p(date_id), _p(out), _dt(out), B, L, y.shape[1], d, feat.shape[1], date_dim,
-                                 C.c_float(fac_date), _stream()), "unmask_fwd")
+                                 C.c_float(fac_date), Lt, self._s()), "unmask_fwd")
 
-    def masktoken_grad(self, dx, mask, tok_id, src_pos, dtok):
+    def masktoken_grad(self, dx, mask, tok_id, src_pos, dtok, Lt=0):
         B, L, d = dx.shape
         self.launches += 1
         _ck(self.L.mb_masktoken_grad(_p(dx), _p(mask), _p(tok_id), _p(src_pos), _p(dtok), _dt(dx), B, L, d,
-                                     dtok.shape[0], _stream()), "masktoken_grad")
+                                     dtok.shape[0], Lt, self._s()), "masktoken_grad")
 
     # ------------------------------------------------------------------ loss
     def loss_fwd_bwd(self, target, preds, dpreds, mask, coef, accum, B, D, Cc, S, p, Lg, mask_off, cg, norm_bands,
@@ -198,7 +208,7 @@ class Kernels:
         if not target.is_cuda:
             raise RuntimeError("maestro_b200 kernels need CUDA tensors (there is no CPU fallback)")
         self.launches += 1
-        _ck(self.L.mb_loss_fwd_bwd(C.byref(P), _dt(preds[0]), _stream()), "loss_fwd_bwd")
+        _ck(self.L.mb_loss_fwd_bwd(C.byref(P), _dt(preds[0]), self._s()), "loss_fwd_bwd")
 
     # ------------------------------------------------------------------ GEMM
     def _gemm_params(self, A, B, Cm, M, N, K, sam, sak, sbn, sbk, ldc, bias=None, residual=None, aux=None, flags=0,
@@ -238,9 +248,9 @@ class Kernels:
         P, tc_ok = self._gemm_params(A, B, Cm, M, N, K, sam, sak, sbn, sbk, ldc, **kw)
         self.launches += 1
         if tc_ok:
-            _ck(self.L.mb_gemm_tc(C.byref(P), _stream()), "gemm_tc")
+            _ck(self.L.mb_gemm_tc(C.byref(P), self._s()), "gemm_tc")
         else:
-            _ck(self.L.mb_gemm_simt(C.byref(P), _dt(A), _stream()), "gemm_simt")
+            _ck(self.L.mb_gemm_simt(C.byref(P), _dt(A), self._s()), "gemm_simt")
             self._simt_colsum(Cm, M, N, kw)
 
     def _simt_colsum(self, Cm, M, N, kw):
@@ -259,38 +269,38 @@ class Kernels:
         for (P, ok), (a, _) in zip(built, problems):   # _ = kwargs of the problem
             if not ok:
                 self.launches += 1
-                _ck(self.L.mb_gemm_simt(C.byref(P), _dt(a[0]), _stream()), "gemm_simt")
+                _ck(self.L.mb_gemm_simt(C.byref(P), _dt(a[0]), self._s()), "gemm_simt")
                 self._simt_colsum(a[2], a[3], a[4], _)
         for i in range(0, len(tc), 4):
             chunk = tc[i:i + 4]
             arr = (_lib.GemmParams * len(chunk))(*chunk)
             self.launches += 1
-            _ck(self.L.mb_gemm_tc_grouped(arr, len(chunk), _stream()), "gemm_tc_grouped")
+            _ck(self.L.mb_gemm_tc_grouped(arr, len(chunk), self._s()), "gemm_tc_grouped")
 
     def softmax_rows(self, s, p, rows, n, scale):
         self.launches += 1
-        _ck(self.L.mb_softmax_rows(_p(s), _p(p), _dt(p), C.c_longlong(rows), n, C.c_float(scale), _stream()), "softmax")
+        _ck(self.L.mb_softmax_rows(_p(s), _p(p), _dt(p), C.c_longlong(rows), n, C.c_float(scale), self._s()), "softmax")
 
     def softmax_bwd_rows(self, p, dp, ds, rows, n, scale):
         self.launches += 1
         _ck(self.L.mb_softmax_bwd_rows(_p(p), _p(dp), _p(ds), _dt(p), C.c_longlong(rows), n, C.c_float(scale),
-                                       _stream()), "softmax_bwd")
+                                       self._s()), "softmax_bwd")
 
     # ------------------------------------------------------------------ fused attention (bf16, tcgen05)
     def attn_fwd(self, qkv, o, lse, Bn, N, H, dh):
         self.launches += 1
-        _ck(self.L.mb_attn_fwd(_p(qkv), _p(o), _p(lse), Bn, N, H, dh, _stream()), "attn_fwd")
+        _ck(self.L.mb_attn_fwd(_p(qkv), _p(o), _p(lse), Bn, N, H, dh, self._s()), "attn_fwd")
 
     def attn_bwd(self, qkv, o, do, lse, dqkv, delta, Bn, N, H, dh):
         self.launches += 2
-        _ck(self.L.mb_attn_bwd(_p(qkv), _p(o), _p(do), _p(lse), _p(dqkv), _p(delta), Bn, N, H, dh, _stream()),
+        _ck(self.L.mb_attn_bwd(_p(qkv), _p(o), _p(do), _p(lse), _p(dqkv), _p(delta), Bn, N, H, dh, self._s()),
             "attn_bwd")
 
     # ------------------------------------------------------------------ optimiser
     def adamw_step(self, p, g, m, v, shadow, hyper, zero_grad):
         self.launches += 1
         _ck(self.L.mb_adamw_step(_p(p), _p(g), _p(m), _p(v), _p(shadow), _p(hyper), C.c_size_t(p.numel()),
-                                 int(zero_grad), _stream()), "adamw_step")
+                                 int(zero_grad), self._s()), "adamw_step")
 
     # ------------------------------------------------------------------ device-side input pipeline
     def raster_transform(self, raw, out, aug, imgs_per_sample, norm_fac, log_scale):
@@ -304,7 +314,7 @@ class Kernels:
         self.launches += 1
         _ck(self.L.mb_raster_transform(_p(raw), code, _p(out), _p(aug), n, int(imgs_per_sample), Cc, H, W,
                                        C.c_float(norm_fac if norm_fac is not None else 1.0),
-                                       int(norm_fac is not None), int(bool(log_scale)), _stream()),
+                                       int(norm_fac is not None), int(bool(log_scale)), self._s()),
             "raster_transform")
 
     def struct_mask(self, mods, seed, offset, out, passes=None, max_pass=0):
@@ -321,5 +331,5 @@ class Kernels:
         if out.shape[-1] != P.L_group or out.dtype != torch.uint8:
             raise ValueError("struct_mask: out must be uint8 [B, L_group]")
         self.launches += 1
-        _ck(self.L.mb_struct_mask(C.byref(P), _p(out), _p(passes), out.shape[0], int(max_pass), _stream()),
+        _ck(self.L.mb_struct_mask(C.byref(P), _p(out), _p(passes), out.shape[0], int(max_pass), self._s()),
             "struct_mask")

@@ -80,3 +80,4 @@ class FusedAdamW:
         self.step_range(0, self.engine.arena.numel)
         # the kernel refreshed the bf16 shadow in the same pass (dgrad reads it untransposed: no other copies)
         self.engine.shadows_fresh = True
+        self.engine.grads_dirty = False          # the kernel zeroed the gradient arena in the same pass

@@ -115,15 +115,17 @@ class MAE(nn.Module):
                                                      embed_dim * decoder_mlp_ratio) for g in names})
         if self.inter_depth:
             self.encoder_inter = Transformer(embed_dim, self.inter_depth, heads, dim_head, embed_dim * mlp_ratio)
-        # per-group mask ratio as the reference exposes it (ssl/mae.py:84-131)
+        else:
+            self.encoder_inter = None               # as the reference (ssl/mae.py:176)
+        # mask ratio per group ("group") or per modality (every other mode) as the reference exposes it (ssl/mae.py:84-131)
         self.mask_ratio = {}
-        for g in names:
-            members = spec.group_members(g) if fusion_mode == "group" else [g]
-            if g == "shared":
-                self.mask_ratio[g] = self.mask_cfg.mask_ratio
-                continue
-            n_dates = sum(spec.inputs[x].num_dates * self.len_bands[x] for x in members)
-            self.mask_ratio[g] = 1 - (1 - self.mask_cfg.mask_ratio) / (n_dates ** self.mask_cfg.mask_scale)
+        if fusion_mode in ("shared", "monotemp", "msgfm"):
+            self.mask_ratio = {n: self.mask_cfg.mask_ratio for n in spec.inputs}
+        else:
+            for g in names:
+                members = spec.group_members(g) if fusion_mode == "group" else [g]
+                n_dates = sum(spec.inputs[x].num_dates * self.len_bands[x] for x in members)
+                self.mask_ratio[g] = 1 - (1 - self.mask_cfg.mask_ratio) / (n_dates ** self.mask_cfg.mask_scale)
         self._eng = None
         self._bound_names: list[str] = []
         self._versions = -1
@@ -144,7 +146,7 @@ class MAE(nn.Module):
         if eng is None or eng.device != device:
             from ..ops import Kernels
             dtype = torch.float32 if os.environ.get("MAESTRO_B200_PRECISION", "bf16") == "fp32" else torch.bfloat16
-            eng = PretrainEngine(self.spec, self.hp, self.mask_cfg, Kernels(), device, dtype,
+            eng = PretrainEngine(self.spec, self.hp, self.mask_cfg, Kernels(device), device, dtype,
                                  fusion_mode=self.fusion_mode, inter_depth=self.inter_depth,
                                  interpolate=self.interpolate, fac_abs_enc=self.fac_abs_enc,
                                  fac_date_enc=self.fac_date_enc)

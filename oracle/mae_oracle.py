@@ -25,8 +25,10 @@ and re-checked live by ``tests/test_oracle_vs_reference.py`` when /root/referenc
 The Transformer sub-path depends on vit-pytorch 1.10.1 which is absent: that part is
 "parity unpinned" against the real package (restated from its published algorithm).
 
-Only ``fusion_mode="group"`` (the reference default, conf/model.py:11) and ``"mod"`` are
-restated; both concatenate (date, token) per modality along the token axis.
+``fusion_mode`` "group" (the reference default, conf/model.py:11) and "mod" concatenate (date, token) per
+modality along the token axis; "shared" / "monotemp" flatten (sample, date) into the batch instead
+(layers/utils.py:26-33) -- every date is its own sequence of grid^2 tokens, no structural masking, plain
+``mask_ratio`` (ssl/mae.py:85-96), one ``"shared"`` stack or one per modality.
 """
 
 from __future__ import annotations
@@ -284,10 +286,11 @@ def forward(sd: dict, spec, hp: dict, batch: dict, struct: dict, noise: dict, ma
     mods = spec.inputs
     if fusion_mode == "group":
         members = {g: spec.group_members(g) for g in spec.group_names}
-    elif fusion_mode == "mod":
+    elif fusion_mode in ("mod", "shared", "monotemp"):
         members = {n: [n] for n in mods}
     else:
-        raise NotImplementedError(fusion_mode)
+        raise ValueError(f"Invalid fusion mode {fusion_mode}.")
+    flat_dates = fusion_mode in ("shared", "monotemp")
     enc_tab = sincos_table(spec.pos_grid, E, date_dim) * fac_abs_enc
     dec_tab = sincos_table(spec.pos_grid, Dd, date_dim)
     ref = batch["ref_date"]
@@ -307,18 +310,24 @@ def forward(sd: dict, spec, hp: dict, batch: dict, struct: dict, noise: dict, ma
         tok_mod[name] = tok.reshape(1, -1, Dd).expand(B, -1, -1)
     x_grp = {g: torch.cat([x_mod[n] for n in ms], 1) for g, ms in members.items()}
     tok_grp = {g: torch.cat([tok_mod[n] for n in ms], 1) for g, ms in members.items()}
+    seq_len = {g: (mods[g].grid ** 2 if flat_dates else x.shape[1]) for g, x in x_grp.items()}
+    if flat_dates:      # [B, G*D*L, .] -> [(B G D), L, .]: every (band group, date) of a sample is one sequence
+        x_grp = {g: x.reshape(-1, seq_len[g], E) for g, x in x_grp.items()}
+        tok_grp = {g: t.reshape(-1, seq_len[g], Dd) for g, t in tok_grp.items()}
     out["x_embed"] = x_grp
 
     # mask
     kept, mask_tok, mask, midx, uidx = {}, {}, {}, {}, {}
-    bidx = torch.arange(B)[:, None]
     for g, x in x_grp.items():
         if ssl_phase != "pretrain":
             kept[g] = x
             continue
         L = x.shape[1]
+        bidx = torch.arange(x.shape[0])[:, None]
         if fusion_mode == "group":
             ratio = group_mask_ratio(spec, mask_cfg, g)
+        elif flat_dates:
+            ratio = mask_cfg.mask_ratio
         else:
             nd = mods[g].num_dates * len(mods[g].band_groups)
             ratio = 1 - (1 - mask_cfg.mask_ratio) / (nd ** mask_cfg.mask_scale)
@@ -345,10 +354,12 @@ def forward(sd: dict, spec, hp: dict, batch: dict, struct: dict, noise: dict, ma
     # enc -> dec, unmask, decoder encodings
     dec_in = {}
     for g, x in enc.items():
-        if f"enc_to_dec.{g}.weight" in sd:
-            x = x @ sd[f"enc_to_dec.{g}.weight"].t() + sd[f"enc_to_dec.{g}.bias"]
+        w = g if f"enc_to_dec.{g}.weight" in sd else "shared"            # model["shared"] fallback, ssl/mim.py:403
+        if f"enc_to_dec.{w}.weight" in sd:
+            x = x @ sd[f"enc_to_dec.{w}.weight"].t() + sd[f"enc_to_dec.{w}.bias"]
         L = mask[g].shape[1]
-        full = torch.zeros(B, L, Dd, dtype=x.dtype)
+        bidx = torch.arange(x.shape[0])[:, None]
+        full = torch.zeros(x.shape[0], L, Dd, dtype=x.dtype)
         where_masked = midx[g] if unmask_order is None else unmask_order[g]
         full[bidx, where_masked] = mask_tok[g].to(x.dtype)
         full[bidx, uidx[g]] = x
@@ -359,7 +370,7 @@ def forward(sd: dict, spec, hp: dict, batch: dict, struct: dict, noise: dict, ma
             de = F.pad(date_channels(dfeat[n], date_dim, fac_date_enc), (Dd - date_dim, 0)).repeat(1, G, 1)
             add = pool_table(dec_tab, m.grid)[None, None] + de[:, :, None, :]   # [B, G*D, L, Dd]
             enc_add.append(add.flatten(1, 2))
-        dec_in[g] = full + torch.cat(enc_add, 1)
+        dec_in[g] = full + torch.cat(enc_add, 1).reshape(full.shape)
     out["x_dec_in"] = dec_in
 
     # decode + pixelify
@@ -375,9 +386,9 @@ def forward(sd: dict, spec, hp: dict, batch: dict, struct: dict, noise: dict, ma
             m = mods[n]
             T = m.tokens
             G, D, L = len(m.band_groups), m.num_dates, m.grid ** 2
-            xm = dec[g][:, off:off + T].reshape(B, G * D, L, Dd)
+            xm = dec[g].reshape(B, -1, Dd)[:, off:off + T].reshape(B, G * D, L, Dd)
             pixels[n] = pixelify(sd, m.embed, xm, m)
-            mk = mask[g][:, off:off + T].reshape(B, G, D, m.grid, m.grid)
+            mk = mask[g].reshape(B, -1)[:, off:off + T].reshape(B, G, D, m.grid, m.grid)
             p = m.patch_size
             mk = mk.repeat_interleave(p, -2).repeat_interleave(p, -1)          # [B,G,D,S,S]
             mask_px[n] = torch.cat([mk[:, gi, :, None].expand(-1, -1, c, -1, -1)

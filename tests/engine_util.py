@@ -12,8 +12,9 @@ from maestro_b200.engine import PretrainEngine
 def run_engine(name: str, kernels, device, dtype, gold=None, inject_order=True):
     spec, hp, sd, batch, inter, loss, seed, bs = U.case_inputs(name)
     gold = gold if gold is not None else U.load_golden(name)
-    struct, noise, order = U.golden_draws(gold, spec)
-    eng = PretrainEngine(spec, hp, MaskSpec(), kernels, device, dtype, inter_depth=inter, loss=loss)
+    fusion = U.fusion_of(name)
+    struct, noise, order = U.golden_draws(gold, spec, fusion)
+    eng = PretrainEngine(spec, hp, MaskSpec(), kernels, device, dtype, fusion_mode=fusion, inter_depth=inter, loss=loss)
     eng.load_state_dict(sd)
     b = {k: v.clone() for k, v in batch.items()}
     ctx = eng.forward(b, struct, noise, order if inject_order else None)

@@ -153,7 +153,7 @@ class FakeKernels:
         dbeta += g.sum((0, 1))
 
     # ------------------------------------------------------------------ masking
-    def mask_indices(self, noise, struct, nm, mask, slot, masked_idx, unmasked_idx, seg_id, seg_counts):
+    def mask_indices(self, noise, struct, nm, mask, slot, masked_idx, unmasked_idx, seg_id, seg_counts, Lt=0):
         keys = noise * (1 - struct.float())
         order = torch.argsort(keys, dim=-1, stable=True)
         mi = order[:, :nm].sort(dim=1).values
@@ -169,8 +169,9 @@ class FakeKernels:
         slot.scatter_(1, mi, ar_m)
         slot.scatter_(1, ui, ar_u)
         if seg_counts is not None:
-            seg_counts += torch.bincount(seg_id[None].expand(B, -1)[m.bool()].long(),
-                                         minlength=seg_counts.numel()).to(seg_counts.dtype)
+            Lt = Lt or noise.shape[1]
+            seg = seg_id[None].expand(noise.numel() // Lt, -1).reshape(B, -1)      # table period Lt over b * L + p
+            seg_counts += torch.bincount(seg[m.bool()].long(), minlength=seg_counts.numel()).to(seg_counts.dtype)
 
     def gather_rows(self, x, idx, out):
         out.copy_(torch.gather(x, 1, idx[..., None].expand(-1, -1, x.shape[-1])))
@@ -179,21 +180,27 @@ class FakeKernels:
         g = torch.gather(dkept, 1, slot.long().clamp(max=dkept.shape[1] - 1)[..., None].expand(-1, -1, dx.shape[-1]))
         dx.copy_(torch.where(mask.bool()[..., None], torch.zeros_like(g), g))
 
-    def unmask_fwd(self, y, mask, slot, tok_id, src_pos, tok, pos, feat, date_id, out, date_dim, fac_date):
+    @staticmethod
+    def _token_kind(tok_id, src_pos, B, L, Lt, dev):
+        """tok_id of the position that feeds each (sequence, position); tables have period Lt over b * L + p."""
+        sp = src_pos.long() if src_pos is not None else torch.arange(L, device=dev)[None].expand(B, -1)
+        base = (torch.arange(B, device=dev)[:, None] * L) % Lt
+        return tok_id.long()[base + sp]
+
+    def unmask_fwd(self, y, mask, slot, tok_id, src_pos, tok, pos, feat, date_id, out, date_dim, fac_date, Lt=0):
         B, L, d = out.shape
+        Lt = Lt or L
         g = torch.gather(y, 1, slot.long().clamp(max=y.shape[1] - 1)[..., None].expand(-1, -1, d)).float()
-        sp = src_pos.long() if src_pos is not None else torch.arange(L, device=out.device)[None].expand(B, -1)
-        tk = tok[tok_id.long()[sp]].to(out.dtype).float()
-        v = torch.where(mask.bool()[..., None], tk, g)
+        tk = tok[self._token_kind(tok_id, src_pos, B, L, Lt, out.device)].to(out.dtype).float()
+        v = torch.where(mask.bool()[..., None], tk, g).reshape(B * L // Lt, Lt, d)
         v = v + pos[None]
         de = _date_channels(feat[:, date_id.long()], date_dim, fac_date)
         v[..., d - date_dim:] += de
-        out.copy_(v.to(out.dtype))
+        out.copy_(v.reshape(B, L, d).to(out.dtype))
 
-    def masktoken_grad(self, dx, mask, tok_id, src_pos, dtok):
+    def masktoken_grad(self, dx, mask, tok_id, src_pos, dtok, Lt=0):
         B, L, d = dx.shape
-        sp = src_pos.long() if src_pos is not None else torch.arange(L, device=dx.device)[None].expand(B, -1)
-        kind = tok_id.long()[sp]
+        kind = self._token_kind(tok_id, src_pos, B, L, Lt or L, dx.device)
         for k in range(dtok.shape[0]):
             sel = mask.bool() & (kind == k)
             dtok[k] += dx[sel].float().sum(0)

@@ -31,16 +31,21 @@ import synth  # noqa: E402
 from maestro_b200.conf import DATASET_SPECS  # noqa: E402
 
 CASES = {
-    # name: (dataset, batch, inter_depth, loss, seed)
+    # name: (dataset, batch, inter_depth, loss, seed[, fusion_mode = "group"])
     "micro_treesat": ("treesatai_ts", 3, 1, "l1_norm", 11),
     "micro_flair": ("flair", 2, 1, "l1_norm", 12),
     "micro_pastis_l2": ("pastis_hd", 2, 0, "l2_norm", 13),
     "micro_s2naip": ("s2_naip", 2, 1, "l1_norm", 14),
+    # the other fusion modes of the reference's own test matrix (tests/test_mae.py:19-39)
+    "micro_treesat_mod": ("treesatai_ts", 2, 1, "l1_norm", 15, "mod"),
+    "micro_treesat_shared": ("treesatai_ts", 2, 0, "l2_norm", 16, "shared"),
+    "micro_treesat_monotemp": ("treesatai_ts", 2, 0, "l1_norm", 17, "monotemp"),
+    "micro_flair_shared": ("flair", 2, 0, "l1_norm", 18, "shared"),
 }
 
 
 def run_reference(dataset: str, batch_size: int, inter_depth: int, loss: str, seed: int,
-                  hp: dict | None = None):
+                  fusion_mode: str = "group", hp: dict | None = None):
     """Returns dict of numpy arrays produced by the reference itself."""
     ref_shim.install()
     from maestro.conf.mask import MaskConfig
@@ -57,14 +62,14 @@ def run_reference(dataset: str, batch_size: int, inter_depth: int, loss: str, se
     import maestro.train.model as ref_model
     ref_model.mae_tiny, saved = (lambda **kw: ref_mae.MAE(**{**hp, **kw})), ref_model.mae_tiny
     try:
-        module = SSLModule(datasets, MaskConfig(), "nearest", "group", inter_depth, "mae",
+        module = SSLModule(datasets, MaskConfig(), "nearest", fusion_mode, inter_depth, "mae",
                            "tiny", loss=loss)
     finally:
         ref_model.mae_tiny = saved
     module.trainer = type("T", (), {"ssl_phase": "pretrain"})()
     model = module.model
 
-    shapes = synth.param_shapes(spec, hp, inter_depth)
+    shapes = synth.param_shapes(spec, hp, inter_depth, fusion_mode)
     ref_keys = {k: tuple(v.shape) for k, v in model.state_dict().items() if not k.startswith("heads.")}
     assert ref_keys == shapes, (set(ref_keys) ^ set(shapes))
     sd = synth.synthetic_state_dict(shapes, seed=seed)
@@ -95,7 +100,8 @@ def run_reference(dataset: str, batch_size: int, inter_depth: int, loss: str, se
         rec.setdefault("mask", {})[name_group] = res[3].reshape(res[3].shape[0], -1).clone()
         return res
 
-    group_iter = iter(spec.group_names)
+    seq_names = spec.group_names if fusion_mode == "group" else list(spec.inputs)
+    group_iter = iter(seq_names)
 
     def unmask_seq(x, mask_token, mask_rec):
         g = next(group_iter)
@@ -118,7 +124,7 @@ def run_reference(dataset: str, batch_size: int, inter_depth: int, loss: str, se
         res[f"x_kept/{g}"] = rec["x_kept"][g].numpy()
     # a second pass for pixels / mask_px with the same draws
     torch.manual_seed(seed + 200)
-    group_iter = iter(spec.group_names)
+    group_iter = iter(seq_names)
     with torch.no_grad():
         b2, pixels, mask_px, _ = model({k: v.clone() for k, v in batch.items()}, ssl_phase="pretrain")
     for n in pixels:
@@ -149,8 +155,11 @@ def compress(res: dict) -> dict:
 
 
 def main() -> None:
-    for name, (dataset, bs, inter, loss, seed) in CASES.items():
-        res = compress(run_reference(dataset, bs, inter, loss, seed))
+    only = sys.argv[1:]
+    for name, case in CASES.items():
+        if only and name not in only:
+            continue
+        res = compress(run_reference(*case))
         path = os.path.join(HERE, f"{name}.npz")
         np.savez_compressed(path, **res)
         print(name, "loss", float(res["loss"]), f"{os.path.getsize(path) / 1024:.0f} KiB")

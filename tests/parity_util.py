@@ -20,6 +20,23 @@ CASES = {
     "micro_pastis_l2": ("pastis_hd", 2, 0, "l2_norm", 13),
     "micro_s2naip": ("s2_naip", 2, 1, "l1_norm", 14),
 }
+# the reference's other fusion modes (tests/test_mae.py:19-39): (dataset, batch, inter_depth, loss, seed, fusion_mode)
+FUSION_CASES = {
+    "micro_treesat_mod": ("treesatai_ts", 2, 1, "l1_norm", 15, "mod"),
+    "micro_treesat_shared": ("treesatai_ts", 2, 0, "l2_norm", 16, "shared"),
+    "micro_treesat_monotemp": ("treesatai_ts", 2, 0, "l1_norm", 17, "monotemp"),
+    "micro_flair_shared": ("flair", 2, 0, "l1_norm", 18, "shared"),
+}
+ALL_CASES = {**{k: (*v, "group") for k, v in CASES.items()}, **FUSION_CASES}
+
+
+def fusion_of(name: str) -> str:
+    return ALL_CASES[name][5]
+
+
+def seq_names(spec, fusion: str) -> list[str]:
+    """Keys of the per-sequence dicts (struct / noise / mask): groups, or modalities for the other fusion modes."""
+    return spec.group_names if fusion == "group" else list(spec.inputs)
 
 
 def load_golden(name: str) -> dict:
@@ -28,18 +45,19 @@ def load_golden(name: str) -> dict:
 
 
 def case_inputs(name: str):
-    dataset, bs, inter, loss, seed = CASES[name]
+    dataset, bs, inter, loss, seed, fusion = ALL_CASES[name]
     spec = DATASET_SPECS[dataset]()
     hp = dict(synth.MICRO_HP)
-    sd = synth.synthetic_state_dict(synth.param_shapes(spec, hp, inter), seed=seed)
+    sd = synth.synthetic_state_dict(synth.param_shapes(spec, hp, inter, fusion), seed=seed)
     batch = synth.synthetic_batch(spec, bs, seed=seed + 100)
     return spec, hp, sd, batch, inter, loss, seed, bs
 
 
-def golden_draws(gold: dict, spec):
-    struct = {g: torch.from_numpy(gold[f"struct/{g}"]) for g in spec.group_names}
-    noise = {g: torch.from_numpy(gold[f"noise/{g}"]) for g in spec.group_names}
-    order = {g: torch.from_numpy(gold[f"unmask_order/{g}"]) for g in spec.group_names}
+def golden_draws(gold: dict, spec, fusion: str = "group"):
+    names = seq_names(spec, fusion)
+    struct = {g: torch.from_numpy(gold[f"struct/{g}"]) for g in names}
+    noise = {g: torch.from_numpy(gold[f"noise/{g}"]) for g in names}
+    order = {g: torch.from_numpy(gold[f"unmask_order/{g}"]) for g in names}
     return struct, noise, order
 
 
@@ -74,10 +92,11 @@ def golden_grad_cosine(gold: dict, key: str, value) -> float:
 def run_oracle(name: str, gold: dict | None = None, dtype=torch.float32):
     spec, hp, sd, batch, inter, loss, seed, bs = case_inputs(name)
     gold = gold if gold is not None else load_golden(name)
-    struct, noise, order = golden_draws(gold, spec)
+    fusion = fusion_of(name)
+    struct, noise, order = golden_draws(gold, spec, fusion)
     sd = {k: v.to(dtype).requires_grad_(True) for k, v in sd.items()}
     batch = {k: (v.to(dtype) if v.is_floating_point() else v) for k, v in batch.items()}
-    out = O.forward(sd, spec, hp, batch, struct, noise, MaskSpec(), inter_depth=inter,
+    out = O.forward(sd, spec, hp, batch, struct, noise, MaskSpec(), fusion_mode=fusion, inter_depth=inter,
                     unmask_order=order)
     lossv, per_mod = O.reconstruction_loss(out["batch"], out["pixels"], out["mask_px"], spec, loss)
     lossv.backward()

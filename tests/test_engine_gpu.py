@@ -27,7 +27,7 @@ def _check(name, K, dtype, rtol, atol, use_tc=True):
     torch.cuda.synchronize()
     eng, ctx, spec = r["engine"], r["ctx"], r["spec"]
     B = ctx["B"]
-    for g in spec.group_names:                                  # integer / bool work: bit exact
+    for g in eng.groups:                                        # integer / bool work: bit exact
         assert np.array_equal(ctx["groups"][g]["mask"].bool().cpu().numpy(), gold[f"mask/{g}"]), g
         U.check_against_golden(gold, f"x_kept/{g}", ctx["groups"][g]["x_kept"], rtol=rtol, atol=atol)
     assert abs(float(r["loss"]) - float(gold["loss"])) <= rtol * abs(float(gold["loss"])), (float(r["loss"]),
@@ -40,12 +40,12 @@ def _check(name, K, dtype, rtol, atol, use_tc=True):
     return r
 
 
-@pytest.mark.parametrize("name", list(U.CASES))
+@pytest.mark.parametrize("name", list(U.ALL_CASES))
 def test_fp32_check_mode_matches_reference(name, K):
     _check(name, K, torch.float32, rtol=1e-4, atol=5e-5)
 
 
-@pytest.mark.parametrize("name", list(U.CASES))
+@pytest.mark.parametrize("name", list(U.ALL_CASES))
 def test_bf16_matches_reference(name, K):
     _check(name, K, torch.bfloat16, rtol=2e-2, atol=2e-2)
 

@@ -125,7 +125,8 @@ def test_cuda_argsort_tie_order_of_unmask_seq():
     masked half comes out ascending, 'own mask token per position' (the product default of ``mb_unmask_fwd``) IS the
     reference's GPU result."""
     gen = torch.Generator().manual_seed(0)
-    lengths = [18, 25, 36, 50, 64, 72, 100, 128, 144, 200, 225, 256, 400, 441, 512, 576, 1024, 2048]
+    lengths = [4, 9, 16, 18, 25, 31, 32, 33, 36, 50, 64, 72, 100, 128, 144, 200, 225, 256, 400, 441, 512, 576, 1024,
+               2048]
     non_ascending = []
     for L in lengths:
         nm = round(0.75 * L)
@@ -156,6 +157,9 @@ def test_cuda_argsort_tie_order_of_unmask_seq():
         with open(os.path.join(out, "argsort_tie_probe.json"), "w") as f:
             json.dump({"torch": torch.__version__, "device": torch.cuda.get_device_name(0), "lengths": lengths,
                        "descending_masked_half_non_ascending": non_ascending, "default_vs_stable_differs": unstable}, f)
-    assert unstable == [], unstable
-    # measured on B200 / torch 2.11: see DESIGN.md section 2 ("Tie-breaking"); the assertion pins that finding
-    assert non_ascending == [], non_ascending
+    assert all(L <= 32 for L in unstable), unstable
+    # measured on B200 / torch 2.11 ("Tie-breaking"): ATen sorts rows of up to 32 elements with a
+    # bitonic network (not stable) and longer rows with a stable radix / merge sort.  Every sequence of the BASELINE
+    # configs in fusion mode "group" is longer than 32 tokens, so there the stable definition IS the reference's CUDA
+    # result; the assertions pin that finding.
+    assert all(L <= 32 for L in non_ascending), non_ascending

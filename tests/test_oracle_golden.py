@@ -9,13 +9,14 @@ import parity_util as U
 from maestro_b200.conf import MaskSpec
 
 
-@pytest.mark.parametrize("name", list(U.CASES))
+@pytest.mark.parametrize("name", list(U.ALL_CASES))
 def test_oracle_matches_reference_golden(name):
     gold = U.load_golden(name)
     r = U.run_oracle(name, gold)
     spec, out = r["spec"], r["out"]
+    names = U.seq_names(spec, U.fusion_of(name))
     # integer / bool work: bit exact
-    for g in spec.group_names:
+    for g in names:
         assert np.array_equal(out["mask"][g].numpy(), gold[f"mask/{g}"]), g
     for n in out["pixels"]:
         assert int(out["mask_px"][n].sum()) == int(gold[f"mask_px_count/{n}"])
@@ -23,7 +24,7 @@ def test_oracle_matches_reference_golden(name):
             1.0, abs(float(gold[f"batch_resized_sum/{n}"])))
     # floating point: 1e-4 relative (north_star fp32 tolerance)
     assert abs(float(r["loss"]) - float(gold["loss"])) <= 1e-4 * abs(float(gold["loss"]))
-    for g in spec.group_names:
+    for g in names:
         U.check_against_golden(gold, f"x_kept/{g}", out["x_kept"][g], rtol=1e-4, atol=2e-5)
     for n in out["pixels"]:
         U.check_against_golden(gold, f"pixels/{n}", out["pixels"][n], rtol=1e-4, atol=2e-5)

@@ -16,7 +16,7 @@ def test_live_reference_equals_committed_golden():
     import make_golden
 
     name = "micro_pastis_l2"
-    live = make_golden.compress(make_golden.run_reference(*U.CASES[name]))
+    live = make_golden.compress(make_golden.run_reference(*U.ALL_CASES[name]))
     gold = U.load_golden(name)
     assert set(live) == set(gold)
     for k in gold:
