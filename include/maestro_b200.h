@@ -194,6 +194,29 @@ int mb_struct_mask(const mb_struct_params* params, unsigned char* out, int* pass
 int mb_adamw_step(float* p, float* g, float* m, float* v, void* shadow, const float* hyper, size_t n, int zero_grad,
                   void* stream);
 
+/* BaseModule.update_ema, maestro/train/base.py:263-274, over the flat arena: ema = momentum * ema + one_minus * param
+ * (one_minus = float(1.0 - momentum), formed in double on the host as the reference does). */
+int mb_ema_update(float* ema, const float* param, size_t n, float momentum, float one_minus, void* stream);
+
+/* ---- probe / finetune heads -------------------------------------------------------------------- */
+/* AttentiveReduce, maestro/layers/head.py:28-64: one learned query per head over each of S sequences of L tokens.
+ * kv [S, L, 2*H*dh] (to_kv output: k then v), q [H*dh] fp32, out [S, H*dh], probs [S, H, L] fp32 (saved). */
+int mb_attn_pool_fwd(const void* kv, const float* q, void* out, float* probs, int dtype, int S, int L, int H, int dh,
+                     float scale, void* stream);
+/* Its backward: dkv [S, L, 2*H*dh] is fully written, dq [H*dh] fp32 accumulates. */
+int mb_attn_pool_bwd(const void* kv, const float* q, const float* probs, const void* dout, void* dkv, float* dq,
+                     int dtype, int S, int L, int H, int dh, float scale, void* stream);
+/* BaseMIM.compute_logits, maestro/ssl/mim.py:353-372: F.interpolate(bilinear) of channel-last token grids
+ * x [n_img, hi*wi, d] -> out [n_img, ho*wo, d] (image n at x + n*in_bs / out + n*out_bs elements) through dense 1-D
+ * weight matrices Wy [ho, hi], Wx [wo, wi]; the backward is the same call with the transposed matrices. */
+int mb_token_resample(const void* x, const float* Wy, const float* Wx, void* out, int dtype, int n_img, int hi, int wi,
+                      int ho, int wo, int d, long long in_bs, long long out_bs, void* stream);
+/* BaseModule.compute_loss_pred, maestro/train/base.py:98-151 (F.cross_entropy over rows whose target is not the
+ * missing value): logits (n, c) at (n / inner) * outer_stride + c * class_stride + n % inner; accum[0] += sum of row
+ * losses, accum[1] += rows counted; dlogits (may be NULL) = softmax - onehot (0 for skipped rows). */
+int mb_xent_fwd_bwd(const float* logits, const long long* target, float* dlogits, double* accum, long long N, int C,
+                    long long inner, long long class_stride, long long outer_stride, long long missing, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

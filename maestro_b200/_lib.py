@@ -16,7 +16,7 @@ HERE = Path(__file__).resolve().parent
 CSRC = HERE / "csrc"
 SO_PATH = HERE / "libmaestro_b200.so"
 SOURCES = ["elementwise.cu", "norm.cu", "mask.cu", "unmask.cu", "loss.cu", "gemm_simt.cu", "gemm_tc.cu",
-           "tmap.cu", "attn_tc.cu", "attn_bwd_tc.cu", "optim.cu", "input.cu"]
+           "tmap.cu", "attn_tc.cu", "attn_bwd_tc.cu", "optim.cu", "input.cu", "head.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"]
 
@@ -176,4 +176,5 @@ EXPORTS = [
     "mb_mask_indices", "mb_gather_rows", "mb_scatter_kept", "mb_unmask_fwd", "mb_masktoken_grad",
     "mb_loss_fwd_bwd", "mb_gemm_simt", "mb_softmax_rows", "mb_softmax_bwd_rows", "mb_gemm_tc", "mb_gemm_tc_grouped",
     "mb_adamw_step", "mb_attn_fwd", "mb_attn_bwd", "mb_raster_transform", "mb_struct_mask", "mb_resize",
+    "mb_ema_update", "mb_attn_pool_fwd", "mb_attn_pool_bwd", "mb_token_resample", "mb_xent_fwd_bwd",
 ]

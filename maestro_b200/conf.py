@@ -61,11 +61,29 @@ class ModalitySpec:
 
 
 @dataclass
+class TargetSpec:
+    """What the heads read of a reference ``TargetConfig`` / ``TargetRasterConfig`` (conf/dataset/utils.py:49-75;
+    ssl/mim.py:169-197).  ``image_size`` (raster targets only) = round(crop_meters / resolution_meters)."""
+
+    name: str
+    type_target: str                # "segment" | "classif" | "multilabel_classif"
+    num_classes: int
+    missing_val: int = -1
+    image_size: int | None = None   # px of a raster target; None for per-sample targets
+
+    @property
+    def is_raster(self) -> bool:
+        return self.image_size is not None
+
+
+@dataclass
 class DatasetSpec:
     name: str
     inputs: dict[str, ModalitySpec]
     grid_pos_enc: int | None = None
     log_inputs: list[str] = field(default_factory=list)
+    targets: dict[str, TargetSpec] = field(default_factory=dict)
+    ref_input: str | None = None    # modality whose token grid carries raster targets (ssl/mim.py:171-197, 350-372)
 
     @property
     def groups(self) -> list[tuple[str, str]]:
@@ -116,11 +134,19 @@ def spec_from_reference(datasets) -> DatasetSpec:
             name_group=mod.name_group,
             name_embed=mod.name_embed,
         )
+    targets = {}
+    for name, t in (getattr(ds, "targets", None) or {}).items():
+        res = getattr(t, "resolution_meters", None)
+        raster = hasattr(t, "bands") and res is not None           # isinstance(target, RasterConfig), ssl/mim.py:171
+        targets[name] = TargetSpec(name, str(t.type_target), int(t.num_classes), int(t.missing_val),
+                                   round(ds.crop_meters / res) if raster else None)
     return DatasetSpec(
         name=getattr(datasets, "name_dataset", getattr(ds, "name", "custom")),
         inputs=inputs,
         grid_pos_enc=ds.grid_pos_enc,
         log_inputs=list(getattr(ds, "log_inputs", [])),
+        targets=targets,
+        ref_input=getattr(ds, "ref_input", None),
     )
 
 
@@ -130,6 +156,8 @@ def flair_spec() -> DatasetSpec:
         name="flair",
         grid_pos_enc=160,
         log_inputs=["aerial"],
+        targets={"cosia": TargetSpec("cosia", "segment", 15, -1, 512)},       # flair.py:42-44, 113-118 (102.4 m / 0.2 m)
+        ref_input="aerial",
         inputs={
             "aerial": ModalitySpec("aerial", 512, 16, [4], norm_bands=[1, 3]),
             "dem": ModalitySpec("dem", 512, 32, [2], rescale_elev=True),
@@ -148,6 +176,7 @@ def treesatai_ts_spec() -> DatasetSpec:
         name="treesatai_ts",
         grid_pos_enc=96,
         log_inputs=["aerial"],
+        targets={"treesat_mlc_thresh": TargetSpec("treesat_mlc_thresh", "multilabel_classif", 15, -1)},   # :29-31, 88-92
         inputs={
             "aerial": ModalitySpec("aerial", 300, 20, [4], norm_bands=[1, 3]),
             "s2": ModalitySpec("s2", 6, 2, [10], num_dates=16, norm_bands=[4, 4, 2]),
@@ -184,6 +213,8 @@ def pastis_hd_spec() -> DatasetSpec:
         name="pastis_hd",
         grid_pos_enc=256,
         log_inputs=["spot"],
+        targets={"pastis_seg": TargetSpec("pastis_seg", "segment", 19, 19, 16)},   # pastis_hd.py:32-34 (160 m / 10 m)
+        ref_input="s2",
         inputs={
             "spot": ModalitySpec("spot", 160, 16, [3]),
             "s2": ModalitySpec("s2", 16, 2, [10], num_dates=16, norm_bands=[4, 4, 2]),

@@ -45,26 +45,71 @@ def reshape_encoding(encoding: torch.Tensor, grid_size: int) -> torch.Tensor:
     return table.reshape(grid_size, k, grid_size, k, dim).mean(dim=(1, 3)).reshape(grid_size * grid_size, dim)
 
 
+def _flatten_dim(fusion_mode: str) -> int:
+    """Axis the date dimension is folded into (layers/utils.py:26-35): the batch for "shared" / "monotemp" (and the
+    croma baselines), the token axis for "mod" / "group"."""
+    if fusion_mode in ("shared", "monotemp", "late-croma", "inter-croma"):
+        return 0
+    if fusion_mode in ("mod", "group"):
+        return 1
+    raise ValueError(f"Invalid fusion mode {fusion_mode}.")
+
+
 def group_mods(x: dict, fusion_mode: str, groups: list[tuple[str, str]]) -> dict:
-    """Concatenate per-modality token tensors [B, D, L, ...] into per-group [B, sum(D*L), ...]."""
-    if fusion_mode not in ("group", "mod"):
-        raise NotImplementedError(fusion_mode)
+    """Group modality sequences (layers/utils.py:12-47): per-modality [B, D, L, ...] -> "group": per group
+    [B, sum(D * L), ...] (modalities concatenated along tokens in ``groups`` order); "mod": per modality
+    [B, D * L, ...]; "shared" / "monotemp": per modality [(B D), L, ...]."""
+    dim = _flatten_dim(fusion_mode)
+    flat = {name: t.flatten(dim, dim + 1) for name, t in x.items()}
+    if fusion_mode != "group":
+        return flat
     out: dict = {}
     for name_mod, name_group in groups:
-        key = name_group if fusion_mode == "group" else name_mod
-        out.setdefault(key, []).append(x[name_mod].flatten(1, 2))
+        out.setdefault(name_group, []).append(flat[name_mod])
     return {k: torch.cat(v, dim=1) for k, v in out.items()}
 
 
 def ungroup_mods(x: dict, fusion_mode: str, groups: list[tuple[str, str]], num_dates: dict, grid_size: dict) -> dict:
-    """Inverse of :func:`group_mods`."""
-    if fusion_mode not in ("group", "mod"):
-        raise NotImplementedError(fusion_mode)
-    out, cursor = {}, {}
-    for name_mod, name_group in groups:
-        key = name_group if fusion_mode == "group" else name_mod
-        n = num_dates[name_mod] * grid_size[name_mod] ** 2
-        o = cursor.get(key, 0)
-        out[name_mod] = x[key][:, o:o + n].unflatten(1, (num_dates[name_mod], -1))
-        cursor[key] = o + n
+    """Inverse of :func:`group_mods` (layers/utils.py:50-100): back to per-modality [B, D, L, ...]."""
+    dim = _flatten_dim(fusion_mode)
+    if fusion_mode == "group":
+        out, cursor = {}, {}
+        for name_mod, name_group in groups:
+            n = num_dates[name_mod] * grid_size[name_mod] ** 2
+            o = cursor.get(name_group, 0)
+            out[name_mod] = x[name_group][:, o:o + n]
+            cursor[name_group] = o + n
+    else:
+        out = dict(x)
+    for name_mod in out:
+        if dim == 0:
+            out[name_mod] = out[name_mod].unflatten(0, (-1, num_dates[name_mod]))
+        else:
+            out[name_mod] = out[name_mod].unflatten(1, (num_dates[name_mod], -1))
     return out
+
+
+def encode_dates(dates: torch.Tensor, ref_date: torch.Tensor, dim: int, date_dim: int, fac_date_enc: float,
+                 grid_size: int, len_bands: int) -> torch.Tensor:
+    """Encode day of year, hour of day and difference to the reference date (layers/utils.py:128-173):
+    int16 (year, doy, hour) [B, D, 3] + ref_date [B, 1, 3] -> [B, len_bands * D, grid_size^2, dim] whose last
+    ``date_dim`` channels are [diff] * (date_dim - 4) + [sin doy, cos doy, sin hour, cos hour], times ``fac_date_enc``.
+
+    The features come from the ``date_features`` kernel (same fp32 operation order as the reference); inside the
+    pretraining step this tensor is never materialised (the add is fused into ``mb_gn_apply`` / ``mb_unmask_fwd``)."""
+    from .. import torch_ops as T
+    feat = T.date_features(dates, ref_date) * fac_date_enc                              # [B, D, 5]
+    B, D, _ = feat.shape
+    enc = torch.cat([feat.new_zeros(B, D, dim - date_dim), feat[..., :1].expand(-1, -1, date_dim - 4), feat[..., 1:]], -1)
+    enc = enc[:, :, None, :].expand(-1, -1, grid_size * grid_size, -1)
+    if len_bands == 1:
+        return enc
+    return enc[:, None].expand(-1, len_bands, -1, -1, -1).flatten(1, 2)
+
+
+def interp_matrix(n_in: int, n_out: int, mode: str = "bilinear") -> torch.Tensor:
+    """Dense [n_out, n_in] matrix of F.interpolate's 1-D weights (align_corners=False): column i is the response to the
+    i-th unit vector, so the product reproduces F.interpolate exactly (used for the token-grid resampling of
+    BaseMIM.compute_logits, ssl/mim.py:353-372; 2-D bilinear interpolation is separable)."""
+    eye = torch.eye(n_in, dtype=torch.float32)[None]                                    # [1, n_in(channels), n_in]
+    return F.interpolate(eye, size=n_out, mode="linear" if mode == "bilinear" else mode, align_corners=False)[0].t().contiguous()

@@ -302,6 +302,41 @@ class Kernels:
         _ck(self.L.mb_adamw_step(_p(p), _p(g), _p(m), _p(v), _p(shadow), _p(hyper), C.c_size_t(p.numel()),
                                  int(zero_grad), self._s()), "adamw_step")
 
+    def ema_update(self, ema, param, momentum):
+        """ema = momentum * ema + (1 - momentum) * param over flat fp32 buffers (train/base.py:263-274)."""
+        if ema.numel() != param.numel():
+            raise ValueError("ema_update: buffers of different size")
+        self.launches += 1
+        _ck(self.L.mb_ema_update(_p(ema), _p(param), C.c_size_t(ema.numel()), C.c_float(momentum),
+                                 C.c_float(1.0 - momentum), self._s()), "ema_update")
+
+    # ------------------------------------------------------------------ probe / finetune heads
+    def attn_pool_fwd(self, kv, q, out, probs, heads, scale):
+        S, L, C2 = kv.shape
+        self.launches += 1
+        _ck(self.L.mb_attn_pool_fwd(_p(kv), _p(q), _p(out), _p(probs), _dt(kv), S, L, heads, C2 // 2 // heads,
+                                    C.c_float(scale), self._s()), "attn_pool_fwd")
+
+    def attn_pool_bwd(self, kv, q, probs, dout, dkv, dq, heads, scale):
+        S, L, C2 = kv.shape
+        self.launches += 1
+        _ck(self.L.mb_attn_pool_bwd(_p(kv), _p(q), _p(probs), _p(dout), _p(dkv), _p(dq), _dt(kv), S, L, heads,
+                                    C2 // 2 // heads, C.c_float(scale), self._s()), "attn_pool_bwd")
+
+    def token_resample(self, x, Wy, Wx, out, n_img, in_bs, out_bs):
+        """out[n, (oy ox), :] = sum Wy[oy, iy] Wx[ox, ix] x[n, (iy ix), :]; x / out may be strided views (bs in elements)."""
+        ho, hi = Wy.shape
+        wo, wi = Wx.shape
+        self.launches += 1
+        _ck(self.L.mb_token_resample(_p(x), _p(Wy), _p(Wx), _p(out), _dt(x), n_img, hi, wi, ho, wo, x.shape[-1],
+                                     C.c_longlong(in_bs), C.c_longlong(out_bs), self._s()), "token_resample")
+
+    def xent_fwd_bwd(self, logits, target, dlogits, accum, N, Cn, inner, class_stride, outer_stride, missing):
+        self.launches += 1
+        _ck(self.L.mb_xent_fwd_bwd(_p(logits), _p(target), _p(dlogits), _p(accum), C.c_longlong(N), Cn,
+                                   C.c_longlong(inner), C.c_longlong(class_stride), C.c_longlong(outer_stride),
+                                   C.c_longlong(missing), self._s()), "xent_fwd_bwd")
+
     # ------------------------------------------------------------------ device-side input pipeline
     def raster_transform(self, raw, out, aug, imgs_per_sample, norm_fac, log_scale):
         """raw [n_img, C, H, W] (uint8 / int16 / uint16 / float32) -> out fp32 (dataset.py:215-257 on the device)."""

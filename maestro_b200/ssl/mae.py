@@ -18,7 +18,15 @@ from torch import nn
 from ..conf import MODEL_SIZES, MaskSpec, spec_from_reference
 from ..engine import PretrainEngine
 from ..layers.embed import Patchify, Pixelify
+from ..layers.head import ClassificationHead, PixelifyHead
+from ..layers.utils import group_mods, interp_matrix, ungroup_mods
 from .vit import Transformer
+
+
+def _on(device: torch.device):
+    """Make the engine's device current for the launches (kernels go to the calling thread's current device)."""
+    import contextlib
+    return torch.cuda.device(device) if device.type == "cuda" else contextlib.nullcontext()
 
 
 def _mask_spec(mask) -> MaskSpec:
@@ -28,8 +36,46 @@ def _mask_spec(mask) -> MaskSpec:
                                                      "mask_dates", "mask_loc")})
 
 
+def _prepare_grads(module, eng) -> None:
+    """Gradient contract of the arena (``module.grad_mode == "alias"``): ``param.grad`` IS a view of the engine's flat
+    gradient arena and the backward kernels accumulate into it (torch semantics: backward adds to ``.grad``).  A
+    parameter whose ``.grad`` is ``None`` was reset by ``optimizer.zero_grad()`` (``set_to_none=True``, the default):
+    its arena range still holds the previous step's gradient and is cleared here before the kernels accumulate."""
+    params = dict(module.named_parameters())
+    stale = [n for n in module._bound_names if params[n].grad is None]
+    if len(stale) == len(module._bound_names):
+        if eng.grads_dirty:
+            eng.zero_grad()
+    else:
+        for n in stale:
+            eng.G[n].zero_()
+
+
+def _publish_grads(module, eng, only=None) -> None:
+    params = dict(module.named_parameters())
+    for n in module._bound_names:
+        if only is not None and not n.startswith(only):
+            continue
+        p, g = params[n], eng.G[n]
+        if p.grad is None:
+            p.grad = g
+        elif p.grad.data_ptr() != g.data_ptr():       # a foreign gradient tensor: fold the arena into it
+            p.grad.add_(g)
+            g.zero_()
+
+
+def _param_grads(module, eng, only=None):
+    """What the autograd node returns for the parameters: nothing in "alias" mode (``.grad`` already aliases the
+    arena -- no 1.3 GB copy per step), the arena views in "autograd" mode (torch accumulates / DDP hooks fire).
+    ``only``: name prefixes of the parameters this backward reaches (the others keep ``grad = None``, as in torch)."""
+    if module.grad_mode == "alias":
+        _publish_grads(module, eng, only)
+        return tuple(None for _ in module._bound_names)
+    return tuple(eng.G[n] if (only is None or n.startswith(only)) else None for n in module._bound_names)
+
+
 class _PretrainFn(torch.autograd.Function):
-    """pixels_rec = MAE(batch); backward consumes d(pixels_rec) and returns every parameter gradient."""
+    """pixels_rec = MAE(batch); backward consumes d(pixels_rec) and fills every parameter gradient."""
 
     @staticmethod
     def forward(ctx, module, batch, draws, *params):  # noqa: ANN001, ANN205
@@ -53,22 +99,54 @@ class _PretrainFn(torch.autograd.Function):
         module, sctx = ctx.module, ctx.sctx
         eng = module._eng
         B = sctx["B"]
-        for (name, mt), dimg in zip(eng.mods.items(), dimgs):
-            mc = sctx["mods"][name]
-            mc["dpred"] = []
-            if dimg is None:
-                dimg = torch.zeros(B, mt.D, mt.C, mt.S, mt.S, dtype=torch.float32, device=eng.device)
-            dimg = dimg.contiguous().view(B * mt.D, mt.C, mt.S, mt.S).float()
-            c0 = 0
-            for gi, c in enumerate(mt.band_groups):
-                rows = torch.empty_like(mc["pred"][gi])
-                eng.K.rows_image(rows, dimg, c0, c, mt.p, 1)
-                mc["dpred"].append(rows)
-                c0 += c
-        eng.zero_grad()
-        eng.backward(sctx)
-        grads = tuple(eng.G[n].clone() for n in module._bound_names)
-        return (None, None, None, *grads)
+        with _on(eng.device):
+            for (name, mt), dimg in zip(eng.mods.items(), dimgs):
+                mc = sctx["mods"][name]
+                mc["dpred"] = []
+                if dimg is None:
+                    dimg = torch.zeros(B, mt.D, mt.C, mt.S, mt.S, dtype=torch.float32, device=eng.device)
+                dimg = dimg.contiguous().view(B * mt.D, mt.C, mt.S, mt.S).float()
+                c0 = 0
+                for gi, c in enumerate(mt.band_groups):
+                    rows = torch.empty_like(mc["pred"][gi])
+                    eng.K.rows_image(rows, dimg, c0, c, mt.p, 1)
+                    mc["dpred"].append(rows)
+                    c0 += c
+            if module.grad_mode == "alias":
+                _prepare_grads(module, eng)
+            else:
+                eng.zero_grad()
+            eng.backward(sctx)
+            return (None, None, None, *_param_grads(module, eng))
+
+
+class _EncodeFn(torch.autograd.Function):
+    """Encoded tokens of every position (probe / finetune forward, ssl/mim.py:473-490); the backward (finetune) runs the
+    unmasked encoder backward of the engine and fills the encoder-side parameter gradients."""
+
+    @staticmethod
+    def forward(ctx, module, batch, *params):  # noqa: ANN001, ANN205
+        eng = module._eng
+        out, sctx = eng.encode(batch, save=True)
+        ctx.module, ctx.sctx = module, sctx
+        return tuple(out[g] for g in eng.groups)
+
+    @staticmethod
+    def backward(ctx, *douts):  # noqa: ANN001, ANN205
+        module, sctx = ctx.module, ctx.sctx
+        eng = module._eng
+        with _on(eng.device):
+            d = {}
+            for g, do in zip(eng.groups.values(), douts):
+                if do is None:
+                    do = torch.zeros(sctx["B"] * g.bmul, g.L, eng.E, dtype=eng.dtype, device=eng.device)
+                d[g.name] = do
+            if module.grad_mode == "alias":
+                _prepare_grads(module, eng)
+            else:
+                eng.zero_grad()
+            eng.encode_backward(sctx, d)
+            return (None, None, *_param_grads(module, eng, ("patch_embed.", "encoder.", "encoder_inter.")))
 
 
 class MAE(nn.Module):
@@ -103,7 +181,24 @@ class MAE(nn.Module):
             self.embed_to_rec[m.embed] = Pixelify(decoder_dim, list(m.band_groups), m.patch_size * self.stride)
         self.mask_token = nn.ParameterDict(
             {n: nn.Parameter(torch.randn(1, g, 1, 1, decoder_dim)) for n, g in self.len_bands.items()})
-        self.heads = nn.ModuleDict()   # probe / finetune heads are outside the pretraining path
+
+        # heads (ssl/mim.py:169-197): PixelifyHead on the reference input's token grid for raster targets,
+        # ClassificationHead over every token otherwise
+        self.heads = nn.ModuleDict()
+        for name_target, target in spec.targets.items():
+            if target.is_raster:
+                if spec.ref_input is None:
+                    msg = f"Ref input must be provided for raster target {name_target}"
+                    raise ValueError(msg)
+                ref_grid_size = self.out_grid_size[spec.ref_input]
+                if target.image_size % ref_grid_size:
+                    msg = (f"Target image size {target.image_size} "
+                           f"is not a multiple of ref input grid {ref_grid_size}")
+                    raise ValueError(msg)
+                self.heads[name_target] = PixelifyHead(type_head, embed_dim * self.stride, target.num_classes,
+                                                       target.image_size // ref_grid_size)
+            else:
+                self.heads[name_target] = ClassificationHead(type_head, embed_dim * self.stride, target.num_classes)
 
         names = spec.group_names if fusion_mode == "group" else (
             list(spec.inputs) if fusion_mode in ("mod", "monotemp") else ["shared"])
@@ -126,27 +221,35 @@ class MAE(nn.Module):
                 members = spec.group_members(g) if fusion_mode == "group" else [g]
                 n_dates = sum(spec.inputs[x].num_dates * self.len_bands[x] for x in members)
                 self.mask_ratio[g] = 1 - (1 - self.mask_cfg.mask_ratio) / (n_dates ** self.mask_cfg.mask_scale)
+        # "alias": param.grad aliases the engine's gradient arena (no copies); "autograd": gradients are handed to torch's
+        # AccumulateGrad (one clone per parameter per step; what a DistributedDataParallel wrapper's hooks need)
+        self.grad_mode = "alias"
         self._eng = None
         self._bound_names: list[str] = []
         self._versions = -1
         self._last_ctx = None
+        self._interp: dict = {}
 
     # the engine holds device arenas and a ctypes handle: never copied / pickled with the module (EMA deep copy)
     def __getstate__(self):  # noqa: ANN204
         state = self.__dict__.copy()
         state["_eng"], state["_last_ctx"], state["_bound_names"], state["_versions"] = None, None, [], -1
+        state["_interp"] = {}
         return state
 
     # ------------------------------------------------------------------ engine binding
     def _engine(self, device: torch.device) -> PretrainEngine:
-        if device.type != "cuda":
+        from .. import torch_ops
+        device = torch.device(device)
+        if device.type != "cuda" and torch_ops._PROVIDER is None:      # (a test double may stand in for the kernels)
             raise RuntimeError("maestro_b200.MAE runs on CUDA only (no CPU fallback); move the module and batch to a GPU")
+        if device.type == "cuda" and device.index is None:
+            device = torch.device("cuda", torch.cuda.current_device())
         params = dict(self.named_parameters())
         eng = self._eng
         if eng is None or eng.device != device:
-            from ..ops import Kernels
             dtype = torch.float32 if os.environ.get("MAESTRO_B200_PRECISION", "bf16") == "fp32" else torch.bfloat16
-            eng = PretrainEngine(self.spec, self.hp, self.mask_cfg, Kernels(device), device, dtype,
+            eng = PretrainEngine(self.spec, self.hp, self.mask_cfg, torch_ops.kernels(device), device, dtype,
                                  fusion_mode=self.fusion_mode, inter_depth=self.inter_depth,
                                  interpolate=self.interpolate, fac_abs_enc=self.fac_abs_enc,
                                  fac_date_enc=self.fac_date_enc)
@@ -169,6 +272,13 @@ class MAE(nn.Module):
         return eng
 
     # ------------------------------------------------------------------ reference API
+    def group(self, x: dict) -> dict:
+        return group_mods(x, self.fusion_mode, self.spec.groups)
+
+    def ungroup(self, x: dict) -> dict:
+        num_dates = {n: m.num_dates * self.len_bands[n] for n, m in self.spec.inputs.items()}
+        return ungroup_mods(x, self.fusion_mode, self.spec.groups, num_dates, self.grid_size)
+
     def mask_struct(self, batch_size: int) -> dict[str, torch.Tensor]:
         """Structural masks per group (host RNG, reference draw order, ssl/mae.py:178-226)."""
         dev = next(self.parameters()).device
@@ -181,28 +291,67 @@ class MAE(nn.Module):
         masking bypassed).  Forward only (frozen-encoder probing / feature extraction) on the same CUDA kernels as the
         pretraining step; mutates ``batch`` like ``resize_and_rescale`` does."""
         eng = self._engine(batch["ref_date"].device)
-        return {g: x.float() for g, x in eng.encode(batch).items()}
+        with _on(eng.device):
+            return {g: x.float() for g, x in eng.encode(batch).items()}
+
+    def _resample(self, x: torch.Tensor, g_in: int, g_out: int) -> torch.Tensor:
+        """F.interpolate(bilinear) of channel-last token grids [B, D, g_in^2, C] -> [B, D, g_out^2, C] (mim.py:353-372)."""
+        if g_in == g_out:
+            return x
+        key = (g_in, g_out, x.device)
+        if key not in self._interp:
+            self._interp[key] = interp_matrix(g_in, g_out).to(x.device)
+        W = self._interp[key]
+        B, D, L, C = x.shape
+        return torch.ops.maestro_b200.token_resample(x.reshape(B * D, L, C), W, W).reshape(B, D, g_out * g_out, C)
+
+    def compute_logits(self, x_enc: dict, ssl_phase: str) -> dict[str, torch.Tensor]:
+        """BaseMIM.compute_logits (ssl/mim.py:343-394): per-modality token grids resampled to the reference input's grid
+        and stacked along the date axis for raster ("segment") targets, every token of every modality concatenated for
+        per-sample targets; one head per target."""
+        x_enc = self.ungroup(dict(x_enc))
+        spec = self.spec
+        x_ref = None
+        if spec.ref_input is not None:
+            g_ref = self.out_grid_size[spec.ref_input]
+            x_ref = torch.cat([self._resample(x, self.out_grid_size[n], g_ref) for n, x in x_enc.items()], dim=1)
+        x_all = torch.cat([x.flatten(1, 2) for x in x_enc.values()], dim=1)
+        logits = {}
+        for name_target, target in spec.targets.items():
+            if target.type_target == "segment":
+                logits[name_target] = self.heads[name_target](x_ref, ssl_phase=ssl_phase)
+            elif target.type_target in ("multilabel_classif", "classif"):
+                logits[name_target] = self.heads[name_target](x_all, ssl_phase=ssl_phase)
+        return logits
 
     def forward(self, batch: dict, ssl_phase: str = "pretrain", struct=None, noise=None, unmask_order=None):
-        if ssl_phase != "pretrain":
-            raise NotImplementedError("probe / finetune forward: compute_logits + heads are outside the B200 "
-                                      "pretraining path (DESIGN.md 'out of scope'); encode_features(batch) returns "
-                                      "the encoder output compute_logits consumes")
+        """``(batch, pixels_rec, mask_rec, None)`` for "pretrain", ``(batch, None, None, logits)`` for "probe" /
+        "finetune" (ssl/mim.py:473-505)."""
         dev = batch["ref_date"].device
         eng = self._engine(dev)
         params = dict(self.named_parameters())
         plist = [params[n] for n in self._bound_names]
-        images = _PretrainFn.apply(self, batch, (struct, noise, unmask_order), *plist)
-        sctx = self._last_ctx
-        B = sctx["B"]
-        pixels_rec, mask_rec = {}, {}
-        for img, (name, mt) in zip(images, eng.mods.items()):
-            pixels_rec[name] = img
-            tm = sctx["groups"][mt.group]["mask"][:, mt.tok_off:mt.tok_off + mt.G * mt.D * mt.L].bool()
-            tm = tm.view(B, mt.G, mt.D, mt.grid, mt.grid)
-            tm = tm.repeat_interleave(mt.p, -2).repeat_interleave(mt.p, -1)
-            mask_rec[name] = torch.cat([tm[:, gi, :, None].expand(-1, -1, c, -1, -1)
-                                        for gi, c in enumerate(mt.band_groups)], dim=2)
+        with _on(eng.device):
+            if ssl_phase != "pretrain":
+                if ssl_phase == "probe" or not torch.is_grad_enabled():      # frozen encoder: no activations kept
+                    with torch.no_grad():
+                        feats = eng.encode(batch)
+                else:
+                    feats = dict(zip(eng.groups, _EncodeFn.apply(self, batch, *plist)))
+                self._versions = sum(params[n]._version for n in self._bound_names)
+                return batch, None, None, self.compute_logits(feats, ssl_phase)
+            images = _PretrainFn.apply(self, batch, (struct, noise, unmask_order), *plist)
+            sctx = self._last_ctx
+            B = sctx["B"]
+            pixels_rec, mask_rec = {}, {}
+            for img, (name, mt) in zip(images, eng.mods.items()):
+                pixels_rec[name] = img
+                g = eng.groups[mt.group]
+                tm = sctx["groups"][mt.group]["mask"].view(B, g.Lt)[:, mt.tok_off:mt.tok_off + mt.G * mt.D * mt.L].bool()
+                tm = tm.view(B, mt.G, mt.D, mt.grid, mt.grid)
+                tm = tm.repeat_interleave(mt.p, -2).repeat_interleave(mt.p, -1)
+                mask_rec[name] = torch.cat([tm[:, gi, :, None].expand(-1, -1, c, -1, -1)
+                                            for gi, c in enumerate(mt.band_groups)], dim=2)
         self._versions = sum(params[n]._version for n in self._bound_names)
         return batch, pixels_rec, mask_rec, None
 

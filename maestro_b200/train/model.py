@@ -1,59 +1,30 @@
-"""``SSLModule`` pretraining glue with the method names of maestro/train/model.py (compute_loss_rec :195-247,
-compute_logs_rec :160-193, pretrain_step :249-274) on the fused kernels.
+"""``SSLModule`` with the method names and return contracts of the reference LightningModule (maestro/train/model.py:
+compute_loss_rec :195-247, compute_logs_rec :160-193, pretrain_step :249-274, configure_optimizers :120-158;
+maestro/train/base.py: compute_loss_pred :98-151, probe_or_finetune_step :189-222, update_ema :263-274) on the fused
+kernels.  Everything Lightning-specific (logging, metrics objects, trainer hooks) stays with the host framework: this
+class is a plain ``nn.Module`` whose methods a ``LightningModule`` forwards to.
 
 ``compute_loss_rec`` keeps the reference's image-layout signature (``pixels_rec[mod]`` fp32 [B,D,C,H,W],
-``mask_rec[mod]`` bool [B,D,C,H,W]) and is one autograd node around the group-norm masked loss kernel
-(csrc/loss.cu).  ``pretrain_step_fused`` is the production path: it never materialises image-layout
-predictions or pixel masks -- the loss kernel consumes the prediction rows and the token mask directly.
+``mask_rec[mod]`` bool [B,D,C,H,W]) and is one custom op (``maestro_b200::masked_group_norm_loss``) per modality.
+``pretrain_step_fused`` is the production path: forward + loss + backward as CUDA-graph replays of the engine's launch
+schedule (captured lazily per batch shape), the gradient all-reduce ranges overlapped with the backward segments when
+``torch.distributed`` is initialised, no image-layout predictions, no pixel masks, no gradient copies.
 """
 
 from __future__ import annotations
+
+import copy
 
 import torch
 from torch import nn
 
 from ..conf import spec_from_reference
-from ..ssl.mae import mae_large, mae_medium, mae_small, mae_tiny
-
-
-class _LossRecFn(torch.autograd.Function):
-    @staticmethod
-    def forward(ctx, K, spec_mod, target, pred_img, mask_img, norm_bands, l2):  # noqa: ANN001, ANN205
-        B, D, C, S, _ = target.shape
-        p, g = spec_mod.patch_size, spec_mod.grid
-        L, bands = g * g, list(spec_mod.band_groups)
-        dev = target.device
-        img = pred_img.detach().contiguous().view(B * D, C, S, S).float()
-        rows, c0, toks = [], 0, []
-        for c in bands:
-            r = torch.empty(B * D * L, c * p * p, dtype=torch.float32, device=dev)
-            K.rows_image(r, img, c0, c, p, 1)
-            rows.append(r)
-            toks.append(mask_img[:, :, c0, ::p, ::p].reshape(B, D * L))
-            c0 += c
-        tok = torch.cat(toks, 1).to(torch.uint8).contiguous()          # [B, G*D*L]
-        count = sum(float(p * p * c) * toks[i].sum() for i, c in enumerate(bands))
-        coef = (1.0 / count).reshape(1).float()
-        accum = torch.zeros(2, dtype=torch.float64, device=dev)
-        drows = [torch.empty_like(r) for r in rows]
-        K.loss_fwd_bwd(target.contiguous().float(), rows, drows, tok, coef, accum, B, D, C, S, p, tok.shape[1], 0,
-                       bands, list(norm_bands) if norm_bands else None, l2)
-        ctx.K, ctx.geo, ctx.drows = K, (B, D, C, S, p, bands), drows
-        return (accum[0] / accum[1]).float()
-
-    @staticmethod
-    def backward(ctx, gout):  # noqa: ANN001, ANN205
-        B, D, C, S, p, bands = ctx.geo
-        dimg = torch.empty(B * D, C, S, S, dtype=torch.float32, device=gout.device)
-        c0 = 0
-        for r, c in zip(ctx.drows, bands):
-            ctx.K.rows_image(r, dimg, c0, c, p, 0)
-            c0 += c
-        return None, None, None, dimg.view(B, D, C, S, S) * gout, None, None, None
+from ..optim import FusedAdamW, OneCycle
+from ..ssl.mae import _on, mae_large, mae_medium, mae_small, mae_tiny
 
 
 class SSLModule(nn.Module):
-    """Pretraining part of the reference LightningModule (everything Lightning-specific stays in the host loop)."""
+    """Pretraining / probing / finetuning steps of the reference LightningModule."""
 
     def __init__(self, datasets, mask, interpolate="nearest", fusion_mode="group", inter_depth=3, model="mae",  # noqa: PLR0913
                  model_size="medium", type_head="attentive", loss="l2_norm", use_date_enc=True, use_ema=False) -> None:
@@ -81,23 +52,39 @@ class SSLModule(nn.Module):
                                            fac_date_enc=1.0 if use_date_enc else 0.0)
         self.ema_model = None
         if use_ema:
-            import copy
             self.ema_model = copy.deepcopy(self.model).to("cpu")
             for p in self.ema_model.parameters():
                 p.requires_grad = False
         self.metrics: dict = {}
+        self._graphed: dict = {}
+        self._reducer = None
+        self._ema_flat = None
+        self.ssl_phase = "pretrain"          # the reference reads it from self.trainer.ssl_phase
 
-    # ------------------------------------------------------------------ reference-shaped API
-    def compute_loss_rec(self, batch, pixels_rec, mask_rec, stage="train"):  # noqa: ANN001, ANN201, ARG002
-        eng = self.model._eng
-        if eng is None:
-            raise RuntimeError("compute_loss_rec needs the CUDA engine: call self.model(batch, 'pretrain') first")
+    def __getstate__(self):  # noqa: ANN204
+        state = self.__dict__.copy()
+        state["_graphed"], state["_reducer"], state["_ema_flat"] = {}, None, None
+        return state
+
+    # ------------------------------------------------------------------ reconstruction loss / logs (pretraining)
+    def compute_loss_rec(self, batch, pixels_rec, mask_rec, stage="train"):  # noqa: ANN001, ANN201
+        """Patch-group-normalised masked L1 / L2 (train/model.py:195-247): per modality the mean over the masked pixels,
+        weighted by D * g^2."""
         losses, weights = [], []
         for name in pixels_rec:
             m = self.spec.inputs[name]
-            w = batch[name].shape[1] * m.grid * m.grid
-            val = _LossRecFn.apply(eng.K, m, batch[name], pixels_rec[name], mask_rec[name],
-                                   self.norm_bands[name] if self.norm_pix_loss else None, self.l2)
+            p, bands = m.patch_size, list(m.band_groups)
+            mk = mask_rec[name]
+            B, D = mk.shape[:2]
+            toks, c0 = [], 0
+            for c in bands:                                   # pixel mask -> token mask of each band group
+                toks.append(mk[:, :, c0, ::p, ::p].reshape(B, -1))
+                c0 += c
+            tok = torch.cat(toks, 1).to(torch.uint8)
+            val, _ = torch.ops.maestro_b200.masked_group_norm_loss(
+                batch[name], pixels_rec[name], tok, bands, list(self.norm_bands[name]) if self.norm_pix_loss else [], p,
+                self.l2)
+            w = D * m.grid * m.grid
             losses.append(w * val)
             weights.append(w)
         loss = torch.stack(losses).sum() / sum(weights)
@@ -107,7 +94,8 @@ class SSLModule(nn.Module):
         return loss
 
     def compute_logs_rec(self, batch, pixels_rec, mask_rec, ssl_phase="pretrain", stage="train"):  # noqa: ANN001, ANN201
-        """Visualisation tensors for sample 0 / date 0 only (the reference builds them for the whole batch, :160-193)."""
+        """Visualisation tensors (train/model.py:160-193).  The reference runs three ``torch.where`` over the whole batch
+        and keeps ``[0, 0]``; the same values are formed here for sample 0 / date 0 only."""
         li, lp, lt = {}, {}, {}
         for name in pixels_rec:
             if name not in self.spec.log_inputs:
@@ -126,13 +114,150 @@ class SSLModule(nn.Module):
         li, lp, lt = self.compute_logs_rec(batch, pixels_rec, mask_rec, ssl_phase=ssl_phase, stage=stage)
         return {"loss": loss, "log_inputs": li, "log_preds": lp, "log_targets": lt}
 
-    # ------------------------------------------------------------------ production path
-    def pretrain_step_fused(self, batch, stage="train"):  # noqa: ANN001, ANN201, ARG002
-        """forward + loss + backward in the engine (gradients land in ``param.grad``-compatible arena views)."""
-        dev = batch["ref_date"].device
+    # ------------------------------------------------------------------ prediction loss (probe / finetune)
+    def compute_loss_pred(self, batch, logits, stage="train"):  # noqa: ANN001, ANN201
+        """BaseModule.compute_loss_pred (train/base.py:98-151): cross entropy ("segment" over pixels, "classif" over
+        samples) or binary cross entropy with logits ("multilabel_classif") over the entries whose target is not the
+        missing value, summed over the targets."""
+        total = 0
+        for name, t in self.spec.targets.items():
+            lg, tg = logits[name], batch[name]
+            if t.type_target in ("segment", "classif"):
+                class_dim = 2 if t.type_target == "segment" else 1
+                valid = (tg != t.missing_val).any()
+                if not bool(valid):
+                    continue
+                val, _ = torch.ops.maestro_b200.cross_entropy(lg, tg.long(), t.missing_val, class_dim)
+                total = total + val
+            else:
+                tgf = tg.float()
+                inds = (tgf != t.missing_val).all(dim=1).nonzero().squeeze(dim=1)
+                if len(inds) == 0:
+                    continue
+                total = total + nn.functional.binary_cross_entropy_with_logits(lg.index_select(0, inds),
+                                                                               tgf.index_select(0, inds))
+        if not isinstance(total, torch.Tensor):
+            total = 0 * list(logits.values()).pop().mean()
+        metric = self.metrics.get(f"loss_pred_{stage}")
+        if metric is not None:
+            metric.update(total.detach())
+        return total
+
+    def probe_or_finetune_step(self, batch, stage="train", ssl_phase=None):  # noqa: ANN001, ANN201
+        """train/base.py:189-222 (the overlay visualisations of compute_logs_pred stay with the host framework)."""
+        phase = ssl_phase or self.ssl_phase
+        model = self.ema_model if (phase == "finetune" and stage != "train" and self.ema_model is not None) else self.model
+        batch, _, _, logits = model(batch, ssl_phase=phase)
+        loss = self.compute_loss_pred(batch, logits, stage=stage)
+        return {"loss": loss, "logits": logits, "log_inputs": {}, "log_preds": {}, "log_targets": {}}
+
+    def shared_step(self, batch, stage="train", ssl_phase=None):  # noqa: ANN001, ANN201
+        phase = ssl_phase or self.ssl_phase
+        if phase == "pretrain":
+            return self.pretrain_step(batch, stage, ssl_phase=phase)
+        if phase in ("probe", "finetune"):
+            return self.probe_or_finetune_step(batch, stage, ssl_phase=phase)
+        msg = f"Invalid ssl phase {phase}. Expected 'pretrain' or 'probe' or 'finetune'"
+        raise ValueError(msg)
+
+    # ------------------------------------------------------------------ optimiser / EMA
+    def configure_optimizers_fused(self, lr: float, total_steps: int, weight_decay: float = 0.01,
+                                   betas=(0.9, 0.999), final_factor: float = 1e4, device=None):
+        """The reference's optimiser (train/model.py:120-158: AdamW + OneCycleLR(pct_start=0.2, cycle_momentum=False,
+        div_factor=1000, final_div_factor=final_factor / 1000), stepped per batch) as ONE fused kernel per step over the
+        engine's arena; parameters outside the arena (the heads) get a stock ``torch.optim.AdamW`` on the same schedule."""
+        dev = torch.device(device) if device is not None else next(self.model.parameters()).device
         eng = self.model._engine(dev)
-        loss = eng.step(batch)
+        sched = OneCycle(lr, total_steps, pct_start=0.2, div_factor=1000.0, final_div_factor=final_factor / 1000.0)
+        return FusedAdamW(eng, lr=lr, betas=betas, weight_decay=weight_decay, schedule=sched)
+
+    def update_ema(self, max_epochs: int) -> None:
+        """BaseModule.update_ema (train/base.py:263-274): ema = momentum * ema + (1 - momentum) * param with
+        momentum = 1 - 1 / (0.2 * max_epochs), one kernel over the flat parameter arena (+ the head parameters)."""
+        if self.ema_model is None:
+            return
+        momentum = 1 - 1 / (max_epochs * 0.2)
+        eng = self.model._eng
+        if eng is None:
+            raise RuntimeError("update_ema needs the CUDA engine: run a step first")
+        names = set(eng.arena.order)
+        if self._ema_flat is None:
+            # lay the EMA copy out like the parameter arena: its nn.Parameters become views of one flat buffer
+            self._ema_flat = torch.zeros_like(eng.arena.param)
+            ema_params = dict(self.ema_model.named_parameters())
+            for n in eng.arena.order:
+                view = eng.arena._view(self._ema_flat, n)
+                view.copy_(ema_params[n].data.to(view.device))
+                ema_params[n].data = view
+            self.ema_model.to(eng.device)
+        with _on(eng.device):
+            eng.K.ema_update(self._ema_flat, eng.arena.param, momentum)
+        for (n, p), (_, pe) in zip(self.model.named_parameters(), self.ema_model.named_parameters()):
+            if n not in names:
+                pe.data.mul_(momentum).add_((1.0 - momentum) * p.detach().data)
+
+    # ------------------------------------------------------------------ production path
+    def _graph_for(self, eng, batch):
+        from ..graph import GraphedPretrainStep
+        import torch.distributed as dist
+        key = tuple((k, tuple(v.shape)) for k, v in sorted(batch.items()) if k in eng.mods or k.endswith("_dates")
+                    or k == "ref_date")
+        g = self._graphed.get(key)
+        if g is None:
+            world = dist.get_world_size() if dist.is_available() and dist.is_initialized() else 1
+            g = GraphedPretrainStep(eng, batch, segments=len(eng.BWD_SEGMENTS) if world > 1 else 1)
+            self._graphed[key] = g
+            if world > 1 and self._reducer is None:
+                from ..dist import GradReducer
+                self._reducer = GradReducer(eng.arena.grad, eng.grad_ranges())
+        return g
+
+    def pretrain_step_fused(self, batch, stage="train", graph: bool = True, accumulate: bool = False):  # noqa: ANN001, ANN201, ARG002
+        """forward + loss + backward in the engine; ``param.grad`` of every arena parameter aliases the engine's gradient
+        arena afterwards (no copies), so any torch optimiser -- or ``configure_optimizers_fused`` -- can step.
+
+        The gradient arena is zeroed at the start of the step unless ``accumulate`` (or the fused AdamW already cleared
+        it in its own pass), so ``optimizer.zero_grad()`` with either ``set_to_none`` setting behaves as in torch.
+        ``graph=True`` replays CUDA graphs captured on first use for this batch shape (host or device tensors; the
+        inputs are copied into the graph's static buffers); with ``torch.distributed`` initialised the backward is cut
+        into segments and each finished arena range is all-reduced (sum) on a side stream while the next segment runs --
+        divide by the world size in the optimiser (``FusedAdamW.step(grad_scale=1 / world)``)."""
+        dev = batch["ref_date"].device
+        if dev.type != "cuda":                      # host batch (pinned): the step runs where the parameters live
+            dev = next(self.model.parameters()).device
+        eng = self.model._engine(dev)
+        eng.loss_kind = self.loss_name
+        with _on(eng.device):
+            if eng.grads_dirty and not accumulate:
+                eng.zero_grad()
+            if not graph:
+                b = {k: v.to(eng.device, non_blocking=True) for k, v in batch.items()}
+                if self._reducer is not None or self._dist_world() > 1:
+                    from ..dist import GradReducer, data_parallel_step
+                    if self._reducer is None:
+                        self._reducer = GradReducer(eng.arena.grad, eng.grad_ranges())
+                    loss = data_parallel_step(eng, b, self._reducer)
+                else:
+                    loss = eng.step(b)
+            else:
+                g = self._graph_for(eng, batch)
+                g.load(batch)
+                eng.grads_dirty = True
+                if self._reducer is None:
+                    loss = g.replay()
+                else:
+                    for i in range(len(g.graphs)):
+                        g.replay(i)
+                        self._reducer.reduce_range(i)
+                    self._reducer.finish()
+                    loss = g.loss
         params = dict(self.model.named_parameters())
         for n in self.model._bound_names:
             params[n].grad = eng.G[n]
+        self.model._versions = sum(params[n]._version for n in self.model._bound_names)
         return {"loss": loss, "log_inputs": {}, "log_preds": {}, "log_targets": {}}
+
+    @staticmethod
+    def _dist_world() -> int:
+        import torch.distributed as dist
+        return dist.get_world_size() if dist.is_available() and dist.is_initialized() else 1

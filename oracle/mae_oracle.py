@@ -396,3 +396,97 @@ def forward(sd: dict, spec, hp: dict, batch: dict, struct: dict, noise: dict, ma
             off += T
     out.update(pixels=pixels, mask_px=mask_px)
     return out
+
+
+# --------------------------------------------------------------------------- probe / finetune heads
+
+
+def attentive_reduce(sd: dict, pre: str, x: torch.Tensor, heads: int = 8) -> torch.Tensor:
+    """AttentiveReduce.forward (layers/head.py:49-64): x [S, L, C] -> [S, C]."""
+    S, L, C = x.shape
+    dh = C // heads
+    out = layer_norm(x, sd[pre + "norm.weight"], sd[pre + "norm.bias"])
+    k, v = (out @ sd[pre + "to_kv.weight"].t()).chunk(2, dim=-1)
+    k = k.reshape(S, L, heads, dh).transpose(1, 2)
+    v = v.reshape(S, L, heads, dh).transpose(1, 2)
+    q = sd[pre + "query"].reshape(1, heads, 1, dh)
+    attn = torch.softmax((q @ k.transpose(-1, -2)) * dh ** -0.5, dim=-1)
+    out = (attn @ v).transpose(1, 2).reshape(S, C)
+    return layer_norm(out, sd[pre + "norm_fc.weight"], sd[pre + "norm_fc.bias"])
+
+
+def _reduce(sd: dict, pre: str, x: torch.Tensor) -> torch.Tensor:
+    if pre + "reduce.query" in sd:                       # type_head == "attentive"
+        return attentive_reduce(sd, pre + "reduce.", x)
+    return x.mean(dim=1)                                  # type_head == "linear"
+
+
+def compute_logits(sd: dict, spec, x_encoded: dict, fusion_mode: str = "group", ssl_phase: str = "finetune") -> dict:
+    """BaseMIM.compute_logits (ssl/mim.py:343-394) + the heads (layers/head.py:67-130) over the encoder output of
+    ``forward(..., ssl_phase="probe" | "finetune")['x_encoded']``."""
+    mods = spec.inputs
+    flat_dates = fusion_mode in ("shared", "monotemp")
+    x_mod = {}
+    if fusion_mode == "group":
+        for g in spec.group_names:
+            off = 0
+            for n in spec.group_members(g):
+                T = mods[n].tokens
+                x_mod[n] = x_encoded[g][:, off:off + T]
+                off += T
+    else:
+        x_mod = dict(x_encoded)
+    for n, m in mods.items():
+        GD = len(m.band_groups) * m.num_dates
+        x = x_mod[n]
+        x_mod[n] = x.reshape(-1, GD, m.grid ** 2, x.shape[-1]) if flat_dates else x.unflatten(1, (GD, -1))
+    x_ref = None
+    if spec.ref_input is not None:
+        g_ref = mods[spec.ref_input].grid
+        parts = []
+        for n, x in x_mod.items():
+            B, D, L, C = x.shape
+            h = mods[n].grid
+            t = x.reshape(B * D, h, h, C).permute(0, 3, 1, 2)
+            t = F.interpolate(t, (g_ref, g_ref), mode="bilinear")
+            parts.append(t.permute(0, 2, 3, 1).reshape(B, D, g_ref * g_ref, C))
+        x_ref = torch.cat(parts, dim=1)
+    x_all = torch.cat([x.flatten(1, 2) for x in x_mod.values()], dim=1)
+    logits = {}
+    for name, t in spec.targets.items():
+        pre = f"heads.{name}."
+        if t.type_target == "segment":
+            x = x_ref.detach() if ssl_phase == "probe" else x_ref
+            B, D, L, C = x.shape
+            out = _reduce(sd, pre, x.permute(0, 2, 1, 3).reshape(B * L, D, C)).reshape(B, 1, L, C)
+            w = sd[pre + "conv.weight"]
+            p = round((w.shape[0] // t.num_classes) ** 0.5)
+            g = round(L ** 0.5)
+            y = out @ w.reshape(w.shape[0], -1).t() + sd[pre + "conv.bias"]              # [B, 1, L, (p1 p2 c)]
+            logits[name] = y.reshape(B, 1, g, g, p, p, t.num_classes).permute(0, 1, 6, 2, 4, 3, 5).reshape(
+                B, 1, t.num_classes, g * p, g * p)
+        else:
+            x = x_all.detach() if ssl_phase == "probe" else x_all
+            logits[name] = _reduce(sd, pre, x) @ sd[pre + "linear.weight"].t() + sd[pre + "linear.bias"]
+    return logits
+
+
+def prediction_loss(spec, logits: dict, batch: dict) -> torch.Tensor:
+    """BaseModule.compute_loss_pred (train/base.py:98-151)."""
+    total = 0
+    for name, t in spec.targets.items():
+        lg, tg = logits[name], batch[name]
+        if t.type_target == "segment":
+            lg = lg[:, 0].permute(0, 2, 3, 1).reshape(-1, t.num_classes)
+            tg = tg.reshape(-1).long()
+        elif t.type_target == "multilabel_classif":
+            tg = tg.float()
+        else:
+            tg = tg.long()
+        ok = (tg != t.missing_val).all(dim=1) if tg.ndim > 1 else tg != t.missing_val
+        inds = ok.nonzero().squeeze(1)
+        if len(inds) == 0:
+            continue
+        fn = F.binary_cross_entropy_with_logits if t.type_target == "multilabel_classif" else F.cross_entropy
+        total = total + fn(lg.index_select(0, inds), tg.index_select(0, inds))
+    return total

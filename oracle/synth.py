@@ -117,15 +117,58 @@ def param_shapes(spec, hp: dict, inter_depth: int, fusion_mode: str = "group") -
     return s
 
 
+def head_param_shapes(spec, hp: dict, type_head: str = "attentive") -> dict[str, tuple]:
+    """``heads.*`` keys / shapes of the reference MAE (ssl/mim.py:169-197, layers/head.py:28-130): a PixelifyHead on the
+    reference input's grid per raster target, a ClassificationHead per per-sample target; the ``reduce`` sub-module
+    (AttentiveReduce) exists for ``type_head="attentive"`` only."""
+    E = hp["embed_dim"]
+    s: dict[str, tuple] = {}
+    for name, t in spec.targets.items():
+        pre = f"heads.{name}."
+        if type_head == "attentive":
+            s[pre + "reduce.norm.weight"] = (E,)
+            s[pre + "reduce.norm.bias"] = (E,)
+            s[pre + "reduce.norm_fc.weight"] = (E,)
+            s[pre + "reduce.norm_fc.bias"] = (E,)
+            s[pre + "reduce.to_kv.weight"] = (2 * E, E)
+            s[pre + "reduce.query"] = (E,)
+        if t.image_size is not None:
+            p = t.image_size // spec.inputs[spec.ref_input].grid
+            s[pre + "conv.weight"] = (t.num_classes * p * p, E, 1, 1)
+            s[pre + "conv.bias"] = (t.num_classes * p * p,)
+        else:
+            s[pre + "linear.weight"] = (t.num_classes, E)
+            s[pre + "linear.bias"] = (t.num_classes,)
+    return s
+
+
+def synthetic_targets(spec, batch_size: int, seed: int = 1) -> dict[str, torch.Tensor]:
+    """Labels shaped as the reference's data pipeline delivers them (train/base.py:108-119): "segment"
+    [B, 1, 1, H, W] integer classes with ~10 % missing values, "classif" [B] classes, "multilabel_classif" [B, C] 0/1."""
+    rs = np.random.RandomState(seed)
+    out = {}
+    for name, t in spec.targets.items():
+        if t.type_target == "segment":
+            S = t.image_size
+            lab = rs.randint(0, t.num_classes - (1 if t.missing_val == t.num_classes - 1 else 0), (batch_size, 1, 1, S, S))
+            lab[rs.rand(batch_size, 1, 1, S, S) < 0.1] = t.missing_val
+            out[name] = torch.from_numpy(lab.astype(np.int64))
+        elif t.type_target == "classif":
+            out[name] = torch.from_numpy(rs.randint(0, t.num_classes, (batch_size,)).astype(np.int64))
+        else:
+            out[name] = torch.from_numpy((rs.rand(batch_size, t.num_classes) < 0.3).astype(np.int64))
+    return out
+
+
 def synthetic_state_dict(shapes: dict[str, tuple], seed: int = 0) -> dict[str, torch.Tensor]:
     """Deterministic parameters: N(0, 1/sqrt(fan_in)) matrices, ~1 norm gains, small biases."""
     rs = np.random.RandomState(seed)
     sd = {}
     for key in sorted(shapes):
         shp = shapes[key]
-        if key.startswith("mask_token."):
+        if key.startswith("mask_token.") or key.endswith(".query"):
             v = rs.randn(*shp)
-        elif len(shp) == 1 and ("norm." in key or ".net.0." in key) and key.endswith("weight"):
+        elif len(shp) == 1 and ("norm." in key or ".net.0." in key or "norm_fc." in key) and key.endswith("weight"):
             v = 1.0 + 0.1 * rs.randn(*shp)
         elif len(shp) == 1:
             v = 0.05 * rs.randn(*shp)

@@ -333,3 +333,58 @@ class FakeKernels:
         out.copy_(torch.from_numpy(m))
         if passes is not None:
             passes.copy_(torch.from_numpy(ps))
+
+    # ------------------------------------------------------------------ heads / EMA (csrc/head.cu)
+    def ema_update(self, ema, param, momentum):
+        ema.mul_(momentum).add_((1.0 - momentum) * param)
+
+    def attn_pool_fwd(self, kv, q, out, probs, heads, scale):
+        S, L, C2 = kv.shape
+        Cc = C2 // 2
+        dh = Cc // heads
+        k = kv[..., :Cc].float().reshape(S, L, heads, dh)
+        v = kv[..., Cc:].float().reshape(S, L, heads, dh)
+        dots = torch.einsum("hd,slhd->shl", q.float().reshape(heads, dh), k) * scale
+        p = torch.softmax(dots, -1)
+        probs.copy_(p)
+        out.copy_(torch.einsum("shl,slhd->shd", p, v).reshape(S, Cc).to(out.dtype))
+
+    def attn_pool_bwd(self, kv, q, probs, dout, dkv, dq, heads, scale):
+        S, L, C2 = kv.shape
+        Cc = C2 // 2
+        dh = Cc // heads
+        k = kv[..., :Cc].float().reshape(S, L, heads, dh)
+        v = kv[..., Cc:].float().reshape(S, L, heads, dh)
+        go = dout.float().reshape(S, heads, dh)
+        p = probs
+        dv = torch.einsum("shl,shd->slhd", p, go)
+        dp = torch.einsum("shd,slhd->shl", go, v)
+        ds = p * (dp - (p * dp).sum(-1, keepdim=True))
+        dk = torch.einsum("shl,hd->slhd", ds, q.float().reshape(heads, dh)) * scale
+        dq += (torch.einsum("shl,slhd->hd", ds, k) * scale).reshape(-1)
+        dkv.copy_(torch.cat([dk.reshape(S, L, Cc), dv.reshape(S, L, Cc)], -1).to(dkv.dtype))
+
+    def token_resample(self, x, Wy, Wx, out, n_img, in_bs, out_bs):
+        ho, hi = Wy.shape
+        wo, wi = Wx.shape
+        d = x.shape[-1]
+        xin = torch.as_strided(x, (n_img, hi, wi, d), (in_bs, wi * d, d, 1), x.storage_offset()).float()
+        y = torch.einsum("ai,bj,nijd->nabd", Wy, Wx, xin)
+        torch.as_strided(out, (n_img, ho, wo, d), (out_bs, wo * d, d, 1), out.storage_offset()).copy_(y.to(out.dtype))
+
+    def xent_fwd_bwd(self, logits, target, dlogits, accum, N, Cn, inner, class_stride, outer_stride, missing):
+        lg = torch.as_strided(logits, (N // inner, inner, Cn), (outer_stride, 1, class_stride), logits.storage_offset())
+        lg2 = lg.reshape(N, Cn).float()
+        t = target.reshape(N)
+        ok = t != missing
+        lsm = torch.log_softmax(lg2, -1)
+        tt = torch.where(ok, t, torch.zeros_like(t))
+        nll = -lsm.gather(1, tt[:, None])[:, 0]
+        accum[0] += nll[ok].double().sum()
+        accum[1] += ok.sum().double()
+        if dlogits is not None:
+            g = lsm.exp()
+            g[torch.arange(N), tt] -= 1.0
+            g = torch.where(ok[:, None], g, torch.zeros_like(g))
+            torch.as_strided(dlogits, (N // inner, inner, Cn), (outer_stride, 1, class_stride),
+                             dlogits.storage_offset()).copy_(g.reshape(N // inner, inner, Cn))
