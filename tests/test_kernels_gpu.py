@@ -457,3 +457,100 @@ def test_fused_attention_fwd_bwd(KK, Bn, N, H, dh):
     close(a[2], b[2], rtol=3e-2, atol=3e-2 * float(b[2].float().abs().max()))
     cos = torch.nn.functional.cosine_similarity(a[2].float().flatten(), b[2].float().flatten(), dim=0)
     assert cos > 0.999, float(cos)
+
+
+# ------------------------------------------------------------------ heads (csrc/head.cu)
+@pytest.mark.parametrize("dt", DT)
+@pytest.mark.parametrize("S,L,H,dh", [(3, 26, 8, 96), (2, 1880, 8, 96), (5, 7, 2, 32), (1, 300, 8, 128)])
+def test_attn_pool_fwd_bwd(KK, dt, S, L, H, dh):
+    Cc = H * dh
+    kv, q, dout = rnd(S, L, 2 * Cc, dt=dt), rnd(Cc, scale=2.0), rnd(S, Cc, dt=dt, seed=3)
+
+    def run(K):
+        out = torch.zeros(S, Cc, dtype=dt, device="cuda")
+        probs = torch.zeros(S, H, L, device="cuda")
+        K.attn_pool_fwd(kv, q, out, probs, H, dh ** -0.5)
+        dkv = torch.zeros_like(kv)
+        dq = torch.zeros(Cc, device="cuda")
+        K.attn_pool_bwd(kv, q, probs, dout, dkv, dq, H, dh ** -0.5)
+        return out, probs, dkv, dq
+    a, b = both(KK, run)
+    t = tol(dt)
+    close(a[0], b[0], **t)
+    close(a[1], b[1], rtol=1e-4, atol=1e-6)
+    close(a[2], b[2], **t)
+    close(a[3], b[3], rtol=1e-3 if dt == torch.float32 else 3e-2, atol=1e-3 if dt == torch.float32 else 3e-2)
+
+
+@pytest.mark.parametrize("dt", DT)
+@pytest.mark.parametrize("hi,ho", [(5, 32), (32, 5), (8, 8), (3, 15)])
+def test_token_resample(KK, dt, hi, ho):
+    from maestro_b200.layers.utils import interp_matrix
+    W = interp_matrix(hi, ho).cuda()
+    x = rnd(6, hi * hi, 64, dt=dt)
+
+    def run(K):
+        out = torch.zeros(6, ho * ho, 64, dtype=dt, device="cuda")
+        K.token_resample(x, W, W, out, 6, hi * hi * 64, ho * ho * 64)
+        return out
+    a, b = both(KK, run)
+    close(a, b, **tol(dt))
+    ref = torch.nn.functional.interpolate(x.float().reshape(6, hi, hi, 64).permute(0, 3, 1, 2), (ho, ho), mode="bilinear")
+    close(a, ref.permute(0, 2, 3, 1).reshape(6, ho * ho, 64), **tol(dt))
+
+
+@pytest.mark.parametrize("shape,class_dim,missing", [((64, 15), 1, -1), ((2, 1, 19, 16, 16), 2, 19), ((3, 1, 15, 32, 32), 2, -1)])
+def test_xent(KK, shape, class_dim, missing):
+    logits = rnd(*shape, scale=2.0)
+    Cn = shape[class_dim]
+    inner = math.prod(shape[class_dim + 1:])
+    N = logits.numel() // Cn
+    g = torch.Generator().manual_seed(1)
+    hi = Cn - 1 if missing == Cn - 1 else Cn
+    target = torch.randint(0, hi, (N,), generator=g)
+    target[torch.rand(N, generator=g) < 0.2] = missing
+    target = target.cuda()
+
+    def run(K):
+        accum = torch.zeros(2, dtype=torch.float64, device="cuda")
+        dl = torch.full_like(logits, 7.0)
+        K.xent_fwd_bwd(logits, target, dl, accum, N, Cn, inner, inner, Cn * inner, missing)
+        return accum, dl
+    a, b = both(KK, run)
+    close(a[0], b[0], rtol=1e-5, atol=1e-5)
+    close(a[1], b[1], rtol=1e-5, atol=1e-5)
+    # and against torch's own cross entropy on the valid rows
+    rows = logits.movedim(class_dim, -1).reshape(N, Cn)
+    ok = target != missing
+    want = torch.nn.functional.cross_entropy(rows[ok], target[ok])
+    assert abs(float(a[0][0] / a[0][1]) - float(want)) < 1e-5 * abs(float(want))
+
+
+def test_mask_tables_with_period(KK):
+    """Fusion "shared" / "monotemp": sequences of L tokens, per-sample tables of period Lt = (G * D) * L."""
+    B, GD, L, d, nk = 3, 4, 9, 32, 2
+    Lt = GD * L
+    noise = torch.rand(B * GD, L, generator=torch.Generator().manual_seed(0)).cuda()
+    struct = torch.zeros(B * GD, L, dtype=torch.uint8, device="cuda")
+    seg_id = (torch.arange(Lt) // (2 * L)).to(torch.int32).cuda()         # two band groups of two dates each
+    tok_id = seg_id.clone()
+    date_id = ((torch.arange(Lt) // L) % 2).to(torch.int32).cuda()
+    pos, feat = rnd(Lt, d), rnd(B, 2, 5)
+    tok, y = rnd(nk, d), rnd(B * GD, 2, d)
+
+    def run(K):
+        mask = torch.zeros(B * GD, L, dtype=torch.uint8, device="cuda")
+        slot = torch.zeros(B * GD, L, dtype=torch.int32, device="cuda")
+        midx = torch.zeros(B * GD, 7, dtype=torch.int64, device="cuda")
+        uidx = torch.zeros(B * GD, 2, dtype=torch.int64, device="cuda")
+        counts = torch.zeros(2, dtype=torch.int32, device="cuda")
+        K.mask_indices(noise, struct, 7, mask, slot, midx, uidx, seg_id, counts, Lt)
+        out = torch.zeros(B * GD, L, d, device="cuda")
+        K.unmask_fwd(y, mask, slot, tok_id, None, tok, pos, feat, date_id, out, 8, 0.5, Lt)
+        dtok = torch.zeros(nk, d, device="cuda")
+        K.masktoken_grad(out, mask, tok_id, None, dtok, Lt)
+        return mask, counts, out, dtok
+    a, b = both(KK, run)
+    assert torch.equal(a[0], b[0]) and torch.equal(a[1], b[1])
+    close(a[2], b[2], rtol=1e-5, atol=1e-5)
+    close(a[3], b[3], rtol=1e-4, atol=1e-4)
