@@ -233,10 +233,6 @@ def run_reference(args):
 def run_ours(args):
     import torch.distributed as dist
 
-    from maestro_b200.engine import PretrainEngine
-    from maestro_b200.ops import Kernels
-    from maestro_b200.optim import FusedAdamW, OneCycle
-
     rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     # libraries (NCCL prints its version banner on stdout) must not pollute the one-JSON-line contract: route fd 1 to
@@ -252,12 +248,17 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=dev)
     spec, hp = DATASET_SPECS[args.dataset](), MODEL_SIZES[args.size]
     B = args.batch
-    K = Kernels()
-    eng = PretrainEngine(spec, hp, MaskSpec(), K, dev, torch.bfloat16, inter_depth=3, loss="l1_norm")
+    # The measured path IS the drop-in path: the reference-shaped SSLModule (maestro/train/model.py) and its fused
+    # step -- what a Lightning training_step forwards to -- not a hand-written loop over the engine.
+    from maestro_b200.train.model import SSLModule
+    mod = SSLModule(spec, MaskSpec(), interpolate="nearest", fusion_mode="group", inter_depth=3, model="mae",
+                    model_size=args.size, loss="l1_norm")
+    mod.to(dev)
+    eng = mod.model._engine(dev)             # the nn.Parameters now alias the engine's flat arena
+    K = eng.K
     eng.init_random(0)
-    opt = FusedAdamW(eng, lr=1e-4, weight_decay=0.01, schedule=OneCycle(1e-4, 100000))
+    opt = mod.configure_optimizers_fused(lr=1e-4, total_steps=100000, weight_decay=0.01)
     host = [synthetic_batch(spec, B, seed=100 + 7 * rank + i, pin=True) for i in range(2)]
-    devb = {k: v.to(dev) for k, v in host[0].items()}
     raw_rasters = None
     if args.input == "raw":
         from maestro_b200.dataset import FLAIR_RASTERS
@@ -272,79 +273,35 @@ def run_ours(args):
     torch.manual_seed(1234 + rank)
 
     use_graph = not args.no_graph
-    gstep = None
-    if use_graph:
-        from maestro_b200.graph import GraphedPretrainStep
-        gstep = GraphedPretrainStep(eng, host[0], segments=len(eng.BWD_SEGMENTS), raw_rasters=raw_rasters,
-                                    struct_on_device=args.struct == "device", struct_seed=4321 + rank)
-        eng.zero_grad()
-        devb = gstep.batch
+    mod.fused_options = dict(raw_rasters=raw_rasters, struct_on_device=args.struct == "device", struct_seed=4321 + rank)
+    if args.h2d_gate >= 0:
+        mod.h2d_gate = args.h2d_gate
+    # device-resident inputs of the `value` leg (fp32 tiles already in HBM when the timed region starts)
+    devb = {k: v.to(dev) for k, v in host[0].items()}
     from maestro_b200.dist import GradReducer
-    reducer = GradReducer(eng.arena.grad, eng.grad_ranges())
+    bytes_per_step = GradReducer(eng.arena.grad, eng.grad_ranges()).bytes_per_step
 
-    gate = {"seg": 0, "marks": None}       # graph index ahead of which the next step's H2D copy may start
+    def step_device(_i=0):
+        return mod.pretrain_step_fused(devb, graph=use_graph, optimizer=opt)["loss"]
 
-    def replay_segments(before_tail=None):
-        """Replay the step graph by graph; for N > 1 all-reduce each finished arena range on the comm stream.
-        ``before_tail`` runs ahead of graph ``gate['seg']``: the latest point that still leaves 1.3x the measured H2D
-        transfer time before the step ends (chosen after the warm-up from event timings: at N = 1 the last three
-        graphs + AdamW = ~5 ms for a 3.9 ms transfer; with 8 ranks sharing the host's memory the transfer is slower
-        and the gate moves earlier).
-        (Updating each finished range with AdamW on the side stream under the remaining backward was measured too:
-        no gain at N = 1, 0.6 % at N = 2 -- the update's CTAs cannot share an SM with the register-full GEMM /
-        attention CTAs, so it only displaces them.)"""
-        n = len(gstep.graphs)
-        for i in range(n):
-            if i == gate["seg"] and before_tail is not None:
-                before_tail()
-            if gate["marks"] is not None:
-                ev = torch.cuda.Event(enable_timing=True)
-                ev.record()
-                gate["marks"].append(ev)
-            gstep.replay(i)
-            if world > 1:
-                reducer.reduce_range(i)
-        reducer.finish()
-
-    def step_device(batch, staged=False, before_tail=None):
-        if use_graph:
-            if not staged:
-                gstep.load(batch)
-            replay_segments(before_tail)
-            loss = gstep.loss
-        else:
-            from maestro_b200.dist import data_parallel_step
-            loss = data_parallel_step(eng, dict(batch), reducer)
-        opt.step(grad_scale=reducer.grad_scale)
-        if gate["marks"] is not None:
-            ev = torch.cuda.Event(enable_timing=True)
-            ev.record()
-            gate["marks"].append(ev)
-        return loss
-
-    prefetched = [False]
     loss_pin = [torch.zeros(1, dtype=torch.float32).pin_memory() for _ in range(2)]
     loss_ev = [torch.cuda.Event() for _ in range(2)]
     loss_pending = [False, False]
+    e2e_count = [0]
 
-    def step_e2e(i):
-        hb = host_e2e[i % 2]
-        if use_graph:
-            # input pipeline: the H2D copy of step i + 1 (pinned host memory -> staging) runs on a copy stream while
-            # step i computes; every step's inputs cross PCIe exactly once, inside the timed region.  The transfer is
-            # gated to start with the last three backward segments, so that it runs under the tail of the backward and
-            # the AdamW update: PCIe ingress slows concurrent kernels (tools/h2d_interference.py), least so there.
-            if not prefetched[0]:
-                gstep.prefetch(hb)
-                prefetched[0] = True
-            gstep.load_prefetched()
-            nxt = host_e2e[(i + 1) % 2]
-            tail = None if args.e2e_ablate == "h2d" else (lambda: gstep.prefetch(nxt, after_current_work=True))
-            loss = step_device(devb, staged=True, before_tail=tail)
+    def step_e2e(_i):
+        # input pipeline (inside SSLModule.pretrain_step_fused): the H2D copy of step i + 1 (pinned host memory ->
+        # staging) runs on a copy stream while step i computes, gated into the backward's tail + AdamW at N = 1 and to
+        # the start of the step when gradients are all-reduced; every step's inputs cross PCIe once, inside the timed
+        # region.
+        i = e2e_count[0]
+        e2e_count[0] += 1
+        hb, nxt = host_e2e[i % 2], host_e2e[(i + 1) % 2]
+        if args.e2e_ablate == "h2d" or not use_graph:
+            src = devb if args.e2e_ablate == "h2d" else hb
+            loss = mod.pretrain_step_fused(src, graph=use_graph, optimizer=opt)["loss"]
         else:
-            for k, v in hb.items():
-                devb[k].copy_(v, non_blocking=True)
-            loss = step_device(devb)
+            loss = mod.pretrain_step_fused(hb, next_batch=nxt, optimizer=opt)["loss"]
         # loss read-back, every step, without draining the queue: step i's loss goes to pinned slot i % 2 behind an
         # event, and the host blocks on step i - 1's event only, so it stays one step ahead of the GPU (the struct-mask
         # draw and the launch of step i + 1 overlap step i).  The last step's copy completes before the closing event.
@@ -376,40 +333,24 @@ def run_ours(args):
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return float(ms[0])
 
-    for i in range(args.warmup):
-        if use_graph and i == args.warmup - 1:
-            gate["marks"] = []                           # time the graphs of the last warm-up step
+    for i in range(max(3, args.warmup)):                 # (the H2D gate is calibrated on the third pipelined call)
         step_e2e(i)
-    if use_graph and gate["marks"]:
-        torch.cuda.synchronize()
-        marks, (h0, h1) = gate["marks"], gstep.h2d_events
-        gate["marks"] = None
-        h2d_ms = h0.elapsed_time(h1)                     # measured with every rank's transfer running
-        tail = [m.elapsed_time(marks[-1]) for m in marks[:-1]]      # time from the start of graph i to the step's end
-        ok = [i for i, t in enumerate(tail) if t >= 1.3 * h2d_ms]
-        gate["seg"] = max(ok) if ok else 0
-        if world > 1:
-            # with a gradient all-reduce in flight the backward is the wrong place for PCIe ingress: measured on 8 GPUs
-            # e2e 32.0 ms gated into the tail (33.2 ms from graph 2) against 30.3 ms with the copy under the forward
-            # (= the run without any H2D copy); 2 GPUs 29.69 -> 29.14 ms.  One GPU keeps the tail (27.43 vs 27.60 ms).
-            gate["seg"] = 0
-        if args.h2d_gate >= 0:
-            gate["seg"] = min(args.h2d_gate, len(tail) - 1)
-        print(f"[rank {rank}] H2D {h2d_ms:.2f} ms per step; gated ahead of graph {gate['seg']} of {len(tail)} "
-              f"({tail[gate['seg']]:.2f} ms before the step ends)", file=sys.stderr)
+    if use_graph and mod.h2d_ms is not None:
+        print(f"[rank {rank}] H2D {mod.h2d_ms:.2f} ms per step; next batch's copy gated ahead of graph {mod.h2d_gate} of "
+              f"{len(eng.BWD_SEGMENTS)}", file=sys.stderr)
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
     # nvidia-smi attaching to the GPU perturbs the first steps after it starts: absorb that outside the timed region
     for i in range(3):
-        step_device(devb)
+        step_device()
     l0 = K.launches
-    ms_dev = timed(lambda i: step_device(devb), args.steps)
+    ms_dev = timed(step_device, args.steps)
     launches = (K.launches - l0) // args.steps
     if use_graph:
-        launches = gstep.launches_per_step + 1
+        launches = next(iter(mod._graphed.values())).launches_per_step + 1
     ms_e2e = timed(step_e2e, args.steps)
-    loss_host[0] = loss_pin[(args.steps - 1) % 2][0]      # timed() has synchronised: the last read-back is complete
+    loss_host[0] = loss_pin[(e2e_count[0] - 1) % 2][0]    # timed() has synchronised: the last read-back is complete
     clocks = sampler.stop() if rank == 0 else None
     last_loss = float(loss_host[0])
 
@@ -436,12 +377,53 @@ def run_ours(args):
         else:
             orig_grouped(problems)
     K.gemm_grouped = grouped_probe
+    # the fused attention launches of the same step: forward 4 N^2 H dh per (sequence, block), backward 2.5x
+    attn_calls = {"fwd": [], "bwd": []}
+    orig_af, orig_ab = K.attn_fwd, K.attn_bwd
+
+    def af_probe(qkv, o, lse, Bn, N, H, dh):
+        attn_calls["fwd"].append((4.0 * N * N * H * dh * Bn, dh, (qkv, o, lse, Bn, N, H, dh)))
+        orig_af(qkv, o, lse, Bn, N, H, dh)
+
+    def ab_probe(qkv, o, do, lse, dqkv, delta, Bn, N, H, dh):
+        attn_calls["bwd"].append((10.0 * N * N * H * dh * Bn, dh, (qkv, o, do, lse, dqkv, delta, Bn, N, H, dh)))
+        orig_ab(qkv, o, do, lse, dqkv, delta, Bn, N, H, dh)
+    K.attn_fwd, K.attn_bwd = af_probe, ab_probe
     eng.zero_grad()
     if args.gemm_breakdown:
         torch.cuda._sleep(int(0.060 * 1.9e9))     # head start for the (slower) Python issue
     eng.step(dict(devb))
     torch.cuda.synchronize()
     K.gemm_grouped = orig_grouped
+    K.attn_fwd, K.attn_bwd = orig_af, orig_ab
+
+    def replay_attn(kind, dh):
+        """Device time (ms) and flops of the step's attention launches of one kind / head dim, back to back."""
+        sel = [c for c in attn_calls[kind] if c[1] == dh]
+        if not sel:
+            return None
+        fn = orig_af if kind == "fwd" else orig_ab
+        best = None
+        for _ in range(3):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            torch.cuda._sleep(int(0.010 * 1.9e9))
+            e0.record()
+            for _, _, a in sel:
+                fn(*a)
+            e1.record()
+            torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1)
+            best = ms if best is None else min(best, ms)
+        fl = sum(c[0] for c in sel)
+        return {"ms_per_step": round(best, 3), "launches": len(sel), "tflops": round(fl / (best * 1e-3) / 1e12, 1)}
+
+    attention = {}
+    for kind in ("fwd", "bwd"):
+        for dh_ in sorted({c[1] for c in attn_calls[kind]}):
+            attention[f"{kind}_dh{dh_}"] = replay_attn(kind, dh_)
+    attn_ms = sum(v["ms_per_step"] for v in attention.values() if v)
+    attn_fl = sum(c[0] for k in attn_calls for c in attn_calls[k])
+    attn_calls.clear()
     for fl, e0, e1, shape in sorted(rec, key=lambda r: -r[1].elapsed_time(r[2])):
         ms = e0.elapsed_time(e1)
         print(f"gemm {shape} {ms * 1e3:8.1f} us {fl / ms / 1e9:7.1f} TF/s", file=sys.stderr)
@@ -498,7 +480,8 @@ def run_ours(args):
                    "l2": "inputs larger than L2 (activations >> 126 MB per step); no flush",
                    "attention": eng.attn_impl, "loss_last": last_loss,
                    "launch": "cuda-graph replay" if use_graph else "python",
-                   "allreduce_bytes_per_step": reducer.bytes_per_step,
+                   "allreduce_bytes_per_step": bytes_per_step if world > 1 else 0,
+                   "api": "SSLModule.pretrain_step_fused(batch, next_batch=..., optimizer=FusedAdamW) -- the drop-in module path",
                    "e2e_input_pipeline": "H2D of step i+1 on a copy stream overlaps step i; loss of every step read back to pinned memory, the host waits one step behind",
                    "e2e_input": ("on-disk dtypes (aerial u8, s2 i16, dem / s1 f32) + augmentation bits, finished by "
                                  "mb_raster_transform on the device" if raw_rasters else
@@ -522,7 +505,12 @@ def run_ours(args):
                           STEP_GFLOP.get(args.dataset, 0) / 1e3 / world, "peak": tf_sus,
                           "frac": value * STEP_GFLOP.get(args.dataset, 0) / 1e3 / world / tf_sus},
         "hbm_kernels": hbm_kernels,
-        "attention_gemm": {"tflops": at_fl / (at_ms * 1e-3) / 1e12 if at_ms > 0 else None, "ms": at_ms},
+        "attention": {"kernels": "attn_fwd_kernel / attn_bwd_* (fused tcgen05 flash attention, one launch per group per "
+                                 "block, back to back, best of 3)",
+                      "by_kind": attention, "ms_per_step": round(attn_ms, 3),
+                      "tflops": round(attn_fl / (attn_ms * 1e-3) / 1e12, 1) if attn_ms > 0 else None,
+                      "frac_of_sustained_peak": round(attn_fl / (attn_ms * 1e-3) / 1e12 / tf_sus, 3) if attn_ms > 0 else None,
+                      "note": "dh = 32 (decoder) is bound by exp2 / MUFU throughput, not the tensor pipe (DESIGN.md section 4)"},
         "cpu_baseline": cpu,
     }
     sys.stdout.flush()

@@ -390,9 +390,40 @@ __global__ void __launch_bounds__(256) colsum_kernel(const T* __restrict__ dy, f
   }
 }
 
+// Any N (e.g. a head's num_classes = 15): lane = column, warps stride over the rows, element-wise loads.
+template <typename T>
+__global__ void __launch_bounds__(256) colsum_scalar_kernel(const T* __restrict__ dy, float* __restrict__ out, int M,
+                                                            int N, int rows_per_block) {
+  __shared__ float red[8][32];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int col = blockIdx.x * 32 + lane;
+  const int m0 = blockIdx.y * rows_per_block;
+  const int m1 = min(M, m0 + rows_per_block);
+  float acc = 0.f;
+  if (col < N)
+    for (int m = m0 + w; m < m1; m += 8) acc += to_f32(dy[static_cast<size_t>(m) * N + col]);
+  red[w][lane] = acc;
+  __syncthreads();
+  if (w == 0 && col < N) {
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) s += red[k][lane];
+    atomicAdd(out + col, s);
+  }
+}
+
 extern "C" int mb_colsum_accum(const void* dy, int dtype, float* out, int M, int N, void* stream) {
   if (M == 0 || N == 0) return 0;
-  if (N % 8 != 0) return -2;
+  if (N % 8 != 0) {
+    int rows_per_block = mb_ceil_div(M, 148);
+    if (rows_per_block < 64) rows_per_block = 64;
+    dim3 grid(mb_ceil_div(N, 32), mb_ceil_div(M, rows_per_block));
+    MB_DISPATCH_DTYPE(dtype, T,
+                      (colsum_scalar_kernel<T><<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+                          static_cast<const T*>(dy), out, M, N, rows_per_block)));
+    MB_CHECK_LAUNCH();
+    return 0;
+  }
   const int V = dtype == MB_DTYPE_BF16 ? 8 : 4;
   const int bx = mb_ceil_div(N, 32 * V);
   int by = (148 * 4) / bx;

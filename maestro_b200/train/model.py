@@ -59,11 +59,18 @@ class SSLModule(nn.Module):
         self._graphed: dict = {}
         self._reducer = None
         self._ema_flat = None
+        self._staged_src = None              # the host batch whose H2D copy is in flight / staged (input pipeline)
+        self._fused_calls = 0
+        self.h2d_gate = None                 # backward segment ahead of which the next batch's copy starts (None: calibrate)
+        self.h2d_ms = None
+        # GraphedPretrainStep options of the fused path: raw_rasters (on-disk dtypes finished on the device),
+        # struct_on_device / struct_seed (Philox structural mask instead of the host generator)
+        self.fused_options: dict = {}
         self.ssl_phase = "pretrain"          # the reference reads it from self.trainer.ssl_phase
 
     def __getstate__(self):  # noqa: ANN204
         state = self.__dict__.copy()
-        state["_graphed"], state["_reducer"], state["_ema_flat"] = {}, None, None
+        state["_graphed"], state["_reducer"], state["_ema_flat"], state["_staged_src"] = {}, None, None, None
         return state
 
     # ------------------------------------------------------------------ reconstruction loss / logs (pretraining)
@@ -199,40 +206,49 @@ class SSLModule(nn.Module):
     # ------------------------------------------------------------------ production path
     def _graph_for(self, eng, batch):
         from ..graph import GraphedPretrainStep
-        import torch.distributed as dist
         key = tuple((k, tuple(v.shape)) for k, v in sorted(batch.items()) if k in eng.mods or k.endswith("_dates")
                     or k == "ref_date")
         g = self._graphed.get(key)
         if g is None:
-            world = dist.get_world_size() if dist.is_available() and dist.is_initialized() else 1
-            g = GraphedPretrainStep(eng, batch, segments=len(eng.BWD_SEGMENTS) if world > 1 else 1)
+            opts = dict(self.fused_options)
+            g = GraphedPretrainStep(eng, batch, segments=len(eng.BWD_SEGMENTS), **opts)
             self._graphed[key] = g
-            if world > 1 and self._reducer is None:
-                from ..dist import GradReducer
-                self._reducer = GradReducer(eng.arena.grad, eng.grad_ranges())
+        if self._dist_world() > 1 and self._reducer is None:
+            from ..dist import GradReducer
+            self._reducer = GradReducer(eng.arena.grad, eng.grad_ranges())
         return g
 
-    def pretrain_step_fused(self, batch, stage="train", graph: bool = True, accumulate: bool = False):  # noqa: ANN001, ANN201, ARG002
+    def pretrain_step_fused(self, batch, stage="train", graph: bool = True, accumulate: bool = False,  # noqa: ANN001, ANN201, ARG002, PLR0913
+                            next_batch=None, optimizer=None):
         """forward + loss + backward in the engine; ``param.grad`` of every arena parameter aliases the engine's gradient
         arena afterwards (no copies), so any torch optimiser -- or ``configure_optimizers_fused`` -- can step.
 
-        The gradient arena is zeroed at the start of the step unless ``accumulate`` (or the fused AdamW already cleared
-        it in its own pass), so ``optimizer.zero_grad()`` with either ``set_to_none`` setting behaves as in torch.
-        ``graph=True`` replays CUDA graphs captured on first use for this batch shape (host or device tensors; the
-        inputs are copied into the graph's static buffers); with ``torch.distributed`` initialised the backward is cut
-        into segments and each finished arena range is all-reduced (sum) on a side stream while the next segment runs --
-        divide by the world size in the optimiser (``FusedAdamW.step(grad_scale=1 / world)``)."""
+        * The gradient arena is zeroed at the start of the step unless ``accumulate`` (or the fused AdamW already
+          cleared it in its own pass), so ``optimizer.zero_grad()`` with either ``set_to_none`` setting behaves as in
+          torch.
+        * ``graph=True`` replays CUDA graphs captured on first use for this batch shape (host or device tensors; the
+          inputs are copied into the graph's static buffers).  The backward is cut into ``engine.BWD_SEGMENTS`` graphs;
+          with ``torch.distributed`` initialised each finished arena range is all-reduced (sum) on a side stream while
+          the next segment runs.
+        * ``next_batch`` (pinned host tensors): the input pipeline.  Its host-to-device copy is started on a copy stream
+          ahead of backward segment ``self.h2d_gate`` of THIS step (calibrated from event timings on the third such
+          call: the latest point that leaves 1.3x the measured transfer time before the step ends; the start of the
+          step when gradients are all-reduced), and the next call -- given that same object as ``batch`` -- finds its
+          inputs already on the device.
+        * ``optimizer`` (a ``FusedAdamW``): stepped inside (``grad_scale = 1 / world``), which puts the update -- the
+          phase least sensitive to PCIe ingress -- inside the window the prefetch is gated into."""
         dev = batch["ref_date"].device
         if dev.type != "cuda":                      # host batch (pinned): the step runs where the parameters live
             dev = next(self.model.parameters()).device
         eng = self.model._engine(dev)
         eng.loss_kind = self.loss_name
+        world = self._dist_world()
         with _on(eng.device):
             if eng.grads_dirty and not accumulate:
                 eng.zero_grad()
             if not graph:
                 b = {k: v.to(eng.device, non_blocking=True) for k, v in batch.items()}
-                if self._reducer is not None or self._dist_world() > 1:
+                if world > 1:
                     from ..dist import GradReducer, data_parallel_step
                     if self._reducer is None:
                         self._reducer = GradReducer(eng.arena.grad, eng.grad_ranges())
@@ -241,21 +257,59 @@ class SSLModule(nn.Module):
                     loss = eng.step(b)
             else:
                 g = self._graph_for(eng, batch)
-                g.load(batch)
-                eng.grads_dirty = True
-                if self._reducer is None:
-                    loss = g.replay()
+                if self._staged_src is not None and self._staged_src is batch:
+                    g.load_prefetched()
                 else:
-                    for i in range(len(g.graphs)):
-                        g.replay(i)
+                    g.load(batch)
+                self._staged_src = None
+                eng.grads_dirty = True
+                marks = [] if (next_batch is not None and self._fused_calls == 2 and self.h2d_gate is None) else None
+                gate = 0 if self.h2d_gate is None else self.h2d_gate
+                for i in range(len(g.graphs)):
+                    if next_batch is not None and i == gate:
+                        g.prefetch(next_batch, after_current_work=i > 0)
+                        self._staged_src = next_batch
+                    if marks is not None:
+                        marks.append(self._mark(eng.device))
+                    g.replay(i)
+                    if self._reducer is not None:
                         self._reducer.reduce_range(i)
+                if self._reducer is not None:
                     self._reducer.finish()
-                    loss = g.loss
+                loss = g.loss
+            if optimizer is not None:
+                optimizer.step(grad_scale=1.0 / world)
+            if graph and marks is not None:
+                marks.append(self._mark(eng.device))
+                self._calibrate_gate(g, marks, world)
+            if next_batch is not None:
+                self._fused_calls += 1
         params = dict(self.model.named_parameters())
         for n in self.model._bound_names:
-            params[n].grad = eng.G[n]
+            if params[n].grad is None or params[n].grad.data_ptr() != eng.G[n].data_ptr():
+                params[n].grad = eng.G[n]
         self.model._versions = sum(params[n]._version for n in self.model._bound_names)
         return {"loss": loss, "log_inputs": {}, "log_preds": {}, "log_targets": {}}
+
+    @staticmethod
+    def _mark(device):  # noqa: ANN001, ANN205
+        ev = torch.cuda.Event(enable_timing=True)
+        ev.record(torch.cuda.current_stream(device))
+        return ev
+
+    def _calibrate_gate(self, g, marks, world: int) -> None:  # noqa: ANN001
+        """Choose the backward segment ahead of which the next batch's H2D copy starts.  PCIe ingress slows concurrent
+        kernels (tools/h2d_interference.py: tcgen05 GEMM +9 %, LayerNorm +32 %), least so under the backward's tail and
+        the AdamW update: pick the latest segment that still leaves 1.3x the measured transfer time before the step
+        ends.  With a gradient all-reduce in flight the backward is the wrong place (the NVLink traffic is on the
+        critical path of the tail; 8 GPUs: 32.0 ms gated into the tail vs 30.3 ms under the forward): gate 0."""
+        torch.cuda.synchronize(g.dev)
+        h0, h1 = g.h2d_events
+        h2d_ms = h0.elapsed_time(h1)
+        tail = [m.elapsed_time(marks[-1]) for m in marks[:-1]]
+        ok = [i for i, t in enumerate(tail) if t >= 1.3 * h2d_ms]
+        self.h2d_gate = 0 if world > 1 else (max(ok) if ok else 0)
+        self.h2d_ms = h2d_ms
 
     @staticmethod
     def _dist_world() -> int:
