@@ -17,87 +17,92 @@ struct RowMap {
 
 // ------------------------------------------------------------------ LayerNorm forward
 // y = (x - mean) * rstd * gamma + beta per row (nn.LayerNorm, eps inside the square root; mean / rstd saved for the
-// backward).  HBM-bound: 2 * d * sizeof(T) bytes per row.  Warp w of the grid walks rows w, w + W, w + 2W, ...; a
-// lane owns NCH 16-byte column chunks, gamma / beta of those columns stay in registers for the whole kernel, and the
-// (still packed) loads of row r + W are in flight while row r is reduced and written.
+// backward).  HBM-bound: 2 * d * sizeof(T) bytes per row -- but only if the instruction stream lets it be: the r1
+// kernel issued 285 warp instructions per 512-wide row (63 % issue-active at 0.52 of the copy bandwidth, 3 CTAs per SM
+// at 80 registers).  This one: packed fp32 math (FFMA2 / FADD2 / FMUL2: two elements per instruction), gamma / beta in
+// shared memory instead of 2 x NE registers, identity row maps without the integer divisions, the (still packed) loads
+// of the next TWO rows of every warp in flight while a row is reduced and written, and a grid of exactly the resident
+// CTAs (no partial wave).  Warp w of the grid walks rows w, w + W, w + 2W, ...; a lane owns NCH 16-byte column chunks.
 constexpr int LNF_THREADS = 256;
 
-template <typename T, int NCH>
-__global__ void __launch_bounds__(LNF_THREADS)
+template <typename T, int NCH, bool MAPPED>
+__global__ void __launch_bounds__(LNF_THREADS, (NCH <= 2 ? 4 : (NCH <= 3 ? 3 : 2)))
 layernorm_fwd_kernel(const T* __restrict__ x, const float* __restrict__ gamma, const float* __restrict__ beta,
                      T* __restrict__ y, float* __restrict__ mean_out, float* __restrict__ rstd_out, int rows, int d,
                      float eps, RowMap in_map, RowMap out_map) {
   constexpr int V = VecIO<T>::N;
-  constexpr int NE = NCH * V;
+  constexpr int NP = Vec2IO<T>::NP;          // float2 pairs per 16-byte chunk
   typedef typename VecIO<T>::Raw Raw;
+  extern __shared__ __align__(16) float gb[];   // gamma [d] | beta [d]
   const int lane = threadIdx.x & 31;
   const int nwarps = blockDim.x >> 5;
   const int gwarp = blockIdx.x * nwarps + (threadIdx.x >> 5);
   const int total_warps = gridDim.x * nwarps;
   const int nvec = d / V;
   const float inv_d = 1.0f / static_cast<float>(d);
+  for (int i = threadIdx.x; i < d; i += blockDim.x) {
+    gb[i] = gamma[i];
+    gb[d + i] = beta[i];
+  }
 
-  Raw nx[NCH];
-  auto issue_loads = [&](int r) {
-    const T* xr = x + in_map.phys(r) * d;
+  Raw n1[NCH], n2[NCH];
+  auto issue_loads = [&](int r, Raw* dst) {
+    const T* xr = x + (MAPPED ? in_map.phys(r) : static_cast<size_t>(r)) * d;
 #pragma unroll
     for (int c = 0; c < NCH; ++c) {
       const int idx = lane + c * 32;
-      nx[c] = idx < nvec ? VecIO<T>::load_raw(xr + idx * V) : VecIO<T>::zero_raw();
+      dst[c] = idx < nvec ? VecIO<T>::load_raw(xr + idx * V) : VecIO<T>::zero_raw();
     }
   };
   int r = gwarp;
-  if (r < rows) issue_loads(r);
-
-  float g[NE], b[NE];
-#pragma unroll
-  for (int c = 0; c < NCH; ++c) {
-    const int idx = lane + c * 32;
-#pragma unroll
-    for (int j = 0; j < V; j += 4) {
-      const bool ok = idx < nvec;
-      const float4 gv = ok ? __ldg(reinterpret_cast<const float4*>(gamma + idx * V + j)) : make_float4(0.f, 0.f, 0.f, 0.f);
-      const float4 bv = ok ? __ldg(reinterpret_cast<const float4*>(beta + idx * V + j)) : make_float4(0.f, 0.f, 0.f, 0.f);
-      g[c * V + j] = gv.x; g[c * V + j + 1] = gv.y; g[c * V + j + 2] = gv.z; g[c * V + j + 3] = gv.w;
-      b[c * V + j] = bv.x; b[c * V + j + 1] = bv.y; b[c * V + j + 2] = bv.z; b[c * V + j + 3] = bv.w;
-    }
-  }
+  if (r < rows) issue_loads(r, n1);
+  if (r + total_warps < rows) issue_loads(r + total_warps, n2);
+  __syncthreads();
 
   for (; r < rows; r += total_warps) {
-    float v[NE];
+    float2 v[NCH * NP];
 #pragma unroll
-    for (int c = 0; c < NCH; ++c) VecIO<T>::unpack(nx[c], v + c * V);
-    if (r + total_warps < rows) issue_loads(r + total_warps);
-    float s = 0.f;
+    for (int c = 0; c < NCH; ++c) {
+      Vec2IO<T>::unpack(n1[c], v + c * NP);
+      n1[c] = n2[c];
+    }
+    if (r + 2 * total_warps < rows) issue_loads(r + 2 * total_warps, n2);
+    float2 s2 = make_float2(0.f, 0.f);
 #pragma unroll
-    for (int e = 0; e < NE; ++e) s += v[e];                 // padding chunks hold zeros
-    const float mean = warp_sum(s) * inv_d;
-    float ss = 0.f;
+    for (int e = 0; e < NCH * NP; ++e) s2 = add2(s2, v[e]);              // padding chunks hold zeros
+    const float mean = warp_sum(s2.x + s2.y) * inv_d;
+    const float2 nm = splat2(-mean);
+    float2 q2 = make_float2(0.f, 0.f);
 #pragma unroll
     for (int c = 0; c < NCH; ++c) {
       if (lane + c * 32 < nvec) {
 #pragma unroll
-        for (int j = 0; j < V; ++j) {
-          const float t = v[c * V + j] - mean;
-          ss = fmaf(t, t, ss);
+        for (int j = 0; j < NP; ++j) {
+          v[c * NP + j] = add2(v[c * NP + j], nm);                       // centred
+          q2 = fma2(v[c * NP + j], v[c * NP + j], q2);
         }
       }
     }
-    const float rstd = rsqrtf(warp_sum(ss) * inv_d + eps);
+    const float rstd = rsqrtf(warp_sum(q2.x + q2.y) * inv_d + eps);
     if (lane == 0 && mean_out != nullptr) {
       mean_out[r] = mean;
       rstd_out[r] = rstd;
     }
-    const float shift = -mean * rstd;
-    T* yr = y + out_map.phys(r) * d;
+    const float2 rs2 = splat2(rstd);
+    T* yr = y + (MAPPED ? out_map.phys(r) : static_cast<size_t>(r)) * d;
 #pragma unroll
     for (int c = 0; c < NCH; ++c) {
       const int idx = lane + c * 32;
       if (idx < nvec) {
-        float o[V];
+        float2 o[NP];
 #pragma unroll
-        for (int j = 0; j < V; ++j) o[j] = fmaf(fmaf(v[c * V + j], rstd, shift), g[c * V + j], b[c * V + j]);
-        VecIO<T>::store(yr + idx * V, o);
+        for (int j = 0; j < NP; j += 2) {
+          const float4 g4 = *reinterpret_cast<const float4*>(gb + idx * V + 2 * j);
+          const float4 b4 = *reinterpret_cast<const float4*>(gb + d + idx * V + 2 * j);
+          o[j] = fma2(mul2(v[c * NP + j], rs2), make_float2(g4.x, g4.y), make_float2(b4.x, b4.y));
+          o[j + 1] = fma2(mul2(v[c * NP + j + 1], rs2), make_float2(g4.z, g4.w), make_float2(b4.z, b4.w));
+        }
+        *reinterpret_cast<Raw*>(yr + idx * V) = Vec2IO<T>::pack(o);
       }
     }
   }
@@ -107,13 +112,22 @@ template <typename T, int NCH>
 static void launch_ln_fwd(const void* x, const float* gamma, const float* beta, void* y, float* mean, float* rstd,
                           int rows, int d, float eps, RowMap im, RowMap om, cudaStream_t st) {
   const int wpb = LNF_THREADS / 32;
-  // at least 2 rows per warp (gamma / beta are loaded once per warp), at most 8 CTAs per SM
+  const bool mapped = !(im.n == rows && im.off == 0 && om.n == rows && om.off == 0);
+  auto kern = mapped ? layernorm_fwd_kernel<T, NCH, true> : layernorm_fwd_kernel<T, NCH, false>;
+  const size_t smem = 2 * static_cast<size_t>(d) * sizeof(float);
+  // persistent grid of exactly the resident CTAs; at least 2 rows per warp (gamma / beta are staged once per CTA)
+  static int per_sm[2] = {0, 0};
+  if (per_sm[mapped] == 0) {
+    int n = 0;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kern, LNF_THREADS, smem);
+    per_sm[mapped] = n > 0 ? n : 1;
+  }
   long long blocks = mb_ceil_div(static_cast<long long>(rows), static_cast<long long>(wpb) * 2);
-  const long long cap = 148LL * 8;
+  const long long cap = 148LL * per_sm[mapped];
   if (blocks > cap) blocks = cap;
   if (blocks < 1) blocks = 1;
-  layernorm_fwd_kernel<T, NCH><<<static_cast<int>(blocks), LNF_THREADS, 0, st>>>(
-      static_cast<const T*>(x), gamma, beta, static_cast<T*>(y), mean, rstd, rows, d, eps, im, om);
+  kern<<<static_cast<int>(blocks), LNF_THREADS, smem, st>>>(static_cast<const T*>(x), gamma, beta, static_cast<T*>(y),
+                                                            mean, rstd, rows, d, eps, im, om);
 }
 
 extern "C" int mb_layernorm_fwd(const void* x, const float* gamma, const float* beta, void* y, float* mean,
@@ -149,16 +163,20 @@ extern "C" int mb_layernorm_fwd(const void* x, const float* gamma, const float* 
 // Every warp owns a ring of `depth` row slots in shared memory that one lane fills with 1D bulk copies
 // (cp.async.bulk, mbarrier completion): up to depth x (x, dy, dres) rows per warp are in flight from HBM without
 // holding registers, which is what the bandwidth-latency product of the chip needs (~45 KB per SM).
+// r2: the r1 kernel issued 551 warp instructions per 512-wide row and was issue-bound (ncu: 55 % issue-active with 12
+// warps per SM at 0.57 of the copy bandwidth).  Packed fp32 math (two elements per instruction), the two row sums
+// reduced together, folded scalars (one FFMA2 chain per output pair) roughly halve the count.
 constexpr int LNB_THREADS = 384;
 
-template <typename T, int NCH>
+template <typename T, int NCH, bool MAPPED>
 __global__ void __launch_bounds__(LNB_THREADS, 1)
 layernorm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x, const float* __restrict__ mean_in,
                      const float* __restrict__ rstd_in, const float* __restrict__ gamma, const T* __restrict__ dres,
                      T* __restrict__ dx, float* __restrict__ dgamma, float* __restrict__ dbeta,
                      float* __restrict__ dbias, int rows, int d, RowMap in_map, RowMap out_map, int depth) {
   constexpr int V = VecIO<T>::N;
-  constexpr int NE = NCH * V;
+  constexpr int NP = Vec2IO<T>::NP;
+  constexpr int NE2 = NCH * NP;
   typedef typename VecIO<T>::Raw Raw;
   extern __shared__ __align__(128) uint8_t smem_raw[];
   // [3][d] partial dgamma / dbeta / dbias | gamma [d] | barriers [nwarps][depth] | ring [nwarps][depth][3][row]
@@ -175,6 +193,7 @@ layernorm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x, const fl
   const int total_warps = gridDim.x * nwarps;
   const int nvec = d / V;
   const bool has_res = dres != nullptr;
+  const bool has_bias = dbias != nullptr;
   for (int i = threadIdx.x; i < 3 * d; i += blockDim.x) sm[i] = 0.f;
   for (int i = threadIdx.x; i < d; i += blockDim.x) gam[i] = gamma[i];
   if (lane == 0) {
@@ -184,7 +203,8 @@ layernorm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x, const fl
   __syncthreads();
 
   auto issue_row = [&](int slot, int r) {   // one lane
-    const size_t pin = in_map.phys(r), pout = out_map.phys(r);
+    const size_t pin = MAPPED ? in_map.phys(r) : static_cast<size_t>(r);
+    const size_t pout = MAPPED ? out_map.phys(r) : static_cast<size_t>(r);
     uint8_t* dst = ring + static_cast<size_t>(slot) * 3 * row_bytes;
     tc::mbar_expect_tx(&bars[slot], (has_res ? 3u : 2u) * row_bytes);
     tc::bulk_load_1d(dst, x + pin * d, row_bytes, &bars[slot]);
@@ -197,18 +217,17 @@ layernorm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x, const fl
       if (rs < rows) issue_row(s, static_cast<int>(rs));
     }
   }
-
-  float ag[NE], ab[NE], ac[NE];
+  float2 ag[NE2], ab[NE2], ac[NE2];
 #pragma unroll
-  for (int e = 0; e < NE; ++e) { ag[e] = 0.f; ab[e] = 0.f; ac[e] = 0.f; }
+  for (int e = 0; e < NE2; ++e) { ag[e] = make_float2(0.f, 0.f); ab[e] = ag[e]; ac[e] = ag[e]; }
   const float inv_d = 1.0f / static_cast<float>(d);
 
   int slot = 0;
   uint32_t phase = 0;
   for (int r = gwarp; r < rows; r += total_warps) {
-    const size_t pin = in_map.phys(r);
+    const size_t pin = MAPPED ? in_map.phys(r) : static_cast<size_t>(r);
     const float mean = mean_in[r], rstd = rstd_in[r];
-    float xh[NE], dv[NE];
+    float2 xh[NE2], dv[NE2];
     Raw cres[NCH];
     tc::mbar_wait(&bars[slot], phase);
     {
@@ -222,8 +241,8 @@ layernorm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x, const fl
         const Raw rx = ok ? VecIO<T>::load_raw(sx + idx * V) : VecIO<T>::zero_raw();
         const Raw rdy = ok ? VecIO<T>::load_raw(sdy + idx * V) : VecIO<T>::zero_raw();
         cres[c] = (ok && has_res) ? VecIO<T>::load_raw(sres + idx * V) : VecIO<T>::zero_raw();
-        VecIO<T>::unpack(rx, xh + c * V);
-        VecIO<T>::unpack(rdy, dv + c * V);
+        Vec2IO<T>::unpack(rx, xh + c * NP);
+        Vec2IO<T>::unpack(rdy, dv + c * NP);
       }
     }
     __syncwarp();   // every lane has read the slot: refill it with the row `depth` rounds ahead
@@ -232,43 +251,48 @@ layernorm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x, const fl
       if (lane == 0 && rn < rows) issue_row(slot, static_cast<int>(rn));
     }
     if (++slot == depth) { slot = 0; phase ^= 1; }
-    float s1 = 0.f, s2 = 0.f;
+    // xhat = x * rstd - mean * rstd; g = dy * gamma; (s1, s2) = (sum g, sum g * xhat); dgamma / dbeta partials
+    const float2 rs2 = splat2(rstd), sh2 = splat2(-mean * rstd);
+    float2 s1 = make_float2(0.f, 0.f), s2 = make_float2(0.f, 0.f);
 #pragma unroll
     for (int c = 0; c < NCH; ++c) {
       const int idx = lane + c * 32;
       if (idx < nvec) {
-        float gv[V];
-        VecIO<float>::load(gam + idx * V, gv);
-        if (V == 8) VecIO<float>::load(gam + idx * V + 4, gv + 4);
 #pragma unroll
-        for (int j = 0; j < V; ++j) {
-          const int e = c * V + j;
-          const float h = (xh[e] - mean) * rstd;
-          const float gg = dv[e] * gv[j];
-          xh[e] = h;
-          s1 += gg;
-          s2 = fmaf(gg, h, s2);
-          ag[e] = fmaf(dv[e], h, ag[e]);
-          ab[e] += dv[e];
-          dv[e] = gg;
+        for (int j = 0; j < NP; j += 2) {
+          const float4 g4 = *reinterpret_cast<const float4*>(gam + idx * V + 2 * j);
+          const float2 gq[2] = {make_float2(g4.x, g4.y), make_float2(g4.z, g4.w)};
+#pragma unroll
+          for (int k = 0; k < 2; ++k) {
+            const int e = c * NP + j + k;
+            const float2 h = fma2(xh[e], rs2, sh2);
+            ag[e] = fma2(dv[e], h, ag[e]);
+            ab[e] = add2(ab[e], dv[e]);
+            const float2 gg = mul2(dv[e], gq[k]);
+            s1 = add2(s1, gg);
+            s2 = fma2(gg, h, s2);
+            xh[e] = h;
+            dv[e] = gg;
+          }
         }
       }
     }
-    s1 = warp_sum(s1) * inv_d;
-    s2 = warp_sum(s2) * inv_d;
+    const float2 tot = warp_sum2(make_float2(s1.x + s1.y, s2.x + s2.y));
+    // dx = dres + rstd * g - rstd * mean(g) - xhat * rstd * mean(g * xhat)
+    const float2 c1 = splat2(-rstd * tot.x * inv_d), c2 = splat2(-rstd * tot.y * inv_d);
 #pragma unroll
     for (int c = 0; c < NCH; ++c) {
       const int idx = lane + c * 32;
       if (idx < nvec) {
-        float o[V];
-        VecIO<T>::unpack(cres[c], o);
+        float2 o[NP];
+        Vec2IO<T>::unpack(cres[c], o);
 #pragma unroll
-        for (int j = 0; j < V; ++j) {
-          const int e = c * V + j;
-          o[j] += rstd * (dv[e] - s1 - xh[e] * s2);
-          ac[e] += o[j];
+        for (int j = 0; j < NP; ++j) {
+          const int e = c * NP + j;
+          o[j] = add2(fma2(xh[e], c2, fma2(dv[e], rs2, o[j])), c1);
+          if (has_bias) ac[e] = add2(ac[e], o[j]);
         }
-        VecIO<T>::store(dx + pin * d + idx * V, o);
+        *reinterpret_cast<Raw*>(dx + pin * d + idx * V) = Vec2IO<T>::pack(o);
       }
     }
   }
@@ -279,9 +303,10 @@ layernorm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x, const fl
 #pragma unroll
       for (int j = 0; j < V; ++j) {
         // column (idx * V + j) lives at [j * nvec + idx]: consecutive lanes -> consecutive banks (conflict-free red)
-        atomicAdd(&sm[j * nvec + idx], ag[c * V + j]);
-        atomicAdd(&sm[d + j * nvec + idx], ab[c * V + j]);
-        if (dbias != nullptr) atomicAdd(&sm[2 * d + j * nvec + idx], ac[c * V + j]);
+        const int e = c * NP + j / 2;
+        atomicAdd(&sm[j * nvec + idx], (j & 1) ? ag[e].y : ag[e].x);
+        atomicAdd(&sm[d + j * nvec + idx], (j & 1) ? ab[e].y : ab[e].x);
+        if (has_bias) atomicAdd(&sm[2 * d + j * nvec + idx], (j & 1) ? ac[e].y : ac[e].x);
       }
     }
   }
@@ -290,7 +315,7 @@ layernorm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x, const fl
     const int si = (i % V) * nvec + i / V;
     atomicAdd(dgamma + i, sm[si]);
     atomicAdd(dbeta + i, sm[d + si]);
-    if (dbias != nullptr) atomicAdd(dbias + i, sm[2 * d + si]);
+    if (has_bias) atomicAdd(dbias + i, sm[2 * d + si]);
   }
 }
 
@@ -312,18 +337,21 @@ static int launch_ln_bwd(const void* dy, const void* x, const float* mean, const
   if (depth < 1) depth = 1;
   const size_t smem = fixed + static_cast<size_t>(nwarps) * depth * (8 + 3 * row_bytes);
   const int nch = mb_ceil_div(d / V, 32);
+  const bool mapped = !(im.n == rows && im.off == 0 && om.n == rows && om.off == 0);
 #define MB_LNB(N_)                                                                                              \
   case N_:                                                                                                      \
     {                                                                                                           \
       static bool attr_done = false;                                                                            \
       if (!attr_done) {                                                                                         \
-        cudaFuncSetAttribute(layernorm_bwd_kernel<T, N_>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024); \
+        cudaFuncSetAttribute(layernorm_bwd_kernel<T, N_, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024); \
+        cudaFuncSetAttribute(layernorm_bwd_kernel<T, N_, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024); \
         attr_done = true;                                                                                       \
       }                                                                                                         \
+      auto kern = mapped ? layernorm_bwd_kernel<T, N_, true> : layernorm_bwd_kernel<T, N_, false>;              \
+      kern<<<blocks, LNB_THREADS, smem, st>>>(                                                                  \
+          static_cast<const T*>(dy), static_cast<const T*>(x), mean, rstd, gamma, static_cast<const T*>(dres),  \
+          static_cast<T*>(dx), dgamma, dbeta, dbias, rows, d, im, om, depth);                                   \
     }                                                                                                           \
-    layernorm_bwd_kernel<T, N_><<<blocks, LNB_THREADS, smem, st>>>(                                              \
-        static_cast<const T*>(dy), static_cast<const T*>(x), mean, rstd, gamma, static_cast<const T*>(dres),    \
-        static_cast<T*>(dx), dgamma, dbeta, dbias, rows, d, im, om, depth);                                     \
     break;
   switch (nch) {
     MB_LNB(1) MB_LNB(2) MB_LNB(3) MB_LNB(4) MB_LNB(5) MB_LNB(6) MB_LNB(7) MB_LNB(8)

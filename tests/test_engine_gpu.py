@@ -41,13 +41,15 @@ def _check(name, K, dtype, rtol, atol, use_tc=True):
     else:
         # bf16 at micro width: vectors (LayerNorm gains of 64 elements, biases) of stacks that see sequences of 2 - 9
         # tokens are rounding-noise dominated one by one -- matrices individually, vectors jointly (as at full size)
+        # (fusion "shared" / "monotemp" on TreeSatAI-TS: a stack sees 16 tokens in all -- 8 sequences of 2 kept tokens)
         big = [(U.golden_grad_cosine(gold, k, g), k) for k, g in eng.grads().items() if g.numel() >= 1024]
-        assert min(big)[0] >= 0.999, min(big)
-        small = [k for k, g in eng.grads().items() if g.numel() < 1024 and f"grad/{k}" in gold]
-        a = np.concatenate([eng.grads()[k].detach().float().cpu().numpy().reshape(-1) for k in small])
-        b = np.concatenate([gold[f"grad/{k}"].reshape(-1) for k in small])
-        cos = float(a.astype(np.float64) @ b.astype(np.float64)) / float(np.linalg.norm(a) * np.linalg.norm(b))
-        assert cos >= 0.999, cos
+        assert min(big)[0] >= (0.999 if U.fusion_of(name) in ("group", "mod") else 0.99), min(big)
+        for sel in (lambda g: g.numel() < 1024, lambda g: True):          # the vectors jointly, then every parameter jointly
+            keys = [k for k, g in eng.grads().items() if sel(g) and f"grad/{k}" in gold]
+            a = np.concatenate([eng.grads()[k].detach().float().cpu().numpy().reshape(-1) for k in keys])
+            b = np.concatenate([gold[f"grad/{k}"].reshape(-1) for k in keys])
+            cos = float(a.astype(np.float64) @ b.astype(np.float64)) / float(np.linalg.norm(a) * np.linalg.norm(b))
+            assert cos >= 0.999, cos
     return r
 
 
