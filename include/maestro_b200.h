@@ -58,6 +58,23 @@ int mb_layernorm_fwd(const void* x, const float* gamma, const float* beta, void*
 int mb_layernorm_bwd(const void* dy, const void* x, const float* mean, const float* rstd, const float* gamma,
                      const void* dres, void* dx, float* dgamma, float* dbeta, float* dbias, int dtype, int rows, int d,
                      int in_n, int in_bs, int in_off, int out_n, int out_bs, int out_off, void* stream);
+/* Grouped forms: `count` (1..4) LayerNorms of one width as ONE launch -- the per-group encoder / decoder stacks of
+ * MAE.encode / MAE.decode (maestro/ssl/mae.py:289-306, looped per group by encode_or_decode, maestro/ssl/mim.py:396-
+ * 403) step in lockstep, so the four LayerNorms of a layer (1 600 - 8 192 rows each) become one kernel whose CTAs are
+ * split between the problems in proportion to their rows.  `problems` is a HOST pointer. */
+typedef struct {
+  const void* x; const float* gamma; const float* beta; void* y; float* mean; float* rstd;
+  int rows;
+  int in_n, in_bs, in_off, out_n, out_bs, out_off;       /* row maps (identity: n = rows, bs = 0, off = 0) */
+} mb_ln_fwd_problem;
+typedef struct {
+  const void* dy; const void* x; const float* mean; const float* rstd; const float* gamma; const void* dres;
+  void* dx; float* dgamma; float* dbeta; float* dbias;   /* dres / dbias may be NULL */
+  int rows;
+  int in_n, in_bs, in_off, out_n, out_bs, out_off;
+} mb_ln_bwd_problem;
+int mb_layernorm_fwd_grouped(const mb_ln_fwd_problem* problems, int count, int dtype, int d, float eps, void* stream);
+int mb_layernorm_bwd_grouped(const mb_ln_bwd_problem* problems, int count, int dtype, int d, void* stream);
 /* nn.GroupNorm(1, E) of PatchifyBands, maestro/layers/embed.py:55,61: per-image sum / sum-of-squares (fp64). */
 int mb_gn_stats(const void* y, int dtype, double* sums, int n_img, long long elems_per_img, void* stream);
 /* GroupNorm apply + enc_add_encodings (maestro/ssl/mim.py:232-252) + group_mods concat (layers/utils.py:12-47). */
@@ -154,6 +171,17 @@ int mb_softmax_bwd_rows(const void* p, float* dp, void* ds, int dtype, long long
 int mb_attn_fwd(const void* qkv, void* o, float* lse, int Bn, int N, int H, int dh, void* stream);
 int mb_attn_bwd(const void* qkv, const void* o, const void* d_o, const float* lse, void* dqkv, float* delta, int Bn,
                 int N, int H, int dh, void* stream);
+
+/* Grouped forms: `count` (1..4) attention problems of one head shape (H, dh) as ONE forward launch / TWO backward
+ * launches -- the four per-group stacks of a layer (sequence lengths 50 .. 1024) run as one grid whose CTA ranges
+ * belong to the problems in turn.  `problems` is a HOST pointer; d_o / dqkv / delta are read by the backward only. */
+typedef struct {
+  const void* qkv; void* o; float* lse;
+  const void* d_o; void* dqkv; float* delta;
+  int Bn, N;
+} mb_attn_problem;
+int mb_attn_fwd_grouped(const mb_attn_problem* problems, int count, int H, int dh, void* stream);
+int mb_attn_bwd_grouped(const mb_attn_problem* problems, int count, int H, int dh, void* stream);
 
 /* ---- device-side input pipeline ----------------------------------------------------------------- */
 #define MB_RAW_U8 0

@@ -87,6 +87,30 @@ class LossParams(C.Structure):
     ]
 
 
+class LnFwdProblem(C.Structure):
+    """Mirror of ``mb_ln_fwd_problem``."""
+
+    _fields_ = [("x", C.c_void_p), ("gamma", C.c_void_p), ("beta", C.c_void_p), ("y", C.c_void_p), ("mean", C.c_void_p),
+                ("rstd", C.c_void_p), ("rows", C.c_int), ("in_n", C.c_int), ("in_bs", C.c_int), ("in_off", C.c_int),
+                ("out_n", C.c_int), ("out_bs", C.c_int), ("out_off", C.c_int)]
+
+
+class LnBwdProblem(C.Structure):
+    """Mirror of ``mb_ln_bwd_problem``."""
+
+    _fields_ = [("dy", C.c_void_p), ("x", C.c_void_p), ("mean", C.c_void_p), ("rstd", C.c_void_p), ("gamma", C.c_void_p),
+                ("dres", C.c_void_p), ("dx", C.c_void_p), ("dgamma", C.c_void_p), ("dbeta", C.c_void_p),
+                ("dbias", C.c_void_p), ("rows", C.c_int), ("in_n", C.c_int), ("in_bs", C.c_int), ("in_off", C.c_int),
+                ("out_n", C.c_int), ("out_bs", C.c_int), ("out_off", C.c_int)]
+
+
+class AttnProblem(C.Structure):
+    """Mirror of ``mb_attn_problem``."""
+
+    _fields_ = [("qkv", C.c_void_p), ("o", C.c_void_p), ("lse", C.c_void_p), ("d_o", C.c_void_p), ("dqkv", C.c_void_p),
+                ("delta", C.c_void_p), ("Bn", C.c_int), ("N", C.c_int)]
+
+
 STRUCT_MAX_MODS = 8
 
 
@@ -176,5 +200,6 @@ EXPORTS = [
     "mb_mask_indices", "mb_gather_rows", "mb_scatter_kept", "mb_unmask_fwd", "mb_masktoken_grad",
     "mb_loss_fwd_bwd", "mb_gemm_simt", "mb_softmax_rows", "mb_softmax_bwd_rows", "mb_gemm_tc", "mb_gemm_tc_grouped",
     "mb_adamw_step", "mb_attn_fwd", "mb_attn_bwd", "mb_raster_transform", "mb_struct_mask", "mb_resize",
+    "mb_layernorm_fwd_grouped", "mb_layernorm_bwd_grouped", "mb_attn_fwd_grouped", "mb_attn_bwd_grouped",
     "mb_ema_update", "mb_attn_pool_fwd", "mb_attn_pool_bwd", "mb_token_resample", "mb_xent_fwd_bwd",
 ]

@@ -11,10 +11,17 @@ namespace {
 constexpr int DKDV_THREADS = 160;
 
 template <int DH>
-__global__ void __launch_bounds__(DKDV_THREADS) attn_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap tm_qkv128,
-                                                            const __grid_constant__ CUtensorMap tm_qsub,
-                                                            const __grid_constant__ CUtensorMap tm_dosub, BwdArgs args) {
+__global__ void __launch_bounds__(DKDV_THREADS) attn_bwd_dkdv_kernel(const __grid_constant__ BwdGroup grp) {
   using C_ = BCfg<DH>;
+  int pi = 0, cta0 = 0;
+#pragma unroll
+  for (int i = 0; i < ATTN_MAX_GROUP - 1; ++i)
+    if (i + 1 < grp.count && static_cast<int>(blockIdx.x) >= grp.cta_end[i]) { pi = i + 1; cta0 = grp.cta_end[i]; }
+  const CUtensorMap& tm_qkv128 = grp.q128[pi];
+  const CUtensorMap& tm_qsub = grp.qsub[pi];
+  const CUtensorMap& tm_dosub = grp.dosub[pi];
+  const BwdArgs& args = grp.a[pi];
+  const int bid = static_cast<int>(blockIdx.x) - cta0;
   constexpr int SUB = C_::SUB, NS = C_::NS;
   constexpr int OFF_K = 0, OFF_V = C_::ROW_TILE, OFF_Q = 2 * C_::ROW_TILE, OFF_DO = OFF_Q + NS * C_::SUB_TILE;
   constexpr int OFF_PT = OFF_DO + NS * C_::SUB_TILE, OFF_DST = OFF_PT + 2 * C_::AS_TILE;
@@ -33,7 +40,7 @@ __global__ void __launch_bounds__(DKDV_THREADS) attn_bwd_dkdv_kernel(const __gri
   const int tid = threadIdx.x, warp = tid >> 5;
   const int N = args.N, H = args.H, inner = H * DH;
   const int r_tiles = (N + BR - 1) / BR;
-  const int rt = blockIdx.x % r_tiles, bh = blockIdx.x / r_tiles;
+  const int rt = bid % r_tiles, bh = bid / r_tiles;
   const int h = bh % H, b = bh / H;
   const int n_sub = (N + SUB - 1) / SUB;
 
@@ -254,25 +261,34 @@ int tmap3(CUtensorMap* tm, const void* base, int Bn, int N, int cols, int DH, in
 }
 
 template <int DH>
-int launch_bwd(const void* qkv, const void* o, const void* d_o, const float* lse, void* dqkv, float* delta, int Bn,
-               int N, int H, cudaStream_t st) {
+int launch_bwd(const mb_attn_problem* ps, int count, int H, cudaStream_t st) {
   using C_ = BCfg<DH>;
-  CUtensorMap q128, do128, qsub, dosub;
-  int rc;
-  if ((rc = tmap3(&q128, qkv, Bn, N, 3 * H * DH, DH, BR)) != 0) return rc;
-  if ((rc = tmap3(&do128, d_o, Bn, N, H * DH, DH, BR)) != 0) return rc;
-  if ((rc = tmap3(&qsub, qkv, Bn, N, 3 * H * DH, DH, C_::SUB)) != 0) return rc;
-  if ((rc = tmap3(&dosub, d_o, Bn, N, H * DH, DH, C_::SUB)) != 0) return rc;
-  BwdArgs a;
-  a.o = static_cast<const bf16*>(o);
-  a.d_o = static_cast<const bf16*>(d_o);
-  a.lse = lse;
-  a.delta = delta;
-  a.dqkv = static_cast<bf16*>(dqkv);
-  a.N = N;
-  a.H = H;
-  a.scale = 1.0f / sqrtf(static_cast<float>(DH));
-  a.scale_log2 = a.scale * 1.4426950408889634f;
+  BwdGroup g;
+  int total = 0, rc;
+  for (int i = 0; i < count; ++i) {
+    const int Bn = ps[i].Bn, N = ps[i].N;
+    if ((rc = tmap3(&g.q128[i], ps[i].qkv, Bn, N, 3 * H * DH, DH, BR)) != 0) return rc;
+    if ((rc = tmap3(&g.do128[i], ps[i].d_o, Bn, N, H * DH, DH, BR)) != 0) return rc;
+    if ((rc = tmap3(&g.qsub[i], ps[i].qkv, Bn, N, 3 * H * DH, DH, C_::SUB)) != 0) return rc;
+    if ((rc = tmap3(&g.dosub[i], ps[i].d_o, Bn, N, H * DH, DH, C_::SUB)) != 0) return rc;
+    BwdArgs& a = g.a[i];
+    a.o = static_cast<const bf16*>(ps[i].o);
+    a.d_o = static_cast<const bf16*>(ps[i].d_o);
+    a.lse = ps[i].lse;
+    a.delta = ps[i].delta;
+    a.dqkv = static_cast<bf16*>(ps[i].dqkv);
+    a.N = N;
+    a.H = H;
+    a.scale = 1.0f / sqrtf(static_cast<float>(DH));
+    a.scale_log2 = a.scale * 1.4426950408889634f;
+    total += Bn * H * ((N + BR - 1) / BR);
+    g.cta_end[i] = total;
+  }
+  for (int i = count; i < ATTN_MAX_GROUP; ++i) {
+    g.q128[i] = g.q128[0]; g.do128[i] = g.do128[0]; g.qsub[i] = g.qsub[0]; g.dosub[i] = g.dosub[0];
+    g.a[i] = g.a[0]; g.cta_end[i] = total;
+  }
+  g.count = count;
   constexpr int SMEM_DQ = 2 * C_::ROW_TILE + 2 * C_::NS * C_::SUB_TILE + 2 * C_::AS_TILE + 128 + 1024;
   constexpr int SMEM_DKDV = 2 * C_::ROW_TILE + 2 * C_::NS * C_::SUB_TILE + 4 * C_::AS_TILE + 2 * 2 * C_::SUB * 4 + 128 + 1024;
   static bool attr = false;
@@ -281,24 +297,34 @@ int launch_bwd(const void* qkv, const void* o, const void* d_o, const float* lse
     cudaFuncSetAttribute(attn_bwd_dkdv_kernel<DH>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_DKDV);
     attr = true;
   }
-  const int grid = Bn * H * ((N + BR - 1) / BR);
-  attn_bwd_dq_kernel<DH><<<grid, DQ_THREADS, SMEM_DQ, st>>>(q128, qsub, do128, a);
-  attn_bwd_dkdv_kernel<DH><<<grid, DKDV_THREADS, SMEM_DKDV, st>>>(q128, qsub, dosub, a);
+  attn_bwd_dq_kernel<DH><<<total, DQ_THREADS, SMEM_DQ, st>>>(g);
+  attn_bwd_dkdv_kernel<DH><<<total, DKDV_THREADS, SMEM_DKDV, st>>>(g);
   cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? 0 : static_cast<int>(e);
 }
 
 }  // namespace
 
-// Gradient of mb_attn_fwd: dqkv [Bn*N, 3*H*dh] bf16 from d_o [Bn*N, H*dh]; delta [Bn, H, N] fp32 is scratch.
-extern "C" int mb_attn_bwd(const void* qkv, const void* o, const void* d_o, const float* lse, void* dqkv, float* delta,
-                           int Bn, int N, int H, int dh, void* stream) {
-  if (Bn == 0 || N == 0) return 0;
+// Gradient of mb_attn_fwd_grouped: per problem dqkv [Bn*N, 3*H*dh] bf16 from d_o [Bn*N, H*dh]; delta [Bn, H, N] fp32 is
+// scratch.  Two launches (dQ, then dK / dV) for the whole group.
+extern "C" int mb_attn_bwd_grouped(const mb_attn_problem* problems, int count, int H, int dh, void* stream) {
+  if (count < 1 || count > ATTN_MAX_GROUP) return -2;
+  mb_attn_problem live[ATTN_MAX_GROUP];
+  int n = 0;
+  for (int i = 0; i < count; ++i)
+    if (problems[i].Bn > 0 && problems[i].N > 0) live[n++] = problems[i];
+  if (n == 0) return 0;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   switch (dh) {
-    case 16: return launch_bwd<16>(qkv, o, d_o, lse, dqkv, delta, Bn, N, H, st);
-    case 32: return launch_bwd<32>(qkv, o, d_o, lse, dqkv, delta, Bn, N, H, st);
-    case 64: return launch_bwd<64>(qkv, o, d_o, lse, dqkv, delta, Bn, N, H, st);
+    case 16: return launch_bwd<16>(live, n, H, st);
+    case 32: return launch_bwd<32>(live, n, H, st);
+    case 64: return launch_bwd<64>(live, n, H, st);
     default: return -2;
   }
+}
+
+extern "C" int mb_attn_bwd(const void* qkv, const void* o, const void* d_o, const float* lse, void* dqkv, float* delta,
+                           int Bn, int N, int H, int dh, void* stream) {
+  const mb_attn_problem p{qkv, const_cast<void*>(o), const_cast<float*>(lse), d_o, dqkv, delta, Bn, N};
+  return mb_attn_bwd_grouped(&p, 1, H, dh, stream);
 }

@@ -10,6 +10,16 @@
 #include "tc_common.cuh"
 #include "tmap.h"
 
+struct mb_attn_problem {     // mirror of include/maestro_b200.h
+  const void* qkv;
+  void* o;
+  float* lse;
+  const void* d_o;
+  void* dqkv;
+  float* delta;
+  int Bn, N;
+};
+
 namespace {
 
 constexpr int BR = 128;  // rows owned by the CTA (TMEM lanes)
@@ -43,6 +53,15 @@ struct BwdArgs {
   float scale, scale_log2;
 };
 
+// Grouped launch (see attn_tc.cu): per problem the four tensor maps of the two kernels, its arguments and CTA range.
+constexpr int ATTN_MAX_GROUP = 4;
+struct BwdGroup {
+  CUtensorMap q128[ATTN_MAX_GROUP], qsub[ATTN_MAX_GROUP], do128[ATTN_MAX_GROUP], dosub[ATTN_MAX_GROUP];
+  BwdArgs a[ATTN_MAX_GROUP];
+  int cta_end[ATTN_MAX_GROUP];
+  int count;
+};
+
 // 16-byte chunk c16 of row `tid` of a K-major [128, BCc] tile whose swizzle span equals its row (128 B: chunk ^ row % 8;
 // 64 B: chunk ^ (row / 2) % 4; 32 B: chunk ^ (row / 4) % 2)
 template <int BCc>
@@ -64,11 +83,17 @@ __device__ __forceinline__ float4 lds_f4(uint32_t addr) {
 constexpr int DQ_THREADS = 160;
 
 template <int DH>
-__global__ void __launch_bounds__(DQ_THREADS) attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_qkv128,
-                                                                 const __grid_constant__ CUtensorMap tm_qsub,
-                                                                 const __grid_constant__ CUtensorMap tm_do128,
-                                                                 BwdArgs args) {
+__global__ void __launch_bounds__(DQ_THREADS) attn_bwd_dq_kernel(const __grid_constant__ BwdGroup grp) {
   using C_ = BCfg<DH>;
+  int pi = 0, cta0 = 0;
+#pragma unroll
+  for (int i = 0; i < ATTN_MAX_GROUP - 1; ++i)
+    if (i + 1 < grp.count && static_cast<int>(blockIdx.x) >= grp.cta_end[i]) { pi = i + 1; cta0 = grp.cta_end[i]; }
+  const CUtensorMap& tm_qkv128 = grp.q128[pi];
+  const CUtensorMap& tm_qsub = grp.qsub[pi];
+  const CUtensorMap& tm_do128 = grp.do128[pi];
+  const BwdArgs& args = grp.a[pi];
+  const int bid = static_cast<int>(blockIdx.x) - cta0;
   constexpr int SUB = C_::SUB, NS = C_::NS;
   constexpr int OFF_Q = 0, OFF_DO = C_::ROW_TILE, OFF_K = 2 * C_::ROW_TILE, OFF_V = OFF_K + NS * C_::SUB_TILE;
   constexpr int OFF_DS = OFF_V + NS * C_::SUB_TILE, OFF_BAR = OFF_DS + 2 * C_::AS_TILE;
@@ -84,7 +109,7 @@ __global__ void __launch_bounds__(DQ_THREADS) attn_bwd_dq_kernel(const __grid_co
   const int tid = threadIdx.x, warp = tid >> 5;
   const int N = args.N, H = args.H, inner = H * DH;
   const int r_tiles = (N + BR - 1) / BR;
-  const int rt = blockIdx.x % r_tiles, bh = blockIdx.x / r_tiles;
+  const int rt = bid % r_tiles, bh = bid / r_tiles;
   const int h = bh % H, b = bh / H;
   const int n_sub = (N + SUB - 1) / SUB;
 

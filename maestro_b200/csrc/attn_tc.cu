@@ -17,6 +17,16 @@
 #include "tc_common.cuh"
 #include "tmap.h"
 
+struct mb_attn_problem {     // mirror of include/maestro_b200.h
+  const void* qkv;
+  void* o;
+  float* lse;
+  const void* d_o;          // backward only
+  void* dqkv;
+  float* delta;
+  int Bn, N;
+};
+
 namespace {
 
 constexpr int BQ = 128;   // query rows per CTA
@@ -44,9 +54,26 @@ struct AttnArgs {
   float scale;
 };
 
+// Grouped launch: up to ATTN_MAX_GROUP problems of one head shape (the per-group stacks of a layer: same H and dh,
+// different sequence lengths / batch) share one grid; CTA ranges [cta_end[p - 1], cta_end[p]) belong to problem p.
+constexpr int ATTN_MAX_GROUP = 4;
+struct AttnGroup {
+  CUtensorMap tm[ATTN_MAX_GROUP];
+  AttnArgs a[ATTN_MAX_GROUP];
+  int cta_end[ATTN_MAX_GROUP];
+  int count;
+};
+
 template <int DH>
-__global__ void __launch_bounds__(128) attn_fwd_kernel(const __grid_constant__ CUtensorMap tm, AttnArgs args) {
+__global__ void __launch_bounds__(128) attn_fwd_kernel(const __grid_constant__ AttnGroup grp) {
   using C_ = ACfg<DH>;
+  int pi = 0, cta0 = 0;
+#pragma unroll
+  for (int i = 0; i < ATTN_MAX_GROUP - 1; ++i)
+    if (i + 1 < grp.count && static_cast<int>(blockIdx.x) >= grp.cta_end[i]) { pi = i + 1; cta0 = grp.cta_end[i]; }
+  const CUtensorMap& tm = grp.tm[pi];
+  const AttnArgs& args = grp.a[pi];
+  const int bid = static_cast<int>(blockIdx.x) - cta0;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
   uint64_t* bar_q = reinterpret_cast<uint64_t*>(smem + C_::OFF_BAR);
@@ -58,8 +85,8 @@ __global__ void __launch_bounds__(128) attn_fwd_kernel(const __grid_constant__ C
   const int tid = threadIdx.x, warp = tid >> 5;
   const int N = args.N, H = args.H;
   const int q_tiles = (N + BQ - 1) / BQ;
-  const int qt = blockIdx.x % q_tiles;
-  const int bh = blockIdx.x / q_tiles;
+  const int qt = bid % q_tiles;
+  const int bh = bid / q_tiles;
   const int h = bh % H, b = bh / H;
   const int inner = H * DH;
   const int kv_tiles = (N + BKV - 1) / BKV;
@@ -272,39 +299,56 @@ int qkv_tmap(CUtensorMap* tm, const void* qkv, int Bn, int N, int cols, int DH, 
 }
 
 template <int DH>
-int launch_fwd(const void* qkv, void* o, float* lse, int Bn, int N, int H, cudaStream_t st) {
+int launch_fwd(const mb_attn_problem* ps, int count, int H, cudaStream_t st) {
   using C_ = ACfg<DH>;
-  CUtensorMap tm;
-  int rc = qkv_tmap(&tm, qkv, Bn, N, 3 * H * DH, DH, BKV);
-  if (rc != 0) return rc;
-  AttnArgs a;
-  a.o = static_cast<bf16*>(o);
-  a.lse = lse;
-  a.N = N;
-  a.H = H;
-  a.scale = 1.0f / sqrtf(static_cast<float>(DH));
-  a.scale_log2 = a.scale * 1.4426950408889634f;
+  AttnGroup g;
+  int total = 0;
+  for (int i = 0; i < count; ++i) {
+    int rc = qkv_tmap(&g.tm[i], ps[i].qkv, ps[i].Bn, ps[i].N, 3 * H * DH, DH, BKV);
+    if (rc != 0) return rc;
+    AttnArgs& a = g.a[i];
+    a.o = static_cast<bf16*>(ps[i].o);
+    a.lse = ps[i].lse;
+    a.N = ps[i].N;
+    a.H = H;
+    a.scale = 1.0f / sqrtf(static_cast<float>(DH));
+    a.scale_log2 = a.scale * 1.4426950408889634f;
+    total += ps[i].Bn * H * ((ps[i].N + BQ - 1) / BQ);
+    g.cta_end[i] = total;
+  }
+  for (int i = count; i < ATTN_MAX_GROUP; ++i) { g.tm[i] = g.tm[0]; g.a[i] = g.a[0]; g.cta_end[i] = total; }
+  g.count = count;
   static bool attr = false;
   if (!attr) {
     cudaFuncSetAttribute(attn_fwd_kernel<DH>, cudaFuncAttributeMaxDynamicSharedMemorySize, C_::SMEM_BYTES);
     attr = true;
   }
-  const int grid = Bn * H * ((N + BQ - 1) / BQ);
-  attn_fwd_kernel<DH><<<grid, 128, C_::SMEM_BYTES, st>>>(tm, a);
+  attn_fwd_kernel<DH><<<total, 128, C_::SMEM_BYTES, st>>>(g);
   cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? 0 : static_cast<int>(e);
 }
 
 }  // namespace
 
-// qkv [Bn*N, 3*H*dh] bf16 -> o [Bn*N, H*dh] bf16, lse [Bn, H, N] fp32.  dh in {16, 32, 64}.
-extern "C" int mb_attn_fwd(const void* qkv, void* o, float* lse, int Bn, int N, int H, int dh, void* stream) {
-  if (Bn == 0 || N == 0) return 0;
+// `count` (1..4) attention problems of one head shape as ONE launch (the longest sequences first gives the best tail).
+extern "C" int mb_attn_fwd_grouped(const mb_attn_problem* problems, int count, int H, int dh, void* stream) {
+  if (count < 1 || count > ATTN_MAX_GROUP) return -2;
+  mb_attn_problem live[ATTN_MAX_GROUP];
+  int n = 0;
+  for (int i = 0; i < count; ++i)
+    if (problems[i].Bn > 0 && problems[i].N > 0) live[n++] = problems[i];
+  if (n == 0) return 0;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   switch (dh) {
-    case 16: return launch_fwd<16>(qkv, o, lse, Bn, N, H, st);
-    case 32: return launch_fwd<32>(qkv, o, lse, Bn, N, H, st);
-    case 64: return launch_fwd<64>(qkv, o, lse, Bn, N, H, st);
+    case 16: return launch_fwd<16>(live, n, H, st);
+    case 32: return launch_fwd<32>(live, n, H, st);
+    case 64: return launch_fwd<64>(live, n, H, st);
     default: return -2;
   }
+}
+
+// qkv [Bn*N, 3*H*dh] bf16 -> o [Bn*N, H*dh] bf16, lse [Bn, H, N] fp32.  dh in {16, 32, 64}.
+extern "C" int mb_attn_fwd(const void* qkv, void* o, float* lse, int Bn, int N, int H, int dh, void* stream) {
+  const mb_attn_problem p{qkv, o, lse, nullptr, nullptr, nullptr, Bn, N};
+  return mb_attn_fwd_grouped(&p, 1, H, dh, stream);
 }

@@ -23,21 +23,55 @@ struct RowMap {
 // shared memory instead of 2 x NE registers, identity row maps without the integer divisions, the (still packed) loads
 // of the next TWO rows of every warp in flight while a row is reduced and written, and a grid of exactly the resident
 // CTAs (no partial wave).  Warp w of the grid walks rows w, w + W, w + 2W, ...; a lane owns NCH 16-byte column chunks.
+// Grouped: up to LN_MAX_GROUP problems of one width (the per-group stacks of one layer, which step in lockstep) share a
+// launch; CTAs are split between the problems in proportion to their rows (`cta_end` prefix), every CTA works on one
+// problem exactly as the single-problem kernel would.  One launch of 15 040 rows instead of four of 1 600 - 8 192.
 constexpr int LNF_THREADS = 256;
+constexpr int LN_MAX_GROUP = 4;
+
+struct LnFwdProblem {
+  const void* x;
+  const float* gamma;
+  const float* beta;
+  void* y;
+  float* mean;
+  float* rstd;
+  int rows;
+  RowMap in_map, out_map;
+  int cta_end;            // exclusive prefix of the CTAs given to problems 0 .. this one
+};
+struct LnFwdArgs {
+  LnFwdProblem p[LN_MAX_GROUP];
+  int count, d;
+  float eps;
+};
 
 template <typename T, int NCH, bool MAPPED>
 __global__ void __launch_bounds__(LNF_THREADS, (NCH <= 2 ? 4 : (NCH <= 3 ? 3 : 2)))
-layernorm_fwd_kernel(const T* __restrict__ x, const float* __restrict__ gamma, const float* __restrict__ beta,
-                     T* __restrict__ y, float* __restrict__ mean_out, float* __restrict__ rstd_out, int rows, int d,
-                     float eps, RowMap in_map, RowMap out_map) {
+layernorm_fwd_kernel(const __grid_constant__ LnFwdArgs args) {
+  int pi = 0, cta0 = 0;
+#pragma unroll
+  for (int i = 0; i < LN_MAX_GROUP - 1; ++i)
+    if (i + 1 < args.count && static_cast<int>(blockIdx.x) >= args.p[i].cta_end) { pi = i + 1; cta0 = args.p[i].cta_end; }
+  const LnFwdProblem& P = args.p[pi];
+  const T* __restrict__ x = static_cast<const T*>(P.x);
+  const float* __restrict__ gamma = P.gamma;
+  const float* __restrict__ beta = P.beta;
+  T* __restrict__ y = static_cast<T*>(P.y);
+  float* __restrict__ mean_out = P.mean;
+  float* __restrict__ rstd_out = P.rstd;
+  const int rows = P.rows, d = args.d;
+  const float eps = args.eps;
+  const RowMap in_map = P.in_map, out_map = P.out_map;
+  const int cta = static_cast<int>(blockIdx.x) - cta0, ncta = P.cta_end - cta0;
   constexpr int V = VecIO<T>::N;
   constexpr int NP = Vec2IO<T>::NP;          // float2 pairs per 16-byte chunk
   typedef typename VecIO<T>::Raw Raw;
   extern __shared__ __align__(16) float gb[];   // gamma [d] | beta [d]
   const int lane = threadIdx.x & 31;
   const int nwarps = blockDim.x >> 5;
-  const int gwarp = blockIdx.x * nwarps + (threadIdx.x >> 5);
-  const int total_warps = gridDim.x * nwarps;
+  const int gwarp = cta * nwarps + (threadIdx.x >> 5);
+  const int total_warps = ncta * nwarps;
   const int nvec = d / V;
   const float inv_d = 1.0f / static_cast<float>(d);
   for (int i = threadIdx.x; i < d; i += blockDim.x) {
@@ -108,38 +142,79 @@ layernorm_fwd_kernel(const T* __restrict__ x, const float* __restrict__ gamma, c
   }
 }
 
+struct mb_ln_fwd_problem {      // mirror of include/maestro_b200.h
+  const void* x;
+  const float* gamma;
+  const float* beta;
+  void* y;
+  float* mean;
+  float* rstd;
+  int rows;
+  int in_n, in_bs, in_off, out_n, out_bs, out_off;
+};
+
+// CTAs of a grouped launch: `cap` resident CTAs split in proportion to the rows, at least one per problem and no
+// more than a problem can use (rows / rows_per_cta)
+static int split_ctas(const int* rows, int count, int cap, int rows_per_cta, int* cta_end) {
+  long long total = 0;
+  for (int i = 0; i < count; ++i) total += rows[i];
+  int used = 0;
+  for (int i = 0; i < count; ++i) {
+    long long want = (static_cast<long long>(rows[i]) * cap + total - 1) / total;
+    const long long mx = mb_ceil_div(rows[i], rows_per_cta);
+    if (want > mx) want = mx;
+    if (want < 1) want = 1;
+    used += static_cast<int>(want);
+    cta_end[i] = used;
+  }
+  return used;
+}
+
 template <typename T, int NCH>
-static void launch_ln_fwd(const void* x, const float* gamma, const float* beta, void* y, float* mean, float* rstd,
-                          int rows, int d, float eps, RowMap im, RowMap om, cudaStream_t st) {
+static void launch_ln_fwd(const mb_ln_fwd_problem* ps, int count, int d, float eps, cudaStream_t st) {
   const int wpb = LNF_THREADS / 32;
-  const bool mapped = !(im.n == rows && im.off == 0 && om.n == rows && om.off == 0);
+  bool mapped = false;
+  for (int i = 0; i < count; ++i)
+    mapped = mapped || !(ps[i].in_n == ps[i].rows && ps[i].in_off == 0 && ps[i].out_n == ps[i].rows && ps[i].out_off == 0);
   auto kern = mapped ? layernorm_fwd_kernel<T, NCH, true> : layernorm_fwd_kernel<T, NCH, false>;
   const size_t smem = 2 * static_cast<size_t>(d) * sizeof(float);
-  // persistent grid of exactly the resident CTAs; at least 2 rows per warp (gamma / beta are staged once per CTA)
+  // persistent grid of (at most) exactly the resident CTAs; at least 2 rows per warp (gamma / beta are staged per CTA)
   static int per_sm[2] = {0, 0};
   if (per_sm[mapped] == 0) {
     int n = 0;
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kern, LNF_THREADS, smem);
     per_sm[mapped] = n > 0 ? n : 1;
   }
-  long long blocks = mb_ceil_div(static_cast<long long>(rows), static_cast<long long>(wpb) * 2);
-  const long long cap = 148LL * per_sm[mapped];
-  if (blocks > cap) blocks = cap;
-  if (blocks < 1) blocks = 1;
-  kern<<<static_cast<int>(blocks), LNF_THREADS, smem, st>>>(static_cast<const T*>(x), gamma, beta, static_cast<T*>(y),
-                                                            mean, rstd, rows, d, eps, im, om);
+  LnFwdArgs a;
+  int rows[LN_MAX_GROUP], cta_end[LN_MAX_GROUP];
+  for (int i = 0; i < count; ++i) rows[i] = ps[i].rows;
+  const int blocks = split_ctas(rows, count, 148 * per_sm[mapped], wpb * 2, cta_end);
+  for (int i = 0; i < count; ++i) {
+    LnFwdProblem& q = a.p[i];
+    q.x = ps[i].x; q.gamma = ps[i].gamma; q.beta = ps[i].beta; q.y = ps[i].y; q.mean = ps[i].mean; q.rstd = ps[i].rstd;
+    q.rows = ps[i].rows;
+    q.in_map = RowMap{ps[i].in_n, ps[i].in_bs, ps[i].in_off};
+    q.out_map = RowMap{ps[i].out_n, ps[i].out_bs, ps[i].out_off};
+    q.cta_end = cta_end[i];
+  }
+  for (int i = count; i < LN_MAX_GROUP; ++i) a.p[i] = a.p[0];
+  a.count = count; a.d = d; a.eps = eps;
+  kern<<<blocks, LNF_THREADS, smem, st>>>(a);
 }
 
-extern "C" int mb_layernorm_fwd(const void* x, const float* gamma, const float* beta, void* y, float* mean,
-                                float* rstd, int dtype, int rows, int d, float eps, int in_n, int in_bs, int in_off,
-                                int out_n, int out_bs, int out_off, void* stream) {
-  if (rows == 0) return 0;
+extern "C" int mb_layernorm_fwd_grouped(const mb_ln_fwd_problem* problems, int count, int dtype, int d, float eps,
+                                        void* stream) {
+  if (count < 1 || count > LN_MAX_GROUP) return -2;
   if (d > 1024 || d % 8 != 0) return -2;
-  RowMap im{in_n, in_bs, in_off}, om{out_n, out_bs, out_off};
+  mb_ln_fwd_problem live[LN_MAX_GROUP];
+  int n = 0;
+  for (int i = 0; i < count; ++i)
+    if (problems[i].rows > 0) live[n++] = problems[i];
+  if (n == 0) return 0;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-#define LNF_CASE(n)                                                                                  \
-  case n:                                                                                            \
-    MB_DISPATCH_DTYPE(dtype, T, (launch_ln_fwd<T, n>(x, gamma, beta, y, mean, rstd, rows, d, eps, im, om, st))); \
+#define LNF_CASE(k)                                                                  \
+  case k:                                                                            \
+    MB_DISPATCH_DTYPE(dtype, T, (launch_ln_fwd<T, k>(live, n, d, eps, st)));         \
     break;
   const int vec = dtype == MB_DTYPE_F32 ? 4 : 8;
   const int nch = mb_ceil_div(d / vec, 32);
@@ -150,6 +225,13 @@ extern "C" int mb_layernorm_fwd(const void* x, const float* gamma, const float* 
 #undef LNF_CASE
   MB_CHECK_LAUNCH();
   return 0;
+}
+
+extern "C" int mb_layernorm_fwd(const void* x, const float* gamma, const float* beta, void* y, float* mean,
+                                float* rstd, int dtype, int rows, int d, float eps, int in_n, int in_bs, int in_off,
+                                int out_n, int out_bs, int out_off, void* stream) {
+  const mb_ln_fwd_problem p{x, gamma, beta, y, mean, rstd, rows, in_n, in_bs, in_off, out_n, out_bs, out_off};
+  return mb_layernorm_fwd_grouped(&p, 1, dtype, d, eps, stream);
 }
 
 // ------------------------------------------------------------------ LayerNorm backward
@@ -168,12 +250,47 @@ extern "C" int mb_layernorm_fwd(const void* x, const float* gamma, const float* 
 // reduced together, folded scalars (one FFMA2 chain per output pair) roughly halve the count.
 constexpr int LNB_THREADS = 384;
 
+struct LnBwdProblem {
+  const void* dy;
+  const void* x;
+  const float* mean;
+  const float* rstd;
+  const float* gamma;
+  const void* dres;
+  void* dx;
+  float* dgamma;
+  float* dbeta;
+  float* dbias;
+  int rows;
+  RowMap in_map, out_map;
+  int cta_end;
+};
+struct LnBwdArgs {
+  LnBwdProblem p[LN_MAX_GROUP];
+  int count, d, depth;
+};
+
 template <typename T, int NCH, bool MAPPED>
 __global__ void __launch_bounds__(LNB_THREADS, 1)
-layernorm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x, const float* __restrict__ mean_in,
-                     const float* __restrict__ rstd_in, const float* __restrict__ gamma, const T* __restrict__ dres,
-                     T* __restrict__ dx, float* __restrict__ dgamma, float* __restrict__ dbeta,
-                     float* __restrict__ dbias, int rows, int d, RowMap in_map, RowMap out_map, int depth) {
+layernorm_bwd_kernel(const __grid_constant__ LnBwdArgs args) {
+  int pi = 0, cta0 = 0;
+#pragma unroll
+  for (int i = 0; i < LN_MAX_GROUP - 1; ++i)
+    if (i + 1 < args.count && static_cast<int>(blockIdx.x) >= args.p[i].cta_end) { pi = i + 1; cta0 = args.p[i].cta_end; }
+  const LnBwdProblem& P = args.p[pi];
+  const T* __restrict__ dy = static_cast<const T*>(P.dy);
+  const T* __restrict__ x = static_cast<const T*>(P.x);
+  const float* __restrict__ mean_in = P.mean;
+  const float* __restrict__ rstd_in = P.rstd;
+  const float* __restrict__ gamma = P.gamma;
+  const T* __restrict__ dres = static_cast<const T*>(P.dres);
+  T* __restrict__ dx = static_cast<T*>(P.dx);
+  float* __restrict__ dgamma = P.dgamma;
+  float* __restrict__ dbeta = P.dbeta;
+  float* __restrict__ dbias = P.dbias;
+  const int rows = P.rows, d = args.d, depth = args.depth;
+  const RowMap in_map = P.in_map, out_map = P.out_map;
+  const int cta = static_cast<int>(blockIdx.x) - cta0, ncta = P.cta_end - cta0;
   constexpr int V = VecIO<T>::N;
   constexpr int NP = Vec2IO<T>::NP;
   constexpr int NE2 = NCH * NP;
@@ -189,8 +306,8 @@ layernorm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x, const fl
   const uint32_t row_bytes = static_cast<uint32_t>(d) * sizeof(T);
   uint8_t* ring = reinterpret_cast<uint8_t*>(reinterpret_cast<uint64_t*>(gam + d) + nwarps * depth) +
                   static_cast<size_t>(wid) * depth * 3 * row_bytes;
-  const int gwarp = blockIdx.x * nwarps + wid;
-  const int total_warps = gridDim.x * nwarps;
+  const int gwarp = cta * nwarps + wid;
+  const int total_warps = ncta * nwarps;
   const int nvec = d / V;
   const bool has_res = dres != nullptr;
   const bool has_bias = dbias != nullptr;
@@ -319,16 +436,25 @@ layernorm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x, const fl
   }
 }
 
+struct mb_ln_bwd_problem {      // mirror of include/maestro_b200.h
+  const void* dy;
+  const void* x;
+  const float* mean;
+  const float* rstd;
+  const float* gamma;
+  const void* dres;
+  void* dx;
+  float* dgamma;
+  float* dbeta;
+  float* dbias;
+  int rows;
+  int in_n, in_bs, in_off, out_n, out_bs, out_off;
+};
+
 template <typename T>
-static int launch_ln_bwd(const void* dy, const void* x, const float* mean, const float* rstd, const float* gamma,
-                         const void* dres, void* dx, float* dgamma, float* dbeta, float* dbias, int rows, int d,
-                         RowMap im, RowMap om, cudaStream_t st) {
+static int launch_ln_bwd(const mb_ln_bwd_problem* ps, int count, int d, cudaStream_t st) {
   constexpr int V = VecIO<T>::N;
   const int nwarps = LNB_THREADS / 32;
-  // at least 4 rows per warp before the per-CTA reduction tail pays off; small groups then leave SMs to the
-  // other groups' kernels that run concurrently on forked streams
-  int blocks = mb_ceil_div(rows, nwarps * 4);
-  if (blocks > 148) blocks = 148;
   // shared memory: column partials + gamma + barriers + per-warp row ring (depth slots of x / dy / dres rows)
   const size_t row_bytes = static_cast<size_t>(d) * sizeof(T);
   const size_t fixed = 4 * static_cast<size_t>(d) * sizeof(float);
@@ -337,7 +463,24 @@ static int launch_ln_bwd(const void* dy, const void* x, const float* mean, const
   if (depth < 1) depth = 1;
   const size_t smem = fixed + static_cast<size_t>(nwarps) * depth * (8 + 3 * row_bytes);
   const int nch = mb_ceil_div(d / V, 32);
-  const bool mapped = !(im.n == rows && im.off == 0 && om.n == rows && om.off == 0);
+  bool mapped = false;
+  for (int i = 0; i < count; ++i)
+    mapped = mapped || !(ps[i].in_n == ps[i].rows && ps[i].in_off == 0 && ps[i].out_n == ps[i].rows && ps[i].out_off == 0);
+  LnBwdArgs a;
+  int rows[LN_MAX_GROUP], cta_end[LN_MAX_GROUP];
+  for (int i = 0; i < count; ++i) rows[i] = ps[i].rows;
+  // one CTA per SM; at least 4 rows per warp before the per-CTA reduction tail pays off
+  const int blocks = split_ctas(rows, count, 148, nwarps * 4, cta_end);
+  for (int i = 0; i < count; ++i) {
+    LnBwdProblem& q = a.p[i];
+    q.dy = ps[i].dy; q.x = ps[i].x; q.mean = ps[i].mean; q.rstd = ps[i].rstd; q.gamma = ps[i].gamma; q.dres = ps[i].dres;
+    q.dx = ps[i].dx; q.dgamma = ps[i].dgamma; q.dbeta = ps[i].dbeta; q.dbias = ps[i].dbias; q.rows = ps[i].rows;
+    q.in_map = RowMap{ps[i].in_n, ps[i].in_bs, ps[i].in_off};
+    q.out_map = RowMap{ps[i].out_n, ps[i].out_bs, ps[i].out_off};
+    q.cta_end = cta_end[i];
+  }
+  for (int i = count; i < LN_MAX_GROUP; ++i) a.p[i] = a.p[0];
+  a.count = count; a.d = d; a.depth = depth;
 #define MB_LNB(N_)                                                                                              \
   case N_:                                                                                                      \
     {                                                                                                           \
@@ -348,9 +491,7 @@ static int launch_ln_bwd(const void* dy, const void* x, const float* mean, const
         attr_done = true;                                                                                       \
       }                                                                                                         \
       auto kern = mapped ? layernorm_bwd_kernel<T, N_, true> : layernorm_bwd_kernel<T, N_, false>;              \
-      kern<<<blocks, LNB_THREADS, smem, st>>>(                                                                  \
-          static_cast<const T*>(dy), static_cast<const T*>(x), mean, rstd, gamma, static_cast<const T*>(dres),  \
-          static_cast<T*>(dx), dgamma, dbeta, dbias, rows, d, im, om, depth);                                   \
+      kern<<<blocks, LNB_THREADS, smem, st>>>(a);                                                               \
     }                                                                                                           \
     break;
   switch (nch) {
@@ -362,21 +503,31 @@ static int launch_ln_bwd(const void* dy, const void* x, const float* mean, const
 }
 
 // dbias may be null.  dgamma / dbeta / dbias accumulate (fp32).
-extern "C" int mb_layernorm_bwd(const void* dy, const void* x, const float* mean, const float* rstd,
-                                const float* gamma, const void* dres, void* dx, float* dgamma, float* dbeta,
-                                float* dbias, int dtype, int rows, int d, int in_n, int in_bs, int in_off, int out_n,
-                                int out_bs, int out_off, void* stream) {
-  if (rows == 0) return 0;
+extern "C" int mb_layernorm_bwd_grouped(const mb_ln_bwd_problem* problems, int count, int dtype, int d, void* stream) {
+  if (count < 1 || count > LN_MAX_GROUP) return -2;
   if (d > 1024 || d % 8 != 0) return -2;
-  RowMap im{in_n, in_bs, in_off}, om{out_n, out_bs, out_off};
+  mb_ln_bwd_problem live[LN_MAX_GROUP];
+  int n = 0;
+  for (int i = 0; i < count; ++i)
+    if (problems[i].rows > 0) live[n++] = problems[i];
+  if (n == 0) return 0;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   int rc;
-  if (dtype == MB_DTYPE_F32) rc = launch_ln_bwd<float>(dy, x, mean, rstd, gamma, dres, dx, dgamma, dbeta, dbias, rows, d, im, om, st);
-  else if (dtype == MB_DTYPE_BF16) rc = launch_ln_bwd<bf16>(dy, x, mean, rstd, gamma, dres, dx, dgamma, dbeta, dbias, rows, d, im, om, st);
+  if (dtype == MB_DTYPE_F32) rc = launch_ln_bwd<float>(live, n, d, st);
+  else if (dtype == MB_DTYPE_BF16) rc = launch_ln_bwd<bf16>(live, n, d, st);
   else return -1;
   if (rc != 0) return rc;
   MB_CHECK_LAUNCH();
   return 0;
+}
+
+extern "C" int mb_layernorm_bwd(const void* dy, const void* x, const float* mean, const float* rstd,
+                                const float* gamma, const void* dres, void* dx, float* dgamma, float* dbeta,
+                                float* dbias, int dtype, int rows, int d, int in_n, int in_bs, int in_off, int out_n,
+                                int out_bs, int out_off, void* stream) {
+  const mb_ln_bwd_problem p{dy, x, mean, rstd, gamma, dres, dx, dgamma, dbeta, dbias, rows,
+                            in_n, in_bs, in_off, out_n, out_bs, out_off};
+  return mb_layernorm_bwd_grouped(&p, 1, dtype, d, stream);
 }
 
 // ------------------------------------------------------------------ GroupNorm(1, E) of the patch embedding

@@ -168,7 +168,9 @@ class PretrainEngine:
         # "flash": fused tcgen05 attention (bf16, dh in {16, 32, 64}); "gemm": materialised scores (fp32 check mode)
         flash_ok = dtype == torch.bfloat16 and all(d in (16, 32, 64) for d in (hp["dim_head"], hp["decoder_dim_head"]))
         self.attn_impl = "flash" if flash_ok else "gemm"
-        self.multi_stream = self.device.type == "cuda" and self.attn_impl == "flash"
+        import os
+        self.multi_stream = (self.device.type == "cuda" and self.attn_impl == "flash"
+                             and os.environ.get("MB_MULTI_STREAM", "1") != "0")       # (0: diagnostic, serial launches)
         self._streams: list = []
         self._build_tables(fac_abs_enc)
         self._build_params()
@@ -462,14 +464,15 @@ class PretrainEngine:
         h1 = [self._new(r, dim) for r in rows]
         m1 = [self._new(r, dtype=f32) for r in rows]
         r1 = [self._new(r, dtype=f32) for r in rows]
-        self._par([lambda i=i: K.layernorm_fwd(xs[i], P[pres[i] + "0.norm.weight"], P[pres[i] + "0.norm.bias"], h1[i],
-                                               m1[i], r1[i], rows[i], dim) for i in range(n)])
+        K.layernorm_fwd_grouped([(xs[i], P[pres[i] + "0.norm.weight"], P[pres[i] + "0.norm.bias"], h1[i], m1[i], r1[i],
+                                  rows[i], None, None) for i in range(n)], dim)
         qkv = [self._new(r, 3 * inner) for r in rows]
         self.lin_fwd_g([(h1[i], rows[i], pres[i] + "0.to_qkv.weight", None, qkv[i], None, None) for i in range(n)])
         if self.attn_impl == "flash":
             o = [self._new(r, inner) for r in rows]
             att = [self._new(b, H, N, dtype=f32) for b, N in zip(Bn, Ns)]   # log-sum-exp per (sample, head, query)
-            self._par([lambda i=i: K.attn_fwd(qkv[i], o[i], att[i], Bn[i], Ns[i], H, dh) for i in range(n)])
+            order = sorted(range(n), key=lambda i: -Ns[i])            # longest sequences first: best tail of the grid
+            K.attn_fwd_grouped([(qkv[i], o[i], att[i], Bn[i], Ns[i]) for i in order], H, dh)
         else:
             o, att = [], []
             for i in range(n):
@@ -482,8 +485,8 @@ class PretrainEngine:
         h2 = [self._new(r, dim) for r in rows]
         m2 = [self._new(r, dtype=f32) for r in rows]
         r2 = [self._new(r, dtype=f32) for r in rows]
-        self._par([lambda i=i: K.layernorm_fwd(x2[i], P[pres[i] + "1.net.0.weight"], P[pres[i] + "1.net.0.bias"], h2[i],
-                                               m2[i], r2[i], rows[i], dim) for i in range(n)])
+        K.layernorm_fwd_grouped([(x2[i], P[pres[i] + "1.net.0.weight"], P[pres[i] + "1.net.0.bias"], h2[i], m2[i], r2[i],
+                                  rows[i], None, None) for i in range(n)], dim)
         u = [self._new(r, mlp) for r in rows]
         a = [self._new(r, mlp) for r in rows]
         self.lin_fwd_g([(h2[i], rows[i], pres[i] + "1.net.1.weight", pres[i] + "1.net.1.bias", a[i], u[i], None)
@@ -512,24 +515,24 @@ class PretrainEngine:
         self.lin_bwd_g([(du[i], rows[i], h2[i], pres[i] + "1.net.1.weight", None, dh2[i], None) for i in range(n)])
         del du
         dx2 = [self._new(r, dim) for r in rows]
-        self._par([lambda i=i: K.layernorm_bwd(dh2[i], x2[i], m2[i], r2[i], P[pres[i] + "1.net.0.weight"], dx3[i], dx2[i],
-                                               G[pres[i] + "1.net.0.weight"], G[pres[i] + "1.net.0.bias"], rows[i], dim,
-                                               dbias=G[pres[i] + "0.to_out.0.bias"]) for i in range(n)])
+        K.layernorm_bwd_grouped([(dh2[i], x2[i], m2[i], r2[i], P[pres[i] + "1.net.0.weight"], dx3[i], dx2[i],
+                                  G[pres[i] + "1.net.0.weight"], G[pres[i] + "1.net.0.bias"], G[pres[i] + "0.to_out.0.bias"],
+                                  rows[i], None, None) for i in range(n)], dim)
         do = [self._new(r, inner) for r in rows]
         self.lin_bwd_g([(dx2[i], rows[i], o[i], pres[i] + "0.to_out.0.weight", None, do[i], None) for i in range(n)])
         if self.attn_impl == "flash":
             dqkv = [self._new(r, 3 * inner) for r in rows]
             delta = [self._new(b, H, N, dtype=torch.float32) for b, N in zip(Bn, Ns)]
-            self._par([lambda i=i: K.attn_bwd(qkv[i], o[i], do[i], att[i], dqkv[i], delta[i], Bn[i], Ns[i], H, dh)
-                       for i in range(n)])
+            order = sorted(range(n), key=lambda i: -Ns[i])
+            K.attn_bwd_grouped([(qkv[i], o[i], do[i], att[i], dqkv[i], delta[i], Bn[i], Ns[i]) for i in order], H, dh)
         else:
             dqkv = [self.attn_bwd(do[i], qkv[i], att[i], Bn[i], Ns[i], H, dh, o=o[i]) for i in range(n)]
         dh1 = dh2  # reuse
         self.lin_bwd_g([(dqkv[i], rows[i], h1[i], pres[i] + "0.to_qkv.weight", None, dh1[i], None) for i in range(n)])
         dx = [self._new(r, dim) for r in rows]
-        self._par([lambda i=i: K.layernorm_bwd(dh1[i], x[i], m1[i], r1[i], P[pres[i] + "0.norm.weight"], dx2[i], dx[i],
-                                               G[pres[i] + "0.norm.weight"], G[pres[i] + "0.norm.bias"], rows[i], dim,
-                                               dbias=sinks[i] if sinks is not None else None) for i in range(n)])
+        K.layernorm_bwd_grouped([(dh1[i], x[i], m1[i], r1[i], P[pres[i] + "0.norm.weight"], dx2[i], dx[i],
+                                  G[pres[i] + "0.norm.weight"], G[pres[i] + "0.norm.bias"],
+                                  sinks[i] if sinks is not None else None, rows[i], None, None) for i in range(n)], dim)
         return dx
 
     def stacks_fwd(self, prefixes, xs, Bn, Ns, dim, depth, H, dh, mlp, save=True):

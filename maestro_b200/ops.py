@@ -132,6 +132,37 @@ class Kernels:
         _ck(self.L.mb_layernorm_bwd(_p(dy), _p(x), _p(mean), _p(rstd), _p(gamma), _p(dres), _p(dx), _p(dgamma),
                                     _p(dbeta), _p(dbias), _dt(x), rows, d, *im, *om, self._s()), "layernorm_bwd")
 
+    def layernorm_fwd_grouped(self, items, d, eps=1e-5):
+        """``items``: [(x, gamma, beta, y, mean, rstd, rows, in_map, out_map)] of one width -- ONE launch (chunks of 4)."""
+        for i in range(0, len(items), 4):
+            chunk = items[i:i + 4]
+            arr = (_lib.LnFwdProblem * len(chunk))()
+            for q, (x, gamma, beta, y, mean, rstd, rows, in_map, out_map) in zip(arr, chunk):
+                for t in (x, gamma, beta, y):
+                    _p(t)
+                q.x, q.gamma, q.beta, q.y = x.data_ptr(), gamma.data_ptr(), beta.data_ptr(), y.data_ptr()
+                q.mean, q.rstd, q.rows = mean.data_ptr(), rstd.data_ptr(), rows
+                (q.in_n, q.in_bs, q.in_off), (q.out_n, q.out_bs, q.out_off) = _rowmap(in_map, rows), _rowmap(out_map, rows)
+            self.launches += 1
+            _ck(self.L.mb_layernorm_fwd_grouped(arr, len(chunk), _dt(chunk[0][0]), d, C.c_float(eps), self._s()),
+                "layernorm_fwd_grouped")
+
+    def layernorm_bwd_grouped(self, items, d):
+        """``items``: [(dy, x, mean, rstd, gamma, dres, dx, dgamma, dbeta, dbias, rows, in_map, out_map)] -- ONE launch."""
+        for i in range(0, len(items), 4):
+            chunk = items[i:i + 4]
+            arr = (_lib.LnBwdProblem * len(chunk))()
+            for q, (dy, x, mean, rstd, gamma, dres, dx, dgamma, dbeta, dbias, rows, in_map, out_map) in zip(arr, chunk):
+                _p(dy)
+                q.dy, q.x, q.mean, q.rstd, q.gamma = dy.data_ptr(), x.data_ptr(), mean.data_ptr(), rstd.data_ptr(), gamma.data_ptr()
+                q.dres = dres.data_ptr() if dres is not None else None
+                q.dx, q.dgamma, q.dbeta = dx.data_ptr(), dgamma.data_ptr(), dbeta.data_ptr()
+                q.dbias = dbias.data_ptr() if dbias is not None else None
+                q.rows = rows
+                (q.in_n, q.in_bs, q.in_off), (q.out_n, q.out_bs, q.out_off) = _rowmap(in_map, rows), _rowmap(out_map, rows)
+            self.launches += 1
+            _ck(self.L.mb_layernorm_bwd_grouped(arr, len(chunk), _dt(chunk[0][1]), d, self._s()), "layernorm_bwd_grouped")
+
     def gn_stats(self, y, sums, n_img):
         self.launches += 1
         _ck(self.L.mb_gn_stats(_p(y), _dt(y), _p(sums), n_img, C.c_longlong(y.numel() // n_img), self._s()), "gn_stats")
@@ -295,6 +326,29 @@ class Kernels:
         self.launches += 2
         _ck(self.L.mb_attn_bwd(_p(qkv), _p(o), _p(do), _p(lse), _p(dqkv), _p(delta), Bn, N, H, dh, self._s()),
             "attn_bwd")
+
+    def attn_fwd_grouped(self, items, H, dh):
+        """``items``: [(qkv, o, lse, Bn, N)] of one head shape -- ONE launch (chunks of 4)."""
+        for i in range(0, len(items), 4):
+            chunk = items[i:i + 4]
+            arr = (_lib.AttnProblem * len(chunk))()
+            for q, (qkv, o, lse, Bn, N) in zip(arr, chunk):
+                _p(qkv)
+                q.qkv, q.o, q.lse, q.Bn, q.N = qkv.data_ptr(), o.data_ptr(), lse.data_ptr(), Bn, N
+            self.launches += 1
+            _ck(self.L.mb_attn_fwd_grouped(arr, len(chunk), H, dh, self._s()), "attn_fwd_grouped")
+
+    def attn_bwd_grouped(self, items, H, dh):
+        """``items``: [(qkv, o, do, lse, dqkv, delta, Bn, N)] -- TWO launches (dQ, dK / dV) for the whole group."""
+        for i in range(0, len(items), 4):
+            chunk = items[i:i + 4]
+            arr = (_lib.AttnProblem * len(chunk))()
+            for q, (qkv, o, do, lse, dqkv, delta, Bn, N) in zip(arr, chunk):
+                _p(qkv)
+                q.qkv, q.o, q.lse, q.Bn, q.N = qkv.data_ptr(), o.data_ptr(), lse.data_ptr(), Bn, N
+                q.d_o, q.dqkv, q.delta = do.data_ptr(), dqkv.data_ptr(), delta.data_ptr()
+            self.launches += 2
+            _ck(self.L.mb_attn_bwd_grouped(arr, len(chunk), H, dh, self._s()), "attn_bwd_grouped")
 
     # ------------------------------------------------------------------ optimiser
     def adamw_step(self, p, g, m, v, shadow, hyper, zero_grad):

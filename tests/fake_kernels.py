@@ -118,6 +118,14 @@ class FakeKernels:
         if dbias is not None:
             dbias += out.sum(0)
 
+    def layernorm_fwd_grouped(self, items, d, eps=1e-5):
+        for x, gamma, beta, y, mean, rstd, rows, in_map, out_map in items:
+            self.layernorm_fwd(x, gamma, beta, y, mean, rstd, rows, d, eps, in_map, out_map)
+
+    def layernorm_bwd_grouped(self, items, d):
+        for dy, x, mean, rstd, gamma, dres, dx, dgamma, dbeta, dbias, rows, in_map, out_map in items:
+            self.layernorm_bwd(dy, x, mean, rstd, gamma, dres, dx, dgamma, dbeta, rows, d, in_map, out_map, dbias=dbias)
+
     def gn_stats(self, y, sums, n_img):
         v = y.reshape(n_img, -1).double()
         sums[:, 0] += v.sum(1)
@@ -305,6 +313,14 @@ class FakeKernels:
         dqkv.copy_(out.to(dqkv.dtype))
 
     # ------------------------------------------------------------------ optimiser
+    def attn_fwd_grouped(self, items, H, dh):
+        for qkv, o, lse, Bn, N in items:
+            self.attn_fwd(qkv, o, lse, Bn, N, H, dh)
+
+    def attn_bwd_grouped(self, items, H, dh):
+        for qkv, o, do, lse, dqkv, delta, Bn, N in items:
+            self.attn_bwd(qkv, o, do, lse, dqkv, delta, Bn, N, H, dh)
+
     def adamw_step(self, p, g, m, v, shadow, hyper, zero_grad):
         lr, b1, b2, eps, wd, bc1, bc2, gs = [float(x) for x in hyper.tolist()]
         gr = g * gs

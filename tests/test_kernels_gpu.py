@@ -554,3 +554,68 @@ def test_mask_tables_with_period(KK):
     assert torch.equal(a[0], b[0]) and torch.equal(a[1], b[1])
     close(a[2], b[2], rtol=1e-5, atol=1e-5)
     close(a[3], b[3], rtol=1e-4, atol=1e-4)
+
+
+# ------------------------------------------------------------------ grouped launches (one kernel for the stacks of a layer)
+@pytest.mark.parametrize("dt", DT)
+@pytest.mark.parametrize("d", [512, 768, 64])
+def test_layernorm_grouped_equals_single(KK, dt, d):
+    K = KK[0]
+    rows = [8192, 2048, 3200, 37]
+    xs = [rnd(r, d, dt=dt, seed=i) for i, r in enumerate(rows)]
+    dys = [rnd(r, d, dt=dt, seed=10 + i) for i, r in enumerate(rows)]
+    dres = [rnd(r, d, dt=dt, seed=20 + i) for i, r in enumerate(rows)]
+    gs = [rnd(d, seed=30 + i) + 1 for i in range(4)]
+    bs = [rnd(d, seed=40 + i) for i in range(4)]
+
+    def run(grouped):
+        ys = [torch.zeros_like(x) for x in xs]
+        ms = [torch.zeros(r, device="cuda") for r in rows]
+        rs = [torch.zeros(r, device="cuda") for r in rows]
+        dxs = [torch.zeros_like(x) for x in xs]
+        dg = [torch.zeros(d, device="cuda") for _ in rows]
+        db = [torch.zeros(d, device="cuda") for _ in rows]
+        dbias = [torch.zeros(d, device="cuda") for _ in rows]
+        if grouped:
+            K.layernorm_fwd_grouped([(xs[i], gs[i], bs[i], ys[i], ms[i], rs[i], rows[i], None, None) for i in range(4)], d)
+            K.layernorm_bwd_grouped([(dys[i], xs[i], ms[i], rs[i], gs[i], dres[i] if i != 1 else None, dxs[i], dg[i], db[i],
+                                      dbias[i] if i != 2 else None, rows[i], None, None) for i in range(4)], d)
+        else:
+            for i in range(4):
+                K.layernorm_fwd(xs[i], gs[i], bs[i], ys[i], ms[i], rs[i], rows[i], d)
+                K.layernorm_bwd(dys[i], xs[i], ms[i], rs[i], gs[i], dres[i] if i != 1 else None, dxs[i], dg[i], db[i],
+                                rows[i], d, dbias=dbias[i] if i != 2 else None)
+        torch.cuda.synchronize()
+        return ys, ms, rs, dxs, dg, db, dbias
+    a, b = run(True), run(False)
+    for i in range(4):
+        assert torch.equal(a[0][i], b[0][i]) and torch.equal(a[1][i], b[1][i]) and torch.equal(a[2][i], b[2][i])
+        assert torch.equal(a[3][i], b[3][i])
+        for k in (4, 5, 6):                       # column sums: atomics in a different order
+            close(a[k][i], b[k][i], rtol=1e-4, atol=1e-3)
+
+
+@pytest.mark.parametrize("H,dh,Ns,Bn", [(12, 64, [256, 64, 100, 50], 8), (16, 32, [1024, 256, 400, 200], 2), (2, 16, [9, 2], 5)])
+def test_attention_grouped_equals_single(KK, H, dh, Ns, Bn):
+    K = KK[0]
+    bf = torch.bfloat16
+    qkv = [rnd(Bn * N, 3 * H * dh, dt=bf, seed=i) for i, N in enumerate(Ns)]
+    do = [rnd(Bn * N, H * dh, dt=bf, seed=9 + i) for i, N in enumerate(Ns)]
+
+    def run(grouped):
+        o = [torch.zeros(Bn * N, H * dh, dtype=bf, device="cuda") for N in Ns]
+        lse = [torch.zeros(Bn, H, N, device="cuda") for N in Ns]
+        dqkv = [torch.zeros_like(q) for q in qkv]
+        delta = [torch.zeros(Bn, H, N, device="cuda") for N in Ns]
+        if grouped:
+            K.attn_fwd_grouped([(qkv[i], o[i], lse[i], Bn, N) for i, N in enumerate(Ns)], H, dh)
+            K.attn_bwd_grouped([(qkv[i], o[i], do[i], lse[i], dqkv[i], delta[i], Bn, N) for i, N in enumerate(Ns)], H, dh)
+        else:
+            for i, N in enumerate(Ns):
+                K.attn_fwd(qkv[i], o[i], lse[i], Bn, N, H, dh)
+                K.attn_bwd(qkv[i], o[i], do[i], lse[i], dqkv[i], delta[i], Bn, N, H, dh)
+        torch.cuda.synchronize()
+        return o, lse, dqkv
+    a, b = run(True), run(False)
+    for i in range(len(Ns)):
+        assert torch.equal(a[0][i], b[0][i]) and torch.equal(a[1][i], b[1][i]) and torch.equal(a[2][i], b[2][i]), i
