@@ -122,7 +122,7 @@ def hbm_kernel_rooflines(K, eng, opt, dev, hbm_peak):
     bf, f32, Bt = torch.bfloat16, torch.float32, 32
     out = []
 
-    def run(name, fns, nbytes, reps=12):
+    def clock(fns, reps):
         for f in fns:
             f()
         torch.cuda.synchronize()
@@ -132,10 +132,21 @@ def hbm_kernel_rooflines(K, eng, opt, dev, hbm_peak):
             fns[i % len(fns)]()
         e1.record()
         torch.cuda.synchronize()
-        us = e0.elapsed_time(e1) * 1e3 / reps
+        return e0.elapsed_time(e1) * 1e3 / reps
+
+    def run(name, fns, nbytes, reps=12, copy_pairs=None):
+        """``copy_pairs``: [(dst, src)] device-to-device copies moving the SAME number of bytes per call (read + write)
+        as the kernel's algorithmic traffic: what this harness gets out of HBM for a launch of that size (the 6.5 TB/s
+        peak is a 2 GiB copy; a 67 MB launch is over before the memory system is in steady state)."""
+        us = clock(fns, reps)
         gbs = nbytes / us / 1e3
-        out.append({"kernel": name, "us": round(us, 2), "bytes": int(nbytes), "achieved": round(gbs, 1), "unit": "GB/s",
-                    "frac": round(gbs / hbm_peak, 3)})
+        rec = {"kernel": name, "us": round(us, 2), "bytes": int(nbytes), "achieved": round(gbs, 1), "unit": "GB/s",
+               "frac": round(gbs / hbm_peak, 3)}
+        if copy_pairs:
+            cus = clock([lambda p=p: p[0].copy_(p[1]) for p in copy_pairs], reps)
+            rec["same_size_copy_us"] = round(cus, 2)
+            rec["frac_of_same_size_copy"] = round(cus / us, 3)
+        out.append(rec)
 
     rows, d = Bt * 1024, 512
     sets = []
@@ -147,10 +158,11 @@ def hbm_kernel_rooflines(K, eng, opt, dev, hbm_peak):
     dg, db, dbias = (torch.zeros(d, device=dev) for _ in range(3))
     run("layernorm_fwd_kernel [32768 x 512 bf16]",
         [lambda s=s: K.layernorm_fwd(s["x"], gamma, beta, s["y"], s["mean"], s["rstd"], rows, d) for s in sets],
-        rows * d * 2 * 2)
+        rows * d * 2 * 2, copy_pairs=[(s["y"], s["x"]) for s in sets])
     run("layernorm_bwd_kernel [32768 x 512 bf16, + dgamma / dbeta / bias grad]",
         [lambda s=s: K.layernorm_bwd(s["dy"], s["x"], s["mean"], s["rstd"], gamma, s["dres"], s["dx"], dg, db, rows, d,
-                                     dbias=dbias) for s in sets], rows * d * 2 * 4)
+                                     dbias=dbias) for s in sets], rows * d * 2 * 4,
+        copy_pairs=[(torch.empty(2 * rows, d, device=dev, dtype=bf), torch.cat([s["x"], s["dy"]])) for s in sets[:2]])
     del sets
     Cc, S, p = 4, 512, 16
     L = (S // p) ** 2
@@ -379,23 +391,23 @@ def run_ours(args):
     K.gemm_grouped = grouped_probe
     # the fused attention launches of the same step: forward 4 N^2 H dh per (sequence, block), backward 2.5x
     attn_calls = {"fwd": [], "bwd": []}
-    orig_af, orig_ab = K.attn_fwd, K.attn_bwd
+    orig_af, orig_ab = K.attn_fwd_grouped, K.attn_bwd_grouped
 
-    def af_probe(qkv, o, lse, Bn, N, H, dh):
-        attn_calls["fwd"].append((4.0 * N * N * H * dh * Bn, dh, (qkv, o, lse, Bn, N, H, dh)))
-        orig_af(qkv, o, lse, Bn, N, H, dh)
+    def af_probe(items, H, dh):
+        attn_calls["fwd"].append((sum(4.0 * it[4] * it[4] * H * dh * it[3] for it in items), dh, (items, H, dh)))
+        orig_af(items, H, dh)
 
-    def ab_probe(qkv, o, do, lse, dqkv, delta, Bn, N, H, dh):
-        attn_calls["bwd"].append((10.0 * N * N * H * dh * Bn, dh, (qkv, o, do, lse, dqkv, delta, Bn, N, H, dh)))
-        orig_ab(qkv, o, do, lse, dqkv, delta, Bn, N, H, dh)
-    K.attn_fwd, K.attn_bwd = af_probe, ab_probe
+    def ab_probe(items, H, dh):
+        attn_calls["bwd"].append((sum(10.0 * it[7] * it[7] * H * dh * it[6] for it in items), dh, (items, H, dh)))
+        orig_ab(items, H, dh)
+    K.attn_fwd_grouped, K.attn_bwd_grouped = af_probe, ab_probe
     eng.zero_grad()
     if args.gemm_breakdown:
         torch.cuda._sleep(int(0.060 * 1.9e9))     # head start for the (slower) Python issue
     eng.step(dict(devb))
     torch.cuda.synchronize()
     K.gemm_grouped = orig_grouped
-    K.attn_fwd, K.attn_bwd = orig_af, orig_ab
+    K.attn_fwd_grouped, K.attn_bwd_grouped = orig_af, orig_ab
 
     def replay_attn(kind, dh):
         """Device time (ms) and flops of the step's attention launches of one kind / head dim, back to back."""
@@ -505,8 +517,8 @@ def run_ours(args):
                           STEP_GFLOP.get(args.dataset, 0) / 1e3 / world, "peak": tf_sus,
                           "frac": value * STEP_GFLOP.get(args.dataset, 0) / 1e3 / world / tf_sus},
         "hbm_kernels": hbm_kernels,
-        "attention": {"kernels": "attn_fwd_kernel / attn_bwd_* (fused tcgen05 flash attention, one launch per group per "
-                                 "block, back to back, best of 3)",
+        "attention": {"kernels": "attn_fwd_kernel / attn_bwd_* (fused tcgen05 flash attention, one grouped launch per "
+                                 "block for the stacks of a layer, back to back, best of 3)",
                       "by_kind": attention, "ms_per_step": round(attn_ms, 3),
                       "tflops": round(attn_fl / (attn_ms * 1e-3) / 1e12, 1) if attn_ms > 0 else None,
                       "frac_of_sustained_peak": round(attn_fl / (attn_ms * 1e-3) / 1e12 / tf_sus, 3) if attn_ms > 0 else None,

@@ -14,7 +14,8 @@ from pathlib import Path
 
 HERE = Path(__file__).resolve().parent
 CSRC = HERE / "csrc"
-SO_PATH = HERE / "libmaestro_b200.so"
+# (MAESTRO_B200_LIB: load another build of the same ABI -- diagnostic builds of tools/, never a fallback)
+SO_PATH = Path(os.environ["MAESTRO_B200_LIB"]) if os.environ.get("MAESTRO_B200_LIB") else HERE / "libmaestro_b200.so"
 SOURCES = ["elementwise.cu", "norm.cu", "mask.cu", "unmask.cu", "loss.cu", "gemm_simt.cu", "gemm_tc.cu",
            "tmap.cu", "attn_tc.cu", "attn_bwd_tc.cu", "optim.cu", "input.cu", "head.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",

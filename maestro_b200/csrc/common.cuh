@@ -151,9 +151,13 @@ __device__ __forceinline__ float warp_max(float v) {
 // ---------------------------------------------------------------- math
 // 2^x on the MUFU pipe, flush-to-zero form (one instruction, no denormal fix-up code around it).
 __device__ __forceinline__ float fast_exp2(float x) {
+#ifdef MB_DIAG_NO_MUFU      // timing experiment only (wrong results): is the kernel bound by the MUFU pipe?
+  return fmaf(x, 0.001f, 1.0f);
+#else
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
+#endif
 }
 __device__ __forceinline__ float gelu_erf(float x) {
   return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f));
