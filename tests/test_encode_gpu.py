@@ -43,7 +43,7 @@ def test_encode_matches_reference_golden(K, name, dtype, tol):
         assert rel(x.float().cpu(), want) <= tol, (g, rel(x.float().cpu(), want))
 
 
-def test_module_encode_features_and_probe_forward_error(K):
+def test_module_encode_features_and_probe_forward(K):
     from maestro_b200.ssl.mae import MAE
     name = "micro_flair"
     spec, hp, sd, batch, inter, loss, seed, bs = U.case_inputs(name)
@@ -55,8 +55,9 @@ def test_module_encode_features_and_probe_forward_error(K):
     for g, x in feats.items():
         assert x.dtype == torch.float32 and not x.requires_grad
         assert rel(x.cpu(), torch.from_numpy(GOLD[f"{name}/{g}"])) <= 2e-2
-    with pytest.raises(NotImplementedError):
-        m(b, ssl_phase="probe")
+    out_b, pix, msk, logits = m(b, ssl_phase="probe")              # (batch, None, None, logits), ssl/mim.py:503-505
+    assert out_b is b and pix is None and msk is None
+    assert set(logits) == set(spec.targets) and all(torch.isfinite(v).all() for v in logits.values())
     with pytest.raises(RuntimeError):                      # no CPU path
         m.cpu().encode_features({k: v.cpu() for k, v in batch.items()})
 
