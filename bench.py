@@ -219,15 +219,60 @@ def cpu_reference_step_time(dataset, size, batch, steps, warmup, threads):
     return sum(times) / len(times)
 
 
+def cpu_reference_modules_step_time(dataset, size, batch, steps, warmup, threads):
+    """The reference's OWN modules (``SSLModule.pretrain_step`` -> ``MAE.forward`` -> ``compute_loss_rec``, then
+    ``backward``; maestro/train/model.py:249-274) on the host cores, fp32, imported from ``oracle/_ref`` (the mirror of
+    /root/reference made by oracle/make_ref.py) through ``oracle/ref_shim.py``.  Returns seconds per step, or None when
+    the mirror is absent."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import ref_shim
+    if not ref_shim.reference_available():
+        return None
+    ref_shim.install()
+    from maestro.conf.mask import MaskConfig
+    from maestro.train.model import SSLModule as RefSSLModule
+    torch.set_num_threads(threads)
+    torch.manual_seed(0)
+    module = RefSSLModule(ref_shim.reference_datasets_config(dataset), MaskConfig(), "nearest", "group", 3, "mae", size,
+                          loss="l1_norm")
+    module.trainer = type("T", (), {"ssl_phase": "pretrain"})()
+    spec = DATASET_SPECS[dataset]()
+    batch_t = synthetic_batch(spec, batch, seed=1)
+    times = []
+    for i in range(warmup + steps):
+        t0 = time.perf_counter()
+        out = module.pretrain_step({k: v.clone() for k, v in batch_t.items()}, stage="train")
+        out["loss"].backward()
+        module.zero_grad(set_to_none=True)
+        dt = time.perf_counter() - t0
+        if i >= warmup:
+            times.append(dt)
+    return sum(times) / len(times)
+
+
+def cpu_arm(dataset, size, batch, steps, warmup, threads):
+    """(seconds per step, kind, description): the reference's own modules when the mirror travelled, else the port."""
+    try:
+        sec = cpu_reference_modules_step_time(dataset, size, batch, steps, warmup, threads)
+    except Exception as e:  # noqa: BLE001  (a broken mirror must not take the GPU line down with it)
+        print(f"[bench] reference modules unavailable ({type(e).__name__}: {e}); timing the oracle port", file=sys.stderr)
+        sec = None
+    if sec is not None:
+        return sec, "reference", ("the reference's own SSLModule.pretrain_step + backward (oracle/_ref mirror of "
+                                  "/root/reference/maestro via oracle/ref_shim.py; vit_pytorch restated), fp32 torch on CPU")
+    sec = cpu_reference_step_time(dataset, size, batch, steps, warmup, threads)
+    return sec, "port", "fp32 torch on CPU, oracle/mae_oracle.py"
+
+
 def run_reference(args):
-    """--impl reference: the reference's algorithm on this box's host cores (oracle port; the reference itself
-    is pure Python over eager torch and /root/reference does not exist on the GPU box)."""
+    """--impl reference: the reference's CPU implementation of the path on this box's host cores: its own modules from
+    the oracle/_ref mirror when that travelled with the snapshot, else the oracle port (``cpu_baseline.kind`` says which)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     threads = os.cpu_count() or 1
     B = args.cpu_batch
-    sec = cpu_reference_step_time(args.dataset, args.size, B, max(1, args.steps), max(1, args.warmup), threads)
+    sec, kind, what = cpu_arm(args.dataset, args.size, B, max(1, args.steps), max(1, args.warmup), threads)
     val = B / sec
     line = {
         "impl": "reference", "metric": "pretrain_tiles_per_sec", "value": val, "unit": "tiles/s", "n_gpus": args.gpus,
@@ -235,8 +280,8 @@ def run_reference(args):
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"MAESTRO ViT-B ({args.size}) MAE pretrain step, {args.dataset} shapes, "
                                f"fwd+bwd on host cores, batch {B}"},
-        "cpu_baseline": {"value": val, "unit": "tiles/s", "cores": threads, "kind": "port",
-                         "sample": f"{args.steps} steps of batch {B} (fp32 torch on CPU, oracle/mae_oracle.py)"},
+        "cpu_baseline": {"value": val, "unit": "tiles/s", "cores": threads, "kind": kind,
+                         "sample": f"{args.steps} steps of batch {B} ({what})"},
         "e2e": {"value": val, "unit": "tiles/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line), flush=True)
@@ -479,9 +524,9 @@ def run_ours(args):
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
         threads = os.cpu_count() or 1
-        sec = cpu_reference_step_time(args.dataset, args.size, args.cpu_batch, 2, 1, threads)
-        cpu = {"value": args.cpu_batch / sec, "unit": "tiles/s", "cores": threads, "kind": "port",
-               "sample": f"2 steps of batch {args.cpu_batch} after 1 warm-up (fp32 torch on CPU, oracle/mae_oracle.py)"}
+        sec, kind, what = cpu_arm(args.dataset, args.size, args.cpu_batch, 2, 1, threads)
+        cpu = {"value": args.cpu_batch / sec, "unit": "tiles/s", "cores": threads, "kind": kind,
+               "sample": f"2 steps of batch {args.cpu_batch} after 1 warm-up ({what})"}
     line = {
         "metric": "pretrain_tiles_per_sec", "value": value, "unit": "tiles/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": step_ms, "higher_is_better": True, "scaling": "weak",

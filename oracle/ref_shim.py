@@ -21,7 +21,18 @@ import os
 import sys
 import types
 
-REFERENCE_ROOT = os.environ.get("MAESTRO_REFERENCE_ROOT", "/root/reference")
+def _reference_root() -> str:
+    """/root/reference in the build container; on the GPU box the mirror made by ``oracle/make_ref.py``
+    (``oracle/_ref/``: git-ignored, shipped with the gpurun snapshot)."""
+    env = os.environ.get("MAESTRO_REFERENCE_ROOT")
+    if env:
+        return env
+    if os.path.isdir("/root/reference/maestro"):
+        return "/root/reference"
+    return os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref")
+
+
+REFERENCE_ROOT = _reference_root()
 
 
 def reference_available() -> bool:
