@@ -166,7 +166,8 @@ def test_fused_step_with_torch_optimizer_and_default_zero_grad(monkeypatch):
                 out["loss"].backward()
             opt.step()
             losses.append(float(out["loss"]))
-        return losses, {k: v.detach().clone() for k, v in mod.model.state_dict().items()}
+        # (the heads are outside the pretraining step and randomly initialised per module: not compared)
+        return losses, {k: v.detach().clone() for k, v in mod.model.state_dict().items() if not k.startswith("heads.")}
 
     la, sa = run(False)
     lb, sb = run(True)
