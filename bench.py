@@ -24,7 +24,21 @@ import torch  # noqa: E402
 
 from maestro_b200.conf import DATASET_SPECS, MODEL_SIZES, MaskSpec  # noqa: E402
 
-GEMM_DRAM_BYTES_PER_LAUNCH = 145.3e6   # measured under ncu, see profiles/r1d_summary.md
+
+
+def gemm_traffic():
+    """DRAM bytes per launch of the dominant kernel: ncu's dram__bytes_read.sum + dram__bytes_write.sum over every
+    gemm_tc launch of one step, digested by tools/gemm_traffic.py into profiles/ (ncu cannot run inside the timed bench)."""
+    for name in ("r2_gemm_dram.json",):
+        try:
+            with open(os.path.join(ROOT, "profiles", name)) as f:
+                d = json.load(f)
+            return d["dram_bytes_per_launch"], f"profiles/{name}: {d['source']}; {d['launches']} launches"
+        except (OSError, KeyError, ValueError):
+            continue
+    return None, "no ncu capture committed for this round"
+
+
 STEP_GFLOP = {"flair": 431.9, "treesatai_ts": 94.6, "s2_naip": 301.3, "pastis_hd": 1009.3}  # SURVEY 8(d), per tile
 
 
@@ -553,9 +567,8 @@ def run_ours(args):
         "clocks": clocks,
         "roofline": {"bound": "tensor", "kernel": "gemm_tc_kernel (tcgen05 GEMM, all linear layers fwd/dgrad/wgrad)",
                      "achieved": achieved, "peak": tf_sus, "unit": "TFLOP/s", "frac": achieved / tf_sus,
-                     "traffic": GEMM_DRAM_BYTES_PER_LAUNCH, "traffic_source": "profiles/r1d_gemm_dram.csv (ncu dram__bytes_"
-                     "read.sum + dram__bytes_write.sum, average over the 208 GEMM launches of one step; algorithmic "
-                     "167 MB per launch)",
+                     "traffic": gemm_traffic()[0], "traffic_source": gemm_traffic()[1],
+                     "algorithmic_bytes_per_launch": 167.0e6,
                      "peak_source": f"{src} (sustained)", "launches": n_tc,
                      "avg_launch_ms": tc_ms / max(1, n_tc), "share_of_step": tc_ms / step_ms},
         "step_roofline": {"gflop_per_tile": STEP_GFLOP.get(args.dataset), "achieved_tflops": value *
