@@ -172,7 +172,9 @@ class SSLModule(nn.Module):
                                    betas=(0.9, 0.999), final_factor: float = 1e4, device=None):
         """The reference's optimiser (train/model.py:120-158: AdamW + OneCycleLR(pct_start=0.2, cycle_momentum=False,
         div_factor=1000, final_div_factor=final_factor / 1000), stepped per batch) as ONE fused kernel per step over the
-        engine's arena; parameters outside the arena (the heads) get a stock ``torch.optim.AdamW`` on the same schedule."""
+        engine's arena (every parameter the pretraining step reaches).  The heads live outside the arena and receive no
+        gradient in pretraining; probe / finetune phases use a stock ``torch.optim.AdamW`` over ``self.model.parameters()``
+        (``param.grad`` of the arena parameters aliases the gradient arena, so it sees them like any other)."""
         dev = torch.device(device) if device is not None else next(self.model.parameters()).device
         eng = self.model._engine(dev)
         sched = OneCycle(lr, total_steps, pct_start=0.2, div_factor=1000.0, final_div_factor=final_factor / 1000.0)
