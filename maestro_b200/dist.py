@@ -51,6 +51,8 @@ class GradReducer:
         self.grad, self.group = grad, group
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.buckets = [split_ranges([r], bucket_elems) for r in ranges]
+        import os
+        self._diag = os.environ.get("MB_DIAG_REDUCE", "")      # "none" / "serial": attribution experiments only
         self.cuda = grad.is_cuda
         self.comm = torch.cuda.Stream(device=grad.device) if (self.cuda and self.world > 1) else None
         self.bytes_per_step = sum(b - a for a, b in ranges) * grad.element_size() if self.world > 1 else 0
@@ -60,7 +62,16 @@ class GradReducer:
         return 1.0 / self.world
 
     def reduce_range(self, i: int) -> None:
-        if self.world == 1:
+        if self.world == 1 or self._diag == "none":
+            return
+        if self._diag == "serial" and i < len(self.buckets) - 1:      # diagnostic: everything after the last segment
+            return
+        if self._diag == "serial":
+            self.comm.wait_stream(torch.cuda.current_stream(self.grad.device))
+            with torch.cuda.stream(self.comm):
+                for bs in self.buckets:
+                    for a, b in bs:
+                        dist.all_reduce(self.grad[a:b], group=self.group)
             return
         if self.comm is None:
             for a, b in self.buckets[i]:
