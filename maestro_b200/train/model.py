@@ -234,9 +234,8 @@ class SSLModule(nn.Module):
           the next segment runs.
         * ``next_batch`` (pinned host tensors): the input pipeline.  Its host-to-device copy is started on a copy stream
           ahead of backward segment ``self.h2d_gate`` of THIS step (calibrated from event timings on the third such
-          call: the latest point that leaves 1.3x the measured transfer time before the step ends; the start of the
-          step when gradients are all-reduced), and the next call -- given that same object as ``batch`` -- finds its
-          inputs already on the device.
+          call: the latest point that leaves 1.3x the measured transfer time before the step ends), and the next call --
+          given that same object as ``batch`` -- finds its inputs already on the device.
         * ``optimizer`` (a ``FusedAdamW``): stepped inside (``grad_scale = 1 / world``), which puts the update -- the
           phase least sensitive to PCIe ingress -- inside the window the prefetch is gated into."""
         dev = batch["ref_date"].device
@@ -303,14 +302,16 @@ class SSLModule(nn.Module):
         """Choose the backward segment ahead of which the next batch's H2D copy starts.  PCIe ingress slows concurrent
         kernels (tools/h2d_interference.py: tcgen05 GEMM +9 %, LayerNorm +32 %), least so under the backward's tail and
         the AdamW update: pick the latest segment that still leaves 1.3x the measured transfer time before the step
-        ends.  With a gradient all-reduce in flight the backward is the wrong place (the NVLink traffic is on the
-        critical path of the tail; 8 GPUs: 32.0 ms gated into the tail vs 30.3 ms under the forward): gate 0."""
+        ends (with 8 ranks sharing the host's memory the transfer is slower and the gate moves earlier by itself)."""
         torch.cuda.synchronize(g.dev)
         h0, h1 = g.h2d_events
         h2d_ms = h0.elapsed_time(h1)
         tail = [m.elapsed_time(marks[-1]) for m in marks[:-1]]
         ok = [i for i, t in enumerate(tail) if t >= 1.3 * h2d_ms]
-        self.h2d_gate = 0 if world > 1 else (max(ok) if ok else 0)
+        # (round 1 started the copy with the step whenever gradients are all-reduced; measured again in round 2 on the
+        # grouped-launch schedule: 2 GPUs 30.73 ms under the forward vs 29.67 ms at the calibrated gate, 29.47 ms without
+        # any copy -- the calibrated gate is used for every world size)
+        self.h2d_gate = max(ok) if ok else 0
         self.h2d_ms = h2d_ms
 
     @staticmethod
