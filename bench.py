@@ -360,6 +360,8 @@ def run_ours(args):
     loss_pending = [False, False]
     e2e_count = [0]
 
+    host_ms = [0.0, 0]
+
     def step_e2e(_i):
         # input pipeline (inside SSLModule.pretrain_step_fused): the H2D copy of step i + 1 (pinned host memory ->
         # staging) runs on a copy stream while step i computes, gated into the backward's tail + AdamW at N = 1 and to
@@ -368,11 +370,14 @@ def run_ours(args):
         i = e2e_count[0]
         e2e_count[0] += 1
         hb, nxt = host_e2e[i % 2], host_e2e[(i + 1) % 2]
+        t_host = time.perf_counter()
         if args.e2e_ablate == "h2d" or not use_graph:
             src = devb if args.e2e_ablate == "h2d" else hb
             loss = mod.pretrain_step_fused(src, graph=use_graph, optimizer=opt)["loss"]
         else:
             loss = mod.pretrain_step_fused(hb, next_batch=nxt, optimizer=opt)["loss"]
+        host_ms[0] += (time.perf_counter() - t_host) * 1e3      # host time to ISSUE one step (no waiting on the GPU)
+        host_ms[1] += 1
         # loss read-back, every step, without draining the queue: step i's loss goes to pinned slot i % 2 behind an
         # event, and the host blocks on step i - 1's event only, so it stays one step ahead of the GPU (the struct-mask
         # draw and the launch of step i + 1 overlap step i).  The last step's copy completes before the closing event.
@@ -420,8 +425,10 @@ def run_ours(args):
     launches = (K.launches - l0) // args.steps
     if use_graph:
         launches = next(iter(mod._graphed.values())).launches_per_step + 1
+    host_ms[0], host_ms[1] = 0.0, 0
     ms_e2e = timed(step_e2e, args.steps)
     loss_host[0] = loss_pin[(e2e_count[0] - 1) % 2][0]    # timed() has synchronised: the last read-back is complete
+    print(f"[rank {rank}] host time to issue one fused step: {host_ms[0] / max(1, host_ms[1]):.2f} ms", file=sys.stderr)
     clocks = sampler.stop() if rank == 0 else None
     last_loss = float(loss_host[0])
 

@@ -260,9 +260,9 @@ class SSLModule(nn.Module):
                 g = self._graph_for(eng, batch)
                 if self._staged_src is not None and self._staged_src is batch:
                     g.load_prefetched()
+                    self._staged_src = None
                 else:
-                    g.load(batch)
-                self._staged_src = None
+                    g.load(batch)        # (a batch staged earlier stays staged: its turn may still come)
                 eng.grads_dirty = True
                 marks = [] if (next_batch is not None and self._fused_calls == 2 and self.h2d_gate is None) else None
                 gate = 0 if self.h2d_gate is None else self.h2d_gate
