@@ -6,7 +6,7 @@ raster I/O stack.  The pretraining path only reads a handful of shape fields fro
 (``ssl/mim.py:49-79,143-157``, ``ssl/mae.py:55-131``, ``train/model.py:38-50``), so the
 product keeps its own plain dataclasses and converts a reference ``DatasetsConfig`` by
 duck typing (:func:`spec_from_reference`).  The four shipped dataset shapes are restated
-here with the file:line they come from; ``tests/test_conf.py`` checks them field by field
+here with the file:line they come from; ``tests/test_oracle_vs_reference.py::test_builtin_specs_equal_reference_configs`` checks them field by field
 against the reference configs when /root/reference is present.
 """
 

@@ -607,6 +607,9 @@ class PretrainEngine:
         out = []
         for name in grp.mods:
             mt = self.mods[name]
+            if self.fusion_mode in ("shared", "monotemp"):       # every probability is None there (mae.py:85-96)
+                out.append((mt.G, mt.D, mt.L, 0.0, 0.0, 0.0, 0.0))
+                continue
             out.append((mt.G, mt.D, mt.L,
                         (mc.mask_mod or 0.0) if (self.fusion_mode == "group" and not alone) else 0.0,
                         (mc.mask_bands or 0.0) if mt.G > 1 else 0.0,
@@ -625,7 +628,7 @@ class PretrainEngine:
         for gi, g in enumerate(self.groups.values()):
             if g.name not in out:
                 out[g.name] = torch.empty(batch_size * g.bmul, g.L, dtype=torch.uint8, device=self.device)
-            if g.bmul > 1:                                # "shared" / "monotemp": no structural masking at all
+            if self.fusion_mode in ("shared", "monotemp"):      # no structural masking at all
                 out[g.name].zero_()
                 continue
             key = (int(seed) ^ ((gi + 1) * 0x9E3779B97F4A7C15)) & (2**64 - 1)

@@ -221,6 +221,15 @@ class MAE(nn.Module):
                 members = spec.group_members(g) if fusion_mode == "group" else [g]
                 n_dates = sum(spec.inputs[x].num_dates * self.len_bands[x] for x in members)
                 self.mask_ratio[g] = 1 - (1 - self.mask_cfg.mask_ratio) / (n_dates ** self.mask_cfg.mask_scale)
+        # structural-mask probabilities per modality, as the reference exposes them (ssl/mae.py:84-131): None = not drawn
+        mc, flat = self.mask_cfg, fusion_mode in ("shared", "monotemp", "msgfm")
+        nd_mod = {n: m.num_dates * self.len_bands[n] for n, m in spec.inputs.items()}
+        nd_grp = {g: sum(nd_mod[x] for x in spec.group_members(g)) for g in spec.group_names}
+        self.mask_mod = {n: (mc.mask_mod if (fusion_mode == "group" and nd_mod[n] != nd_grp[m.group]) else None)
+                         for n, m in spec.inputs.items()}
+        self.mask_bands = {n: (mc.mask_bands if (not flat and self.len_bands[n] > 1) else None) for n in spec.inputs}
+        self.mask_dates = {n: (mc.mask_dates if (not flat and m.num_dates > 1) else None) for n, m in spec.inputs.items()}
+        self.mask_loc = {n: (None if flat else mc.mask_loc) for n in spec.inputs}
         # "alias": param.grad aliases the engine's gradient arena (no copies); "autograd": gradients are handed to torch's
         # AccumulateGrad (one clone per parameter per step; what a DistributedDataParallel wrapper's hooks need)
         self.grad_mode = "alias"

@@ -48,6 +48,35 @@ def test_factories_and_errors():
         SSLModule(spec, MaskSpec(), fusion_mode="shared", inter_depth=3, model_size="tiny")
 
 
+def test_mask_ratio_logic_equals_reference():
+    """Row C (maestro/ssl/mae.py:55-131), incl. mask_scale != 0: ``mask_ratio`` and the structural-mask probabilities per
+    modality against the reference's own constructor (tests/golden/mask_ratio.json, made by make_maskratio_golden.py), and
+    the engine's per-group ratio / number of masked tokens / draw probabilities derived from the same rules."""
+    import json
+    import os
+    from fake_kernels import FakeKernels
+    from maestro_b200.engine import PretrainEngine
+    gold = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "mask_ratio.json")))
+    for key, want in gold.items():
+        dataset, fusion, ratio, scale = key.split("/")
+        spec, mask = DATASET_SPECS[dataset](), MaskSpec(mask_ratio=float(ratio), mask_scale=float(scale))
+        m = MAE(spec, mask, fusion_mode=fusion, inter_depth=0, **synth.MICRO_HP)
+        assert set(m.mask_ratio) == set(want["mask_ratio"]), key
+        for k, v in want["mask_ratio"].items():
+            assert abs(m.mask_ratio[k] - v) < 1e-12, (key, k)
+        for attr in ("mask_mod", "mask_bands", "mask_dates", "mask_loc"):
+            assert getattr(m, attr) == want[attr], (key, attr)
+        eng = PretrainEngine(spec, synth.MICRO_HP, mask, FakeKernels(), "cpu", torch.float32, fusion_mode=fusion,
+                             inter_depth=0)
+        for g in eng.groups.values():
+            assert abs(g.ratio - want["mask_ratio"][g.name]) < 1e-12, (key, g.name)
+            assert g.nm == round(want["mask_ratio"][g.name] * g.L), (key, g.name)
+            if g.bmul == 1:
+                for name, (_, _, _, pm, pb, pd, pl) in zip(g.mods, eng.struct_mods(g.name)):
+                    assert (pm, pb, pd, pl) == tuple(want[a][name] or 0.0 for a in ("mask_mod", "mask_bands", "mask_dates",
+                                                                                     "mask_loc")), (key, name)
+
+
 def test_deepcopy_to_cpu_and_no_cpu_forward():
     spec = DATASET_SPECS["treesatai_ts"]()
     m = MAE(spec, MaskSpec(), inter_depth=1, **synth.MICRO_HP)
