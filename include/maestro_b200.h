@@ -84,6 +84,15 @@ int mb_gn_apply(const void* y, const double* sums, const float* gamma, const flo
 int mb_gn_bwd(const void* dy, const void* y, const float* stats, const float* gamma, double* sums2, void* dconv,
               float* dgamma, float* dbeta, int dtype, int n_img, int D, int L, int E, int out_bs, int out_off,
               void* stream);
+/* mb_gn_stats + mb_gn_apply in one call that allocates nothing and needs no caller scratch: the [n_img, 2] fp64 sums
+ * live in a file-scope device array (64 KiB per GPU that loads the library, held until exit).  No counterpart in the
+ * reference: added for callers that cannot call cudaMalloc (CUDA graph
+ * capture, serving loops).  n_img <= mb_gn_static_max_images() (4096), else -4.  Every call shares the array (cleared
+ * on the stream at the start of each call): calls that overlap on the GPU race. */
+int mb_gn_static_max_images(void);
+int mb_gn_fwd_static(const void* y, const float* gamma, const float* beta, const float* pos, const float* feat,
+                     void* out, float* stats_out, int dtype, int n_img, int D, int L, int E, float eps, int out_bs,
+                     int out_off, int date_dim, float fac_date, int feat_bs, int feat_off, void* stream);
 
 /* ---- masking ------------------------------------------------------------------------------------------------ */
 /* MAE.mask_seq index math, maestro/ssl/mae.py:239-259 (rand*struct -> argsort -> argsort -> gather -> sort x2).

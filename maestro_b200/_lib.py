@@ -171,7 +171,8 @@ def header_prototypes() -> dict[str, list]:
     text = re.sub(r"/\*.*?\*/", " ", HEADER.read_text(), flags=re.S)
     protos = {}
     for m in re.finditer(r"\bint\s+(mb_\w+)\s*\(([^)]*)\)\s*;", text):
-        protos[m.group(1)] = [_ctype_of(a) for a in m.group(2).split(",")]
+        args = m.group(2).strip()
+        protos[m.group(1)] = [] if args == "void" else [_ctype_of(a) for a in args.split(",")]
     return protos
 
 
@@ -197,7 +198,8 @@ def lib() -> C.CDLL:
 EXPORTS = [
     "mb_cast_f32_to_bf16", "mb_cast_transpose_f32_to_bf16", "mb_resize_nearest", "mb_im2col", "mb_rows_image",
     "mb_date_features", "mb_colsum_accum",
-    "mb_layernorm_fwd", "mb_layernorm_bwd", "mb_gn_stats", "mb_gn_apply", "mb_gn_bwd",
+    "mb_layernorm_fwd", "mb_layernorm_bwd", "mb_gn_stats", "mb_gn_apply", "mb_gn_bwd", "mb_gn_static_max_images",
+    "mb_gn_fwd_static",
     "mb_mask_indices", "mb_gather_rows", "mb_scatter_kept", "mb_unmask_fwd", "mb_masktoken_grad",
     "mb_loss_fwd_bwd", "mb_gemm_simt", "mb_softmax_rows", "mb_softmax_bwd_rows", "mb_gemm_tc", "mb_gemm_tc_grouped",
     "mb_adamw_step", "mb_attn_fwd", "mb_attn_bwd", "mb_raster_transform", "mb_struct_mask", "mb_resize",

@@ -804,3 +804,59 @@ extern "C" int mb_gn_bwd(const void* dy, const void* y, const float* stats, cons
   MB_CHECK_LAUNCH();
   return 0;
 }
+
+// ------------------------------------------------------------------ GroupNorm forward without any allocation
+// mb_gn_fwd_static = mb_gn_stats + mb_gn_apply with the [n_img, 2] fp64 sum scratch in a file-scope device array
+// instead of a caller-provided buffer: for callers that cannot allocate (graph capture, serving loops).  No
+// counterpart in the reference.  Limit: MB_GN_STATIC_MAX_IMG images per
+// call (64 KiB of device memory per GPU that loads the library, held until exit).  Every call shares the array:
+// calls that overlap on the GPU (different streams) race.
+#define MB_GN_STATIC_MAX_IMG 4096
+static __device__ __align__(256) double g_gn_static_sums[2 * MB_GN_STATIC_MAX_IMG];
+
+namespace {
+constexpr int GN_STATIC_MAX_DEV = 64;
+double* g_gn_static_ptr[GN_STATIC_MAX_DEV] = {};      // device address of the array, per device (host code cannot
+                                                      // use the symbol's name as a pointer)
+// Once per device, with that device current.
+int gn_static_scratch(double** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return static_cast<int>(e);
+  if (dev < 0 || dev >= GN_STATIC_MAX_DEV) return -3;
+  double* p = __atomic_load_n(&g_gn_static_ptr[dev], __ATOMIC_ACQUIRE);
+  if (p == nullptr) {
+    e = cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_gn_static_sums);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    if (p == nullptr) return -3;
+    __atomic_store_n(&g_gn_static_ptr[dev], p, __ATOMIC_RELEASE);   // same value from every thread that raced here
+  }
+  *out = p;
+  return 0;
+}
+}  // namespace
+
+extern "C" int mb_gn_static_max_images(void) { return MB_GN_STATIC_MAX_IMG; }
+
+// Returns 0, -2 for unsupported shapes (as mb_gn_stats / mb_gn_apply), -4 when n_img exceeds
+// MB_GN_STATIC_MAX_IMG, a positive cudaError_t otherwise.  Calls no cudaMalloc / cudaFree.
+extern "C" int mb_gn_fwd_static(const void* y, const float* gamma, const float* beta, const float* pos,
+                                const float* feat, void* out, float* stats_out, int dtype, int n_img, int D, int L,
+                                int E, float eps, int out_bs, int out_off, int date_dim, float fac_date, int feat_bs,
+                                int feat_off, void* stream) {
+  if (n_img == 0) return 0;
+  if (n_img < 0) return -2;
+  if (n_img > MB_GN_STATIC_MAX_IMG) return -4;
+  if (E % 8 != 0) return -2;
+  double* sums = nullptr;
+  int rc = gn_static_scratch(&sums);
+  if (rc != 0) return rc;
+  // the array keeps the previous call's sums: the statistics kernel accumulates, so start from zero
+  cudaError_t e = cudaMemsetAsync(sums, 0, static_cast<size_t>(n_img) * 2 * sizeof(double),
+                                  static_cast<cudaStream_t>(stream));
+  if (e != cudaSuccess) return static_cast<int>(e);
+  rc = mb_gn_stats(y, dtype, sums, n_img, static_cast<long long>(L) * E, stream);
+  if (rc != 0) return rc;
+  return mb_gn_apply(y, sums, gamma, beta, pos, feat, out, stats_out, dtype, n_img, D, L, E, eps, out_bs, out_off,
+                     date_dim, fac_date, feat_bs, feat_off, stream);
+}

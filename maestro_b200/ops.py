@@ -174,6 +174,15 @@ class Kernels:
                                n_img, D, L, E, C.c_float(eps), out_bs, out_off, date_dim, C.c_float(fac_date),
                                feat.shape[1], feat_off, self._s()), "gn_apply")
 
+    def gn_fwd_static(self, y, gamma, beta, pos, feat, out, stats, n_img, D, L, E, eps, out_bs, out_off, date_dim,
+                      fac_date, feat_off):
+        """``gn_stats`` + ``gn_apply`` with the library's own static sum scratch: no allocation, no caller scratch;
+        ``n_img`` <= ``mb_gn_static_max_images()`` (4096); calls that overlap on the GPU race on the shared array."""
+        self.launches += 2
+        _ck(self.L.mb_gn_fwd_static(_p(y), _p(gamma), _p(beta), _p(pos), _p(feat), _p(out), _p(stats), _dt(y),
+                                    n_img, D, L, E, C.c_float(eps), out_bs, out_off, date_dim, C.c_float(fac_date),
+                                    feat.shape[1], feat_off, self._s()), "gn_fwd_static")
+
     def gn_bwd(self, dy, y, stats, gamma, sums2, dconv, dgamma, dbeta, n_img, D, L, E, out_bs, out_off):
         self.launches += 2
         _ck(self.L.mb_gn_bwd(_p(dy), _p(y), _p(stats), _p(gamma), _p(sums2), _p(dconv), _p(dgamma), _p(dbeta),
