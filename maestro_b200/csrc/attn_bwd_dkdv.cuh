@@ -62,6 +62,8 @@ __global__ void __launch_bounds__(DKDV_THREADS) attn_bwd_dkdv_kernel(const __gri
   __syncthreads();
   tc::tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
+  pdl_launch();
+  pdl_wait();
   // columns: S^T [2][SUB] | dP^T [2][SUB] | dK [DH] | dV [DH]
   const uint32_t tm_st = tmem_base, tm_dpt = tmem_base + 2 * SUB, tm_dk = tmem_base + 4 * SUB, tm_dv = tm_dk + DH;
   const uint32_t lane_base = static_cast<uint32_t>(warp * 32) << 16;
@@ -297,8 +299,8 @@ int launch_bwd(const mb_attn_problem* ps, int count, int H, cudaStream_t st) {
     cudaFuncSetAttribute(attn_bwd_dkdv_kernel<DH>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_DKDV);
     attr = true;
   }
-  attn_bwd_dq_kernel<DH><<<total, DQ_THREADS, SMEM_DQ, st>>>(g);
-  attn_bwd_dkdv_kernel<DH><<<total, DKDV_THREADS, SMEM_DKDV, st>>>(g);
+  mb_launch(attn_bwd_dq_kernel<DH>, dim3(total), dim3(DQ_THREADS), SMEM_DQ, st, g);
+  mb_launch(attn_bwd_dkdv_kernel<DH>, dim3(total), dim3(DKDV_THREADS), SMEM_DKDV, st, g);
   cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? 0 : static_cast<int>(e);
 }

@@ -131,6 +131,8 @@ __global__ void __launch_bounds__(DQ_THREADS) attn_bwd_dq_kernel(const __grid_co
   __syncthreads();
   tc::tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
+  pdl_launch();
+  pdl_wait();
   // columns: S [2][SUB] | dP [2][SUB] | dQ [DH]
   const uint32_t tm_s = tmem_base, tm_dp = tmem_base + 2 * SUB, tm_dq = tmem_base + 4 * SUB;
   const uint32_t lane_base = static_cast<uint32_t>(warp * 32) << 16;

@@ -108,6 +108,8 @@ __global__ void __launch_bounds__(128) attn_fwd_kernel(const __grid_constant__ A
   __syncthreads();
   tc::tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
+  pdl_launch();
+  pdl_wait();
   const uint32_t tm_s = tmem_base;          // S: columns [0, 64)
   const uint32_t tm_o = tmem_base + BKV;    // O tile: columns [64, 64 + DH)
   const uint32_t lane_base = static_cast<uint32_t>(warp * 32) << 16;
@@ -323,7 +325,7 @@ int launch_fwd(const mb_attn_problem* ps, int count, int H, cudaStream_t st) {
     cudaFuncSetAttribute(attn_fwd_kernel<DH>, cudaFuncAttributeMaxDynamicSharedMemorySize, C_::SMEM_BYTES);
     attr = true;
   }
-  attn_fwd_kernel<DH><<<total, 128, C_::SMEM_BYTES, st>>>(g);
+  mb_launch(attn_fwd_kernel<DH>, dim3(total), dim3(128), C_::SMEM_BYTES, st, g);
   cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? 0 : static_cast<int>(e);
 }

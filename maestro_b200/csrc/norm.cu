@@ -49,6 +49,8 @@ struct LnFwdArgs {
 template <typename T, int NCH, bool MAPPED>
 __global__ void __launch_bounds__(LNF_THREADS, (NCH <= 2 ? 4 : (NCH <= 3 ? 3 : 2)))
 layernorm_fwd_kernel(const __grid_constant__ LnFwdArgs args) {
+  pdl_launch();
+  pdl_wait();
   int pi = 0, cta0 = 0;
 #pragma unroll
   for (int i = 0; i < LN_MAX_GROUP - 1; ++i)
@@ -199,7 +201,7 @@ static void launch_ln_fwd(const mb_ln_fwd_problem* ps, int count, int d, float e
   }
   for (int i = count; i < LN_MAX_GROUP; ++i) a.p[i] = a.p[0];
   a.count = count; a.d = d; a.eps = eps;
-  kern<<<blocks, LNF_THREADS, smem, st>>>(a);
+  mb_launch(kern, dim3(blocks), dim3(LNF_THREADS), smem, st, a);
 }
 
 extern "C" int mb_layernorm_fwd_grouped(const mb_ln_fwd_problem* problems, int count, int dtype, int d, float eps,
@@ -273,6 +275,8 @@ struct LnBwdArgs {
 template <typename T, int NCH, bool MAPPED>
 __global__ void __launch_bounds__(LNB_THREADS, 1)
 layernorm_bwd_kernel(const __grid_constant__ LnBwdArgs args) {
+  pdl_launch();
+  pdl_wait();
   int pi = 0, cta0 = 0;
 #pragma unroll
   for (int i = 0; i < LN_MAX_GROUP - 1; ++i)
@@ -491,7 +495,7 @@ static int launch_ln_bwd(const mb_ln_bwd_problem* ps, int count, int d, cudaStre
         attr_done = true;                                                                                       \
       }                                                                                                         \
       auto kern = mapped ? layernorm_bwd_kernel<T, N_, true> : layernorm_bwd_kernel<T, N_, false>;              \
-      kern<<<blocks, LNB_THREADS, smem, st>>>(a);                                                               \
+      mb_launch(kern, dim3(blocks), dim3(LNB_THREADS), smem, st, a);                                                            \
     }                                                                                                           \
     break;
   switch (nch) {

@@ -91,13 +91,56 @@ def grouped(args):
             print(f"{stack}/{kind:12s} grouped x{len(probs)}  {ms * 1e3:8.1f} us  {fl / ms / 1e9:7.1f} TFLOP/s", flush=True)
 
 
+def cublas(args):
+    """The same shapes as plain library GEMMs (torch.mm -> cuBLASLt, bf16 in, bf16 out, NO bias / GELU / residual
+    epilogue and bf16 instead of fp32 weight-gradient outputs): the practical ceiling a vendor kernel reaches on these
+    sizes, to put next to the epilogue-carrying numbers of the default mode."""
+    dev = "cuda"
+    bf = torch.bfloat16
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    tot_fl, tot_ms = 0.0, 0.0
+    for name, layout, M, N, Kd, _ in cases():
+        if args.only and args.only not in name:
+            continue
+        if layout == "k":
+            A, B = torch.randn(M, Kd, device=dev).to(bf), torch.randn(N, Kd, device=dev).to(bf)
+            run = lambda: torch.mm(A, B.t())  # noqa: E731
+        elif layout == "kmn":
+            A, B = torch.randn(M, Kd, device=dev).to(bf), torch.randn(Kd, N, device=dev).to(bf)
+            run = lambda: torch.mm(A, B)  # noqa: E731
+        else:
+            A, B = torch.randn(Kd, M, device=dev).to(bf), torch.randn(Kd, N, device=dev).to(bf)
+            run = lambda: torch.mm(A.t(), B)  # noqa: E731
+        for _ in range(3):
+            run()
+        ms = 0.0
+        for _ in range(args.iters):
+            flush.fill_(1)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            run()
+            e1.record()
+            torch.cuda.synchronize()
+            ms += e0.elapsed_time(e1)
+        ms /= args.iters
+        fl = 2.0 * M * N * Kd
+        tot_fl += fl
+        tot_ms += ms
+        print(f"cublas {name:28s} M={M:6d} N={N:5d} K={Kd:6d}  {ms * 1e3:8.1f} us  {fl / ms / 1e9:7.1f} TFLOP/s", flush=True)
+    if tot_ms:
+        print(f"cublas TOTAL {tot_ms:.3f} ms  {tot_fl / tot_ms / 1e9:.1f} TFLOP/s")
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--grouped", action="store_true", help="time the 4-problem grouped launches of the step")
     ap.add_argument("--iters", type=int, default=10)
     ap.add_argument("--only", default="")
     ap.add_argument("--once", action="store_true", help="one launch per shape (for ncu)")
+    ap.add_argument("--cublas", action="store_true", help="time torch.mm (cuBLASLt) on the same shapes instead")
     args = ap.parse_args()
+    if args.cublas:
+        return cublas(args)
     if args.grouped:
         return grouped(args)
     K = Kernels()
