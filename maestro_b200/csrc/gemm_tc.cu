@@ -18,6 +18,7 @@
 // 16-byte loads (8 rows x 64 B per instruction, the tile pulled into L2 by a TMA prefetch while the main loop runs)
 // and transposed to "thread = row" through the same staging buffer.
 // fp32 outputs (wgrad accumulation) use direct 16-byte stores / red.add.
+#include <algorithm>
 #include <mutex>
 #include <unordered_map>
 #include <string>
@@ -40,6 +41,19 @@ constexpr int EPI_WARP0 = 4;
 constexpr int EPI_WARPS = 16;
 constexpr int STG_BYTES = 32 * 32 * 2;   // one epilogue warp: 32 rows x 32 bf16 columns
 constexpr int MAX_GROUP = 4;
+
+// Diagnostic builds only (tools/_diag/build_diag.sh; results are WRONG, timing only): 1 = the epilogue only reads the
+// accumulator and releases it; 2 = everything but the TMA stores; 3 = direct 16-byte global stores instead of staging + TMA.
+#ifndef MB_DIAG_EPI
+#define MB_DIAG_EPI 0
+#endif
+// bf16 output path of the epilogue: 1 (default) = one 2 KB TMA tile store per 32 x 32 chunk; 0 = staged chunk ->
+// coalesced 16-byte global stores (8 rows x 64 B per warp instruction).  Measured (profiles/r2b_gemm_epilogue.md): equal
+// on plain / residual epilogues, TMA 5-15 % ahead where the epilogue is issue-bound (GELU, GELU').  fp32 outputs
+// (weight gradients) always go through the staging buffer to coalesced red.add / stores.
+#ifndef MB_EPI_TMA_STORE
+#define MB_EPI_TMA_STORE 1
+#endif
 
 // PAIR: two CTAs of a cluster (one TPC) run ONE 256 x BN tcgen05.mma.cta_group::2 tile; each CTA stages its own 128
 // rows of A and HALF of the B tile (BN / 2 rows), so a CTA pulls 32 KB instead of 48 KB per k-block into its SM.
@@ -154,7 +168,7 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
     }
     for (int s = 0; s < 2; ++s) {
       tc::mbar_init(&tfull_bar[s], 1);
-      tc::mbar_init(&tempty_bar[s], (PAIR ? 2 : 1) * EPI_WARPS * 32);   // PAIR: the leader's collects both epilogues
+      tc::mbar_init(&tempty_bar[s], (PAIR ? 2 : 1) * EPI_WARPS);        // one arrival per epilogue warp; PAIR: the leader's collects both CTAs'
     }
     tc::fence_barrier_init();
   }
@@ -187,7 +201,7 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
         {
           // pull this tile's epilogue input (residual / saved gelu') into L2 while the main loop runs
           const TcProblem& P = args.p[tc_.p];
-          if (!(args.flags & GEMM_OUT_F32) && ((args.flags & GEMM_DGELU) || P.residual != nullptr)) {
+          if (MB_DIAG_EPI != 1 && !(args.flags & GEMM_OUT_F32) && ((args.flags & GEMM_DGELU) || P.residual != nullptr)) {
             for (int cc = 0; cc < BN / 64; ++cc) {
               const int c0 = tc_.n_blk * BN + cc * 64;
               if (c0 < P.N) tc::tma_prefetch_l2_2d(&maps.pf[tc_.p], c0, tc_.m_blk * BM);
@@ -294,9 +308,29 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
     uint32_t acc_phase = 0;
     // hand the accumulator back to the MMA issuer (PAIR: the leader CTA's barrier counts both CTAs' epilogue threads)
     const uint32_t te0 = PAIR ? tc::mapa_u32(&tempty_bar[0], 0) : 0u, te1 = PAIR ? tc::mapa_u32(&tempty_bar[1], 0) : 0u;
-    auto release_acc = [&](int a) {
-      if constexpr (PAIR) tc::mbar_arrive_cluster(a == 0 ? te0 : te1);
-      else tc::mbar_arrive(&tempty_bar[a]);
+    auto release_acc = [&](int a) {   // after tcgen05.wait::ld + fence::before_thread_sync of every lane
+      __syncwarp();
+      if (lane == 0) {
+        if constexpr (PAIR) tc::mbar_arrive_cluster(a == 0 ? te0 : te1);
+        else tc::mbar_arrive(&tempty_bar[a]);
+      }
+    };
+    constexpr bool TMA_ST = MB_EPI_TMA_STORE != 0;
+    // staged 32 x 32 bf16 chunk (every lane has written its own row) -> global memory, coalesced: instruction i covers
+    // rows 8i .. 8i+7, four lanes per 64-byte row segment (whole sectors, no completion to wait for)
+    auto flush_chunk = [&](bf16* base, const TcProblem& P, int row0, int col0) {
+      __syncwarp();
+      const int cc = col0 + static_cast<int>(co_j) * 8;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const uint32_t rr = i * 8 + co_row;
+        const uint32_t a = stg_u32 + rr * 64 + ((co_j ^ ((rr >> 1) & 3)) << 4);
+        uint4 v;
+        asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a) : "memory");
+        const int row = row0 + static_cast<int>(rr);
+        if (MB_DIAG_EPI != 2 && row < P.M && cc < P.N)
+          *reinterpret_cast<uint4*>(base + static_cast<size_t>(row) * P.ldc + cc) = v;
+      }
     };
     constexpr bool SPEC = EF >= 0;
     const bool out_f32 = SPEC ? false : (args.flags & GEMM_OUT_F32) != 0;
@@ -322,7 +356,7 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
         const bool has_res = SPEC ? (EF & EPI_RES) != 0 : P.residual != nullptr;
         const bool has_bias = SPEC ? (EF & EPI_BIAS) != 0 : P.bias != nullptr;
         const bool has_colsum = SPEC ? (EF & EPI_COLSUM) != 0 : P.colsum != nullptr;
-        const bool need_in = f_dgelu || has_res;
+        const bool need_in = (MB_DIAG_EPI != 1) && (f_dgelu || has_res);
         const bf16* src = static_cast<const bf16*>(f_dgelu ? P.aux : P.residual);
 #pragma unroll 1
         for (int c2 = 0; c2 < nch; ++c2) {
@@ -352,9 +386,12 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
             tc::tc_fence_before();
             release_acc(acc);
           }
+#if MB_DIAG_EPI == 1
+          continue;
+#endif
           // (3) transpose the input chunk to "thread = row" through the staging buffer
           if (need_in) {
-            if (lane == 0) tc::tma_store_wait_read();
+            if (TMA_ST && lane == 0) tc::tma_store_wait_read();
             __syncwarp();
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
@@ -395,7 +432,7 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
           // erf / exp terms are shared between the activation and its derivative)
           uint32_t o[16];
           if (f_gelu) {
-            if (lane == 0) tc::tma_store_wait_read();
+            if (TMA_ST && lane == 0) tc::tma_store_wait_read();
             __syncwarp();
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
@@ -410,11 +447,15 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
               asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(own_base + ((j ^ own_x) << 4)), "r"(w[0]),
                            "r"(w[1]), "r"(w[2]), "r"(w[3]) : "memory");
             }
-            tc::fence_proxy_async();
-            __syncwarp();
-            if (lane == 0) {
-              tc::tma_store_2d(&maps.x[tc_.p], stg, col0, row0);
-              tc::tma_store_commit();
+            if constexpr (TMA_ST) {
+              tc::fence_proxy_async();
+              __syncwarp();
+              if (lane == 0 && MB_DIAG_EPI != 2) {
+                tc::tma_store_2d(&maps.x[tc_.p], stg, col0, row0);
+                tc::tma_store_commit();
+              }
+            } else {
+              flush_chunk(static_cast<bf16*>(P.aux), P, row0, col0);
             }
           }
           // (6) GELU' / residual
@@ -430,7 +471,21 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
             }
           }
           // (7) main output
-          if (lane == 0) tc::tma_store_wait_read();
+#if MB_DIAG_EPI == 3
+          if (!f_gelu && !has_colsum) {
+            if (row0 + lane < P.M) {
+              bf16* crow = static_cast<bf16*>(P.C) + static_cast<size_t>(row0 + lane) * P.ldc + col0;
+#pragma unroll
+              for (int j = 0; j < 4; ++j)
+                if (col0 + j * 8 < P.N)
+                  *reinterpret_cast<uint4*>(crow + j * 8) =
+                      make_uint4(pack_bf16x2(v2[4 * j].x, v2[4 * j].y), pack_bf16x2(v2[4 * j + 1].x, v2[4 * j + 1].y),
+                                 pack_bf16x2(v2[4 * j + 2].x, v2[4 * j + 2].y), pack_bf16x2(v2[4 * j + 3].x, v2[4 * j + 3].y));
+            }
+            continue;
+          }
+#endif
+          if (TMA_ST && lane == 0) tc::tma_store_wait_read();
           __syncwarp();
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
@@ -444,11 +499,15 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
             asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(own_base + ((j ^ own_x) << 4)), "r"(w0),
                          "r"(w1), "r"(w2), "r"(w3) : "memory");
           }
-          tc::fence_proxy_async();
-          __syncwarp();
-          if (lane == 0) {
-            tc::tma_store_2d(&maps.c[tc_.p], stg, col0, row0);
-            tc::tma_store_commit();
+          if constexpr (TMA_ST) {
+            tc::fence_proxy_async();
+            __syncwarp();
+            if (lane == 0 && MB_DIAG_EPI != 2) {
+              tc::tma_store_2d(&maps.c[tc_.p], stg, col0, row0);
+              tc::tma_store_commit();
+            }
+          } else {
+            flush_chunk(static_cast<bf16*>(P.C), P, row0, col0);
           }
           // (8) optional column sums of the rounded outputs (bias gradient of the layer that produced this dY): lane
           // l walks column l of the staged 32 x 32 chunk (one conflict-free 64-byte row segment per step)
@@ -473,9 +532,6 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
         // ---------------- fp32 outputs (gradient accumulation): direct 16-byte stores / red.add ----------------
         tc::mbar_wait(&tfull_bar[acc], acc_phase);
         tc::tc_fence_after();
-        const int row = row0 + lane;
-        const bool row_ok = row < P.M;
-        float* crow = static_cast<float*>(P.C) + static_cast<size_t>(row_ok ? row : 0) * P.ldc;
 #pragma unroll 1
         for (int c2 = 0; c2 < nch; ++c2) {
           const int ch = quarter * CH_PER_Q + c2;
@@ -487,19 +543,36 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
             tc::tc_fence_before();
             release_acc(acc);
           }
-          if (row_ok) {
+          if (MB_DIAG_EPI != 1) {
+            // 16 columns at a time through the staging buffer (32 rows x 64 B, same swizzle as the bf16 chunks), then
+            // coalesced: one red / store instruction covers 8 rows x 64 B instead of 32 rows x 16 B
+            const bool accum = (args.flags & GEMM_ACCUM) != 0;
 #pragma unroll
-            for (int q = 0; q < 8; ++q) {
-              const int col = col0 + q * 4;
-              if (col >= P.N) break;
-              float4 o = make_float4(__uint_as_float(r[4 * q]) * alpha, __uint_as_float(r[4 * q + 1]) * alpha,
-                                     __uint_as_float(r[4 * q + 2]) * alpha, __uint_as_float(r[4 * q + 3]) * alpha);
-              if (P.bias != nullptr) {
-                const float4 b = __ldg(reinterpret_cast<const float4*>(P.bias + col));
-                o.x += b.x; o.y += b.y; o.z += b.z; o.w += b.w;
+            for (int h = 0; h < 2; ++h) {
+              __syncwarp();
+#pragma unroll
+              for (int j = 0; j < 4; ++j)
+                asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(own_base + ((j ^ own_x) << 4)),
+                             "r"(r[16 * h + 4 * j]), "r"(r[16 * h + 4 * j + 1]), "r"(r[16 * h + 4 * j + 2]),
+                             "r"(r[16 * h + 4 * j + 3]) : "memory");
+              __syncwarp();
+              const int col = col0 + h * 16 + static_cast<int>(co_j) * 4;
+              float4 b = make_float4(0.f, 0.f, 0.f, 0.f);
+              if (P.bias != nullptr && col < P.N) b = __ldg(reinterpret_cast<const float4*>(P.bias + col));
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                const uint32_t rr = i * 8 + co_row;
+                const uint32_t a = stg_u32 + rr * 64 + ((co_j ^ ((rr >> 1) & 3)) << 4);
+                float4 o;
+                asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(o.x), "=f"(o.y), "=f"(o.z), "=f"(o.w) : "r"(a) : "memory");
+                const int row = row0 + static_cast<int>(rr);
+                if (row < P.M && col < P.N) {
+                  o.x = fmaf(o.x, alpha, b.x); o.y = fmaf(o.y, alpha, b.y); o.z = fmaf(o.z, alpha, b.z); o.w = fmaf(o.w, alpha, b.w);
+                  float4* dst = reinterpret_cast<float4*>(static_cast<float*>(P.C) + static_cast<size_t>(row) * P.ldc + col);
+                  if (accum) atomicAdd(dst, o);
+                  else *dst = o;
+                }
               }
-              if (args.flags & GEMM_ACCUM) atomicAdd(reinterpret_cast<float4*>(crow + col), o);
-              else *reinterpret_cast<float4*>(crow + col) = o;
             }
           }
         }
@@ -578,17 +651,53 @@ int launch(const GemmParams* Ps, int count, cudaStream_t st) {
     maps.a[i] = maps.a[0]; maps.b[i] = maps.b[0]; maps.c[i] = maps.c[0]; maps.x[i] = maps.x[0];
     maps.pf[i] = maps.pf[0];
   }
+  // Split-K (weight gradients; fp32 red.add combines the partials): work items of at most `split_target` k-blocks.
+  // The target minimises the makespan of the persistent schedule (item t runs on CTA t mod grid; an item costs its
+  // k-blocks plus an epilogue) over the whole group -- "cover the chip twice" left e.g. 180 items for 74 CTA pairs
+  // (3 waves of 47 k-blocks, the last one 43 % full) where 144 items (2 waves of 59) do the same work 16 % sooner.
+  int split_target = 1 << 30;
+  if (flags & GEMM_ACCUM) {
+    const int slots = MC ? num_sms() / 2 : num_sms();
+    int kbs[MAX_GROUP], max_kb = 1;
+    for (int i = 0; i < count; ++i) { kbs[i] = (a.p[i].K + BK - 1) / BK; max_kb = std::max(max_kb, kbs[i]); }
+    constexpr int EPI_KB = 6;           // a 128 x 256 fp32 red epilogue costs about as much as 6 k-blocks
+    long long best = -1;
+    int prev_sp[MAX_GROUP] = {0, 0, 0, 0};
+    int load[256];
+    for (int tgt = max_kb; tgt >= std::min(max_kb, 4); --tgt) {
+      int sp[MAX_GROUP];
+      bool same = true;
+      long long items = 0;
+      for (int i = 0; i < count; ++i) {
+        sp[i] = (kbs[i] + tgt - 1) / tgt;
+        same = same && sp[i] == prev_sp[i];
+        items += static_cast<long long>(a.p[i].mblocks) * a.p[i].nblocks * sp[i];
+      }
+      if (same) continue;
+      for (int i = 0; i < count; ++i) prev_sp[i] = sp[i];
+      if (items > 16 * slots) break;    // finer than 16 waves never wins
+      const int grid = static_cast<int>(std::min<long long>(items, std::min(slots, 256)));
+      for (int c = 0; c < grid; ++c) load[c] = 0;
+      int c = 0;
+      for (int i = 0; i < count; ++i) {
+        const int len = (kbs[i] + sp[i] - 1) / sp[i] + EPI_KB;
+        const int n = a.p[i].mblocks * a.p[i].nblocks * sp[i];
+        for (int t = 0; t < n; ++t) { load[c] += len; if (++c == grid) c = 0; }
+      }
+      int span = 0;
+      for (int k = 0; k < grid; ++k) span = std::max(span, load[k]);
+      // +items: red traffic grows with the number of partial tiles (tie-break towards fewer splits)
+      const long long cost = static_cast<long long>(span) * 4096 + items;
+      if (best < 0 || cost < best) { best = cost; split_target = tgt; }
+    }
+  }
   int total = 0;
   for (int i = 0; i < count; ++i) {
     TcProblem& q = a.p[i];
     const int kblocks = (q.K + BK - 1) / BK;
     int splits = 1;
     if (flags & GEMM_ACCUM) {
-      // split the contraction so that the grid covers the chip (fp32 red.add combines the partials)
-      const long long slots = MC ? num_sms() / 2 : num_sms();
-      splits = static_cast<int>((2LL * slots + tiles_mn_total - 1) / tiles_mn_total);
-      if (splits > kblocks) splits = kblocks;
-      if (splits < 1) splits = 1;
+      splits = (kblocks + split_target - 1) / split_target;
       const int per = (kblocks + splits - 1) / splits;
       splits = (kblocks + per - 1) / per;  // no empty split
     }
@@ -641,9 +750,12 @@ int launch(const GemmParams* Ps, int count, cudaStream_t st) {
   return e == cudaSuccess ? 0 : static_cast<int>(e);
 }
 
-// MB_GEMM_PAIR = 0: never, 1: always, 2 (default): where it measured faster (tools/gemm_bench.py, profiles/):
-// long-K weight-gradient GEMMs gain 11-15 % from the lower operand traffic per SM; short-K tiles are bound by their
-// epilogue and lose 5-10 % to the coupling of the two CTAs' epilogues, so they stay on single-CTA tiles.
+// MB_GEMM_PAIR = 0: never, 1: always, 2 (default): where it measured faster (tools/gemm_bench.py,
+// profiles/r2b_gemm_epilogue.md).  A pair stages 32 KB instead of 48 KB per k-block into each SM, which is what lets
+// the epilogue's stores and the operand loads share the L2: every shape of the transformer blocks gains 6-12 % except
+// the short-K bias + residual out-projections (equal), which stay on single-CTA tiles.  (Before r2b the pair's
+// accumulator hand-back was a cluster-scope release arrive = MEMBAR.ALL.GPU per epilogue thread, and pairs had no
+// compile-time epilogues; both made short-K pairs slower than single tiles.)
 int pair_mode() {
   static int mode = -1;
   if (mode < 0) {
@@ -653,10 +765,28 @@ int pair_mode() {
   return mode;
 }
 
+template <int BN, bool A_MN, bool B_MN, bool MC>
+int launch_epi(const GemmParams* Ps, int count, cudaStream_t st, int ef) {
+  if constexpr (!A_MN) {
+    if constexpr (!B_MN) {      // forward: y = x W^T
+      if (ef == EPI_PLAIN) return launch<BN, A_MN, B_MN, MC, EPI_PLAIN>(Ps, count, st);
+      if (ef == (EPI_BIAS | EPI_RES)) return launch<BN, A_MN, B_MN, MC, EPI_BIAS | EPI_RES>(Ps, count, st);
+      if (ef == (EPI_BIAS | EPI_GELU)) return launch<BN, A_MN, B_MN, MC, EPI_BIAS | EPI_GELU>(Ps, count, st);
+    } else {                    // dgrad: dx = dy W
+      if (ef == EPI_PLAIN) return launch<BN, A_MN, B_MN, MC, EPI_PLAIN>(Ps, count, st);
+      if (ef == EPI_COLSUM) return launch<BN, A_MN, B_MN, MC, EPI_COLSUM>(Ps, count, st);
+      if (ef == (EPI_DGELU | EPI_COLSUM)) return launch<BN, A_MN, B_MN, MC, EPI_DGELU | EPI_COLSUM>(Ps, count, st);
+      if (ef == EPI_DGELU) return launch<BN, A_MN, B_MN, MC, EPI_DGELU>(Ps, count, st);
+    }
+  }
+  return launch<BN, A_MN, B_MN, MC>(Ps, count, st);
+}
+
 template <int BN, bool A_MN, bool B_MN>
 int launch_any(const GemmParams* Ps, int count, cudaStream_t st) {
   bool mc = pair_mode() == 1;
-  if (pair_mode() == 2 && (Ps[0].flags & GEMM_ACCUM)) {
+  if (pair_mode() == 2) {
+    static const int pair_min_k = [] { const char* e = std::getenv("MB_GEMM_PAIR_MINK"); return e ? std::atoi(e) : 4000; }();
     long long singles = 0, pairs = 0;
     int max_k = 0;
     for (int i = 0; i < count; ++i) {
@@ -665,11 +795,13 @@ int launch_any(const GemmParams* Ps, int count, cudaStream_t st) {
       pairs += (mb + 1) / 2 * nb;
       max_k = Ps[i].K > max_k ? Ps[i].K : max_k;
     }
-    mc = 2 * pairs == singles && max_k >= 12000;
+    const bool pairable = 40 * pairs <= 21 * singles;     // at most 5 % of the pair tiles' rows are padding
+    if (Ps[0].flags & GEMM_ACCUM) mc = pairable && max_k >= pair_min_k;
+    else if (Ps[0].flags & GEMM_OUT_F32) mc = false;
+    else mc = pairable && !(Ps[0].residual != nullptr && max_k <= 1024);
   }
   if (Ps[0].flags & GEMM_PAIR_ON) mc = true;
   if (Ps[0].flags & GEMM_PAIR_OFF) mc = false;
-  if (mc) return launch<BN, A_MN, B_MN, true>(Ps, count, st);
   // compile-time epilogues for the shapes of the transformer blocks (bf16 out, alpha = 1, the same inputs / outputs
   // in every problem of the group); MB_GEMM_EPI=0 keeps the run-time epilogue (A/B measurements)
   static const bool spec_on = [] { const char* e = std::getenv("MB_GEMM_EPI"); return !(e && e[0] == '0'); }();
@@ -686,19 +818,7 @@ int launch_any(const GemmParams* Ps, int count, cudaStream_t st) {
           (Ps[i].colsum != nullptr) != (Ps[0].colsum != nullptr))
         ef = EPI_GENERIC;
   }
-  if constexpr (!A_MN) {
-    if constexpr (!B_MN) {      // forward: y = x W^T
-      if (ef == EPI_PLAIN) return launch<BN, A_MN, B_MN, false, EPI_PLAIN>(Ps, count, st);
-      if (ef == (EPI_BIAS | EPI_RES)) return launch<BN, A_MN, B_MN, false, EPI_BIAS | EPI_RES>(Ps, count, st);
-      if (ef == (EPI_BIAS | EPI_GELU)) return launch<BN, A_MN, B_MN, false, EPI_BIAS | EPI_GELU>(Ps, count, st);
-    } else {                    // dgrad: dx = dy W
-      if (ef == EPI_PLAIN) return launch<BN, A_MN, B_MN, false, EPI_PLAIN>(Ps, count, st);
-      if (ef == EPI_COLSUM) return launch<BN, A_MN, B_MN, false, EPI_COLSUM>(Ps, count, st);
-      if (ef == (EPI_DGELU | EPI_COLSUM)) return launch<BN, A_MN, B_MN, false, EPI_DGELU | EPI_COLSUM>(Ps, count, st);
-      if (ef == EPI_DGELU) return launch<BN, A_MN, B_MN, false, EPI_DGELU>(Ps, count, st);
-    }
-  }
-  return launch<BN, A_MN, B_MN, false>(Ps, count, st);
+  return mc ? launch_epi<BN, A_MN, B_MN, true>(Ps, count, st, ef) : launch_epi<BN, A_MN, B_MN, false>(Ps, count, st, ef);
 }
 
 }  // namespace
@@ -740,7 +860,9 @@ extern "C" int mb_gemm_tc_grouped(const GemmParams* params, int count, void* str
     }
     const long long sms = num_sms();
     const long long w256 = (t256 + sms - 1) / sms * 256;
-    const long long w128 = (t128 + sms - 1) / sms * 141;  // 128 * 1.1
+    // measured (profiles/r2b_gemm_epilogue.md): a 128-wide k-block takes 0.76 of a 256-wide one (128 x 128 MMAs read
+    // A + B from shared memory at the port's full rate), not 0.5
+    const long long w128 = (t128 + sms - 1) / sms * 195;
     wide = w256 <= w128;
   }
   if (a_k && b_k) return wide ? launch_any<256, false, false>(live, n, st) : launch_any<128, false, false>(live, n, st);

@@ -195,9 +195,12 @@ __device__ __forceinline__ uint32_t mapa_u32(const void* ptr, uint32_t rank) {
   asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(smem_u32(ptr)), "r"(rank));
   return r;
 }
-// arrive on an mbarrier of another CTA of the cluster (address from mapa_u32)
+// arrive on an mbarrier of another CTA of the cluster (address from mapa_u32).  Default semantics (.release.cta): the
+// cluster-scope release form compiles to MEMBAR.ALL.GPU + CCTL.IVALL per arriving thread, i.e. every epilogue thread
+// waits for the acknowledgement of all its outstanding global stores before it can hand the accumulator back.  The
+// hand-over only orders tcgen05.ld against the next MMA, which the tcgen05 fences on both sides do.
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
 // TMA load into this CTA's shared memory whose completion bytes are counted on an mbarrier that may live in the peer
 // CTA of the pair (`bar_cluster_addr` from mapa_u32).

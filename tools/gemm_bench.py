@@ -72,7 +72,7 @@ def grouped(args):
     for stack in ("enc", "dec"):
         kinds = [c[0].split("/")[1] for c in allc if c[0].startswith(f"{stack}_aerial/")]
         for kind in kinds:
-            if args.only and args.only not in f"{stack}/{kind}":
+            if args.only and not any(t in f"{stack}/{kind}" for t in args.only.split(",")):
                 continue
             probs = [build(*c, dev) for c in allc if c[0].startswith(stack + "_") and c[0].endswith("/" + kind)]
             fl = sum(2.0 * a[3] * a[4] * a[5] for a, _ in probs)
@@ -100,7 +100,7 @@ def cublas(args):
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     tot_fl, tot_ms = 0.0, 0.0
     for name, layout, M, N, Kd, _ in cases():
-        if args.only and args.only not in name:
+        if args.only and not any(t in name for t in args.only.split(",")):
             continue
         if layout == "k":
             A, B = torch.randn(M, Kd, device=dev).to(bf), torch.randn(N, Kd, device=dev).to(bf)
@@ -148,7 +148,7 @@ def main():
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     tot_fl, tot_ms = 0.0, 0.0
     for name, layout, M, N, Kd, epi in cases():
-        if args.only and args.only not in name:
+        if args.only and not any(t in name for t in args.only.split(",")):
             continue
         bf = torch.bfloat16
         if layout in ("k", "kmn"):
