@@ -163,8 +163,8 @@ __global__ void __launch_bounds__(DKDV_THREADS) attn_bwd_dkdv_kernel(const __gri
   auto put_stats = [&](int j) {
     if (tid < SUB) {
       float* d = s_stat + (j & 1) * 2 * SUB;
-      d[tid] = n_lse * 1.4426950408889634f;
-      d[SUB + tid] = n_delta * sc;                            // delta pre-multiplied by the score scale
+      d[tid] = n_lse * -1.4426950408889634f;                  // both NEGATED: they are the addends of the packed FMAs
+      d[SUB + tid] = n_delta * -sc;                           // delta pre-multiplied by the score scale
     }
   };
   fetch_stats(0);
@@ -204,15 +204,15 @@ __global__ void __launch_bounds__(DKDV_THREADS) attn_bwd_dkdv_kernel(const __gri
         const float ls[8] = {l0.x, l0.y, l0.z, l0.w, l1.x, l1.y, l1.z, l1.w};
         const float ds[8] = {e0.x, e0.y, e0.z, e0.w, e1.x, e1.y, e1.z, e1.w};
 #pragma unroll
-        for (int k2 = 0; k2 < 4; ++k2) {
-          float p2[2], d2[2];
-#pragma unroll
-          for (int e = 0; e < 2; ++e) {
-            const int idx = v8 * 8 + 2 * k2 + e;
-            const float p = fast_exp2(fmaf(__uint_as_float(s[idx]), c, -ls[2 * k2 + e]));
-            p2[e] = p;
-            d2[e] = p * fmaf(__uint_as_float(dp[idx]), sc, -ds[2 * k2 + e]);
-          }
+        for (int k2 = 0; k2 < 4; ++k2) {   // packed fp32 (FFMA2 / FMUL2)
+          const int idx = v8 * 8 + 2 * k2;
+          const float2 x = fma2(make_float2(__uint_as_float(s[idx]), __uint_as_float(s[idx + 1])), splat2(c),
+                                make_float2(ls[2 * k2], ls[2 * k2 + 1]));
+          const float2 g = fma2(make_float2(__uint_as_float(dp[idx]), __uint_as_float(dp[idx + 1])), splat2(sc),
+                                make_float2(ds[2 * k2], ds[2 * k2 + 1]));
+          const float2 p2v = make_float2(fast_exp2(x.x), fast_exp2(x.y));
+          const float2 d2v = mul2(p2v, g);
+          const float p2[2] = {p2v.x, p2v.y}, d2[2] = {d2v.x, d2v.y};
           __nv_bfloat162 hp = __floats2bfloat162_rn(p2[0], p2[1]);
           __nv_bfloat162 hd = __floats2bfloat162_rn(d2[0], d2[1]);
           wp[k2] = *reinterpret_cast<uint32_t*>(&hp);

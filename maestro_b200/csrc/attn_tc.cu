@@ -6,8 +6,8 @@
 //         o   [Bn * N, H * DH] bf16, lse [Bn, H, N] fp32 (natural log of the softmax denominator, scaled scores).
 //
 // Forward: one CTA (128 threads) per (sample, head, 128-query tile).  Thread t owns query row t == TMEM lane t, so
-// row max / row sum need no shuffles.  Per 64-key tile: S = Q K^T (tcgen05.mma, fp32 in TMEM) -> two passes of
-// tcgen05.ld over the row (max, then exp2 + sum) -> P (bf16) written to shared memory in the K-major 128B-swizzle
+// row max / row sum need no shuffles.  Per 64-key tile: S = Q K^T (tcgen05.mma, fp32 in TMEM) -> the row's 64 scores
+// in registers (one tcgen05.ld pass; ragged last tiles: two masked passes) -> max, exp2 + sum -> P (bf16) written to shared memory in the K-major 128B-swizzle
 // layout -> O_tile = P V (V consumed as an MN-major operand straight from its TMA tile) -> registers accumulate
 // O with the online-softmax rescale.  K/V tiles are double-buffered; the next S = Q K^T is issued before the
 // current P V result is consumed so the tensor pipe overlaps the exp work.  S (64 columns) + O (<= 64) take 128
@@ -29,6 +29,12 @@ struct mb_attn_problem {     // mirror of include/maestro_b200.h
 
 namespace {
 
+// Full key tiles read their 64 scores from TMEM once (64 registers) instead of once for the max and once for the exp;
+// with the register budget pinned to 4 CTAs per SM (3 at dh = 64) the forward is 12 % faster over the step's shapes
+// (profiles/r2b_attn_probe.txt: 2.33 -> 2.05 ms; without the pin 2.45 ms -- occupancy matters more than the pass).
+#ifndef MB_ATTN_FWD_ONEPASS
+#define MB_ATTN_FWD_ONEPASS 1   // A/B builds: tools/_diag/build_diag.sh
+#endif
 constexpr int BQ = 128;   // query rows per CTA
 constexpr int BKV = 64;   // keys per tile: S (64) + O (<= 64) fit 128 TMEM columns -> up to 4 CTAs share an SM
 
@@ -64,8 +70,11 @@ struct AttnGroup {
   int count;
 };
 
+#ifndef MB_ATTN_FWD_MINB
+#define MB_ATTN_FWD_MINB 4
+#endif
 template <int DH>
-__global__ void __launch_bounds__(128) attn_fwd_kernel(const __grid_constant__ AttnGroup grp) {
+__global__ void __launch_bounds__(128, (MB_ATTN_FWD_MINB > 1 && DH == 64) ? MB_ATTN_FWD_MINB - 1 : MB_ATTN_FWD_MINB) attn_fwd_kernel(const __grid_constant__ AttnGroup grp) {
   using C_ = ACfg<DH>;
   int pi = 0, cta0 = 0;
 #pragma unroll
@@ -170,8 +179,46 @@ __global__ void __launch_bounds__(128) attn_fwd_kernel(const __grid_constant__ A
     const int kv_valid = min(BKV, N - j * BKV);
     tc::mbar_wait(bar_s, ph);
     tc::tc_fence_after();
+    float mx, alpha, mc, lsum;
+#if MB_ATTN_FWD_ONEPASS
+    if (kv_valid == BKV) {
+      // full tile: the 64 scores of the row are read from TMEM ONCE (64 registers), then max -> exp2 -> P
+      uint32_t r[64];
+      tc::tmem_ld_32x32(tm_s + lane_base, r);
+      tc::tmem_ld_32x32(tm_s + lane_base + 32, r + 32);
+      tc::tmem_ld_wait();
+      float m4[4] = {__uint_as_float(r[0]), __uint_as_float(r[1]), __uint_as_float(r[2]), __uint_as_float(r[3])};
+#pragma unroll
+      for (int i = 4; i < 64; i += 4) {
+        m4[0] = fmaxf(m4[0], __uint_as_float(r[i]));
+        m4[1] = fmaxf(m4[1], __uint_as_float(r[i + 1]));
+        m4[2] = fmaxf(m4[2], __uint_as_float(r[i + 2]));
+        m4[3] = fmaxf(m4[3], __uint_as_float(r[i + 3]));
+      }
+      mx = fmaxf(fmaxf(m_run, fmaxf(m4[0], m4[1])), fmaxf(m4[2], m4[3]));
+      alpha = exp2f((m_run - mx) * c);
+      mc = mx * c;
+      float ls[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+      for (int c16 = 0; c16 < 8; ++c16) {
+        uint32_t w[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {   // scalar on purpose: the packed form (FFMA2 / FADD2) needs aligned register pairs
+          // and spills at the 128-register budget that keeps 4 CTAs per SM (measured 2.06 -> 2.20 ms per step)
+          const float p0 = fast_exp2(fmaf(__uint_as_float(r[c16 * 8 + 2 * i]), c, -mc));
+          const float p1 = fast_exp2(fmaf(__uint_as_float(r[c16 * 8 + 2 * i + 1]), c, -mc));
+          ls[i] += p0 + p1;
+          __nv_bfloat162 hb = __floats2bfloat162_rn(p0, p1);
+          w[i] = *reinterpret_cast<uint32_t*>(&hb);
+        }
+        *reinterpret_cast<uint4*>(p_row + ((c16 ^ (tid & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
+      }
+      lsum = (ls[0] + ls[1]) + (ls[2] + ls[3]);
+    } else
+#endif
+    {
     // pass 1: row max over the valid keys (mask-free for chunks that lie entirely inside the sequence)
-    float mx = m_run;
+    mx = m_run;
 #pragma unroll 1
     for (int ch = 0; ch < BKV / 32; ++ch) {
       if (ch * 32 >= kv_valid) break;
@@ -192,9 +239,9 @@ __global__ void __launch_bounds__(128) attn_fwd_kernel(const __grid_constant__ A
           if (ch * 32 + i < kv_valid) mx = fmaxf(mx, __uint_as_float(r[i]));
       }
     }
-    const float alpha = exp2f((m_run - mx) * c);   // m_run = -inf on the first tile -> 0
-    const float mc = mx * c;
-    float lsum = 0.f;
+    alpha = exp2f((m_run - mx) * c);   // m_run = -inf on the first tile -> 0
+    mc = mx * c;
+    lsum = 0.f;
     // pass 2: p = exp2(s * c - m * c), write bf16 P row (K-major, 128B swizzle), accumulate the row sum
     if (kv_valid == BKV) {
       // full tile: no masks; 4 independent partial sums keep the FADD chain short
@@ -245,6 +292,7 @@ __global__ void __launch_bounds__(128) attn_fwd_kernel(const __grid_constant__ A
           *reinterpret_cast<uint4*>(p_row + ((c16 ^ (tid & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
         }
       }
+    }
     }
     l_run = l_run * alpha + lsum;
     m_run = mx;
