@@ -14,6 +14,7 @@ schedule (captured lazily per batch shape), the gradient all-reduce ranges overl
 from __future__ import annotations
 
 import copy
+import os
 
 import torch
 from torch import nn
@@ -66,11 +67,18 @@ class SSLModule(nn.Module):
         # GraphedPretrainStep options of the fused path: raw_rasters (on-disk dtypes finished on the device),
         # struct_on_device / struct_seed (Philox structural mask instead of the host generator)
         self.fused_options: dict = {}
+        # Opt-in (MB_OPT_OVERLAP=1): the fused AdamW range by range on a side stream, each range as soon as its gradients
+        # are final (and all-reduced), under the remaining backward segments instead of after them.  Measured slower than
+        # one pass after the backward (FLAIR-HUB ViT-B: 1 GPU 24.62 vs 24.06 ms, 2 GPUs 26.19 vs 25.45 ms,
+        # profiles/r2b_summary.md): the 11 GB streaming pass takes L2 / HBM from the GEMMs it runs beside.
+        self.overlap_optimizer = os.environ.get("MB_OPT_OVERLAP", "0") == "1"
+        self._opt_stream = None
         self.ssl_phase = "pretrain"          # the reference reads it from self.trainer.ssl_phase
 
     def __getstate__(self):  # noqa: ANN204
         state = self.__dict__.copy()
         state["_graphed"], state["_reducer"], state["_ema_flat"], state["_staged_src"] = {}, None, None, None
+        state["_opt_stream"] = None
         return state
 
     # ------------------------------------------------------------------ reconstruction loss / logs (pretraining)
@@ -266,6 +274,17 @@ class SSLModule(nn.Module):
                 eng.grads_dirty = True
                 marks = [] if (next_batch is not None and self._fused_calls == 2 and self.h2d_gate is None) else None
                 gate = 0 if self.h2d_gate is None else self.h2d_gate
+                overlap = (optimizer is not None and self.overlap_optimizer and hasattr(optimizer, "step_range")
+                           and len(g.graphs) == len(eng.BWD_SEGMENTS))
+                if overlap:
+                    main = torch.cuda.current_stream(eng.device)
+                    side = self._reducer.comm if (self._reducer is not None and self._reducer.comm is not None) else None
+                    if side is None:
+                        if self._opt_stream is None:
+                            self._opt_stream = torch.cuda.Stream(device=eng.device)
+                        side = self._opt_stream
+                    ranges = eng.grad_ranges()
+                    optimizer.step_begin(grad_scale=1.0 / world)     # hyper-parameters: on the main stream, ahead of graph 0
                 for i in range(len(g.graphs)):
                     if next_batch is not None and i == gate:
                         g.prefetch(next_batch, after_current_work=i > 0)
@@ -275,7 +294,18 @@ class SSLModule(nn.Module):
                     g.replay(i)
                     if self._reducer is not None:
                         self._reducer.reduce_range(i)
-                if self._reducer is not None:
+                    if overlap:
+                        # range i is final after segment i (and summed over the ranks by the collective just queued on
+                        # `side`); no later segment reads its parameters or writes its gradients
+                        side.wait_stream(main)
+                        with torch.cuda.stream(side):
+                            optimizer.step_range(*ranges[i])
+                if overlap:
+                    main.wait_stream(side)
+                    eng.shadows_fresh = True
+                    eng.grads_dirty = False
+                    optimizer = None
+                elif self._reducer is not None:
                     self._reducer.finish()
                 loss = g.loss
             if optimizer is not None:

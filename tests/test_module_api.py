@@ -228,3 +228,37 @@ def test_graph_replay_sees_new_weights(monkeypatch):
     mod.model._engine(torch.device("cuda"))                   # notices the version bump -> shadows stale
     l1 = float(g.replay())
     assert abs(l1 - l0) > 1e-3 * abs(l0), (l0, l1)
+
+
+@pytest.mark.gpu
+def test_fused_step_overlapped_optimizer_equals_serial(monkeypatch):
+    """The fused AdamW stepped range by range on a side stream, each range right after the backward segment that
+    finalises its gradients (the default of ``pretrain_step_fused(..., optimizer=...)``), must give the parameters of
+    one AdamW pass after the whole backward."""
+    monkeypatch.setenv("MAESTRO_B200_PRECISION", "fp32")
+    spec, hp, sd, batch, inter, loss, seed, bs = U.case_inputs("micro_flair")
+
+    def run(overlap):
+        mod = SSLModule(spec, MaskSpec(), inter_depth=inter, model_size="tiny", loss=loss)
+        mod.model = MAE(spec, MaskSpec(), inter_depth=inter, **hp)
+        mod.model.load_state_dict(sd, strict=False)
+        mod.cuda()
+        mod.overlap_optimizer = overlap
+        opt = mod.configure_optimizers_fused(lr=1e-2, total_steps=100, weight_decay=0.01)
+        torch.manual_seed(11)
+        losses = []
+        for step in range(4):
+            b = {k: v.cuda() for k, v in batch.items()}
+            losses.append(mod.pretrain_step_fused(b, graph=True, optimizer=opt)["loss"].clone())
+        torch.cuda.synchronize()
+        eng = mod.model._eng
+        assert eng.shadows_fresh and not eng.grads_dirty
+        assert float(eng.arena.grad.abs().max()) == 0.0          # the update zeroed every range of the gradient arena
+        return [float(x) for x in losses], eng.arena.param.detach().clone(), opt.m.clone()
+
+    la, pa, ma = run(True)
+    lb, pb, mb = run(False)
+    assert la[0] == pytest.approx(lb[0], rel=1e-6) and la[-1] == pytest.approx(lb[-1], rel=1e-4)
+    assert la[-1] != la[0]                                       # the parameters moved
+    assert float((pa - pb).norm() / pb.norm()) < 1e-5
+    assert float((ma - mb).norm() / mb.norm()) < 1e-4
