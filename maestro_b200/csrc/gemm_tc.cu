@@ -54,15 +54,23 @@ constexpr int MAX_GROUP = 4;
 #ifndef MB_EPI_TMA_STORE
 #define MB_EPI_TMA_STORE 1
 #endif
+#ifndef MB_EPI_STG_BUFS
+#define MB_EPI_STG_BUFS 1   // 2: see Cfg::STG_BUFS (measured: +3 % on the K = 512 GELU / GELU' GEMMs, -2..4 % everywhere else)
+#endif
 
 // PAIR: two CTAs of a cluster (one TPC) run ONE 256 x BN tcgen05.mma.cta_group::2 tile; each CTA stages its own 128
 // rows of A and HALF of the B tile (BN / 2 rows), so a CTA pulls 32 KB instead of 48 KB per k-block into its SM.
-template <int BN, bool PAIR> struct Cfg {
+template <int BN, bool PAIR, int EF = -1> struct Cfg {
   static constexpr int B_ROWS = PAIR ? BN / 2 : BN;
   static constexpr int B_BYTES = B_ROWS * BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int STAGES = PAIR ? ((BN == 256) ? 6 : 8) : ((BN == 256) ? 4 : 6);
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_WARPS * STG_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+  // MB_EPI_STG_BUFS=2 (A/B builds): pair tiles with a compile-time bf16 epilogue alternate between TWO staging buffers
+  // per epilogue warp, so a warp only waits for the TMA store before the last one (cp.async.bulk.wait_group.read 1) --
+  // paid with one operand stage of the pair's ring (6 -> 5 / 8 -> 6).  Measured (profiles/r2b_summary.md): the operand
+  // stage is worth more on every shape except the K = 512 GELU / GELU' GEMMs; off by default.
+  static constexpr int STG_BUFS = (PAIR && EF >= 0 && MB_EPI_STG_BUFS == 2) ? 2 : 1;
+  static constexpr int STAGES = PAIR ? ((BN == 256) ? (STG_BUFS == 2 ? 5 : 6) : (STG_BUFS == 2 ? 6 : 8)) : ((BN == 256) ? 4 : 6);
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_WARPS * STG_BYTES * STG_BUFS + 1024 /*align slack*/ + 256 /*barriers*/;
 };
 
 struct TcProblem {
@@ -136,12 +144,13 @@ enum : int { EPI_GENERIC = -1, EPI_PLAIN = 0, EPI_BIAS = 1, EPI_RES = 2, EPI_GEL
 template <int BN, bool A_MN, bool B_MN, bool PAIR, int EF>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcArgs args) {
-  using C_ = Cfg<BN, PAIR>;
+  using C_ = Cfg<BN, PAIR, EF>;
   constexpr int STAGES = C_::STAGES;
+  constexpr int NBUF = C_::STG_BUFS;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
   uint8_t* stg_base = smem + STAGES * C_::STAGE_BYTES;
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(stg_base + EPI_WARPS * STG_BYTES);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(stg_base + EPI_WARPS * STG_BYTES * NBUF);
   uint64_t* empty_bar = full_bar + STAGES;
   uint64_t* tfull_bar = empty_bar + STAGES;
   uint64_t* tempty_bar = tfull_bar + 2;
@@ -297,7 +306,7 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
     const int ew = warp & 3;                       // TMEM lanes [32 * ew, 32 * ew + 32) (a warp may only touch its quarter)
     const int quarter = (warp - EPI_WARP0) >> 2;   // columns [quarter * BN / 4, (quarter + 1) * BN / 4)
     constexpr int CH_PER_Q = BN / 128;             // 32-column chunks per warp
-    uint8_t* stg = stg_base + (warp - EPI_WARP0) * STG_BYTES;
+    uint8_t* stg = stg_base + (warp - EPI_WARP0) * STG_BYTES * NBUF;
     const uint32_t stg_u32 = tc::smem_u32(stg);
     // staging buffer: 32 rows x 64 B, 64-byte swizzle (16-byte chunk j of row r sits at chunk j ^ ((r >> 1) & 3)),
     // as the TMA store map expects.  "own" = row `lane`; "co" = coalesced view, instruction i covers rows 8i..8i+7.
@@ -306,6 +315,7 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
     const uint32_t co_row = static_cast<uint32_t>(lane >> 2), co_j = static_cast<uint32_t>(lane & 3);
     int acc = 0;
     uint32_t acc_phase = 0;
+    uint32_t sboff = 0;       // byte offset of the staging buffer the next store is staged in (NBUF == 2: alternates)
     // hand the accumulator back to the MMA issuer (PAIR: the leader CTA's barrier counts both CTAs' epilogue threads)
     const uint32_t te0 = PAIR ? tc::mapa_u32(&tempty_bar[0], 0) : 0u, te1 = PAIR ? tc::mapa_u32(&tempty_bar[1], 0) : 0u;
     auto release_acc = [&](int a) {   // after tcgen05.wait::ld + fence::before_thread_sync of every lane
@@ -391,19 +401,19 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
 #endif
           // (3) transpose the input chunk to "thread = row" through the staging buffer
           if (need_in) {
-            if (TMA_ST && lane == 0) tc::tma_store_wait_read();
+            if (TMA_ST && lane == 0) tc::tma_store_wait_read_n<NBUF - 1>();
             __syncwarp();
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
               const uint32_t rr = i * 8 + co_row;
-              const uint32_t a = stg_u32 + rr * 64 + ((co_j ^ ((rr >> 1) & 3)) << 4);
+              const uint32_t a = stg_u32 + sboff + rr * 64 + ((co_j ^ ((rr >> 1) & 3)) << 4);
               asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(pre[i].x), "r"(pre[i].y),
                            "r"(pre[i].z), "r"(pre[i].w) : "memory");
             }
             __syncwarp();
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
-              const uint32_t a = own_base + ((j ^ own_x) << 4);
+              const uint32_t a = own_base + sboff + ((j ^ own_x) << 4);
               asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(pre[j].x), "=r"(pre[j].y), "=r"(pre[j].z),
                            "=r"(pre[j].w) : "r"(a) : "memory");
             }
@@ -432,7 +442,7 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
           // erf / exp terms are shared between the activation and its derivative)
           uint32_t o[16];
           if (f_gelu) {
-            if (TMA_ST && lane == 0) tc::tma_store_wait_read();
+            if (TMA_ST && lane == 0) tc::tma_store_wait_read_n<NBUF - 1>();
             __syncwarp();
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
@@ -444,16 +454,17 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
                 w[q] = pack_bf16x2(d.x, d.y);
                 o[4 * j + q] = pack_bf16x2(g.x, g.y);   // packed at once: 16 live registers instead of 32
               }
-              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(own_base + ((j ^ own_x) << 4)), "r"(w[0]),
+              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(own_base + sboff + ((j ^ own_x) << 4)), "r"(w[0]),
                            "r"(w[1]), "r"(w[2]), "r"(w[3]) : "memory");
             }
             if constexpr (TMA_ST) {
               tc::fence_proxy_async();
               __syncwarp();
               if (lane == 0 && MB_DIAG_EPI != 2) {
-                tc::tma_store_2d(&maps.x[tc_.p], stg, col0, row0);
+                tc::tma_store_2d(&maps.x[tc_.p], stg + sboff, col0, row0);
                 tc::tma_store_commit();
               }
+              if constexpr (NBUF == 2) sboff ^= STG_BYTES;
             } else {
               flush_chunk(static_cast<bf16*>(P.aux), P, row0, col0);
             }
@@ -485,7 +496,7 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
             continue;
           }
 #endif
-          if (TMA_ST && lane == 0) tc::tma_store_wait_read();
+          if (TMA_ST && lane == 0) tc::tma_store_wait_read_n<NBUF - 1>();
           __syncwarp();
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
@@ -496,14 +507,14 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
               w0 = pack_bf16x2(v2[4 * j].x, v2[4 * j].y); w1 = pack_bf16x2(v2[4 * j + 1].x, v2[4 * j + 1].y);
               w2 = pack_bf16x2(v2[4 * j + 2].x, v2[4 * j + 2].y); w3 = pack_bf16x2(v2[4 * j + 3].x, v2[4 * j + 3].y);
             }
-            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(own_base + ((j ^ own_x) << 4)), "r"(w0),
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(own_base + sboff + ((j ^ own_x) << 4)), "r"(w0),
                          "r"(w1), "r"(w2), "r"(w3) : "memory");
           }
           if constexpr (TMA_ST) {
             tc::fence_proxy_async();
             __syncwarp();
             if (lane == 0 && MB_DIAG_EPI != 2) {
-              tc::tma_store_2d(&maps.c[tc_.p], stg, col0, row0);
+              tc::tma_store_2d(&maps.c[tc_.p], stg + sboff, col0, row0);
               tc::tma_store_commit();
             }
           } else {
@@ -513,7 +524,7 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
           // l walks column l of the staged 32 x 32 chunk (one conflict-free 64-byte row segment per step)
           if (has_colsum) {
             const int nrows = min(32, P.M - row0);
-            const uint32_t cbase = stg_u32 + (lane & 7) * 2;
+            const uint32_t cbase = stg_u32 + sboff + (lane & 7) * 2;
             const uint32_t cj = static_cast<uint32_t>(lane >> 3);
             float cs0 = 0.f, cs1 = 0.f;
 #pragma unroll 8
@@ -527,6 +538,7 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
             }
             if (nrows > 0 && col0 + lane < P.N) atomicAdd(P.colsum + col0 + lane, cs0 + cs1);
           }
+          if constexpr (TMA_ST && NBUF == 2) sboff ^= STG_BYTES;   // the next chunk (or GELU output) stages into the other buffer
         }
       } else if (nch > 0) {
         // ---------------- fp32 outputs (gradient accumulation): direct 16-byte stores / red.add ----------------
@@ -605,7 +617,7 @@ int num_sms() { return mb_num_sms(); }
 // PAIR: 2-CTA clusters running cta_group::2 MMAs (see the kernel); tiles are scheduled as vertical pairs of m-blocks.
 template <int BN, bool A_MN, bool B_MN, bool MC, int EF = EPI_GENERIC>
 int launch(const GemmParams* Ps, int count, cudaStream_t st) {
-  using C_ = Cfg<BN, MC>;
+  using C_ = Cfg<BN, MC, EF>;
   TcMaps maps;
   TcArgs a;
   std::memset(&a, 0, sizeof(a));
