@@ -29,7 +29,7 @@ from maestro_b200.conf import DATASET_SPECS, MODEL_SIZES, MaskSpec  # noqa: E402
 def gemm_traffic():
     """DRAM bytes per launch of the dominant kernel: ncu's dram__bytes_read.sum + dram__bytes_write.sum over every
     gemm_tc launch of one step, digested by tools/gemm_traffic.py into profiles/ (ncu cannot run inside the timed bench)."""
-    for name in ("r2_gemm_dram.json",):
+    for name in ("r2b_gemm_dram.json", "r2_gemm_dram.json"):
         try:
             with open(os.path.join(ROOT, "profiles", name)) as f:
                 d = json.load(f)
