@@ -672,7 +672,8 @@ int launch(const GemmParams* Ps, int count, cudaStream_t st) {
     const int slots = MC ? num_sms() / 2 : num_sms();
     int kbs[MAX_GROUP], max_kb = 1;
     for (int i = 0; i < count; ++i) { kbs[i] = (a.p[i].K + BK - 1) / BK; max_kb = std::max(max_kb, kbs[i]); }
-    constexpr int EPI_KB = 6;           // a 128 x 256 fp32 red epilogue costs about as much as 6 k-blocks
+    // a 128 x 256 fp32 red epilogue costs about as much as EPI_KB k-blocks (MB_GEMM_SPLIT_EPI: sweeps, tools/gemm_bench.py)
+    static const int EPI_KB = [] { const char* e = std::getenv("MB_GEMM_SPLIT_EPI"); return e ? std::atoi(e) : 6; }();
     long long best = -1;
     int prev_sp[MAX_GROUP] = {0, 0, 0, 0};
     int load[256];

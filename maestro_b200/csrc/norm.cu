@@ -46,7 +46,8 @@ struct LnFwdArgs {
   float eps;
 };
 
-template <typename T, int NCH, bool MAPPED>
+// EXACT: see layernorm_bwd_kernel (d == NCH * 32 * V known at compile time, no lane out of range)
+template <typename T, int NCH, bool MAPPED, bool EXACT = false>
 __global__ void __launch_bounds__(LNF_THREADS, (NCH <= 2 ? 4 : (NCH <= 3 ? 3 : 2)))
 layernorm_fwd_kernel(const __grid_constant__ LnFwdArgs args) {
   pdl_launch();
@@ -62,11 +63,11 @@ layernorm_fwd_kernel(const __grid_constant__ LnFwdArgs args) {
   T* __restrict__ y = static_cast<T*>(P.y);
   float* __restrict__ mean_out = P.mean;
   float* __restrict__ rstd_out = P.rstd;
-  const int rows = P.rows, d = args.d;
+  constexpr int V = VecIO<T>::N;
+  const int rows = P.rows, d = EXACT ? NCH * 32 * V : args.d;
   const float eps = args.eps;
   const RowMap in_map = P.in_map, out_map = P.out_map;
   const int cta = static_cast<int>(blockIdx.x) - cta0, ncta = P.cta_end - cta0;
-  constexpr int V = VecIO<T>::N;
   constexpr int NP = Vec2IO<T>::NP;          // float2 pairs per 16-byte chunk
   typedef typename VecIO<T>::Raw Raw;
   extern __shared__ __align__(16) float gb[];   // gamma [d] | beta [d]
@@ -87,7 +88,7 @@ layernorm_fwd_kernel(const __grid_constant__ LnFwdArgs args) {
 #pragma unroll
     for (int c = 0; c < NCH; ++c) {
       const int idx = lane + c * 32;
-      dst[c] = idx < nvec ? VecIO<T>::load_raw(xr + idx * V) : VecIO<T>::zero_raw();
+      dst[c] = (EXACT || idx < nvec) ? VecIO<T>::load_raw(xr + idx * V) : VecIO<T>::zero_raw();
     }
   };
   int r = gwarp;
@@ -111,7 +112,7 @@ layernorm_fwd_kernel(const __grid_constant__ LnFwdArgs args) {
     float2 q2 = make_float2(0.f, 0.f);
 #pragma unroll
     for (int c = 0; c < NCH; ++c) {
-      if (lane + c * 32 < nvec) {
+      if (EXACT || lane + c * 32 < nvec) {
 #pragma unroll
         for (int j = 0; j < NP; ++j) {
           v[c * NP + j] = add2(v[c * NP + j], nm);                       // centred
@@ -129,7 +130,7 @@ layernorm_fwd_kernel(const __grid_constant__ LnFwdArgs args) {
 #pragma unroll
     for (int c = 0; c < NCH; ++c) {
       const int idx = lane + c * 32;
-      if (idx < nvec) {
+      if (EXACT || idx < nvec) {
         float2 o[NP];
 #pragma unroll
         for (int j = 0; j < NP; j += 2) {
@@ -179,9 +180,14 @@ static void launch_ln_fwd(const mb_ln_fwd_problem* ps, int count, int d, float e
   for (int i = 0; i < count; ++i)
     mapped = mapped || !(ps[i].in_n == ps[i].rows && ps[i].in_off == 0 && ps[i].out_n == ps[i].rows && ps[i].out_off == 0);
   auto kern = mapped ? layernorm_fwd_kernel<T, NCH, true> : layernorm_fwd_kernel<T, NCH, false>;
+  if constexpr (sizeof(T) == 2 && NCH >= 2 && NCH <= 4) {
+    if (d == NCH * 32 * VecIO<T>::N)
+      kern = mapped ? layernorm_fwd_kernel<T, NCH, true, true> : layernorm_fwd_kernel<T, NCH, false, true>;
+  }
   const size_t smem = 2 * static_cast<size_t>(d) * sizeof(float);
   // persistent grid of (at most) exactly the resident CTAs; at least 2 rows per warp (gamma / beta are staged per CTA)
-  static int per_sm[2] = {0, 0};
+  static int per_sm_tab[4] = {0, 0, 0, 0};
+  int* per_sm = per_sm_tab + (d == NCH * 32 * VecIO<T>::N ? 2 : 0);
   if (per_sm[mapped] == 0) {
     int n = 0;
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kern, LNF_THREADS, smem);
@@ -272,7 +278,10 @@ struct LnBwdArgs {
   int count, d, depth;
 };
 
-template <typename T, int NCH, bool MAPPED>
+// EXACT: d == NCH * 32 * V (the 512 / 768 / 1024-wide rows of the shipped models): d is a compile-time constant and
+// no lane is ever out of range -- the per-chunk predicates, their divergence bookkeeping (BSSY / BSYNC) and most of
+// the address arithmetic disappear from the row loop.
+template <typename T, int NCH, bool MAPPED, bool EXACT = false>
 __global__ void __launch_bounds__(LNB_THREADS, 1)
 layernorm_bwd_kernel(const __grid_constant__ LnBwdArgs args) {
   pdl_launch();
@@ -292,10 +301,10 @@ layernorm_bwd_kernel(const __grid_constant__ LnBwdArgs args) {
   float* __restrict__ dgamma = P.dgamma;
   float* __restrict__ dbeta = P.dbeta;
   float* __restrict__ dbias = P.dbias;
-  const int rows = P.rows, d = args.d, depth = args.depth;
+  constexpr int V = VecIO<T>::N;
+  const int rows = P.rows, d = EXACT ? NCH * 32 * V : args.d, depth = args.depth;
   const RowMap in_map = P.in_map, out_map = P.out_map;
   const int cta = static_cast<int>(blockIdx.x) - cta0, ncta = P.cta_end - cta0;
-  constexpr int V = VecIO<T>::N;
   constexpr int NP = Vec2IO<T>::NP;
   constexpr int NE2 = NCH * NP;
   typedef typename VecIO<T>::Raw Raw;
@@ -358,7 +367,7 @@ layernorm_bwd_kernel(const __grid_constant__ LnBwdArgs args) {
 #pragma unroll
       for (int c = 0; c < NCH; ++c) {
         const int idx = lane + c * 32;
-        const bool ok = idx < nvec;
+        const bool ok = EXACT || idx < nvec;
         const Raw rx = ok ? VecIO<T>::load_raw(sx + idx * V) : VecIO<T>::zero_raw();
         const Raw rdy = ok ? VecIO<T>::load_raw(sdy + idx * V) : VecIO<T>::zero_raw();
         cres[c] = (ok && has_res) ? VecIO<T>::load_raw(sres + idx * V) : VecIO<T>::zero_raw();
@@ -378,7 +387,7 @@ layernorm_bwd_kernel(const __grid_constant__ LnBwdArgs args) {
 #pragma unroll
     for (int c = 0; c < NCH; ++c) {
       const int idx = lane + c * 32;
-      if (idx < nvec) {
+      if (EXACT || idx < nvec) {
 #pragma unroll
         for (int j = 0; j < NP; j += 2) {
           const float4 g4 = *reinterpret_cast<const float4*>(gam + idx * V + 2 * j);
@@ -404,7 +413,7 @@ layernorm_bwd_kernel(const __grid_constant__ LnBwdArgs args) {
 #pragma unroll
     for (int c = 0; c < NCH; ++c) {
       const int idx = lane + c * 32;
-      if (idx < nvec) {
+      if (EXACT || idx < nvec) {
         float2 o[NP];
         Vec2IO<T>::unpack(cres[c], o);
 #pragma unroll
@@ -420,7 +429,7 @@ layernorm_bwd_kernel(const __grid_constant__ LnBwdArgs args) {
 #pragma unroll
   for (int c = 0; c < NCH; ++c) {
     const int idx = lane + c * 32;
-    if (idx < nvec) {
+    if (EXACT || idx < nvec) {
 #pragma unroll
       for (int j = 0; j < V; ++j) {
         // column (idx * V + j) lives at [j * nvec + idx]: consecutive lanes -> consecutive banks (conflict-free red)
@@ -495,6 +504,17 @@ static int launch_ln_bwd(const mb_ln_bwd_problem* ps, int count, int d, cudaStre
         attr_done = true;                                                                                       \
       }                                                                                                         \
       auto kern = mapped ? layernorm_bwd_kernel<T, N_, true> : layernorm_bwd_kernel<T, N_, false>;              \
+      if constexpr (sizeof(T) == 2 && N_ >= 2 && N_ <= 4) {                                                     \
+        if (d == N_ * 32 * V) {                                                                                 \
+          static bool attr_x = false;                                                                           \
+          if (!attr_x) {                                                                                        \
+            cudaFuncSetAttribute(layernorm_bwd_kernel<T, N_, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024); \
+            cudaFuncSetAttribute(layernorm_bwd_kernel<T, N_, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024); \
+            attr_x = true;                                                                                      \
+          }                                                                                                     \
+          kern = mapped ? layernorm_bwd_kernel<T, N_, true, true> : layernorm_bwd_kernel<T, N_, false, true>;   \
+        }                                                                                                       \
+      }                                                                                                         \
       mb_launch(kern, dim3(blocks), dim3(LNB_THREADS), smem, st, a);                                                            \
     }                                                                                                           \
     break;
