@@ -73,6 +73,19 @@ template <int BN, bool PAIR, int EF = -1> struct Cfg {
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_WARPS * STG_BYTES * STG_BUFS + 1024 /*align slack*/ + 256 /*barriers*/;
 };
 
+// MB_DIAG_TIMING (diagnostic builds only): CTA 0 stamps clock64() per tile: [tile][0] MMA warp got the accumulator,
+// [1] MMA warp issued the tile's last commit, [2] epilogue warp 4 starts waiting for the accumulator, [3] has it,
+// [4] has issued its last store of the tile.  Read back with mb_diag_gemm_timing().
+#ifndef MB_DIAG_TIMING
+#define MB_DIAG_TIMING 0
+#endif
+#if MB_DIAG_TIMING
+__device__ unsigned long long g_gemm_stamps[64 * 8];
+#define MB_STAMP(tile_i, slot) do { if (blockIdx.x == 0 && (tile_i) < 64) g_gemm_stamps[(tile_i) * 8 + (slot)] = clock64(); } while (0)
+#else
+#define MB_STAMP(tile_i, slot) do { } while (0)
+#endif
+
 struct TcProblem {
   void* C;
   const float* bias;
@@ -268,10 +281,12 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      for (int t = tile0; t < total_tiles; t += tile_step) {
+      int tile_i = 0;
+      for (int t = tile0; t < total_tiles; t += tile_step, ++tile_i) {
         const TileCoord tc_ = decode_tile(args, t, !A_MN, mc_rank);
         tc::mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
         tc::tc_fence_after();
+        MB_STAMP(tile_i, 0);
         const uint32_t d_tmem = tmem_base + acc * BN;
         for (int kb = tc_.kb0; kb < tc_.kb1; ++kb) {
           tc::mbar_wait(&full_bar[stage], phase);
@@ -296,6 +311,7 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
         }
         if constexpr (PAIR) tc::umma_commit_pair(&tfull_bar[acc], 0x3);       // both CTAs' epilogues read their half
         else tc::umma_commit(&tfull_bar[acc]);
+        MB_STAMP(tile_i, 1);
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       }
     }
@@ -347,7 +363,10 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
     const bool f_gelu = SPEC ? (EF & EPI_GELU) != 0 : (args.flags & GEMM_GELU) != 0;
     const bool f_dgelu = SPEC ? (EF & EPI_DGELU) != 0 : (args.flags & GEMM_DGELU) != 0;
     const float alpha = SPEC ? 1.0f : args.alpha;
+    int tile_i = -1;
     for (int t = tile0; t < total_tiles; t += tile_step) {
+      ++tile_i;
+      if (warp == EPI_WARP0 && lane == 0) MB_STAMP(tile_i, 2);
       const TileCoord tc_ = decode_tile(args, t, !A_MN, mc_rank);
       const TcProblem& P = args.p[tc_.p];
       const int row0 = tc_.m_blk * BM + ew * 32;
@@ -388,6 +407,7 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
           if (c2 == 0) {
             tc::mbar_wait(&tfull_bar[acc], acc_phase);
             tc::tc_fence_after();
+            if (warp == EPI_WARP0 && lane == 0) MB_STAMP(tile_i, 3);
           }
           uint32_t r[32];
           tc::tmem_ld_32x32(t_addr + ch * 32, r);
@@ -589,6 +609,7 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
           }
         }
       }
+      if (warp == EPI_WARP0 && lane == 0) MB_STAMP(tile_i, 4);
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
     if (lane == 0) tc::tma_store_wait_all();   // shared memory must stay valid until the last store has read it
@@ -883,5 +904,11 @@ extern "C" int mb_gemm_tc_grouped(const GemmParams* params, int count, void* str
   if (a_mn && b_mn) return wide ? launch_any<256, true, true>(live, n, st) : launch_any<128, true, true>(live, n, st);
   return -5;
 }
+
+#if MB_DIAG_TIMING
+extern "C" int mb_diag_gemm_timing(unsigned long long* host, int n) {
+  return static_cast<int>(cudaMemcpyFromSymbol(host, g_gemm_stamps, sizeof(unsigned long long) * (n < 512 ? n : 512)));
+}
+#endif
 
 extern "C" int mb_gemm_tc(const GemmParams* params, void* stream) { return mb_gemm_tc_grouped(params, 1, stream); }
