@@ -8,7 +8,7 @@ namespace {
 // pipe works on S^T / dP^T of half j + 1 (issued one pass earlier) and on the gradient MMAs of half j - 1, so neither
 // the MMA latency nor the single-thread issue sequence sits between two passes.  Warps 0-3 (thread = key row = TMEM
 // lane) run the passes; one lane of warp 4 issues every TMA load and MMA, driven by mbarriers only.
-constexpr int DKDV_THREADS = 160;
+constexpr int DKDV_THREADS = 128 * NH + 32;   // NH warps per TMEM lane quarter split the columns of every pass (attn_bwd_tc.cu)
 
 template <int DH>
 __global__ void __launch_bounds__(DKDV_THREADS) attn_bwd_dkdv_kernel(const __grid_constant__ BwdGroup grp) {
@@ -50,7 +50,7 @@ __global__ void __launch_bounds__(DKDV_THREADS) attn_bwd_dkdv_kernel(const __gri
     for (int i = 0; i < 2; ++i) {
       tc::mbar_init(&bar_s[i], 1);
       tc::mbar_init(&bar_o[i], 1);
-      tc::mbar_init(&bar_p[i], BR);
+      tc::mbar_init(&bar_p[i], BR * NH);
     }
     tc::fence_barrier_init();
   }
@@ -66,7 +66,8 @@ __global__ void __launch_bounds__(DKDV_THREADS) attn_bwd_dkdv_kernel(const __gri
   pdl_wait();
   // columns: S^T [2][SUB] | dP^T [2][SUB] | dK [DH] | dV [DH]
   const uint32_t tm_st = tmem_base, tm_dpt = tmem_base + 2 * SUB, tm_dk = tmem_base + 4 * SUB, tm_dv = tm_dk + DH;
-  const uint32_t lane_base = static_cast<uint32_t>(warp * 32) << 16;
+  const uint32_t lane_base = static_cast<uint32_t>((warp & 3) * 32) << 16;
+  const int krow = tid & 127, half = tid >> 7;       // key row of the tile / column half owned by this thread
   constexpr uint32_t idesc_s = tc::make_idesc_bf16(BR, SUB, 0, 0);   // [128 keys] x [SUB queries], K = DH
   constexpr uint32_t idesc_g = tc::make_idesc_bf16(BR, DH, 0, 1);    // [128 keys] x [DH], K = SUB queries (B MN-major)
   const uint32_t sK = tc::smem_u32(smem + OFF_K), sV = tc::smem_u32(smem + OFF_V);
@@ -106,9 +107,9 @@ __global__ void __launch_bounds__(DKDV_THREADS) attn_bwd_dkdv_kernel(const __gri
     tc::umma_commit(&bar_o[j & 1]);
   };
 
-  if (warp == 4) {
+  if (warp == BWD_CTRL_WARP) {
     // ===================== control lane: TMA loads + every MMA =====================
-    if (tid == 128) {
+    if (tid == 128 * NH) {
       int s_stage = 0, l_stage = 0, g_stage = 0, l_next = 0;
       uint32_t s_par = 0;
       tc::mbar_expect_tx(bar_kv, 2 * C_::ROW_TILE);
@@ -146,7 +147,7 @@ __global__ void __launch_bounds__(DKDV_THREADS) attn_bwd_dkdv_kernel(const __gri
     }
   } else {
   // ===================== compute warps =====================
-  const int row = rt * BR + tid;           // key row owned by this thread
+  const int row = rt * BR + krow;          // key row owned by this thread (shared by the NH threads of the row)
   const bool row_ok = row < N;
   const float c = args.scale_log2, sc = args.scale;
   const size_t stat_base = (static_cast<size_t>(b) * H + h) * N;
@@ -169,18 +170,19 @@ __global__ void __launch_bounds__(DKDV_THREADS) attn_bwd_dkdv_kernel(const __gri
   };
   fetch_stats(0);
   put_stats(0);
-  asm volatile("bar.sync 1, 128;" ::: "memory");
+  asm volatile("bar.sync 1, %0;" ::"n"(128 * NH) : "memory");
+  constexpr int CW = SUB / NH;               // columns of a pass handled by this thread
   for (int j = 0; j < n_sub; ++j) {
     const int bufi = j & 1;
     const uint32_t st = tc::smem_u32(s_stat + bufi * 2 * SUB);
-    const uint32_t pt_row = sPT + bufi * C_::AS_TILE + tid * C_::AS_ROW;
-    const uint32_t dst_row = sDST + bufi * C_::AS_TILE + tid * C_::AS_ROW;
+    const uint32_t pt_row = sPT + bufi * C_::AS_TILE + krow * C_::AS_ROW;
+    const uint32_t dst_row = sDST + bufi * C_::AS_TILE + krow * C_::AS_ROW;
     if (j + 1 < n_sub) fetch_stats(j + 1);
-    float4 lsv[SUB / 4], dsv[SUB / 4];                        // this half's statistics: in registers before S^T lands
+    float4 lsv[CW / 4], dsv[CW / 4];                          // this thread's statistics: in registers before S^T lands
 #pragma unroll
-    for (int q4 = 0; q4 < SUB / 4; ++q4) {
-      lsv[q4] = lds_f4(st + q4 * 16);
-      dsv[q4] = lds_f4(st + (SUB + q4 * 4) * 4);
+    for (int q4 = 0; q4 < CW / 4; ++q4) {
+      lsv[q4] = lds_f4(st + (half * CW + q4 * 4) * 4);
+      dsv[q4] = lds_f4(st + (SUB + half * CW + q4 * 4) * 4);
     }
     tc::mbar_wait(&bar_s[bufi], (j >> 1) & 1);
     if (j >= 2) tc::mbar_wait(&bar_o[bufi], ((j - 2) >> 1) & 1);   // gradient MMAs of half j - 2 have read `bufi`
@@ -188,17 +190,12 @@ __global__ void __launch_bounds__(DKDV_THREADS) attn_bwd_dkdv_kernel(const __gri
     // P^T and dS^T.  No masks: queries past N are zero rows of Q and dO (TMA zero fill), so their columns multiply
     // zero rows in dV += P^T dO and dK += dS^T Q; key rows past N are never stored.  st[] holds finite values there.
     {
-      uint32_t s[SUB], dp[SUB];
-      if constexpr (SUB == 32) {
-        tc::tmem_ld_32x32(tm_st + lane_base + bufi * SUB, s);
-        tc::tmem_ld_32x32(tm_dpt + lane_base + bufi * SUB, dp);
-      } else {
-        tc::tmem_ld_32x16(tm_st + lane_base + bufi * SUB, s);
-        tc::tmem_ld_32x16(tm_dpt + lane_base + bufi * SUB, dp);
-      }
+      uint32_t s[CW], dp[CW];
+      tc::tmem_ld_32xN<CW>(tm_st + lane_base + bufi * SUB + half * CW, s);
+      tc::tmem_ld_32xN<CW>(tm_dpt + lane_base + bufi * SUB + half * CW, dp);
       tc::tmem_ld_wait();
 #pragma unroll
-      for (int v8 = 0; v8 < SUB / 8; ++v8) {
+      for (int v8 = 0; v8 < CW / 8; ++v8) {
         uint32_t wp[4], wd[4];
         const float4 l0 = lsv[2 * v8], l1 = lsv[2 * v8 + 1], e0 = dsv[2 * v8], e1 = dsv[2 * v8 + 1];
         const float ls[8] = {l0.x, l0.y, l0.z, l0.w, l1.x, l1.y, l1.z, l1.w};
@@ -218,33 +215,52 @@ __global__ void __launch_bounds__(DKDV_THREADS) attn_bwd_dkdv_kernel(const __gri
           wp[k2] = *reinterpret_cast<uint32_t*>(&hp);
           wd[k2] = *reinterpret_cast<uint32_t*>(&hd);
         }
-        store_a_chunk_s<SUB>(pt_row, tid, v8, wp);
-        store_a_chunk_s<SUB>(dst_row, tid, v8, wd);
+        store_a_chunk_s<SUB>(pt_row, krow, half * (CW / 8) + v8, wp);
+        store_a_chunk_s<SUB>(dst_row, krow, half * (CW / 8) + v8, wd);
       }
     }
     if (j + 1 < n_sub) put_stats(j + 1);
     tc::fence_proxy_async();
     tc::tc_fence_before();
     tc::mbar_arrive(&bar_p[bufi]);
-    asm volatile("bar.sync 1, 128;" ::: "memory");   // next half's statistics are visible to the four warps
+    asm volatile("bar.sync 1, %0;" ::"n"(128 * NH) : "memory");   // next half's statistics are visible to the compute warps
   }
   tc::mbar_wait(&bar_o[(n_sub - 1) & 1], ((n_sub - 1) >> 1) & 1);   // a commit covers every MMA issued before it
   tc::tc_fence_after();
   bf16* out = args.dqkv + (static_cast<size_t>(b) * N + (row_ok ? row : 0)) * 3 * inner + h * DH;
+  if constexpr (NH == 1) {
 #pragma unroll
-  for (int which = 0; which < 2; ++which) {   // 0: dK, 1: dV
+    for (int which = 0; which < 2; ++which) {   // 0: dK, 1: dV
 #pragma unroll
-    for (int ch = 0; ch < (DH + 31) / 32; ++ch) {
-      uint32_t r[32];
-      tc::tmem_ld_32x32((which == 0 ? tm_dk : tm_dv) + lane_base + ch * 32, r);
+      for (int ch = 0; ch < (DH + 31) / 32; ++ch) {
+        uint32_t r[32];
+        tc::tmem_ld_32x32((which == 0 ? tm_dk : tm_dv) + lane_base + ch * 32, r);
+        tc::tmem_ld_wait();
+#pragma unroll
+        for (int v8 = 0; v8 < 4; ++v8) {
+          if (ch * 32 + v8 * 8 < DH && row_ok) {
+            float v[8];
+#pragma unroll
+            for (int k2 = 0; k2 < 8; ++k2) v[k2] = __uint_as_float(r[v8 * 8 + k2]);
+            VecIO<bf16>::store(out + (which + 1) * inner + ch * 32 + v8 * 8, v);
+          }
+        }
+      }
+    }
+  } else {
+    constexpr int OW = DH / NH;                // output columns of dK and of dV written by this thread
+#pragma unroll
+    for (int which = 0; which < 2; ++which) {   // 0: dK, 1: dV
+      uint32_t r[OW];
+      tc::tmem_ld_32xN<OW>((which == 0 ? tm_dk : tm_dv) + lane_base + half * OW, r);
       tc::tmem_ld_wait();
 #pragma unroll
-      for (int v8 = 0; v8 < 4; ++v8) {
-        if (ch * 32 + v8 * 8 < DH && row_ok) {
+      for (int v8 = 0; v8 < OW / 8; ++v8) {
+        if (row_ok) {
           float v[8];
 #pragma unroll
           for (int k2 = 0; k2 < 8; ++k2) v[k2] = __uint_as_float(r[v8 * 8 + k2]);
-          VecIO<bf16>::store(out + (which + 1) * inner + ch * 32 + v8 * 8, v);
+          VecIO<bf16>::store(out + (which + 1) * inner + half * OW + v8 * 8, v);
         }
       }
     }

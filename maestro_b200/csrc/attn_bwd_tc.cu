@@ -83,7 +83,16 @@ __device__ __forceinline__ float4 lds_f4(uint32_t addr) {
 // Same software pipeline as the dK / dV kernel (attn_bwd_dkdv.cuh): SUB-key half tiles, S / dP accumulators and the dS
 // operand double-buffered, K / V halves in an NS-stage TMA ring, warps 0-3 = query rows, one lane of warp 4 issues
 // every TMA load and MMA.
-constexpr int DQ_THREADS = 160;
+// NH warps share each TMEM lane quarter (warps w, w + 4, ...) and split the columns of every pass between them.
+// NH = 1 (default): one warp per lane quarter.  NH = 2 (8 compute warps per CTA, 32 per SM) was measured SLOWER --
+// 5.55 vs 5.10 ms per step over the step's shapes (profiles/r2b_attn_probe_nh2.txt): the fixed cost of a pass
+// (barrier waits, fences, TMEM loads) is paid per thread, and halving the columns per thread doubles its share.
+#ifndef MB_ATTN_BWD_NH
+#define MB_ATTN_BWD_NH 1
+#endif
+constexpr int NH = MB_ATTN_BWD_NH;
+constexpr int BWD_CTRL_WARP = 4 * NH;          // its first lane issues every TMA load and MMA
+constexpr int DQ_THREADS = 128 * NH + 32;
 
 template <int DH>
 __global__ void __launch_bounds__(DQ_THREADS) attn_bwd_dq_kernel(const __grid_constant__ BwdGroup grp) {
@@ -122,7 +131,7 @@ __global__ void __launch_bounds__(DQ_THREADS) attn_bwd_dq_kernel(const __grid_co
     for (int i = 0; i < 2; ++i) {
       tc::mbar_init(&bar_s[i], 1);
       tc::mbar_init(&bar_o[i], 1);
-      tc::mbar_init(&bar_p[i], BR);
+      tc::mbar_init(&bar_p[i], BR * NH);
     }
     tc::fence_barrier_init();
   }
@@ -138,7 +147,8 @@ __global__ void __launch_bounds__(DQ_THREADS) attn_bwd_dq_kernel(const __grid_co
   pdl_wait();
   // columns: S [2][SUB] | dP [2][SUB] | dQ [DH]
   const uint32_t tm_s = tmem_base, tm_dp = tmem_base + 2 * SUB, tm_dq = tmem_base + 4 * SUB;
-  const uint32_t lane_base = static_cast<uint32_t>(warp * 32) << 16;
+  const uint32_t lane_base = static_cast<uint32_t>((warp & 3) * 32) << 16;
+  const int qrow = tid & 127, half = tid >> 7;      // row of the tile / column half owned by this thread
   constexpr uint32_t idesc_s = tc::make_idesc_bf16(BR, SUB, 0, 0);
   constexpr uint32_t idesc_dq = tc::make_idesc_bf16(BR, DH, 0, 1);
   const uint32_t sQ = tc::smem_u32(smem + OFF_Q), sDO = tc::smem_u32(smem + OFF_DO), sDS = tc::smem_u32(smem + OFF_DS);
@@ -172,9 +182,9 @@ __global__ void __launch_bounds__(DQ_THREADS) attn_bwd_dq_kernel(const __grid_co
     tc::umma_commit(&bar_o[j & 1]);
   };
 
-  if (warp == 4) {
+  if (warp == BWD_CTRL_WARP) {
     // ===================== control lane: TMA loads + every MMA =====================
-    if (tid == 128) {
+    if (tid == 128 * NH) {
       int s_stage = 0, l_stage = 0, g_stage = 0, l_next = 0;
       uint32_t s_par = 0;
       tc::mbar_expect_tx(bar_q, 2 * C_::ROW_TILE);
@@ -212,8 +222,8 @@ __global__ void __launch_bounds__(DQ_THREADS) attn_bwd_dq_kernel(const __grid_co
     }
   } else {
     // ===================== compute warps: thread = query row =====================
-    // per-row constants: lse (log2 domain) and delta = sum_d dO * O
-    const int row = rt * BR + tid;
+    // per-row constants: lse (log2 domain) and delta = sum_d dO * O (both threads of a row compute them)
+    const int row = rt * BR + qrow;
     const bool row_ok = row < N;
     float lse2 = 0.f, delta = 0.f;
     if (row_ok) {
@@ -228,30 +238,26 @@ __global__ void __launch_bounds__(DQ_THREADS) attn_bwd_dq_kernel(const __grid_co
       }
       const size_t li = (static_cast<size_t>(b) * H + h) * N + row;
       lse2 = args.lse[li] * 1.4426950408889634f;
-      args.delta[li] = delta;
+      if (half == 0) args.delta[li] = delta;
     }
     const float c = args.scale_log2, sc = args.scale;
     const float delta_sc = delta * sc;
+    constexpr int CW = SUB / NH;               // columns of a pass handled by this thread
 
     for (int j = 0; j < n_sub; ++j) {
       const int bufi = j & 1;
-      const uint32_t ds_row = sDS + bufi * C_::AS_TILE + tid * C_::AS_ROW;
+      const uint32_t ds_row = sDS + bufi * C_::AS_TILE + qrow * C_::AS_ROW;
       tc::mbar_wait(&bar_s[bufi], (j >> 1) & 1);
       if (j >= 2) tc::mbar_wait(&bar_o[bufi], ((j - 2) >> 1) & 1);   // the dQ MMA of half j - 2 has read `bufi`
       tc::tc_fence_after();
       // dS = P * (dP - delta) * scale.  No masks: keys past N are zero rows of K and V, so whatever lands in their
       // dS columns multiplies zero rows of K in dQ += dS K; query rows past N are never stored.
-      uint32_t s[SUB], dp[SUB];
-      if constexpr (SUB == 32) {
-        tc::tmem_ld_32x32(tm_s + lane_base + bufi * SUB, s);
-        tc::tmem_ld_32x32(tm_dp + lane_base + bufi * SUB, dp);
-      } else {
-        tc::tmem_ld_32x16(tm_s + lane_base + bufi * SUB, s);
-        tc::tmem_ld_32x16(tm_dp + lane_base + bufi * SUB, dp);
-      }
+      uint32_t s[CW], dp[CW];
+      tc::tmem_ld_32xN<CW>(tm_s + lane_base + bufi * SUB + half * CW, s);
+      tc::tmem_ld_32xN<CW>(tm_dp + lane_base + bufi * SUB + half * CW, dp);
       tc::tmem_ld_wait();
 #pragma unroll
-      for (int v8 = 0; v8 < SUB / 8; ++v8) {
+      for (int v8 = 0; v8 < CW / 8; ++v8) {
         uint32_t w[4];
 #pragma unroll
         for (int i = 0; i < 4; ++i) {   // packed fp32 (FFMA2 / FMUL2): 1.5 instead of 3 issue slots of FP32 per element
@@ -262,7 +268,7 @@ __global__ void __launch_bounds__(DQ_THREADS) attn_bwd_dq_kernel(const __grid_co
           __nv_bfloat162 hb = __floats2bfloat162_rn(d2.x, d2.y);
           w[i] = *reinterpret_cast<uint32_t*>(&hb);
         }
-        store_a_chunk_s<SUB>(ds_row, tid, v8, w);
+        store_a_chunk_s<SUB>(ds_row, qrow, half * (CW / 8) + v8, w);
       }
       tc::fence_proxy_async();
       tc::tc_fence_before();
@@ -271,18 +277,34 @@ __global__ void __launch_bounds__(DQ_THREADS) attn_bwd_dq_kernel(const __grid_co
     tc::mbar_wait(&bar_o[(n_sub - 1) & 1], ((n_sub - 1) >> 1) & 1);   // a commit covers every MMA issued before it
     tc::tc_fence_after();
     bf16* out = args.dqkv + (static_cast<size_t>(b) * N + (row_ok ? row : 0)) * 3 * inner + h * DH;
+    if constexpr (NH == 1) {
 #pragma unroll
-    for (int ch = 0; ch < (DH + 31) / 32; ++ch) {
-      uint32_t r[32];
-      tc::tmem_ld_32x32(tm_dq + lane_base + ch * 32, r);   // warp-collective: executed by every thread
+      for (int ch = 0; ch < (DH + 31) / 32; ++ch) {
+        uint32_t r[32];
+        tc::tmem_ld_32x32(tm_dq + lane_base + ch * 32, r);   // warp-collective: executed by every thread
+        tc::tmem_ld_wait();
+#pragma unroll
+        for (int v8 = 0; v8 < 4; ++v8) {
+          if (ch * 32 + v8 * 8 < DH && row_ok) {
+            float v[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) v[i] = __uint_as_float(r[v8 * 8 + i]);
+            VecIO<bf16>::store(out + ch * 32 + v8 * 8, v);
+          }
+        }
+      }
+    } else {
+      constexpr int OW = DH / NH;              // output columns written by this thread
+      uint32_t r[OW];
+      tc::tmem_ld_32xN<OW>(tm_dq + lane_base + half * OW, r);   // warp-collective: executed by every thread
       tc::tmem_ld_wait();
 #pragma unroll
-      for (int v8 = 0; v8 < 4; ++v8) {
-        if (ch * 32 + v8 * 8 < DH && row_ok) {
+      for (int v8 = 0; v8 < OW / 8; ++v8) {
+        if (row_ok) {
           float v[8];
 #pragma unroll
           for (int i = 0; i < 8; ++i) v[i] = __uint_as_float(r[v8 * 8 + i]);
-          VecIO<bf16>::store(out + ch * 32 + v8 * 8, v);
+          VecIO<bf16>::store(out + half * OW + v8 * 8, v);
         }
       }
     }

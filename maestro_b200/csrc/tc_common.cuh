@@ -159,6 +159,20 @@ __device__ __forceinline__ void tmem_ld_32x16(uint32_t taddr, uint32_t* r) {
       : "r"(taddr)
       : "memory");
 }
+// 32 lanes x 8 columns of fp32
+__device__ __forceinline__ void tmem_ld_32x8(uint32_t taddr, uint32_t* r) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+               : "r"(taddr)
+               : "memory");
+}
+// NC (8 / 16 / 32) columns
+template <int NC> __device__ __forceinline__ void tmem_ld_32xN(uint32_t taddr, uint32_t* r) {
+  static_assert(NC == 8 || NC == 16 || NC == 32, "tmem_ld_32xN: 8, 16 or 32 columns");
+  if constexpr (NC == 8) tmem_ld_32x8(taddr, r);
+  else if constexpr (NC == 16) tmem_ld_32x16(taddr, r);
+  else tmem_ld_32x32(taddr, r);
+}
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 // ---------------------------------------------------------------- descriptors
