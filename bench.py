@@ -587,7 +587,7 @@ def run_ours(args):
                       "by_kind": attention, "ms_per_step": round(attn_ms, 3),
                       "tflops": round(attn_fl / (attn_ms * 1e-3) / 1e12, 1) if attn_ms > 0 else None,
                       "frac_of_sustained_peak": round(attn_fl / (attn_ms * 1e-3) / 1e12 / tf_sus, 3) if attn_ms > 0 else None,
-                      "note": "dh = 32 (decoder) is bound by exp2 / MUFU throughput, not the tensor pipe (DESIGN.md section 4)"},
+                      "note": "no pipe is saturated (ncu: issue-active ~50 %, XU 32-53 %, tensor 13-16 %): these kernels are bound by per-tile latencies at 4 CTAs per SM, not by MUFU or the tensor pipe (DESIGN.md section 4, profiles/r2b_summary.md section 4)"},
         "cpu_baseline": cpu,
     }
     sys.stdout.flush()
