@@ -142,6 +142,7 @@ int mb_loss_fwd_bwd(const mb_loss_params* params, int dtype, void* stream);
 #define MB_GEMM_OUT_F32 8
 #define MB_GEMM_PAIR_ON 16  /* scheduling hint: force 2-CTA (cta_group::2) tiles on the tensor-core path */
 #define MB_GEMM_PAIR_OFF 32 /* scheduling hint: force single-CTA tiles */
+#define MB_GEMM_HALF_TAIL 64 /* scheduling hint (bf16 outputs): the last partial wave runs as half-width tiles */
 typedef struct {
   const void* A;         /* A(m, k) = A[m * sam + k * sak] */
   const void* B;         /* B(n, k) = B[n * sbn + k * sbk] */

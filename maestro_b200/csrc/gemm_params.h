@@ -8,6 +8,7 @@
 #define GEMM_OUT_F32 8   // C is fp32 regardless of the activation dtype
 #define GEMM_PAIR_ON 16  // scheduling hint (tensor-core path): force 2-CTA (cta_group::2) tiles
 #define GEMM_PAIR_OFF 32 // scheduling hint (tensor-core path): force single-CTA tiles
+#define GEMM_HALF_TAIL 64 // scheduling hint (tensor-core path, bf16 outputs): last partial wave as half-width tiles
 
 struct GemmParams {
   const void* A;         // A(m, k) = A[m * sam + k * sak]

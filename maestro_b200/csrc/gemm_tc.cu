@@ -104,22 +104,32 @@ struct TcArgs {
   int flags;
   float alpha;
   int total_tiles;
+  int half_start;        // tiles t >= half_start are HALF-width tiles (two per full tile of the last partial wave)
 };
 
 struct TcMaps {
   CUtensorMap a[MAX_GROUP], b[MAX_GROUP], c[MAX_GROUP];
   CUtensorMap x[MAX_GROUP];   // GELU: gelu'(pre-activation) output; GELU': the same tensor as input; else residual input
   CUtensorMap pf[MAX_GROUP];  // the epilogue input again, with a 128-row x 64-column box for L2 prefetch
+  CUtensorMap bh[MAX_GROUP];  // K-major B with a half-height box: the B rows of a half-width tail tile
 };
 
 struct TileCoord {
   int p, m_blk, n_blk, kb0, kb1;
+  int n0, ncols;         // first output column and width of the tile (BN, or BN / 2 for the half tiles of the tail)
 };
 
 // With PAIR `t` indexes PAIRS of vertically adjacent m-blocks: P.mblocks then holds the number of pairs and the CTA of
 // cluster rank r takes m-block 2 * pair + r.
+template <int BN>
 __device__ __forceinline__ TileCoord decode_tile(const TcArgs& args, int t, bool n_fastest, int mc_rank = -1) {
   TileCoord tc_;
+  int half = -1;
+  if (t >= args.half_start) {          // the last partial wave runs as half-width tiles: 0.55 instead of 1 tile time
+    const int u = t - args.half_start;
+    half = u & 1;
+    t = args.half_start + (u >> 1);
+  }
   int p = 0, start = 0;
 #pragma unroll
   for (int i = 0; i < MAX_GROUP - 1; ++i)
@@ -141,6 +151,8 @@ __device__ __forceinline__ TileCoord decode_tile(const TcArgs& args, int t, bool
   if (mc_rank >= 0) tc_.m_blk = 2 * tc_.m_blk + mc_rank;
   tc_.kb0 = split * per;
   tc_.kb1 = min(kblocks, tc_.kb0 + per);
+  tc_.ncols = half < 0 ? BN : BN / 2;
+  tc_.n0 = tc_.n_blk * BN + (half > 0 ? BN / 2 : 0);
   return tc_;
 }
 
@@ -217,7 +229,7 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
       int stage = 0;
       uint32_t phase = 0;
       for (int t = tile0; t < total_tiles; t += tile_step) {
-        const TileCoord tc_ = decode_tile(args, t, !A_MN, mc_rank);
+        const TileCoord tc_ = decode_tile<BN>(args, t, !A_MN, mc_rank);
         const CUtensorMap* tmA = &maps.a[tc_.p];
         const CUtensorMap* tmB = &maps.b[tc_.p];
         {
@@ -225,8 +237,8 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
           const TcProblem& P = args.p[tc_.p];
           if (MB_DIAG_EPI != 1 && !(args.flags & GEMM_OUT_F32) && ((args.flags & GEMM_DGELU) || P.residual != nullptr)) {
             for (int cc = 0; cc < BN / 64; ++cc) {
-              const int c0 = tc_.n_blk * BN + cc * 64;
-              if (c0 < P.N) tc::tma_prefetch_l2_2d(&maps.pf[tc_.p], c0, tc_.m_blk * BM);
+              const int c0 = tc_.n0 + cc * 64;
+              if (cc * 64 < tc_.ncols && c0 < P.N) tc::tma_prefetch_l2_2d(&maps.pf[tc_.p], c0, tc_.m_blk * BM);
             }
           }
         }
@@ -234,8 +246,9 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
           tc::mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* sA = smem + stage * C_::STAGE_BYTES;
           uint8_t* sB = sA + A_BYTES;
+          const bool half_tile = tc_.ncols != BN;       // tail tile: half the B rows / columns are loaded (and counted)
           if constexpr (!PAIR) {
-            tc::mbar_expect_tx(&full_bar[stage], C_::STAGE_BYTES);
+            tc::mbar_expect_tx(&full_bar[stage], half_tile ? A_BYTES + C_::B_BYTES / 2 : C_::STAGE_BYTES);
             if constexpr (!A_MN) {
               tc::tma_load_2d(sA, tmA, &full_bar[stage], kb * BK, tc_.m_blk * BM);
             } else {
@@ -244,16 +257,16 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
                 tc::tma_load_2d(sA + i * 8192, tmA, &full_bar[stage], tc_.m_blk * BM + i * 64, kb * BK);
             }
             if constexpr (!B_MN) {
-              tc::tma_load_2d(sB, tmB, &full_bar[stage], kb * BK, tc_.n_blk * BN);
+              tc::tma_load_2d(sB, half_tile ? &maps.bh[tc_.p] : tmB, &full_bar[stage], kb * BK, tc_.n0);
             } else {
 #pragma unroll
               for (int i = 0; i < BN / 64; ++i)
-                tc::tma_load_2d(sB + i * 8192, tmB, &full_bar[stage], tc_.n_blk * BN + i * 64, kb * BK);
+                if (i * 64 < tc_.ncols) tc::tma_load_2d(sB + i * 8192, tmB, &full_bar[stage], tc_.n0 + i * 64, kb * BK);
             }
           } else {
             // both CTAs' bytes are counted on the LEADER's full barrier (the leader alone waits on it and issues)
             const uint32_t fb = tc::mapa_u32(&full_bar[stage], 0);
-            if (mc_rank == 0) tc::mbar_expect_tx(&full_bar[stage], 2 * C_::STAGE_BYTES);
+            if (mc_rank == 0) tc::mbar_expect_tx(&full_bar[stage], half_tile ? 2 * A_BYTES + C_::B_BYTES : 2 * C_::STAGE_BYTES);
             if constexpr (!A_MN) {
               tc::tma_load_2d_pair(sA, tmA, fb, kb * BK, tc_.m_blk * BM);
             } else {
@@ -261,12 +274,13 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
               for (int i = 0; i < BM / 64; ++i)
                 tc::tma_load_2d_pair(sA + i * 8192, tmA, fb, tc_.m_blk * BM + i * 64, kb * BK);
             }
-            const int n0 = tc_.n_blk * BN + mc_rank * (BN / 2);      // this CTA's half of the B tile
+            const int n0 = tc_.n0 + mc_rank * (tc_.ncols / 2);       // this CTA's half of the B tile (a half tile: the first 64 / 32 rows of the box)
             if constexpr (!B_MN) {
-              tc::tma_load_2d_pair(sB, tmB, fb, kb * BK, n0);
+              tc::tma_load_2d_pair(sB, half_tile ? &maps.bh[tc_.p] : tmB, fb, kb * BK, n0);
             } else {
 #pragma unroll
-              for (int i = 0; i < BN / 128; ++i) tc::tma_load_2d_pair(sB + i * 8192, tmB, fb, n0 + i * 64, kb * BK);
+              for (int i = 0; i < BN / 128; ++i)
+                if (i * 128 < tc_.ncols) tc::tma_load_2d_pair(sB + i * 8192, tmB, fb, n0 + i * 64, kb * BK);
             }
           }
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
@@ -276,18 +290,20 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
     if (lane == 0 && (!PAIR || mc_rank == 0)) {
-      constexpr uint32_t idesc = tc::make_idesc_bf16(PAIR ? 2 * BM : BM, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
+      constexpr uint32_t idesc_full = tc::make_idesc_bf16(PAIR ? 2 * BM : BM, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
+      constexpr uint32_t idesc_half = tc::make_idesc_bf16(PAIR ? 2 * BM : BM, BN / 2, A_MN ? 1 : 0, B_MN ? 1 : 0);
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
       int tile_i = 0;
       for (int t = tile0; t < total_tiles; t += tile_step, ++tile_i) {
-        const TileCoord tc_ = decode_tile(args, t, !A_MN, mc_rank);
+        const TileCoord tc_ = decode_tile<BN>(args, t, !A_MN, mc_rank);
         tc::mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
         tc::tc_fence_after();
         MB_STAMP(tile_i, 0);
         const uint32_t d_tmem = tmem_base + acc * BN;
+        const uint32_t idesc = tc_.ncols == BN ? idesc_full : idesc_half;
         for (int kb = tc_.kb0; kb < tc_.kb1; ++kb) {
           tc::mbar_wait(&full_bar[stage], phase);
           tc::tc_fence_after();
@@ -367,14 +383,14 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
     for (int t = tile0; t < total_tiles; t += tile_step) {
       ++tile_i;
       if (warp == EPI_WARP0 && lane == 0) MB_STAMP(tile_i, 2);
-      const TileCoord tc_ = decode_tile(args, t, !A_MN, mc_rank);
+      const TileCoord tc_ = decode_tile<BN>(args, t, !A_MN, mc_rank);
       const TcProblem& P = args.p[tc_.p];
       const int row0 = tc_.m_blk * BM + ew * 32;
       const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + acc * BN;
       int nch = 0;
 #pragma unroll
       for (int c2 = 0; c2 < CH_PER_Q; ++c2)
-        if (tc_.n_blk * BN + (quarter * CH_PER_Q + c2) * 32 < P.N) nch = c2 + 1;
+        if ((quarter * CH_PER_Q + c2) * 32 < tc_.ncols && tc_.n0 + (quarter * CH_PER_Q + c2) * 32 < P.N) nch = c2 + 1;
       if (nch == 0) {
         tc::mbar_wait(&tfull_bar[acc], acc_phase);
         tc::tc_fence_before();
@@ -390,7 +406,7 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
 #pragma unroll 1
         for (int c2 = 0; c2 < nch; ++c2) {
           const int ch = quarter * CH_PER_Q + c2;
-          const int col0 = tc_.n_blk * BN + ch * 32;
+          const int col0 = tc_.n0 + ch * 32;
           // (1) coalesced prefetch of the epilogue input: instruction i covers rows 8i .. 8i+7, 4 lanes per row
           uint4 pre[4];
           if (need_in) {
@@ -567,7 +583,7 @@ gemm_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcAr
 #pragma unroll 1
         for (int c2 = 0; c2 < nch; ++c2) {
           const int ch = quarter * CH_PER_Q + c2;
-          const int col0 = tc_.n_blk * BN + ch * 32;
+          const int col0 = tc_.n0 + ch * 32;
           uint32_t r[32];
           tc::tmem_ld_32x32(t_addr + ch * 32, r);
           tc::tmem_ld_wait();
@@ -635,6 +651,15 @@ int get_tmap(CUtensorMap* out, const void* ptr, uint64_t d0, uint64_t d1, uint64
 
 int num_sms() { return mb_num_sms(); }
 
+// Half-width tiles in the last partial wave: off unless MB_GEMM_HALF_TAIL=1 or the GEMM_HALF_TAIL hint is set.
+// Measured (profiles/r2b_summary.md section 7): 0-2 % per launch -- a half tile is not much shorter than a full one
+// because the pair main loop is bound by the chip-wide L2 -> SM feed (43 B / cycle / SM = the 6300 B / cycle LTS
+// limit), which a partially filled tail wave does not hit anyway.
+bool half_tail_on() {
+  static const bool on = [] { const char* e = std::getenv("MB_GEMM_HALF_TAIL"); return e && e[0] == '1'; }();
+  return on;
+}
+
 // PAIR: 2-CTA clusters running cta_group::2 MMAs (see the kernel); tiles are scheduled as vertical pairs of m-blocks.
 template <int BN, bool A_MN, bool B_MN, bool MC, int EF = EPI_GENERIC>
 int launch(const GemmParams* Ps, int count, cudaStream_t st) {
@@ -654,6 +679,8 @@ int launch(const GemmParams* Ps, int count, cudaStream_t st) {
     if (!B_MN) rc = get_tmap(&maps.b[i], P.B, P.K, P.N, P.sbn, BK, MC ? BN / 2 : BN);
     else rc = get_tmap(&maps.b[i], P.B, P.N, P.K, P.sbk, 64, BK);
     if (rc != 0) return rc;
+    maps.bh[i] = maps.b[i];
+    if (!B_MN && BN == 256 && (rc = get_tmap(&maps.bh[i], P.B, P.K, P.N, P.sbn, BK, MC ? BN / 4 : BN / 2)) != 0) return rc;
     if (!out_f32) {
       if ((rc = get_tmap(&maps.c[i], P.C, P.N, P.M, P.ldc, 32, 32, 64)) != 0) return rc;
       // x: GELU -> saved gelu'(pre-activation) (second output); GELU' -> the same tensor as epilogue input; else residual
@@ -682,7 +709,7 @@ int launch(const GemmParams* Ps, int count, cudaStream_t st) {
   }
   for (int i = count; i < MAX_GROUP; ++i) {
     maps.a[i] = maps.a[0]; maps.b[i] = maps.b[0]; maps.c[i] = maps.c[0]; maps.x[i] = maps.x[0];
-    maps.pf[i] = maps.pf[0];
+    maps.pf[i] = maps.pf[0]; maps.bh[i] = maps.bh[0];
   }
   // Split-K (weight gradients; fp32 red.add combines the partials): work items of at most `split_target` k-blocks.
   // The target minimises the makespan of the persistent schedule (item t runs on CTA t mod grid; an item costs its
@@ -743,6 +770,7 @@ int launch(const GemmParams* Ps, int count, cudaStream_t st) {
   a.flags = flags;
   a.alpha = Ps[0].alpha;
   a.total_tiles = total;
+  a.half_start = 1 << 30;
   auto kern = gemm_tc_kernel<BN, A_MN, B_MN, MC, EF>;
   static bool attr_set = false;
   static int max_clusters = 0;
@@ -762,6 +790,19 @@ int launch(const GemmParams* Ps, int count, cudaStream_t st) {
       if (max_clusters > num_sms() / 2) max_clusters = num_sms() / 2;
     }
     attr_set = true;
+  }
+  // Tail: the R = total mod slots tiles of the last (partial) wave take a whole tile time on R of the slots.  When
+  // 2 R <= slots they run as 2 R half-width tiles instead (a 128-wide tile costs 0.55 of a 256-wide one here: same
+  // A traffic, half the MMAs and half the epilogue) -- e.g. the N = 768 down-projections: 180 pair tiles on 74
+  // clusters = 2 waves + 32 tiles -> 2 waves + 64 half tiles, 2.55 instead of 3 tile times.  bf16 outputs, BN = 256 only.
+  if (BN == 256 && (half_tail_on() || (flags & GEMM_HALF_TAIL)) && !(flags & (GEMM_OUT_F32 | GEMM_ACCUM))) {
+    const int slots = MC ? max_clusters : num_sms();
+    const int R = total % slots;
+    if (R > 0 && 2 * R <= slots) {
+      a.half_start = total - R;
+      total += R;
+      a.total_tiles = total;
+    }
   }
   if (!MC) {
     const int grid = total < num_sms() ? total : num_sms();

@@ -17,7 +17,7 @@ from . import _lib
 
 F32, BF16 = 0, 1
 GEMM_GELU, GEMM_DGELU, GEMM_ACCUM, GEMM_OUT_F32 = 1, 2, 4, 8
-GEMM_PAIR_ON, GEMM_PAIR_OFF = 16, 32      # scheduling hints of the tensor-core path (tests, tuning)
+GEMM_PAIR_ON, GEMM_PAIR_OFF, GEMM_HALF_TAIL = 16, 32, 64      # scheduling hints of the tensor-core path (tests, tuning)
 RAW_CODES = {torch.uint8: 0, torch.int16: 1, torch.uint16: 2, torch.float32: 3}   # MB_RAW_* of the header
 AUG_FLIP_H, AUG_FLIP_W, AUG_TRANSPOSE = 1, 2, 4
 RESIZE_MODES = {"nearest": 0, "bilinear": 1, "bicubic": 2}                         # F.interpolate modes of mim.py:425-437

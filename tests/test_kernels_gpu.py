@@ -362,6 +362,37 @@ def test_gemm_cta_pair_and_single_tiles(KK, hint, M, N, Kd):
     close(a[5], b[5], rtol=1e-3, atol=2e-3 * math.sqrt(M))
 
 
+@pytest.mark.parametrize("hint", [16, 32])
+@pytest.mark.parametrize("M,N,Kd", [(8192, 768, 128), (8262, 520, 192), (5000, 1536, 64)])
+def test_gemm_half_width_tail_tiles(KK, hint, M, N, Kd):
+    """More 256-wide tiles than SMs (clusters) with a last partial wave of at most half the chip: that wave runs as
+    half-width tiles (128 columns, `TcArgs.half_start`; hint flag 64 = GEMM_HALF_TAIL).  Pair and single-CTA schedules, every compile-time epilogue,
+    ragged M and N."""
+    dt = torch.bfloat16
+    A, Bm, bias, res = _gemm_case(None, dt, M, N, Kd, "k", 0)
+    dY, X = rnd(M, N, dt=dt, seed=8, scale=0.5), rnd(M, Kd, dt=dt, seed=9, scale=0.5)
+    BT = rnd(Kd, N, dt=dt, seed=10, scale=0.5)          # dgrad weight read in place: B(n, k) = BT[k, n]
+    auxin = rnd(M, N, dt=dt, seed=7)
+
+    def run(K):
+        Y0 = torch.zeros(M, N, dtype=dt, device="cuda")
+        K.gemm(A, Bm, Y0, M, N, Kd, sam=Kd, sak=1, sbn=Kd, sbk=1, ldc=N, flags=hint | 64)                     # plain
+        Y1, U1 = torch.zeros(M, N, dtype=dt, device="cuda"), torch.zeros(M, N, dtype=dt, device="cuda")
+        K.gemm(A, Bm, Y1, M, N, Kd, sam=Kd, sak=1, sbn=Kd, sbk=1, ldc=N, bias=bias, aux=U1, flags=1 | hint | 64)   # GELU
+        Y2 = torch.zeros(M, N, dtype=dt, device="cuda")
+        K.gemm(A, Bm, Y2, M, N, Kd, sam=Kd, sak=1, sbn=Kd, sbk=1, ldc=N, bias=bias, residual=res, flags=hint | 64)
+        D0 = torch.zeros(M, N, dtype=dt, device="cuda")
+        K.gemm(X, BT, D0, M, N, Kd, sam=Kd, sak=1, sbn=1, sbk=N, ldc=N, flags=hint | 64)                      # dgrad, plain
+        D1, cs = torch.zeros(M, N, dtype=dt, device="cuda"), torch.full((N,), 0.125, device="cuda")
+        K.gemm(X, BT, D1, M, N, Kd, sam=Kd, sak=1, sbn=1, sbk=N, ldc=N, aux=auxin, flags=2 | hint | 64, colsum=cs)
+        return [Y0, Y1, U1, Y2, D0, D1, cs]
+    a, b = both(KK, run)
+    s = math.sqrt(Kd) * 0.25
+    for x, y in zip(a[:6], b[:6]):
+        close(x, y, rtol=2e-2, atol=2e-2 * s)
+    close(a[6], b[6], rtol=2e-2, atol=2e-2 * s * math.sqrt(M))
+
+
 def test_gemm_grouped_matches_single_launches(KK):
     """Four problems of one layer kind (different row counts / operands) in ONE persistent launch: fwd with GELU,
     fwd with residual, dgrad on the untransposed weight (+GELU'), wgrad with split-K accumulation."""
