@@ -7,8 +7,9 @@ namespace {
 // buffer j & 1 (P^T, dS^T) and Q / dO stage j % NS.  While the threads run the exp / dS pass of half j, the tensor
 // pipe works on S^T / dP^T of half j + 1 (issued one pass earlier) and on the gradient MMAs of half j - 1, so neither
 // the MMA latency nor the single-thread issue sequence sits between two passes.  Warps 0-3 (thread = key row = TMEM
-// lane) run the passes; one lane of warp 4 issues every TMA load and MMA, driven by mbarriers only.
-constexpr int DKDV_THREADS = 128 * NH + 32;   // NH warps per TMEM lane quarter split the columns of every pass (attn_bwd_tc.cu)
+// lane) run the passes; one lane each of warps 4 / 5 / 6 issues the score MMAs / the gradient MMAs / the TMA loads,
+// driven by mbarriers only.
+constexpr int DKDV_THREADS = 128 * NH + 96;   // compute warps (NH per TMEM lane quarter) + three control warps
 
 template <int DH>
 __global__ void __launch_bounds__(DKDV_THREADS) attn_bwd_dkdv_kernel(const __grid_constant__ BwdGroup grp) {
@@ -107,11 +108,15 @@ __global__ void __launch_bounds__(DKDV_THREADS) attn_bwd_dkdv_kernel(const __gri
     tc::umma_commit(&bar_o[j & 1]);
   };
 
-  if (warp == BWD_CTRL_WARP) {
-    // ===================== control lane: TMA loads + every MMA =====================
-    if (tid == 128 * NH) {
-      int s_stage = 0, l_stage = 0, g_stage = 0, l_next = 0;
-      uint32_t s_par = 0;
+  if (warp >= BWD_CTRL_WARP) {
+    // ===================== three control lanes, one per warp, driven by mbarriers only =====================
+    // The per-pass timeline (profiles/r2b_attn_timeline.txt) showed ONE control lane as the bottleneck of the kernel:
+    // ~850 cycles to issue the 6 small MMAs of a pass (descriptor arithmetic + tcgen05.mma + commits from a single
+    // thread) + ~300 for the loads, 1565 cycles per pass in total, while the compute warps worked ~450 and waited the
+    // rest.  The three jobs are independent: warp +0 issues S^T / dP^T, warp +1 the gradient MMAs, warp +2 the TMA loads.
+    if (tid == 128 * NH + 64) {
+      // ---- loader: K / V once, then the Q / dO ring (a stage is free when the gradient MMAs that read it are done)
+      int l_stage = 0, l_next = 0;
       tc::mbar_expect_tx(bar_kv, 2 * C_::ROW_TILE);
       tc::tma_load_3d(smem + OFF_K, &tm_qkv128, bar_kv, inner + h * DH, rt * BR, b);
       tc::tma_load_3d(smem + OFF_V, &tm_qkv128, bar_kv, 2 * inner + h * DH, rt * BR, b);
@@ -119,30 +124,36 @@ __global__ void __launch_bounds__(DKDV_THREADS) attn_bwd_dkdv_kernel(const __gri
         load_q(l_next, l_stage);
         if (++l_stage == NS) l_stage = 0;
       }
+      for (int j = 1; l_next < n_sub; ++j) {                 // stage (j - 1) % NS: read last by the gradient MMAs of half j - 1
+        tc::mbar_wait(&bar_o[(j - 1) & 1], ((j - 1) >> 1) & 1);
+        load_q(l_next, l_stage);
+        ++l_next;
+        if (++l_stage == NS) l_stage = 0;
+      }
+    } else if (tid == 128 * NH) {
+      // ---- S^T / dP^T issuer: half j + 2 goes into the TMEM buffer pass j has just drained
+      int s_stage = 0;
+      uint32_t s_par = 0;
       tc::mbar_wait(bar_kv, 0);
-      for (int j = 0; j < 2 && j < n_sub; ++j) {
+      for (int j = 0; j < n_sub; ++j) {
+        if (j >= 2) tc::mbar_wait(&bar_p[j & 1], ((j - 2) >> 1) & 1);   // pass j - 2 has read buffer j & 1
         tc::mbar_wait(&bar_q[s_stage], s_par);
         tc::tc_fence_after();
+        MB_ASTAMP(j, 0);
         issue_s(j, s_stage);
+        MB_ASTAMP(j, 1);
         if (++s_stage == NS) { s_stage = 0; s_par ^= 1; }
       }
+    } else if (tid == 128 * NH + 32) {
+      // ---- gradient issuer: dV += P^T dO, dK += dS^T Q of half j once its operands are in shared memory
+      int g_stage = 0;
       for (int j = 0; j < n_sub; ++j) {
-        tc::mbar_wait(&bar_p[j & 1], (j >> 1) & 1);          // P^T / dS^T of half j are in shared memory
+        tc::mbar_wait(&bar_p[j & 1], (j >> 1) & 1);
         tc::tc_fence_after();
+        MB_ASTAMP(j, 2);
         issue_grads(j, g_stage);
+        MB_ASTAMP(j, 3);
         if (++g_stage == NS) g_stage = 0;
-        if (j + 2 < n_sub) {               // S^T / dP^T of half j + 2 into the TMEM buffer pass j has just drained
-          tc::mbar_wait(&bar_q[s_stage], s_par);
-          tc::tc_fence_after();
-          issue_s(j + 2, s_stage);
-          if (++s_stage == NS) { s_stage = 0; s_par ^= 1; }
-        }
-        if (j >= 1 && l_next < n_sub) {    // the gradient MMAs of half j - 1 (issued a pass ago) free its Q / dO stage
-          tc::mbar_wait(&bar_o[(j - 1) & 1], ((j - 1) >> 1) & 1);
-          load_q(l_next, l_stage);
-          ++l_next;
-          if (++l_stage == NS) l_stage = 0;
-        }
       }
     }
   } else {
@@ -184,9 +195,12 @@ __global__ void __launch_bounds__(DKDV_THREADS) attn_bwd_dkdv_kernel(const __gri
       lsv[q4] = lds_f4(st + (half * CW + q4 * 4) * 4);
       dsv[q4] = lds_f4(st + (SUB + half * CW + q4 * 4) * 4);
     }
+    if (tid == 0) MB_ASTAMP(j, 4);
     tc::mbar_wait(&bar_s[bufi], (j >> 1) & 1);
+    if (tid == 0) MB_ASTAMP(j, 5);
     if (j >= 2) tc::mbar_wait(&bar_o[bufi], ((j - 2) >> 1) & 1);   // gradient MMAs of half j - 2 have read `bufi`
     tc::tc_fence_after();
+    if (tid == 0) MB_ASTAMP(j, 6);
     // P^T and dS^T.  No masks: queries past N are zero rows of Q and dO (TMA zero fill), so their columns multiply
     // zero rows in dV += P^T dO and dK += dS^T Q; key rows past N are never stored.  st[] holds finite values there.
     {
@@ -223,6 +237,7 @@ __global__ void __launch_bounds__(DKDV_THREADS) attn_bwd_dkdv_kernel(const __gri
     tc::fence_proxy_async();
     tc::tc_fence_before();
     tc::mbar_arrive(&bar_p[bufi]);
+    if (tid == 0) MB_ASTAMP(j, 7);
     asm volatile("bar.sync 1, %0;" ::"n"(128 * NH) : "memory");   // next half's statistics are visible to the compute warps
   }
   tc::mbar_wait(&bar_o[(n_sub - 1) & 1], ((n_sub - 1) >> 1) & 1);   // a commit covers every MMA issued before it

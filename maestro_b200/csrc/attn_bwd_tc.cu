@@ -20,6 +20,19 @@ struct mb_attn_problem {     // mirror of include/maestro_b200.h
   int Bn, N;
 };
 
+#ifndef MB_DIAG_TIMING
+#define MB_DIAG_TIMING 0
+#endif
+#if MB_DIAG_TIMING   // diagnostic builds: CTA 0 of the dK / dV kernel stamps clock64() per pass (tools/_diag/attn_timeline.py)
+__device__ unsigned long long g_attn_stamps[128 * 8];
+#define MB_ASTAMP(pass_i, slot) do { if (blockIdx.x == 0 && (pass_i) < 128) g_attn_stamps[(pass_i) * 8 + (slot)] = clock64(); } while (0)
+extern "C" int mb_diag_attn_timing(unsigned long long* host, int n) {
+  return static_cast<int>(cudaMemcpyFromSymbol(host, g_attn_stamps, sizeof(unsigned long long) * (n < 1024 ? n : 1024)));
+}
+#else
+#define MB_ASTAMP(pass_i, slot) do { } while (0)
+#endif
+
 namespace {
 
 constexpr int BR = 128;  // rows owned by the CTA (TMEM lanes)
@@ -91,8 +104,8 @@ __device__ __forceinline__ float4 lds_f4(uint32_t addr) {
 #define MB_ATTN_BWD_NH 1
 #endif
 constexpr int NH = MB_ATTN_BWD_NH;
-constexpr int BWD_CTRL_WARP = 4 * NH;          // its first lane issues every TMA load and MMA
-constexpr int DQ_THREADS = 128 * NH + 32;
+constexpr int BWD_CTRL_WARP = 4 * NH;          // first of three control warps: score MMAs / gradient MMAs / TMA loads
+constexpr int DQ_THREADS = 128 * NH + 96;   // + three control warps
 
 template <int DH>
 __global__ void __launch_bounds__(DQ_THREADS) attn_bwd_dq_kernel(const __grid_constant__ BwdGroup grp) {
@@ -182,11 +195,10 @@ __global__ void __launch_bounds__(DQ_THREADS) attn_bwd_dq_kernel(const __grid_co
     tc::umma_commit(&bar_o[j & 1]);
   };
 
-  if (warp == BWD_CTRL_WARP) {
-    // ===================== control lane: TMA loads + every MMA =====================
-    if (tid == 128 * NH) {
-      int s_stage = 0, l_stage = 0, g_stage = 0, l_next = 0;
-      uint32_t s_par = 0;
+  if (warp >= BWD_CTRL_WARP) {
+    // ===================== three control lanes (see attn_bwd_dkdv.cuh): S / dP issuer, dQ issuer, loader =====================
+    if (tid == 128 * NH + 64) {
+      int l_stage = 0, l_next = 0;
       tc::mbar_expect_tx(bar_q, 2 * C_::ROW_TILE);
       tc::tma_load_3d(smem + OFF_Q, &tm_qkv128, bar_q, h * DH, rt * BR, b);
       tc::tma_load_3d(smem + OFF_DO, &tm_do128, bar_q, h * DH, rt * BR, b);
@@ -194,30 +206,30 @@ __global__ void __launch_bounds__(DQ_THREADS) attn_bwd_dq_kernel(const __grid_co
         load_kv(l_next, l_stage);
         if (++l_stage == NS) l_stage = 0;
       }
+      for (int j = 1; l_next < n_sub; ++j) {                 // the dQ MMA of half j - 1 frees its K / V stage
+        tc::mbar_wait(&bar_o[(j - 1) & 1], ((j - 1) >> 1) & 1);
+        load_kv(l_next, l_stage);
+        ++l_next;
+        if (++l_stage == NS) l_stage = 0;
+      }
+    } else if (tid == 128 * NH) {
+      int s_stage = 0;
+      uint32_t s_par = 0;
       tc::mbar_wait(bar_q, 0);
-      for (int j = 0; j < 2 && j < n_sub; ++j) {
+      for (int j = 0; j < n_sub; ++j) {
+        if (j >= 2) tc::mbar_wait(&bar_p[j & 1], ((j - 2) >> 1) & 1);   // pass j - 2 has read buffer j & 1
         tc::mbar_wait(&bar_kv[s_stage], s_par);
         tc::tc_fence_after();
         issue_s_dp(j, s_stage);
         if (++s_stage == NS) { s_stage = 0; s_par ^= 1; }
       }
+    } else if (tid == 128 * NH + 32) {
+      int g_stage = 0;
       for (int j = 0; j < n_sub; ++j) {
         tc::mbar_wait(&bar_p[j & 1], (j >> 1) & 1);          // dS of half j is in shared memory
         tc::tc_fence_after();
         issue_dq(j, g_stage);
         if (++g_stage == NS) g_stage = 0;
-        if (j + 2 < n_sub) {               // S / dP of half j + 2 into the TMEM buffer pass j has just drained
-          tc::mbar_wait(&bar_kv[s_stage], s_par);
-          tc::tc_fence_after();
-          issue_s_dp(j + 2, s_stage);
-          if (++s_stage == NS) { s_stage = 0; s_par ^= 1; }
-        }
-        if (j >= 1 && l_next < n_sub) {    // the dQ MMA of half j - 1 (issued a pass ago) frees its K / V stage
-          tc::mbar_wait(&bar_o[(j - 1) & 1], ((j - 1) >> 1) & 1);
-          load_kv(l_next, l_stage);
-          ++l_next;
-          if (++l_stage == NS) l_stage = 0;
-        }
       }
     }
   } else {
